@@ -1,0 +1,787 @@
+/*
+ * gjd_api.cu — host runtime behind the C ABI of include/gjd.h: context, worker pool, pinned staging,
+ * device arenas, sub-batch pipeline.  Host C++ only (no kernels here); compiled by nvcc for the
+ * CUDA runtime headers.
+ *
+ * Replaces the per-image extract()/allocate()/clean() storm of the reference
+ * (cuda-decoder/src/parser.cu:324-471, 684-700; ~26 CUDA API calls per image) with O(1) API calls
+ * per sub-batch: one staging copy, one descriptor upload, one pipeline of launches, merged D2H copies.
+ */
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <condition_variable>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <functional>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/gjd.h"
+#include "gjd_kernels.h"
+#include "gjd_parse.h"
+#include "gjd_types.h"
+
+#define GJD_VERSION_STR "0.1"
+#define GJD_STR2(x) #x
+#define GJD_STR(x) GJD_STR2(x)
+
+namespace {
+
+/* ---------------------------------------------------------------- worker pool --------- */
+
+class Pool {
+public:
+    explicit Pool(int n) {
+        for (int i = 0; i < n; i++) th_.emplace_back([this] { loop(); });
+    }
+    ~Pool() {
+        {
+            std::lock_guard<std::mutex> l(m_);
+            stop_ = true;
+        }
+        cv_.notify_all();
+        for (auto& t : th_) t.join();
+    }
+    /* fn(i) for i in [0,n), dynamically chunked; the caller participates. */
+    void parallel_for(size_t n, size_t chunk, const std::function<void(size_t)>& fn) {
+        if (n == 0) return;
+        if (th_.empty() || n <= chunk) {
+            for (size_t i = 0; i < n; i++) fn(i);
+            return;
+        }
+        {
+            std::lock_guard<std::mutex> l(m_);
+            fn_ = &fn; n_ = n; chunk_ = chunk; next_.store(0); pending_ = (int)th_.size(); gen_++;
+        }
+        cv_.notify_all();
+        work();
+        std::unique_lock<std::mutex> l(m_);
+        done_.wait(l, [this] { return pending_ == 0; });
+        fn_ = nullptr;
+    }
+    int size() const { return (int)th_.size() + 1; }
+
+private:
+    void work() {
+        for (;;) {
+            size_t b = next_.fetch_add(chunk_);
+            if (b >= n_) break;
+            size_t e = std::min(n_, b + chunk_);
+            for (size_t i = b; i < e; i++) (*fn_)(i);
+        }
+    }
+    void loop() {
+        uint64_t seen = 0;
+        for (;;) {
+            {
+                std::unique_lock<std::mutex> l(m_);
+                cv_.wait(l, [&] { return stop_ || gen_ != seen; });
+                if (stop_) return;
+                seen = gen_;
+            }
+            work();
+            {
+                std::lock_guard<std::mutex> l(m_);
+                if (--pending_ == 0) done_.notify_one();
+            }
+        }
+    }
+    std::vector<std::thread> th_;
+    std::mutex m_;
+    std::condition_variable cv_, done_;
+    const std::function<void(size_t)>* fn_ = nullptr;
+    size_t n_ = 0, chunk_ = 1;
+    std::atomic<size_t> next_{0};
+    int pending_ = 0;
+    uint64_t gen_ = 0;
+    bool stop_ = false;
+};
+
+/* ---------------------------------------------------------------- buffers ------------- */
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 8 + 4096;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) { e = cudaMalloc(&p, bytes); want = bytes; }
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+struct PinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 8 + 4096;
+        cudaError_t e = cudaHostAlloc(&p, want, cudaHostAllocDefault);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct ItemGeom {
+    int32_t status = GJD_OK;   /* host-side status (parse / unstuff) */
+    int32_t width = 0, height = 0;
+    size_t out_bytes = 0;      /* bytes of the image's output region */
+    size_t pitch = 0, pstride = 0;
+};
+
+}  // namespace
+
+/* ---------------------------------------------------------------- batch (one slot) ---- */
+
+struct gjd_batch {
+    int32_t n = 0;
+    std::vector<GjdParsed> parsed;
+    std::vector<ItemGeom> geom;
+    std::vector<GjdImage> imgs;      /* device descriptors, only for items with status OK */
+    std::vector<int32_t> img_of;     /* item -> index into imgs, or -1 */
+    std::vector<GjdDhtSet> dhts;
+    std::vector<GjdQuantSet> quants;
+    PinBuf h_scan, h_meta, h_status;
+    DevBuf d_scan, d_meta, d_luts, d_sinfo, d_seqmaps, d_coef, d_dcdiff, d_tilebase, d_tileimg, d_rgb, d_status;
+    GjdDevBatch view{};
+    GjdStageEvents ev{};
+    bool ev_ok = false;
+    cudaStream_t stream = nullptr;
+    size_t scan_alloc = 0, rgb_alloc = 0;
+    uint64_t pixels = 0, padded_pixels = 0, scan_bytes = 0, subseqs = 0;
+    int launches = 0;
+    bool ran = false;
+
+    void release() {
+        h_scan.release(); h_meta.release(); h_status.release();
+        d_scan.release(); d_meta.release(); d_luts.release(); d_sinfo.release(); d_seqmaps.release();
+        d_coef.release(); d_dcdiff.release(); d_tilebase.release(); d_tileimg.release(); d_rgb.release();
+        d_status.release();
+        if (ev_ok) for (auto& e : ev.e) cudaEventDestroy(e);
+        ev_ok = false;
+        if (stream) cudaStreamDestroy(stream);
+        stream = nullptr;
+    }
+};
+
+struct gjd_ctx {
+    int device = 0;
+    size_t scratch = 0;
+    Pool* pool = nullptr;
+    gjd_batch slot[2];
+    gjd_batch* last = nullptr;     /* batch whose stage events gjd_stage_times reports */
+    std::string cuda_err;
+    int transform_variant = 0;
+};
+
+namespace {
+
+int cuda_fail(gjd_ctx* ctx, cudaError_t e, const char* what) {
+    if (ctx) ctx->cuda_err = std::string(what) + ": " + cudaGetErrorString(e);
+    return e == cudaErrorMemoryAllocation ? GJD_E_NOMEM : GJD_E_CUDA;
+}
+#define GJD_TRY(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return cuda_fail(ctx, e_, #call); } while (0)
+
+int batch_init(gjd_ctx* ctx, gjd_batch* b) {
+    if (!b->stream) GJD_TRY(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
+    if (!b->ev_ok) {
+        for (auto& e : b->ev.e) GJD_TRY(cudaEventCreate(&e));
+        b->ev_ok = true;
+    }
+    return GJD_OK;
+}
+
+uint64_t fnv1a(const void* p, size_t n) {
+    const uint8_t* s = (const uint8_t*)p;
+    uint64_t h = 1469598103934665603ull;
+    for (size_t i = 0; i < n; i++) { h ^= s[i]; h *= 1099511628211ull; }
+    return h;
+}
+
+/* Estimated device bytes one image needs (scan + sinfo + coef + dc + rgb). */
+size_t estimate_bytes(const gjd_item& it, const ItemGeom& g) {
+    size_t pw = align_up((size_t)g.width, 8), ph = align_up((size_t)g.height, 8);
+    return pw * ph * 7 + g.out_bytes + it.len * 2 + 65536;
+}
+
+/*
+ * Parse + unstuff items [first, first+n) into the batch's pinned staging, build descriptors, and
+ * enqueue the H2D copies + table/map kernels on the batch stream.
+ * pre: parsed/geom for the items are already filled by parse_all (indexed from `first`).
+ */
+int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* parsed, const ItemGeom* geom,
+                int32_t n, bool own_output) {
+    int rc = batch_init(ctx, b);
+    if (rc) return rc;
+    b->n = n;
+    b->ran = false;
+    b->geom.assign(geom, geom + n);
+    b->img_of.assign(n, -1);
+    b->imgs.clear();
+    b->dhts.clear();
+    b->quants.clear();
+
+    /* scan staging offsets from file sizes (upper bound of the unstuffed scan) */
+    std::vector<size_t> soff(n + 1, 0);
+    for (int32_t i = 0; i < n; i++)
+        soff[i + 1] = soff[i] + (b->geom[i].status == GJD_OK ? align_up(items[i].len + 16, 128) : 0);
+    b->scan_alloc = soff[n] + 256;
+    GJD_TRY(b->h_scan.ensure(b->scan_alloc));
+    uint8_t* hs = (uint8_t*)b->h_scan.p;
+
+    std::vector<long> ulen(n, 0);
+    ctx->pool->parallel_for((size_t)n, 4, [&](size_t i) {
+        if (b->geom[i].status != GJD_OK) return;
+        const GjdParsed& p = parsed[i];
+        uint8_t* dst = hs + soff[i];
+        long m = gjd_unstuff(p.scan_begin, p.file_end, dst);
+        if (m < 0) { b->geom[i].status = (int32_t)m; return; }
+        memset(dst + m, 0, 16);
+        ulen[i] = m;
+    });
+
+    /* descriptors */
+    std::unordered_map<uint64_t, std::vector<uint32_t>> lut_index, quant_index;
+    uint32_t seq = 0, tile = 0;
+    size_t rgb_off = 0;
+    b->pixels = b->padded_pixels = b->scan_bytes = b->subseqs = 0;
+    for (int32_t i = 0; i < n; i++) {
+        ItemGeom& g = b->geom[i];
+        if (g.status != GJD_OK) continue;
+        const GjdParsed& p = parsed[i];
+        if ((uint64_t)ulen[i] * 8 >= 0xffff0000ull) { g.status = GJD_E_UNSUPPORTED; continue; }
+        GjdImage d;
+        memset(&d, 0, sizeof(d));
+        d.scan_off = soff[i];
+        d.scan_bits = (uint32_t)(ulen[i] * 8);
+        d.sub_count = std::max<uint32_t>(1u, (d.scan_bits + GJD_SUBSEQ_BITS - 1) / GJD_SUBSEQ_BITS);
+        d.seq_first = seq;
+        d.seq_count = (d.sub_count + GJD_SEQ_SUBS - 1) / GJD_SEQ_SUBS;
+        d.width = (uint32_t)g.width;
+        d.height = (uint32_t)g.height;
+        d.mcus_x = (d.width + 7) / 8;
+        d.mcu_count = d.mcus_x * ((d.height + 7) / 8);
+        d.tile_first = tile;
+        d.tile_count = (d.mcu_count + GJD_TILE_MCUS - 1) / GJD_TILE_MCUS;
+        d.coef_off = (uint64_t)tile * GJD_TILE_I16;
+        d.blk_first = tile * 96u;
+        d.row_pitch = (uint32_t)g.pitch;
+        d.plane_stride = g.pstride;
+        if (items[i].rgb_on_device && items[i].rgb && !own_output) {
+            d.out_is_ptr = 1;
+            d.out_off = (uint64_t)(uintptr_t)items[i].rgb;
+        } else {
+            d.out_is_ptr = 0;
+            d.out_off = rgb_off;
+            rgb_off += align_up(g.out_bytes, 256);
+        }
+        memcpy(d.tabsel, p.tabsel, 8);
+        memcpy(d.qsel, p.qsel, 4);
+        /* Huffman table set: dedup by content */
+        {
+            uint64_t h = fnv1a(&p.dht, sizeof(GjdDhtSet));
+            auto& cand = lut_index[h];
+            int found = -1;
+            for (uint32_t id : cand)
+                if (memcmp(&b->dhts[id], &p.dht, sizeof(GjdDhtSet)) == 0) { found = (int)id; break; }
+            if (found < 0) {
+                if (b->dhts.size() >= 65535) { g.status = GJD_E_NOMEM; continue; }
+                found = (int)b->dhts.size();
+                b->dhts.push_back(p.dht);
+                cand.push_back((uint32_t)found);
+            }
+            d.lut_id = (uint16_t)found;
+        }
+        {
+            GjdQuantSet q;
+            for (int c = 0; c < 3; c++)
+                for (int k = 0; k < 64; k++) q.q[c][k] = p.quant[p.qsel[c]][k];
+            uint64_t h = fnv1a(&q, sizeof(q));
+            auto& cand = quant_index[h];
+            int found = -1;
+            for (uint32_t id : cand)
+                if (memcmp(&b->quants[id], &q, sizeof(q)) == 0) { found = (int)id; break; }
+            if (found < 0) {
+                if (b->quants.size() >= 65535) { g.status = GJD_E_NOMEM; continue; }
+                found = (int)b->quants.size();
+                b->quants.push_back(q);
+                cand.push_back((uint32_t)found);
+            }
+            d.quant_id = (uint16_t)found;
+        }
+        seq += d.seq_count;
+        tile += d.tile_count;
+        b->img_of[i] = (int32_t)b->imgs.size();
+        b->imgs.push_back(d);
+        b->pixels += (uint64_t)d.width * d.height;
+        b->padded_pixels += (uint64_t)d.mcu_count * 64;
+        b->scan_bytes += (uint64_t)ulen[i];
+        b->subseqs += d.sub_count;
+    }
+    b->rgb_alloc = rgb_off;
+
+    const uint32_t n_img = (uint32_t)b->imgs.size();
+    GjdDevBatch& v = b->view;
+    memset(&v, 0, sizeof(v));
+    v.n_img = n_img;
+    v.n_seq = seq;
+    v.n_tile = tile;
+    if (n_img == 0) return GJD_OK;
+
+    /* one pinned block for descriptors + DHT sets + quant sets, one H2D copy */
+    size_t o_img = 0;
+    size_t o_dht = align_up(o_img + sizeof(GjdImage) * n_img, 256);
+    size_t o_q = align_up(o_dht + sizeof(GjdDhtSet) * b->dhts.size(), 256);
+    size_t meta = align_up(o_q + sizeof(GjdQuantSet) * b->quants.size(), 256);
+    GJD_TRY(b->h_meta.ensure(meta));
+    memcpy((uint8_t*)b->h_meta.p + o_img, b->imgs.data(), sizeof(GjdImage) * n_img);
+    memcpy((uint8_t*)b->h_meta.p + o_dht, b->dhts.data(), sizeof(GjdDhtSet) * b->dhts.size());
+    memcpy((uint8_t*)b->h_meta.p + o_q, b->quants.data(), sizeof(GjdQuantSet) * b->quants.size());
+
+    GJD_TRY(b->d_meta.ensure(meta));
+    GJD_TRY(b->d_scan.ensure(b->scan_alloc));
+    GJD_TRY(b->d_luts.ensure(sizeof(GjdLutSet) * b->dhts.size()));
+    GJD_TRY(b->d_sinfo.ensure((size_t)seq * GJD_SEQ_SUBS * sizeof(uint2)));
+    GJD_TRY(b->d_seqmaps.ensure((size_t)seq * 2 * sizeof(uint32_t)));
+    GJD_TRY(b->d_coef.ensure((size_t)tile * GJD_TILE_I16 * sizeof(int16_t)));
+    GJD_TRY(b->d_dcdiff.ensure((size_t)tile * 96 * sizeof(int16_t)));
+    GJD_TRY(b->d_tilebase.ensure((size_t)tile * sizeof(int4)));
+    GJD_TRY(b->d_tileimg.ensure((size_t)tile * sizeof(uint32_t)));
+    GJD_TRY(b->d_rgb.ensure(std::max<size_t>(b->rgb_alloc, 256)));
+    GJD_TRY(b->d_status.ensure((size_t)(n_img + 1) * sizeof(uint32_t)));
+    GJD_TRY(b->h_status.ensure((size_t)(n_img + 1) * sizeof(uint32_t)));
+
+    v.imgs = (const GjdImage*)((uint8_t*)b->d_meta.p + o_img);
+    v.scan = (const uint8_t*)b->d_scan.p;
+    v.luts = (const GjdLutSet*)b->d_luts.p;
+    v.quants = (const GjdQuantSet*)((uint8_t*)b->d_meta.p + o_q);
+    v.sinfo = (uint2*)b->d_sinfo.p;
+    v.seq_img = (uint32_t*)b->d_seqmaps.p;
+    v.seq_base = (uint32_t*)b->d_seqmaps.p + seq;
+    v.coef = (int16_t*)b->d_coef.p;
+    v.dcdiff = (int16_t*)b->d_dcdiff.p;
+    v.tilebase = (int4*)b->d_tilebase.p;
+    v.tile_img = (uint32_t*)b->d_tileimg.p;
+    v.rgb = (uint8_t*)b->d_rgb.p;
+    v.status = (uint32_t*)b->d_status.p;
+    v.nosync = (uint32_t*)b->d_status.p + n_img;
+
+    GJD_TRY(cudaMemcpyAsync(b->d_scan.p, b->h_scan.p, soff[n] + 16, cudaMemcpyHostToDevice, b->stream));
+    GJD_TRY(cudaMemcpyAsync(b->d_meta.p, b->h_meta.p, meta, cudaMemcpyHostToDevice, b->stream));
+    GJD_TRY(gjd_launch_build_luts((const GjdDhtSet*)((uint8_t*)b->d_meta.p + o_dht), (GjdLutSet*)b->d_luts.p,
+                                  (uint32_t)b->dhts.size(), b->stream));
+    GJD_TRY(gjd_launch_fill_maps(v, b->stream));
+    return GJD_OK;
+}
+
+int batch_enqueue_run(gjd_ctx* ctx, gjd_batch* b) {
+    if (b->view.n_img == 0) { b->launches = 0; b->ran = true; return GJD_OK; }
+    GJD_TRY(gjd_launch_pipeline(b->view, b->stream, &b->ev, ctx->transform_variant, &b->launches));
+    GJD_TRY(cudaMemcpyAsync(b->h_status.p, b->d_status.p, (size_t)(b->view.n_img + 1) * sizeof(uint32_t),
+                            cudaMemcpyDeviceToHost, b->stream));
+    b->ran = true;
+    ctx->last = b;
+    return GJD_OK;
+}
+
+/* Wait for the batch.  If a sequence boundary did not converge in the single fix-up round of the
+ * pipeline (a chain crossing a whole 256-subsequence sequence without merging: never seen on real
+ * streams, kept for correctness), iterate the fix-up to its fixed point and redo the later stages. */
+int batch_wait(gjd_ctx* ctx, gjd_batch* b) {
+    if (!b->stream) return GJD_OK;
+    GJD_TRY(cudaStreamSynchronize(b->stream));
+    if (!b->ran || b->view.n_img == 0) return GJD_OK;
+    uint32_t* hst = (uint32_t*)b->h_status.p;
+    if (hst[b->view.n_img] == 0) return GJD_OK;
+    for (int guard = 0; guard < 65536 && hst[b->view.n_img] != 0; guard++) {
+        GJD_TRY(cudaMemsetAsync(b->view.nosync, 0, sizeof(uint32_t), b->stream));
+        GJD_TRY(gjd_launch_fix(b->view, b->stream));
+        GJD_TRY(cudaMemcpyAsync(hst + b->view.n_img, b->view.nosync, sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                                b->stream));
+        GJD_TRY(cudaStreamSynchronize(b->stream));
+    }
+    int launches = 0;
+    GJD_TRY(gjd_launch_pipeline(b->view, b->stream, nullptr, ctx->transform_variant, &launches, true));
+    GJD_TRY(cudaMemcpyAsync(b->h_status.p, b->d_status.p, (size_t)(b->view.n_img + 1) * sizeof(uint32_t),
+                            cudaMemcpyDeviceToHost, b->stream));
+    GJD_TRY(cudaStreamSynchronize(b->stream));
+    return 1;   /* outputs were regenerated: the caller repeats its D2H copies */
+}
+
+void set_item_status(gjd_batch* b, gjd_item* items) {
+    const uint32_t* hst = (const uint32_t*)b->h_status.p;
+    for (int32_t i = 0; i < b->n; i++) {
+        int32_t st = b->geom[i].status;
+        if (st == GJD_OK && b->img_of[i] >= 0 && b->ran && hst[b->img_of[i]] != 0) st = GJD_E_CORRUPT;
+        b->geom[i].status = st;
+        if (items) {
+            items[i].status = st;
+            items[i].width = b->geom[i].width;
+            items[i].height = b->geom[i].height;
+        }
+    }
+}
+
+/* Header parse of every item (parallel). */
+void parse_all(gjd_ctx* ctx, const gjd_item* items, int32_t n, std::vector<GjdParsed>& parsed,
+               std::vector<ItemGeom>& geom) {
+    parsed.resize(n);
+    geom.assign(n, ItemGeom());
+    ctx->pool->parallel_for((size_t)n, 16, [&](size_t i) {
+        ItemGeom& g = geom[i];
+        if (!items[i].jpg) { g.status = GJD_E_ARG; return; }
+        int rc = gjd_parse_headers(items[i].jpg, items[i].len, &parsed[i]);
+        g.width = parsed[i].width;
+        g.height = parsed[i].height;
+        if (rc) { g.status = rc; return; }
+        g.pitch = items[i].row_pitch ? items[i].row_pitch : (size_t)g.width;
+        g.pstride = items[i].plane_stride ? items[i].plane_stride : g.pitch * (size_t)g.height;
+        if (g.pitch < (size_t)g.width || g.pstride < g.pitch * (size_t)g.height || g.pitch > 0xffffffffull) {
+            g.status = GJD_E_ARG;
+            return;
+        }
+        g.out_bytes = 2 * g.pstride + g.pitch * (size_t)g.height;
+    });
+}
+
+}  // namespace
+
+/* ---------------------------------------------------------------- C ABI --------------- */
+
+extern "C" {
+
+const char* gjd_version(void) {
+    return "gjd " GJD_VERSION_STR " sm_100a subseq=" GJD_STR(GJD_SUBSEQ_BITS) " lut=" GJD_STR(GJD_LUT_BITS);
+}
+
+const char* gjd_strerror(int st) {
+    switch (st) {
+        case GJD_OK: return "ok";
+        case GJD_E_ARG: return "invalid argument";
+        case GJD_E_CUDA: return "CUDA runtime error";
+        case GJD_E_NOMEM: return "out of memory";
+        case GJD_E_FORMAT: return "not a JPEG or malformed/truncated marker segment";
+        case GJD_E_UNSUPPORTED: return "JPEG outside the 8-bit 4:4:4 baseline single-scan contract";
+        case GJD_E_CORRUPT: return "corrupt entropy-coded data";
+        case GJD_E_NODEVICE: return "no usable CUDA device (libgjd has no CPU decode path)";
+        case GJD_E_IO: return "file I/O error";
+        default: return "unknown status";
+    }
+}
+
+const char* gjd_last_cuda_error(gjd_ctx* ctx) { return ctx ? ctx->cuda_err.c_str() : ""; }
+
+int gjd_create(gjd_ctx** out, int device, size_t scratch_bytes_hint) {
+    if (!out) return GJD_E_ARG;
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) return GJD_E_NODEVICE;
+    if (device < 0 || device >= count) return GJD_E_ARG;
+    if (cudaSetDevice(device) != cudaSuccess) return GJD_E_NODEVICE;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return GJD_E_NODEVICE;
+    if (prop.major < 10) return GJD_E_NODEVICE;   /* kernels are built for sm_100a only */
+    gjd_ctx* ctx = new (std::nothrow) gjd_ctx();
+    if (!ctx) return GJD_E_NOMEM;
+    ctx->device = device;
+    ctx->scratch = scratch_bytes_hint ? scratch_bytes_hint : ((size_t)6 << 30);
+    int threads = (int)std::thread::hardware_concurrency();
+    if (const char* e = getenv("GJD_HOST_THREADS")) threads = atoi(e);
+    threads = std::max(1, std::min(threads, 64));
+    ctx->pool = new Pool(threads - 1);
+    if (const char* e = getenv("GJD_TRANSFORM_VARIANT")) ctx->transform_variant = atoi(e);
+    *out = ctx;
+    return GJD_OK;
+}
+
+void gjd_destroy(gjd_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    for (auto& s : ctx->slot) {
+        if (s.stream) cudaStreamSynchronize(s.stream);
+        s.release();
+    }
+    delete ctx->pool;
+    delete ctx;
+}
+
+int gjd_peek(const uint8_t* jpg, size_t len, int32_t* width, int32_t* height) {
+    if (!jpg) return GJD_E_ARG;
+    GjdParsed p;
+    int rc = gjd_parse_headers(jpg, len, &p);
+    if (width) *width = p.width;
+    if (height) *height = p.height;
+    return rc;
+}
+
+void* gjd_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+    return p;
+}
+void gjd_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+/* D2H of every image of a staged+run batch into the callers' buffers; adjacent regions merge. */
+static int enqueue_d2h(gjd_ctx* ctx, gjd_batch* b, gjd_item* items) {
+    const uint8_t* dbase = (const uint8_t*)b->d_rgb.p;
+    uint8_t* run_dst = nullptr;
+    const uint8_t* run_src = nullptr;
+    size_t run_len = 0;
+    for (int32_t i = 0; i < b->n; i++) {
+        int32_t k = b->img_of[i];
+        if (k < 0) continue;
+        const GjdImage& d = b->imgs[k];
+        if (d.out_is_ptr || !items[i].rgb) continue;
+        const uint8_t* src = dbase + d.out_off;
+        size_t len = b->geom[i].out_bytes;
+        if (run_len && run_dst + run_len == items[i].rgb && run_src + run_len == src) {
+            run_len += len;
+            continue;
+        }
+        if (run_len) GJD_TRY(cudaMemcpyAsync(run_dst, run_src, run_len, cudaMemcpyDeviceToHost, b->stream));
+        run_dst = items[i].rgb; run_src = src; run_len = len;
+    }
+    if (run_len) GJD_TRY(cudaMemcpyAsync(run_dst, run_src, run_len, cudaMemcpyDeviceToHost, b->stream));
+    return GJD_OK;
+}
+
+int gjd_decode_batch(gjd_ctx* ctx, gjd_item* items, int32_t n) {
+    if (!ctx || (n > 0 && !items) || n < 0) return GJD_E_ARG;
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return GJD_E_NODEVICE;
+    if (n == 0) return GJD_OK;
+    std::vector<GjdParsed> parsed;
+    std::vector<ItemGeom> geom;
+    parse_all(ctx, items, n, parsed, geom);
+
+    /* sub-batches under the scratch budget, alternating between the two slots */
+    struct Span { int32_t first, count; };
+    std::vector<Span> spans;
+    {
+        size_t acc = 0;
+        int32_t first = 0;
+        for (int32_t i = 0; i < n; i++) {
+            size_t need = geom[i].status == GJD_OK ? estimate_bytes(items[i], geom[i]) : 0;
+            if (i > first && acc + need > ctx->scratch) {
+                spans.push_back({first, i - first});
+                first = i;
+                acc = 0;
+            }
+            acc += need;
+        }
+        spans.push_back({first, n - first});
+    }
+    int rc = GJD_OK;
+    int32_t pending[2] = {-1, -1};   /* span index in flight on each slot */
+    auto finish = [&](int s) -> int {
+        if (pending[s] < 0) return GJD_OK;
+        gjd_batch* b = &ctx->slot[s];
+        const Span& sp = spans[pending[s]];
+        int w = batch_wait(ctx, b);
+        if (w < 0) return w;
+        if (w == 1) {   /* outputs regenerated on the slow path */
+            int r2 = enqueue_d2h(ctx, b, items + sp.first);
+            if (r2) return r2;
+            if (cudaStreamSynchronize(b->stream) != cudaSuccess) return GJD_E_CUDA;
+        }
+        set_item_status(b, items + sp.first);
+        pending[s] = -1;
+        return GJD_OK;
+    };
+    for (size_t k = 0; k < spans.size() && rc == GJD_OK; k++) {
+        int s = (int)(k & 1);
+        rc = finish(s);
+        if (rc) break;
+        gjd_batch* b = &ctx->slot[s];
+        const Span& sp = spans[k];
+        rc = batch_stage(ctx, b, items + sp.first, parsed.data() + sp.first, geom.data() + sp.first, sp.count, false);
+        if (rc) break;
+        rc = batch_enqueue_run(ctx, b);
+        if (rc) break;
+        rc = enqueue_d2h(ctx, b, items + sp.first);
+        pending[s] = (int32_t)k;
+    }
+    for (int s = 0; s < 2; s++) {
+        int r2 = finish(s);
+        if (rc == GJD_OK) rc = r2;
+    }
+    if (rc != GJD_OK)
+        for (int32_t i = 0; i < n; i++)
+            if (items[i].status == GJD_OK && geom[i].status != GJD_OK) items[i].status = geom[i].status;
+    return rc;
+}
+
+int gjd_batch_prepare(gjd_ctx* ctx, gjd_item* items, int32_t n, gjd_batch** out) {
+    if (!ctx || !out || (n > 0 && !items) || n < 0) return GJD_E_ARG;
+    *out = nullptr;
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return GJD_E_NODEVICE;
+    gjd_batch* b = new (std::nothrow) gjd_batch();
+    if (!b) return GJD_E_NOMEM;
+    std::vector<ItemGeom> geom;
+    parse_all(ctx, items, n, b->parsed, geom);
+    /* items without a caller buffer get a tight library-owned device buffer */
+    int rc = batch_stage(ctx, b, items, b->parsed.data(), geom.data(), n, false);
+    if (rc == GJD_OK && cudaStreamSynchronize(b->stream) != cudaSuccess) rc = cuda_fail(ctx, cudaGetLastError(), "prepare");
+    if (rc != GJD_OK) {
+        b->release();
+        delete b;
+        return rc;
+    }
+    set_item_status(b, items);
+    b->parsed.clear();
+    b->parsed.shrink_to_fit();
+    *out = b;
+    return GJD_OK;
+}
+
+int gjd_batch_run(gjd_ctx* ctx, gjd_batch* b) {
+    if (!ctx || !b) return GJD_E_ARG;
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return GJD_E_NODEVICE;
+    return batch_enqueue_run(ctx, b);
+}
+
+int gjd_batch_sync(gjd_ctx* ctx, gjd_batch* b) {
+    if (!ctx || !b) return GJD_E_ARG;
+    int w = batch_wait(ctx, b);
+    if (w < 0) return w;
+    set_item_status(b, nullptr);
+    for (int32_t i = 0; i < b->n; i++)
+        if (b->geom[i].status == GJD_E_CORRUPT) return GJD_E_CORRUPT;
+    return GJD_OK;
+}
+
+int gjd_batch_status(gjd_ctx* ctx, gjd_batch* b, int32_t i) {
+    if (!ctx || !b || i < 0 || i >= b->n) return GJD_E_ARG;
+    return b->geom[i].status;
+}
+
+int gjd_batch_fetch(gjd_ctx* ctx, gjd_batch* b, int32_t i, uint8_t* rgb_host) {
+    if (!ctx || !b || !rgb_host || i < 0 || i >= b->n) return GJD_E_ARG;
+    int32_t k = b->img_of[i];
+    if (k < 0) return b->geom[i].status ? b->geom[i].status : GJD_E_ARG;
+    const GjdImage& d = b->imgs[k];
+    const uint8_t* src = d.out_is_ptr ? (const uint8_t*)(uintptr_t)d.out_off : (const uint8_t*)b->d_rgb.p + d.out_off;
+    for (int c = 0; c < 3; c++)
+        GJD_TRY(cudaMemcpy2DAsync(rgb_host + (size_t)c * d.width * d.height, d.width, src + (size_t)c * d.plane_stride,
+                                  d.row_pitch, d.width, d.height, cudaMemcpyDeviceToHost, b->stream));
+    GJD_TRY(cudaStreamSynchronize(b->stream));
+    return GJD_OK;
+}
+
+void gjd_batch_free(gjd_ctx* ctx, gjd_batch* b) {
+    if (!b) return;
+    if (ctx) {
+        cudaSetDevice(ctx->device);
+        if (ctx->last == b) ctx->last = nullptr;
+    }
+    if (b->stream) cudaStreamSynchronize(b->stream);
+    b->release();
+    delete b;
+}
+
+int gjd_batch_info(gjd_ctx* ctx, gjd_batch* b, uint64_t info[5]) {
+    if (!ctx || !b || !info) return GJD_E_ARG;
+    info[0] = b->pixels; info[1] = b->padded_pixels; info[2] = b->scan_bytes; info[3] = b->subseqs;
+    info[4] = (uint64_t)b->launches;
+    return GJD_OK;
+}
+
+int gjd_stage_times(gjd_ctx* ctx, float ms[4]) {
+    if (!ctx || !ms) return GJD_E_ARG;
+    gjd_batch* b = ctx->last;
+    if (!b || !b->ev_ok || !b->ran || b->view.n_img == 0) return GJD_E_ARG;
+    GJD_TRY(cudaEventSynchronize(b->ev.e[4]));
+    GJD_TRY(cudaEventElapsedTime(&ms[0], b->ev.e[1], b->ev.e[2]));
+    GJD_TRY(cudaEventElapsedTime(&ms[1], b->ev.e[2], b->ev.e[3]));
+    GJD_TRY(cudaEventElapsedTime(&ms[2], b->ev.e[3], b->ev.e[4]));
+    GJD_TRY(cudaEventElapsedTime(&ms[3], b->ev.e[0], b->ev.e[4]));
+    return GJD_OK;
+}
+
+int gjd_decode_coeffs(gjd_ctx* ctx, const uint8_t* jpg, size_t len, int16_t* coeffs_host) {
+    if (!ctx || !jpg || !coeffs_host) return GJD_E_ARG;
+    gjd_item it;
+    memset(&it, 0, sizeof(it));
+    it.jpg = jpg;
+    it.len = len;
+    gjd_batch* b = nullptr;
+    int rc = gjd_batch_prepare(ctx, &it, 1, &b);
+    if (rc) return rc;
+    if (it.status != GJD_OK) { rc = it.status; gjd_batch_free(ctx, b); return rc; }
+    rc = gjd_batch_run(ctx, b);
+    if (rc == GJD_OK) rc = gjd_batch_sync(ctx, b);
+    if (rc == GJD_OK || rc == GJD_E_CORRUPT) {
+        int rc0 = rc;
+        size_t ncoef = (size_t)b->imgs[0].mcu_count * 192;
+        DevBuf tmp;
+        cudaError_t e = tmp.ensure(ncoef * sizeof(int16_t));
+        if (e == cudaSuccess) e = gjd_launch_export_coefs(b->view, 0, (int16_t*)tmp.p, b->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(coeffs_host, tmp.p, ncoef * sizeof(int16_t), cudaMemcpyDeviceToHost, b->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
+        tmp.release();
+        rc = e == cudaSuccess ? rc0 : cuda_fail(ctx, e, "export_coefs");
+    }
+    gjd_batch_free(ctx, b);
+    return rc;
+}
+
+int gjd_test_color(gjd_ctx* ctx, const int16_t* y, const int16_t* cb, const int16_t* cr, size_t n,
+                   uint8_t* r, uint8_t* g, uint8_t* bl) {
+    if (!ctx || !y || !cb || !cr || !r || !g || !bl) return GJD_E_ARG;
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return GJD_E_NODEVICE;
+    if (n == 0) return GJD_OK;
+    DevBuf in, out;
+    GJD_TRY(in.ensure(n * 6));
+    GJD_TRY(out.ensure(n * 3));
+    int16_t* di = (int16_t*)in.p;
+    uint8_t* dout = (uint8_t*)out.p;
+    int rc = GJD_OK;
+    cudaError_t e = cudaMemcpy(di, y, n * 2, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(di + n, cb, n * 2, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(di + 2 * n, cr, n * 2, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = gjd_launch_test_color(di, di + n, di + 2 * n, n, dout, dout + n, dout + 2 * n, 0);
+    if (e == cudaSuccess) e = cudaMemcpy(r, dout, n, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(g, dout + n, n, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(bl, dout + 2 * n, n, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) rc = cuda_fail(ctx, e, "gjd_test_color");
+    in.release();
+    out.release();
+    return rc;
+}
+
+int gjd_test_idct(gjd_ctx* ctx, const int16_t* coef_zz, size_t nblocks, const uint8_t quant_zz[64], int16_t* samples) {
+    if (!ctx || !coef_zz || !quant_zz || !samples) return GJD_E_ARG;
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return GJD_E_NODEVICE;
+    if (nblocks == 0) return GJD_OK;
+    DevBuf in, out, q;
+    GJD_TRY(in.ensure(nblocks * 128));
+    GJD_TRY(out.ensure(nblocks * 128));
+    GJD_TRY(q.ensure(256));
+    int32_t hq[64];
+    for (int i = 0; i < 64; i++) hq[i] = quant_zz[i];
+    int rc = GJD_OK;
+    cudaError_t e = cudaMemcpy(in.p, coef_zz, nblocks * 128, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(q.p, hq, 256, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = gjd_launch_test_idct((const int16_t*)in.p, nblocks, (const int32_t*)q.p, (int16_t*)out.p, 0);
+    if (e == cudaSuccess) e = cudaMemcpy(samples, out.p, nblocks * 128, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) rc = cuda_fail(ctx, e, "gjd_test_idct");
+    in.release(); out.release(); q.release();
+    return rc;
+}
+
+}  /* extern "C" */

@@ -1,0 +1,370 @@
+/*
+ * gjd_devfn.cuh — the arithmetic of the hot path as __host__ __device__ inline functions.
+ *
+ * The CUDA kernels (gjd_kernels.cu) are built from these.  They also compile as plain C++
+ * (GJD_HD expands to nothing without __CUDACC__) so that tests/hostsim can single-step the very
+ * same functions on the build machine, which has no GPU.  The host build is test scaffolding
+ * only: libgjd.so has no CPU decode path.
+ *
+ * Semantics follow the reference's CPU decoder (paths relative to the reference root):
+ *   entropy decode  cpp-decoder/src/parser.cpp:105-134, utils/stream.cpp:8-22,44-51
+ *   dezigzag        cpp-decoder/src/idct.cpp:7-32
+ *   IDCT            cpp-decoder/src/idct.cpp:34-133, constants idct.h:4-9
+ *   colour          cpp-decoder/utils/color.cpp:3-18
+ */
+#ifndef GJD_DEVFN_CUH
+#define GJD_DEVFN_CUH
+
+#include <stdint.h>
+#include "gjd_types.h"
+
+#ifdef __CUDACC__
+#define GJD_HD __host__ __device__ __forceinline__
+#else
+#define GJD_HD inline
+#endif
+
+/* ------------------------------------------------------------------ Huffman tables ---- */
+
+/* Pack one decoded symbol into the LUT entry format of gjd_types.h. */
+GJD_HD uint32_t gjd_make_entry(uint32_t code_len, uint32_t sym, uint32_t isdc) {
+    uint32_t size = sym & 15u;
+    uint32_t adv = isdc ? 1u : ((sym == 0u) ? 0u : (sym >> 4) + 1u);
+    return (code_len + size) | (size << 5) | (adv << 9);
+}
+#define GJD_ENTRY_BAD 0x4000u   /* bit 14: no code assigned to these bits */
+
+/* Canonical code tables from BITS[16]: lim[L] = first unused code of length L left-aligned to
+ * 16 bits (non-decreasing in L), off[L] = valptr[L] - mincode[L].
+ * (The reference's leftmost-free-leaf insertion, huffmanTree.cpp:34-68, yields this assignment.) */
+GJD_HD void gjd_canonical(const uint8_t bits[16], uint32_t lim[17], int32_t off[17]) {
+    uint32_t code = 0, k = 0;
+    lim[0] = 0; off[0] = 0;
+    for (int L = 1; L <= 16; L++) {
+        off[L] = (int32_t)k - (int32_t)code;
+        code += bits[L - 1];
+        k += bits[L - 1];
+        lim[L] = code << (16 - L);
+        code <<= 1;
+    }
+}
+
+/* Resolve a 16-bit window against the canonical tables, lengths from..16. */
+GJD_HD uint32_t gjd_resolve(const uint32_t* lim, const int32_t* off, const uint8_t* vals,
+                            uint32_t isdc, uint32_t win16, int from) {
+    for (int L = from; L <= 16; L++) {
+        if (win16 < lim[L]) {
+            uint32_t idx = (uint32_t)(off[L] + (int32_t)(win16 >> (16 - L))) & 255u;
+            return gjd_make_entry((uint32_t)L, vals[idx], isdc);
+        }
+    }
+    /* unassigned code: consume 16 bits, advance one slot; flagged for the write pass */
+    return 16u | (1u << 9) | GJD_ENTRY_BAD;
+}
+
+/* Primary LUT entry for index i (GJD_LUT_BITS leading bits). */
+GJD_HD uint16_t gjd_lut_entry(const uint32_t* lim, const int32_t* off, const uint8_t* vals,
+                              uint32_t isdc, uint32_t i) {
+    uint32_t win16 = i << (16 - GJD_LUT_BITS);
+    for (int L = 1; L <= GJD_LUT_BITS; L++) {
+        if (win16 < lim[L]) {
+            uint32_t idx = (uint32_t)(off[L] + (int32_t)(win16 >> (16 - L))) & 255u;
+            return (uint16_t)gjd_make_entry((uint32_t)L, vals[idx], isdc);
+        }
+    }
+    return (uint16_t)GJD_LUT_SLOW;
+}
+
+/* ------------------------------------------------------------------ bit reader -------- */
+
+GJD_HD uint32_t gjd_bswap32(uint32_t x) {
+#ifdef __CUDA_ARCH__
+    return __byte_perm(x, 0, 0x0123);
+#else
+    return (x >> 24) | ((x >> 8) & 0xff00u) | ((x << 8) & 0xff0000u) | (x << 24);
+#endif
+}
+
+/* Two cached big-endian words of the scan; wi = index of w0. */
+struct GjdWin {
+    uint32_t wi, w0, w1;
+};
+
+GJD_HD void gjd_win_init(GjdWin& c, const uint32_t* scan, uint32_t p) {
+    c.wi = p >> 5;
+    c.w0 = gjd_bswap32(scan[c.wi]);
+    c.w1 = gjd_bswap32(scan[c.wi + 1]);
+}
+
+/* 32 bits of the scan starting at bit p (MSB first).  p may advance by at most 32 bits per call. */
+GJD_HD uint32_t gjd_peek32(GjdWin& c, const uint32_t* scan, uint32_t p) {
+    uint32_t wi = p >> 5;
+    if (wi != c.wi) {
+        c.w0 = c.w1;
+        c.w1 = gjd_bswap32(scan[wi + 1]);
+        c.wi = wi;
+    }
+#ifdef __CUDA_ARCH__
+    return __funnelshift_l(c.w1, c.w0, p);   /* shift amount taken mod 32 */
+#else
+    uint32_t sh = p & 31u;
+    return sh ? (c.w0 << sh) | (c.w1 >> (32u - sh)) : c.w0;
+#endif
+}
+
+/* ------------------------------------------------------------------ entropy decode ---- */
+
+/* Decoder state between symbols: p = bit position in the image's unstuffed scan, n = coefficient
+ * slots advanced so far, pos = comp*64 + zigzag index (0..191) of the next slot.
+ * This is the (p, n, c, z) state of the reference's decodeSequence (cuda-decoder/src/parser.cu:50-121). */
+struct GjdState {
+    uint32_t p, n, pos;
+};
+
+/* tabsel packed: bits [4c+1:4c] = LUT slot of component c's DC table, [4c+3:4c+2] = its AC table. */
+GJD_HD uint32_t gjd_pack_tabsel(const uint8_t tabsel[8]) {
+    uint32_t s = 0;
+    for (int c = 0; c < 3; c++) s |= ((uint32_t)(tabsel[c] & 3) << (4 * c)) | ((uint32_t)(tabsel[4 + c] & 3) << (4 * c + 2));
+    return s;
+}
+
+struct GjdNoSink {
+    GJD_HD void operator()(uint32_t, int, uint32_t) const {}
+};
+
+/* Decode symbols that START before end_bits, beginning at state s.  A symbol that would run past
+ * scan_bits is padding and is not counted.  When WRITE, every non-zero coefficient is handed to
+ * sink(slot_index_relative_to_s.n==0, value, entry) — slot index counts from the state's n.
+ * Follows JPEGParser::buildMCU (cpp-decoder/src/parser.cpp:105-134): DC size/diff; AC run/size with
+ * EOB = 0x00, "length += run", value bits always consumed, coefficient kept only if index < 64. */
+template <bool WRITE, class Sink>
+GJD_HD void gjd_decode_span(const uint32_t* scan, const GjdLutSet* lut, uint32_t tabsel,
+                            uint32_t end_bits, uint32_t scan_bits, GjdState& s, Sink sink, uint32_t& bad) {
+    if (s.p >= end_bits) return;
+    GjdWin win;
+    gjd_win_init(win, scan, s.p);
+    uint32_t p = s.p, n = s.n, pos = s.pos;
+    while (p < end_bits) {
+        uint32_t w = gjd_peek32(win, scan, p);
+        uint32_t z = pos & 63u;
+        uint32_t c = pos >> 6;
+        uint32_t slot = (tabsel >> (4u * c + (z ? 2u : 0u))) & 3u;
+        uint32_t e = lut->lut[slot][w >> (32 - GJD_LUT_BITS)];
+        if (e & GJD_LUT_SLOW)
+            e = gjd_resolve(lut->lim[slot], lut->off[slot], lut->vals[slot], lut->isdc[slot], w >> 16,
+                            GJD_LUT_BITS + 1);
+        uint32_t total = e & 31u;
+        if (p + total > scan_bits) break;
+        uint32_t adv = (e >> 9) & 31u;
+        uint32_t znew = adv ? z + adv : 64u;
+        bool inside = znew <= 64u;
+        if (!inside) znew = 64u;
+        if (WRITE) {
+            uint32_t size = (e >> 5) & 15u;
+            if (e & GJD_ENTRY_BAD) bad |= GJD_DEV_BADCODE;
+            if (inside && (size != 0u || z == 0u)) {
+                int v = 0;
+                if (size) {
+                    uint32_t len = total - size;
+                    uint32_t vb = (w << len) >> (32u - size);
+                    /* Stream::decodeNumber, cpp-decoder/utils/stream.cpp:44-51 */
+                    v = (vb >> (size - 1u)) ? (int)vb : (int)vb - (int)((1u << size) - 1u);
+                }
+                sink(n + (znew - 1u - z), v, e);
+            }
+        }
+        uint32_t d = znew - z;
+        n += d;
+        pos += d;
+        if (pos == 192u) pos = 0u;
+        p += total;
+    }
+    s.p = p; s.n = n; s.pos = pos;
+}
+
+/* ------------------------------------------------------------------ IDCT -------------- */
+
+/* natural index (row*8+col) -> zigzag index; cpp-decoder/src/idct.cpp:7-18 */
+#define GJD_ZZ_TABLE                                                                        \
+    { 0,  1,  5,  6, 14, 15, 27, 28,  2,  4,  7, 13, 16, 26, 29, 42,  3,  8, 12, 17, 25, 30, 41, 43, \
+      9, 11, 18, 24, 31, 40, 44, 53, 10, 19, 23, 32, 39, 45, 52, 54, 20, 22, 33, 38, 46, 51, 55, 60, \
+     21, 34, 37, 47, 50, 56, 59, 61, 35, 36, 48, 49, 57, 58, 62, 63 }
+
+#define GJD_C1 2841
+#define GJD_C2 2676
+#define GJD_C3 2408
+#define GJD_C5 1609
+#define GJD_C6 1108
+#define GJD_C7 565
+
+/* Row pass on b[0..7] (stride 1); general path only — the reference's all-zero shortcut
+ * (idct.cpp:38-41) is value-identical: ((b0<<11)+128)>>8 == b0<<3. */
+GJD_HD void gjd_idct_row(int& b0, int& b1, int& b2, int& b3, int& b4, int& b5, int& b6, int& b7) {
+    int x0, x1, x2, x3, x4, x5, x6, x7, x8;
+    x1 = b4 * 2048; x2 = b6; x3 = b2; x4 = b1; x5 = b7; x6 = b5; x7 = b3;
+    x0 = b0 * 2048 + 128;
+    x8 = GJD_C7 * (x4 + x5);
+    x4 = x8 + (GJD_C1 - GJD_C7) * x4;
+    x5 = x8 - (GJD_C1 + GJD_C7) * x5;
+    x8 = GJD_C3 * (x6 + x7);
+    x6 = x8 - (GJD_C3 - GJD_C5) * x6;
+    x7 = x8 - (GJD_C3 + GJD_C5) * x7;
+    x8 = x0 + x1;
+    x0 -= x1;
+    x1 = GJD_C6 * (x3 + x2);
+    x2 = x1 - (GJD_C2 + GJD_C6) * x2;
+    x3 = x1 + (GJD_C2 - GJD_C6) * x3;
+    x1 = x4 + x6;
+    x4 -= x6;
+    x6 = x5 + x7;
+    x5 -= x7;
+    x7 = x8 + x3;
+    x8 -= x3;
+    x3 = x0 + x2;
+    x0 -= x2;
+    x2 = (181 * (x4 + x5) + 128) >> 8;
+    x4 = (181 * (x4 - x5) + 128) >> 8;
+    b0 = (x7 + x1) >> 8;
+    b1 = (x3 + x2) >> 8;
+    b2 = (x0 + x4) >> 8;
+    b3 = (x8 + x6) >> 8;
+    b4 = (x8 - x6) >> 8;
+    b5 = (x0 - x4) >> 8;
+    b6 = (x3 - x2) >> 8;
+    b7 = (x7 - x1) >> 8;
+}
+
+/* clip(v >> 14) to [-256,255] (idct.cpp:20-22), returned with a +256 bias: [0,511]. */
+GJD_HD int gjd_descale_clip_biased(int v) {
+#ifdef __CUDA_ARCH__
+    return __viaddmin_s32_relu(v >> 14, 256, 511);
+#else
+    int t = (v >> 14) + 256;
+    t = t > 511 ? 511 : t;
+    return t < 0 ? 0 : t;
+#endif
+}
+
+/* Column pass (idct.cpp:79-122; shortcut :83-86 is value-identical to the general path).
+ * Outputs are clip(.)+256, i.e. in [0,511]. */
+GJD_HD void gjd_idct_col(int& b0, int& b1, int& b2, int& b3, int& b4, int& b5, int& b6, int& b7) {
+    int x0, x1, x2, x3, x4, x5, x6, x7, x8;
+    x1 = b4 * 256; x2 = b6; x3 = b2; x4 = b1; x5 = b7; x6 = b5; x7 = b3;
+    x0 = b0 * 256 + 8192;
+    x8 = GJD_C7 * (x4 + x5) + 4;
+    x4 = (x8 + (GJD_C1 - GJD_C7) * x4) >> 3;
+    x5 = (x8 - (GJD_C1 + GJD_C7) * x5) >> 3;
+    x8 = GJD_C3 * (x6 + x7) + 4;
+    x6 = (x8 - (GJD_C3 - GJD_C5) * x6) >> 3;
+    x7 = (x8 - (GJD_C3 + GJD_C5) * x7) >> 3;
+    x8 = x0 + x1;
+    x0 -= x1;
+    x1 = GJD_C6 * (x3 + x2) + 4;
+    x2 = (x1 - (GJD_C2 + GJD_C6) * x2) >> 3;
+    x3 = (x1 + (GJD_C2 - GJD_C6) * x3) >> 3;
+    x1 = x4 + x6;
+    x4 -= x6;
+    x6 = x5 + x7;
+    x5 -= x7;
+    x7 = x8 + x3;
+    x8 -= x3;
+    x3 = x0 + x2;
+    x0 -= x2;
+    x2 = (181 * (x4 + x5) + 128) >> 8;
+    x4 = (181 * (x4 - x5) + 128) >> 8;
+    b0 = gjd_descale_clip_biased(x7 + x1);
+    b1 = gjd_descale_clip_biased(x3 + x2);
+    b2 = gjd_descale_clip_biased(x0 + x4);
+    b3 = gjd_descale_clip_biased(x8 + x6);
+    b4 = gjd_descale_clip_biased(x8 - x6);
+    b5 = gjd_descale_clip_biased(x0 - x4);
+    b6 = gjd_descale_clip_biased(x3 - x2);
+    b7 = gjd_descale_clip_biased(x7 - x1);
+}
+
+/* Full 8x8: v[] natural order, dequantised in, biased samples (clip+256) out. */
+GJD_HD void gjd_idct8x8(int v[64]) {
+#pragma unroll
+    for (int r = 0; r < 8; r++)
+        gjd_idct_row(v[8 * r], v[8 * r + 1], v[8 * r + 2], v[8 * r + 3], v[8 * r + 4], v[8 * r + 5],
+                     v[8 * r + 6], v[8 * r + 7]);
+#pragma unroll
+    for (int c = 0; c < 8; c++)
+        gjd_idct_col(v[c], v[8 + c], v[16 + c], v[24 + c], v[32 + c], v[40 + c], v[48 + c], v[56 + c]);
+}
+
+/* ------------------------------------------------------------------ colour ------------ */
+/*
+ * The reference computes (color.cpp:10-16, called as colorConversion(Y, Cr, Cb)):
+ *     float r = Cr*(2-2*0.299) + Y;  float b = Cb*(2-2*0.114) + Y;      (double math, rounded to float)
+ *     float g = (Y - 0.114*b - 0.299*r)/0.587;                           (double math on the floats)
+ *     R = clamp((int)(r+128)) ...                                        (float add, truncation)
+ * With Y,Cb,Cr integers in [-256,255]:
+ *   - r+128 and b+128 are never within rounding distance of a non-integer boundary (fractions are
+ *     multiples of 1/500 and 1/250) and truncation vs floor only differs below 0, where the clamp
+ *     wins — so R and B equal clamp(Y + 128 + floor(K*C / 2^20)) with K = ceil(1.402*2^20),
+ *     ceil(1.772*2^20).  Proven over all 2^18 (Y,C) pairs (tests/test_color.py).
+ *   - g is a rational with denominator 587000: float rounding can flip the truncation when the exact
+ *     value is within 2.8e-5 of an integer (843 of the 2^27 triples).  The fast path evaluates G in
+ *     2^-20 fixed point and, when the fraction is within 2^-14 of an integer, falls back to the
+ *     reference's own IEEE sequence (gjd_color_g_exact).  Proven over all 2^27 triples.
+ * Inputs to the fast path carry the +256 bias of gjd_descale_clip_biased.
+ */
+#define GJD_KR 1470104            /* ceil(1.402 * 2^20) */
+#define GJD_KB 1858077            /* ceil(1.772 * 2^20) */
+#define GJD_KGB 360853            /* round(0.114*1.772/0.587 * 2^20) */
+#define GJD_KGR 748826            /* round(0.299*1.402/0.587 * 2^20) */
+#define GJD_GDELTA 64             /* danger half-width, 2^-14 in 2^-20 units */
+#define GJD_CONST_R (-256 * GJD_KR - (128 << 20))
+#define GJD_CONST_B (-256 * GJD_KB - (128 << 20))
+#define GJD_CONST_G (256 * GJD_KGB + 256 * GJD_KGR - (128 << 20) + GJD_GDELTA)
+
+GJD_HD int gjd_addmin_relu(int a, int b, int c) {   /* max(min(a+b, c), 0) */
+#ifdef __CUDA_ARCH__
+    return __viaddmin_s32_relu(a, b, c);
+#else
+    int t = a + b;
+    t = t > c ? c : t;
+    return t < 0 ? 0 : t;
+#endif
+}
+
+/* The reference's IEEE sequence for G, on unbiased inputs. No FMA contraction anywhere. */
+GJD_HD int gjd_color_g_exact(int y, int cb, int cr) {
+#ifdef __CUDA_ARCH__
+    float r = __double2float_rn(__dadd_rn(__dmul_rn((double)cr, (2 - 2 * 0.299)), (double)y));
+    float b = __double2float_rn(__dadd_rn(__dmul_rn((double)cb, (2 - 2 * 0.114)), (double)y));
+    double t = __dsub_rn(__dsub_rn((double)y, __dmul_rn(0.114, (double)b)), __dmul_rn(0.299, (double)r));
+    float g = __double2float_rn(__ddiv_rn(t, 0.587));
+    int G = __float2int_rz(__fadd_rn(g, 128.0f));
+#else
+    volatile double rd = (double)cr * (2 - 2 * 0.299);
+    volatile double rs = rd + (double)y;
+    float r = (float)rs;
+    volatile double bd = (double)cb * (2 - 2 * 0.114);
+    volatile double bs = bd + (double)y;
+    float b = (float)bs;
+    volatile double m1 = 0.114 * (double)b;
+    volatile double m2 = 0.299 * (double)r;
+    volatile double t1 = (double)y - m1;
+    volatile double t2 = t1 - m2;
+    float g = (float)(t2 / 0.587);
+    volatile float gs = g + 128.0f;
+    int G = (int)gs;
+#endif
+    return G > 255 ? 255 : (G < 0 ? 0 : G);
+}
+
+/* Fast path on biased inputs (yb, cbb, crb in [0,511]). */
+GJD_HD void gjd_color(int yb, int cbb, int crb, int& R, int& G, int& B) {
+    int tr = crb * GJD_KR + GJD_CONST_R;
+    int tb = cbb * GJD_KB + GJD_CONST_B;
+    int tg = crb * (-GJD_KGR) + GJD_CONST_G;
+    tg = cbb * (-GJD_KGB) + tg;
+    R = gjd_addmin_relu(tr >> 20, yb, 255);
+    B = gjd_addmin_relu(tb >> 20, yb, 255);
+    G = gjd_addmin_relu(tg >> 20, yb, 255);
+    if ((uint32_t)(tg & 0xFFFFF) < 2u * GJD_GDELTA) G = gjd_color_g_exact(yb - 256, cbb - 256, crb - 256);
+}
+
+#endif /* GJD_DEVFN_CUH */

@@ -1,0 +1,564 @@
+/*
+ * gjd_kernels.cu — the sm_100a kernels of the decode path.
+ *
+ *   k_build_luts    DHT (BITS/HUFFVAL) -> flattened lookup tables, one block per table set
+ *   k_fill_maps     sequence -> image and tile -> image maps
+ *   k_huff_sync     cold decode of every subsequence + self-synchronisation inside a sequence
+ *   k_huff_fix      boundary fix-up between sequences
+ *   k_seq_scan      exclusive scan of per-sequence coefficient counts (per image)
+ *   k_huff_write    re-decode from the synchronised states, scatter coefficients / DC differences
+ *   k_dc_tilebase   DC predictor at the start of every 32-MCU tile
+ *   k_transform     DC prefix + dequantise + dezigzag + integer IDCT + colour + RGB store
+ *
+ * Stage structure after the reference's decodeImage / parallelHuffManDecode
+ * (cuda-decoder/src/parser.cu:613-661, 132-208); none of its code is reused.
+ */
+#include "gjd_kernels.h"
+
+#include "gjd_devfn.cuh"
+
+#define GJD_SYNC_THREADS 256
+static_assert(GJD_SYNC_THREADS == GJD_SEQ_SUBS, "one thread per subsequence of a sequence");
+
+/* ------------------------------------------------------------------ small helpers ----- */
+
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) >= o) v += t;
+    }
+    return v;
+}
+
+/* Exclusive scan over a 256-thread block; *total gets the block sum. ws: 8 words of shared memory. */
+__device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* ws, uint32_t* total) {
+    uint32_t incl = warp_incl_scan(v);
+    uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    __syncthreads();   /* ws may still be read from a previous call */
+    if (lane == 31) ws[wid] = incl;
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        uint32_t t = ws[w];
+        if (w < (int)wid) base += t;
+        tot += t;
+    }
+    *total = tot;
+    return base + incl - v;
+}
+
+__device__ __forceinline__ void copy_lut_to_smem(GjdLutSet* dst, const GjdLutSet* src) {
+    static_assert(sizeof(GjdLutSet) % 16 == 0, "GjdLutSet must be a multiple of 16 bytes");
+    const uint4* s = reinterpret_cast<const uint4*>(src);
+    uint4* d = reinterpret_cast<uint4*>(dst);
+    for (uint32_t i = threadIdx.x; i < sizeof(GjdLutSet) / 16; i += blockDim.x) d[i] = __ldg(s + i);
+}
+
+/* ------------------------------------------------------------------ tables and maps --- */
+
+__global__ void __launch_bounds__(256) k_build_luts(const GjdDhtSet* __restrict__ dht, GjdLutSet* __restrict__ luts) {
+    const GjdDhtSet& in = dht[blockIdx.x];
+    GjdLutSet& out = luts[blockIdx.x];
+    __shared__ uint32_t lim[4][17];
+    __shared__ int32_t off[4][17];
+    if (threadIdx.x < 4) {
+        gjd_canonical(in.bits[threadIdx.x], lim[threadIdx.x], off[threadIdx.x]);
+        for (int L = 0; L <= 16; L++) {
+            out.lim[threadIdx.x][L] = lim[threadIdx.x][L];
+            out.off[threadIdx.x][L] = off[threadIdx.x][L];
+        }
+        out.isdc[threadIdx.x] = in.isdc[threadIdx.x];
+    }
+    for (uint32_t i = threadIdx.x; i < 4 * 256; i += blockDim.x) out.vals[i >> 8][i & 255] = in.vals[i >> 8][i & 255];
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < 4 * GJD_LUT_SIZE; i += blockDim.x) {
+        uint32_t t = i / GJD_LUT_SIZE, j = i % GJD_LUT_SIZE;
+        out.lut[t][j] = gjd_lut_entry(lim[t], off[t], in.vals[t], in.isdc[t], j);
+    }
+}
+
+__global__ void __launch_bounds__(128) k_fill_maps(GjdDevBatch b) {
+    uint32_t img = blockIdx.x;
+    const GjdImage& d = b.imgs[img];
+    for (uint32_t i = threadIdx.x; i < d.seq_count; i += blockDim.x) b.seq_img[d.seq_first + i] = img;
+    for (uint32_t i = threadIdx.x; i < d.tile_count; i += blockDim.x) b.tile_img[d.tile_first + i] = img;
+}
+
+/* ------------------------------------------------------------------ entropy: sync ----- */
+/*
+ * One block per sequence (256 subsequences of 1024 bits of one image), one thread per subsequence.
+ * Phase 1: every thread decodes its own subsequence from a cold state (component 0, zigzag 0, first
+ * bit of the subsequence).  Phase 2, in lock-step rounds: thread i carries its running state into
+ * subsequence i+r, compares the end state with the one stored there and overwrites it; a match means
+ * its chain has merged with the chain that started later, and the thread retires.
+ */
+__global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
+    __shared__ GjdLutSet lut;
+    __shared__ uint32_t sp[GJD_SEQ_SUBS];
+    __shared__ uint32_t sn[GJD_SEQ_SUBS];
+
+    const uint32_t g = blockIdx.x, tid = threadIdx.x;
+    const GjdImage& d = b.imgs[b.seq_img[g]];
+    const uint32_t ls = g - d.seq_first;
+    const uint32_t sub0 = ls * GJD_SEQ_SUBS;
+    const uint32_t sub_count = d.sub_count, scan_bits = d.scan_bits;
+    const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
+    const uint32_t tabsel = gjd_pack_tabsel(d.tabsel);
+    copy_lut_to_smem(&lut, b.luts + d.lut_id);
+    __syncthreads();
+
+    const bool active = sub0 + tid < sub_count;
+    GjdState st;
+    st.p = (sub0 + tid) * GJD_SUBSEQ_BITS;
+    st.n = 0;
+    st.pos = 0;
+    uint32_t bad = 0;
+    if (active) {
+        uint32_t end = min((sub0 + tid + 1) * GJD_SUBSEQ_BITS, scan_bits);
+        gjd_decode_span<false>(scan, &lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
+    }
+    sp[tid] = st.p;
+    sn[tid] = (st.n << 8) | st.pos;
+    __syncthreads();
+
+    bool synced = !active;
+    for (uint32_t r = 1; r < GJD_SEQ_SUBS; r++) {
+        uint32_t j = tid + r;
+        bool go = !synced && j < GJD_SEQ_SUBS && sub0 + j < sub_count;
+        bool still = false;
+        if (go) {
+            st.n = 0;
+            uint32_t end = min((sub0 + j + 1) * GJD_SUBSEQ_BITS, scan_bits);
+            gjd_decode_span<false>(scan, &lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
+            bool match = sp[j] == st.p && (sn[j] & 255u) == st.pos;
+            sp[j] = st.p;
+            sn[j] = (st.n << 8) | st.pos;
+            if (match) synced = true; else still = true;
+        } else {
+            synced = true;
+        }
+        if (!__syncthreads_or(still)) break;
+    }
+    if (active) b.sinfo[(size_t)g * GJD_SEQ_SUBS + tid] = make_uint2(sp[tid], sn[tid]);
+}
+
+/*
+ * One thread per sequence that is not the first of its image: continue from the final state of the
+ * previous sequence until the chain merges with what k_huff_sync left.  A chain that crosses the
+ * whole sequence without merging is counted in *nosync; the host then repeats this kernel.
+ */
+__global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= b.n_seq) return;
+    uint32_t img = b.seq_img[g];
+    const GjdImage& d = b.imgs[img];
+    uint32_t ls = g - d.seq_first;
+    if (ls == 0) return;
+    const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
+    const GjdLutSet* lut = b.luts + d.lut_id;
+    const uint32_t tabsel = gjd_pack_tabsel(d.tabsel);
+    const uint32_t scan_bits = d.scan_bits;
+    uint2* si = b.sinfo + (size_t)g * GJD_SEQ_SUBS;
+    uint2 prev = si[-1];
+    GjdState st;
+    st.p = prev.x;
+    st.pos = prev.y & 255u;
+    uint32_t bad = 0;
+    bool merged = false;
+    uint32_t t = 0;
+    for (; t < GJD_SEQ_SUBS; t++) {
+        uint32_t sub = ls * GJD_SEQ_SUBS + t;
+        if (sub >= d.sub_count) { merged = true; break; }
+        st.n = 0;
+        uint32_t end = min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
+        gjd_decode_span<false>(scan, lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
+        uint2 old = si[t];
+        si[t] = make_uint2(st.p, (st.n << 8) | st.pos);
+        if (old.x == st.p && (old.y & 255u) == st.pos) { merged = true; break; }
+    }
+    if (!merged && ls + 1 < d.seq_count) {
+        atomicAdd(b.nosync, 1u);
+    }
+}
+
+/* ------------------------------------------------------------------ entropy: scan ----- */
+/*
+ * One block per image: coefficient count of every sequence, exclusive scan over the image's
+ * sequences -> seq_base.  Also checks the image's total against 192 * MCUs.
+ */
+__global__ void __launch_bounds__(256) k_seq_scan(GjdDevBatch b) {
+    __shared__ uint32_t ws[8];
+    const uint32_t img = blockIdx.x, tid = threadIdx.x;
+    const GjdImage& d = b.imgs[img];
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < d.seq_count; base += 256) {
+        uint32_t s = base + tid, total = 0;
+        if (s < d.seq_count) {
+            const uint2* si = b.sinfo + (size_t)(d.seq_first + s) * GJD_SEQ_SUBS;
+            uint32_t cnt = min(GJD_SEQ_SUBS, d.sub_count - s * GJD_SEQ_SUBS);
+            for (uint32_t t = 0; t < cnt; t++) total += si[t].y >> 8;
+        }
+        uint32_t blocksum;
+        uint32_t excl = block_excl_scan_256(total, ws, &blocksum);
+        if (s < d.seq_count) b.seq_base[d.seq_first + s] = carry + excl;
+        carry += blocksum;
+    }
+    if (tid == 0 && carry != 192u * d.mcu_count) atomicOr(b.status + img, GJD_DEV_BADCOUNT);
+}
+
+/* ------------------------------------------------------------------ entropy: write ---- */
+
+struct GjdCoefSink {
+    int16_t* coef;      /* image's first tile */
+    int16_t* dcdiff;    /* image's first block */
+    uint32_t idx0;      /* coefficient index at state.n == 0 */
+    uint32_t total;     /* 192 * mcu_count */
+    uint32_t* bad;
+    __device__ __forceinline__ void operator()(uint32_t rel, int v, uint32_t) const {
+        uint32_t idx = idx0 + rel;
+        if (idx >= total) { *bad |= GJD_DEV_BADCOUNT; return; }
+        uint32_t blk = idx >> 6, k = idx & 63u;
+        if (k == 0u) {
+            dcdiff[blk] = (int16_t)v;
+        } else {
+            uint32_t mcu = blk / 3u, c = blk - mcu * 3u;
+            uint32_t tile = mcu >> 5, lane = mcu & 31u;
+            size_t a = (size_t)tile * GJD_TILE_I16 + (((c << 3) + (k >> 3)) * 32u + lane) * 8u + (k & 7u);
+            coef[a] = (int16_t)v;
+        }
+    }
+};
+
+/*
+ * One block per sequence.  Thread i starts from the synchronised end state of subsequence i-1, at
+ * coefficient index seq_base + (block-exclusive scan of the counts), and writes every non-zero AC
+ * coefficient to its tiled slot and every DC difference to dcdiff.
+ */
+__global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_write(GjdDevBatch b) {
+    __shared__ GjdLutSet lut;
+    __shared__ uint32_t ws[8];
+    const uint32_t g = blockIdx.x, tid = threadIdx.x;
+    const uint32_t img = b.seq_img[g];
+    const GjdImage& d = b.imgs[img];
+    const uint32_t ls = g - d.seq_first;
+    const uint32_t sub = ls * GJD_SEQ_SUBS + tid;
+    const uint32_t scan_bits = d.scan_bits;
+    const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
+    const uint32_t tabsel = gjd_pack_tabsel(d.tabsel);
+    const bool active = sub < d.sub_count;
+    const uint2* si = b.sinfo + (size_t)g * GJD_SEQ_SUBS;
+    copy_lut_to_smem(&lut, b.luts + d.lut_id);
+
+    uint32_t n = active ? (si[tid].y >> 8) : 0u;
+    uint32_t blocksum;
+    uint32_t excl = block_excl_scan_256(n, ws, &blocksum);   /* has the __syncthreads the LUT copy needs */
+    if (!active) return;
+
+    GjdState st;
+    st.p = 0; st.n = 0; st.pos = 0;
+    if (sub != 0u) {
+        uint2 prev = si[(int)tid - 1];
+        st.p = prev.x;
+        st.pos = prev.y & 255u;
+    }
+    uint32_t bad = 0;
+    GjdCoefSink sink;
+    sink.coef = b.coef + d.coef_off;
+    sink.dcdiff = b.dcdiff + (size_t)d.blk_first;
+    sink.idx0 = b.seq_base[g] + excl;
+    sink.total = 192u * d.mcu_count;
+    sink.bad = &bad;
+    if (sink.idx0 % 192u != st.pos && st.p < scan_bits) bad |= GJD_DEV_BADSTATE;
+    uint32_t end = min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
+    gjd_decode_span<true>(scan, &lut, tabsel, end, scan_bits, st, sink, bad);
+    if (bad) atomicOr(b.status + img, bad);
+}
+
+/* ------------------------------------------------------------------ DC predictors ----- */
+/*
+ * One block per image.  Thread t sums the DC differences of tile t (32 MCUs x 3 components =
+ * 96 int16, contiguous), the block scans the sums: tilebase[tile] = predictors at the tile start
+ * (cpp-decoder/src/parser.cpp:108-111,141: three running predictors, never reset).
+ */
+__global__ void __launch_bounds__(256) k_dc_tilebase(GjdDevBatch b) {
+    __shared__ uint32_t ws[8];
+    const uint32_t tid = threadIdx.x;
+    const GjdImage& d = b.imgs[blockIdx.x];
+    const uint4* dc = reinterpret_cast<const uint4*>(b.dcdiff + (size_t)d.blk_first);
+    int carry[3] = {0, 0, 0};
+    for (uint32_t base = 0; base < d.tile_count; base += 256) {
+        uint32_t t = base + tid;
+        int sum[3] = {0, 0, 0};
+        if (t < d.tile_count) {
+#pragma unroll
+            for (int i = 0; i < 12; i++) {
+                uint4 v = __ldg(dc + (size_t)t * 12 + i);
+                uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    sum[(i * 8 + j * 2) % 3] += (int)(int16_t)(w[j] & 0xffffu);
+                    sum[(i * 8 + j * 2 + 1) % 3] += (int)w[j] >> 16;
+                }
+            }
+        }
+        int excl[3];
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            uint32_t tot;
+            excl[c] = (int)block_excl_scan_256((uint32_t)sum[c], ws, &tot) + carry[c];
+            carry[c] += (int)tot;
+        }
+        if (t < d.tile_count) b.tilebase[d.tile_first + t] = make_int4(excl[0], excl[1], excl[2], 0);
+    }
+}
+
+/* ------------------------------------------------------------------ transform --------- */
+
+/* zigzag index -> natural index (inverse of GJD_ZZ_TABLE) */
+__host__ __device__ constexpr int gjd_nat_of_zz(int k) {
+    constexpr int zz[64] = GJD_ZZ_TABLE;
+    int r = 0;
+    for (int i = 0; i < 64; i++)
+        if (zz[i] == k) r = i;
+    return r;
+}
+template <int K> struct GjdNat { static constexpr int value = gjd_nat_of_zz(K); };
+
+template <int K> struct GjdDequant {
+    /* w[]: 32 packed words (two int16 each, zigzag order); q: 64 ints (zigzag order) in shared memory */
+    static __device__ __forceinline__ void run(const uint32_t* w, const int4* q, int dc, int* v) {
+        GjdDequant<K - 1>::run(w, q, dc, v);
+        int4 qq = q[K / 4];
+        int qk = (K % 4 == 0) ? qq.x : (K % 4 == 1) ? qq.y : (K % 4 == 2) ? qq.z : qq.w;
+        int cv = (K == 0) ? dc : ((K & 1) ? ((int)w[K / 2] >> 16) : (int)(int16_t)(w[K / 2] & 0xffffu));
+        v[GjdNat<K>::value] = cv * qk;
+    }
+};
+template <> struct GjdDequant<-1> {
+    static __device__ __forceinline__ void run(const uint32_t*, const int4*, int, int*) {}
+};
+
+__device__ __forceinline__ int warp_incl_scan_i(int v, uint32_t lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, v, o);
+        if ((int)lane >= o) v += t;
+    }
+    return v;
+}
+
+#define GJD_TRANSFORM_WARPS 4
+
+/*
+ * One warp per tile of 32 MCUs, one thread per MCU (three 8x8 blocks -> 64 RGB pixels).
+ * Per component: eight coalesced 16-byte loads (the tile layout puts lane l's chunk ch at
+ * (ch*32 + l)*16 bytes), dequantise from a broadcast shared-memory copy of the quantisation table,
+ * dezigzag by compile-time register renaming, integer IDCT in registers.  Cb and Cr are parked
+ * packed in 64 registers; after the Y block the colour conversion runs per row and each row of
+ * each plane leaves as one 8-byte store (a warp covers 256 contiguous bytes of a row).
+ */
+__global__ void __launch_bounds__(32 * GJD_TRANSFORM_WARPS) k_transform(GjdDevBatch b) {
+    __shared__ int4 sq[GJD_TRANSFORM_WARPS][48];
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    const uint32_t tile = blockIdx.x * GJD_TRANSFORM_WARPS + warp;
+    if (tile >= b.n_tile) return;
+    const GjdImage& d = b.imgs[b.tile_img[tile]];
+    const uint32_t ltile = tile - d.tile_first;
+    const uint32_t mcu = ltile * GJD_TILE_MCUS + lane;
+    const bool valid = mcu < d.mcu_count;
+
+    const int4* qg = reinterpret_cast<const int4*>(b.quants + d.quant_id);
+    sq[warp][lane] = __ldg(qg + lane);
+    if (lane < 16) sq[warp][32 + lane] = __ldg(qg + 32 + lane);
+
+    const int16_t* dcd = b.dcdiff + (size_t)d.blk_first + (size_t)ltile * 96u + lane * 3u;
+    const int4 tb = b.tilebase[tile];
+    const int dcv0 = warp_incl_scan_i((int)dcd[0], lane) + tb.x;
+    const int dcv1 = warp_incl_scan_i((int)dcd[1], lane) + tb.y;
+    const int dcv2 = warp_incl_scan_i((int)dcd[2], lane) + tb.z;
+    __syncwarp();
+    if (!valid) return;
+
+    const uint4* cp = reinterpret_cast<const uint4*>(b.coef + d.coef_off + (size_t)ltile * GJD_TILE_I16) + lane;
+    const uint32_t W = d.width, H = d.height;
+    const uint32_t by = mcu / d.mcus_x, bx = mcu - by * d.mcus_x;
+    const uint32_t x0 = bx * 8u, y0 = by * 8u;
+    uint8_t* out = d.out_is_ptr ? reinterpret_cast<uint8_t*>(d.out_off) : b.rgb + d.out_off;
+    const size_t pitch = d.row_pitch, pstride = d.plane_stride;
+    const bool fast = (x0 + 8u <= W) && (((size_t)out | pitch | pstride) & 7u) == 0;
+
+    uint32_t pc[64];
+#pragma unroll 1
+    for (int it = 0; it < 3; it++) {
+        const int c = (it == 2) ? 0 : it + 1;   /* Cb, Cr, then Y */
+        uint32_t w[32];
+#pragma unroll
+        for (int ch = 0; ch < 8; ch++) {
+            uint4 t = __ldg(cp + (c * 8 + ch) * 32);
+            w[4 * ch] = t.x; w[4 * ch + 1] = t.y; w[4 * ch + 2] = t.z; w[4 * ch + 3] = t.w;
+        }
+        int v[64];
+        GjdDequant<63>::run(w, &sq[warp][c * 16], (c == 0) ? dcv0 : (c == 1) ? dcv1 : dcv2, v);
+        gjd_idct8x8(v);
+        if (it == 0) {
+#pragma unroll
+            for (int i = 0; i < 64; i++) pc[i] = (uint32_t)v[i];
+        } else if (it == 1) {
+#pragma unroll
+            for (int i = 0; i < 64; i++) pc[i] |= (uint32_t)v[i] << 16;
+        } else {
+#pragma unroll
+            for (int r = 0; r < 8; r++) {
+                if (y0 + r < H) {
+                    uint32_t pr[2] = {0, 0}, pg[2] = {0, 0}, pb[2] = {0, 0};
+#pragma unroll
+                    for (int x = 0; x < 8; x++) {
+                        int R, G, B;
+                        gjd_color(v[8 * r + x], (int)(pc[8 * r + x] & 0xffffu), (int)(pc[8 * r + x] >> 16), R, G, B);
+                        pr[x >> 2] |= (uint32_t)R << (8 * (x & 3));
+                        pg[x >> 2] |= (uint32_t)G << (8 * (x & 3));
+                        pb[x >> 2] |= (uint32_t)B << (8 * (x & 3));
+                    }
+                    uint8_t* row = out + (size_t)(y0 + r) * pitch + x0;
+                    if (fast) {
+                        *reinterpret_cast<uint2*>(row) = make_uint2(pr[0], pr[1]);
+                        *reinterpret_cast<uint2*>(row + pstride) = make_uint2(pg[0], pg[1]);
+                        *reinterpret_cast<uint2*>(row + 2 * pstride) = make_uint2(pb[0], pb[1]);
+                    } else {
+#pragma unroll
+                        for (int x = 0; x < 8; x++) {
+                            if (x0 + x < W) {
+                                row[x] = (uint8_t)(pr[x >> 2] >> (8 * (x & 3)));
+                                row[pstride + x] = (uint8_t)(pg[x >> 2] >> (8 * (x & 3)));
+                                row[2 * pstride + x] = (uint8_t)(pb[x >> 2] >> (8 * (x & 3)));
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
+
+/* ------------------------------------------------------------------ test hooks -------- */
+
+/* Quantised coefficients of one image in the reference layout mcu*192 + comp*64 + k, absolute DC. */
+__global__ void __launch_bounds__(128) k_export_coefs(GjdDevBatch b, uint32_t img, int16_t* __restrict__ out) {
+    const GjdImage& d = b.imgs[img];
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    const uint32_t ltile = blockIdx.x * 4 + warp;
+    if (ltile >= d.tile_count) return;
+    const uint32_t mcu = ltile * GJD_TILE_MCUS + lane;
+    const int16_t* dcd = b.dcdiff + (size_t)d.blk_first + (size_t)ltile * 96u + lane * 3u;
+    const int4 tb = b.tilebase[d.tile_first + ltile];
+    int dc[3];
+    dc[0] = warp_incl_scan_i((int)dcd[0], lane) + tb.x;
+    dc[1] = warp_incl_scan_i((int)dcd[1], lane) + tb.y;
+    dc[2] = warp_incl_scan_i((int)dcd[2], lane) + tb.z;
+    if (mcu >= d.mcu_count) return;
+    const int16_t* tile = b.coef + d.coef_off + (size_t)ltile * GJD_TILE_I16;
+    for (uint32_t c = 0; c < 3; c++)
+        for (uint32_t k = 0; k < 64; k++) {
+            int16_t v = tile[(((c << 3) + (k >> 3)) * 32u + lane) * 8u + (k & 7u)];
+            if (k == 0) v = (int16_t)dc[c];
+            out[(size_t)mcu * 192u + c * 64u + k] = v;
+        }
+}
+
+__global__ void k_test_color(const int16_t* __restrict__ y, const int16_t* __restrict__ cb,
+                             const int16_t* __restrict__ cr, size_t n, uint8_t* __restrict__ r,
+                             uint8_t* __restrict__ g, uint8_t* __restrict__ bl) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int R, G, B;
+    gjd_color((int)y[i] + 256, (int)cb[i] + 256, (int)cr[i] + 256, R, G, B);
+    r[i] = (uint8_t)R; g[i] = (uint8_t)G; bl[i] = (uint8_t)B;
+}
+
+__global__ void k_test_idct(const int16_t* __restrict__ coef, size_t nblocks, const int32_t* __restrict__ quant,
+                            int16_t* __restrict__ out) {
+    __shared__ int4 q[16];
+    if (threadIdx.x < 16) q[threadIdx.x] = reinterpret_cast<const int4*>(quant)[threadIdx.x];
+    __syncthreads();
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nblocks) return;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(coef + i * 64);
+    uint32_t w[32];
+#pragma unroll
+    for (int j = 0; j < 32; j++) w[j] = src[j];
+    int v[64];
+    GjdDequant<63>::run(w, q, (int)(int16_t)(w[0] & 0xffffu), v);
+    gjd_idct8x8(v);
+#pragma unroll
+    for (int j = 0; j < 64; j++) out[i * 64 + j] = (int16_t)(v[j] - 256);
+}
+
+/* ------------------------------------------------------------------ launchers --------- */
+
+#define GJD_CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
+
+cudaError_t gjd_launch_build_luts(const GjdDhtSet* dht, GjdLutSet* luts, uint32_t n, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    k_build_luts<<<n, 256, 0, s>>>(dht, luts);
+    return cudaGetLastError();
+}
+
+cudaError_t gjd_launch_fill_maps(const GjdDevBatch& b, cudaStream_t s) {
+    if (b.n_img == 0) return cudaSuccess;
+    k_fill_maps<<<b.n_img, 128, 0, s>>>(b);
+    return cudaGetLastError();
+}
+
+cudaError_t gjd_launch_fix(const GjdDevBatch& b, cudaStream_t s) {
+    k_huff_fix<<<(b.n_seq + 127) / 128, 128, 0, s>>>(b);
+    return cudaGetLastError();
+}
+
+cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdStageEvents* ev,
+                                int transform_variant, int* launches, bool skip_sync) {
+    (void)transform_variant;
+    int n = 0;
+    if (b.n_img == 0) { if (launches) *launches = 0; return cudaSuccess; }
+    if (ev) GJD_CK(cudaEventRecord(ev->e[0], s));
+    GJD_CK(cudaMemsetAsync(b.coef, 0, (size_t)b.n_tile * GJD_TILE_I16 * sizeof(int16_t), s));
+    GJD_CK(cudaMemsetAsync(b.dcdiff, 0, (size_t)b.n_tile * 96 * sizeof(int16_t), s));
+    GJD_CK(cudaMemsetAsync(b.status, 0, (size_t)b.n_img * sizeof(uint32_t), s));
+    GJD_CK(cudaMemsetAsync(b.nosync, 0, sizeof(uint32_t), s));
+    if (ev) GJD_CK(cudaEventRecord(ev->e[1], s));
+    if (!skip_sync) {
+        k_huff_sync<<<b.n_seq, GJD_SYNC_THREADS, 0, s>>>(b); n++;
+        k_huff_fix<<<(b.n_seq + 127) / 128, 128, 0, s>>>(b); n++;
+    }
+    if (ev) GJD_CK(cudaEventRecord(ev->e[2], s));
+    k_seq_scan<<<b.n_img, 256, 0, s>>>(b); n++;
+    k_huff_write<<<b.n_seq, GJD_SYNC_THREADS, 0, s>>>(b); n++;
+    k_dc_tilebase<<<b.n_img, 256, 0, s>>>(b); n++;
+    if (ev) GJD_CK(cudaEventRecord(ev->e[3], s));
+    k_transform<<<(b.n_tile + GJD_TRANSFORM_WARPS - 1) / GJD_TRANSFORM_WARPS, 32 * GJD_TRANSFORM_WARPS, 0, s>>>(b); n++;
+    if (ev) GJD_CK(cudaEventRecord(ev->e[4], s));
+    if (launches) *launches = n;
+    return cudaGetLastError();
+}
+
+cudaError_t gjd_launch_export_coefs(const GjdDevBatch& b, uint32_t img, int16_t* out, cudaStream_t s) {
+    /* tile_count is only known on the device side of the descriptor; the caller passes n_tile of a
+     * single-image batch */
+    k_export_coefs<<<(b.n_tile + 3) / 4, 128, 0, s>>>(b, img, out);
+    return cudaGetLastError();
+}
+
+cudaError_t gjd_launch_test_color(const int16_t* y, const int16_t* cb, const int16_t* cr, size_t n,
+                                  uint8_t* r, uint8_t* g, uint8_t* bl, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    k_test_color<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(y, cb, cr, n, r, g, bl);
+    return cudaGetLastError();
+}
+
+cudaError_t gjd_launch_test_idct(const int16_t* coef, size_t nblocks, const int32_t* quant, int16_t* out,
+                                 cudaStream_t s) {
+    if (nblocks == 0) return cudaSuccess;
+    k_test_idct<<<(unsigned)((nblocks + 127) / 128), 128, 0, s>>>(coef, nblocks, quant, out);
+    return cudaGetLastError();
+}

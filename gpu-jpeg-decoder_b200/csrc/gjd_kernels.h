@@ -1,0 +1,54 @@
+/*
+ * gjd_kernels.h — launchers of the sm_100a kernels (gjd_kernels.cu).  Internal.
+ */
+#ifndef GJD_KERNELS_H
+#define GJD_KERNELS_H
+
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "gjd_types.h"
+
+/* Device view of one resident batch (see the HBM layout in gjd_types.h). */
+struct GjdDevBatch {
+    const GjdImage* imgs;
+    uint32_t n_img;
+    const uint8_t* scan;
+    const GjdLutSet* luts;
+    const GjdQuantSet* quants;
+    uint2* sinfo;          /* [n_seq * GJD_SEQ_SUBS] */
+    uint32_t* seq_img;     /* [n_seq]  sequence -> image */
+    uint32_t* seq_base;    /* [n_seq]  coefficient index (within the image) at the sequence start */
+    uint32_t n_seq;
+    int16_t* coef;         /* [n_tile * GJD_TILE_I16] */
+    int16_t* dcdiff;       /* [n_tile * 96] */
+    int4* tilebase;        /* [n_tile] DC predictors at the tile start (x,y,z = comp 0,1,2) */
+    uint32_t* tile_img;    /* [n_tile] tile -> image */
+    uint32_t n_tile;
+    uint8_t* rgb;          /* output arena (images with out_is_ptr == 0) */
+    uint32_t* status;      /* [n_img] GJD_DEV_* bits */
+    uint32_t* nosync;      /* [1] sequences whose boundary fix-up ran off the end of the sequence */
+};
+
+/* Stage timing events recorded by gjd_launch_pipeline: e[0] start, e[1] after the scratch clears,
+ * e[2] after the sync stages, e[3] after the write stages, e[4] after the transform. */
+struct GjdStageEvents {
+    cudaEvent_t e[5];
+};
+
+cudaError_t gjd_launch_build_luts(const GjdDhtSet* dht, GjdLutSet* luts, uint32_t n, cudaStream_t s);
+cudaError_t gjd_launch_fill_maps(const GjdDevBatch& b, cudaStream_t s);
+/* Clears scratch and runs every decode stage. transform_variant selects the transform kernel
+ * implementation (0 = default).  Returns the number of kernel launches in *launches. */
+cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdStageEvents* ev,
+                                int transform_variant, int* launches, bool skip_sync = false);
+/* Re-run of the boundary fix-up only (slow path when *nosync != 0). */
+cudaError_t gjd_launch_fix(const GjdDevBatch& b, cudaStream_t s);
+cudaError_t gjd_launch_export_coefs(const GjdDevBatch& b, uint32_t img, int16_t* out, cudaStream_t s);
+cudaError_t gjd_launch_test_color(const int16_t* y, const int16_t* cb, const int16_t* cr, size_t n,
+                                  uint8_t* r, uint8_t* g, uint8_t* bl, cudaStream_t s);
+cudaError_t gjd_launch_test_idct(const int16_t* coef, size_t nblocks, const int32_t* quant, int16_t* out,
+                                 cudaStream_t s);
+
+#endif

@@ -1,0 +1,162 @@
+/*
+ * gjd_parse.cpp — host JPEG marker parse + scan unstuffing.  See gjd_parse.h.
+ */
+#include "gjd_parse.h"
+
+#include <string.h>
+
+#include "../../include/gjd.h"
+
+namespace {
+
+inline uint32_t be16(const uint8_t* p) { return ((uint32_t)p[0] << 8) | p[1]; }
+
+/* DQT payload: one or more (Pq|Tq, 64 bytes) tables. */
+int parse_dqt(const uint8_t* p, size_t n, GjdParsed* o) {
+    while (n > 0) {
+        uint32_t pq = p[0] >> 4, tq = p[0] & 15;
+        if (tq > 3) return GJD_E_FORMAT;
+        if (pq != 0) return GJD_E_UNSUPPORTED;   /* 16-bit tables: not baseline 8-bit */
+        if (n < 65) return GJD_E_FORMAT;
+        memcpy(o->quant[tq], p + 1, 64);
+        o->quant_seen[tq] = 1;
+        p += 65;
+        n -= 65;
+    }
+    return GJD_OK;
+}
+
+/* DHT payload: one or more (Tc|Th, BITS[16], HUFFVAL) tables. */
+int parse_dht(const uint8_t* p, size_t n, GjdParsed* o) {
+    while (n > 0) {
+        if (n < 17) return GJD_E_FORMAT;
+        uint32_t tc = p[0] >> 4, th = p[0] & 15;
+        if (tc > 1 || th > 3) return GJD_E_FORMAT;
+        uint32_t total = 0, code = 0;
+        for (int i = 0; i < 16; i++) {
+            total += p[1 + i];
+            code = (code + p[1 + i]) << 1;
+            if (code > (2u << (i + 1))) return GJD_E_FORMAT;   /* oversubscribed code space */
+        }
+        if (total > 256 || n < 17 + total) return GJD_E_FORMAT;
+        if (th <= 1) {   /* baseline allows Th 0/1 only; other tables are ignored unless SOS selects them */
+            int slot = (int)(tc * 2 + th);
+            memcpy(o->dht.bits[slot], p + 1, 16);
+            memset(o->dht.vals[slot], 0, 256);
+            memcpy(o->dht.vals[slot], p + 17, total);
+            o->dht.isdc[slot] = tc == 0;
+            o->dht_seen[slot] = 1;
+        }
+        p += 17 + total;
+        n -= 17 + total;
+    }
+    return GJD_OK;
+}
+
+}  // namespace
+
+int gjd_parse_headers(const uint8_t* d, size_t len, GjdParsed* o) {
+    if (!d || !o) return GJD_E_ARG;
+    if (len < 4 || d[0] != 0xFF || d[1] != 0xD8) return GJD_E_FORMAT;
+    memset(&o->dht, 0, sizeof(o->dht));
+    o->file_end = d + len;
+    uint8_t comp_id[3] = {0, 0, 0};
+    bool have_sof = false;
+    size_t pos = 2;
+    for (;;) {
+        /* next marker: FF, optional fill FFs, code */
+        if (pos + 2 > len) return GJD_E_FORMAT;
+        if (d[pos] != 0xFF) return GJD_E_FORMAT;
+        while (pos + 1 < len && d[pos + 1] == 0xFF) pos++;
+        if (pos + 2 > len) return GJD_E_FORMAT;
+        uint32_t m = d[pos + 1];
+        pos += 2;
+        if (m == 0xD8 || m == 0x01 || (m >= 0xD0 && m <= 0xD7)) continue;   /* standalone */
+        if (m == 0xD9) return GJD_E_FORMAT;                                /* EOI before SOS */
+        if (pos + 2 > len) return GJD_E_FORMAT;
+        uint32_t seg = be16(d + pos);
+        if (seg < 2 || pos + seg > len) return GJD_E_FORMAT;
+        const uint8_t* body = d + pos + 2;
+        size_t blen = seg - 2;
+        switch (m) {
+            case 0xDB: { int rc = parse_dqt(body, blen, o); if (rc) return rc; break; }
+            case 0xC4: { int rc = parse_dht(body, blen, o); if (rc) return rc; break; }
+            case 0xC0: {
+                if (have_sof) return GJD_E_FORMAT;
+                if (blen < 6) return GJD_E_FORMAT;
+                uint32_t prec = body[0], nf = body[5];
+                o->height = (int32_t)be16(body + 1);
+                o->width = (int32_t)be16(body + 3);
+                if (prec != 8 || nf != 3) return GJD_E_UNSUPPORTED;
+                if (blen < 6 + 3 * nf) return GJD_E_FORMAT;
+                if (o->width <= 0 || o->height <= 0) return GJD_E_UNSUPPORTED;   /* DNL-defined height */
+                for (uint32_t c = 0; c < 3; c++) {
+                    comp_id[c] = body[6 + 3 * c];
+                    if (body[7 + 3 * c] != 0x11) return GJD_E_UNSUPPORTED;      /* 4:4:4 only */
+                    uint32_t tq = body[8 + 3 * c];
+                    if (tq > 3) return GJD_E_FORMAT;
+                    o->qsel[c] = (uint8_t)tq;
+                }
+                have_sof = true;
+                break;
+            }
+            case 0xC1: case 0xC2: case 0xC3: case 0xC5: case 0xC6: case 0xC7:
+            case 0xC9: case 0xCA: case 0xCB: case 0xCD: case 0xCE: case 0xCF:
+                return GJD_E_UNSUPPORTED;   /* extended / progressive / lossless / arithmetic */
+            case 0xDD:
+                if (blen < 2) return GJD_E_FORMAT;
+                o->restart_interval = be16(body);
+                break;
+            case 0xDA: {
+                if (!have_sof) return GJD_E_FORMAT;
+                if (blen < 1) return GJD_E_FORMAT;
+                uint32_t ns = body[0];
+                if (ns != 3) return GJD_E_UNSUPPORTED;   /* non-interleaved / multi-scan */
+                if (blen < 1 + 2 * ns + 3) return GJD_E_FORMAT;
+                for (uint32_t c = 0; c < 3; c++) {
+                    if (body[1 + 2 * c] != comp_id[c]) return GJD_E_UNSUPPORTED;
+                    uint32_t td = body[2 + 2 * c] >> 4, ta = body[2 + 2 * c] & 15;
+                    if (td > 1 || ta > 1) return GJD_E_UNSUPPORTED;
+                    if (!o->dht_seen[td] || !o->dht_seen[2 + ta]) return GJD_E_FORMAT;
+                    o->tabsel[c] = (uint8_t)td;
+                    o->tabsel[4 + c] = (uint8_t)(2 + ta);
+                }
+                const uint8_t* sp = body + 1 + 2 * ns;
+                if (sp[0] != 0 || sp[1] != 63 || sp[2] != 0) return GJD_E_UNSUPPORTED;
+                for (uint32_t c = 0; c < 3; c++)
+                    if (!o->quant_seen[o->qsel[c]]) return GJD_E_FORMAT;
+                if (o->restart_interval != 0) return GJD_E_UNSUPPORTED;   /* DRI/RSTn: SURVEY §8f-1 */
+                o->scan_begin = d + pos + seg;
+                return GJD_OK;
+            }
+            default:
+                break;   /* APPn, COM, anything else with a length: skipped */
+        }
+        pos += seg;
+    }
+}
+
+long gjd_unstuff(const uint8_t* p, const uint8_t* end, uint8_t* dst) {
+    uint8_t* o = dst;
+    for (;;) {
+        if (p >= end) return GJD_E_FORMAT;
+        const uint8_t* q = (const uint8_t*)memchr(p, 0xFF, (size_t)(end - p));
+        if (!q || q + 1 >= end) return GJD_E_FORMAT;   /* no EOI: the reference runs off the buffer */
+        size_t run = (size_t)(q - p);
+        memcpy(o, p, run);
+        o += run;
+        uint8_t m = q[1];
+        if (m == 0x00) {
+            *o++ = 0xFF;
+            p = q + 2;
+        } else if (m == 0xD9) {
+            return (long)(o - dst);
+        } else if (m == 0xFF) {
+            p = q + 1;   /* fill byte */
+        } else if (m >= 0xD0 && m <= 0xD7) {
+            return GJD_E_UNSUPPORTED;
+        } else {
+            return GJD_E_FORMAT;
+        }
+    }
+}

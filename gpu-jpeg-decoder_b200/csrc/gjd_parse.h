@@ -1,0 +1,38 @@
+/*
+ * gjd_parse.h — host-side JPEG container parse (the role of JPEGParser::extract,
+ * cpp-decoder/src/parser.cpp:24-103, and extract(), cuda-decoder/src/parser.cu:360-471).
+ */
+#ifndef GJD_PARSE_H
+#define GJD_PARSE_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include "gjd_types.h"
+
+struct GjdParsed {
+    int32_t width = 0, height = 0;
+    const uint8_t* scan_begin = nullptr;   /* first entropy-coded byte (after the SOS header)      */
+    const uint8_t* file_end = nullptr;     /* one past the last byte of the file                    */
+    GjdDhtSet dht;                         /* slots 0=DC0 1=DC1 2=AC0 3=AC1                        */
+    uint8_t dht_seen[4] = {0, 0, 0, 0};
+    uint8_t quant[4][64];                  /* by Tq, zigzag order as stored                         */
+    uint8_t quant_seen[4] = {0, 0, 0, 0};
+    uint8_t tabsel[8] = {0};               /* [c] DC slot, [4+c] AC slot of component c             */
+    uint8_t qsel[4] = {0};                 /* [c] Tq of component c                                 */
+    uint32_t restart_interval = 0;
+};
+
+/* Parse every marker segment up to and including the SOS header.  Returns a gjd_status.
+ * A superset of what the reference parser accepts: APPn/COM/unknown segments are
+ * skipped by length, DQT/DHT may hold several tables in any order, selectors in SOF0/SOS are
+ * honoured; everything outside the 8-bit 4:4:4 baseline single-scan contract is rejected with
+ * GJD_E_UNSUPPORTED instead of being mis-decoded. */
+int gjd_parse_headers(const uint8_t* jpg, size_t len, GjdParsed* out);
+
+/* Copy the entropy-coded segment [src, end) to dst, removing the stuffed 0x00 after every 0xFF and
+ * stopping at EOI (FF D9), exactly like the byte loop at cpp-decoder/src/parser.cpp:84-99 (and its
+ * twin cuda-decoder/src/parser.cu:450-462).  dst needs (end - src) bytes.  Returns the unstuffed
+ * length, or a negative gjd_status (truncated scan, RSTn, any other marker inside the scan). */
+long gjd_unstuff(const uint8_t* src, const uint8_t* end, uint8_t* dst);
+
+#endif

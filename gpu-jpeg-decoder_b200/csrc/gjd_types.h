@@ -1,0 +1,94 @@
+/*
+ * gjd_types.h — internal structures shared by the host code and the CUDA kernels.
+ *
+ * HBM layout of one resident batch (all offsets 256-byte aligned, one arena per kind):
+ *
+ *   scan   u8    unstuffed entropy-coded bytes of every image, each image starting on a
+ *                128-byte boundary and followed by >= 16 zero bytes.
+ *   sinfo  u32x2 one state per subsequence (GJD_SUBSEQ_BITS bits of one image's scan), padded per
+ *                image to a multiple of GJD_SEQ_SUBS ("sequence" = the subsequences one thread
+ *                block synchronises): {p, (n << 8) | pos}.
+ *   coef   i16   quantised AC coefficients in zigzag order, tiled for the transform kernel:
+ *                tile = 32 consecutive MCUs of one image; 16-byte chunk ch = comp*8 + k/8 of
+ *                MCU lane l sits at tile*12288 + (ch*32 + l)*16 bytes.  Slot k = 0 is unused
+ *                (DC lives in dcdiff).  Cleared before every run; the write pass stores non-zeros.
+ *   dcdiff i16   DC differences, [global block index] (block = mcu*3 + comp within the image).
+ *   tilebase i32 [tile][4]: DC predictor of each component at the start of the tile.
+ *   rgb    u8    planar R,G,B output per image in the caller's pitch/stride geometry.
+ */
+#ifndef GJD_TYPES_H
+#define GJD_TYPES_H
+
+#include <stdint.h>
+
+#define GJD_SUBSEQ_BITS   1024u    /* bits per subsequence (one thread)            */
+#define GJD_SUBSEQ_BYTES  (GJD_SUBSEQ_BITS / 8u)
+#define GJD_SEQ_SUBS      256u     /* subsequences per sequence (one thread block) */
+#define GJD_LUT_BITS      10       /* primary Huffman LUT index width              */
+#define GJD_LUT_SIZE      (1 << GJD_LUT_BITS)
+#define GJD_TILE_MCUS     32u      /* MCUs per coefficient tile (one warp)         */
+#define GJD_TILE_I16      (GJD_TILE_MCUS * 192u)
+
+/* LUT entry (u16):  [4:0] total bits = code length + value size (1..27)
+ *                   [8:5] value size (0..15)
+ *                   [13:9] advance = run + 1 (1..16); 0 = EOB (jump to the end of the block)
+ *                   [15]   code longer than GJD_LUT_BITS: resolve with the canonical tables   */
+#define GJD_LUT_SLOW 0x8000u
+
+/* One Huffman table set (the 4 tables an image uses), device-resident, built by k_build_luts.
+ * Slots: 0 = DC table of component 0, 1 = DC table of components 1/2 … the per-image
+ * comp -> slot mapping is in GjdImage::tabsel. */
+typedef struct GjdLutSet {
+    uint16_t lut[4][GJD_LUT_SIZE];   /* primary LUTs                                             */
+    uint32_t lim[4][17];             /* lim[L] = first unused code of length L, left-aligned to 16 bits */
+    int32_t  off[4][17];             /* valptr[L] - mincode[L]                                   */
+    uint8_t  vals[4][256];           /* HUFFVAL                                                  */
+    uint8_t  isdc[4];                /* 1 for DC tables (value size = symbol, advance = 1)       */
+    uint8_t  pad[12];
+} GjdLutSet;
+
+/* Raw DHT content the LUT builder consumes (host -> device). */
+typedef struct GjdDhtSet {
+    uint8_t bits[4][16];
+    uint8_t vals[4][256];
+    uint8_t isdc[4];
+    uint8_t pad[12];
+} GjdDhtSet;
+
+/* The quantisation table of each component, zigzag order, widened to i32 for broadcast loads. */
+typedef struct GjdQuantSet {
+    int32_t q[3][64];
+} GjdQuantSet;
+
+/* Per-image device descriptor. */
+typedef struct GjdImage {
+    uint64_t scan_off;      /* byte offset of the unstuffed scan in the scan arena            */
+    uint64_t coef_off;      /* i16 offset of the image's first tile in the coef arena         */
+    uint64_t out_off;       /* byte offset in the rgb arena, or a raw device address           */
+    uint64_t plane_stride;  /* bytes between planes                                            */
+    uint32_t row_pitch;     /* bytes between rows                                              */
+    uint32_t scan_bits;     /* unstuffed scan length in bits                                   */
+    uint32_t sub_count;     /* subsequences                                                    */
+    uint32_t seq_first;     /* global index of the image's first sequence                      */
+    uint32_t seq_count;
+    uint32_t tile_first;    /* global index of the image's first coefficient tile              */
+    uint32_t tile_count;
+    uint32_t blk_first;     /* global index of the image's first 8x8 block (dcdiff)            */
+    uint32_t mcu_count;
+    uint32_t mcus_x;
+    uint32_t width, height;
+    uint16_t lut_id;        /* index into the GjdLutSet array                                  */
+    uint16_t quant_id;      /* index into the GjdQuantSet array                                */
+    uint8_t  tabsel[8];     /* [c] = LUT slot of component c's DC table, [4+c] = AC table      */
+    uint8_t  qsel[4];       /* [c] = quant table (0/1) of component c                          */
+    uint32_t out_is_ptr;    /* out_off is an absolute device address (caller-owned buffer)     */
+    uint32_t pad0;
+} GjdImage;
+
+/* Device-written status bits per image. */
+#define GJD_DEV_BADCODE   1u   /* write pass met an unassigned Huffman code                     */
+#define GJD_DEV_BADSTATE  2u   /* synchronised state disagrees with the coefficient index       */
+#define GJD_DEV_BADCOUNT  4u   /* decoded coefficient count != 192 * MCUs                       */
+#define GJD_DEV_NOSYNC    8u   /* a sequence boundary did not converge in one fix-up round      */
+
+#endif

@@ -1,0 +1,254 @@
+/*
+ * hostsim.cpp — TEST SCAFFOLDING: steps the product's __host__ __device__ functions
+ * (gpu-jpeg-decoder_b200/csrc/gjd_devfn.cuh) and host parser on the CPU, thread by thread, in the
+ * same order the CUDA kernels of gjd_kernels.cu do (cold decode, lock-step synchronisation rounds,
+ * boundary fix-up, count scan, write pass into the tiled coefficient layout, tile DC bases,
+ * transform).  It exists because the build machine has no GPU: it lets `pytest -m "not gpu"` check
+ * the algorithm and every arithmetic function against the oracle before a kernel ever runs.
+ * It is not part of libgjd.so and nothing in the product can reach it.
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "../../gpu-jpeg-decoder_b200/csrc/gjd_devfn.cuh"
+#include "../../gpu-jpeg-decoder_b200/csrc/gjd_parse.h"
+#include "../../include/gjd.h"
+
+namespace {
+
+struct Sink {
+    int16_t* coef;
+    int16_t* dcdiff;
+    uint32_t idx0, total;
+    uint32_t* bad;
+    void operator()(uint32_t rel, int v, uint32_t) const {
+        uint32_t idx = idx0 + rel;
+        if (idx >= total) { *bad |= GJD_DEV_BADCOUNT; return; }
+        uint32_t blk = idx >> 6, k = idx & 63u;
+        if (k == 0u) {
+            dcdiff[blk] = (int16_t)v;
+        } else {
+            uint32_t mcu = blk / 3u, c = blk - mcu * 3u;
+            uint32_t tile = mcu >> 5, lane = mcu & 31u;
+            size_t a = (size_t)tile * GJD_TILE_I16 + (((c << 3) + (k >> 3)) * 32u + lane) * 8u + (k & 7u);
+            coef[a] = (int16_t)v;
+        }
+    }
+};
+
+const int kZZ[64] = GJD_ZZ_TABLE;
+
+}  // namespace
+
+extern "C" {
+
+/* stats: [0] max synchronisation rounds inside a sequence, [1] fix-up subsequences decoded,
+ *        [2] device status bits, [3] nosync count, [4] subsequences, [5] sequences */
+int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16_t* coef_out, uint8_t* rgb_out,
+                   int32_t* width, int32_t* height, uint32_t stats[6]) {
+    (void)subseq_bits_unused;
+    GjdParsed p;
+    int rc = gjd_parse_headers(jpg, len, &p);
+    if (rc) return rc;
+    if (width) *width = p.width;
+    if (height) *height = p.height;
+    std::vector<uint8_t> scanbuf((size_t)(p.file_end - p.scan_begin) + 64, 0);
+    long ulen = gjd_unstuff(p.scan_begin, p.file_end, scanbuf.data());
+    if (ulen < 0) return (int)ulen;
+    memset(scanbuf.data() + ulen, 0, 16);
+    /* word-aligned copy */
+    std::vector<uint32_t> scanw((scanbuf.size() + 3) / 4 + 4, 0);
+    memcpy(scanw.data(), scanbuf.data(), scanbuf.size());
+    const uint32_t* scan = scanw.data();
+
+    /* k_build_luts */
+    GjdLutSet* lut = (GjdLutSet*)calloc(1, sizeof(GjdLutSet));
+    for (int t = 0; t < 4; t++) {
+        gjd_canonical(p.dht.bits[t], lut->lim[t], lut->off[t]);
+        memcpy(lut->vals[t], p.dht.vals[t], 256);
+        lut->isdc[t] = p.dht.isdc[t];
+        for (uint32_t i = 0; i < GJD_LUT_SIZE; i++)
+            lut->lut[t][i] = gjd_lut_entry(lut->lim[t], lut->off[t], lut->vals[t], lut->isdc[t], i);
+    }
+    const uint32_t tabsel = gjd_pack_tabsel(p.tabsel);
+    const uint32_t scan_bits = (uint32_t)ulen * 8u;
+    const uint32_t sub_count = std::max<uint32_t>(1u, (scan_bits + GJD_SUBSEQ_BITS - 1) / GJD_SUBSEQ_BITS);
+    const uint32_t seq_count = (sub_count + GJD_SEQ_SUBS - 1) / GJD_SEQ_SUBS;
+    const uint32_t W = (uint32_t)p.width, H = (uint32_t)p.height;
+    const uint32_t mcus_x = (W + 7) / 8, mcu_count = mcus_x * ((H + 7) / 8);
+    const uint32_t tile_count = (mcu_count + 31) / 32;
+    std::vector<uint32_t> sp((size_t)seq_count * GJD_SEQ_SUBS, 0), sn((size_t)seq_count * GJD_SEQ_SUBS, 0);
+    uint32_t bad = 0, max_rounds = 0, fix_decodes = 0, nosync = 0, status = 0;
+
+    /* k_huff_sync: one "block" per sequence */
+    for (uint32_t g = 0; g < seq_count; g++) {
+        uint32_t sub0 = g * GJD_SEQ_SUBS;
+        std::vector<GjdState> st(GJD_SEQ_SUBS);
+        std::vector<char> synced(GJD_SEQ_SUBS, 0);
+        uint32_t* bp = &sp[(size_t)g * GJD_SEQ_SUBS];
+        uint32_t* bn = &sn[(size_t)g * GJD_SEQ_SUBS];
+        for (uint32_t tid = 0; tid < GJD_SEQ_SUBS; tid++) {
+            bool active = sub0 + tid < sub_count;
+            st[tid].p = (sub0 + tid) * GJD_SUBSEQ_BITS; st[tid].n = 0; st[tid].pos = 0;
+            if (active) {
+                uint32_t end = std::min((sub0 + tid + 1) * GJD_SUBSEQ_BITS, scan_bits);
+                gjd_decode_span<false>(scan, lut, tabsel, end, scan_bits, st[tid], GjdNoSink(), bad);
+            }
+            bp[tid] = st[tid].p;
+            bn[tid] = (st[tid].n << 8) | st[tid].pos;
+            synced[tid] = !active;
+        }
+        for (uint32_t r = 1; r < GJD_SEQ_SUBS; r++) {
+            bool any = false;
+            for (uint32_t tid = 0; tid < GJD_SEQ_SUBS; tid++) {
+                uint32_t j = tid + r;
+                bool go = !synced[tid] && j < GJD_SEQ_SUBS && sub0 + j < sub_count;
+                if (go) {
+                    st[tid].n = 0;
+                    uint32_t end = std::min((sub0 + j + 1) * GJD_SUBSEQ_BITS, scan_bits);
+                    gjd_decode_span<false>(scan, lut, tabsel, end, scan_bits, st[tid], GjdNoSink(), bad);
+                    bool match = bp[j] == st[tid].p && (bn[j] & 255u) == st[tid].pos;
+                    bp[j] = st[tid].p;
+                    bn[j] = (st[tid].n << 8) | st[tid].pos;
+                    if (match) synced[tid] = 1; else any = true;
+                } else {
+                    synced[tid] = 1;
+                }
+            }
+            max_rounds = std::max(max_rounds, r);
+            if (!any) break;
+        }
+    }
+    /* k_huff_fix, iterated to its fixed point like batch_wait does */
+    for (int iter = 0; iter < 65536; iter++) {
+        uint32_t ns = 0;
+        for (uint32_t g = 1; g < seq_count; g++) {
+            GjdState st;
+            st.p = sp[(size_t)g * GJD_SEQ_SUBS - 1];
+            st.pos = sn[(size_t)g * GJD_SEQ_SUBS - 1] & 255u;
+            bool merged = false;
+            for (uint32_t t = 0; t < GJD_SEQ_SUBS; t++) {
+                uint32_t sub = g * GJD_SEQ_SUBS + t;
+                if (sub >= sub_count) { merged = true; break; }
+                st.n = 0;
+                uint32_t end = std::min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
+                gjd_decode_span<false>(scan, lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
+                fix_decodes++;
+                size_t a = (size_t)g * GJD_SEQ_SUBS + t;
+                bool match = sp[a] == st.p && (sn[a] & 255u) == st.pos;
+                sp[a] = st.p;
+                sn[a] = (st.n << 8) | st.pos;
+                if (match) { merged = true; break; }
+            }
+            if (!merged && g + 1 < seq_count) ns++;
+        }
+        nosync += ns;
+        if (ns == 0) break;
+    }
+    /* k_seq_scan */
+    std::vector<uint32_t> seq_base(seq_count, 0);
+    uint32_t carry = 0;
+    for (uint32_t g = 0; g < seq_count; g++) {
+        seq_base[g] = carry;
+        uint32_t cnt = std::min<uint32_t>(GJD_SEQ_SUBS, sub_count - g * GJD_SEQ_SUBS);
+        for (uint32_t t = 0; t < cnt; t++) carry += sn[(size_t)g * GJD_SEQ_SUBS + t] >> 8;
+    }
+    if (carry != 192u * mcu_count) status |= GJD_DEV_BADCOUNT;
+    /* k_huff_write */
+    std::vector<int16_t> coef((size_t)tile_count * GJD_TILE_I16, 0), dcdiff((size_t)tile_count * 96, 0);
+    for (uint32_t g = 0; g < seq_count; g++) {
+        uint32_t excl = 0;
+        for (uint32_t tid = 0; tid < GJD_SEQ_SUBS; tid++) {
+            uint32_t sub = g * GJD_SEQ_SUBS + tid;
+            if (sub >= sub_count) break;
+            size_t a = (size_t)g * GJD_SEQ_SUBS + tid;
+            GjdState st; st.p = 0; st.n = 0; st.pos = 0;
+            if (sub != 0) { st.p = sp[a - 1]; st.pos = sn[a - 1] & 255u; }
+            uint32_t tbad = 0;
+            Sink sink{coef.data(), dcdiff.data(), seq_base[g] + excl, 192u * mcu_count, &tbad};
+            if (sink.idx0 % 192u != st.pos && st.p < scan_bits) tbad |= GJD_DEV_BADSTATE;
+            uint32_t end = std::min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
+            gjd_decode_span<true>(scan, lut, tabsel, end, scan_bits, st, sink, tbad);
+            status |= tbad;
+            excl += sn[a] >> 8;
+        }
+    }
+    /* k_dc_tilebase + k_transform / k_export_coefs */
+    int q[3][64];
+    for (int c = 0; c < 3; c++)
+        for (int k = 0; k < 64; k++) q[c][k] = p.quant[p.qsel[c]][k];
+    int pred[3] = {0, 0, 0};
+    for (uint32_t mcu = 0; mcu < mcu_count; mcu++) {
+        uint32_t tile = mcu >> 5, lane = mcu & 31u;
+        int samples[3][64];
+        for (int c = 0; c < 3; c++) {
+            pred[c] += dcdiff[(size_t)tile * 96 + lane * 3 + c];
+            int v[64];
+            for (int k = 0; k < 64; k++) {
+                int cv = coef[(size_t)tile * GJD_TILE_I16 + (((c << 3) + (k >> 3)) * 32u + lane) * 8u + (k & 7)];
+                if (k == 0) cv = pred[c];
+                if (coef_out) coef_out[(size_t)mcu * 192 + c * 64 + k] = (int16_t)cv;
+                int nat = 0;
+                for (int i = 0; i < 64; i++) if (kZZ[i] == k) nat = i;
+                v[nat] = cv * q[c][k];
+            }
+            gjd_idct8x8(v);
+            memcpy(samples[c], v, sizeof(v));
+        }
+        if (rgb_out) {
+            uint32_t by = mcu / mcus_x, bx = mcu % mcus_x;
+            for (int r = 0; r < 8; r++)
+                for (int x = 0; x < 8; x++) {
+                    uint32_t py = by * 8 + r, px = bx * 8 + x;
+                    if (py >= H || px >= W) continue;
+                    int R, G, B;
+                    gjd_color(samples[0][8 * r + x], samples[1][8 * r + x], samples[2][8 * r + x], R, G, B);
+                    size_t o = (size_t)py * W + px;
+                    rgb_out[o] = (uint8_t)R;
+                    rgb_out[(size_t)W * H + o] = (uint8_t)G;
+                    rgb_out[2 * (size_t)W * H + o] = (uint8_t)B;
+                }
+        }
+    }
+    if (stats) {
+        stats[0] = max_rounds; stats[1] = fix_decodes; stats[2] = status; stats[3] = nosync;
+        stats[4] = sub_count; stats[5] = seq_count;
+    }
+    free(lut);
+    return status ? GJD_E_CORRUPT : GJD_OK;
+}
+
+/* gjd_color on unbiased inputs, all (y, cb, cr) in [-256,255]^3 with y fixed: out[cb+256][cr+256][3] */
+void hostsim_color_plane(int y, uint8_t* out) {
+    for (int cb = -256; cb < 256; cb++)
+        for (int cr = -256; cr < 256; cr++) {
+            int R, G, B;
+            gjd_color(y + 256, cb + 256, cr + 256, R, G, B);
+            uint8_t* o = out + ((size_t)(cb + 256) * 512 + (cr + 256)) * 3;
+            o[0] = (uint8_t)R; o[1] = (uint8_t)G; o[2] = (uint8_t)B;
+        }
+}
+
+/* dequantised natural-order block in, clip(.) samples (unbiased) out */
+void hostsim_idct(const int32_t* in, int32_t* out, size_t nblocks) {
+    for (size_t b = 0; b < nblocks; b++) {
+        int v[64];
+        for (int i = 0; i < 64; i++) v[i] = in[b * 64 + i];
+        gjd_idct8x8(v);
+        for (int i = 0; i < 64; i++) out[b * 64 + i] = v[i] - 256;
+    }
+}
+
+int hostsim_parse(const uint8_t* jpg, size_t len, int32_t* w, int32_t* h) {
+    GjdParsed p;
+    int rc = gjd_parse_headers(jpg, len, &p);
+    if (w) *w = p.width;
+    if (h) *h = p.height;
+    return rc;
+}
+
+}  /* extern "C" */
