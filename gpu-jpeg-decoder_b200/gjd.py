@@ -1,0 +1,266 @@
+"""ctypes shim over libgjd.so (include/gjd.h).
+
+This is the Python mirror of the reference-facing interface: the reference's callers are C++
+(`cuda-decoder/main.cu:32-39`, `cuda-decoder/benchmark_thoughput/benchmark.cu:49-93`) and its
+harness is Python driving the CLI (`testing/compare.py:37-64`); the tests and bench.py use this shim
+to call the same C ABI those callers would bind.  There is no Python or CPU decode path here: if the
+shared library is missing the import of `lib()` raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "build", "libgjd.so")
+
+OK, E_ARG, E_CUDA, E_NOMEM, E_FORMAT, E_UNSUPPORTED, E_CORRUPT, E_NODEVICE, E_IO = 0, -1, -2, -3, -4, -5, -6, -7, -8
+
+
+class Item(C.Structure):
+    _fields_ = [
+        ("jpg", C.c_void_p),
+        ("len", C.c_size_t),
+        ("rgb", C.c_void_p),
+        ("plane_stride", C.c_size_t),
+        ("row_pitch", C.c_size_t),
+        ("rgb_on_device", C.c_int32),
+        ("width", C.c_int32),
+        ("height", C.c_int32),
+        ("status", C.c_int32),
+    ]
+
+
+_lib = None
+
+
+def lib():
+    """Load libgjd.so; fail loudly when the CUDA extension has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `make -C {_HERE}` (or __graft_entry__.build()). "
+            "gjd has no CPU fallback."
+        )
+    L = C.CDLL(LIB_PATH)
+    vp, sz, i32 = C.c_void_p, C.c_size_t, C.c_int32
+    L.gjd_create.argtypes = [C.POINTER(vp), C.c_int, sz]
+    L.gjd_destroy.argtypes = [vp]
+    L.gjd_destroy.restype = None
+    L.gjd_peek.argtypes = [vp, sz, C.POINTER(i32), C.POINTER(i32)]
+    L.gjd_decode_batch.argtypes = [vp, C.POINTER(Item), i32]
+    L.gjd_batch_prepare.argtypes = [vp, C.POINTER(Item), i32, C.POINTER(vp)]
+    L.gjd_batch_run.argtypes = [vp, vp]
+    L.gjd_batch_sync.argtypes = [vp, vp]
+    L.gjd_batch_status.argtypes = [vp, vp, i32]
+    L.gjd_batch_fetch.argtypes = [vp, vp, i32, vp]
+    L.gjd_batch_free.argtypes = [vp, vp]
+    L.gjd_batch_free.restype = None
+    L.gjd_batch_info.argtypes = [vp, vp, C.POINTER(C.c_uint64)]
+    L.gjd_decode_coeffs.argtypes = [vp, vp, sz, vp]
+    L.gjd_stage_times.argtypes = [vp, C.POINTER(C.c_float)]
+    L.gjd_test_color.argtypes = [vp, vp, vp, vp, sz, vp, vp, vp]
+    L.gjd_test_idct.argtypes = [vp, vp, sz, vp, vp]
+    L.gjd_host_alloc.argtypes = [sz]
+    L.gjd_host_alloc.restype = vp
+    L.gjd_host_free.argtypes = [vp]
+    L.gjd_host_free.restype = None
+    L.gjd_write_array.argtypes = [C.c_char_p, i32, i32, vp]
+    L.gjd_write_ppm.argtypes = [C.c_char_p, i32, i32, vp]
+    L.gjd_strerror.argtypes = [C.c_int]
+    L.gjd_strerror.restype = C.c_char_p
+    L.gjd_last_cuda_error.argtypes = [vp]
+    L.gjd_last_cuda_error.restype = C.c_char_p
+    L.gjd_version.restype = C.c_char_p
+    _lib = L
+    return L
+
+
+class GjdError(RuntimeError):
+    def __init__(self, status, detail=""):
+        self.status = status
+        msg = lib().gjd_strerror(status).decode()
+        super().__init__(f"gjd status {status}: {msg} {detail}".strip())
+
+
+def peek(data: bytes):
+    w, h = C.c_int32(), C.c_int32()
+    rc = lib().gjd_peek(C.cast(C.c_char_p(data), C.c_void_p), len(data), C.byref(w), C.byref(h))
+    return rc, w.value, h.value
+
+
+class PinnedBuffer:
+    """Page-locked host memory from gjd_host_alloc, exposed as a uint8 numpy array."""
+
+    def __init__(self, nbytes):
+        self.nbytes = int(nbytes)
+        self.ptr = lib().gjd_host_alloc(max(self.nbytes, 1))
+        if not self.ptr:
+            raise MemoryError("gjd_host_alloc failed")
+        self.array = np.ctypeslib.as_array((C.c_uint8 * max(self.nbytes, 1)).from_address(self.ptr))[: self.nbytes]
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            lib().gjd_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Decoder:
+    """One gjd_ctx (one host thread, one CUDA device)."""
+
+    def __init__(self, device=0, scratch_bytes=0):
+        self._ctx = C.c_void_p()
+        rc = lib().gjd_create(C.byref(self._ctx), device, scratch_bytes)
+        if rc != OK:
+            raise GjdError(rc)
+
+    def close(self):
+        if self._ctx:
+            lib().gjd_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _detail(self):
+        return lib().gjd_last_cuda_error(self._ctx).decode()
+
+    # -- end-to-end ---------------------------------------------------------------------------
+    def make_items(self, files):
+        """Item array for a list of `bytes` (kept alive by the returned holder list)."""
+        n = len(files)
+        items = (Item * n)()
+        hold = []
+        for i, d in enumerate(files):
+            buf = C.c_char_p(d)
+            hold.append(buf)
+            items[i].jpg = C.cast(buf, C.c_void_p)
+            items[i].len = len(d)
+        return items, hold
+
+    def decode(self, files):
+        """Decode a list of JPEG `bytes`; returns (list of (3,H,W) uint8 arrays or None, list of status)."""
+        n = len(files)
+        items, hold = self.make_items(files)
+        outs = []
+        for i, d in enumerate(files):
+            rc, w, h = peek(d)
+            if rc == OK:
+                a = np.empty((3, h, w), np.uint8)
+                items[i].rgb = a.ctypes.data
+                outs.append(a)
+            else:
+                outs.append(None)
+        rc = lib().gjd_decode_batch(self._ctx, items, n)
+        if rc != OK:
+            raise GjdError(rc, self._detail())
+        st = [items[i].status for i in range(n)]
+        return [o if s == OK else None for o, s in zip(outs, st)], st
+
+    def decode_batch_raw(self, items, n):
+        rc = lib().gjd_decode_batch(self._ctx, items, n)
+        if rc != OK:
+            raise GjdError(rc, self._detail())
+
+    def decode_coeffs(self, data: bytes):
+        rc, w, h = peek(data)
+        if rc != OK:
+            raise GjdError(rc)
+        nm = ((w + 7) // 8) * ((h + 7) // 8)
+        out = np.empty(nm * 192, np.int16)
+        rc = lib().gjd_decode_coeffs(self._ctx, C.cast(C.c_char_p(data), C.c_void_p), len(data), out.ctypes.data)
+        if rc != OK:
+            raise GjdError(rc, self._detail())
+        return out, w, h
+
+    def stage_times(self):
+        ms = (C.c_float * 4)()
+        rc = lib().gjd_stage_times(self._ctx, ms)
+        if rc != OK:
+            raise GjdError(rc, self._detail())
+        return list(ms)
+
+    # -- resident batch -----------------------------------------------------------------------
+    def prepare(self, files):
+        items, hold = self.make_items(files)
+        b = C.c_void_p()
+        rc = lib().gjd_batch_prepare(self._ctx, items, len(files), C.byref(b))
+        if rc != OK:
+            raise GjdError(rc, self._detail())
+        return ResidentBatch(self, b, items, len(files))
+
+    # -- test hooks ---------------------------------------------------------------------------
+    def test_color(self, y, cb, cr):
+        y = np.ascontiguousarray(y, np.int16)
+        cb = np.ascontiguousarray(cb, np.int16)
+        cr = np.ascontiguousarray(cr, np.int16)
+        n = y.size
+        r, g, b = (np.empty(n, np.uint8) for _ in range(3))
+        rc = lib().gjd_test_color(self._ctx, y.ctypes.data, cb.ctypes.data, cr.ctypes.data, n,
+                                  r.ctypes.data, g.ctypes.data, b.ctypes.data)
+        if rc != OK:
+            raise GjdError(rc, self._detail())
+        return r, g, b
+
+    def test_idct(self, coef_zz, quant_zz):
+        coef_zz = np.ascontiguousarray(coef_zz, np.int16).reshape(-1, 64)
+        q = np.ascontiguousarray(quant_zz, np.uint8)
+        out = np.empty_like(coef_zz)
+        rc = lib().gjd_test_idct(self._ctx, coef_zz.ctypes.data, coef_zz.shape[0], q.ctypes.data, out.ctypes.data)
+        if rc != OK:
+            raise GjdError(rc, self._detail())
+        return out
+
+
+class ResidentBatch:
+    def __init__(self, dec, handle, items, n):
+        self.dec, self.h, self.items, self.n = dec, handle, items, n
+
+    def run(self):
+        rc = lib().gjd_batch_run(self.dec._ctx, self.h)
+        if rc != OK:
+            raise GjdError(rc, self.dec._detail())
+
+    def sync(self):
+        return lib().gjd_batch_sync(self.dec._ctx, self.h)
+
+    def status(self, i):
+        return lib().gjd_batch_status(self.dec._ctx, self.h, i)
+
+    def info(self):
+        v = (C.c_uint64 * 5)()
+        lib().gjd_batch_info(self.dec._ctx, self.h, v)
+        return dict(pixels=v[0], padded_pixels=v[1], scan_bytes=v[2], subseqs=v[3], launches=v[4])
+
+    def fetch(self, i):
+        w, h = self.items[i].width, self.items[i].height
+        out = np.empty((3, h, w), np.uint8)
+        rc = lib().gjd_batch_fetch(self.dec._ctx, self.h, i, out.ctypes.data)
+        if rc != OK:
+            raise GjdError(rc, self.dec._detail())
+        return out
+
+    def free(self):
+        if self.h:
+            lib().gjd_batch_free(self.dec._ctx, self.h)
+            self.h = None
+
+
+def write_array(path, rgb):
+    """rgb: (3,H,W) uint8."""
+    rgb = np.ascontiguousarray(rgb, np.uint8)
+    rc = lib().gjd_write_array(path.encode(), rgb.shape[2], rgb.shape[1], rgb.ctypes.data)
+    if rc != OK:
+        raise GjdError(rc)

@@ -324,6 +324,18 @@ void gjdo_color(int y, int cb, int cr, int* R, int* G, int* B) {
     *B = clamp255((int)(b + 128));
 }
 
+/* Bulk form for the exhaustive colour test: all (cb, cr) in [-256,255]^2 at a fixed y,
+ * out[((cb+256)*512 + (cr+256))*3 + {0,1,2}] = R,G,B. */
+void gjdo_color_plane(int y, uint8_t* out) {
+    for (int cb = -256; cb < 256; cb++)
+        for (int cr = -256; cr < 256; cr++) {
+            int r, g, b;
+            gjdo_color(y, cb, cr, &r, &g, &b);
+            uint8_t* o = out + ((size_t)(cb + 256) * 512 + (size_t)(cr + 256)) * 3;
+            o[0] = (uint8_t)r; o[1] = (uint8_t)g; o[2] = (uint8_t)b;
+        }
+}
+
 /* ---- decode: cpp-decoder/src/parser.cpp:105-195 ----------------------------------------- */
 
 static int build_block(bitreader* br, const hufftab* dc, const hufftab* ac, const uint8_t* q,

@@ -52,6 +52,7 @@ int gjdo_decode(const uint8_t* jpg, size_t len, int* width, int* height,
 void gjdo_idct_block(int blk[64]);                    /* in: natural order dequantised; idct.cpp:34-133 */
 void gjdo_dezigzag(const int zz[64], int nat[64]);    /* idct.cpp:7-32  */
 void gjdo_color(int y, int cb, int cr, int* r, int* g, int* b);   /* color.cpp:3-18 */
+void gjdo_color_plane(int y, uint8_t* out);            /* all (cb,cr) at one y; see .c */
 extern const uint8_t gjdo_zigzag_of_natural[64];      /* table[x][y] at idct.cpp:7-18 */
 
 /* `.array` text writer, parser.cpp:197-210.  Returns bytes written or <0. */

@@ -1,0 +1,59 @@
+"""The C-ABI library loads on a machine without a GPU, exports every symbol include/gjd.h declares, and
+refuses to create a context instead of falling back to a CPU path."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+
+from conftest import ROOT
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "gjd.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(gjd_[a-z_0-9]+)\s*\(", src)))
+
+
+def test_exports_every_declared_symbol():
+    import gjd
+    L = gjd.lib()
+    names = _declared()
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(L, n), f"libgjd.so does not export {n}"
+
+
+def test_version_and_strerror():
+    import gjd
+    L = gjd.lib()
+    assert b"sm_100a" in L.gjd_version()
+    assert L.gjd_strerror(-7).startswith(b"no usable CUDA device")
+
+
+def test_peek_is_host_only(golden):
+    import gjd
+    rc, w, h = gjd.peek(golden["images/8_401x363"])
+    assert (rc, w, h) == (0, 401, 363)
+    rc, w, h = gjd.peek(b"\xff\xd8\xff\xd9")
+    assert rc == gjd.E_FORMAT
+
+
+def test_no_cpu_fallback_without_device():
+    import gjd
+    import torch
+    if torch.cuda.is_available():
+        return
+    ctx = C.c_void_p()
+    rc = gjd.lib().gjd_create(C.byref(ctx), 0, 0)
+    assert rc == gjd.E_NODEVICE and not ctx.value
+
+
+def test_array_writer_format(golden, ground_truth, tmp_path):
+    import hashlib, json, gjd
+    from conftest import GOLDEN
+    sha = json.load(open(os.path.join(GOLDEN, "array_sha256.json")))
+    for stem, want in sha.items():
+        p = str(tmp_path / (stem + ".array"))
+        gjd.write_array(p, ground_truth[stem])
+        assert hashlib.sha256(open(p, "rb").read()).hexdigest() == want

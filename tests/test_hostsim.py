@@ -1,0 +1,87 @@
+"""CPU checks of the product's own arithmetic and algorithm (no GPU): the __host__ __device__
+functions of gpu-jpeg-decoder_b200/csrc/gjd_devfn.cuh and the host parser, stepped by tests/hostsim in the
+order the kernels run them, against the oracle and the golden vectors."""
+import numpy as np
+import pytest
+
+from conftest import golden_files
+
+NAMES = sorted(golden_files())
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_hostsim_bit_exact(hostsim, golden, ref_outputs, name):
+    rc, coef, rgb, stats = hostsim.decode(golden[name])
+    assert rc == 0
+    assert np.array_equal(coef, ref_outputs[name + "/coef"])
+    assert np.array_equal(rgb, ref_outputs[name + "/rgb"])
+    assert stats[2] == 0 and stats[3] == 0
+
+
+def test_colour_exhaustive(hostsim, oracle):
+    """gjd_color (integer fast path + IEEE fallback) == cpp-decoder/utils/color.cpp on all 2^27 triples."""
+    a = np.empty((512, 512, 3), np.uint8)
+    b = np.empty((512, 512, 3), np.uint8)
+    for y in range(-256, 256):
+        hostsim.lib.hostsim_color_plane(y, a.ctypes.data)
+        oracle.lib.gjdo_color_plane(y, b.ctypes.data)
+        assert np.array_equal(a, b), f"colour mismatch at y={y}"
+
+
+def test_idct_random_blocks(hostsim, oracle):
+    rng = np.random.default_rng(7)
+    n = 4000
+    blocks = np.zeros((n, 64), np.int32)
+    # sparse, dense, and extreme-range dequantised coefficients
+    blocks[: n // 2] = rng.integers(-300, 300, (n // 2, 64)) * (rng.random((n // 2, 64)) < 0.2)
+    blocks[n // 2 : 3 * n // 4] = rng.integers(-2048, 2048, (n // 4, 64))
+    blocks[3 * n // 4 :] = rng.integers(-32768, 32768, (n - 3 * n // 4, 64))
+    blocks[0] = 0
+    blocks[1] = 0
+    blocks[1, 0] = 1016
+    out = np.zeros_like(blocks)
+    hostsim.lib.hostsim_idct(blocks.ctypes.data, out.ctypes.data, n)
+    want = blocks.copy()
+    for i in range(n):
+        oracle.lib.gjdo_idct_block(want[i].ctypes.data)
+    assert np.array_equal(out, want)
+
+
+def test_parser_contract(hostsim, golden):
+    import gen_synth
+    if not gen_synth.have_cjpeg():
+        pytest.skip("vendored cjpeg not built (tools/_build/libjpeg)")
+    import subprocess, os
+    img = gen_synth.make_image(3, 64, 48)
+    ppm = b"P6\n64 48\n255\n" + img.tobytes()
+    env = dict(os.environ, LD_LIBRARY_PATH=os.path.join(gen_synth.LIBJPEG, "lib"))
+    cj = os.path.join(gen_synth.LIBJPEG, "bin", "cjpeg")
+
+    def enc(*args):
+        return subprocess.run([cj, *args], input=ppm, stdout=subprocess.PIPE, check=True, env=env).stdout
+
+    ok = enc("-quality", "90", "-sample", "1x1", "-baseline")
+    assert hostsim.parse(ok)[0] == 0
+    assert hostsim.parse(enc("-sample", "2x2"))[0] == -5          # subsampled
+    assert hostsim.parse(enc("-sample", "1x1", "-progressive"))[0] == -5
+    assert hostsim.parse(enc("-grayscale"))[0] == -5
+    assert hostsim.parse(enc("-sample", "1x1", "-restart", "1"))[0] == -5   # DRI: SURVEY §8f-1
+    assert hostsim.parse(enc("-sample", "1x1", "-arithmetic"))[0] == -5
+    assert hostsim.parse(ok[:100])[0] == -4                       # truncated header
+    assert hostsim.parse(b"not a jpeg at all")[0] == -4
+    rc, *_ = hostsim.decode(ok[: len(ok) - 40])                   # truncated scan, no EOI
+    assert rc == -4
+    # APPn/COM segments anywhere are skipped by length (the reference parser would desynchronise)
+    com = ok[:2] + b"\xff\xfe\x00\x10" + b"x" * 14 + b"\xff\xe1\x00\x08" + b"Exif\x00\x00" + ok[2:]
+    rc, coef, rgb, _ = hostsim.decode(com)
+    rc0, coef0, rgb0, _ = hostsim.decode(ok)
+    assert rc == 0 and rc0 == 0 and np.array_equal(rgb, rgb0)
+
+
+def test_corrupt_scan_is_flagged(hostsim, golden):
+    data = bytearray(golden["images/5_200x200"])
+    # cut a chunk out of the middle of the entropy-coded data: counts cannot add up
+    mid = len(data) // 2
+    bad = bytes(data[:mid] + data[mid + 301 :])
+    rc, coef, rgb, stats = hostsim.decode(bad)
+    assert rc in (-6, -4)
