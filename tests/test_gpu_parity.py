@@ -1,0 +1,176 @@
+"""Parity tests proper: the CUDA path, called through the C ABI (libgjd.so), against the golden vectors
+made from the unmodified reference and against the oracle on seeded synthetic inputs.
+Bit-exact everywhere (coefficients, IDCT samples, pixels): integer/byte work, no tolerance."""
+import hashlib
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT, golden_files
+
+pytestmark = pytest.mark.gpu
+NAMES = sorted(golden_files())
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_coefficients_bit_exact(decoder, golden, ref_outputs, name):
+    coef, w, h = decoder.decode_coeffs(golden[name])
+    assert np.array_equal(coef, ref_outputs[name + "/coef"])
+
+
+def test_pixels_bit_exact_batch(decoder, golden, ref_outputs):
+    """Every fixture in ONE mixed-size batch (different Huffman/quant tables per image)."""
+    files = [golden[n] for n in NAMES]
+    outs, st = decoder.decode(files)
+    assert st == [0] * len(files)
+    for n, o in zip(NAMES, outs):
+        assert np.array_equal(o, ref_outputs[n + "/rgb"]), n
+
+
+def test_pixels_vs_reference_ground_truth(decoder, golden, ground_truth):
+    for key in ground_truth.files:
+        stem = key.split("/")[-1]
+        outs, st = decoder.decode([golden["images/" + stem]])
+        assert st == [0] and np.array_equal(outs[0], ground_truth[key]), key
+
+
+def test_single_image_calls_match_batch(decoder, golden, ref_outputs):
+    for n in NAMES[:6]:
+        outs, st = decoder.decode([golden[n]])
+        assert st == [0] and np.array_equal(outs[0], ref_outputs[n + "/rgb"])
+
+
+def test_colour_exhaustive_on_device(decoder, oracle):
+    """All 2^27 (Y,Cb,Cr) triples through the device colour function vs cpp-decoder/utils/color.cpp."""
+    cb, cr = np.meshgrid(np.arange(-256, 256, dtype=np.int16), np.arange(-256, 256, dtype=np.int16), indexing="ij")
+    cb, cr = cb.ravel(), cr.ravel()
+    want = np.empty((512 * 512, 3), np.uint8)
+    for y0 in range(-256, 256, 16):
+        ys = np.repeat(np.arange(y0, y0 + 16, dtype=np.int16), cb.size)
+        r, g, b = decoder.test_color(ys, np.tile(cb, 16), np.tile(cr, 16))
+        for k in range(16):
+            oracle.lib.gjdo_color_plane(y0 + k, want.ctypes.data)
+            sl = slice(k * cb.size, (k + 1) * cb.size)
+            assert np.array_equal(r[sl], want[:, 0]) and np.array_equal(g[sl], want[:, 1]) and np.array_equal(b[sl], want[:, 2]), y0 + k
+
+
+def test_idct_on_device(decoder, oracle):
+    rng = np.random.default_rng(11)
+    n = 20000
+    coef = np.zeros((n, 64), np.int16)
+    coef[: n // 2] = rng.integers(-60, 60, (n // 2, 64)) * (rng.random((n // 2, 64)) < 0.15)
+    coef[n // 2 :] = rng.integers(-1023, 1024, (n - n // 2, 64))
+    coef[:, 0] = rng.integers(-2047, 2048, n)
+    q = rng.integers(1, 256, 64).astype(np.uint8)
+    got = decoder.test_idct(coef, q)
+    zz = np.ctypeslib.as_array((__import__("ctypes").c_uint8 * 64).in_dll(oracle.lib, "gjdo_zigzag_of_natural"))
+    deq = coef.astype(np.int32) * q.astype(np.int32)[None]
+    nat = np.ascontiguousarray(deq[:, zz])
+    for i in range(n):
+        oracle.lib.gjdo_idct_block(nat[i].ctypes.data)
+    assert np.array_equal(got.astype(np.int32), nat)
+
+
+def test_error_statuses(decoder, golden):
+    good = golden["images/3_120x120"]
+    files = [good, good[: len(good) // 2], b"garbage", good]
+    outs, st = decoder.decode(files)
+    assert st[0] == 0 and st[3] == 0 and st[1] == -4 and st[2] == -4
+    assert np.array_equal(outs[0], outs[3])
+    # corrupt entropy data: flagged per image, neighbours unaffected
+    data = bytearray(golden["images/5_200x200"])
+    mid = len(data) // 2
+    bad = bytes(data[:mid] + data[mid + 301 :])
+    outs, st = decoder.decode([good, bad, good])
+    assert st[0] == 0 and st[2] == 0 and st[1] in (-6, -4)
+
+
+def test_empty_batch(decoder):
+    outs, st = decoder.decode([])
+    assert outs == [] and st == []
+
+
+def test_cli_array_output(golden, tmp_path):
+    """`./decoder <file.jpg>` from a testing/-like cwd, byte-compared with the reference's committed arrays."""
+    sha = json.load(open(os.path.join(GOLDEN, "array_sha256.json")))
+    work = tmp_path / "testing"
+    work.mkdir()
+    exe = os.path.join(ROOT, "gjd-decoder", "decoder")
+    for stem, want in sha.items():
+        subprocess.run([exe, os.path.join(GOLDEN, "images", stem + ".jpg")], cwd=str(work), check=True)
+        out = work / "gjd_output_arrays" / (stem + ".array")
+        assert hashlib.sha256(out.read_bytes()).hexdigest() == want, stem
+    r = subprocess.run([exe], cwd=str(work), stdout=subprocess.PIPE)
+    assert r.returncode == 1 and b"Please provide the name of the image file" in r.stdout
+
+
+def test_synthetic_seeded_vs_oracle(decoder, oracle):
+    """Seeded synthetic images (sizes incl. non-multiples of 8, q 25..100, optimised tables) vs the oracle."""
+    import gen_synth
+    if not gen_synth.have_cjpeg():
+        pytest.skip("vendored cjpeg missing")
+    specs = [(21, 1024, 1024, 90, False), (22, 777, 555, 75, True), (23, 2048, 512, 95, False),
+             (24, 129, 1031, 100, False), (25, 1536, 1536, 50, True)]
+    files = [gen_synth.synth_jpeg(*s) for s in specs]
+    outs, st = decoder.decode(files)
+    assert st == [0] * len(files)
+    for f, o in zip(files, outs):
+        rc, coef, rgb, _, W, H = oracle.decode(f)
+        assert rc == 0 and np.array_equal(o, rgb)
+        got, _, _ = decoder.decode_coeffs(f)
+        assert np.array_equal(got, coef)
+
+
+def test_resident_batch_and_subbatches(golden, ref_outputs):
+    """Resident API, and gjd_decode_batch forced into many pipelined sub-batches by a tiny scratch hint."""
+    import gjd
+    files = [golden[n] for n in NAMES] * 3
+    with gjd.Decoder(0, scratch_bytes=1 << 20) as d:
+        outs, st = d.decode(files)
+        assert st == [0] * len(files)
+        for i, o in enumerate(outs):
+            assert np.array_equal(o, ref_outputs[NAMES[i % len(NAMES)] + "/rgb"])
+        b = d.prepare(files)
+        for _ in range(2):
+            b.run()
+            assert b.sync() == 0
+        for i in range(len(files)):
+            assert np.array_equal(b.fetch(i), ref_outputs[NAMES[i % len(NAMES)] + "/rgb"])
+        info = b.info()
+        assert info["launches"] >= 5 and info["pixels"] > 0
+        ms = d.stage_times()
+        assert all(m >= 0 for m in ms)
+        b.free()
+
+
+def test_throughput_shape_property(decoder, oracle):
+    """BASELINE config 3 shape at reduced count: 1024x1024 q90 batch with repeats — duplicates must decode
+    identically (checksum of checksums), and a sample is checked against the oracle."""
+    import gen_synth
+    if not gen_synth.have_cjpeg():
+        pytest.skip("vendored cjpeg missing")
+    base = [gen_synth.synth_jpeg(s, 1024, 1024, 90) for s in range(8)]
+    files = [base[i % 8] for i in range(96)]
+    outs, st = decoder.decode(files)
+    assert st == [0] * 96
+    sums = [hashlib.md5(o.tobytes()).hexdigest() for o in outs]
+    for i in range(96):
+        assert sums[i] == sums[i % 8]
+    for i in (0, 5):
+        rc, _, rgb, _, W, H = oracle.decode(base[i], want_coef=False)
+        assert np.array_equal(outs[i], rgb)
+
+
+def test_huffman_stress_8192(decoder, oracle):
+    """BASELINE config 4: one 8192x8192 q90 image without restart markers (intra-image parallel Huffman)."""
+    import gen_synth
+    if not gen_synth.have_cjpeg():
+        pytest.skip("vendored cjpeg missing")
+    f = gen_synth.synth_jpeg(1000, 8192, 8192, 90)
+    outs, st = decoder.decode([f])
+    assert st == [0]
+    rc, _, rgb, _, W, H = oracle.decode(f, want_coef=False)
+    assert rc == 0 and np.array_equal(outs[0], rgb)
