@@ -1,0 +1,22 @@
+"""Small driver for ncu: prepare a resident c3 batch and run the GPU pipeline a few times.
+usage: python tools/profile_run.py [images] [runs]"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "gpu-jpeg-decoder_b200"))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+import gen_synth
+import gjd
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 300
+runs = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+base = gen_synth.c3_files()
+files = [base[i % len(base)] for i in range(n)]
+with gjd.Decoder(0) as d:
+    b = d.prepare(files)
+    for _ in range(runs):
+        b.run()
+        assert b.sync() == 0
+    print("stage ms", d.stage_times(), b.info())
+    b.free()
