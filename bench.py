@@ -287,7 +287,7 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
             "config": {"workload": WORKLOAD % args.images, "images_per_gpu": args.images,
                        "scan_bytes_per_gpu": info["scan_bytes"], "subsequences_per_gpu": info["subseqs"],
-                       "l2": "inputs larger than L2 (coefficient scratch %.1f GB, scans %.2f GB per step)" % (info["padded_pixels"] * 6 / 1e9, info["scan_bytes"] / 1e9),
+                       "l2": "inputs+outputs larger than L2 (scans %.2f GB read 3x, RGB %.1f GB written per step)" % (info["scan_bytes"] / 1e9, info["pixels"] * 3 / 1e9),
                        "timing": "CUDA events on the launching stream per step (value); wall clock around gjd_decode_batch (e2e, %d steps)" % e2e_steps,
                        "parallelism": "replicas: one sub-batch per GPU, no collective"},
             "stages_ms": {"entropy_sync": round(stage[0] / args.steps, 3), "entropy_write": round(stage[1] / args.steps, 3),

@@ -158,7 +158,7 @@ struct gjd_batch {
     std::vector<GjdDhtSet> dhts;
     std::vector<GjdQuantSet> quants;
     PinBuf h_scan, h_meta, h_status;
-    DevBuf d_scan, d_meta, d_luts, d_sinfo, d_seqmaps, d_coef, d_dcdiff, d_tilebase, d_tileimg, d_rgb, d_status;
+    DevBuf d_scan, d_meta, d_luts, d_sinfo, d_seqmaps, d_mcup, d_dcdiff, d_tilebase, d_tileimg, d_tbimg, d_rgb, d_status;
     GjdDevBatch view{};
     GjdStageEvents ev{};
     bool ev_ok = false;
@@ -171,7 +171,7 @@ struct gjd_batch {
     void release() {
         h_scan.release(); h_meta.release(); h_status.release();
         d_scan.release(); d_meta.release(); d_luts.release(); d_sinfo.release(); d_seqmaps.release();
-        d_coef.release(); d_dcdiff.release(); d_tilebase.release(); d_tileimg.release(); d_rgb.release();
+        d_mcup.release(); d_dcdiff.release(); d_tilebase.release(); d_tileimg.release(); d_tbimg.release(); d_rgb.release();
         d_status.release();
         if (ev_ok) for (auto& e : ev.e) cudaEventDestroy(e);
         ev_ok = false;
@@ -214,10 +214,10 @@ uint64_t fnv1a(const void* p, size_t n) {
     return h;
 }
 
-/* Estimated device bytes one image needs (scan + sinfo + coef + dc + rgb). */
+/* Estimated device bytes one image needs (scan + sinfo + MCU index + dc + rgb). */
 size_t estimate_bytes(const gjd_item& it, const ItemGeom& g) {
     size_t pw = align_up((size_t)g.width, 8), ph = align_up((size_t)g.height, 8);
-    return pw * ph * 7 + g.out_bytes + it.len * 2 + 65536;
+    return pw * ph / 8 + g.out_bytes + it.len * 3 + 65536;
 }
 
 /*
@@ -258,7 +258,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
 
     /* descriptors */
     std::unordered_map<uint64_t, std::vector<uint32_t>> lut_index, quant_index;
-    uint32_t seq = 0, tile = 0;
+    uint32_t seq = 0, tile = 0, tb = 0;
     size_t rgb_off = 0;
     b->pixels = b->padded_pixels = b->scan_bytes = b->subseqs = 0;
     for (int32_t i = 0; i < n; i++) {
@@ -279,8 +279,8 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         d.mcu_count = d.mcus_x * ((d.height + 7) / 8);
         d.tile_first = tile;
         d.tile_count = (d.mcu_count + GJD_TILE_MCUS - 1) / GJD_TILE_MCUS;
-        d.coef_off = (uint64_t)tile * GJD_TILE_I16;
-        d.blk_first = tile * 96u;
+        d.tb_first = tb;
+        d.tb_count = (d.tile_count + GJD_TB_TILES - 1) / GJD_TB_TILES;
         d.row_pitch = (uint32_t)g.pitch;
         d.plane_stride = g.pstride;
         if (items[i].rgb_on_device && items[i].rgb && !own_output) {
@@ -327,6 +327,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         }
         seq += d.seq_count;
         tile += d.tile_count;
+        tb += d.tb_count;
         b->img_of[i] = (int32_t)b->imgs.size();
         b->imgs.push_back(d);
         b->pixels += (uint64_t)d.width * d.height;
@@ -342,6 +343,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     v.n_img = n_img;
     v.n_seq = seq;
     v.n_tile = tile;
+    v.n_tb = tb;
     if (n_img == 0) return GJD_OK;
 
     /* one pinned block for descriptors + DHT sets + quant sets, one H2D copy */
@@ -359,7 +361,8 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     GJD_TRY(b->d_luts.ensure(sizeof(GjdLutSet) * b->dhts.size()));
     GJD_TRY(b->d_sinfo.ensure((size_t)seq * GJD_SEQ_SUBS * sizeof(uint2)));
     GJD_TRY(b->d_seqmaps.ensure((size_t)seq * 2 * sizeof(uint32_t)));
-    GJD_TRY(b->d_coef.ensure((size_t)tile * GJD_TILE_I16 * sizeof(int16_t)));
+    GJD_TRY(b->d_mcup.ensure((size_t)tile * GJD_TILE_MCUS * sizeof(uint32_t)));
+    GJD_TRY(b->d_tbimg.ensure((size_t)tb * sizeof(uint32_t)));
     GJD_TRY(b->d_dcdiff.ensure((size_t)tile * 96 * sizeof(int16_t)));
     GJD_TRY(b->d_tilebase.ensure((size_t)tile * sizeof(int4)));
     GJD_TRY(b->d_tileimg.ensure((size_t)tile * sizeof(uint32_t)));
@@ -374,7 +377,8 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     v.sinfo = (uint2*)b->d_sinfo.p;
     v.seq_img = (uint32_t*)b->d_seqmaps.p;
     v.seq_base = (uint32_t*)b->d_seqmaps.p + seq;
-    v.coef = (int16_t*)b->d_coef.p;
+    v.mcu_p = (uint32_t*)b->d_mcup.p;
+    v.tb_img = (uint32_t*)b->d_tbimg.p;
     v.dcdiff = (int16_t*)b->d_dcdiff.p;
     v.tilebase = (int4*)b->d_tilebase.p;
     v.tile_img = (uint32_t*)b->d_tileimg.p;
@@ -730,7 +734,7 @@ int gjd_decode_coeffs(gjd_ctx* ctx, const uint8_t* jpg, size_t len, int16_t* coe
         size_t ncoef = (size_t)b->imgs[0].mcu_count * 192;
         DevBuf tmp;
         cudaError_t e = tmp.ensure(ncoef * sizeof(int16_t));
-        if (e == cudaSuccess) e = gjd_launch_export_coefs(b->view, 0, (int16_t*)tmp.p, b->stream);
+        if (e == cudaSuccess) e = gjd_launch_export_coefs(b->view, (int16_t*)tmp.p, b->stream);
         if (e == cudaSuccess) e = cudaMemcpyAsync(coeffs_host, tmp.p, ncoef * sizeof(int16_t), cudaMemcpyDeviceToHost, b->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
         tmp.release();

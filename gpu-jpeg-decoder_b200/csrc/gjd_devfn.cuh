@@ -132,12 +132,29 @@ struct GjdNoSink {
     GJD_HD void operator()(uint32_t, int, uint32_t) const {}
 };
 
+/* JPEG EXTEND of the `size` value bits that follow a code of `len` bits in the 32-bit window w
+ * (Stream::decodeNumber, cpp-decoder/utils/stream.cpp:44-51). */
+GJD_HD int gjd_extend(uint32_t w, uint32_t len, uint32_t size) {
+    if (size == 0u) return 0;
+    uint32_t vb = (w << len) >> (32u - size);
+    return (vb >> (size - 1u)) ? (int)vb : (int)vb - (int)((1u << size) - 1u);
+}
+
+GJD_HD uint32_t gjd_lookup(const GjdLutSet* lut, uint32_t slot, uint32_t w) {
+    uint32_t e = lut->lut[slot][w >> (32 - GJD_LUT_BITS)];
+    if (e & GJD_LUT_SLOW)
+        e = gjd_resolve(lut->lim[slot], lut->off[slot], lut->vals[slot], lut->isdc[slot], w >> 16, GJD_LUT_BITS + 1);
+    return e;
+}
+
+#define GJD_MODE_COUNT 0   /* advance the state only                                           */
+#define GJD_MODE_INDEX 1   /* also hand every DC symbol to sink(slots_so_far, dc_diff, bit_pos) */
+
 /* Decode symbols that START before end_bits, beginning at state s.  A symbol that would run past
- * scan_bits is padding and is not counted.  When WRITE, every non-zero coefficient is handed to
- * sink(slot_index_relative_to_s.n==0, value, entry) — slot index counts from the state's n.
+ * scan_bits is padding and is not counted.
  * Follows JPEGParser::buildMCU (cpp-decoder/src/parser.cpp:105-134): DC size/diff; AC run/size with
  * EOB = 0x00, "length += run", value bits always consumed, coefficient kept only if index < 64. */
-template <bool WRITE, class Sink>
+template <int MODE, class Sink>
 GJD_HD void gjd_decode_span(const uint32_t* scan, const GjdLutSet* lut, uint32_t tabsel,
                             uint32_t end_bits, uint32_t scan_bits, GjdState& s, Sink sink, uint32_t& bad) {
     if (s.p >= end_bits) return;
@@ -149,28 +166,17 @@ GJD_HD void gjd_decode_span(const uint32_t* scan, const GjdLutSet* lut, uint32_t
         uint32_t z = pos & 63u;
         uint32_t c = pos >> 6;
         uint32_t slot = (tabsel >> (4u * c + (z ? 2u : 0u))) & 3u;
-        uint32_t e = lut->lut[slot][w >> (32 - GJD_LUT_BITS)];
-        if (e & GJD_LUT_SLOW)
-            e = gjd_resolve(lut->lim[slot], lut->off[slot], lut->vals[slot], lut->isdc[slot], w >> 16,
-                            GJD_LUT_BITS + 1);
+        uint32_t e = gjd_lookup(lut, slot, w);
         uint32_t total = e & 31u;
         if (p + total > scan_bits) break;
         uint32_t adv = (e >> 9) & 31u;
         uint32_t znew = adv ? z + adv : 64u;
-        bool inside = znew <= 64u;
-        if (!inside) znew = 64u;
-        if (WRITE) {
-            uint32_t size = (e >> 5) & 15u;
+        if (znew > 64u) znew = 64u;
+        if (MODE == GJD_MODE_INDEX) {
             if (e & GJD_ENTRY_BAD) bad |= GJD_DEV_BADCODE;
-            if (inside && (size != 0u || z == 0u)) {
-                int v = 0;
-                if (size) {
-                    uint32_t len = total - size;
-                    uint32_t vb = (w << len) >> (32u - size);
-                    /* Stream::decodeNumber, cpp-decoder/utils/stream.cpp:44-51 */
-                    v = (vb >> (size - 1u)) ? (int)vb : (int)vb - (int)((1u << size) - 1u);
-                }
-                sink(n + (znew - 1u - z), v, e);
+            if (z == 0u) {
+                uint32_t size = (e >> 5) & 15u;
+                sink(n, gjd_extend(w, total - size, size), p);
             }
         }
         uint32_t d = znew - z;
@@ -180,6 +186,46 @@ GJD_HD void gjd_decode_span(const uint32_t* scan, const GjdLutSet* lut, uint32_t
         p += total;
     }
     s.p = p; s.n = n; s.pos = pos;
+}
+
+/* One 8x8 block for the fused transform kernel: DC difference, then AC coefficients handed to
+ * store(zigzag_index, value).  Returns the bit position after the block; *kmax = last non-zero
+ * zigzag index (0 if none).  Same buildMCU semantics as above. */
+GJD_HD int gjd_decode_dc(const uint32_t* scan, GjdWin& win, const GjdLutSet* lut, uint32_t dcslot,
+                         uint32_t& p, uint32_t scan_bits, uint32_t& bad) {
+    uint32_t w = gjd_peek32(win, scan, p);
+    uint32_t e = gjd_lookup(lut, dcslot, w);
+    uint32_t total = e & 31u, size = (e >> 5) & 15u;
+    if (e & GJD_ENTRY_BAD) bad |= GJD_DEV_BADCODE;
+    if (p + total > scan_bits) { bad |= GJD_DEV_BADCOUNT; return 0; }
+    p += total;
+    return gjd_extend(w, total - size, size);
+}
+
+template <class Store>
+GJD_HD void gjd_decode_ac(const uint32_t* scan, GjdWin& win, const GjdLutSet* lut, uint32_t acslot,
+                          uint32_t& p, uint32_t scan_bits, Store store, uint32_t& kmax, uint32_t& bad) {
+    uint32_t z = 1u, km = 0u, pp = p;
+    while (z < 64u) {
+        uint32_t w = gjd_peek32(win, scan, pp);
+        uint32_t e = gjd_lookup(lut, acslot, w);
+        uint32_t total = e & 31u;
+        if (e & GJD_ENTRY_BAD) bad |= GJD_DEV_BADCODE;
+        if (pp + total > scan_bits) { bad |= GJD_DEV_BADCOUNT; break; }
+        pp += total;
+        uint32_t adv = (e >> 9) & 31u;
+        if (adv == 0u) break;                    /* EOB */
+        z += adv - 1u;                           /* run */
+        if (z >= 64u) break;
+        uint32_t size = (e >> 5) & 15u;
+        if (size) {
+            store(z, gjd_extend(w, total - size, size));
+            km = z;
+        }
+        z++;
+    }
+    p = pp;
+    kmax = km;
 }
 
 /* ------------------------------------------------------------------ IDCT -------------- */

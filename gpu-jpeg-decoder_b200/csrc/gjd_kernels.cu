@@ -6,9 +6,10 @@
  *   k_huff_sync     cold decode of every subsequence + self-synchronisation inside a sequence
  *   k_huff_fix      boundary fix-up between sequences
  *   k_seq_scan      exclusive scan of per-sequence coefficient counts (per image)
- *   k_huff_write    re-decode from the synchronised states, scatter coefficients / DC differences
+ *   k_huff_index    re-decode from the synchronised states: bit position of every MCU + DC differences
  *   k_dc_tilebase   DC predictor at the start of every 32-MCU tile
- *   k_transform     DC prefix + dequantise + dezigzag + integer IDCT + colour + RGB store
+ *   k_transform     per MCU: Huffman-decode its three blocks from the indexed bit position into
+ *                   shared memory (dequantised), DC prefix, integer IDCT, colour, RGB store
  *
  * Stage structure after the reference's decodeImage / parallelHuffManDecode
  * (cuda-decoder/src/parser.cu:613-661, 132-208); none of its code is reused.
@@ -84,6 +85,7 @@ __global__ void __launch_bounds__(128) k_fill_maps(GjdDevBatch b) {
     const GjdImage& d = b.imgs[img];
     for (uint32_t i = threadIdx.x; i < d.seq_count; i += blockDim.x) b.seq_img[d.seq_first + i] = img;
     for (uint32_t i = threadIdx.x; i < d.tile_count; i += blockDim.x) b.tile_img[d.tile_first + i] = img;
+    for (uint32_t i = threadIdx.x; i < d.tb_count; i += blockDim.x) b.tb_img[d.tb_first + i] = img;
 }
 
 /* ------------------------------------------------------------------ entropy: sync ----- */
@@ -117,7 +119,7 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
     uint32_t bad = 0;
     if (active) {
         uint32_t end = min((sub0 + tid + 1) * GJD_SUBSEQ_BITS, scan_bits);
-        gjd_decode_span<false>(scan, &lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
+        gjd_decode_span<GJD_MODE_COUNT>(scan, &lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
     }
     sp[tid] = st.p;
     sn[tid] = (st.n << 8) | st.pos;
@@ -131,7 +133,7 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
         if (go) {
             st.n = 0;
             uint32_t end = min((sub0 + j + 1) * GJD_SUBSEQ_BITS, scan_bits);
-            gjd_decode_span<false>(scan, &lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
+            gjd_decode_span<GJD_MODE_COUNT>(scan, &lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
             bool match = sp[j] == st.p && (sn[j] & 255u) == st.pos;
             sp[j] = st.p;
             sn[j] = (st.n << 8) | st.pos;
@@ -173,7 +175,7 @@ __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
         if (sub >= d.sub_count) { merged = true; break; }
         st.n = 0;
         uint32_t end = min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
-        gjd_decode_span<false>(scan, lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
+        gjd_decode_span<GJD_MODE_COUNT>(scan, lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
         uint2 old = si[t];
         si[t] = make_uint2(st.p, (st.n << 8) | st.pos);
         if (old.x == st.p && (old.y & 255u) == st.pos) { merged = true; break; }
@@ -208,35 +210,30 @@ __global__ void __launch_bounds__(256) k_seq_scan(GjdDevBatch b) {
     if (tid == 0 && carry != 192u * d.mcu_count) atomicOr(b.status + img, GJD_DEV_BADCOUNT);
 }
 
-/* ------------------------------------------------------------------ entropy: write ---- */
+/* ------------------------------------------------------------------ entropy: index ---- */
 
-struct GjdCoefSink {
-    int16_t* coef;      /* image's first tile */
-    int16_t* dcdiff;    /* image's first block */
+struct GjdIndexSink {
+    uint32_t* mcu_p;    /* image's first tile */
+    int16_t* dcdiff;
     uint32_t idx0;      /* coefficient index at state.n == 0 */
     uint32_t total;     /* 192 * mcu_count */
     uint32_t* bad;
-    __device__ __forceinline__ void operator()(uint32_t rel, int v, uint32_t) const {
+    __device__ __forceinline__ void operator()(uint32_t rel, int v, uint32_t p) const {
         uint32_t idx = idx0 + rel;
         if (idx >= total) { *bad |= GJD_DEV_BADCOUNT; return; }
-        uint32_t blk = idx >> 6, k = idx & 63u;
-        if (k == 0u) {
-            dcdiff[blk] = (int16_t)v;
-        } else {
-            uint32_t mcu = blk / 3u, c = blk - mcu * 3u;
-            uint32_t tile = mcu >> 5, lane = mcu & 31u;
-            size_t a = (size_t)tile * GJD_TILE_I16 + (((c << 3) + (k >> 3)) * 32u + lane) * 8u + (k & 7u);
-            coef[a] = (int16_t)v;
-        }
+        uint32_t blk = idx >> 6;
+        dcdiff[blk] = (int16_t)v;
+        uint32_t mcu = blk / 3u;
+        if (blk == mcu * 3u) mcu_p[mcu] = p;
     }
 };
 
 /*
  * One block per sequence.  Thread i starts from the synchronised end state of subsequence i-1, at
- * coefficient index seq_base + (block-exclusive scan of the counts), and writes every non-zero AC
- * coefficient to its tiled slot and every DC difference to dcdiff.
+ * coefficient index seq_base + (block-exclusive scan of the counts), and records for every DC symbol
+ * it meets the DC difference and — for the first block of an MCU — the bit position.
  */
-__global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_write(GjdDevBatch b) {
+__global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_index(GjdDevBatch b) {
     __shared__ GjdLutSet lut;
     __shared__ uint32_t ws[8];
     const uint32_t g = blockIdx.x, tid = threadIdx.x;
@@ -264,15 +261,15 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_write(GjdDevBatch b) 
         st.pos = prev.y & 255u;
     }
     uint32_t bad = 0;
-    GjdCoefSink sink;
-    sink.coef = b.coef + d.coef_off;
-    sink.dcdiff = b.dcdiff + (size_t)d.blk_first;
+    GjdIndexSink sink;
+    sink.mcu_p = b.mcu_p + (size_t)d.tile_first * GJD_TILE_MCUS;
+    sink.dcdiff = b.dcdiff + (size_t)d.tile_first * 96u;
     sink.idx0 = b.seq_base[g] + excl;
     sink.total = 192u * d.mcu_count;
     sink.bad = &bad;
     if (sink.idx0 % 192u != st.pos && st.p < scan_bits) bad |= GJD_DEV_BADSTATE;
     uint32_t end = min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
-    gjd_decode_span<true>(scan, &lut, tabsel, end, scan_bits, st, sink, bad);
+    gjd_decode_span<GJD_MODE_INDEX>(scan, &lut, tabsel, end, scan_bits, st, sink, bad);
     if (bad) atomicOr(b.status + img, bad);
 }
 
@@ -286,7 +283,7 @@ __global__ void __launch_bounds__(256) k_dc_tilebase(GjdDevBatch b) {
     __shared__ uint32_t ws[8];
     const uint32_t tid = threadIdx.x;
     const GjdImage& d = b.imgs[blockIdx.x];
-    const uint4* dc = reinterpret_cast<const uint4*>(b.dcdiff + (size_t)d.blk_first);
+    const uint4* dc = reinterpret_cast<const uint4*>(b.dcdiff + (size_t)d.tile_first * 96u);
     int carry[3] = {0, 0, 0};
     for (uint32_t base = 0; base < d.tile_count; base += 256) {
         uint32_t t = base + tid;
@@ -316,30 +313,6 @@ __global__ void __launch_bounds__(256) k_dc_tilebase(GjdDevBatch b) {
 
 /* ------------------------------------------------------------------ transform --------- */
 
-/* zigzag index -> natural index (inverse of GJD_ZZ_TABLE) */
-__host__ __device__ constexpr int gjd_nat_of_zz(int k) {
-    constexpr int zz[64] = GJD_ZZ_TABLE;
-    int r = 0;
-    for (int i = 0; i < 64; i++)
-        if (zz[i] == k) r = i;
-    return r;
-}
-template <int K> struct GjdNat { static constexpr int value = gjd_nat_of_zz(K); };
-
-template <int K> struct GjdDequant {
-    /* w[]: 32 packed words (two int16 each, zigzag order); q: 64 ints (zigzag order) in shared memory */
-    static __device__ __forceinline__ void run(const uint32_t* w, const int4* q, int dc, int* v) {
-        GjdDequant<K - 1>::run(w, q, dc, v);
-        int4 qq = q[K / 4];
-        int qk = (K % 4 == 0) ? qq.x : (K % 4 == 1) ? qq.y : (K % 4 == 2) ? qq.z : qq.w;
-        int cv = (K == 0) ? dc : ((K & 1) ? ((int)w[K / 2] >> 16) : (int)(int16_t)(w[K / 2] & 0xffffu));
-        v[GjdNat<K>::value] = cv * qk;
-    }
-};
-template <> struct GjdDequant<-1> {
-    static __device__ __forceinline__ void run(const uint32_t*, const int4*, int, int*) {}
-};
-
 __device__ __forceinline__ int warp_incl_scan_i(int v, uint32_t lane) {
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -349,90 +322,151 @@ __device__ __forceinline__ int warp_incl_scan_i(int v, uint32_t lane) {
     return v;
 }
 
-#define GJD_TRANSFORM_WARPS 4
+#define GJD_TRANSFORM_THREADS 128
+
+/* natural index -> zigzag index as a compile-time function (GJD_ZZ_TABLE) */
+__host__ __device__ constexpr int gjd_zz_of_nat(int i) {
+    constexpr int zz[64] = GJD_ZZ_TABLE;
+    return zz[i];
+}
+template <int I> struct GjdZz { static constexpr int value = gjd_zz_of_nat(I); };
+
+/* v[natural i] = scratch[zigzag(i)] for the calling thread; scratch layout [k/4][thread] int4,
+ * q4 = &scratch[0][tid]. */
+template <int I> struct GjdGather {
+    static __device__ __forceinline__ void run(const int4* q4, int* v) {
+        GjdGather<I - 1>::run(q4, v);
+        constexpr int k = GjdZz<I>::value;
+        const int4& t = q4[(k >> 2) * GJD_TRANSFORM_THREADS];
+        v[I] = (k & 3) == 0 ? t.x : (k & 3) == 1 ? t.y : (k & 3) == 2 ? t.z : t.w;
+    }
+};
+template <> struct GjdGather<-1> {
+    static __device__ __forceinline__ void run(const int4*, int*) {}
+};
+
+struct GjdScratchStore {
+    int* mine;            /* &scratch[0][tid] viewed as int: element k at mine[(k>>2)*THREADS*4 + (k&3)] */
+    const int* q;         /* quantisation table of the component, zigzag order */
+    __device__ __forceinline__ void operator()(uint32_t k, int v) const {
+        mine[(k >> 2) * (GJD_TRANSFORM_THREADS * 4) + (k & 3u)] = v * q[k];
+    }
+};
 
 /*
- * One warp per tile of 32 MCUs, one thread per MCU (three 8x8 blocks -> 64 RGB pixels).
- * Per component: eight coalesced 16-byte loads (the tile layout puts lane l's chunk ch at
- * (ch*32 + l)*16 bytes), dequantise from a broadcast shared-memory copy of the quantisation table,
- * dezigzag by compile-time register renaming, integer IDCT in registers.  Cb and Cr are parked
- * packed in 64 registers; after the Y block the colour conversion runs per row and each row of
- * each plane leaves as one 8-byte store (a warp covers 256 contiguous bytes of a row).
+ * Fused decode + transform.  One thread block per GJD_TB_TILES tiles of one image (the block loads
+ * that image's Huffman LUTs and quantisation tables once), one warp per tile, one thread per MCU.
+ * Per MCU and component: clear the thread's 64-entry shared-memory scratch, Huffman-decode the block
+ * from mcu_p (the three blocks of an MCU are consecutive in the scan) storing value * q[k] at its
+ * zigzag slot, warp-scan the DC differences onto the tile's DC base, gather the scratch in natural
+ * order (compile-time renaming = dezigzag), integer IDCT in registers.  Y and Cb are parked packed
+ * (9 bits each) in 64 registers; after Cr the colour conversion runs per row and each row of each
+ * plane leaves as one 8-byte store (a warp covers 256 contiguous bytes of a row).
+ * EXPORT = true turns the kernel into the coefficient test hook: quantisation forced to 1 and the
+ * scratch written out in the reference layout mcu*192 + comp*64 + k instead of being transformed.
  */
-__global__ void __launch_bounds__(32 * GJD_TRANSFORM_WARPS) k_transform(GjdDevBatch b) {
-    __shared__ int4 sq[GJD_TRANSFORM_WARPS][48];
-    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-    const uint32_t tile = blockIdx.x * GJD_TRANSFORM_WARPS + warp;
-    if (tile >= b.n_tile) return;
-    const GjdImage& d = b.imgs[b.tile_img[tile]];
-    const uint32_t ltile = tile - d.tile_first;
-    const uint32_t mcu = ltile * GJD_TILE_MCUS + lane;
-    const bool valid = mcu < d.mcu_count;
+template <bool EXPORT>
+__global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 3) k_transform(GjdDevBatch b, int16_t* __restrict__ coef_out) {
+    __shared__ GjdLutSet lut;
+    __shared__ int sq[3][64];
+    __shared__ int4 scratch[16][GJD_TRANSFORM_THREADS];
 
-    const int4* qg = reinterpret_cast<const int4*>(b.quants + d.quant_id);
-    sq[warp][lane] = __ldg(qg + lane);
-    if (lane < 16) sq[warp][32 + lane] = __ldg(qg + 32 + lane);
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
+    const GjdImage& d = b.imgs[b.tb_img[blockIdx.x]];
+    const uint32_t ltb = blockIdx.x - d.tb_first;
+    copy_lut_to_smem(&lut, b.luts + d.lut_id);
+    {
+        const int* qg = reinterpret_cast<const int*>(b.quants + d.quant_id);
+        for (uint32_t i = tid; i < 192; i += GJD_TRANSFORM_THREADS) sq[i / 64][i % 64] = EXPORT ? 1 : __ldg(qg + i);
+    }
+    __syncthreads();
 
-    const int16_t* dcd = b.dcdiff + (size_t)d.blk_first + (size_t)ltile * 96u + lane * 3u;
-    const int4 tb = b.tilebase[tile];
-    const int dcv0 = warp_incl_scan_i((int)dcd[0], lane) + tb.x;
-    const int dcv1 = warp_incl_scan_i((int)dcd[1], lane) + tb.y;
-    const int dcv2 = warp_incl_scan_i((int)dcd[2], lane) + tb.z;
-    __syncwarp();
-    if (!valid) return;
-
-    const uint4* cp = reinterpret_cast<const uint4*>(b.coef + d.coef_off + (size_t)ltile * GJD_TILE_I16) + lane;
+    const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
+    const uint32_t scan_bits = d.scan_bits;
+    const uint32_t tabsel = gjd_pack_tabsel(d.tabsel);
     const uint32_t W = d.width, H = d.height;
-    const uint32_t by = mcu / d.mcus_x, bx = mcu - by * d.mcus_x;
-    const uint32_t x0 = bx * 8u, y0 = by * 8u;
     uint8_t* out = d.out_is_ptr ? reinterpret_cast<uint8_t*>(d.out_off) : b.rgb + d.out_off;
     const size_t pitch = d.row_pitch, pstride = d.plane_stride;
-    const bool fast = (x0 + 8u <= W) && (((size_t)out | pitch | pstride) & 7u) == 0;
+    const bool aligned = (((size_t)out | pitch | pstride) & 7u) == 0;
+    int4* mine4 = &scratch[0][tid];
+    uint32_t bad = 0;
 
-    uint32_t pc[64];
+    for (uint32_t t = warp; t < GJD_TB_TILES; t += GJD_TRANSFORM_THREADS / 32) {
+        const uint32_t ltile = ltb * GJD_TB_TILES + t;
+        if (ltile >= d.tile_count) break;
+        const uint32_t mcu = ltile * GJD_TILE_MCUS + lane;
+        const bool valid = mcu < d.mcu_count;
+        const int4 tb = b.tilebase[d.tile_first + ltile];
+        uint32_t p = valid ? b.mcu_p[(size_t)(d.tile_first + ltile) * GJD_TILE_MCUS + lane] : 0u;
+        if (p >= scan_bits) { if (valid) bad |= GJD_DEV_BADCOUNT; p = 0u; }
+        GjdWin win;
+        gjd_win_init(win, scan, p);
+        const uint32_t by = mcu / d.mcus_x, bx = mcu - by * d.mcus_x;
+        const uint32_t x0 = bx * 8u, y0 = by * 8u;
+        const bool fast = aligned && (x0 + 8u <= W);
+
+        uint32_t ycc[64];
 #pragma unroll 1
-    for (int it = 0; it < 3; it++) {
-        const int c = (it == 2) ? 0 : it + 1;   /* Cb, Cr, then Y */
-        uint32_t w[32];
+        for (int c = 0; c < 3; c++) {
 #pragma unroll
-        for (int ch = 0; ch < 8; ch++) {
-            uint4 t = __ldg(cp + (c * 8 + ch) * 32);
-            w[4 * ch] = t.x; w[4 * ch + 1] = t.y; w[4 * ch + 2] = t.z; w[4 * ch + 3] = t.w;
-        }
-        int v[64];
-        GjdDequant<63>::run(w, &sq[warp][c * 16], (c == 0) ? dcv0 : (c == 1) ? dcv1 : dcv2, v);
-        gjd_idct8x8(v);
-        if (it == 0) {
-#pragma unroll
-            for (int i = 0; i < 64; i++) pc[i] = (uint32_t)v[i];
-        } else if (it == 1) {
-#pragma unroll
-            for (int i = 0; i < 64; i++) pc[i] |= (uint32_t)v[i] << 16;
-        } else {
-#pragma unroll
-            for (int r = 0; r < 8; r++) {
-                if (y0 + r < H) {
-                    uint32_t pr[2] = {0, 0}, pg[2] = {0, 0}, pb[2] = {0, 0};
-#pragma unroll
-                    for (int x = 0; x < 8; x++) {
-                        int R, G, B;
-                        gjd_color(v[8 * r + x], (int)(pc[8 * r + x] & 0xffffu), (int)(pc[8 * r + x] >> 16), R, G, B);
-                        pr[x >> 2] |= (uint32_t)R << (8 * (x & 3));
-                        pg[x >> 2] |= (uint32_t)G << (8 * (x & 3));
-                        pb[x >> 2] |= (uint32_t)B << (8 * (x & 3));
+            for (int j = 0; j < 16; j++) mine4[j * GJD_TRANSFORM_THREADS] = make_int4(0, 0, 0, 0);
+            int diff = 0;
+            uint32_t kmax = 0;
+            if (valid) {
+                diff = gjd_decode_dc(scan, win, &lut, (tabsel >> (4 * c)) & 3u, p, scan_bits, bad);
+                GjdScratchStore st;
+                st.mine = reinterpret_cast<int*>(mine4);
+                st.q = sq[c];
+                gjd_decode_ac(scan, win, &lut, (tabsel >> (4 * c + 2)) & 3u, p, scan_bits, st, kmax, bad);
+            }
+            __syncwarp();
+            const int dc = warp_incl_scan_i(diff, lane) + (c == 0 ? tb.x : c == 1 ? tb.y : tb.z);
+            if (EXPORT) {
+                if (valid) {
+                    const int* m = reinterpret_cast<const int*>(mine4);
+                    for (int k = 0; k < 64; k++) {
+                        int v = k == 0 ? dc : m[(k >> 2) * (GJD_TRANSFORM_THREADS * 4) + (k & 3)];
+                        coef_out[(size_t)mcu * 192u + c * 64u + k] = (int16_t)v;
                     }
-                    uint8_t* row = out + (size_t)(y0 + r) * pitch + x0;
-                    if (fast) {
-                        *reinterpret_cast<uint2*>(row) = make_uint2(pr[0], pr[1]);
-                        *reinterpret_cast<uint2*>(row + pstride) = make_uint2(pg[0], pg[1]);
-                        *reinterpret_cast<uint2*>(row + 2 * pstride) = make_uint2(pb[0], pb[1]);
-                    } else {
+                }
+                continue;
+            }
+            int v[64];
+            GjdGather<63>::run(mine4, v);
+            v[0] = dc * sq[c][0];
+            gjd_idct8x8(v);
+            if (c == 0) {
+#pragma unroll
+                for (int i = 0; i < 64; i++) ycc[i] = (uint32_t)v[i];
+            } else if (c == 1) {
+#pragma unroll
+                for (int i = 0; i < 64; i++) ycc[i] |= (uint32_t)v[i] << 9;
+            } else if (valid) {
+#pragma unroll
+                for (int r = 0; r < 8; r++) {
+                    if (y0 + r < H) {
+                        uint32_t pr[2] = {0, 0}, pg[2] = {0, 0}, pb[2] = {0, 0};
 #pragma unroll
                         for (int x = 0; x < 8; x++) {
-                            if (x0 + x < W) {
-                                row[x] = (uint8_t)(pr[x >> 2] >> (8 * (x & 3)));
-                                row[pstride + x] = (uint8_t)(pg[x >> 2] >> (8 * (x & 3)));
-                                row[2 * pstride + x] = (uint8_t)(pb[x >> 2] >> (8 * (x & 3)));
+                            int R, G, B;
+                            gjd_color((int)(ycc[8 * r + x] & 511u), (int)(ycc[8 * r + x] >> 9), v[8 * r + x], R, G, B);
+                            pr[x >> 2] |= (uint32_t)R << (8 * (x & 3));
+                            pg[x >> 2] |= (uint32_t)G << (8 * (x & 3));
+                            pb[x >> 2] |= (uint32_t)B << (8 * (x & 3));
+                        }
+                        uint8_t* row = out + (size_t)(y0 + r) * pitch + x0;
+                        if (fast) {
+                            *reinterpret_cast<uint2*>(row) = make_uint2(pr[0], pr[1]);
+                            *reinterpret_cast<uint2*>(row + pstride) = make_uint2(pg[0], pg[1]);
+                            *reinterpret_cast<uint2*>(row + 2 * pstride) = make_uint2(pb[0], pb[1]);
+                        } else {
+#pragma unroll
+                            for (int x = 0; x < 8; x++) {
+                                if (x0 + x < W) {
+                                    row[x] = (uint8_t)(pr[x >> 2] >> (8 * (x & 3)));
+                                    row[pstride + x] = (uint8_t)(pg[x >> 2] >> (8 * (x & 3)));
+                                    row[2 * pstride + x] = (uint8_t)(pb[x >> 2] >> (8 * (x & 3)));
+                                }
                             }
                         }
                     }
@@ -440,32 +474,10 @@ __global__ void __launch_bounds__(32 * GJD_TRANSFORM_WARPS) k_transform(GjdDevBa
             }
         }
     }
+    if (bad) atomicOr(b.status + b.tb_img[blockIdx.x], bad);
 }
 
 /* ------------------------------------------------------------------ test hooks -------- */
-
-/* Quantised coefficients of one image in the reference layout mcu*192 + comp*64 + k, absolute DC. */
-__global__ void __launch_bounds__(128) k_export_coefs(GjdDevBatch b, uint32_t img, int16_t* __restrict__ out) {
-    const GjdImage& d = b.imgs[img];
-    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-    const uint32_t ltile = blockIdx.x * 4 + warp;
-    if (ltile >= d.tile_count) return;
-    const uint32_t mcu = ltile * GJD_TILE_MCUS + lane;
-    const int16_t* dcd = b.dcdiff + (size_t)d.blk_first + (size_t)ltile * 96u + lane * 3u;
-    const int4 tb = b.tilebase[d.tile_first + ltile];
-    int dc[3];
-    dc[0] = warp_incl_scan_i((int)dcd[0], lane) + tb.x;
-    dc[1] = warp_incl_scan_i((int)dcd[1], lane) + tb.y;
-    dc[2] = warp_incl_scan_i((int)dcd[2], lane) + tb.z;
-    if (mcu >= d.mcu_count) return;
-    const int16_t* tile = b.coef + d.coef_off + (size_t)ltile * GJD_TILE_I16;
-    for (uint32_t c = 0; c < 3; c++)
-        for (uint32_t k = 0; k < 64; k++) {
-            int16_t v = tile[(((c << 3) + (k >> 3)) * 32u + lane) * 8u + (k & 7u)];
-            if (k == 0) v = (int16_t)dc[c];
-            out[(size_t)mcu * 192u + c * 64u + k] = v;
-        }
-}
 
 __global__ void k_test_color(const int16_t* __restrict__ y, const int16_t* __restrict__ cb,
                              const int16_t* __restrict__ cr, size_t n, uint8_t* __restrict__ r,
@@ -477,19 +489,18 @@ __global__ void k_test_color(const int16_t* __restrict__ y, const int16_t* __res
     r[i] = (uint8_t)R; g[i] = (uint8_t)G; bl[i] = (uint8_t)B;
 }
 
-__global__ void k_test_idct(const int16_t* __restrict__ coef, size_t nblocks, const int32_t* __restrict__ quant,
-                            int16_t* __restrict__ out) {
-    __shared__ int4 q[16];
-    if (threadIdx.x < 16) q[threadIdx.x] = reinterpret_cast<const int4*>(quant)[threadIdx.x];
-    __syncthreads();
+/* dequantise + dezigzag + IDCT of stand-alone blocks, through the same scratch gather as k_transform */
+__global__ void __launch_bounds__(GJD_TRANSFORM_THREADS) k_test_idct(const int16_t* __restrict__ coef, size_t nblocks,
+                                                                      const int32_t* __restrict__ quant,
+                                                                      int16_t* __restrict__ out) {
+    __shared__ int4 scratch[16][GJD_TRANSFORM_THREADS];
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nblocks) return;
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(coef + i * 64);
-    uint32_t w[32];
-#pragma unroll
-    for (int j = 0; j < 32; j++) w[j] = src[j];
+    int* mine = reinterpret_cast<int*>(&scratch[0][threadIdx.x]);
+    for (int k = 0; k < 64; k++)
+        mine[(k >> 2) * (GJD_TRANSFORM_THREADS * 4) + (k & 3)] = (int)coef[i * 64 + k] * quant[k];
     int v[64];
-    GjdDequant<63>::run(w, q, (int)(int16_t)(w[0] & 0xffffu), v);
+    GjdGather<63>::run(&scratch[0][threadIdx.x], v);
     gjd_idct8x8(v);
 #pragma unroll
     for (int j = 0; j < 64; j++) out[i * 64 + j] = (int16_t)(v[j] - 256);
@@ -522,10 +533,9 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     int n = 0;
     if (b.n_img == 0) { if (launches) *launches = 0; return cudaSuccess; }
     if (ev) GJD_CK(cudaEventRecord(ev->e[0], s));
-    GJD_CK(cudaMemsetAsync(b.coef, 0, (size_t)b.n_tile * GJD_TILE_I16 * sizeof(int16_t), s));
     GJD_CK(cudaMemsetAsync(b.dcdiff, 0, (size_t)b.n_tile * 96 * sizeof(int16_t), s));
-    GJD_CK(cudaMemsetAsync(b.status, 0, (size_t)b.n_img * sizeof(uint32_t), s));
-    GJD_CK(cudaMemsetAsync(b.nosync, 0, sizeof(uint32_t), s));
+    GJD_CK(cudaMemsetAsync(b.mcu_p, 0xff, (size_t)b.n_tile * GJD_TILE_MCUS * sizeof(uint32_t), s));
+    GJD_CK(cudaMemsetAsync(b.status, 0, (size_t)(b.n_img + 1) * sizeof(uint32_t), s));
     if (ev) GJD_CK(cudaEventRecord(ev->e[1], s));
     if (!skip_sync) {
         k_huff_sync<<<b.n_seq, GJD_SYNC_THREADS, 0, s>>>(b); n++;
@@ -533,19 +543,18 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     }
     if (ev) GJD_CK(cudaEventRecord(ev->e[2], s));
     k_seq_scan<<<b.n_img, 256, 0, s>>>(b); n++;
-    k_huff_write<<<b.n_seq, GJD_SYNC_THREADS, 0, s>>>(b); n++;
+    k_huff_index<<<b.n_seq, GJD_SYNC_THREADS, 0, s>>>(b); n++;
     k_dc_tilebase<<<b.n_img, 256, 0, s>>>(b); n++;
     if (ev) GJD_CK(cudaEventRecord(ev->e[3], s));
-    k_transform<<<(b.n_tile + GJD_TRANSFORM_WARPS - 1) / GJD_TRANSFORM_WARPS, 32 * GJD_TRANSFORM_WARPS, 0, s>>>(b); n++;
+    k_transform<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr); n++;
     if (ev) GJD_CK(cudaEventRecord(ev->e[4], s));
     if (launches) *launches = n;
     return cudaGetLastError();
 }
 
-cudaError_t gjd_launch_export_coefs(const GjdDevBatch& b, uint32_t img, int16_t* out, cudaStream_t s) {
-    /* tile_count is only known on the device side of the descriptor; the caller passes n_tile of a
-     * single-image batch */
-    k_export_coefs<<<(b.n_tile + 3) / 4, 128, 0, s>>>(b, img, out);
+cudaError_t gjd_launch_export_coefs(const GjdDevBatch& b, int16_t* out, cudaStream_t s) {
+    /* single-image batch: out is indexed by the image's own MCU numbers */
+    k_transform<true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, out);
     return cudaGetLastError();
 }
 
@@ -559,6 +568,6 @@ cudaError_t gjd_launch_test_color(const int16_t* y, const int16_t* cb, const int
 cudaError_t gjd_launch_test_idct(const int16_t* coef, size_t nblocks, const int32_t* quant, int16_t* out,
                                  cudaStream_t s) {
     if (nblocks == 0) return cudaSuccess;
-    k_test_idct<<<(unsigned)((nblocks + 127) / 128), 128, 0, s>>>(coef, nblocks, quant, out);
+    k_test_idct<<<(unsigned)((nblocks + GJD_TRANSFORM_THREADS - 1) / GJD_TRANSFORM_THREADS), GJD_TRANSFORM_THREADS, 0, s>>>(coef, nblocks, quant, out);
     return cudaGetLastError();
 }

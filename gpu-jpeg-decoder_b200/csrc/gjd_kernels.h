@@ -21,11 +21,13 @@ struct GjdDevBatch {
     uint32_t* seq_img;     /* [n_seq]  sequence -> image */
     uint32_t* seq_base;    /* [n_seq]  coefficient index (within the image) at the sequence start */
     uint32_t n_seq;
-    int16_t* coef;         /* [n_tile * GJD_TILE_I16] */
+    uint32_t* mcu_p;       /* [n_tile * 32] bit position of every MCU's first symbol */
     int16_t* dcdiff;       /* [n_tile * 96] */
     int4* tilebase;        /* [n_tile] DC predictors at the tile start (x,y,z = comp 0,1,2) */
     uint32_t* tile_img;    /* [n_tile] tile -> image */
     uint32_t n_tile;
+    uint32_t* tb_img;      /* [n_tb] transform block -> image */
+    uint32_t n_tb;
     uint8_t* rgb;          /* output arena (images with out_is_ptr == 0) */
     uint32_t* status;      /* [n_img] GJD_DEV_* bits */
     uint32_t* nosync;      /* [1] sequences whose boundary fix-up ran off the end of the sequence */
@@ -45,7 +47,7 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
                                 int transform_variant, int* launches, bool skip_sync = false);
 /* Re-run of the boundary fix-up only (slow path when *nosync != 0). */
 cudaError_t gjd_launch_fix(const GjdDevBatch& b, cudaStream_t s);
-cudaError_t gjd_launch_export_coefs(const GjdDevBatch& b, uint32_t img, int16_t* out, cudaStream_t s);
+cudaError_t gjd_launch_export_coefs(const GjdDevBatch& b, int16_t* out, cudaStream_t s);
 cudaError_t gjd_launch_test_color(const int16_t* y, const int16_t* cb, const int16_t* cr, size_t n,
                                   uint8_t* r, uint8_t* g, uint8_t* bl, cudaStream_t s);
 cudaError_t gjd_launch_test_idct(const int16_t* coef, size_t nblocks, const int32_t* quant, int16_t* out,

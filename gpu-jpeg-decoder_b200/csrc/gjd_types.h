@@ -8,12 +8,13 @@
  *   sinfo  u32x2 one state per subsequence (GJD_SUBSEQ_BITS bits of one image's scan), padded per
  *                image to a multiple of GJD_SEQ_SUBS ("sequence" = the subsequences one thread
  *                block synchronises): {p, (n << 8) | pos}.
- *   coef   i16   quantised AC coefficients in zigzag order, tiled for the transform kernel:
- *                tile = 32 consecutive MCUs of one image; 16-byte chunk ch = comp*8 + k/8 of
- *                MCU lane l sits at tile*12288 + (ch*32 + l)*16 bytes.  Slot k = 0 is unused
- *                (DC lives in dcdiff).  Cleared before every run; the write pass stores non-zeros.
- *   dcdiff i16   DC differences, [global block index] (block = mcu*3 + comp within the image).
+ *   mcu_p  u32   bit position (in the image's unstuffed scan) of the first symbol of every MCU,
+ *                [tile*32 + lane]; tile = 32 consecutive MCUs of one image (one warp of the
+ *                transform kernel).  Written by the index pass.
+ *   dcdiff i16   DC differences, [tile*96 + lane*3 + comp].  Cleared before every run.
  *   tilebase i32 [tile][4]: DC predictor of each component at the start of the tile.
+ * There is no coefficient buffer: the transform kernel re-decodes each MCU's symbols from mcu_p
+ * straight into shared memory (12 B/px of HBM traffic and a scattered 2-byte write pass avoided).
  *   rgb    u8    planar R,G,B output per image in the caller's pitch/stride geometry.
  */
 #ifndef GJD_TYPES_H
@@ -27,7 +28,7 @@
 #define GJD_LUT_BITS      10       /* primary Huffman LUT index width              */
 #define GJD_LUT_SIZE      (1 << GJD_LUT_BITS)
 #define GJD_TILE_MCUS     32u      /* MCUs per coefficient tile (one warp)         */
-#define GJD_TILE_I16      (GJD_TILE_MCUS * 192u)
+#define GJD_TB_TILES      32u      /* tiles per transform thread block (one image)  */
 
 /* LUT entry (u16):  [4:0] total bits = code length + value size (1..27)
  *                   [8:5] value size (0..15)
@@ -63,7 +64,6 @@ typedef struct GjdQuantSet {
 /* Per-image device descriptor. */
 typedef struct GjdImage {
     uint64_t scan_off;      /* byte offset of the unstuffed scan in the scan arena            */
-    uint64_t coef_off;      /* i16 offset of the image's first tile in the coef arena         */
     uint64_t out_off;       /* byte offset in the rgb arena, or a raw device address           */
     uint64_t plane_stride;  /* bytes between planes                                            */
     uint32_t row_pitch;     /* bytes between rows                                              */
@@ -73,7 +73,8 @@ typedef struct GjdImage {
     uint32_t seq_count;
     uint32_t tile_first;    /* global index of the image's first coefficient tile              */
     uint32_t tile_count;
-    uint32_t blk_first;     /* global index of the image's first 8x8 block (dcdiff)            */
+    uint32_t tb_first;      /* global index of the image's first transform block               */
+    uint32_t tb_count;      /* ceil(tile_count / GJD_TB_TILES)                                 */
     uint32_t mcu_count;
     uint32_t mcus_x;
     uint32_t width, height;
@@ -82,7 +83,7 @@ typedef struct GjdImage {
     uint8_t  tabsel[8];     /* [c] = LUT slot of component c's DC table, [4+c] = AC table      */
     uint8_t  qsel[4];       /* [c] = quant table (0/1) of component c                          */
     uint32_t out_is_ptr;    /* out_off is an absolute device address (caller-owned buffer)     */
-    uint32_t pad0;
+    uint32_t pad0, pad1, pad2;
 } GjdImage;
 
 /* Device-written status bits per image. */

@@ -2,8 +2,8 @@
  * hostsim.cpp — TEST SCAFFOLDING: steps the product's __host__ __device__ functions
  * (gpu-jpeg-decoder_b200/csrc/gjd_devfn.cuh) and host parser on the CPU, thread by thread, in the
  * same order the CUDA kernels of gjd_kernels.cu do (cold decode, lock-step synchronisation rounds,
- * boundary fix-up, count scan, write pass into the tiled coefficient layout, tile DC bases,
- * transform).  It exists because the build machine has no GPU: it lets `pytest -m "not gpu"` check
+ * boundary fix-up, count scan, index pass (MCU bit positions + DC differences), and the fused
+ * per-MCU decode + transform).  It exists because the build machine has no GPU: it lets `pytest -m "not gpu"` check
  * the algorithm and every arithmetic function against the oracle before a kernel ever runs.
  * It is not part of libgjd.so and nothing in the product can reach it.
  */
@@ -21,23 +21,24 @@
 namespace {
 
 struct Sink {
-    int16_t* coef;
+    uint32_t* mcu_p;
     int16_t* dcdiff;
     uint32_t idx0, total;
     uint32_t* bad;
-    void operator()(uint32_t rel, int v, uint32_t) const {
+    void operator()(uint32_t rel, int v, uint32_t p) const {
         uint32_t idx = idx0 + rel;
         if (idx >= total) { *bad |= GJD_DEV_BADCOUNT; return; }
-        uint32_t blk = idx >> 6, k = idx & 63u;
-        if (k == 0u) {
-            dcdiff[blk] = (int16_t)v;
-        } else {
-            uint32_t mcu = blk / 3u, c = blk - mcu * 3u;
-            uint32_t tile = mcu >> 5, lane = mcu & 31u;
-            size_t a = (size_t)tile * GJD_TILE_I16 + (((c << 3) + (k >> 3)) * 32u + lane) * 8u + (k & 7u);
-            coef[a] = (int16_t)v;
-        }
+        uint32_t blk = idx >> 6;
+        dcdiff[blk] = (int16_t)v;
+        uint32_t mcu = blk / 3u;
+        if (blk == mcu * 3u) mcu_p[mcu] = p;
     }
+};
+
+struct Store {
+    int* blk;
+    const int* q;
+    void operator()(uint32_t k, int v) const { blk[k] = v * q[k]; }
 };
 
 const int kZZ[64] = GJD_ZZ_TABLE;
@@ -96,7 +97,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
             st[tid].p = (sub0 + tid) * GJD_SUBSEQ_BITS; st[tid].n = 0; st[tid].pos = 0;
             if (active) {
                 uint32_t end = std::min((sub0 + tid + 1) * GJD_SUBSEQ_BITS, scan_bits);
-                gjd_decode_span<false>(scan, lut, tabsel, end, scan_bits, st[tid], GjdNoSink(), bad);
+                gjd_decode_span<GJD_MODE_COUNT>(scan, lut, tabsel, end, scan_bits, st[tid], GjdNoSink(), bad);
             }
             bp[tid] = st[tid].p;
             bn[tid] = (st[tid].n << 8) | st[tid].pos;
@@ -110,7 +111,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
                 if (go) {
                     st[tid].n = 0;
                     uint32_t end = std::min((sub0 + j + 1) * GJD_SUBSEQ_BITS, scan_bits);
-                    gjd_decode_span<false>(scan, lut, tabsel, end, scan_bits, st[tid], GjdNoSink(), bad);
+                    gjd_decode_span<GJD_MODE_COUNT>(scan, lut, tabsel, end, scan_bits, st[tid], GjdNoSink(), bad);
                     bool match = bp[j] == st[tid].p && (bn[j] & 255u) == st[tid].pos;
                     bp[j] = st[tid].p;
                     bn[j] = (st[tid].n << 8) | st[tid].pos;
@@ -136,7 +137,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
                 if (sub >= sub_count) { merged = true; break; }
                 st.n = 0;
                 uint32_t end = std::min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
-                gjd_decode_span<false>(scan, lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
+                gjd_decode_span<GJD_MODE_COUNT>(scan, lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
                 fix_decodes++;
                 size_t a = (size_t)g * GJD_SEQ_SUBS + t;
                 bool match = sp[a] == st.p && (sn[a] & 255u) == st.pos;
@@ -158,8 +159,9 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
         for (uint32_t t = 0; t < cnt; t++) carry += sn[(size_t)g * GJD_SEQ_SUBS + t] >> 8;
     }
     if (carry != 192u * mcu_count) status |= GJD_DEV_BADCOUNT;
-    /* k_huff_write */
-    std::vector<int16_t> coef((size_t)tile_count * GJD_TILE_I16, 0), dcdiff((size_t)tile_count * 96, 0);
+    /* k_huff_index */
+    std::vector<uint32_t> mcu_p((size_t)tile_count * 32, 0xffffffffu);
+    std::vector<int16_t> dcdiff((size_t)tile_count * 96, 0);
     for (uint32_t g = 0; g < seq_count; g++) {
         uint32_t excl = 0;
         for (uint32_t tid = 0; tid < GJD_SEQ_SUBS; tid++) {
@@ -169,33 +171,43 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
             GjdState st; st.p = 0; st.n = 0; st.pos = 0;
             if (sub != 0) { st.p = sp[a - 1]; st.pos = sn[a - 1] & 255u; }
             uint32_t tbad = 0;
-            Sink sink{coef.data(), dcdiff.data(), seq_base[g] + excl, 192u * mcu_count, &tbad};
+            Sink sink{mcu_p.data(), dcdiff.data(), seq_base[g] + excl, 192u * mcu_count, &tbad};
             if (sink.idx0 % 192u != st.pos && st.p < scan_bits) tbad |= GJD_DEV_BADSTATE;
             uint32_t end = std::min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
-            gjd_decode_span<true>(scan, lut, tabsel, end, scan_bits, st, sink, tbad);
+            gjd_decode_span<GJD_MODE_INDEX>(scan, lut, tabsel, end, scan_bits, st, sink, tbad);
             status |= tbad;
             excl += sn[a] >> 8;
         }
     }
-    /* k_dc_tilebase + k_transform / k_export_coefs */
-    int q[3][64];
+    /* k_dc_tilebase + k_transform (fused decode) */
+    int q[3][64], qone[64];
     for (int c = 0; c < 3; c++)
         for (int k = 0; k < 64; k++) q[c][k] = p.quant[p.qsel[c]][k];
+    for (int k = 0; k < 64; k++) qone[k] = 1;
     int pred[3] = {0, 0, 0};
     for (uint32_t mcu = 0; mcu < mcu_count; mcu++) {
-        uint32_t tile = mcu >> 5, lane = mcu & 31u;
         int samples[3][64];
+        uint32_t bp = mcu_p[mcu];
+        if (bp >= scan_bits) { status |= GJD_DEV_BADCOUNT; bp = 0; }
+        GjdWin win;
+        gjd_win_init(win, scan, bp);
         for (int c = 0; c < 3; c++) {
-            pred[c] += dcdiff[(size_t)tile * 96 + lane * 3 + c];
+            int zz[64] = {0}, zq[64] = {0};
+            uint32_t kmax = 0, tbad = 0;
+            uint32_t bp2 = bp;
+            GjdWin win2 = win;
+            int diff = gjd_decode_dc(scan, win, lut, (tabsel >> (4 * c)) & 3u, bp, scan_bits, tbad);
+            gjd_decode_ac(scan, win, lut, (tabsel >> (4 * c + 2)) & 3u, bp, scan_bits, Store{zz, q[c]}, kmax, tbad);
+            /* EXPORT variant: same decode with q = 1 */
+            gjd_decode_dc(scan, win2, lut, (tabsel >> (4 * c)) & 3u, bp2, scan_bits, tbad);
+            gjd_decode_ac(scan, win2, lut, (tabsel >> (4 * c + 2)) & 3u, bp2, scan_bits, Store{zq, qone}, kmax, tbad);
+            status |= tbad;
+            pred[c] += diff;
             int v[64];
-            for (int k = 0; k < 64; k++) {
-                int cv = coef[(size_t)tile * GJD_TILE_I16 + (((c << 3) + (k >> 3)) * 32u + lane) * 8u + (k & 7)];
-                if (k == 0) cv = pred[c];
-                if (coef_out) coef_out[(size_t)mcu * 192 + c * 64 + k] = (int16_t)cv;
-                int nat = 0;
-                for (int i = 0; i < 64; i++) if (kZZ[i] == k) nat = i;
-                v[nat] = cv * q[c][k];
-            }
+            for (int i = 0; i < 64; i++) v[i] = zz[kZZ[i]];
+            v[0] = pred[c] * q[c][0];
+            if (coef_out)
+                for (int k = 0; k < 64; k++) coef_out[(size_t)mcu * 192 + c * 64 + k] = (int16_t)(k == 0 ? pred[c] : zq[k]);
             gjd_idct8x8(v);
             memcpy(samples[c], v, sizeof(v));
         }
