@@ -158,7 +158,7 @@ struct gjd_batch {
     std::vector<GjdDhtSet> dhts;
     std::vector<GjdQuantSet> quants;
     PinBuf h_scan, h_meta, h_status;
-    DevBuf d_scan, d_meta, d_luts, d_sinfo, d_seqmaps, d_mcup, d_dcdiff, d_tilebase, d_tileimg, d_tbimg, d_rgb, d_status;
+    DevBuf d_scan, d_meta, d_luts, d_sinfo, d_seqmaps, d_coef, d_blkmeta, d_tilebase, d_tileimg, d_tbimg, d_rgb, d_status;
     GjdDevBatch view{};
     GjdStageEvents ev{};
     bool ev_ok = false;
@@ -171,7 +171,7 @@ struct gjd_batch {
     void release() {
         h_scan.release(); h_meta.release(); h_status.release();
         d_scan.release(); d_meta.release(); d_luts.release(); d_sinfo.release(); d_seqmaps.release();
-        d_mcup.release(); d_dcdiff.release(); d_tilebase.release(); d_tileimg.release(); d_tbimg.release(); d_rgb.release();
+        d_coef.release(); d_blkmeta.release(); d_tilebase.release(); d_tileimg.release(); d_tbimg.release(); d_rgb.release();
         d_status.release();
         if (ev_ok) for (auto& e : ev.e) cudaEventDestroy(e);
         ev_ok = false;
@@ -214,10 +214,10 @@ uint64_t fnv1a(const void* p, size_t n) {
     return h;
 }
 
-/* Estimated device bytes one image needs (scan + sinfo + MCU index + dc + rgb). */
+/* Estimated device bytes one image needs (scan + sinfo + coefficient lines + block meta + rgb). */
 size_t estimate_bytes(const gjd_item& it, const ItemGeom& g) {
     size_t pw = align_up((size_t)g.width, 8), ph = align_up((size_t)g.height, 8);
-    return pw * ph / 8 + g.out_bytes + it.len * 3 + 65536;
+    return pw * ph * 6 + pw * ph / 4 + g.out_bytes + it.len * 3 + 65536;
 }
 
 /*
@@ -361,9 +361,9 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     GJD_TRY(b->d_luts.ensure(sizeof(GjdLutSet) * b->dhts.size()));
     GJD_TRY(b->d_sinfo.ensure((size_t)seq * GJD_SEQ_SUBS * sizeof(uint2)));
     GJD_TRY(b->d_seqmaps.ensure((size_t)seq * 2 * sizeof(uint32_t)));
-    GJD_TRY(b->d_mcup.ensure((size_t)tile * GJD_TILE_MCUS * sizeof(uint32_t)));
+    GJD_TRY(b->d_coef.ensure((size_t)tile * 96 * 64 * sizeof(int16_t)));
     GJD_TRY(b->d_tbimg.ensure((size_t)tb * sizeof(uint32_t)));
-    GJD_TRY(b->d_dcdiff.ensure((size_t)tile * 96 * sizeof(int16_t)));
+    GJD_TRY(b->d_blkmeta.ensure((size_t)tile * 96 * sizeof(uint32_t)));
     GJD_TRY(b->d_tilebase.ensure((size_t)tile * sizeof(int4)));
     GJD_TRY(b->d_tileimg.ensure((size_t)tile * sizeof(uint32_t)));
     GJD_TRY(b->d_rgb.ensure(std::max<size_t>(b->rgb_alloc, 256)));
@@ -377,9 +377,9 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     v.sinfo = (uint2*)b->d_sinfo.p;
     v.seq_img = (uint32_t*)b->d_seqmaps.p;
     v.seq_base = (uint32_t*)b->d_seqmaps.p + seq;
-    v.mcu_p = (uint32_t*)b->d_mcup.p;
+    v.coef = (int16_t*)b->d_coef.p;
     v.tb_img = (uint32_t*)b->d_tbimg.p;
-    v.dcdiff = (int16_t*)b->d_dcdiff.p;
+    v.meta = (uint32_t*)b->d_blkmeta.p;
     v.tilebase = (int4*)b->d_tilebase.p;
     v.tile_img = (uint32_t*)b->d_tileimg.p;
     v.rgb = (uint8_t*)b->d_rgb.p;

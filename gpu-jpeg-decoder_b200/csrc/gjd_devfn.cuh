@@ -20,8 +20,10 @@
 
 #ifdef __CUDACC__
 #define GJD_HD __host__ __device__ __forceinline__
+#define GJD_HD_COLD __host__ __device__ __noinline__   /* rare paths: kept out of line (code size) */
 #else
 #define GJD_HD inline
+#define GJD_HD_COLD inline
 #endif
 
 /* ------------------------------------------------------------------ Huffman tables ---- */
@@ -128,10 +130,6 @@ GJD_HD uint32_t gjd_pack_tabsel(const uint8_t tabsel[8]) {
     return s;
 }
 
-struct GjdNoSink {
-    GJD_HD void operator()(uint32_t, int, uint32_t) const {}
-};
-
 /* JPEG EXTEND of the `size` value bits that follow a code of `len` bits in the 32-bit window w
  * (Stream::decodeNumber, cpp-decoder/utils/stream.cpp:44-51). */
 GJD_HD int gjd_extend(uint32_t w, uint32_t len, uint32_t size) {
@@ -147,16 +145,12 @@ GJD_HD uint32_t gjd_lookup(const GjdLutSet* lut, uint32_t slot, uint32_t w) {
     return e;
 }
 
-#define GJD_MODE_COUNT 0   /* advance the state only                                           */
-#define GJD_MODE_INDEX 1   /* also hand every DC symbol to sink(slots_so_far, dc_diff, bit_pos) */
-
 /* Decode symbols that START before end_bits, beginning at state s.  A symbol that would run past
  * scan_bits is padding and is not counted.
  * Follows JPEGParser::buildMCU (cpp-decoder/src/parser.cpp:105-134): DC size/diff; AC run/size with
  * EOB = 0x00, "length += run", value bits always consumed, coefficient kept only if index < 64. */
-template <int MODE, class Sink>
-GJD_HD void gjd_decode_span(const uint32_t* scan, const GjdLutSet* lut, uint32_t tabsel,
-                            uint32_t end_bits, uint32_t scan_bits, GjdState& s, Sink sink, uint32_t& bad) {
+GJD_HD void gjd_count_span(const uint32_t* scan, const GjdLutSet* lut, uint32_t tabsel,
+                           uint32_t end_bits, uint32_t scan_bits, GjdState& s) {
     if (s.p >= end_bits) return;
     GjdWin win;
     gjd_win_init(win, scan, s.p);
@@ -172,13 +166,6 @@ GJD_HD void gjd_decode_span(const uint32_t* scan, const GjdLutSet* lut, uint32_t
         uint32_t adv = (e >> 9) & 31u;
         uint32_t znew = adv ? z + adv : 64u;
         if (znew > 64u) znew = 64u;
-        if (MODE == GJD_MODE_INDEX) {
-            if (e & GJD_ENTRY_BAD) bad |= GJD_DEV_BADCODE;
-            if (z == 0u) {
-                uint32_t size = (e >> 5) & 15u;
-                sink(n, gjd_extend(w, total - size, size), p);
-            }
-        }
         uint32_t d = znew - z;
         n += d;
         pos += d;
@@ -188,44 +175,86 @@ GJD_HD void gjd_decode_span(const uint32_t* scan, const GjdLutSet* lut, uint32_t
     s.p = p; s.n = n; s.pos = pos;
 }
 
-/* One 8x8 block for the fused transform kernel: DC difference, then AC coefficients handed to
- * store(zigzag_index, value).  Returns the bit position after the block; *kmax = last non-zero
- * zigzag index (0 if none).  Same buildMCU semantics as above. */
-GJD_HD int gjd_decode_dc(const uint32_t* scan, GjdWin& win, const GjdLutSet* lut, uint32_t dcslot,
-                         uint32_t& p, uint32_t scan_bits, uint32_t& bad) {
-    uint32_t w = gjd_peek32(win, scan, p);
-    uint32_t e = gjd_lookup(lut, dcslot, w);
-    uint32_t total = e & 31u, size = (e >> 5) & 15u;
-    if (e & GJD_ENTRY_BAD) bad |= GJD_DEV_BADCODE;
-    if (p + total > scan_bits) { bad |= GJD_DEV_BADCOUNT; return 0; }
-    p += total;
-    return gjd_extend(w, total - size, size);
-}
+/* Warp-wide "any lane still running": keeps the 32 lanes of a warp in one converged loop on the GPU
+ * (every lane of the warp must call it); the identity on the host. */
+#ifdef __CUDA_ARCH__
+#define GJD_WARP_ANY(x) __any_sync(0xffffffffu, (x))
+#else
+#define GJD_WARP_ANY(x) (x)
+#endif
 
-template <class Store>
-GJD_HD void gjd_decode_ac(const uint32_t* scan, GjdWin& win, const GjdLutSet* lut, uint32_t acslot,
-                          uint32_t& p, uint32_t scan_bits, Store store, uint32_t& kmax, uint32_t& bad) {
-    uint32_t z = 1u, km = 0u, pp = p;
-    while (z < 64u) {
-        uint32_t w = gjd_peek32(win, scan, pp);
-        uint32_t e = gjd_lookup(lut, acslot, w);
-        uint32_t total = e & 31u;
-        if (e & GJD_ENTRY_BAD) bad |= GJD_DEV_BADCODE;
-        if (pp + total > scan_bits) { bad |= GJD_DEV_BADCOUNT; break; }
-        pp += total;
-        uint32_t adv = (e >> 9) & 31u;
-        if (adv == 0u) break;                    /* EOB */
-        z += adv - 1u;                           /* run */
-        if (z >= 64u) break;
-        uint32_t size = (e >> 5) & 15u;
-        if (size) {
-            store(z, gjd_extend(w, total - size, size));
-            km = z;
+/*
+ * Write pass of one subsequence.  The thread starts at the synchronised state s (bit position p,
+ * pos = comp*64 + zigzag) whose next coefficient slot is idx0, and OWNS every 8x8 block whose DC symbol
+ * starts in [s.p, end_bits): it first skips the tail of the block it starts inside (that block belongs
+ * to the thread before it), then decodes its blocks completely — running past end_bits to finish the
+ * last one.  Per block it calls sink.store(k, value) for every non-zero AC coefficient (zigzag index
+ * k, increasing) and then sink.flush(block_index, dc_difference, kmax) with kmax = the last non-zero
+ * zigzag index (0 = DC only).  One flat loop over symbols for skip and own phases alike, driven by a
+ * warp vote, so the lanes of a warp stay converged: ALL 32 lanes call this (enable = false for lanes
+ * without a subsequence).
+ * Same buildMCU semantics as gjd_count_span (cpp-decoder/src/parser.cpp:105-134).
+ */
+template <class Sink>
+GJD_HD void gjd_write_span(const uint32_t* scan, const GjdLutSet* lut, uint32_t tabsel, uint32_t end_bits,
+                           uint32_t scan_bits, GjdState s, uint32_t idx0, uint32_t nblocks, bool enable,
+                           Sink& sink, uint32_t& bad) {
+    bool run = enable && s.p < end_bits;
+    GjdWin win;
+    win.wi = 0; win.w0 = 0; win.w1 = 0;
+    if (run) gjd_win_init(win, scan, s.p);
+    uint32_t p = s.p, pos = s.pos;
+    bool own = (pos & 63u) == 0u;                    /* false: inside the previous thread's block */
+    uint32_t blk = (idx0 + 63u) >> 6;
+    int dcdiff = 0;
+    uint32_t kmax = 0;
+    while (GJD_WARP_ANY(run)) {
+        if (!run) continue;
+        const uint32_t z = pos & 63u;
+        if (p >= end_bits && (z == 0u || !own)) { run = false; continue; }
+        const uint32_t c = pos >> 6;
+        const uint32_t w = gjd_peek32(win, scan, p);
+        const uint32_t e = gjd_lookup(lut, (tabsel >> (4u * c + (z ? 2u : 0u))) & 3u, w);
+        const uint32_t total = e & 31u;
+        if (p + total > scan_bits) {                 /* padding at a block start is the normal end */
+            if (own && z != 0u) bad |= GJD_DEV_BADCOUNT;
+            run = false;
+            continue;
         }
-        z++;
+        const uint32_t size = (e >> 5) & 15u;
+        const uint32_t adv = (e >> 9) & 31u;
+        p += total;
+        uint32_t znew;
+        if (own) {
+            if (e & GJD_ENTRY_BAD) bad |= GJD_DEV_BADCODE;
+            if (blk >= nblocks) { bad |= GJD_DEV_BADCOUNT; run = false; continue; }
+            const int v = gjd_extend(w, total - size, size);
+            if (z == 0u) {
+                dcdiff = v;
+                znew = 1u;
+            } else if (adv == 0u) {
+                znew = 64u;                          /* EOB */
+            } else {
+                const uint32_t k = z + adv - 1u;     /* run */
+                if (k < 64u && size) { sink.store(k, v); kmax = k; }
+                znew = k + 1u;
+            }
+        } else {
+            znew = adv ? z + adv : 64u;
+        }
+        if (znew >= 64u) {
+            if (own) {
+                sink.flush(blk, dcdiff, kmax);
+                blk++;
+                kmax = 0u;
+            }
+            own = true;
+            pos = (pos | 63u) + 1u;
+            if (pos == 192u) pos = 0u;
+        } else {
+            pos = (pos & ~63u) + znew;
+        }
     }
-    p = pp;
-    kmax = km;
 }
 
 /* ------------------------------------------------------------------ IDCT -------------- */
@@ -376,7 +405,7 @@ GJD_HD int gjd_addmin_relu(int a, int b, int c) {   /* max(min(a+b, c), 0) */
 }
 
 /* The reference's IEEE sequence for G, on unbiased inputs. No FMA contraction anywhere. */
-GJD_HD int gjd_color_g_exact(int y, int cb, int cr) {
+GJD_HD_COLD int gjd_color_g_exact(int y, int cb, int cr) {
 #ifdef __CUDA_ARCH__
     float r = __double2float_rn(__dadd_rn(__dmul_rn((double)cr, (2 - 2 * 0.299)), (double)y));
     float b = __double2float_rn(__dadd_rn(__dmul_rn((double)cb, (2 - 2 * 0.114)), (double)y));
@@ -401,8 +430,9 @@ GJD_HD int gjd_color_g_exact(int y, int cb, int cr) {
     return G > 255 ? 255 : (G < 0 ? 0 : G);
 }
 
-/* Fast path on biased inputs (yb, cbb, crb in [0,511]). */
-GJD_HD void gjd_color(int yb, int cbb, int crb, int& R, int& G, int& B) {
+/* Fast path on biased inputs (yb, cbb, crb in [0,511]).  Returns true when G sits in the danger zone
+ * and must be recomputed with gjd_color_g_exact (843 of the 2^27 triples). */
+GJD_HD bool gjd_color_fast(int yb, int cbb, int crb, int& R, int& G, int& B) {
     int tr = crb * GJD_KR + GJD_CONST_R;
     int tb = cbb * GJD_KB + GJD_CONST_B;
     int tg = crb * (-GJD_KGR) + GJD_CONST_G;
@@ -410,7 +440,11 @@ GJD_HD void gjd_color(int yb, int cbb, int crb, int& R, int& G, int& B) {
     R = gjd_addmin_relu(tr >> 20, yb, 255);
     B = gjd_addmin_relu(tb >> 20, yb, 255);
     G = gjd_addmin_relu(tg >> 20, yb, 255);
-    if ((uint32_t)(tg & 0xFFFFF) < 2u * GJD_GDELTA) G = gjd_color_g_exact(yb - 256, cbb - 256, crb - 256);
+    return (uint32_t)(tg & 0xFFFFF) < 2u * GJD_GDELTA;
+}
+
+GJD_HD void gjd_color(int yb, int cbb, int crb, int& R, int& G, int& B) {
+    if (gjd_color_fast(yb, cbb, crb, R, G, B)) G = gjd_color_g_exact(yb - 256, cbb - 256, crb - 256);
 }
 
 #endif /* GJD_DEVFN_CUH */

@@ -6,10 +6,11 @@
  *   k_huff_sync     cold decode of every subsequence + self-synchronisation inside a sequence
  *   k_huff_fix      boundary fix-up between sequences
  *   k_seq_scan      exclusive scan of per-sequence coefficient counts (per image)
- *   k_huff_index    re-decode from the synchronised states: bit position of every MCU + DC differences
+ *   k_huff_write    re-decode from the synchronised states; every thread stages the blocks it owns in
+ *                   shared memory and writes them as whole 32-byte sectors (+ DC difference, kmax)
  *   k_dc_tilebase   DC predictor at the start of every 32-MCU tile
- *   k_transform     per MCU: Huffman-decode its three blocks from the indexed bit position into
- *                   shared memory (dequantised), DC prefix, integer IDCT, colour, RGB store
+ *   k_transform     per 8x8 block: load the coefficient sectors, DC prefix, dequantise, dezigzag, integer
+ *                   IDCT in registers; samples meet in shared memory for colour conversion + RGB store
  *
  * Stage structure after the reference's decodeImage / parallelHuffManDecode
  * (cuda-decoder/src/parser.cu:613-661, 132-208); none of its code is reused.
@@ -116,10 +117,9 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
     st.p = (sub0 + tid) * GJD_SUBSEQ_BITS;
     st.n = 0;
     st.pos = 0;
-    uint32_t bad = 0;
     if (active) {
         uint32_t end = min((sub0 + tid + 1) * GJD_SUBSEQ_BITS, scan_bits);
-        gjd_decode_span<GJD_MODE_COUNT>(scan, &lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
+        gjd_count_span(scan, &lut, tabsel, end, scan_bits, st);
     }
     sp[tid] = st.p;
     sn[tid] = (st.n << 8) | st.pos;
@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
         if (go) {
             st.n = 0;
             uint32_t end = min((sub0 + j + 1) * GJD_SUBSEQ_BITS, scan_bits);
-            gjd_decode_span<GJD_MODE_COUNT>(scan, &lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
+            gjd_count_span(scan, &lut, tabsel, end, scan_bits, st);
             bool match = sp[j] == st.p && (sn[j] & 255u) == st.pos;
             sp[j] = st.p;
             sn[j] = (st.n << 8) | st.pos;
@@ -167,7 +167,6 @@ __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
     GjdState st;
     st.p = prev.x;
     st.pos = prev.y & 255u;
-    uint32_t bad = 0;
     bool merged = false;
     uint32_t t = 0;
     for (; t < GJD_SEQ_SUBS; t++) {
@@ -175,7 +174,7 @@ __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
         if (sub >= d.sub_count) { merged = true; break; }
         st.n = 0;
         uint32_t end = min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
-        gjd_decode_span<GJD_MODE_COUNT>(scan, lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
+        gjd_count_span(scan, lut, tabsel, end, scan_bits, st);
         uint2 old = si[t];
         si[t] = make_uint2(st.p, (st.n << 8) | st.pos);
         if (old.x == st.p && (old.y & 255u) == st.pos) { merged = true; break; }
@@ -210,31 +209,45 @@ __global__ void __launch_bounds__(256) k_seq_scan(GjdDevBatch b) {
     if (tid == 0 && carry != 192u * d.mcu_count) atomicOr(b.status + img, GJD_DEV_BADCOUNT);
 }
 
-/* ------------------------------------------------------------------ entropy: index ---- */
+/* ------------------------------------------------------------------ entropy: write ---- */
 
-struct GjdIndexSink {
-    uint32_t* mcu_p;    /* image's first tile */
-    int16_t* dcdiff;
-    uint32_t idx0;      /* coefficient index at state.n == 0 */
-    uint32_t total;     /* 192 * mcu_count */
-    uint32_t* bad;
-    __device__ __forceinline__ void operator()(uint32_t rel, int v, uint32_t p) const {
-        uint32_t idx = idx0 + rel;
-        if (idx >= total) { *bad |= GJD_DEV_BADCOUNT; return; }
-        uint32_t blk = idx >> 6;
-        dcdiff[blk] = (int16_t)v;
-        uint32_t mcu = blk / 3u;
-        if (blk == mcu * 3u) mcu_p[mcu] = p;
+#define GJD_WRITE_THREADS 256
+static_assert(GJD_WRITE_THREADS == GJD_SEQ_SUBS, "one thread per subsequence of a sequence");
+
+/*
+ * Staging of the block a thread is decoding: 64 int16 per thread in shared memory, interleaved across
+ * the block's threads in 16-byte chunks (chunk j of thread t at buf[j][t]) so that the flush is eight
+ * conflict-free 128-bit loads.  flush() moves the 32-byte sectors up to kmax to the coefficient line
+ * of the block (whole sectors only: no read-modify-write in L2/HBM), re-zeroes them, and writes meta.
+ */
+struct GjdWriteSink {
+    uint4* mine;       /* &buf[0][tid] */
+    uint4* coef;       /* the image's first coefficient line, 8 uint4 per block */
+    uint32_t* meta;    /* the image's first meta word */
+    __device__ __forceinline__ void store(uint32_t k, int v) const {
+        reinterpret_cast<int16_t*>(mine + (k >> 3) * GJD_WRITE_THREADS)[k & 7u] = (int16_t)v;
+    }
+    __device__ __forceinline__ void flush(uint32_t blk, int dcdiff, uint32_t kmax) const {
+        meta[blk] = ((uint32_t)dcdiff & 0xffffu) | (kmax << 16);
+        if (kmax == 0u) return;
+        uint4* dst = coef + (size_t)blk * 8u;
+        const uint32_t nchunk = ((kmax >> 4) + 1u) * 2u;
+        for (uint32_t j = 0; j < nchunk; j++) {
+            uint4* src = mine + j * GJD_WRITE_THREADS;
+            dst[j] = *src;
+            *src = make_uint4(0u, 0u, 0u, 0u);
+        }
     }
 };
 
 /*
  * One block per sequence.  Thread i starts from the synchronised end state of subsequence i-1, at
- * coefficient index seq_base + (block-exclusive scan of the counts), and records for every DC symbol
- * it meets the DC difference and — for the first block of an MCU — the bit position.
+ * coefficient index seq_base + (block-exclusive scan of the counts), and writes the blocks it owns
+ * (gjd_write_span).
  */
-__global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_index(GjdDevBatch b) {
+__global__ void __launch_bounds__(GJD_WRITE_THREADS, 5) k_huff_write(GjdDevBatch b) {
     __shared__ GjdLutSet lut;
+    __shared__ uint4 buf[8][GJD_WRITE_THREADS];
     __shared__ uint32_t ws[8];
     const uint32_t g = blockIdx.x, tid = threadIdx.x;
     const uint32_t img = b.seq_img[g];
@@ -247,57 +260,55 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_index(GjdDevBatch b) 
     const bool active = sub < d.sub_count;
     const uint2* si = b.sinfo + (size_t)g * GJD_SEQ_SUBS;
     copy_lut_to_smem(&lut, b.luts + d.lut_id);
+#pragma unroll
+    for (int j = 0; j < 8; j++) buf[j][tid] = make_uint4(0u, 0u, 0u, 0u);
 
     uint32_t n = active ? (si[tid].y >> 8) : 0u;
     uint32_t blocksum;
     uint32_t excl = block_excl_scan_256(n, ws, &blocksum);   /* has the __syncthreads the LUT copy needs */
-    if (!active) return;
 
     GjdState st;
     st.p = 0; st.n = 0; st.pos = 0;
-    if (sub != 0u) {
+    if (active && sub != 0u) {
         uint2 prev = si[(int)tid - 1];
         st.p = prev.x;
         st.pos = prev.y & 255u;
     }
     uint32_t bad = 0;
-    GjdIndexSink sink;
-    sink.mcu_p = b.mcu_p + (size_t)d.tile_first * GJD_TILE_MCUS;
-    sink.dcdiff = b.dcdiff + (size_t)d.tile_first * 96u;
-    sink.idx0 = b.seq_base[g] + excl;
-    sink.total = 192u * d.mcu_count;
-    sink.bad = &bad;
-    if (sink.idx0 % 192u != st.pos && st.p < scan_bits) bad |= GJD_DEV_BADSTATE;
+    GjdWriteSink sink;
+    sink.mine = &buf[0][tid];
+    sink.coef = reinterpret_cast<uint4*>(b.coef) + (size_t)d.tile_first * (96u * 8u);
+    sink.meta = b.meta + (size_t)d.tile_first * 96u;
+    const uint32_t idx0 = b.seq_base[g] + excl;
+    if (active && idx0 % 192u != st.pos && st.p < scan_bits) bad |= GJD_DEV_BADSTATE;
     uint32_t end = min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
-    gjd_decode_span<GJD_MODE_INDEX>(scan, &lut, tabsel, end, scan_bits, st, sink, bad);
+    gjd_write_span(scan, &lut, tabsel, end, scan_bits, st, idx0, 3u * d.mcu_count, active, sink, bad);
     if (bad) atomicOr(b.status + img, bad);
 }
 
 /* ------------------------------------------------------------------ DC predictors ----- */
 /*
  * One block per image.  Thread t sums the DC differences of tile t (32 MCUs x 3 components =
- * 96 int16, contiguous), the block scans the sums: tilebase[tile] = predictors at the tile start
+ * 96 meta words, contiguous), the block scans the sums: tilebase[tile] = predictors at the tile start
  * (cpp-decoder/src/parser.cpp:108-111,141: three running predictors, never reset).
  */
 __global__ void __launch_bounds__(256) k_dc_tilebase(GjdDevBatch b) {
     __shared__ uint32_t ws[8];
     const uint32_t tid = threadIdx.x;
     const GjdImage& d = b.imgs[blockIdx.x];
-    const uint4* dc = reinterpret_cast<const uint4*>(b.dcdiff + (size_t)d.tile_first * 96u);
+    const uint4* mt = reinterpret_cast<const uint4*>(b.meta + (size_t)d.tile_first * 96u);
     int carry[3] = {0, 0, 0};
     for (uint32_t base = 0; base < d.tile_count; base += 256) {
         uint32_t t = base + tid;
         int sum[3] = {0, 0, 0};
         if (t < d.tile_count) {
 #pragma unroll
-            for (int i = 0; i < 12; i++) {
-                uint4 v = __ldg(dc + (size_t)t * 12 + i);
-                uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    sum[(i * 8 + j * 2) % 3] += (int)(int16_t)(w[j] & 0xffffu);
-                    sum[(i * 8 + j * 2 + 1) % 3] += (int)w[j] >> 16;
-                }
+            for (int i = 0; i < 24; i++) {
+                uint4 v = __ldg(mt + (size_t)t * 24 + i);
+                sum[(i * 4) % 3] += (int)(int16_t)(v.x & 0xffffu);
+                sum[(i * 4 + 1) % 3] += (int)(int16_t)(v.y & 0xffffu);
+                sum[(i * 4 + 2) % 3] += (int)(int16_t)(v.z & 0xffffu);
+                sum[(i * 4 + 3) % 3] += (int)(int16_t)(v.w & 0xffffu);
             }
         }
         int excl[3];
@@ -322,7 +333,7 @@ __device__ __forceinline__ int warp_incl_scan_i(int v, uint32_t lane) {
     return v;
 }
 
-#define GJD_TRANSFORM_THREADS 128
+#define GJD_TRANSFORM_THREADS 96
 
 /* natural index -> zigzag index as a compile-time function (GJD_ZZ_TABLE) */
 __host__ __device__ constexpr int gjd_zz_of_nat(int i) {
@@ -331,150 +342,151 @@ __host__ __device__ constexpr int gjd_zz_of_nat(int i) {
 }
 template <int I> struct GjdZz { static constexpr int value = gjd_zz_of_nat(I); };
 
-/* v[natural i] = scratch[zigzag(i)] for the calling thread; scratch layout [k/4][thread] int4,
- * q4 = &scratch[0][tid]. */
-template <int I> struct GjdGather {
-    static __device__ __forceinline__ void run(const int4* q4, int* v) {
-        GjdGather<I - 1>::run(q4, v);
+/* v[natural i] = coefficient at zigzag(i) of the block held as 32 packed words (two int16 each), times
+ * q[zigzag(i)]; the dezigzag is a compile-time renaming of registers. */
+template <int I> struct GjdUnpack {
+    static __device__ __forceinline__ void run(const uint32_t* w, const int* q, int* v) {
+        GjdUnpack<I - 1>::run(w, q, v);
         constexpr int k = GjdZz<I>::value;
-        const int4& t = q4[(k >> 2) * GJD_TRANSFORM_THREADS];
-        v[I] = (k & 3) == 0 ? t.x : (k & 3) == 1 ? t.y : (k & 3) == 2 ? t.z : t.w;
+        const int c = (k & 1) ? ((int)w[k >> 1] >> 16) : (int)(int16_t)(w[k >> 1] & 0xffffu);
+        v[I] = c * q[k];
     }
 };
-template <> struct GjdGather<-1> {
-    static __device__ __forceinline__ void run(const int4*, int*) {}
-};
-
-struct GjdScratchStore {
-    int* mine;            /* &scratch[0][tid] viewed as int: element k at mine[(k>>2)*THREADS*4 + (k&3)] */
-    const int* q;         /* quantisation table of the component, zigzag order */
-    __device__ __forceinline__ void operator()(uint32_t k, int v) const {
-        mine[(k >> 2) * (GJD_TRANSFORM_THREADS * 4) + (k & 3u)] = v * q[k];
-    }
+template <> struct GjdUnpack<0> {
+    static __device__ __forceinline__ void run(const uint32_t*, const int*, int*) {}
 };
 
 /*
- * Fused decode + transform.  One thread block per GJD_TB_TILES tiles of one image (the block loads
- * that image's Huffman LUTs and quantisation tables once), one warp per tile, one thread per MCU.
- * Per MCU and component: clear the thread's 64-entry shared-memory scratch, Huffman-decode the block
- * from mcu_p (the three blocks of an MCU are consecutive in the scan) storing value * q[k] at its
- * zigzag slot, warp-scan the DC differences onto the tile's DC base, gather the scratch in natural
- * order (compile-time renaming = dezigzag), integer IDCT in registers.  Y and Cb are parked packed
- * (9 bits each) in 64 registers; after Cr the colour conversion runs per row and each row of each
- * plane leaves as one 8-byte store (a warp covers 256 contiguous bytes of a row).
- * EXPORT = true turns the kernel into the coefficient test hook: quantisation forced to 1 and the
- * scratch written out in the reference layout mcu*192 + comp*64 + k instead of being transformed.
+ * One thread block (3 warps) per GJD_TB_TILES tiles of one image; per tile, warp c takes component c
+ * and lane l the 8x8 block of MCU l:
+ *   transform phase  load the block's coefficient sectors (only those the write pass produced: kmax from
+ *                    meta), warp-scan the DC differences onto the tile's DC base, dequantise + dezigzag
+ *                    into 64 registers, integer IDCT in registers, park the 64 samples (biased, 9 bits,
+ *                    as u16) in shared memory [comp][row][lane] — conflict-free 128-bit stores.
+ *   colour phase     warp c takes rows c, c+3, c+6: lane l reads row r of Y, Cb, Cr of MCU l (three
+ *                    128-bit loads), converts 8 pixels and stores 8 bytes per plane; a warp covers 256
+ *                    contiguous bytes of an image row.
+ * The sample buffer is double-buffered, so one __syncthreads per tile separates the phases.
+ * Splitting the components over warps keeps the straight-line code (unpack + IDCT, ~1100 instructions)
+ * inside the 32 KB instruction cache; the fused one-thread-per-MCU variant (4500 instructions) was
+ * instruction-fetch bound (profiles/r01b).
+ * EXPORT = true is the coefficient test hook: blocks are written out in the reference layout
+ * mcu*192 + comp*64 + k with the absolute DC in slot 0 instead of being transformed.
  */
 template <bool EXPORT>
-__global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 3) k_transform(GjdDevBatch b, int16_t* __restrict__ coef_out) {
-    __shared__ GjdLutSet lut;
+__global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 6) k_transform(GjdDevBatch b, int16_t* __restrict__ coef_out) {
     __shared__ int sq[3][64];
-    __shared__ int4 scratch[16][GJD_TRANSFORM_THREADS];
+    __shared__ uint4 smp[2][3][8][32];
 
-    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
+    const uint32_t tid = threadIdx.x, c = tid >> 5, lane = tid & 31u;
     const GjdImage& d = b.imgs[b.tb_img[blockIdx.x]];
     const uint32_t ltb = blockIdx.x - d.tb_first;
-    copy_lut_to_smem(&lut, b.luts + d.lut_id);
     {
         const int* qg = reinterpret_cast<const int*>(b.quants + d.quant_id);
-        for (uint32_t i = tid; i < 192; i += GJD_TRANSFORM_THREADS) sq[i / 64][i % 64] = EXPORT ? 1 : __ldg(qg + i);
+        for (uint32_t i = tid; i < 192; i += GJD_TRANSFORM_THREADS) sq[i / 64][i % 64] = __ldg(qg + i);
     }
     __syncthreads();
 
-    const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
-    const uint32_t scan_bits = d.scan_bits;
-    const uint32_t tabsel = gjd_pack_tabsel(d.tabsel);
     const uint32_t W = d.width, H = d.height;
     uint8_t* out = d.out_is_ptr ? reinterpret_cast<uint8_t*>(d.out_off) : b.rgb + d.out_off;
     const size_t pitch = d.row_pitch, pstride = d.plane_stride;
     const bool aligned = (((size_t)out | pitch | pstride) & 7u) == 0;
-    int4* mine4 = &scratch[0][tid];
-    uint32_t bad = 0;
+    const int* q = sq[c];
 
-    for (uint32_t t = warp; t < GJD_TB_TILES; t += GJD_TRANSFORM_THREADS / 32) {
+#pragma unroll 1
+    for (uint32_t t = 0; t < GJD_TB_TILES; t++) {
         const uint32_t ltile = ltb * GJD_TB_TILES + t;
         if (ltile >= d.tile_count) break;
         const uint32_t mcu = ltile * GJD_TILE_MCUS + lane;
         const bool valid = mcu < d.mcu_count;
+        const size_t blk = (size_t)(d.tile_first + ltile) * 96u + lane * 3u + c;
+
+        /* ---- transform phase: component c of MCU `lane` ---- */
+        const uint32_t m = valid ? __ldg(b.meta + blk) : 0u;
+        const uint32_t kmax = (m >> 16) & 63u;
+        const uint32_t nsec = kmax ? (kmax >> 4) + 1u : 0u;
+        const uint4* src = reinterpret_cast<const uint4*>(b.coef) + blk * 8u;
+        uint32_t w[32];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            uint4 r = make_uint4(0u, 0u, 0u, 0u);
+            if ((uint32_t)(j >> 1) < nsec) r = __ldcs(src + j);
+            w[4 * j] = r.x; w[4 * j + 1] = r.y; w[4 * j + 2] = r.z; w[4 * j + 3] = r.w;
+        }
         const int4 tb = b.tilebase[d.tile_first + ltile];
-        uint32_t p = valid ? b.mcu_p[(size_t)(d.tile_first + ltile) * GJD_TILE_MCUS + lane] : 0u;
-        if (p >= scan_bits) { if (valid) bad |= GJD_DEV_BADCOUNT; p = 0u; }
-        GjdWin win;
-        gjd_win_init(win, scan, p);
+        const int dc = warp_incl_scan_i((int)(int16_t)(m & 0xffffu), lane) + (c == 0 ? tb.x : c == 1 ? tb.y : tb.z);
+        if (EXPORT) {
+            if (valid) {
+                uint4* o = reinterpret_cast<uint4*>(coef_out + (size_t)mcu * 192u + c * 64u);
+                w[0] = (w[0] & 0xffff0000u) | ((uint32_t)dc & 0xffffu);
+#pragma unroll
+                for (int j = 0; j < 8; j++) o[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+            }
+            continue;
+        }
+        {
+            int v[64];
+            GjdUnpack<63>::run(w, q, v);
+            v[0] = dc * q[0];
+            gjd_idct8x8(v);
+#pragma unroll
+            for (int r = 0; r < 8; r++)
+                smp[t & 1u][c][r][lane] = make_uint4((uint32_t)v[8 * r] | ((uint32_t)v[8 * r + 1] << 16),
+                                                     (uint32_t)v[8 * r + 2] | ((uint32_t)v[8 * r + 3] << 16),
+                                                     (uint32_t)v[8 * r + 4] | ((uint32_t)v[8 * r + 5] << 16),
+                                                     (uint32_t)v[8 * r + 6] | ((uint32_t)v[8 * r + 7] << 16));
+        }
+        __syncthreads();
+
+        /* ---- colour phase: rows c, c+3, c+6 of MCU `lane` ---- */
         const uint32_t by = mcu / d.mcus_x, bx = mcu - by * d.mcus_x;
         const uint32_t x0 = bx * 8u, y0 = by * 8u;
         const bool fast = aligned && (x0 + 8u <= W);
-
-        uint32_t ycc[64];
 #pragma unroll 1
-        for (int c = 0; c < 3; c++) {
+        for (uint32_t r = c; r < 8u; r += 3u) {
+            if (!valid || y0 + r >= H) continue;
+            const uint4 y4 = smp[t & 1u][0][r][lane], b4 = smp[t & 1u][1][r][lane], r4 = smp[t & 1u][2][r][lane];
+            const uint32_t yw[4] = {y4.x, y4.y, y4.z, y4.w}, bw[4] = {b4.x, b4.y, b4.z, b4.w}, rw[4] = {r4.x, r4.y, r4.z, r4.w};
+            uint32_t pr[2] = {0, 0}, pg[2] = {0, 0}, pb[2] = {0, 0}, danger = 0;
 #pragma unroll
-            for (int j = 0; j < 16; j++) mine4[j * GJD_TRANSFORM_THREADS] = make_int4(0, 0, 0, 0);
-            int diff = 0;
-            uint32_t kmax = 0;
-            if (valid) {
-                diff = gjd_decode_dc(scan, win, &lut, (tabsel >> (4 * c)) & 3u, p, scan_bits, bad);
-                GjdScratchStore st;
-                st.mine = reinterpret_cast<int*>(mine4);
-                st.q = sq[c];
-                gjd_decode_ac(scan, win, &lut, (tabsel >> (4 * c + 2)) & 3u, p, scan_bits, st, kmax, bad);
+            for (int x = 0; x < 8; x++) {
+                const int sh = (x & 1) * 16;
+                int R, G, B;
+                if (gjd_color_fast((int)((yw[x >> 1] >> sh) & 0xffffu), (int)((bw[x >> 1] >> sh) & 0xffffu),
+                                   (int)((rw[x >> 1] >> sh) & 0xffffu), R, G, B))
+                    danger |= 1u << x;
+                pr[x >> 2] |= (uint32_t)R << (8 * (x & 3));
+                pg[x >> 2] |= (uint32_t)G << (8 * (x & 3));
+                pb[x >> 2] |= (uint32_t)B << (8 * (x & 3));
             }
-            __syncwarp();
-            const int dc = warp_incl_scan_i(diff, lane) + (c == 0 ? tb.x : c == 1 ? tb.y : tb.z);
-            if (EXPORT) {
-                if (valid) {
-                    const int* m = reinterpret_cast<const int*>(mine4);
-                    for (int k = 0; k < 64; k++) {
-                        int v = k == 0 ? dc : m[(k >> 2) * (GJD_TRANSFORM_THREADS * 4) + (k & 3)];
-                        coef_out[(size_t)mcu * 192u + c * 64u + k] = (int16_t)v;
-                    }
+            uint64_t g8 = ((uint64_t)pg[1] << 32) | pg[0];
+            if (danger) {   /* rare: G of the flagged pixels again with the reference's IEEE sequence */
+                const uint16_t* ys = reinterpret_cast<const uint16_t*>(&smp[t & 1u][0][r][lane]);
+                const uint16_t* bs = reinterpret_cast<const uint16_t*>(&smp[t & 1u][1][r][lane]);
+                const uint16_t* rs = reinterpret_cast<const uint16_t*>(&smp[t & 1u][2][r][lane]);
+#pragma unroll 1
+                for (uint32_t x = 0; x < 8u; x++) {
+                    if (!((danger >> x) & 1u)) continue;
+                    const uint64_t G = (uint64_t)gjd_color_g_exact((int)ys[x] - 256, (int)bs[x] - 256, (int)rs[x] - 256);
+                    g8 = (g8 & ~(0xffull << (8u * x))) | (G << (8u * x));
                 }
-                continue;
             }
-            int v[64];
-            GjdGather<63>::run(mine4, v);
-            v[0] = dc * sq[c][0];
-            gjd_idct8x8(v);
-            if (c == 0) {
-#pragma unroll
-                for (int i = 0; i < 64; i++) ycc[i] = (uint32_t)v[i];
-            } else if (c == 1) {
-#pragma unroll
-                for (int i = 0; i < 64; i++) ycc[i] |= (uint32_t)v[i] << 9;
-            } else if (valid) {
-#pragma unroll
-                for (int r = 0; r < 8; r++) {
-                    if (y0 + r < H) {
-                        uint32_t pr[2] = {0, 0}, pg[2] = {0, 0}, pb[2] = {0, 0};
-#pragma unroll
-                        for (int x = 0; x < 8; x++) {
-                            int R, G, B;
-                            gjd_color((int)(ycc[8 * r + x] & 511u), (int)(ycc[8 * r + x] >> 9), v[8 * r + x], R, G, B);
-                            pr[x >> 2] |= (uint32_t)R << (8 * (x & 3));
-                            pg[x >> 2] |= (uint32_t)G << (8 * (x & 3));
-                            pb[x >> 2] |= (uint32_t)B << (8 * (x & 3));
-                        }
-                        uint8_t* row = out + (size_t)(y0 + r) * pitch + x0;
-                        if (fast) {
-                            *reinterpret_cast<uint2*>(row) = make_uint2(pr[0], pr[1]);
-                            *reinterpret_cast<uint2*>(row + pstride) = make_uint2(pg[0], pg[1]);
-                            *reinterpret_cast<uint2*>(row + 2 * pstride) = make_uint2(pb[0], pb[1]);
-                        } else {
-#pragma unroll
-                            for (int x = 0; x < 8; x++) {
-                                if (x0 + x < W) {
-                                    row[x] = (uint8_t)(pr[x >> 2] >> (8 * (x & 3)));
-                                    row[pstride + x] = (uint8_t)(pg[x >> 2] >> (8 * (x & 3)));
-                                    row[2 * pstride + x] = (uint8_t)(pb[x >> 2] >> (8 * (x & 3)));
-                                }
-                            }
-                        }
-                    }
+            uint8_t* row = out + (size_t)(y0 + r) * pitch + x0;
+            if (fast) {
+                __stcs(reinterpret_cast<uint2*>(row), make_uint2(pr[0], pr[1]));
+                __stcs(reinterpret_cast<uint2*>(row + pstride), make_uint2((uint32_t)g8, (uint32_t)(g8 >> 32)));
+                __stcs(reinterpret_cast<uint2*>(row + 2 * pstride), make_uint2(pb[0], pb[1]));
+            } else {
+                const uint64_t r8 = ((uint64_t)pr[1] << 32) | pr[0], b8 = ((uint64_t)pb[1] << 32) | pb[0];
+#pragma unroll 1
+                for (uint32_t x = 0; x < 8u && x0 + x < W; x++) {
+                    row[x] = (uint8_t)(r8 >> (8u * x));
+                    row[pstride + x] = (uint8_t)(g8 >> (8u * x));
+                    row[2 * pstride + x] = (uint8_t)(b8 >> (8u * x));
                 }
             }
         }
     }
-    if (bad) atomicOr(b.status + b.tb_img[blockIdx.x], bad);
 }
 
 /* ------------------------------------------------------------------ test hooks -------- */
@@ -489,18 +501,22 @@ __global__ void k_test_color(const int16_t* __restrict__ y, const int16_t* __res
     r[i] = (uint8_t)R; g[i] = (uint8_t)G; bl[i] = (uint8_t)B;
 }
 
-/* dequantise + dezigzag + IDCT of stand-alone blocks, through the same scratch gather as k_transform */
+/* dequantise + dezigzag + IDCT of stand-alone blocks, through the same unpack as k_transform */
 __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS) k_test_idct(const int16_t* __restrict__ coef, size_t nblocks,
                                                                       const int32_t* __restrict__ quant,
                                                                       int16_t* __restrict__ out) {
-    __shared__ int4 scratch[16][GJD_TRANSFORM_THREADS];
+    __shared__ int sq[64];
+    if (threadIdx.x < 64) sq[threadIdx.x] = quant[threadIdx.x];
+    __syncthreads();
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nblocks) return;
-    int* mine = reinterpret_cast<int*>(&scratch[0][threadIdx.x]);
-    for (int k = 0; k < 64; k++)
-        mine[(k >> 2) * (GJD_TRANSFORM_THREADS * 4) + (k & 3)] = (int)coef[i * 64 + k] * quant[k];
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(coef + i * 64);
+    uint32_t w[32];
+#pragma unroll
+    for (int j = 0; j < 32; j++) w[j] = src[j];
     int v[64];
-    GjdGather<63>::run(&scratch[0][threadIdx.x], v);
+    GjdUnpack<63>::run(w, sq, v);
+    v[0] = (int)(int16_t)(w[0] & 0xffffu) * sq[0];
     gjd_idct8x8(v);
 #pragma unroll
     for (int j = 0; j < 64; j++) out[i * 64 + j] = (int16_t)(v[j] - 256);
@@ -533,8 +549,7 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     int n = 0;
     if (b.n_img == 0) { if (launches) *launches = 0; return cudaSuccess; }
     if (ev) GJD_CK(cudaEventRecord(ev->e[0], s));
-    GJD_CK(cudaMemsetAsync(b.dcdiff, 0, (size_t)b.n_tile * 96 * sizeof(int16_t), s));
-    GJD_CK(cudaMemsetAsync(b.mcu_p, 0xff, (size_t)b.n_tile * GJD_TILE_MCUS * sizeof(uint32_t), s));
+    GJD_CK(cudaMemsetAsync(b.meta, 0, (size_t)b.n_tile * 96 * sizeof(uint32_t), s));
     GJD_CK(cudaMemsetAsync(b.status, 0, (size_t)(b.n_img + 1) * sizeof(uint32_t), s));
     if (ev) GJD_CK(cudaEventRecord(ev->e[1], s));
     if (!skip_sync) {
@@ -543,7 +558,7 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     }
     if (ev) GJD_CK(cudaEventRecord(ev->e[2], s));
     k_seq_scan<<<b.n_img, 256, 0, s>>>(b); n++;
-    k_huff_index<<<b.n_seq, GJD_SYNC_THREADS, 0, s>>>(b); n++;
+    k_huff_write<<<b.n_seq, GJD_WRITE_THREADS, 0, s>>>(b); n++;
     k_dc_tilebase<<<b.n_img, 256, 0, s>>>(b); n++;
     if (ev) GJD_CK(cudaEventRecord(ev->e[3], s));
     k_transform<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr); n++;

@@ -21,8 +21,8 @@ struct GjdDevBatch {
     uint32_t* seq_img;     /* [n_seq]  sequence -> image */
     uint32_t* seq_base;    /* [n_seq]  coefficient index (within the image) at the sequence start */
     uint32_t n_seq;
-    uint32_t* mcu_p;       /* [n_tile * 32] bit position of every MCU's first symbol */
-    int16_t* dcdiff;       /* [n_tile * 96] */
+    int16_t* coef;         /* [n_tile * 96 * 64] quantised coefficients, one 128-byte line per block */
+    uint32_t* meta;        /* [n_tile * 96] per block: DC difference | kmax << 16 */
     int4* tilebase;        /* [n_tile] DC predictors at the tile start (x,y,z = comp 0,1,2) */
     uint32_t* tile_img;    /* [n_tile] tile -> image */
     uint32_t n_tile;
@@ -34,7 +34,8 @@ struct GjdDevBatch {
 };
 
 /* Stage timing events recorded by gjd_launch_pipeline: e[0] start, e[1] after the scratch clears,
- * e[2] after the sync stages, e[3] after the write stages, e[4] after the transform. */
+ * e[2] after the sync stages, e[3] after the write stages (count scan, coefficient write pass, DC
+ * bases), e[4] after the transform. */
 struct GjdStageEvents {
     cudaEvent_t e[5];
 };

@@ -8,13 +8,15 @@
  *   sinfo  u32x2 one state per subsequence (GJD_SUBSEQ_BITS bits of one image's scan), padded per
  *                image to a multiple of GJD_SEQ_SUBS ("sequence" = the subsequences one thread
  *                block synchronises): {p, (n << 8) | pos}.
- *   mcu_p  u32   bit position (in the image's unstuffed scan) of the first symbol of every MCU,
- *                [tile*32 + lane]; tile = 32 consecutive MCUs of one image (one warp of the
- *                transform kernel).  Written by the index pass.
- *   dcdiff i16   DC differences, [tile*96 + lane*3 + comp].  Cleared before every run.
+ *   coef   i16   quantised coefficients, zigzag order, one 128-byte line per 8x8 block:
+ *                [(tile*96 + lane*3 + comp) * 64 + k]; tile = 32 consecutive MCUs of one image (one
+ *                warp of the transform kernel), so an image's blocks sit in the reference order
+ *                mcu*192 + comp*64 + k (cuda-decoder/src/parser.cu:538).  Only the 32-byte sectors up
+ *                to the block's last non-zero coefficient are written (and later read); slot 0 is
+ *                unused (the DC difference travels in meta).
+ *   meta   u32   per block, same index as coef lines: [15:0] DC difference (i16), [21:16] kmax = the
+ *                last non-zero zigzag index (0 = DC only: no coef sector written).  Cleared per run.
  *   tilebase i32 [tile][4]: DC predictor of each component at the start of the tile.
- * There is no coefficient buffer: the transform kernel re-decodes each MCU's symbols from mcu_p
- * straight into shared memory (12 B/px of HBM traffic and a scattered 2-byte write pass avoided).
  *   rgb    u8    planar R,G,B output per image in the caller's pitch/stride geometry.
  */
 #ifndef GJD_TYPES_H
@@ -28,7 +30,7 @@
 #define GJD_LUT_BITS      10       /* primary Huffman LUT index width              */
 #define GJD_LUT_SIZE      (1 << GJD_LUT_BITS)
 #define GJD_TILE_MCUS     32u      /* MCUs per coefficient tile (one warp)         */
-#define GJD_TB_TILES      32u      /* tiles per transform thread block (one image)  */
+#define GJD_TB_TILES      8u       /* tiles per transform thread block (one image)  */
 
 /* LUT entry (u16):  [4:0] total bits = code length + value size (1..27)
  *                   [8:5] value size (0..15)

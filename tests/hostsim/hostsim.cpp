@@ -2,8 +2,8 @@
  * hostsim.cpp — TEST SCAFFOLDING: steps the product's __host__ __device__ functions
  * (gpu-jpeg-decoder_b200/csrc/gjd_devfn.cuh) and host parser on the CPU, thread by thread, in the
  * same order the CUDA kernels of gjd_kernels.cu do (cold decode, lock-step synchronisation rounds,
- * boundary fix-up, count scan, index pass (MCU bit positions + DC differences), and the fused
- * per-MCU decode + transform).  It exists because the build machine has no GPU: it lets `pytest -m "not gpu"` check
+ * boundary fix-up, count scan, coefficient write pass with block ownership and sector flushes, DC
+ * prefix and the per-MCU transform).  It exists because the build machine has no GPU: it lets `pytest -m "not gpu"` check
  * the algorithm and every arithmetic function against the oracle before a kernel ever runs.
  * It is not part of libgjd.so and nothing in the product can reach it.
  */
@@ -20,25 +20,22 @@
 
 namespace {
 
-struct Sink {
-    uint32_t* mcu_p;
-    int16_t* dcdiff;
-    uint32_t idx0, total;
-    uint32_t* bad;
-    void operator()(uint32_t rel, int v, uint32_t p) const {
-        uint32_t idx = idx0 + rel;
-        if (idx >= total) { *bad |= GJD_DEV_BADCOUNT; return; }
-        uint32_t blk = idx >> 6;
-        dcdiff[blk] = (int16_t)v;
-        uint32_t mcu = blk / 3u;
-        if (blk == mcu * 3u) mcu_p[mcu] = p;
+/* host twin of GjdWriteSink (gjd_kernels.cu): a 64-entry staging block per thread, flushed as whole
+ * 32-byte sectors up to kmax */
+struct WriteSink {
+    int16_t stage[64];
+    int16_t* coef;      /* image coefficient lines, 64 int16 per block */
+    uint32_t* meta;
+    uint8_t* written;   /* per block: times flushed (must end up exactly 1) */
+    void store(uint32_t k, int v) { stage[k] = (int16_t)v; }
+    void flush(uint32_t blk, int dcdiff, uint32_t kmax) {
+        meta[blk] = ((uint32_t)dcdiff & 0xffffu) | (kmax << 16);
+        written[blk]++;
+        if (kmax == 0u) return;
+        uint32_t n = ((kmax >> 4) + 1u) * 16u;
+        memcpy(coef + (size_t)blk * 64, stage, n * sizeof(int16_t));
+        memset(stage, 0, n * sizeof(int16_t));
     }
-};
-
-struct Store {
-    int* blk;
-    const int* q;
-    void operator()(uint32_t k, int v) const { blk[k] = v * q[k]; }
 };
 
 const int kZZ[64] = GJD_ZZ_TABLE;
@@ -97,7 +94,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
             st[tid].p = (sub0 + tid) * GJD_SUBSEQ_BITS; st[tid].n = 0; st[tid].pos = 0;
             if (active) {
                 uint32_t end = std::min((sub0 + tid + 1) * GJD_SUBSEQ_BITS, scan_bits);
-                gjd_decode_span<GJD_MODE_COUNT>(scan, lut, tabsel, end, scan_bits, st[tid], GjdNoSink(), bad);
+                gjd_count_span(scan, lut, tabsel, end, scan_bits, st[tid]);
             }
             bp[tid] = st[tid].p;
             bn[tid] = (st[tid].n << 8) | st[tid].pos;
@@ -111,7 +108,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
                 if (go) {
                     st[tid].n = 0;
                     uint32_t end = std::min((sub0 + j + 1) * GJD_SUBSEQ_BITS, scan_bits);
-                    gjd_decode_span<GJD_MODE_COUNT>(scan, lut, tabsel, end, scan_bits, st[tid], GjdNoSink(), bad);
+                    gjd_count_span(scan, lut, tabsel, end, scan_bits, st[tid]);
                     bool match = bp[j] == st[tid].p && (bn[j] & 255u) == st[tid].pos;
                     bp[j] = st[tid].p;
                     bn[j] = (st[tid].n << 8) | st[tid].pos;
@@ -137,7 +134,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
                 if (sub >= sub_count) { merged = true; break; }
                 st.n = 0;
                 uint32_t end = std::min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
-                gjd_decode_span<GJD_MODE_COUNT>(scan, lut, tabsel, end, scan_bits, st, GjdNoSink(), bad);
+                gjd_count_span(scan, lut, tabsel, end, scan_bits, st);
                 fix_decodes++;
                 size_t a = (size_t)g * GJD_SEQ_SUBS + t;
                 bool match = sp[a] == st.p && (sn[a] & 255u) == st.pos;
@@ -159,9 +156,10 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
         for (uint32_t t = 0; t < cnt; t++) carry += sn[(size_t)g * GJD_SEQ_SUBS + t] >> 8;
     }
     if (carry != 192u * mcu_count) status |= GJD_DEV_BADCOUNT;
-    /* k_huff_index */
-    std::vector<uint32_t> mcu_p((size_t)tile_count * 32, 0xffffffffu);
-    std::vector<int16_t> dcdiff((size_t)tile_count * 96, 0);
+    /* k_huff_write */
+    std::vector<int16_t> coef((size_t)tile_count * 96 * 64, (int16_t)0x7e7e);   /* stale garbage where nothing is written */
+    std::vector<uint32_t> meta((size_t)tile_count * 96, 0);
+    std::vector<uint8_t> written((size_t)tile_count * 96, 0);
     for (uint32_t g = 0; g < seq_count; g++) {
         uint32_t excl = 0;
         for (uint32_t tid = 0; tid < GJD_SEQ_SUBS; tid++) {
@@ -171,40 +169,36 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
             GjdState st; st.p = 0; st.n = 0; st.pos = 0;
             if (sub != 0) { st.p = sp[a - 1]; st.pos = sn[a - 1] & 255u; }
             uint32_t tbad = 0;
-            Sink sink{mcu_p.data(), dcdiff.data(), seq_base[g] + excl, 192u * mcu_count, &tbad};
-            if (sink.idx0 % 192u != st.pos && st.p < scan_bits) tbad |= GJD_DEV_BADSTATE;
+            WriteSink sink;
+            memset(sink.stage, 0, sizeof(sink.stage));
+            sink.coef = coef.data(); sink.meta = meta.data(); sink.written = written.data();
+            uint32_t idx0 = seq_base[g] + excl;
+            if (idx0 % 192u != st.pos && st.p < scan_bits) tbad |= GJD_DEV_BADSTATE;
             uint32_t end = std::min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
-            gjd_decode_span<GJD_MODE_INDEX>(scan, lut, tabsel, end, scan_bits, st, sink, tbad);
+            gjd_write_span(scan, lut, tabsel, end, scan_bits, st, idx0, 3u * mcu_count, true, sink, tbad);
+            for (int k = 0; k < 64; k++) if (sink.stage[k]) tbad |= GJD_DEV_BADSTATE;   /* staging must be left clean */
             status |= tbad;
             excl += sn[a] >> 8;
         }
     }
-    /* k_dc_tilebase + k_transform (fused decode) */
-    int q[3][64], qone[64];
+    for (uint32_t bk = 0; bk < 3u * mcu_count; bk++) if (written[bk] != 1) status |= GJD_DEV_BADCOUNT;
+    /* k_dc_tilebase + k_transform */
+    int q[3][64];
     for (int c = 0; c < 3; c++)
         for (int k = 0; k < 64; k++) q[c][k] = p.quant[p.qsel[c]][k];
-    for (int k = 0; k < 64; k++) qone[k] = 1;
     int pred[3] = {0, 0, 0};
     for (uint32_t mcu = 0; mcu < mcu_count; mcu++) {
         int samples[3][64];
-        uint32_t bp = mcu_p[mcu];
-        if (bp >= scan_bits) { status |= GJD_DEV_BADCOUNT; bp = 0; }
-        GjdWin win;
-        gjd_win_init(win, scan, bp);
         for (int c = 0; c < 3; c++) {
-            int zz[64] = {0}, zq[64] = {0};
-            uint32_t kmax = 0, tbad = 0;
-            uint32_t bp2 = bp;
-            GjdWin win2 = win;
-            int diff = gjd_decode_dc(scan, win, lut, (tabsel >> (4 * c)) & 3u, bp, scan_bits, tbad);
-            gjd_decode_ac(scan, win, lut, (tabsel >> (4 * c + 2)) & 3u, bp, scan_bits, Store{zz, q[c]}, kmax, tbad);
-            /* EXPORT variant: same decode with q = 1 */
-            gjd_decode_dc(scan, win2, lut, (tabsel >> (4 * c)) & 3u, bp2, scan_bits, tbad);
-            gjd_decode_ac(scan, win2, lut, (tabsel >> (4 * c + 2)) & 3u, bp2, scan_bits, Store{zq, qone}, kmax, tbad);
-            status |= tbad;
-            pred[c] += diff;
+            size_t bk = (size_t)mcu * 3 + c;
+            uint32_t m = meta[bk];
+            uint32_t kmax = (m >> 16) & 63u;
+            uint32_t nsec = kmax ? (kmax >> 4) + 1u : 0u;
+            int zq[64] = {0};
+            for (uint32_t k = 0; k < nsec * 16u; k++) zq[k] = coef[bk * 64 + k];
+            pred[c] += (int)(int16_t)(m & 0xffffu);
             int v[64];
-            for (int i = 0; i < 64; i++) v[i] = zz[kZZ[i]];
+            for (int i = 0; i < 64; i++) v[i] = zq[kZZ[i]] * q[c][kZZ[i]];
             v[0] = pred[c] * q[c][0];
             if (coef_out)
                 for (int k = 0; k < 64; k++) coef_out[(size_t)mcu * 192 + c * 64 + k] = (int16_t)(k == 0 ? pred[c] : zq[k]);
