@@ -295,15 +295,18 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         memcpy(d.qsel, p.qsel, 4);
         /* Huffman table set: dedup by content */
         {
-            uint64_t h = fnv1a(&p.dht, sizeof(GjdDhtSet));
+            GjdDhtSet key = p.dht;              /* the LUT ring depends on the scan's table selectors too */
+            memcpy(key.tabsel, p.tabsel, 8);
+            memset(key.pad, 0, sizeof(key.pad));
+            uint64_t h = fnv1a(&key, sizeof(GjdDhtSet));
             auto& cand = lut_index[h];
             int found = -1;
             for (uint32_t id : cand)
-                if (memcmp(&b->dhts[id], &p.dht, sizeof(GjdDhtSet)) == 0) { found = (int)id; break; }
+                if (memcmp(&b->dhts[id], &key, sizeof(GjdDhtSet)) == 0) { found = (int)id; break; }
             if (found < 0) {
                 if (b->dhts.size() >= 65535) { g.status = GJD_E_NOMEM; continue; }
                 found = (int)b->dhts.size();
-                b->dhts.push_back(p.dht);
+                b->dhts.push_back(key);
                 cand.push_back((uint32_t)found);
             }
             d.lut_id = (uint16_t)found;

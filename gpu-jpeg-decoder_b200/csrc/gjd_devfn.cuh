@@ -31,10 +31,10 @@
 /* Pack one decoded symbol into the LUT entry format of gjd_types.h. */
 GJD_HD uint32_t gjd_make_entry(uint32_t code_len, uint32_t sym, uint32_t isdc) {
     uint32_t size = sym & 15u;
-    uint32_t adv = isdc ? 1u : ((sym == 0u) ? 0u : (sym >> 4) + 1u);
+    uint32_t adv = isdc ? 1u : ((sym == 0u) ? GJD_ADV_EOB : (sym >> 4) + 1u);
     return (code_len + size) | (size << 5) | (adv << 9);
 }
-#define GJD_ENTRY_BAD 0x4000u   /* bit 14: no code assigned to these bits */
+#define GJD_ENTRY_BAD 0x10000u   /* bit 16 (slow path only): no code assigned to these bits */
 
 /* Canonical code tables from BITS[16]: lim[L] = first unused code of length L left-aligned to
  * 16 bits (non-decreasing in L), off[L] = valptr[L] - mincode[L].
@@ -64,7 +64,7 @@ GJD_HD uint32_t gjd_resolve(const uint32_t* lim, const int32_t* off, const uint8
     return 16u | (1u << 9) | GJD_ENTRY_BAD;
 }
 
-/* Primary LUT entry for index i (GJD_LUT_BITS leading bits). */
+/* Primary LUT entry for index i (GJD_LUT_BITS leading bits); 0 = not resolvable from these bits. */
 GJD_HD uint16_t gjd_lut_entry(const uint32_t* lim, const int32_t* off, const uint8_t* vals,
                               uint32_t isdc, uint32_t i) {
     uint32_t win16 = i << (16 - GJD_LUT_BITS);
@@ -74,7 +74,12 @@ GJD_HD uint16_t gjd_lut_entry(const uint32_t* lim, const int32_t* off, const uin
             return (uint16_t)gjd_make_entry((uint32_t)L, vals[idx], isdc);
         }
     }
-    return (uint16_t)GJD_LUT_SLOW;
+    return 0;
+}
+
+/* DHT slot behind ring position r (0..5): even = DC table, odd = AC table of component r/2. */
+GJD_HD uint32_t gjd_ring_slot(const uint8_t tabsel[8], uint32_t r) {
+    return (uint32_t)tabsel[(r & 1u) * 4u + (r >> 1)] & 3u;
 }
 
 /* ------------------------------------------------------------------ bit reader -------- */
@@ -116,18 +121,17 @@ GJD_HD uint32_t gjd_peek32(GjdWin& c, const uint32_t* scan, uint32_t p) {
 
 /* ------------------------------------------------------------------ entropy decode ---- */
 
-/* Decoder state between symbols: p = bit position in the image's unstuffed scan, n = coefficient
- * slots advanced so far, pos = comp*64 + zigzag index (0..191) of the next slot.
+/* Decoder state between symbols as stored in sinfo: p = bit position in the image's unstuffed scan,
+ * n = coefficient slots advanced so far, pos = comp*64 + zigzag index (0..191) of the next slot.
  * This is the (p, n, c, z) state of the reference's decodeSequence (cuda-decoder/src/parser.cu:50-121). */
 struct GjdState {
     uint32_t p, n, pos;
 };
 
-/* tabsel packed: bits [4c+1:4c] = LUT slot of component c's DC table, [4c+3:4c+2] = its AC table. */
-GJD_HD uint32_t gjd_pack_tabsel(const uint8_t tabsel[8]) {
-    uint32_t s = 0;
-    for (int c = 0; c < 3; c++) s |= ((uint32_t)(tabsel[c] & 3) << (4 * c)) | ((uint32_t)(tabsel[4 + c] & 3) << (4 * c + 2));
-    return s;
+/* Inside the loops the state is (p, q, tb): q = slot counter with q & 63 = zigzag index (starts at
+ * pos, never wraps), tb = byte offset of the current table in the LUT ring. */
+GJD_HD uint32_t gjd_ring_of_pos(uint32_t pos) {
+    return ((pos >> 6) * 2u + ((pos & 63u) ? 1u : 0u)) * GJD_RING_STRIDE;
 }
 
 /* JPEG EXTEND of the `size` value bits that follow a code of `len` bits in the 32-bit window w
@@ -138,41 +142,83 @@ GJD_HD int gjd_extend(uint32_t w, uint32_t len, uint32_t size) {
     return (vb >> (size - 1u)) ? (int)vb : (int)vb - (int)((1u << size) - 1u);
 }
 
-GJD_HD uint32_t gjd_lookup(const GjdLutSet* lut, uint32_t slot, uint32_t w) {
-    uint32_t e = lut->lut[slot][w >> (32 - GJD_LUT_BITS)];
-    if (e & GJD_LUT_SLOW)
-        e = gjd_resolve(lut->lim[slot], lut->off[slot], lut->vals[slot], lut->isdc[slot], w >> 16, GJD_LUT_BITS + 1);
+/* Where the decoders read the LUT ring from: a GjdLutSet in generic (global or host) memory ... */
+struct GjdLutMem {
+    const GjdLutSet* set;
+    GJD_HD uint32_t entry(uint32_t off) const {
+        return *reinterpret_cast<const uint16_t*>(reinterpret_cast<const char*>(set->lut) + off);
+    }
+};
+#ifdef __CUDACC__
+/* ... or a copy in shared memory, addressed by its 32-bit shared-window offset (one LDS, no generic
+ * address arithmetic in the loop). */
+struct GjdLutSmem {
+    const GjdLutSet* set;
+    uint32_t base;
+    __device__ __forceinline__ explicit GjdLutSmem(const GjdLutSet* s) : set(s) {
+        /* opaque move: keeps the window offset in a register instead of re-deriving it per symbol */
+        asm volatile("mov.u32 %0, %1;" : "=r"(base) : "r"((uint32_t)__cvta_generic_to_shared(s->lut)));
+    }
+    __device__ __forceinline__ uint32_t entry(uint32_t off) const {
+        uint16_t v;
+        asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(base + off));
+        return v;
+    }
+};
+#endif
+
+/* Rare path: the code is longer than GJD_LUT_BITS, or unassigned.  An unassigned code consumes 16 bits
+ * and comes back with advance 0 (no slot): the write pass flags it, and both passes treat it alike. */
+GJD_HD_COLD uint32_t gjd_lookup_slow(const GjdLutSet* lut, uint32_t tb, uint32_t w) {
+    uint32_t slot = lut->slot_of[tb / GJD_RING_STRIDE];
+    uint32_t e = gjd_resolve(lut->lim[slot], lut->off[slot], lut->vals[slot], lut->isdc[slot], w >> 16, GJD_LUT_BITS + 1);
+    return (e & GJD_ENTRY_BAD) ? 16u : e;
+}
+
+/* One symbol at window w with the ring at tb: the 16-bit LUT entry. */
+template <class Lut>
+GJD_HD uint32_t gjd_lookup(const Lut& lut, uint32_t tb, uint32_t w) {
+    uint32_t e = lut.entry(tb + ((w >> (31 - GJD_LUT_BITS)) & (GJD_RING_STRIDE - 2u)));
+    if ((e & 31u) == 0u) e = gjd_lookup_slow(lut.set, tb, w);
     return e;
+}
+
+/* Advance the slot counter and the table ring over the symbol with entry e.  Returns the new zigzag
+ * index (64 = the block is complete). */
+GJD_HD uint32_t gjd_advance(uint32_t e, uint32_t& q, uint32_t& tb) {
+    const uint32_t qz = q & 63u;
+    uint32_t t = qz + (e >> 9);
+    t = t > 64u ? 64u : t;
+    q = q - qz + t;
+    if (qz == 0u || t == 64u) {          /* after a DC symbol, and at a block end: next table */
+        tb += GJD_RING_STRIDE;
+        if (tb == GJD_RING_BYTES) tb = 0u;
+    }
+    return t;
 }
 
 /* Decode symbols that START before end_bits, beginning at state s.  A symbol that would run past
  * scan_bits is padding and is not counted.
  * Follows JPEGParser::buildMCU (cpp-decoder/src/parser.cpp:105-134): DC size/diff; AC run/size with
  * EOB = 0x00, "length += run", value bits always consumed, coefficient kept only if index < 64. */
-GJD_HD void gjd_count_span(const uint32_t* scan, const GjdLutSet* lut, uint32_t tabsel,
-                           uint32_t end_bits, uint32_t scan_bits, GjdState& s) {
+template <class Lut>
+GJD_HD void gjd_count_span(const uint32_t* scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
+                           GjdState& s) {
     if (s.p >= end_bits) return;
     GjdWin win;
     gjd_win_init(win, scan, s.p);
-    uint32_t p = s.p, n = s.n, pos = s.pos;
+    uint32_t p = s.p, q = s.pos, tb = gjd_ring_of_pos(s.pos);
     while (p < end_bits) {
-        uint32_t w = gjd_peek32(win, scan, p);
-        uint32_t z = pos & 63u;
-        uint32_t c = pos >> 6;
-        uint32_t slot = (tabsel >> (4u * c + (z ? 2u : 0u))) & 3u;
-        uint32_t e = gjd_lookup(lut, slot, w);
-        uint32_t total = e & 31u;
-        if (p + total > scan_bits) break;
-        uint32_t adv = (e >> 9) & 31u;
-        uint32_t znew = adv ? z + adv : 64u;
-        if (znew > 64u) znew = 64u;
-        uint32_t d = znew - z;
-        n += d;
-        pos += d;
-        if (pos == 192u) pos = 0u;
-        p += total;
+        const uint32_t w = gjd_peek32(win, scan, p);
+        const uint32_t e = gjd_lookup(lut, tb, w);
+        const uint32_t pn = p + (e & 31u);
+        if (pn > scan_bits) break;
+        p = pn;
+        gjd_advance(e, q, tb);
     }
-    s.p = p; s.n = n; s.pos = pos;
+    s.p = p;
+    s.n += q - s.pos;
+    s.pos = q % 192u;
 }
 
 /* Warp-wide "any lane still running": keeps the 32 lanes of a warp in one converged loop on the GPU
@@ -195,64 +241,50 @@ GJD_HD void gjd_count_span(const uint32_t* scan, const GjdLutSet* lut, uint32_t 
  * without a subsequence).
  * Same buildMCU semantics as gjd_count_span (cpp-decoder/src/parser.cpp:105-134).
  */
-template <class Sink>
-GJD_HD void gjd_write_span(const uint32_t* scan, const GjdLutSet* lut, uint32_t tabsel, uint32_t end_bits,
-                           uint32_t scan_bits, GjdState s, uint32_t idx0, uint32_t nblocks, bool enable,
-                           Sink& sink, uint32_t& bad) {
+template <class Lut, class Sink>
+GJD_HD void gjd_write_span(const uint32_t* scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
+                           GjdState s, uint32_t idx0, uint32_t nblocks, bool enable, Sink& sink, uint32_t& bad) {
     bool run = enable && s.p < end_bits;
     GjdWin win;
     win.wi = 0; win.w0 = 0; win.w1 = 0;
     if (run) gjd_win_init(win, scan, s.p);
-    uint32_t p = s.p, pos = s.pos;
-    bool own = (pos & 63u) == 0u;                    /* false: inside the previous thread's block */
+    uint32_t p = s.p, q = s.pos, tb = gjd_ring_of_pos(s.pos);
+    bool own = (q & 63u) == 0u;                      /* false: inside the previous thread's block */
     uint32_t blk = (idx0 + 63u) >> 6;
     int dcdiff = 0;
     uint32_t kmax = 0;
     while (GJD_WARP_ANY(run)) {
         if (!run) continue;
-        const uint32_t z = pos & 63u;
+        const uint32_t z = q & 63u;
         if (p >= end_bits && (z == 0u || !own)) { run = false; continue; }
-        const uint32_t c = pos >> 6;
         const uint32_t w = gjd_peek32(win, scan, p);
-        const uint32_t e = gjd_lookup(lut, (tabsel >> (4u * c + (z ? 2u : 0u))) & 3u, w);
+        const uint32_t e = gjd_lookup(lut, tb, w);
         const uint32_t total = e & 31u;
         if (p + total > scan_bits) {                 /* padding at a block start is the normal end */
             if (own && z != 0u) bad |= GJD_DEV_BADCOUNT;
             run = false;
             continue;
         }
-        const uint32_t size = (e >> 5) & 15u;
-        const uint32_t adv = (e >> 9) & 31u;
         p += total;
-        uint32_t znew;
-        if (own) {
-            if (e & GJD_ENTRY_BAD) bad |= GJD_DEV_BADCODE;
-            if (blk >= nblocks) { bad |= GJD_DEV_BADCOUNT; run = false; continue; }
-            const int v = gjd_extend(w, total - size, size);
-            if (z == 0u) {
-                dcdiff = v;
-                znew = 1u;
-            } else if (adv == 0u) {
-                znew = 64u;                          /* EOB */
-            } else {
-                const uint32_t k = z + adv - 1u;     /* run */
-                if (k < 64u && size) { sink.store(k, v); kmax = k; }
-                znew = k + 1u;
-            }
-        } else {
-            znew = adv ? z + adv : 64u;
+        const uint32_t t = gjd_advance(e, q, tb);
+        if (!own) {
+            own = t == 64u;
+            continue;
         }
-        if (znew >= 64u) {
-            if (own) {
-                sink.flush(blk, dcdiff, kmax);
-                blk++;
-                kmax = 0u;
-            }
-            own = true;
-            pos = (pos | 63u) + 1u;
-            if (pos == 192u) pos = 0u;
-        } else {
-            pos = (pos & ~63u) + znew;
+        if (e < 512u) bad |= GJD_DEV_BADCODE;       /* advance 0: unassigned code */
+        const uint32_t size = (e >> 5) & 15u;
+        const int v = gjd_extend(w, total - size, size);
+        if (z == 0u) {
+            dcdiff = v;
+        } else if (size) {                           /* EOB and ZRL carry no value */
+            const uint32_t k = z + (e >> 9) - 1u;
+            if (k < 64u) { sink.store(k, v); kmax = k; }
+        }
+        if (t == 64u) {
+            if (blk >= nblocks) { bad |= GJD_DEV_BADCOUNT; run = false; continue; }
+            sink.flush(blk, dcdiff, kmax);
+            blk++;
+            kmax = 0u;
         }
     }
 }

@@ -73,11 +73,13 @@ __global__ void __launch_bounds__(256) k_build_luts(const GjdDhtSet* __restrict_
         }
         out.isdc[threadIdx.x] = in.isdc[threadIdx.x];
     }
+    if (threadIdx.x < GJD_RING_TABLES) out.slot_of[threadIdx.x] = (uint8_t)gjd_ring_slot(in.tabsel, threadIdx.x);
     for (uint32_t i = threadIdx.x; i < 4 * 256; i += blockDim.x) out.vals[i >> 8][i & 255] = in.vals[i >> 8][i & 255];
     __syncthreads();
-    for (uint32_t i = threadIdx.x; i < 4 * GJD_LUT_SIZE; i += blockDim.x) {
-        uint32_t t = i / GJD_LUT_SIZE, j = i % GJD_LUT_SIZE;
-        out.lut[t][j] = gjd_lut_entry(lim[t], off[t], in.vals[t], in.isdc[t], j);
+    for (uint32_t i = threadIdx.x; i < GJD_RING_TABLES * GJD_LUT_SIZE; i += blockDim.x) {
+        uint32_t r = i / GJD_LUT_SIZE, j = i % GJD_LUT_SIZE;
+        uint32_t t = gjd_ring_slot(in.tabsel, r);
+        out.lut[r][j] = gjd_lut_entry(lim[t], off[t], in.vals[t], in.isdc[t], j);
     }
 }
 
@@ -108,8 +110,8 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
     const uint32_t sub0 = ls * GJD_SEQ_SUBS;
     const uint32_t sub_count = d.sub_count, scan_bits = d.scan_bits;
     const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
-    const uint32_t tabsel = gjd_pack_tabsel(d.tabsel);
     copy_lut_to_smem(&lut, b.luts + d.lut_id);
+    const GjdLutSmem slut(&lut);
     __syncthreads();
 
     const bool active = sub0 + tid < sub_count;
@@ -119,7 +121,7 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
     st.pos = 0;
     if (active) {
         uint32_t end = min((sub0 + tid + 1) * GJD_SUBSEQ_BITS, scan_bits);
-        gjd_count_span(scan, &lut, tabsel, end, scan_bits, st);
+        gjd_count_span(scan, slut, end, scan_bits, st);
     }
     sp[tid] = st.p;
     sn[tid] = (st.n << 8) | st.pos;
@@ -133,7 +135,7 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
         if (go) {
             st.n = 0;
             uint32_t end = min((sub0 + j + 1) * GJD_SUBSEQ_BITS, scan_bits);
-            gjd_count_span(scan, &lut, tabsel, end, scan_bits, st);
+            gjd_count_span(scan, slut, end, scan_bits, st);
             bool match = sp[j] == st.p && (sn[j] & 255u) == st.pos;
             sp[j] = st.p;
             sn[j] = (st.n << 8) | st.pos;
@@ -159,8 +161,8 @@ __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
     uint32_t ls = g - d.seq_first;
     if (ls == 0) return;
     const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
-    const GjdLutSet* lut = b.luts + d.lut_id;
-    const uint32_t tabsel = gjd_pack_tabsel(d.tabsel);
+    GjdLutMem glut;
+    glut.set = b.luts + d.lut_id;
     const uint32_t scan_bits = d.scan_bits;
     uint2* si = b.sinfo + (size_t)g * GJD_SEQ_SUBS;
     uint2 prev = si[-1];
@@ -174,7 +176,7 @@ __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
         if (sub >= d.sub_count) { merged = true; break; }
         st.n = 0;
         uint32_t end = min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
-        gjd_count_span(scan, lut, tabsel, end, scan_bits, st);
+        gjd_count_span(scan, glut, end, scan_bits, st);
         uint2 old = si[t];
         si[t] = make_uint2(st.p, (st.n << 8) | st.pos);
         if (old.x == st.p && (old.y & 255u) == st.pos) { merged = true; break; }
@@ -231,11 +233,18 @@ struct GjdWriteSink {
         meta[blk] = ((uint32_t)dcdiff & 0xffffu) | (kmax << 16);
         if (kmax == 0u) return;
         uint4* dst = coef + (size_t)blk * 8u;
-        const uint32_t nchunk = ((kmax >> 4) + 1u) * 2u;
-        for (uint32_t j = 0; j < nchunk; j++) {
-            uint4* src = mine + j * GJD_WRITE_THREADS;
-            dst[j] = *src;
-            *src = make_uint4(0u, 0u, 0u, 0u);
+        const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+        for (uint32_t s = 0; s < 4; s++) {
+            if (s == 0u || kmax >= 16u * s) {
+                uint4* s0 = mine + (2u * s) * GJD_WRITE_THREADS;
+                uint4* s1 = mine + (2u * s + 1u) * GJD_WRITE_THREADS;
+                const uint4 a = *s0, c = *s1;
+                dst[2u * s] = a;
+                dst[2u * s + 1u] = c;
+                *s0 = zero;
+                *s1 = zero;
+            }
         }
     }
 };
@@ -245,7 +254,7 @@ struct GjdWriteSink {
  * coefficient index seq_base + (block-exclusive scan of the counts), and writes the blocks it owns
  * (gjd_write_span).
  */
-__global__ void __launch_bounds__(GJD_WRITE_THREADS, 5) k_huff_write(GjdDevBatch b) {
+__global__ void __launch_bounds__(GJD_WRITE_THREADS, 4) k_huff_write(GjdDevBatch b) {
     __shared__ GjdLutSet lut;
     __shared__ uint4 buf[8][GJD_WRITE_THREADS];
     __shared__ uint32_t ws[8];
@@ -256,10 +265,10 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, 5) k_huff_write(GjdDevBatch
     const uint32_t sub = ls * GJD_SEQ_SUBS + tid;
     const uint32_t scan_bits = d.scan_bits;
     const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
-    const uint32_t tabsel = gjd_pack_tabsel(d.tabsel);
     const bool active = sub < d.sub_count;
     const uint2* si = b.sinfo + (size_t)g * GJD_SEQ_SUBS;
     copy_lut_to_smem(&lut, b.luts + d.lut_id);
+    const GjdLutSmem slut(&lut);
 #pragma unroll
     for (int j = 0; j < 8; j++) buf[j][tid] = make_uint4(0u, 0u, 0u, 0u);
 
@@ -282,7 +291,7 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, 5) k_huff_write(GjdDevBatch
     const uint32_t idx0 = b.seq_base[g] + excl;
     if (active && idx0 % 192u != st.pos && st.p < scan_bits) bad |= GJD_DEV_BADSTATE;
     uint32_t end = min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
-    gjd_write_span(scan, &lut, tabsel, end, scan_bits, st, idx0, 3u * d.mcu_count, active, sink, bad);
+    gjd_write_span(scan, slut, end, scan_bits, st, idx0, 3u * d.mcu_count, active, sink, bad);
     if (bad) atomicOr(b.status + img, bad);
 }
 

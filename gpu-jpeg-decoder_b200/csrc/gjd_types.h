@@ -32,30 +32,37 @@
 #define GJD_TILE_MCUS     32u      /* MCUs per coefficient tile (one warp)         */
 #define GJD_TB_TILES      8u       /* tiles per transform thread block (one image)  */
 
-/* LUT entry (u16):  [4:0] total bits = code length + value size (1..27)
- *                   [8:5] value size (0..15)
- *                   [13:9] advance = run + 1 (1..16); 0 = EOB (jump to the end of the block)
- *                   [15]   code longer than GJD_LUT_BITS: resolve with the canonical tables   */
-#define GJD_LUT_SLOW 0x8000u
+/* LUT entry (u16):  [4:0]  total bits = code length + value size (1..27); 0 = code longer than
+ *                          GJD_LUT_BITS (or unassigned): resolve with the canonical tables
+ *                   [8:5]  value size (0..15)
+ *                   [15:9] slot advance = run + 1 (1..16; DC symbols: 1); 64 = EOB (to the block end) */
+#define GJD_ADV_EOB 64u
+#define GJD_RING_TABLES 6
+#define GJD_RING_STRIDE (GJD_LUT_SIZE * 2u)                  /* bytes per table of the ring        */
+#define GJD_RING_BYTES  (GJD_RING_TABLES * GJD_RING_STRIDE)
 
-/* One Huffman table set (the 4 tables an image uses), device-resident, built by k_build_luts.
- * Slots: 0 = DC table of component 0, 1 = DC table of components 1/2 … the per-image
- * comp -> slot mapping is in GjdImage::tabsel. */
+/* One Huffman table set as the decoders use it, device-resident, built by k_build_luts from a
+ * GjdDhtSet: the primary LUTs laid out as a RING in scan order — DC(comp 0), AC(comp 0), DC(comp 1),
+ * AC(comp 1), DC(comp 2), AC(comp 2) — so that "next table" is "+1 table, wrap after 6" (a DC symbol
+ * and a block end each advance the ring by one).  The canonical tables of the 4 DHT slots
+ * (0,1 = DC Th 0,1; 2,3 = AC Th 0,1) serve the rare long codes; slot_of maps ring position -> slot. */
 typedef struct GjdLutSet {
-    uint16_t lut[4][GJD_LUT_SIZE];   /* primary LUTs                                             */
+    uint16_t lut[GJD_RING_TABLES][GJD_LUT_SIZE];
     uint32_t lim[4][17];             /* lim[L] = first unused code of length L, left-aligned to 16 bits */
     int32_t  off[4][17];             /* valptr[L] - mincode[L]                                   */
     uint8_t  vals[4][256];           /* HUFFVAL                                                  */
     uint8_t  isdc[4];                /* 1 for DC tables (value size = symbol, advance = 1)       */
-    uint8_t  pad[12];
+    uint8_t  slot_of[GJD_RING_TABLES];
+    uint8_t  pad[6];
 } GjdLutSet;
 
-/* Raw DHT content the LUT builder consumes (host -> device). */
+/* Raw DHT content + the scan's table selectors: what the LUT builder consumes (host -> device). */
 typedef struct GjdDhtSet {
     uint8_t bits[4][16];
     uint8_t vals[4][256];
     uint8_t isdc[4];
-    uint8_t pad[12];
+    uint8_t tabsel[8];               /* [c] = slot of component c's DC table, [4+c] = its AC table */
+    uint8_t pad[4];
 } GjdDhtSet;
 
 /* The quantisation table of each component, zigzag order, widened to i32 for broadcast loads. */

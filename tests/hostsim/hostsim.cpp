@@ -69,10 +69,15 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
         gjd_canonical(p.dht.bits[t], lut->lim[t], lut->off[t]);
         memcpy(lut->vals[t], p.dht.vals[t], 256);
         lut->isdc[t] = p.dht.isdc[t];
-        for (uint32_t i = 0; i < GJD_LUT_SIZE; i++)
-            lut->lut[t][i] = gjd_lut_entry(lut->lim[t], lut->off[t], lut->vals[t], lut->isdc[t], i);
     }
-    const uint32_t tabsel = gjd_pack_tabsel(p.tabsel);
+    for (uint32_t r = 0; r < GJD_RING_TABLES; r++) {
+        uint32_t t = gjd_ring_slot(p.tabsel, r);
+        lut->slot_of[r] = (uint8_t)t;
+        for (uint32_t i = 0; i < GJD_LUT_SIZE; i++)
+            lut->lut[r][i] = gjd_lut_entry(lut->lim[t], lut->off[t], lut->vals[t], lut->isdc[t], i);
+    }
+    GjdLutMem hlut;
+    hlut.set = lut;
     const uint32_t scan_bits = (uint32_t)ulen * 8u;
     const uint32_t sub_count = std::max<uint32_t>(1u, (scan_bits + GJD_SUBSEQ_BITS - 1) / GJD_SUBSEQ_BITS);
     const uint32_t seq_count = (sub_count + GJD_SEQ_SUBS - 1) / GJD_SEQ_SUBS;
@@ -94,7 +99,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
             st[tid].p = (sub0 + tid) * GJD_SUBSEQ_BITS; st[tid].n = 0; st[tid].pos = 0;
             if (active) {
                 uint32_t end = std::min((sub0 + tid + 1) * GJD_SUBSEQ_BITS, scan_bits);
-                gjd_count_span(scan, lut, tabsel, end, scan_bits, st[tid]);
+                gjd_count_span(scan, hlut, end, scan_bits, st[tid]);
             }
             bp[tid] = st[tid].p;
             bn[tid] = (st[tid].n << 8) | st[tid].pos;
@@ -108,7 +113,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
                 if (go) {
                     st[tid].n = 0;
                     uint32_t end = std::min((sub0 + j + 1) * GJD_SUBSEQ_BITS, scan_bits);
-                    gjd_count_span(scan, lut, tabsel, end, scan_bits, st[tid]);
+                    gjd_count_span(scan, hlut, end, scan_bits, st[tid]);
                     bool match = bp[j] == st[tid].p && (bn[j] & 255u) == st[tid].pos;
                     bp[j] = st[tid].p;
                     bn[j] = (st[tid].n << 8) | st[tid].pos;
@@ -134,7 +139,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
                 if (sub >= sub_count) { merged = true; break; }
                 st.n = 0;
                 uint32_t end = std::min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
-                gjd_count_span(scan, lut, tabsel, end, scan_bits, st);
+                gjd_count_span(scan, hlut, end, scan_bits, st);
                 fix_decodes++;
                 size_t a = (size_t)g * GJD_SEQ_SUBS + t;
                 bool match = sp[a] == st.p && (sn[a] & 255u) == st.pos;
@@ -175,7 +180,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
             uint32_t idx0 = seq_base[g] + excl;
             if (idx0 % 192u != st.pos && st.p < scan_bits) tbad |= GJD_DEV_BADSTATE;
             uint32_t end = std::min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
-            gjd_write_span(scan, lut, tabsel, end, scan_bits, st, idx0, 3u * mcu_count, true, sink, tbad);
+            gjd_write_span(scan, hlut, end, scan_bits, st, idx0, 3u * mcu_count, true, sink, tbad);
             for (int k = 0; k < 64; k++) if (sink.stage[k]) tbad |= GJD_DEV_BADSTATE;   /* staging must be left clean */
             status |= tbad;
             excl += sn[a] >> 8;
