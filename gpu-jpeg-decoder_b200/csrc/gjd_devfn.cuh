@@ -137,14 +137,23 @@ GJD_HD uint32_t gjd_ring_of_pos(uint32_t pos) {
 /* JPEG EXTEND of the `size` value bits that follow a code of `len` bits in the 32-bit window w
  * (Stream::decodeNumber, cpp-decoder/utils/stream.cpp:44-51). */
 GJD_HD int gjd_extend(uint32_t w, uint32_t len, uint32_t size) {
+#ifdef __CUDA_ARCH__
+    /* branch-free; shifts by 32 give 0 on the GPU, so size == 0 yields 0 */
+    const int t = (int)(w << len);                       /* value bits left-aligned */
+    const uint32_t vb = (uint32_t)t >> (32u - size);
+    const int neg = ~(t >> 31);                          /* all ones when the leading value bit is 0 */
+    return (int)vb + (neg & (int)(1u - (1u << size)));
+#else
     if (size == 0u) return 0;
     uint32_t vb = (w << len) >> (32u - size);
     return (vb >> (size - 1u)) ? (int)vb : (int)vb - (int)((1u << size) - 1u);
+#endif
 }
 
 /* Where the decoders read the LUT ring from: a GjdLutSet in generic (global or host) memory ... */
 struct GjdLutMem {
     const GjdLutSet* set;
+    uint32_t* badcode;      /* set to 1 when an unassigned code is met (write pass only; may be null) */
     GJD_HD uint32_t entry(uint32_t off) const {
         return *reinterpret_cast<const uint16_t*>(reinterpret_cast<const char*>(set->lut) + off);
     }
@@ -154,8 +163,9 @@ struct GjdLutMem {
  * address arithmetic in the loop). */
 struct GjdLutSmem {
     const GjdLutSet* set;
+    uint32_t* badcode;
     uint32_t base;
-    __device__ __forceinline__ explicit GjdLutSmem(const GjdLutSet* s) : set(s) {
+    __device__ __forceinline__ explicit GjdLutSmem(const GjdLutSet* s, uint32_t* bc = nullptr) : set(s), badcode(bc) {
         /* opaque move: keeps the window offset in a register instead of re-deriving it per symbol */
         asm volatile("mov.u32 %0, %1;" : "=r"(base) : "r"((uint32_t)__cvta_generic_to_shared(s->lut)));
     }
@@ -169,32 +179,33 @@ struct GjdLutSmem {
 
 /* Rare path: the code is longer than GJD_LUT_BITS, or unassigned.  An unassigned code consumes 16 bits
  * and comes back with advance 0 (no slot): the write pass flags it, and both passes treat it alike. */
-GJD_HD_COLD uint32_t gjd_lookup_slow(const GjdLutSet* lut, uint32_t tb, uint32_t w) {
+GJD_HD_COLD uint32_t gjd_lookup_slow(const GjdLutSet* lut, uint32_t tb, uint32_t w, uint32_t room, uint32_t* badcode) {
     uint32_t slot = lut->slot_of[tb / GJD_RING_STRIDE];
     uint32_t e = gjd_resolve(lut->lim[slot], lut->off[slot], lut->vals[slot], lut->isdc[slot], w >> 16, GJD_LUT_BITS + 1);
-    return (e & GJD_ENTRY_BAD) ? 16u : e;
-}
-
-/* One symbol at window w with the ring at tb: the 16-bit LUT entry. */
-template <class Lut>
-GJD_HD uint32_t gjd_lookup(const Lut& lut, uint32_t tb, uint32_t w) {
-    uint32_t e = lut.entry(tb + ((w >> (31 - GJD_LUT_BITS)) & (GJD_RING_STRIDE - 2u)));
-    if ((e & 31u) == 0u) e = gjd_lookup_slow(lut.set, tb, w);
+    if (e & GJD_ENTRY_BAD) {
+        /* only a symbol that lies inside the scan counts (the padding after the last MCU does not);
+         * benign race: every writer stores the same value */
+        if (badcode && room >= 16u) *badcode = 1u;
+        e = 16u;
+    }
     return e;
 }
 
-/* Advance the slot counter and the table ring over the symbol with entry e.  Returns the new zigzag
- * index (64 = the block is complete). */
-GJD_HD uint32_t gjd_advance(uint32_t e, uint32_t& q, uint32_t& tb) {
-    const uint32_t qz = q & 63u;
-    uint32_t t = qz + (e >> 9);
-    t = t > 64u ? 64u : t;
-    q = q - qz + t;
-    if (qz == 0u || t == 64u) {          /* after a DC symbol, and at a block end: next table */
+/* One symbol at window w with the ring at tb: the 16-bit LUT entry.  room = bits left in the scan. */
+template <class Lut>
+GJD_HD uint32_t gjd_lookup(const Lut& lut, uint32_t tb, uint32_t w, uint32_t room) {
+    uint32_t e = lut.entry(tb + ((w >> (31 - GJD_LUT_BITS)) & (GJD_RING_STRIDE - 2u)));
+    if ((e & 31u) == 0u) e = gjd_lookup_slow(lut.set, tb, w, room, lut.badcode);
+    return e;
+}
+
+/* Ring step for a symbol decoded at zigzag index z whose successor index is zn (>= 64: block done). */
+GJD_HD uint32_t gjd_ring_next(uint32_t tb, uint32_t z, uint32_t zn) {
+    if (z == 0u || zn >= 64u) {
         tb += GJD_RING_STRIDE;
         if (tb == GJD_RING_BYTES) tb = 0u;
     }
-    return t;
+    return tb;
 }
 
 /* Decode symbols that START before end_bits, beginning at state s.  A symbol that would run past
@@ -207,18 +218,22 @@ GJD_HD void gjd_count_span(const uint32_t* scan, const Lut& lut, uint32_t end_bi
     if (s.p >= end_bits) return;
     GjdWin win;
     gjd_win_init(win, scan, s.p);
-    uint32_t p = s.p, q = s.pos, tb = gjd_ring_of_pos(s.pos);
+    uint32_t p = s.p, z = s.pos & 63u, tb = gjd_ring_of_pos(s.pos), nb = 0;
     while (p < end_bits) {
         const uint32_t w = gjd_peek32(win, scan, p);
-        const uint32_t e = gjd_lookup(lut, tb, w);
+        const uint32_t e = gjd_lookup(lut, tb, w, scan_bits - p);
         const uint32_t pn = p + (e & 31u);
         if (pn > scan_bits) break;
         p = pn;
-        gjd_advance(e, q, tb);
+        const uint32_t zn = z + (e >> 9);
+        tb = gjd_ring_next(tb, z, zn);
+        z = zn;
+        if (zn >= 64u) { z = 0u; nb++; }
     }
+    const uint32_t adv = nb * 64u + z - (s.pos & 63u);      /* slots advanced (mod 2^32 arithmetic is exact) */
     s.p = p;
-    s.n += q - s.pos;
-    s.pos = q % 192u;
+    s.n += adv;
+    s.pos = (s.pos + adv) % 192u;
 }
 
 /* Warp-wide "any lane still running": keeps the 32 lanes of a warp in one converged loop on the GPU
@@ -236,55 +251,69 @@ GJD_HD void gjd_count_span(const uint32_t* scan, const Lut& lut, uint32_t end_bi
  * to the thread before it), then decodes its blocks completely — running past end_bits to finish the
  * last one.  Per block it calls sink.store(k, value) for every non-zero AC coefficient (zigzag index
  * k, increasing) and then sink.flush(block_index, dc_difference, kmax) with kmax = the last non-zero
- * zigzag index (0 = DC only).  One flat loop over symbols for skip and own phases alike, driven by a
- * warp vote, so the lanes of a warp stay converged: ALL 32 lanes call this (enable = false for lanes
- * without a subsequence).
- * Same buildMCU semantics as gjd_count_span (cpp-decoder/src/parser.cpp:105-134).
+ * zigzag index (0 = DC only).  Both phases are flat loops over symbols driven by a warp vote, so the
+ * lanes of a warp stay converged: ALL 32 lanes call this (enable = false for lanes without a
+ * subsequence).  Same buildMCU semantics as gjd_count_span (cpp-decoder/src/parser.cpp:105-134).
  */
 template <class Lut, class Sink>
 GJD_HD void gjd_write_span(const uint32_t* scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
                            GjdState s, uint32_t idx0, uint32_t nblocks, bool enable, Sink& sink, uint32_t& bad) {
-    bool run = enable && s.p < end_bits;
+    uint32_t run = (enable && s.p < end_bits) ? 1u : 0u;
     GjdWin win;
     win.wi = 0; win.w0 = 0; win.w1 = 0;
     if (run) gjd_win_init(win, scan, s.p);
-    uint32_t p = s.p, q = s.pos, tb = gjd_ring_of_pos(s.pos);
-    bool own = (q & 63u) == 0u;                      /* false: inside the previous thread's block */
+    uint32_t p = s.p, z = s.pos & 63u, tb = gjd_ring_of_pos(s.pos);
     uint32_t blk = (idx0 + 63u) >> 6;
+
+    /* phase A: the tail of a block that belongs to the previous thread */
+    uint32_t skip = (run && z != 0u) ? 1u : 0u;
+    while (GJD_WARP_ANY(skip != 0u)) {
+        if (skip) {
+            const uint32_t w = gjd_peek32(win, scan, p);
+            const uint32_t e = gjd_lookup(lut, tb, w, scan_bits - p);
+            const uint32_t pn = p + (e & 31u);
+            if (p >= end_bits || pn > scan_bits) {
+                skip = 0u; run = 0u;                 /* owns nothing (a truncated block is its owner's to report) */
+            } else {
+                p = pn;
+                const uint32_t zn = z + (e >> 9);
+                tb = gjd_ring_next(tb, z, zn);
+                z = zn >= 64u ? 0u : zn;
+                if (z == 0u) skip = 0u;
+            }
+        }
+    }
+
+    /* phase B: the blocks this thread owns */
     int dcdiff = 0;
     uint32_t kmax = 0;
-    while (GJD_WARP_ANY(run)) {
-        if (!run) continue;
-        const uint32_t z = q & 63u;
-        if (p >= end_bits && (z == 0u || !own)) { run = false; continue; }
-        const uint32_t w = gjd_peek32(win, scan, p);
-        const uint32_t e = gjd_lookup(lut, tb, w);
-        const uint32_t total = e & 31u;
-        if (p + total > scan_bits) {                 /* padding at a block start is the normal end */
-            if (own && z != 0u) bad |= GJD_DEV_BADCOUNT;
-            run = false;
-            continue;
-        }
-        p += total;
-        const uint32_t t = gjd_advance(e, q, tb);
-        if (!own) {
-            own = t == 64u;
-            continue;
-        }
-        if (e < 512u) bad |= GJD_DEV_BADCODE;       /* advance 0: unassigned code */
-        const uint32_t size = (e >> 5) & 15u;
-        const int v = gjd_extend(w, total - size, size);
-        if (z == 0u) {
-            dcdiff = v;
-        } else if (size) {                           /* EOB and ZRL carry no value */
-            const uint32_t k = z + (e >> 9) - 1u;
-            if (k < 64u) { sink.store(k, v); kmax = k; }
-        }
-        if (t == 64u) {
-            if (blk >= nblocks) { bad |= GJD_DEV_BADCOUNT; run = false; continue; }
-            sink.flush(blk, dcdiff, kmax);
-            blk++;
-            kmax = 0u;
+    while (GJD_WARP_ANY(run != 0u)) {
+        if (run) {
+            const uint32_t w = gjd_peek32(win, scan, p);     /* (reads at most one word into the padding) */
+            const uint32_t e = gjd_lookup(lut, tb, w, scan_bits - p);
+            const uint32_t total = e & 31u;
+            const uint32_t pn = p + total;
+            const bool stop = z == 0u && p >= end_bits;
+            if (stop || pn > scan_bits) {                    /* padding at a block start is the normal end */
+                if (z != 0u) bad |= GJD_DEV_BADCOUNT;
+                run = 0u;
+            } else {
+                p = pn;
+                const uint32_t size = (e >> 5) & 15u;
+                const uint32_t zn = z + (e >> 9);            /* next zigzag index; >= 64: block complete */
+                const int v = gjd_extend(w, total - size, size);
+                if (z == 0u) dcdiff = v;
+                else if (size != 0u && zn <= 64u) { sink.store(zn - 1u, v); kmax = zn - 1u; }
+                tb = gjd_ring_next(tb, z, zn);
+                z = zn;
+                if (zn >= 64u) {
+                    z = 0u;
+                    if (blk >= nblocks) { bad |= GJD_DEV_BADCOUNT; run = 0u; }
+                    else sink.flush(blk, dcdiff, kmax);
+                    blk++;
+                    kmax = 0u;
+                }
+            }
         }
     }
 }

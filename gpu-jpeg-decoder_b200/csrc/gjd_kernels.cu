@@ -163,6 +163,7 @@ __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
     const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
     GjdLutMem glut;
     glut.set = b.luts + d.lut_id;
+    glut.badcode = nullptr;
     const uint32_t scan_bits = d.scan_bits;
     uint2* si = b.sinfo + (size_t)g * GJD_SEQ_SUBS;
     uint2 prev = si[-1];
@@ -229,21 +230,25 @@ struct GjdWriteSink {
     __device__ __forceinline__ void store(uint32_t k, int v) const {
         reinterpret_cast<int16_t*>(mine + (k >> 3) * GJD_WRITE_THREADS)[k & 7u] = (int16_t)v;
     }
+    __device__ __forceinline__ void sector(uint4* dst, uint32_t sct) const {
+        uint4* s0 = mine + (2u * sct) * GJD_WRITE_THREADS;
+        uint4* s1 = mine + (2u * sct + 1u) * GJD_WRITE_THREADS;
+        const uint4 a = *s0, c = *s1;
+        dst[2u * sct] = a;
+        dst[2u * sct + 1u] = c;
+        *s0 = make_uint4(0u, 0u, 0u, 0u);
+        *s1 = make_uint4(0u, 0u, 0u, 0u);
+    }
     __device__ __forceinline__ void flush(uint32_t blk, int dcdiff, uint32_t kmax) const {
         meta[blk] = ((uint32_t)dcdiff & 0xffffu) | (kmax << 16);
         if (kmax == 0u) return;
         uint4* dst = coef + (size_t)blk * 8u;
-        const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
-#pragma unroll
-        for (uint32_t s = 0; s < 4; s++) {
-            if (s == 0u || kmax >= 16u * s) {
-                uint4* s0 = mine + (2u * s) * GJD_WRITE_THREADS;
-                uint4* s1 = mine + (2u * s + 1u) * GJD_WRITE_THREADS;
-                const uint4 a = *s0, c = *s1;
-                dst[2u * s] = a;
-                dst[2u * s + 1u] = c;
-                *s0 = zero;
-                *s1 = zero;
+        sector(dst, 0u);
+        if (kmax >= 16u) {
+            sector(dst, 1u);
+            if (kmax >= 32u) {
+                sector(dst, 2u);
+                if (kmax >= 48u) sector(dst, 3u);
             }
         }
     }
@@ -258,6 +263,7 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, 4) k_huff_write(GjdDevBatch
     __shared__ GjdLutSet lut;
     __shared__ uint4 buf[8][GJD_WRITE_THREADS];
     __shared__ uint32_t ws[8];
+    __shared__ uint32_t badcode;
     const uint32_t g = blockIdx.x, tid = threadIdx.x;
     const uint32_t img = b.seq_img[g];
     const GjdImage& d = b.imgs[img];
@@ -268,7 +274,8 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, 4) k_huff_write(GjdDevBatch
     const bool active = sub < d.sub_count;
     const uint2* si = b.sinfo + (size_t)g * GJD_SEQ_SUBS;
     copy_lut_to_smem(&lut, b.luts + d.lut_id);
-    const GjdLutSmem slut(&lut);
+    const GjdLutSmem slut(&lut, &badcode);
+    if (tid == 0) badcode = 0u;
 #pragma unroll
     for (int j = 0; j < 8; j++) buf[j][tid] = make_uint4(0u, 0u, 0u, 0u);
 
@@ -293,6 +300,8 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, 4) k_huff_write(GjdDevBatch
     uint32_t end = min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
     gjd_write_span(scan, slut, end, scan_bits, st, idx0, 3u * d.mcu_count, active, sink, bad);
     if (bad) atomicOr(b.status + img, bad);
+    __syncthreads();
+    if (tid == 0 && badcode) atomicOr(b.status + img, GJD_DEV_BADCODE);
 }
 
 /* ------------------------------------------------------------------ DC predictors ----- */

@@ -76,8 +76,10 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
         for (uint32_t i = 0; i < GJD_LUT_SIZE; i++)
             lut->lut[r][i] = gjd_lut_entry(lut->lim[t], lut->off[t], lut->vals[t], lut->isdc[t], i);
     }
+    uint32_t badcode = 0;
     GjdLutMem hlut;
     hlut.set = lut;
+    hlut.badcode = &badcode;
     const uint32_t scan_bits = (uint32_t)ulen * 8u;
     const uint32_t sub_count = std::max<uint32_t>(1u, (scan_bits + GJD_SUBSEQ_BITS - 1) / GJD_SUBSEQ_BITS);
     const uint32_t seq_count = (sub_count + GJD_SEQ_SUBS - 1) / GJD_SEQ_SUBS;
@@ -160,6 +162,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
         uint32_t cnt = std::min<uint32_t>(GJD_SEQ_SUBS, sub_count - g * GJD_SEQ_SUBS);
         for (uint32_t t = 0; t < cnt; t++) carry += sn[(size_t)g * GJD_SEQ_SUBS + t] >> 8;
     }
+    badcode = 0;   /* only the write pass reports unassigned codes */
     if (carry != 192u * mcu_count) status |= GJD_DEV_BADCOUNT;
     /* k_huff_write */
     std::vector<int16_t> coef((size_t)tile_count * 96 * 64, (int16_t)0x7e7e);   /* stale garbage where nothing is written */
@@ -187,6 +190,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
         }
     }
     for (uint32_t bk = 0; bk < 3u * mcu_count; bk++) if (written[bk] != 1) status |= GJD_DEV_BADCOUNT;
+    if (badcode) status |= GJD_DEV_BADCODE;
     /* k_dc_tilebase + k_transform */
     int q[3][64];
     for (int c = 0; c < 3; c++)

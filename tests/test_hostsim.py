@@ -85,3 +85,21 @@ def test_corrupt_scan_is_flagged(hostsim, golden):
     bad = bytes(data[:mid] + data[mid + 301 :])
     rc, coef, rgb, stats = hostsim.decode(bad)
     assert rc in (-6, -4)
+
+
+def test_hostsim_seeded_synthetic(hostsim, oracle):
+    """Freshly encoded images (not in the golden set): odd sizes, q 25..100, optimised tables — the
+    hostsim pipeline vs the oracle, pixels and coefficients."""
+    import gen_synth
+    if not gen_synth.have_cjpeg():
+        pytest.skip("vendored cjpeg not built (tools/_build/libjpeg)")
+    specs = [(22, 777, 555, 75, True), (24, 129, 1031, 100, False), (31, 640, 360, 25, True), (32, 1024, 1024, 90, False),
+             (33, 8, 2048, 95, True), (34, 2048, 8, 50, False)]
+    for sp in specs:
+        data = gen_synth.synth_jpeg(*sp)
+        rc, coef, rgb, stats = hostsim.decode(data)
+        assert rc == 0 and stats[2] == 0, (sp, rc, list(stats))
+        orc, want_coef, want_rgb, _, _, _ = oracle.decode(data)
+        assert orc == 0
+        assert np.array_equal(rgb, want_rgb), sp
+        assert np.array_equal(coef, want_coef), sp
