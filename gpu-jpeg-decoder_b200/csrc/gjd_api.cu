@@ -188,6 +188,8 @@ struct gjd_ctx {
     gjd_batch* last = nullptr;     /* batch whose stage events gjd_stage_times reports */
     std::string cuda_err;
     int transform_variant = 0;
+    uint64_t min_subseqs = 1200000;   /* ~4 waves of 148 SMs x 2048 threads */
+    int force_sub_log2 = 0;           /* GJD_SUB_LOG2: fixed subsequence length (tests, experiments) */
 };
 
 namespace {
@@ -256,6 +258,16 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         ulen[i] = m;
     });
 
+    /* subsequence length for this batch: the longest that still leaves >= GJD_MIN_SUBSEQS threads */
+    uint32_t sub_log2 = GJD_SUB_LOG2_MIN;
+    {
+        uint64_t total_bits = 0;
+        for (int32_t i = 0; i < n; i++) total_bits += (uint64_t)std::max<long>(ulen[i], 0) * 8;
+        while (sub_log2 < GJD_SUB_LOG2_MAX && (total_bits >> (sub_log2 + 1)) >= ctx->min_subseqs) sub_log2++;
+        if (ctx->force_sub_log2) sub_log2 = (uint32_t)ctx->force_sub_log2;
+    }
+    const uint64_t sub_bits = 1ull << sub_log2;
+
     /* descriptors */
     std::unordered_map<uint64_t, std::vector<uint32_t>> lut_index, quant_index;
     uint32_t seq = 0, tile = 0, tb = 0;
@@ -270,7 +282,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         memset(&d, 0, sizeof(d));
         d.scan_off = soff[i];
         d.scan_bits = (uint32_t)(ulen[i] * 8);
-        d.sub_count = std::max<uint32_t>(1u, (d.scan_bits + GJD_SUBSEQ_BITS - 1) / GJD_SUBSEQ_BITS);
+        d.sub_count = std::max<uint32_t>(1u, (uint32_t)(((uint64_t)d.scan_bits + sub_bits - 1) / sub_bits));
         d.seq_first = seq;
         d.seq_count = (d.sub_count + GJD_SEQ_SUBS - 1) / GJD_SEQ_SUBS;
         d.width = (uint32_t)g.width;
@@ -345,6 +357,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     memset(&v, 0, sizeof(v));
     v.n_img = n_img;
     v.n_seq = seq;
+    v.sub_log2 = sub_log2;
     v.n_tile = tile;
     v.n_tb = tb;
     if (n_img == 0) return GJD_OK;
@@ -363,7 +376,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     GJD_TRY(b->d_scan.ensure(b->scan_alloc));
     GJD_TRY(b->d_luts.ensure(sizeof(GjdLutSet) * b->dhts.size()));
     GJD_TRY(b->d_sinfo.ensure((size_t)seq * GJD_SEQ_SUBS * sizeof(uint2)));
-    GJD_TRY(b->d_seqmaps.ensure((size_t)seq * 2 * sizeof(uint32_t)));
+    GJD_TRY(b->d_seqmaps.ensure((size_t)seq * 4 * sizeof(uint32_t)));
     GJD_TRY(b->d_coef.ensure((size_t)tile * 96 * 64 * sizeof(int16_t)));
     GJD_TRY(b->d_tbimg.ensure((size_t)tb * sizeof(uint32_t)));
     GJD_TRY(b->d_blkmeta.ensure((size_t)tile * 96 * sizeof(uint32_t)));
@@ -380,6 +393,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     v.sinfo = (uint2*)b->d_sinfo.p;
     v.seq_img = (uint32_t*)b->d_seqmaps.p;
     v.seq_base = (uint32_t*)b->d_seqmaps.p + seq;
+    v.seq_in = (uint2*)((uint32_t*)b->d_seqmaps.p + 2 * (size_t)seq);
     v.coef = (int16_t*)b->d_coef.p;
     v.tb_img = (uint32_t*)b->d_tbimg.p;
     v.meta = (uint32_t*)b->d_blkmeta.p;
@@ -474,7 +488,7 @@ void parse_all(gjd_ctx* ctx, const gjd_item* items, int32_t n, std::vector<GjdPa
 extern "C" {
 
 const char* gjd_version(void) {
-    return "gjd " GJD_VERSION_STR " sm_100a subseq=" GJD_STR(GJD_SUBSEQ_BITS) " lut=" GJD_STR(GJD_LUT_BITS);
+    return "gjd " GJD_VERSION_STR " sm_100a subseq=2^" GJD_STR(GJD_SUB_LOG2_MIN) "..2^" GJD_STR(GJD_SUB_LOG2_MAX) " lut=" GJD_STR(GJD_LUT_BITS);
 }
 
 const char* gjd_strerror(int st) {
@@ -513,6 +527,11 @@ int gjd_create(gjd_ctx** out, int device, size_t scratch_bytes_hint) {
     threads = std::max(1, std::min(threads, 64));
     ctx->pool = new Pool(threads - 1);
     if (const char* e = getenv("GJD_TRANSFORM_VARIANT")) ctx->transform_variant = atoi(e);
+    if (const char* e = getenv("GJD_SUB_LOG2")) {
+        int k = atoi(e);
+        if (k >= 8 && k <= 16) ctx->force_sub_log2 = k;
+    }
+    if (const char* e = getenv("GJD_MIN_SUBSEQS")) ctx->min_subseqs = (uint64_t)std::max(1ll, atoll(e));
     *out = ctx;
     return GJD_OK;
 }

@@ -3,7 +3,7 @@
  *
  *   k_build_luts    DHT (BITS/HUFFVAL) -> flattened lookup tables, one block per table set
  *   k_fill_maps     sequence -> image and tile -> image maps
- *   k_huff_sync     cold decode of every subsequence + self-synchronisation inside a sequence
+ *   k_huff_sync     look-back decode of every subsequence + entry/exit state validation inside a sequence
  *   k_huff_fix      boundary fix-up between sequences
  *   k_seq_scan      exclusive scan of per-sequence coefficient counts (per image)
  *   k_huff_write    re-decode from the synchronised states; every thread stages the blocks it owns in
@@ -93,11 +93,19 @@ __global__ void __launch_bounds__(128) k_fill_maps(GjdDevBatch b) {
 
 /* ------------------------------------------------------------------ entropy: sync ----- */
 /*
- * One block per sequence (256 subsequences of 1024 bits of one image), one thread per subsequence.
- * Phase 1: every thread decodes its own subsequence from a cold state (component 0, zigzag 0, first
- * bit of the subsequence).  Phase 2, in lock-step rounds: thread i carries its running state into
- * subsequence i+r, compares the end state with the one stored there and overwrites it; a match means
- * its chain has merged with the chain that started later, and the thread retires.
+ * One block per sequence (256 subsequences of S = 2^sub_log2 bits of one image), one thread per
+ * subsequence i.
+ * Phase 1 (look-back): the thread starts cold (component 0, zigzag 0) GJD_LOOKBACK_BITS before its
+ * subsequence; by the time it reaches the boundary i*S it has almost always fallen into step with the
+ * true symbol sequence (self-synchronisation; 99.8 % within 512 bits on the benchmark images).  Its
+ * state at the boundary is its entry state Ein_i; from there it decodes its own subsequence, counting
+ * coefficient slots, to the exit state Eout_i.  Subsequence 0 of an image starts from the true state.
+ * Phase 2 (validation): Ein_i must equal Eout_{i-1}.  A thread whose entry state differs re-decodes its
+ * subsequence from Eout_{i-1}; rounds repeat until nothing changes (the first wrong thread of a chain
+ * is always repaired, so this terminates).  The first thread of a sequence cannot see its predecessor
+ * (another thread block): it leaves Ein in seq_in for k_huff_fix.
+ * After the reference's parallelHuffManDecode (cuda-decoder/src/parser.cu:132-173), which continues
+ * every thread through whole slices instead.
  */
 __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
     __shared__ GjdLutSet lut;
@@ -107,51 +115,58 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
     const uint32_t g = blockIdx.x, tid = threadIdx.x;
     const GjdImage& d = b.imgs[b.seq_img[g]];
     const uint32_t ls = g - d.seq_first;
-    const uint32_t sub0 = ls * GJD_SEQ_SUBS;
+    const uint32_t sub = ls * GJD_SEQ_SUBS + tid;
     const uint32_t sub_count = d.sub_count, scan_bits = d.scan_bits;
+    const uint32_t S = 1u << b.sub_log2;
     const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
     copy_lut_to_smem(&lut, b.luts + d.lut_id);
     const GjdLutSmem slut(&lut);
     __syncthreads();
 
-    const bool active = sub0 + tid < sub_count;
+    const bool active = sub < sub_count;
+    const uint32_t start = sub << b.sub_log2;
+    const uint32_t end = active ? min(start + S, scan_bits) : 0u;
     GjdState st;
-    st.p = (sub0 + tid) * GJD_SUBSEQ_BITS;
-    st.n = 0;
-    st.pos = 0;
+    st.p = 0; st.n = 0; st.pos = 0;
+    uint32_t in_p = 0, in_pos = 0;
     if (active) {
-        uint32_t end = min((sub0 + tid + 1) * GJD_SUBSEQ_BITS, scan_bits);
+        if (sub != 0u) {
+            st.p = start > GJD_LOOKBACK_BITS ? start - GJD_LOOKBACK_BITS : 0u;
+            gjd_count_span(scan, slut, start, scan_bits, st);
+        }
+        in_p = st.p; in_pos = st.pos;
+        st.n = 0;
         gjd_count_span(scan, slut, end, scan_bits, st);
     }
     sp[tid] = st.p;
     sn[tid] = (st.n << 8) | st.pos;
-    __syncthreads();
+    if (tid == 0 && ls != 0u) b.seq_in[g] = make_uint2(in_p, in_pos);
 
-    bool synced = !active;
-    for (uint32_t r = 1; r < GJD_SEQ_SUBS; r++) {
-        uint32_t j = tid + r;
-        bool go = !synced && j < GJD_SEQ_SUBS && sub0 + j < sub_count;
-        bool still = false;
-        if (go) {
-            st.n = 0;
-            uint32_t end = min((sub0 + j + 1) * GJD_SUBSEQ_BITS, scan_bits);
-            gjd_count_span(scan, slut, end, scan_bits, st);
-            bool match = sp[j] == st.p && (sn[j] & 255u) == st.pos;
-            sp[j] = st.p;
-            sn[j] = (st.n << 8) | st.pos;
-            if (match) synced = true; else still = true;
-        } else {
-            synced = true;
+    for (uint32_t r = 0; r < GJD_SEQ_SUBS; r++) {
+        __syncthreads();
+        bool bad = false;
+        if (active && tid != 0u) {
+            const uint32_t pp = sp[tid - 1], ppos = sn[tid - 1] & 255u;
+            bad = pp != in_p || ppos != in_pos;
+            if (bad) {
+                st.p = in_p = pp; st.pos = in_pos = ppos; st.n = 0;
+                gjd_count_span(scan, slut, end, scan_bits, st);
+            }
         }
-        if (!__syncthreads_or(still)) break;
+        if (!__syncthreads_or(bad)) break;
+        if (bad) {
+            sp[tid] = st.p;
+            sn[tid] = (st.n << 8) | st.pos;
+        }
     }
     if (active) b.sinfo[(size_t)g * GJD_SEQ_SUBS + tid] = make_uint2(sp[tid], sn[tid]);
 }
 
 /*
- * One thread per sequence that is not the first of its image: continue from the final state of the
- * previous sequence until the chain merges with what k_huff_sync left.  A chain that crosses the
- * whole sequence without merging is counted in *nosync; the host then repeats this kernel.
+ * One thread per sequence that is not the first of its image: if the entry state of the sequence's first
+ * subsequence differs from the exit state of the previous sequence, continue from that exit state until
+ * the chain merges with what k_huff_sync left.  A chain that crosses the whole sequence without merging
+ * is counted in *nosync; the host then repeats this kernel.
  */
 __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
@@ -160,23 +175,25 @@ __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
     const GjdImage& d = b.imgs[img];
     uint32_t ls = g - d.seq_first;
     if (ls == 0) return;
+    uint2* si = b.sinfo + (size_t)g * GJD_SEQ_SUBS;
+    const uint2 prev = si[-1];
+    const uint2 ein = b.seq_in[g];
+    if (prev.x == ein.x && (prev.y & 255u) == ein.y) return;
+    b.seq_in[g] = make_uint2(prev.x, prev.y & 255u);
     const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
     GjdLutMem glut;
     glut.set = b.luts + d.lut_id;
     glut.badcode = nullptr;
     const uint32_t scan_bits = d.scan_bits;
-    uint2* si = b.sinfo + (size_t)g * GJD_SEQ_SUBS;
-    uint2 prev = si[-1];
     GjdState st;
     st.p = prev.x;
     st.pos = prev.y & 255u;
     bool merged = false;
-    uint32_t t = 0;
-    for (; t < GJD_SEQ_SUBS; t++) {
+    for (uint32_t t = 0; t < GJD_SEQ_SUBS; t++) {
         uint32_t sub = ls * GJD_SEQ_SUBS + t;
         if (sub >= d.sub_count) { merged = true; break; }
         st.n = 0;
-        uint32_t end = min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
+        uint32_t end = min((sub + 1) << b.sub_log2, scan_bits);
         gjd_count_span(scan, glut, end, scan_bits, st);
         uint2 old = si[t];
         si[t] = make_uint2(st.p, (st.n << 8) | st.pos);
@@ -297,7 +314,7 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, 4) k_huff_write(GjdDevBatch
     sink.meta = b.meta + (size_t)d.tile_first * 96u;
     const uint32_t idx0 = b.seq_base[g] + excl;
     if (active && idx0 % 192u != st.pos && st.p < scan_bits) bad |= GJD_DEV_BADSTATE;
-    uint32_t end = min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
+    uint32_t end = min((sub + 1) << b.sub_log2, scan_bits);
     gjd_write_span(scan, slut, end, scan_bits, st, idx0, 3u * d.mcu_count, active, sink, bad);
     if (bad) atomicOr(b.status + img, bad);
     __syncthreads();

@@ -5,7 +5,7 @@
  *
  *   scan   u8    unstuffed entropy-coded bytes of every image, each image starting on a
  *                128-byte boundary and followed by >= 16 zero bytes.
- *   sinfo  u32x2 one state per subsequence (GJD_SUBSEQ_BITS bits of one image's scan), padded per
+ *   sinfo  u32x2 one state per subsequence (2^sub_log2 bits of one image's scan), padded per
  *                image to a multiple of GJD_SEQ_SUBS ("sequence" = the subsequences one thread
  *                block synchronises): {p, (n << 8) | pos}.
  *   coef   i16   quantised coefficients, zigzag order, one 128-byte line per 8x8 block:
@@ -24,8 +24,9 @@
 
 #include <stdint.h>
 
-#define GJD_SUBSEQ_BITS   1024u    /* bits per subsequence (one thread)            */
-#define GJD_SUBSEQ_BYTES  (GJD_SUBSEQ_BITS / 8u)
+#define GJD_SUB_LOG2_MIN   10u      /* subsequence (one thread) = 2^k bits, k chosen per batch:        */
+#define GJD_SUB_LOG2_MAX   13u      /* long enough to amortise the look-back, short enough to fill the GPU */
+#define GJD_LOOKBACK_BITS 512u     /* cold-start distance before a subsequence (k_huff_sync)          */
 #define GJD_SEQ_SUBS      256u     /* subsequences per sequence (one thread block) */
 #define GJD_LUT_BITS      10       /* primary Huffman LUT index width              */
 #define GJD_LUT_SIZE      (1 << GJD_LUT_BITS)

@@ -81,7 +81,7 @@ class HostSim:
         rc = self.lib.hostsim_parse(C.cast(C.c_char_p(data), C.c_void_p), len(data), C.byref(w), C.byref(h))
         return rc, w.value, h.value
 
-    def decode(self, data):
+    def decode(self, data, sub_log2=0):
         rc, W, H = self.parse(data)
         if rc != 0:
             return rc, None, None, None
@@ -90,7 +90,7 @@ class HostSim:
         rgb = np.zeros((3, H, W), np.uint8)
         stats = np.zeros(6, np.uint32)
         w, h = C.c_int32(), C.c_int32()
-        rc = self.lib.hostsim_decode(C.cast(C.c_char_p(data), C.c_void_p), len(data), 0, coef.ctypes.data,
+        rc = self.lib.hostsim_decode(C.cast(C.c_char_p(data), C.c_void_p), len(data), sub_log2, coef.ctypes.data,
                                      rgb.ctypes.data, C.byref(w), C.byref(h), stats.ctypes.data)
         return rc, coef, rgb, stats
 

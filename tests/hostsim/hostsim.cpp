@@ -46,9 +46,10 @@ extern "C" {
 
 /* stats: [0] max synchronisation rounds inside a sequence, [1] fix-up subsequences decoded,
  *        [2] device status bits, [3] nosync count, [4] subsequences, [5] sequences */
-int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16_t* coef_out, uint8_t* rgb_out,
+int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* coef_out, uint8_t* rgb_out,
                    int32_t* width, int32_t* height, uint32_t stats[6]) {
-    (void)subseq_bits_unused;
+    const uint32_t sub_log2 = sub_log2_arg ? (uint32_t)sub_log2_arg : GJD_SUB_LOG2_MIN;
+    const uint32_t S = 1u << sub_log2;
     GjdParsed p;
     int rc = gjd_parse_headers(jpg, len, &p);
     if (rc) return rc;
@@ -81,7 +82,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
     hlut.set = lut;
     hlut.badcode = &badcode;
     const uint32_t scan_bits = (uint32_t)ulen * 8u;
-    const uint32_t sub_count = std::max<uint32_t>(1u, (scan_bits + GJD_SUBSEQ_BITS - 1) / GJD_SUBSEQ_BITS);
+    const uint32_t sub_count = std::max<uint32_t>(1u, (uint32_t)(((uint64_t)scan_bits + S - 1) / S));
     const uint32_t seq_count = (sub_count + GJD_SEQ_SUBS - 1) / GJD_SEQ_SUBS;
     const uint32_t W = (uint32_t)p.width, H = (uint32_t)p.height;
     const uint32_t mcus_x = (W + 7) / 8, mcu_count = mcus_x * ((H + 7) / 8);
@@ -90,63 +91,72 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
     uint32_t bad = 0, max_rounds = 0, fix_decodes = 0, nosync = 0, status = 0;
 
     /* k_huff_sync: one "block" per sequence */
+    std::vector<uint32_t> seq_in_p(seq_count, 0), seq_in_pos(seq_count, 0);
     for (uint32_t g = 0; g < seq_count; g++) {
-        uint32_t sub0 = g * GJD_SEQ_SUBS;
-        std::vector<GjdState> st(GJD_SEQ_SUBS);
-        std::vector<char> synced(GJD_SEQ_SUBS, 0);
         uint32_t* bp = &sp[(size_t)g * GJD_SEQ_SUBS];
         uint32_t* bn = &sn[(size_t)g * GJD_SEQ_SUBS];
+        std::vector<uint32_t> in_p(GJD_SEQ_SUBS, 0), in_pos(GJD_SEQ_SUBS, 0), endb(GJD_SEQ_SUBS, 0);
+        std::vector<char> active(GJD_SEQ_SUBS, 0);
         for (uint32_t tid = 0; tid < GJD_SEQ_SUBS; tid++) {
-            bool active = sub0 + tid < sub_count;
-            st[tid].p = (sub0 + tid) * GJD_SUBSEQ_BITS; st[tid].n = 0; st[tid].pos = 0;
-            if (active) {
-                uint32_t end = std::min((sub0 + tid + 1) * GJD_SUBSEQ_BITS, scan_bits);
-                gjd_count_span(scan, hlut, end, scan_bits, st[tid]);
+            uint32_t sub = g * GJD_SEQ_SUBS + tid;
+            active[tid] = sub < sub_count;
+            GjdState st; st.p = 0; st.n = 0; st.pos = 0;
+            if (active[tid]) {
+                uint32_t start = sub << sub_log2;
+                endb[tid] = std::min(start + S, scan_bits);
+                if (sub != 0) {
+                    st.p = start > GJD_LOOKBACK_BITS ? start - GJD_LOOKBACK_BITS : 0u;
+                    gjd_count_span(scan, hlut, start, scan_bits, st);
+                }
+                in_p[tid] = st.p; in_pos[tid] = st.pos;
+                st.n = 0;
+                gjd_count_span(scan, hlut, endb[tid], scan_bits, st);
             }
-            bp[tid] = st[tid].p;
-            bn[tid] = (st[tid].n << 8) | st[tid].pos;
-            synced[tid] = !active;
+            bp[tid] = st.p;
+            bn[tid] = (st.n << 8) | st.pos;
         }
-        for (uint32_t r = 1; r < GJD_SEQ_SUBS; r++) {
+        seq_in_p[g] = in_p[0]; seq_in_pos[g] = in_pos[0];
+        for (uint32_t r = 0; r < GJD_SEQ_SUBS; r++) {
+            /* all threads read their predecessor first, then the repaired ones write (two barriers) */
+            std::vector<uint32_t> np(GJD_SEQ_SUBS), nn(GJD_SEQ_SUBS);
+            std::vector<char> badv(GJD_SEQ_SUBS, 0);
             bool any = false;
-            for (uint32_t tid = 0; tid < GJD_SEQ_SUBS; tid++) {
-                uint32_t j = tid + r;
-                bool go = !synced[tid] && j < GJD_SEQ_SUBS && sub0 + j < sub_count;
-                if (go) {
-                    st[tid].n = 0;
-                    uint32_t end = std::min((sub0 + j + 1) * GJD_SUBSEQ_BITS, scan_bits);
-                    gjd_count_span(scan, hlut, end, scan_bits, st[tid]);
-                    bool match = bp[j] == st[tid].p && (bn[j] & 255u) == st[tid].pos;
-                    bp[j] = st[tid].p;
-                    bn[j] = (st[tid].n << 8) | st[tid].pos;
-                    if (match) synced[tid] = 1; else any = true;
-                } else {
-                    synced[tid] = 1;
+            for (uint32_t tid = 1; tid < GJD_SEQ_SUBS; tid++) {
+                if (!active[tid]) continue;
+                uint32_t pp = bp[tid - 1], ppos = bn[tid - 1] & 255u;
+                if (pp != in_p[tid] || ppos != in_pos[tid]) {
+                    GjdState st; st.p = in_p[tid] = pp; st.pos = in_pos[tid] = ppos; st.n = 0;
+                    gjd_count_span(scan, hlut, endb[tid], scan_bits, st);
+                    np[tid] = st.p; nn[tid] = (st.n << 8) | st.pos;
+                    badv[tid] = 1; any = true;
                 }
             }
-            max_rounds = std::max(max_rounds, r);
             if (!any) break;
+            max_rounds = std::max(max_rounds, r + 1);
+            for (uint32_t tid = 1; tid < GJD_SEQ_SUBS; tid++)
+                if (badv[tid]) { bp[tid] = np[tid]; bn[tid] = nn[tid]; }
         }
     }
     /* k_huff_fix, iterated to its fixed point like batch_wait does */
     for (int iter = 0; iter < 65536; iter++) {
         uint32_t ns = 0;
         for (uint32_t g = 1; g < seq_count; g++) {
-            GjdState st;
-            st.p = sp[(size_t)g * GJD_SEQ_SUBS - 1];
-            st.pos = sn[(size_t)g * GJD_SEQ_SUBS - 1] & 255u;
+            size_t base = (size_t)g * GJD_SEQ_SUBS;
+            uint32_t pp = sp[base - 1], ppos = sn[base - 1] & 255u;
+            if (pp == seq_in_p[g] && ppos == seq_in_pos[g]) continue;
+            seq_in_p[g] = pp; seq_in_pos[g] = ppos;
+            GjdState st; st.p = pp; st.pos = ppos;
             bool merged = false;
             for (uint32_t t = 0; t < GJD_SEQ_SUBS; t++) {
                 uint32_t sub = g * GJD_SEQ_SUBS + t;
                 if (sub >= sub_count) { merged = true; break; }
                 st.n = 0;
-                uint32_t end = std::min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
+                uint32_t end = std::min((sub + 1) << sub_log2, scan_bits);
                 gjd_count_span(scan, hlut, end, scan_bits, st);
                 fix_decodes++;
-                size_t a = (size_t)g * GJD_SEQ_SUBS + t;
-                bool match = sp[a] == st.p && (sn[a] & 255u) == st.pos;
-                sp[a] = st.p;
-                sn[a] = (st.n << 8) | st.pos;
+                bool match = sp[base + t] == st.p && (sn[base + t] & 255u) == st.pos;
+                sp[base + t] = st.p;
+                sn[base + t] = (st.n << 8) | st.pos;
                 if (match) { merged = true; break; }
             }
             if (!merged && g + 1 < seq_count) ns++;
@@ -182,7 +192,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int subseq_bits_unused, int16
             sink.coef = coef.data(); sink.meta = meta.data(); sink.written = written.data();
             uint32_t idx0 = seq_base[g] + excl;
             if (idx0 % 192u != st.pos && st.p < scan_bits) tbad |= GJD_DEV_BADSTATE;
-            uint32_t end = std::min((sub + 1) * GJD_SUBSEQ_BITS, scan_bits);
+            uint32_t end = std::min((sub + 1) << sub_log2, scan_bits);
             gjd_write_span(scan, hlut, end, scan_bits, st, idx0, 3u * mcu_count, true, sink, tbad);
             for (int k = 0; k < 64; k++) if (sink.stage[k]) tbad |= GJD_DEV_BADSTATE;   /* staging must be left clean */
             status |= tbad;

@@ -174,3 +174,25 @@ def test_huffman_stress_8192(decoder, oracle):
     assert st == [0]
     rc, _, rgb, _, W, H = oracle.decode(f, want_coef=False)
     assert rc == 0 and np.array_equal(outs[0], rgb)
+
+
+@pytest.mark.parametrize("sub_log2", [8, 11, 13])
+def test_subsequence_lengths(golden, ref_outputs, oracle, sub_log2, monkeypatch):
+    """The subsequence length is chosen per batch; force the extremes (256 bits = shorter than the look-back,
+    8192 bits) and check pixels and coefficients stay bit-exact."""
+    import gjd
+    import gen_synth
+    monkeypatch.setenv("GJD_SUB_LOG2", str(sub_log2))
+    files = [golden[n] for n in NAMES]
+    with gjd.Decoder(0) as d:
+        outs, st = d.decode(files)
+        assert st == [0] * len(files)
+        for n, o in zip(NAMES, outs):
+            assert np.array_equal(o, ref_outputs[n + "/rgb"]), n
+        got, _, _ = d.decode_coeffs(golden[NAMES[0]])
+        assert np.array_equal(got, ref_outputs[NAMES[0] + "/coef"])
+        if gen_synth.have_cjpeg():
+            f = gen_synth.synth_jpeg(41, 2048, 1536, 90)
+            o, st = d.decode([f])
+            rc, _, rgb, _, W, H = oracle.decode(f, want_coef=False)
+            assert st == [0] and np.array_equal(o[0], rgb)

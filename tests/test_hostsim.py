@@ -11,11 +11,13 @@ NAMES = sorted(golden_files())
 
 @pytest.mark.parametrize("name", NAMES)
 def test_hostsim_bit_exact(hostsim, golden, ref_outputs, name):
-    rc, coef, rgb, stats = hostsim.decode(golden[name])
-    assert rc == 0
-    assert np.array_equal(coef, ref_outputs[name + "/coef"])
-    assert np.array_equal(rgb, ref_outputs[name + "/rgb"])
-    assert stats[2] == 0 and stats[3] == 0
+    # sub_log2: the default and, to multiply the boundary cases, subsequences shorter than the look-back
+    for sub_log2 in (0, 8, 12):
+        rc, coef, rgb, stats = hostsim.decode(golden[name], sub_log2)
+        assert rc == 0
+        assert np.array_equal(coef, ref_outputs[name + "/coef"])
+        assert np.array_equal(rgb, ref_outputs[name + "/rgb"])
+        assert stats[2] == 0 and stats[3] == 0
 
 
 def test_colour_exhaustive(hostsim, oracle):
