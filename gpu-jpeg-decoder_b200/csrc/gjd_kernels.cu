@@ -378,18 +378,41 @@ __host__ __device__ constexpr int gjd_zz_of_nat(int i) {
 template <int I> struct GjdZz { static constexpr int value = gjd_zz_of_nat(I); };
 
 /* v[natural i] = coefficient at zigzag(i) of the block held as 32 packed words (two int16 each), times
- * q[zigzag(i)]; the dezigzag is a compile-time renaming of registers. */
-template <int I> struct GjdUnpack {
+ * q[zigzag(i)]; the dezigzag is a compile-time renaming of registers.  Coefficients with zigzag index
+ * >= KLIM are known to be zero (kmax < KLIM for the whole warp): they become literal zeros, and the
+ * compiler prunes the butterflies of gjd_idct8x8 that only see zeros (e.g. KLIM = 16: rows 5-7 vanish,
+ * row 4 is DC-only).  Exactness is untouched: it is the same arithmetic on the same values. */
+template <int I, int KLIM> struct GjdUnpack {
     static __device__ __forceinline__ void run(const uint32_t* w, const int* q, int* v) {
-        GjdUnpack<I - 1>::run(w, q, v);
+        GjdUnpack<I - 1, KLIM>::run(w, q, v);
         constexpr int k = GjdZz<I>::value;
-        const int c = (k & 1) ? ((int)w[k >> 1] >> 16) : (int)(int16_t)(w[k >> 1] & 0xffffu);
-        v[I] = c * q[k];
+        if (k < KLIM) {
+            const int c = (k & 1) ? ((int)w[k >> 1] >> 16) : (int)(int16_t)(w[k >> 1] & 0xffffu);
+            v[I] = c * q[k];
+        } else {
+            v[I] = 0;
+        }
     }
 };
-template <> struct GjdUnpack<0> {
+template <int KLIM> struct GjdUnpack<0, KLIM> {
     static __device__ __forceinline__ void run(const uint32_t*, const int*, int*) {}
 };
+
+/* dequantise + dezigzag + IDCT of one block (w: packed zigzag coefficients, dc: absolute DC), then park
+ * the 64 samples (biased, u16) in shared memory rows dst[r * 32] */
+template <int KLIM>
+__device__ __forceinline__ void gjd_block_to_samples(const uint32_t* w, const int* q, int dc, uint4* dst) {
+    int v[64];
+    GjdUnpack<63, KLIM>::run(w, q, v);
+    v[0] = dc * q[0];
+    gjd_idct8x8(v);
+#pragma unroll
+    for (int r = 0; r < 8; r++)
+        dst[r * 32] = make_uint4((uint32_t)v[8 * r] | ((uint32_t)v[8 * r + 1] << 16),
+                                 (uint32_t)v[8 * r + 2] | ((uint32_t)v[8 * r + 3] << 16),
+                                 (uint32_t)v[8 * r + 4] | ((uint32_t)v[8 * r + 5] << 16),
+                                 (uint32_t)v[8 * r + 6] | ((uint32_t)v[8 * r + 7] << 16));
+}
 
 /*
  * One thread block (3 warps) per GJD_TB_TILES tiles of one image; per tile, warp c takes component c
@@ -398,7 +421,7 @@ template <> struct GjdUnpack<0> {
  *                    meta), warp-scan the DC differences onto the tile's DC base, dequantise + dezigzag
  *                    into 64 registers, integer IDCT in registers, park the 64 samples (biased, 9 bits,
  *                    as u16) in shared memory [comp][row][lane] — conflict-free 128-bit stores.
- *   colour phase     warp c takes rows c, c+3, c+6: lane l reads row r of Y, Cb, Cr of MCU l (three
+ *   colour phase     the warps split the 8 rows (2/3/3): lane l reads row r of Y, Cb, Cr of MCU l (three
  *                    128-bit loads), converts 8 pixels and stores 8 bytes per plane; a warp covers 256
  *                    contiguous bytes of an image row.
  * The sample buffer is double-buffered, so one __syncthreads per tile separates the phases.
@@ -437,6 +460,11 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 6) k_transform(GjdDevBa
         const size_t blk = (size_t)(d.tile_first + ltile) * 96u + lane * 3u + c;
 
         /* ---- transform phase: component c of MCU `lane` ---- */
+        if (t + 1u < GJD_TB_TILES && ltile + 1u < d.tile_count) {
+            /* the next tile's coefficient line and meta word on their way to L2 while this tile computes */
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const uint4*>(b.coef) + (blk + 96u) * 8u));
+            if (lane < 12u && c == 0u) asm volatile("prefetch.global.L2 [%0];" ::"l"(b.meta + blk + 96u - lane * 3u + lane * 8u));
+        }
         const uint32_t m = valid ? __ldg(b.meta + blk) : 0u;
         const uint32_t kmax = (m >> 16) & 63u;
         const uint32_t nsec = kmax ? (kmax >> 4) + 1u : 0u;
@@ -459,26 +487,19 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 6) k_transform(GjdDevBa
             }
             continue;
         }
-        {
-            int v[64];
-            GjdUnpack<63>::run(w, q, v);
-            v[0] = dc * q[0];
-            gjd_idct8x8(v);
-#pragma unroll
-            for (int r = 0; r < 8; r++)
-                smp[t & 1u][c][r][lane] = make_uint4((uint32_t)v[8 * r] | ((uint32_t)v[8 * r + 1] << 16),
-                                                     (uint32_t)v[8 * r + 2] | ((uint32_t)v[8 * r + 3] << 16),
-                                                     (uint32_t)v[8 * r + 4] | ((uint32_t)v[8 * r + 5] << 16),
-                                                     (uint32_t)v[8 * r + 6] | ((uint32_t)v[8 * r + 7] << 16));
-        }
+        /* warp-uniform choice: most chroma tiles of photographic images have no coefficient past k = 15 */
+        if (__reduce_max_sync(0xffffffffu, kmax) < 16u) gjd_block_to_samples<16>(w, q, dc, &smp[t & 1u][c][0][lane]);
+        else gjd_block_to_samples<64>(w, q, dc, &smp[t & 1u][c][0][lane]);
         __syncthreads();
 
         /* ---- colour phase: rows c, c+3, c+6 of MCU `lane` ---- */
         const uint32_t by = mcu / d.mcus_x, bx = mcu - by * d.mcus_x;
         const uint32_t x0 = bx * 8u, y0 = by * 8u;
         const bool fast = aligned && (x0 + 8u <= W);
+        /* rows 0-1 for the luma warp (its transform is the long one), 2-4 and 5-7 for the chroma warps */
+        const uint32_t r0 = c == 0u ? 0u : 3u * c - 1u, r1 = 3u * c + 2u;
 #pragma unroll 1
-        for (uint32_t r = c; r < 8u; r += 3u) {
+        for (uint32_t r = r0; r < r1; r++) {
             if (!valid || y0 + r >= H) continue;
             const uint4 y4 = smp[t & 1u][0][r][lane], b4 = smp[t & 1u][1][r][lane], r4 = smp[t & 1u][2][r][lane];
             const uint32_t yw[4] = {y4.x, y4.y, y4.z, y4.w}, bw[4] = {b4.x, b4.y, b4.z, b4.w}, rw[4] = {r4.x, r4.y, r4.z, r4.w};
@@ -550,7 +571,7 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS) k_test_idct(const int16
 #pragma unroll
     for (int j = 0; j < 32; j++) w[j] = src[j];
     int v[64];
-    GjdUnpack<63>::run(w, sq, v);
+    GjdUnpack<63, 64>::run(w, sq, v);
     v[0] = (int)(int16_t)(w[0] & 0xffffu) * sq[0];
     gjd_idct8x8(v);
 #pragma unroll

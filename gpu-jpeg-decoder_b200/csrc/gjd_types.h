@@ -31,7 +31,7 @@
 #define GJD_LUT_BITS      10       /* primary Huffman LUT index width              */
 #define GJD_LUT_SIZE      (1 << GJD_LUT_BITS)
 #define GJD_TILE_MCUS     32u      /* MCUs per coefficient tile (one warp)         */
-#define GJD_TB_TILES      8u       /* tiles per transform thread block (one image)  */
+#define GJD_TB_TILES      32u      /* tiles per transform thread block (one image)  */
 
 /* LUT entry (u16):  [4:0]  total bits = code length + value size (1..27); 0 = code longer than
  *                          GJD_LUT_BITS (or unassigned): resolve with the canonical tables
