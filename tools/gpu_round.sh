@@ -1,0 +1,21 @@
+#!/bin/bash
+# One GPU-box visit: parity tests, bench (both arms), ncu launch list, ncu --set full of the hot kernels.
+# usage: tools/gpu_round.sh <tag>     (outputs under gpurun_out/<tag>_*)
+tag=${1:-rXX}
+out=gpurun_out
+mkdir -p $out
+nvidia-smi --query-gpu=name,clocks.max.sm,clocks.max.mem,power.limit --format=csv > $out/${tag}_gpu.txt 2>&1
+timeout 900 python -m pytest tests -m gpu -x -q > $out/${tag}_pytest.log 2>&1; echo "pytest rc=$?" >> $out/${tag}_pytest.log
+tail -3 $out/${tag}_pytest.log
+timeout 600 python bench.py --steps 10 --warmup 3 > $out/${tag}_bench.json 2> $out/${tag}_bench.err; echo "bench rc=$?"
+cat $out/${tag}_bench.json
+if [ "$2" != "quick" ]; then
+timeout 300 python tools/profile_run.py 300 3 > $out/${tag}_profrun.log 2>&1 && \
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/${tag}_launches.csv \
+    python tools/profile_run.py 3000 2 > $out/${tag}_ncu_launch.log 2>&1
+for k in k_transform k_huff_write k_huff_sync; do
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:$k -s 1 -c 1 -f -o $out/${tag}_$k \
+    python tools/profile_run.py 1000 2 > $out/${tag}_ncu_$k.log 2>&1
+done
+fi
+ls -la $out | tail -20
