@@ -160,3 +160,43 @@ long gjd_unstuff(const uint8_t* p, const uint8_t* end, uint8_t* dst) {
         }
     }
 }
+
+/* ---- multi-GPU sharding: greedy LPT over padded pixel counts ------------------------ */
+#include <algorithm>
+#include <numeric>
+#include <queue>
+#include <vector>
+#include "../../include/gjd.h"
+
+extern "C" int gjd_partition(const uint64_t* weight, int32_t n, int32_t parts, int32_t* part_of, uint64_t* load) {
+    if (n < 0 || parts < 1 || (n > 0 && (!weight || !part_of))) return GJD_E_ARG;
+    std::vector<int32_t> order(n);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return weight[a] > weight[b]; });
+    /* min-heap on (load, part): the lightest part takes the next-heaviest image */
+    typedef std::pair<uint64_t, int32_t> Slot;
+    std::priority_queue<Slot, std::vector<Slot>, std::greater<Slot>> heap;
+    for (int32_t p = 0; p < parts; p++) heap.push(Slot(0, p));
+    std::vector<uint64_t> acc(parts, 0);
+    for (int32_t i : order) {
+        if (weight[i] == 0) { part_of[i] = -1; continue; }
+        Slot s = heap.top();
+        heap.pop();
+        part_of[i] = s.second;
+        acc[s.second] = s.first + weight[i];
+        heap.push(Slot(acc[s.second], s.second));
+    }
+    if (load) std::copy(acc.begin(), acc.end(), load);
+    return GJD_OK;
+}
+
+extern "C" int gjd_partition_weights(const gjd_item* items, int32_t n, uint64_t* weight) {
+    if (n < 0 || (n > 0 && (!items || !weight))) return GJD_E_ARG;
+    for (int32_t i = 0; i < n; i++) {
+        GjdParsed p;
+        weight[i] = 0;
+        if (items[i].jpg && gjd_parse_headers(items[i].jpg, items[i].len, &p) == GJD_OK)
+            weight[i] = (uint64_t)(8 * ((p.width + 7) / 8)) * (uint64_t)(8 * ((p.height + 7) / 8));
+    }
+    return GJD_OK;
+}

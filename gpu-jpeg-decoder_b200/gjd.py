@@ -69,6 +69,8 @@ def lib():
     L.gjd_host_free.restype = None
     L.gjd_write_array.argtypes = [C.c_char_p, i32, i32, vp]
     L.gjd_write_ppm.argtypes = [C.c_char_p, i32, i32, vp]
+    L.gjd_partition.argtypes = [vp, i32, i32, vp, vp]
+    L.gjd_partition_weights.argtypes = [C.POINTER(Item), i32, vp]
     L.gjd_strerror.argtypes = [C.c_int]
     L.gjd_strerror.restype = C.c_char_p
     L.gjd_last_cuda_error.argtypes = [vp]
@@ -264,3 +266,31 @@ def write_array(path, rgb):
     rc = lib().gjd_write_array(path.encode(), rgb.shape[2], rgb.shape[1], rgb.ctypes.data)
     if rc != OK:
         raise GjdError(rc)
+
+
+def partition(files, parts):
+    """Greedy-LPT assignment of JPEG `bytes` objects to `parts` devices (gjd_partition over
+    gjd_partition_weights).  Returns (part_of int32[n], load uint64[parts], weight uint64[n])."""
+    n = len(files)
+    items = (Item * max(n, 1))()
+    hold = []
+    for i, d in enumerate(files):
+        buf = C.c_char_p(d)
+        hold.append(buf)
+        items[i].jpg = C.cast(buf, C.c_void_p)
+        items[i].len = len(d)
+    weight = np.zeros(max(n, 1), np.uint64)
+    part_of = np.full(max(n, 1), -1, np.int32)
+    load = np.zeros(parts, np.uint64)
+    rc = lib().gjd_partition_weights(items, n, weight.ctypes.data)
+    if rc == OK:
+        rc = lib().gjd_partition(weight.ctypes.data, n, parts, part_of.ctypes.data, load.ctypes.data)
+    if rc != OK:
+        raise GjdError(rc)
+    return part_of[:n], load, weight[:n]
+
+
+def shard_indices(files, rank, world):
+    """Indices of the images rank `rank` of `world` decodes (every rank computes the same partition)."""
+    part_of, load, _ = partition(files, world)
+    return [int(i) for i in np.nonzero(part_of == rank)[0]], load

@@ -121,6 +121,18 @@ int  gjd_test_color(gjd_ctx* ctx, const int16_t* y, const int16_t* cb, const int
 int  gjd_test_idct(gjd_ctx* ctx, const int16_t* coef_zz, size_t nblocks, const uint8_t quant_zz[64],
                    int16_t* samples);
 
+/* Multi-GPU sharding (host-only, no CUDA): assign n independent images to `parts` devices by greedy
+ * longest-processing-time on the padded pixel count 8*ceil(W/8) * 8*ceil(H/8) (the unit both the
+ * coefficient traffic and, roughly, the scan bits follow).  Deterministic: ties go to the lower image
+ * index, then to the lower part.  part_of[i] receives the device of image i (or -1 when weight[i] is 0,
+ * i.e. an image gjd_peek rejected); load[p] (may be NULL) the padded pixels assigned to part p.
+ * The reference has no multi-GPU path; this replaces "one batchDecodeKernel over everything"
+ * (cuda-decoder/benchmark_thoughput/benchmark.cu:56-70) by one such launch per device.  There is no
+ * exchange step between shards, hence no collective. */
+int  gjd_partition(const uint64_t* weight, int32_t n, int32_t parts, int32_t* part_of, uint64_t* load);
+/* Convenience over gjd_peek: weight[i] = padded pixel count of items[i] (0 if the header is unusable). */
+int  gjd_partition_weights(const gjd_item* items, int32_t n, uint64_t* weight);
+
 /* Pinned host memory helpers (callers that want full-speed H2D/D2H). */
 void* gjd_host_alloc(size_t bytes);
 void  gjd_host_free(void* p);
