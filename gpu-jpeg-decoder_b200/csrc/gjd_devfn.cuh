@@ -64,7 +64,10 @@ GJD_HD uint32_t gjd_resolve(const uint32_t* lim, const int32_t* off, const uint8
     return 16u | (1u << 9) | GJD_ENTRY_BAD;
 }
 
-/* Primary LUT entry for index i (GJD_LUT_BITS leading bits); 0 = not resolvable from these bits. */
+/* Primary LUT entry for index i (GJD_LUT_BITS leading bits).  Codes longer than GJD_LUT_BITS occupy the
+ * top of the code space (lim[] is non-decreasing), i.e. the prefixes >= lim[GJD_LUT_BITS] >> 6: the first
+ * GJD_LUT2_PREFIXES of them link to a 64-entry sub-table of the secondary LUT ((rank + 1) << 5, low five
+ * bits 0); 0 = not resolvable from tables (gjd_lookup_slow). */
 GJD_HD uint16_t gjd_lut_entry(const uint32_t* lim, const int32_t* off, const uint8_t* vals,
                               uint32_t isdc, uint32_t i) {
     uint32_t win16 = i << (16 - GJD_LUT_BITS);
@@ -74,7 +77,18 @@ GJD_HD uint16_t gjd_lut_entry(const uint32_t* lim, const int32_t* off, const uin
             return (uint16_t)gjd_make_entry((uint32_t)L, vals[idx], isdc);
         }
     }
-    return 0;
+    uint32_t rank = i - (lim[GJD_LUT_BITS] >> (16 - GJD_LUT_BITS));
+    return rank < (uint32_t)GJD_LUT2_PREFIXES ? (uint16_t)((rank + 1u) << 5) : (uint16_t)0;
+}
+
+/* Secondary LUT entry i2 = rank * 64 + (the 6 bits after the primary index): the whole 16-bit window is
+ * known, so every assigned code resolves; 0 = unassigned code (left to gjd_lookup_slow, which flags it). */
+GJD_HD uint16_t gjd_lut2_entry(const uint32_t* lim, const int32_t* off, const uint8_t* vals,
+                               uint32_t isdc, uint32_t i2) {
+    uint32_t j = (lim[GJD_LUT_BITS] >> (16 - GJD_LUT_BITS)) + (i2 >> 6);
+    if (j >= (uint32_t)GJD_LUT_SIZE) return 0;
+    uint32_t e = gjd_resolve(lim, off, vals, isdc, (j << 6) | (i2 & 63u), GJD_LUT_BITS + 1);
+    return (e & GJD_ENTRY_BAD) ? (uint16_t)0 : (uint16_t)e;
 }
 
 /* DHT slot behind ring position r (0..5): even = DC table, odd = AC table of component r/2. */
@@ -191,11 +205,16 @@ GJD_HD_COLD uint32_t gjd_lookup_slow(const GjdLutSet* lut, uint32_t tb, uint32_t
     return e;
 }
 
-/* One symbol at window w with the ring at tb: the 16-bit LUT entry.  room = bits left in the scan. */
+/* One symbol at window w with the ring at tb: the 16-bit LUT entry.  room = bits left in the scan.
+ * Primary LUT on the first GJD_LUT_BITS bits; a long code follows its link into the secondary LUT. */
 template <class Lut>
 GJD_HD uint32_t gjd_lookup(const Lut& lut, uint32_t tb, uint32_t w, uint32_t room) {
     uint32_t e = lut.entry(tb + ((w >> (31 - GJD_LUT_BITS)) & (GJD_RING_STRIDE - 2u)));
-    if ((e & 31u) == 0u) e = gjd_lookup_slow(lut.set, tb, w, room, lut.badcode);
+    if ((e & 31u) == 0u) {
+        /* sub-table ((e >> 5) - 1) of secondary table tb / RING_STRIDE, entry = next 6 bits */
+        if (e) e = lut.entry((GJD_RING_BYTES - 128u) + (tb >> 1) + e * 4u + ((w >> 15) & 126u));
+        if ((e & 31u) == 0u) e = gjd_lookup_slow(lut.set, tb, w, room, lut.badcode);
+    }
     return e;
 }
 

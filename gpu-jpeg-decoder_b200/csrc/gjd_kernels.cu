@@ -81,6 +81,11 @@ __global__ void __launch_bounds__(256) k_build_luts(const GjdDhtSet* __restrict_
         uint32_t t = gjd_ring_slot(in.tabsel, r);
         out.lut[r][j] = gjd_lut_entry(lim[t], off[t], in.vals[t], in.isdc[t], j);
     }
+    for (uint32_t i = threadIdx.x; i < GJD_RING_TABLES * GJD_LUT2_SIZE; i += blockDim.x) {
+        uint32_t r = i / GJD_LUT2_SIZE, j = i % GJD_LUT2_SIZE;
+        uint32_t t = gjd_ring_slot(in.tabsel, r);
+        out.lut2[r][j] = gjd_lut2_entry(lim[t], off[t], in.vals[t], in.isdc[t], j);
+    }
 }
 
 __global__ void __launch_bounds__(128) k_fill_maps(GjdDevBatch b) {
@@ -276,9 +281,11 @@ struct GjdWriteSink {
  * coefficient index seq_base + (block-exclusive scan of the counts), and writes the blocks it owns
  * (gjd_write_span).
  */
+#define GJD_WRITE_SMEM (sizeof(GjdLutSet) + 8u * GJD_WRITE_THREADS * sizeof(uint4))   /* dynamic: > 48 KB */
 __global__ void __launch_bounds__(GJD_WRITE_THREADS, 4) k_huff_write(GjdDevBatch b) {
-    __shared__ GjdLutSet lut;
-    __shared__ uint4 buf[8][GJD_WRITE_THREADS];
+    extern __shared__ uint4 dyn_smem[];
+    GjdLutSet& lut = *reinterpret_cast<GjdLutSet*>(dyn_smem);
+    uint4 (*buf)[GJD_WRITE_THREADS] = reinterpret_cast<uint4 (*)[GJD_WRITE_THREADS]>(dyn_smem + sizeof(GjdLutSet) / 16);
     __shared__ uint32_t ws[8];
     __shared__ uint32_t badcode;
     const uint32_t g = blockIdx.x, tid = threadIdx.x;
@@ -614,7 +621,12 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     }
     if (ev) GJD_CK(cudaEventRecord(ev->e[2], s));
     k_seq_scan<<<b.n_img, 256, 0, s>>>(b); n++;
-    k_huff_write<<<b.n_seq, GJD_WRITE_THREADS, 0, s>>>(b); n++;
+    static bool write_attr = false;   /* opt in to > 48 KB of dynamic shared memory, once per process */
+    if (!write_attr) {
+        GJD_CK(cudaFuncSetAttribute(k_huff_write, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GJD_WRITE_SMEM));
+        write_attr = true;
+    }
+    k_huff_write<<<b.n_seq, GJD_WRITE_THREADS, GJD_WRITE_SMEM, s>>>(b); n++;
     k_dc_tilebase<<<b.n_img, 256, 0, s>>>(b); n++;
     if (ev) GJD_CK(cudaEventRecord(ev->e[3], s));
     k_transform<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr); n++;

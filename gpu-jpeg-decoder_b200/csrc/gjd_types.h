@@ -30,17 +30,22 @@
 #define GJD_SEQ_SUBS      256u     /* subsequences per sequence (one thread block) */
 #define GJD_LUT_BITS      10       /* primary Huffman LUT index width              */
 #define GJD_LUT_SIZE      (1 << GJD_LUT_BITS)
+#define GJD_LUT2_PREFIXES  8       /* secondary LUT: 64-entry sub-tables for the first 8 unresolved prefixes */
+#define GJD_LUT2_SIZE     (GJD_LUT2_PREFIXES * 64)
 #define GJD_TILE_MCUS     32u      /* MCUs per coefficient tile (one warp)         */
 #define GJD_TB_TILES      32u      /* tiles per transform thread block (one image)  */
 
 /* LUT entry (u16):  [4:0]  total bits = code length + value size (1..27); 0 = code longer than
- *                          GJD_LUT_BITS (or unassigned): resolve with the canonical tables
+ *                          GJD_LUT_BITS (or unassigned): then [15:5] = 1 + rank of this prefix among the
+ *                          unresolved ones when its 64-entry sub-table exists in lut2 (indexed by the next
+ *                          6 bits; same entry format), else 0 = resolve with the canonical tables
  *                   [8:5]  value size (0..15)
  *                   [15:9] slot advance = run + 1 (1..16; DC symbols: 1); 64 = EOB (to the block end) */
 #define GJD_ADV_EOB 64u
 #define GJD_RING_TABLES 6
 #define GJD_RING_STRIDE (GJD_LUT_SIZE * 2u)                  /* bytes per table of the ring        */
 #define GJD_RING_BYTES  (GJD_RING_TABLES * GJD_RING_STRIDE)
+#define GJD_LUT2_STRIDE  (GJD_LUT2_SIZE * 2u)                 /* bytes per secondary table (= RING_STRIDE / 2) */
 
 /* One Huffman table set as the decoders use it, device-resident, built by k_build_luts from a
  * GjdDhtSet: the primary LUTs laid out as a RING in scan order — DC(comp 0), AC(comp 0), DC(comp 1),
@@ -49,6 +54,7 @@
  * (0,1 = DC Th 0,1; 2,3 = AC Th 0,1) serve the rare long codes; slot_of maps ring position -> slot. */
 typedef struct GjdLutSet {
     uint16_t lut[GJD_RING_TABLES][GJD_LUT_SIZE];
+    uint16_t lut2[GJD_RING_TABLES][GJD_LUT2_SIZE];   /* directly behind lut: one offset space for both */
     uint32_t lim[4][17];             /* lim[L] = first unused code of length L, left-aligned to 16 bits */
     int32_t  off[4][17];             /* valptr[L] - mincode[L]                                   */
     uint8_t  vals[4][256];           /* HUFFVAL                                                  */

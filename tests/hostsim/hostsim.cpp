@@ -76,6 +76,8 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
         lut->slot_of[r] = (uint8_t)t;
         for (uint32_t i = 0; i < GJD_LUT_SIZE; i++)
             lut->lut[r][i] = gjd_lut_entry(lut->lim[t], lut->off[t], lut->vals[t], lut->isdc[t], i);
+        for (uint32_t i = 0; i < GJD_LUT2_SIZE; i++)
+            lut->lut2[r][i] = gjd_lut2_entry(lut->lim[t], lut->off[t], lut->vals[t], lut->isdc[t], i);
     }
     uint32_t badcode = 0;
     GjdLutMem hlut;
@@ -274,6 +276,48 @@ int hostsim_parse(const uint8_t* jpg, size_t len, int32_t* w, int32_t* h) {
     if (w) *w = p.width;
     if (h) *h = p.height;
     return rc;
+}
+
+/* Every 16-bit window against every ring table of the image's DHTs: the two-level LUT (gjd_lookup) must
+ * give the entry the canonical tables give (gjd_resolve from length 1).  out[0] = windows that differ,
+ * out[1] = windows that are assigned codes yet miss both LUT levels (served by gjd_lookup_slow),
+ * out[2] = windows with a code longer than GJD_LUT_BITS. */
+int hostsim_lut_check(const uint8_t* jpg, size_t len, uint32_t out[3]) {
+    GjdParsed p;
+    int rc = gjd_parse_headers(jpg, len, &p);
+    if (rc) return rc;
+    GjdLutSet* lut = (GjdLutSet*)calloc(1, sizeof(GjdLutSet));
+    for (int t = 0; t < 4; t++) {
+        gjd_canonical(p.dht.bits[t], lut->lim[t], lut->off[t]);
+        memcpy(lut->vals[t], p.dht.vals[t], 256);
+        lut->isdc[t] = p.dht.isdc[t];
+    }
+    out[0] = out[1] = out[2] = 0;
+    for (uint32_t r = 0; r < GJD_RING_TABLES; r++) {
+        uint32_t t = gjd_ring_slot(p.tabsel, r);
+        lut->slot_of[r] = (uint8_t)t;
+        for (uint32_t i = 0; i < GJD_LUT_SIZE; i++)
+            lut->lut[r][i] = gjd_lut_entry(lut->lim[t], lut->off[t], lut->vals[t], lut->isdc[t], i);
+        for (uint32_t i = 0; i < GJD_LUT2_SIZE; i++)
+            lut->lut2[r][i] = gjd_lut2_entry(lut->lim[t], lut->off[t], lut->vals[t], lut->isdc[t], i);
+        GjdLutMem m;
+        uint32_t badcode = 0;
+        m.set = lut; m.badcode = &badcode;
+        for (uint32_t win = 0; win < 65536u; win++) {
+            const uint32_t w = win << 16, tb = r * GJD_RING_STRIDE;
+            uint32_t want = gjd_resolve(lut->lim[t], lut->off[t], lut->vals[t], lut->isdc[t], win, 1);
+            if (want & GJD_ENTRY_BAD) want = 16u;
+            if (gjd_lookup(m, tb, w, 64u) != want) out[0]++;
+            uint32_t e = m.entry(tb + ((w >> (31 - GJD_LUT_BITS)) & (GJD_RING_STRIDE - 2u)));
+            if ((e & 31u) == 0u) {
+                if (want != 16u) out[2]++;
+                uint32_t e2 = e ? m.entry((GJD_RING_BYTES - 128u) + (tb >> 1) + e * 4u + ((w >> 15) & 126u)) : 0u;
+                if ((e2 & 31u) == 0u && want != 16u) out[1]++;
+            }
+        }
+    }
+    free(lut);
+    return 0;
 }
 
 }  /* extern "C" */

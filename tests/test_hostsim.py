@@ -105,3 +105,18 @@ def test_hostsim_seeded_synthetic(hostsim, oracle):
         assert orc == 0
         assert np.array_equal(rgb, want_rgb), sp
         assert np.array_equal(coef, want_coef), sp
+
+
+def test_two_level_lut_matches_canonical_tables(hostsim, golden):
+    """All 65536 windows x 6 ring tables of every fixture (standard and optimised DHTs): the primary +
+    secondary LUT lookup equals the canonical-table walk, and no assigned code is left to the slow path."""
+    import ctypes as C
+    long_codes = 0
+    for name, data in sorted(golden.items()):
+        out = np.zeros(3, np.uint32)
+        rc = hostsim.lib.hostsim_lut_check(C.cast(C.c_char_p(data), C.c_void_p), len(data), out.ctypes.data)
+        assert rc == 0, name
+        assert out[0] == 0, (name, out)
+        assert out[1] == 0, (name, out)
+        long_codes += int(out[2])
+    assert long_codes > 0
