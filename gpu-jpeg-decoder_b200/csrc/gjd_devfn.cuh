@@ -510,9 +510,11 @@ GJD_HD_COLD int gjd_color_g_exact(int y, int cb, int cr) {
     return G > 255 ? 255 : (G < 0 ? 0 : G);
 }
 
-/* Fast path on biased inputs (yb, cbb, crb in [0,511]).  Returns true when G sits in the danger zone
- * and must be recomputed with gjd_color_g_exact (843 of the 2^27 triples). */
-GJD_HD bool gjd_color_fast(int yb, int cbb, int crb, int& R, int& G, int& B) {
+/* Fast path on biased inputs (yb, cbb, crb in [0,511]).  Returns the fraction field of G left-aligned
+ * (tg << 12): G sits in the danger zone and must be recomputed with gjd_color_g_exact (843 of the 2^27
+ * triples) when it is below GJD_FRAC_DANGER. */
+#define GJD_FRAC_DANGER ((2u * GJD_GDELTA) << 12)
+GJD_HD uint32_t gjd_color_fast_frac(int yb, int cbb, int crb, int& R, int& G, int& B) {
     int tr = crb * GJD_KR + GJD_CONST_R;
     int tb = cbb * GJD_KB + GJD_CONST_B;
     int tg = crb * (-GJD_KGR) + GJD_CONST_G;
@@ -520,7 +522,10 @@ GJD_HD bool gjd_color_fast(int yb, int cbb, int crb, int& R, int& G, int& B) {
     R = gjd_addmin_relu(tr >> 20, yb, 255);
     B = gjd_addmin_relu(tb >> 20, yb, 255);
     G = gjd_addmin_relu(tg >> 20, yb, 255);
-    return (uint32_t)(tg & 0xFFFFF) < 2u * GJD_GDELTA;
+    return (uint32_t)tg * 4096u;
+}
+GJD_HD bool gjd_color_fast(int yb, int cbb, int crb, int& R, int& G, int& B) {
+    return gjd_color_fast_frac(yb, cbb, crb, R, G, B) < GJD_FRAC_DANGER;
 }
 
 GJD_HD void gjd_color(int yb, int cbb, int crb, int& R, int& G, int& B) {

@@ -415,10 +415,10 @@ __device__ __forceinline__ void gjd_block_to_samples(const uint32_t* w, const in
     gjd_idct8x8(v);
 #pragma unroll
     for (int r = 0; r < 8; r++)
-        dst[r * 32] = make_uint4((uint32_t)v[8 * r] | ((uint32_t)v[8 * r + 1] << 16),
-                                 (uint32_t)v[8 * r + 2] | ((uint32_t)v[8 * r + 3] << 16),
-                                 (uint32_t)v[8 * r + 4] | ((uint32_t)v[8 * r + 5] << 16),
-                                 (uint32_t)v[8 * r + 6] | ((uint32_t)v[8 * r + 7] << 16));
+        dst[r * 32] = make_uint4((uint32_t)v[8 * r + 1] * 65536u + (uint32_t)v[8 * r],
+                                 (uint32_t)v[8 * r + 3] * 65536u + (uint32_t)v[8 * r + 2],
+                                 (uint32_t)v[8 * r + 5] * 65536u + (uint32_t)v[8 * r + 4],
+                                 (uint32_t)v[8 * r + 7] * 65536u + (uint32_t)v[8 * r + 6]);
 }
 
 /*
@@ -438,8 +438,8 @@ __device__ __forceinline__ void gjd_block_to_samples(const uint32_t* w, const in
  * EXPORT = true is the coefficient test hook: blocks are written out in the reference layout
  * mcu*192 + comp*64 + k with the absolute DC in slot 0 instead of being transformed.
  */
-template <bool EXPORT>
-__global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 6) k_transform(GjdDevBatch b, int16_t* __restrict__ coef_out) {
+template <bool EXPORT, int MINB>
+__global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDevBatch b, int16_t* __restrict__ coef_out) {
     __shared__ int sq[3][64];
     __shared__ uint4 smp[2][3][8][32];
 
@@ -510,28 +510,31 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 6) k_transform(GjdDevBa
             if (!valid || y0 + r >= H) continue;
             const uint4 y4 = smp[t & 1u][0][r][lane], b4 = smp[t & 1u][1][r][lane], r4 = smp[t & 1u][2][r][lane];
             const uint32_t yw[4] = {y4.x, y4.y, y4.z, y4.w}, bw[4] = {b4.x, b4.y, b4.z, b4.w}, rw[4] = {r4.x, r4.y, r4.z, r4.w};
-            uint32_t pr[2] = {0, 0}, pg[2] = {0, 0}, pb[2] = {0, 0}, danger = 0;
+            /* bytes are packed by multiply-add (values are 0..255, so + is |): one IMAD/LEA per pixel and
+             * channel; the danger test of the 8 pixels is one unsigned min over the fraction fields */
+            uint32_t pr[2] = {0, 0}, pg[2] = {0, 0}, pb[2] = {0, 0}, fmin = 0xffffffffu;
 #pragma unroll
             for (int x = 0; x < 8; x++) {
                 const int sh = (x & 1) * 16;
                 int R, G, B;
-                if (gjd_color_fast((int)((yw[x >> 1] >> sh) & 0xffffu), (int)((bw[x >> 1] >> sh) & 0xffffu),
-                                   (int)((rw[x >> 1] >> sh) & 0xffffu), R, G, B))
-                    danger |= 1u << x;
-                pr[x >> 2] |= (uint32_t)R << (8 * (x & 3));
-                pg[x >> 2] |= (uint32_t)G << (8 * (x & 3));
-                pb[x >> 2] |= (uint32_t)B << (8 * (x & 3));
+                const uint32_t frac = gjd_color_fast_frac((int)((yw[x >> 1] >> sh) & 0xffffu), (int)((bw[x >> 1] >> sh) & 0xffffu),
+                                                          (int)((rw[x >> 1] >> sh) & 0xffffu), R, G, B);
+                fmin = min(fmin, frac);
+                pr[x >> 2] = (uint32_t)R * (1u << (8 * (x & 3))) + pr[x >> 2];
+                pg[x >> 2] = (uint32_t)G * (1u << (8 * (x & 3))) + pg[x >> 2];
+                pb[x >> 2] = (uint32_t)B * (1u << (8 * (x & 3))) + pb[x >> 2];
             }
             uint64_t g8 = ((uint64_t)pg[1] << 32) | pg[0];
-            if (danger) {   /* rare: G of the flagged pixels again with the reference's IEEE sequence */
+            if (fmin < GJD_FRAC_DANGER) {   /* rare: G of the flagged pixels again with the reference's IEEE sequence */
                 const uint16_t* ys = reinterpret_cast<const uint16_t*>(&smp[t & 1u][0][r][lane]);
                 const uint16_t* bs = reinterpret_cast<const uint16_t*>(&smp[t & 1u][1][r][lane]);
                 const uint16_t* rs = reinterpret_cast<const uint16_t*>(&smp[t & 1u][2][r][lane]);
 #pragma unroll 1
                 for (uint32_t x = 0; x < 8u; x++) {
-                    if (!((danger >> x) & 1u)) continue;
-                    const uint64_t G = (uint64_t)gjd_color_g_exact((int)ys[x] - 256, (int)bs[x] - 256, (int)rs[x] - 256);
-                    g8 = (g8 & ~(0xffull << (8u * x))) | (G << (8u * x));
+                    int R, G, B;
+                    if (gjd_color_fast_frac((int)ys[x], (int)bs[x], (int)rs[x], R, G, B) >= GJD_FRAC_DANGER) continue;
+                    const uint64_t Ge = (uint64_t)gjd_color_g_exact((int)ys[x] - 256, (int)bs[x] - 256, (int)rs[x] - 256);
+                    g8 = (g8 & ~(0xffull << (8u * x))) | (Ge << (8u * x));
                 }
             }
             uint8_t* row = out + (size_t)(y0 + r) * pitch + x0;
@@ -629,7 +632,9 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     k_huff_write<<<b.n_seq, GJD_WRITE_THREADS, GJD_WRITE_SMEM, s>>>(b); n++;
     k_dc_tilebase<<<b.n_img, 256, 0, s>>>(b); n++;
     if (ev) GJD_CK(cudaEventRecord(ev->e[3], s));
-    k_transform<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr); n++;
+    if (transform_variant == 1) k_transform<false, 6><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
+    else k_transform<false, 8><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
+    n++;
     if (ev) GJD_CK(cudaEventRecord(ev->e[4], s));
     if (launches) *launches = n;
     return cudaGetLastError();
@@ -637,7 +642,7 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
 
 cudaError_t gjd_launch_export_coefs(const GjdDevBatch& b, int16_t* out, cudaStream_t s) {
     /* single-image batch: out is indexed by the image's own MCU numbers */
-    k_transform<true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, out);
+    k_transform<true, 6><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, out);
     return cudaGetLastError();
 }
 
