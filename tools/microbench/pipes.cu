@@ -1,0 +1,46 @@
+// Issue-rate microbenchmark for the integer instructions the decode kernels lean on (sm_100a).
+// build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o pipes pipes.cu ; run: ./pipes
+#include <cstdio>
+#include <cuda_runtime.h>
+#define N_IT 2048
+template <int OP>
+__global__ void __launch_bounds__(256) k(int* out, int seed) {
+    int a[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) a[i] = seed + threadIdx.x * (i + 1);
+    int c = seed | 3;
+    for (int it = 0; it < N_IT; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            if (OP == 0) asm volatile("mad.lo.s32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c));
+            if (OP == 1) asm volatile("mul.hi.s32 %0, %0, %1;" : "+r"(a[i]) : "r"(c));
+            if (OP == 2) asm volatile("shr.s32 %0, %0, 3;" : "+r"(a[i]));
+            if (OP == 3) asm volatile("lop3.b32 %0, %0, %1, %0, 0x96;" : "+r"(a[i]) : "r"(c));
+            if (OP == 4) asm volatile("{.reg .u32 t; shr.s32 t, %0, 3; add.s32 %0, t, %1;}" : "+r"(a[i]) : "r"(c));   // LEA.HI.SX32
+            if (OP == 5) { asm volatile("mad.lo.s32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); asm volatile("shr.s32 %0, %0, 3;" : "+r"(a[i])); }
+            if (OP == 6) asm volatile("mul.hi.u32 %0, %0, 65536;" : "+r"(a[i]));
+            if (OP == 7) asm volatile("prmt.b32 %0, %0, %1, 0x9910;" : "+r"(a[i]) : "r"(c));
+            if (OP == 8) asm volatile("{.reg .s32 t; add.s32 t, %0, %1; min.s32 t, t, 511; max.s32 %0, t, 0;}" : "+r"(a[i]) : "r"(c));
+        }
+    }
+    int s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += a[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+template <int OP> void run(const char* name, int per_iter) {
+    int* d; cudaMalloc(&d, 148 * 8 * 256 * sizeof(int));
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    k<OP><<<148 * 8, 256>>>(d, 7); cudaDeviceSynchronize();
+    cudaEventRecord(e0); k<OP><<<148 * 8, 256>>>(d, 7); cudaEventRecord(e1); cudaEventSynchronize(e1);
+    float ms; cudaEventElapsedTime(&ms, e0, e1);
+    double warp_inst = 148.0 * 8 * 8 * (double)N_IT * 8 * per_iter;   // blocks * warps * iters * 8 chains
+    printf("%-34s %8.3f ms  %6.2f warp-inst/clk/SM (at 1.965 GHz)\n", name, ms, warp_inst / (ms * 1e-3) / 148 / 1.965e9);
+    cudaFree(d);
+}
+int main() {
+    run<0>("IMAD", 1); run<1>("IMAD.HI (s32, reg)", 1); run<2>("SHF.R.S32", 1); run<3>("LOP3", 1);
+    run<4>("LEA.HI.SX32 (shr+add)", 1); run<5>("IMAD + SHF pair", 2); run<6>("IMAD.HI.U32 x 65536", 1);
+    run<7>("PRMT", 1); run<8>("VIADDMNMX.RELU (add,min,max)", 1);
+    return 0;
+}
