@@ -154,6 +154,7 @@ struct gjd_batch {
     std::vector<GjdParsed> parsed;
     std::vector<ItemGeom> geom;
     std::vector<GjdImage> imgs;      /* device descriptors, only for items with status OK */
+    std::vector<GjdSegment> segs;    /* restart intervals of those images (one per image without restarts) */
     std::vector<int32_t> img_of;     /* item -> index into imgs, or -1 */
     std::vector<GjdDhtSet> dhts;
     std::vector<GjdQuantSet> quants;
@@ -236,23 +237,28 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     b->geom.assign(geom, geom + n);
     b->img_of.assign(n, -1);
     b->imgs.clear();
+    b->segs.clear();
     b->dhts.clear();
     b->quants.clear();
 
     /* scan staging offsets from file sizes (upper bound of the unstuffed scan) */
     std::vector<size_t> soff(n + 1, 0);
     for (int32_t i = 0; i < n; i++)
-        soff[i + 1] = soff[i] + (b->geom[i].status == GJD_OK ? align_up(items[i].len + 16, 128) : 0);
+        soff[i + 1] = soff[i] + (b->geom[i].status == GJD_OK
+                                     ? align_up(items[i].len + 16 + (parsed[i].restart_interval ? items[i].len / 2 + 64 : 0), 128)
+                                     : 0);
     b->scan_alloc = soff[n] + 256;
     GJD_TRY(b->h_scan.ensure(b->scan_alloc));
     uint8_t* hs = (uint8_t*)b->h_scan.p;
 
     std::vector<long> ulen(n, 0);
+    std::vector<std::vector<uint32_t>> rst_off(n), rst_len(n);   /* restart intervals (images with DRI only) */
     ctx->pool->parallel_for((size_t)n, 4, [&](size_t i) {
         if (b->geom[i].status != GJD_OK) return;
         const GjdParsed& p = parsed[i];
         uint8_t* dst = hs + soff[i];
-        long m = gjd_unstuff(p.scan_begin, p.file_end, dst);
+        long m = p.restart_interval ? gjd_unstuff_segments(p.scan_begin, p.file_end, dst, &rst_off[i], &rst_len[i])
+                                    : gjd_unstuff(p.scan_begin, p.file_end, dst);
         if (m < 0) { b->geom[i].status = (int32_t)m; return; }
         memset(dst + m, 0, 16);
         ulen[i] = m;
@@ -280,11 +286,6 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         if ((uint64_t)ulen[i] * 8 >= 0xffff0000ull) { g.status = GJD_E_UNSUPPORTED; continue; }
         GjdImage d;
         memset(&d, 0, sizeof(d));
-        d.scan_off = soff[i];
-        d.scan_bits = (uint32_t)(ulen[i] * 8);
-        d.sub_count = std::max<uint32_t>(1u, (uint32_t)(((uint64_t)d.scan_bits + sub_bits - 1) / sub_bits));
-        d.seq_first = seq;
-        d.seq_count = (d.sub_count + GJD_SEQ_SUBS - 1) / GJD_SEQ_SUBS;
         d.width = (uint32_t)g.width;
         d.height = (uint32_t)g.height;
         d.mcus_x = (d.width + 7) / 8;
@@ -303,8 +304,10 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
             d.out_off = rgb_off;
             rgb_off += align_up(g.out_bytes, 256);
         }
-        memcpy(d.tabsel, p.tabsel, 8);
-        memcpy(d.qsel, p.qsel, 4);
+        d.restart_interval = p.restart_interval;
+        const uint32_t nseg = p.restart_interval ? (d.mcu_count + p.restart_interval - 1) / p.restart_interval : 1u;
+        if (p.restart_interval && rst_off[i].size() != nseg) { g.status = GJD_E_CORRUPT; continue; }
+        uint16_t lut_id = 0;
         /* Huffman table set: dedup by content */
         {
             GjdDhtSet key = p.dht;              /* the LUT ring depends on the scan's table selectors too */
@@ -321,7 +324,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
                 b->dhts.push_back(key);
                 cand.push_back((uint32_t)found);
             }
-            d.lut_id = (uint16_t)found;
+            lut_id = (uint16_t)found;
         }
         {
             GjdQuantSet q;
@@ -340,7 +343,27 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
             }
             d.quant_id = (uint16_t)found;
         }
-        seq += d.seq_count;
+        d.seg_first = (uint32_t)b->segs.size();
+        d.seg_count = nseg;
+        for (uint32_t k = 0; k < nseg; k++) {
+            GjdSegment sg;
+            memset(&sg, 0, sizeof(sg));
+            const uint32_t off = p.restart_interval ? rst_off[i][k] : 0u;
+            const uint32_t len = p.restart_interval ? rst_len[i][k] : (uint32_t)ulen[i];
+            sg.scan_off = soff[i] + off;
+            sg.scan_bits = len * 8u;
+            sg.sub_count = std::max<uint32_t>(1u, (uint32_t)(((uint64_t)sg.scan_bits + sub_bits - 1) / sub_bits));
+            sg.seq_first = seq;
+            sg.seq_count = (sg.sub_count + GJD_SEQ_SUBS - 1) / GJD_SEQ_SUBS;
+            sg.img = (uint32_t)b->imgs.size();
+            const uint32_t mcu0 = k * p.restart_interval;
+            sg.blk_first = 3u * mcu0;
+            sg.blk_count = 3u * (p.restart_interval ? std::min(p.restart_interval, d.mcu_count - mcu0) : d.mcu_count);
+            sg.lut_id = lut_id;
+            seq += sg.seq_count;
+            b->subseqs += sg.sub_count;
+            b->segs.push_back(sg);
+        }
         tile += d.tile_count;
         tb += d.tb_count;
         b->img_of[i] = (int32_t)b->imgs.size();
@@ -348,7 +371,6 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         b->pixels += (uint64_t)d.width * d.height;
         b->padded_pixels += (uint64_t)d.mcu_count * 64;
         b->scan_bytes += (uint64_t)ulen[i];
-        b->subseqs += d.sub_count;
     }
     b->rgb_alloc = rgb_off;
 
@@ -356,6 +378,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     GjdDevBatch& v = b->view;
     memset(&v, 0, sizeof(v));
     v.n_img = n_img;
+    v.n_seg = (uint32_t)b->segs.size();
     v.n_seq = seq;
     v.sub_log2 = sub_log2;
     v.n_tile = tile;
@@ -364,11 +387,13 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
 
     /* one pinned block for descriptors + DHT sets + quant sets, one H2D copy */
     size_t o_img = 0;
-    size_t o_dht = align_up(o_img + sizeof(GjdImage) * n_img, 256);
+    size_t o_seg = align_up(o_img + sizeof(GjdImage) * n_img, 256);
+    size_t o_dht = align_up(o_seg + sizeof(GjdSegment) * b->segs.size(), 256);
     size_t o_q = align_up(o_dht + sizeof(GjdDhtSet) * b->dhts.size(), 256);
     size_t meta = align_up(o_q + sizeof(GjdQuantSet) * b->quants.size(), 256);
     GJD_TRY(b->h_meta.ensure(meta));
     memcpy((uint8_t*)b->h_meta.p + o_img, b->imgs.data(), sizeof(GjdImage) * n_img);
+    memcpy((uint8_t*)b->h_meta.p + o_seg, b->segs.data(), sizeof(GjdSegment) * b->segs.size());
     memcpy((uint8_t*)b->h_meta.p + o_dht, b->dhts.data(), sizeof(GjdDhtSet) * b->dhts.size());
     memcpy((uint8_t*)b->h_meta.p + o_q, b->quants.data(), sizeof(GjdQuantSet) * b->quants.size());
 
@@ -387,11 +412,12 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     GJD_TRY(b->h_status.ensure((size_t)(n_img + 1) * sizeof(uint32_t)));
 
     v.imgs = (const GjdImage*)((uint8_t*)b->d_meta.p + o_img);
+    v.segs = (const GjdSegment*)((uint8_t*)b->d_meta.p + o_seg);
     v.scan = (const uint8_t*)b->d_scan.p;
     v.luts = (const GjdLutSet*)b->d_luts.p;
     v.quants = (const GjdQuantSet*)((uint8_t*)b->d_meta.p + o_q);
     v.sinfo = (uint2*)b->d_sinfo.p;
-    v.seq_img = (uint32_t*)b->d_seqmaps.p;
+    v.seq_seg = (uint32_t*)b->d_seqmaps.p;
     v.seq_base = (uint32_t*)b->d_seqmaps.p + seq;
     v.seq_in = (uint2*)((uint32_t*)b->d_seqmaps.p + 2 * (size_t)seq);
     v.coef = (int16_t*)b->d_coef.p;

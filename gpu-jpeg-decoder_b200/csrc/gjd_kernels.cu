@@ -89,11 +89,17 @@ __global__ void __launch_bounds__(256) k_build_luts(const GjdDhtSet* __restrict_
 }
 
 __global__ void __launch_bounds__(128) k_fill_maps(GjdDevBatch b) {
-    uint32_t img = blockIdx.x;
-    const GjdImage& d = b.imgs[img];
-    for (uint32_t i = threadIdx.x; i < d.seq_count; i += blockDim.x) b.seq_img[d.seq_first + i] = img;
-    for (uint32_t i = threadIdx.x; i < d.tile_count; i += blockDim.x) b.tile_img[d.tile_first + i] = img;
-    for (uint32_t i = threadIdx.x; i < d.tb_count; i += blockDim.x) b.tb_img[d.tb_first + i] = img;
+    /* blocks [0, n_img): tile and transform-block maps; blocks [n_img, n_img + n_seg): sequence -> segment */
+    if (blockIdx.x < b.n_img) {
+        uint32_t img = blockIdx.x;
+        const GjdImage& d = b.imgs[img];
+        for (uint32_t i = threadIdx.x; i < d.tile_count; i += blockDim.x) b.tile_img[d.tile_first + i] = img;
+        for (uint32_t i = threadIdx.x; i < d.tb_count; i += blockDim.x) b.tb_img[d.tb_first + i] = img;
+    } else {
+        uint32_t sg = blockIdx.x - b.n_img;
+        const GjdSegment& d = b.segs[sg];
+        for (uint32_t i = threadIdx.x; i < d.seq_count; i += blockDim.x) b.seq_seg[d.seq_first + i] = sg;
+    }
 }
 
 /* ------------------------------------------------------------------ entropy: sync ----- */
@@ -118,7 +124,7 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
     __shared__ uint32_t sn[GJD_SEQ_SUBS];
 
     const uint32_t g = blockIdx.x, tid = threadIdx.x;
-    const GjdImage& d = b.imgs[b.seq_img[g]];
+    const GjdSegment& d = b.segs[b.seq_seg[g]];
     const uint32_t ls = g - d.seq_first;
     const uint32_t sub = ls * GJD_SEQ_SUBS + tid;
     const uint32_t sub_count = d.sub_count, scan_bits = d.scan_bits;
@@ -176,8 +182,7 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
 __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= b.n_seq) return;
-    uint32_t img = b.seq_img[g];
-    const GjdImage& d = b.imgs[img];
+    const GjdSegment& d = b.segs[b.seq_seg[g]];
     uint32_t ls = g - d.seq_first;
     if (ls == 0) return;
     uint2* si = b.sinfo + (size_t)g * GJD_SEQ_SUBS;
@@ -211,13 +216,14 @@ __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
 
 /* ------------------------------------------------------------------ entropy: scan ----- */
 /*
- * One block per image: coefficient count of every sequence, exclusive scan over the image's
- * sequences -> seq_base.  Also checks the image's total against 192 * MCUs.
+ * One block per segment: coefficient count of every sequence, exclusive scan over the segment's
+ * sequences -> seq_base.  Also checks the segment's total against 64 * its block count.
  */
 __global__ void __launch_bounds__(256) k_seq_scan(GjdDevBatch b) {
     __shared__ uint32_t ws[8];
-    const uint32_t img = blockIdx.x, tid = threadIdx.x;
-    const GjdImage& d = b.imgs[img];
+    const uint32_t tid = threadIdx.x;
+    const GjdSegment& d = b.segs[blockIdx.x];
+    const uint32_t img = d.img;
     uint32_t carry = 0;
     for (uint32_t base = 0; base < d.seq_count; base += 256) {
         uint32_t s = base + tid, total = 0;
@@ -231,7 +237,7 @@ __global__ void __launch_bounds__(256) k_seq_scan(GjdDevBatch b) {
         if (s < d.seq_count) b.seq_base[d.seq_first + s] = carry + excl;
         carry += blocksum;
     }
-    if (tid == 0 && carry != 192u * d.mcu_count) atomicOr(b.status + img, GJD_DEV_BADCOUNT);
+    if (tid == 0 && carry != 64u * d.blk_count) atomicOr(b.status + img, GJD_DEV_BADCOUNT);
 }
 
 /* ------------------------------------------------------------------ entropy: write ---- */
@@ -289,8 +295,8 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, 4) k_huff_write(GjdDevBatch
     __shared__ uint32_t ws[8];
     __shared__ uint32_t badcode;
     const uint32_t g = blockIdx.x, tid = threadIdx.x;
-    const uint32_t img = b.seq_img[g];
-    const GjdImage& d = b.imgs[img];
+    const GjdSegment& d = b.segs[b.seq_seg[g]];
+    const uint32_t img = d.img;
     const uint32_t ls = g - d.seq_first;
     const uint32_t sub = ls * GJD_SEQ_SUBS + tid;
     const uint32_t scan_bits = d.scan_bits;
@@ -317,12 +323,13 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, 4) k_huff_write(GjdDevBatch
     uint32_t bad = 0;
     GjdWriteSink sink;
     sink.mine = &buf[0][tid];
-    sink.coef = reinterpret_cast<uint4*>(b.coef) + (size_t)d.tile_first * (96u * 8u);
-    sink.meta = b.meta + (size_t)d.tile_first * 96u;
+    const size_t blk0 = (size_t)b.imgs[img].tile_first * 96u + d.blk_first;   /* the segment's first block */
+    sink.coef = reinterpret_cast<uint4*>(b.coef) + blk0 * 8u;
+    sink.meta = b.meta + blk0;
     const uint32_t idx0 = b.seq_base[g] + excl;
     if (active && idx0 % 192u != st.pos && st.p < scan_bits) bad |= GJD_DEV_BADSTATE;
     uint32_t end = min((sub + 1) << b.sub_log2, scan_bits);
-    gjd_write_span(scan, slut, end, scan_bits, st, idx0, 3u * d.mcu_count, active, sink, bad);
+    gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad);
     if (bad) atomicOr(b.status + img, bad);
     __syncthreads();
     if (tid == 0 && badcode) atomicOr(b.status + img, GJD_DEV_BADCODE);
@@ -376,6 +383,32 @@ __device__ __forceinline__ int warp_incl_scan_i(int v, uint32_t lane) {
 }
 
 #define GJD_TRANSFORM_THREADS 96
+
+/* DC of (mcu, component c) in an image with restart intervals (T.81 E.1.4: the predictors restart from 0
+ * every restart_interval MCUs).  incl = inclusive warp scan of the tile's DC differences, tb = the plain
+ * running sums at the tile start (k_dc_tilebase ignores restarts).  A lane whose interval starts inside the
+ * tile subtracts the scan value just before the interval start; the others need the plain sum at their
+ * interval start ms0 (the same for all of them), read from the tile that holds ms0.  Warp-converged. */
+__device__ __noinline__ int gjd_restart_dc(const int4* __restrict__ tilebase_img, const uint32_t* __restrict__ meta_img,
+                                           uint32_t ri, uint32_t ltile, uint32_t mcu, uint32_t c, uint32_t lane,
+                                           int incl, int4 tb) {
+    const uint32_t m0 = ltile * GJD_TILE_MCUS;
+    const uint32_t ms = mcu - mcu % ri;                 /* first MCU of this lane's interval */
+    const int before = __shfl_sync(0xffffffffu, incl, ms > m0 ? ms - m0 - 1u : 0u);
+    const int p_tile = c == 0 ? tb.x : c == 1 ? tb.y : tb.z;
+    const uint32_t ms0 = m0 - m0 % ri;                  /* interval running at the tile start */
+    int p_ms0 = p_tile;
+    if (ms0 != m0) {                                    /* warp-uniform */
+        const uint32_t j = ms0 / GJD_TILE_MCUS, r = ms0 % GJD_TILE_MCUS;
+        const int4 tj = tilebase_img[j];
+        int v = 0;
+        if (lane < r) v = (int)(int16_t)(__ldg(meta_img + (size_t)j * 96u + lane * 3u + c) & 0xffffu);
+        p_ms0 = (c == 0 ? tj.x : c == 1 ? tj.y : tj.z) + __reduce_add_sync(0xffffffffu, v);
+    }
+    if (ms > m0) return incl - before;
+    if (ms == m0) return incl;
+    return incl + p_tile - p_ms0;
+}
 
 /* natural index -> zigzag index as a compile-time function (GJD_ZZ_TABLE) */
 __host__ __device__ constexpr int gjd_zz_of_nat(int i) {
@@ -484,7 +517,13 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
             w[4 * j] = r.x; w[4 * j + 1] = r.y; w[4 * j + 2] = r.z; w[4 * j + 3] = r.w;
         }
         const int4 tb = b.tilebase[d.tile_first + ltile];
-        const int dc = warp_incl_scan_i((int)(int16_t)(m & 0xffffu), lane) + (c == 0 ? tb.x : c == 1 ? tb.y : tb.z);
+        int dc = warp_incl_scan_i((int)(int16_t)(m & 0xffffu), lane);
+        if (d.restart_interval == 0u) {
+            dc += c == 0 ? tb.x : c == 1 ? tb.y : tb.z;
+        } else {
+            dc = gjd_restart_dc(b.tilebase + d.tile_first, b.meta + (size_t)d.tile_first * 96u, d.restart_interval,
+                                ltile, mcu, c, lane, dc, tb);
+        }
         if (EXPORT) {
             if (valid) {
                 uint4* o = reinterpret_cast<uint4*>(coef_out + (size_t)mcu * 192u + c * 64u);
@@ -600,7 +639,7 @@ cudaError_t gjd_launch_build_luts(const GjdDhtSet* dht, GjdLutSet* luts, uint32_
 
 cudaError_t gjd_launch_fill_maps(const GjdDevBatch& b, cudaStream_t s) {
     if (b.n_img == 0) return cudaSuccess;
-    k_fill_maps<<<b.n_img, 128, 0, s>>>(b);
+    k_fill_maps<<<b.n_img + b.n_seg, 128, 0, s>>>(b);
     return cudaGetLastError();
 }
 
@@ -623,7 +662,7 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
         k_huff_fix<<<(b.n_seq + 127) / 128, 128, 0, s>>>(b); n++;
     }
     if (ev) GJD_CK(cudaEventRecord(ev->e[2], s));
-    k_seq_scan<<<b.n_img, 256, 0, s>>>(b); n++;
+    k_seq_scan<<<b.n_seg, 256, 0, s>>>(b); n++;
     static bool write_attr = false;   /* opt in to > 48 KB of dynamic shared memory, once per process */
     if (!write_attr) {
         GJD_CK(cudaFuncSetAttribute(k_huff_write, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GJD_WRITE_SMEM));

@@ -14,12 +14,14 @@
 struct GjdDevBatch {
     const GjdImage* imgs;
     uint32_t n_img;
+    const GjdSegment* segs;
+    uint32_t n_seg;
     const uint8_t* scan;
     const GjdLutSet* luts;
     const GjdQuantSet* quants;
     uint2* sinfo;          /* [n_seq * GJD_SEQ_SUBS] */
-    uint32_t* seq_img;     /* [n_seq]  sequence -> image */
-    uint32_t* seq_base;    /* [n_seq]  coefficient index (within the image) at the sequence start */
+    uint32_t* seq_seg;     /* [n_seq]  sequence -> segment */
+    uint32_t* seq_base;    /* [n_seq]  coefficient index (within the segment) at the sequence start */
     uint2* seq_in;         /* [n_seq]  entry state {p, pos} of the sequence's first subsequence (k_huff_sync -> k_huff_fix) */
     uint32_t n_seq;
     uint32_t sub_log2;     /* log2 of the subsequence length in bits (per batch) */

@@ -5,6 +5,8 @@
 
 #include <string.h>
 
+#include <vector>
+
 #include "../../include/gjd.h"
 
 namespace {
@@ -125,7 +127,6 @@ int gjd_parse_headers(const uint8_t* d, size_t len, GjdParsed* o) {
                 if (sp[0] != 0 || sp[1] != 63 || sp[2] != 0) return GJD_E_UNSUPPORTED;
                 for (uint32_t c = 0; c < 3; c++)
                     if (!o->quant_seen[o->qsel[c]]) return GJD_E_FORMAT;
-                if (o->restart_interval != 0) return GJD_E_UNSUPPORTED;   /* DRI/RSTn: SURVEY §8f-1 */
                 o->scan_begin = d + pos + seg;
                 return GJD_OK;
             }
@@ -136,8 +137,13 @@ int gjd_parse_headers(const uint8_t* d, size_t len, GjdParsed* o) {
     }
 }
 
-long gjd_unstuff(const uint8_t* p, const uint8_t* end, uint8_t* dst) {
+long gjd_unstuff_segments(const uint8_t* p, const uint8_t* end, uint8_t* dst, std::vector<uint32_t>* seg_off,
+                          std::vector<uint32_t>* seg_len) {
     uint8_t* o = dst;
+    uint8_t* seg = dst;          /* start of the current restart interval */
+    uint32_t expect = 0;         /* RSTn numbers cycle 0..7 (T.81 E.1.4) */
+    if (seg_off) seg_off->clear();
+    if (seg_len) seg_len->clear();
     for (;;) {
         if (p >= end) return GJD_E_FORMAT;
         const uint8_t* q = (const uint8_t*)memchr(p, 0xFF, (size_t)(end - p));
@@ -150,15 +156,28 @@ long gjd_unstuff(const uint8_t* p, const uint8_t* end, uint8_t* dst) {
             *o++ = 0xFF;
             p = q + 2;
         } else if (m == 0xD9) {
+            if (seg_off) seg_off->push_back((uint32_t)(seg - dst));
+            if (seg_len) seg_len->push_back((uint32_t)(o - seg));
             return (long)(o - dst);
         } else if (m == 0xFF) {
             p = q + 1;   /* fill byte */
         } else if (m >= 0xD0 && m <= 0xD7) {
-            return GJD_E_UNSUPPORTED;
+            if (!seg_off) return GJD_E_UNSUPPORTED;          /* caller did not announce a restart interval */
+            if ((uint32_t)(m - 0xD0) != expect) return GJD_E_FORMAT;
+            expect = (expect + 1u) & 7u;
+            seg_off->push_back((uint32_t)(seg - dst));
+            if (seg_len) seg_len->push_back((uint32_t)(o - seg));
+            while ((size_t)(o - dst) & 3u) *o++ = 0;         /* the next interval starts on a 4-byte boundary */
+            seg = o;
+            p = q + 2;
         } else {
             return GJD_E_FORMAT;
         }
     }
+}
+
+long gjd_unstuff(const uint8_t* p, const uint8_t* end, uint8_t* dst) {
+    return gjd_unstuff_segments(p, end, dst, nullptr, nullptr);
 }
 
 /* ---- multi-GPU sharding: greedy LPT over padded pixel counts ------------------------ */

@@ -7,6 +7,8 @@
 
 #include <stddef.h>
 #include <stdint.h>
+#include <vector>
+
 #include "gjd_types.h"
 
 struct GjdParsed {
@@ -26,7 +28,7 @@ struct GjdParsed {
  * A superset of what the reference parser accepts: APPn/COM/unknown segments are
  * skipped by length, DQT/DHT may hold several tables in any order, selectors in SOF0/SOS are
  * honoured; everything outside the 8-bit 4:4:4 baseline single-scan contract is rejected with
- * GJD_E_UNSUPPORTED instead of being mis-decoded. */
+ * GJD_E_UNSUPPORTED instead of being mis-decoded.  DRI is accepted: restart_interval = MCUs per interval. */
 int gjd_parse_headers(const uint8_t* jpg, size_t len, GjdParsed* out);
 
 /* Copy the entropy-coded segment [src, end) to dst, removing the stuffed 0x00 after every 0xFF and
@@ -34,5 +36,13 @@ int gjd_parse_headers(const uint8_t* jpg, size_t len, GjdParsed* out);
  * twin cuda-decoder/src/parser.cu:450-462).  dst needs (end - src) bytes.  Returns the unstuffed
  * length, or a negative gjd_status (truncated scan, RSTn, any other marker inside the scan). */
 long gjd_unstuff(const uint8_t* src, const uint8_t* end, uint8_t* dst);
+
+/* The same with restart markers (DRI/RSTn, T.81 B.2.4.4 + E.1.4; outside the reference's parser, which
+ * keeps FF Dn as data, cpp-decoder/src/parser.cpp:84-96): every RSTn ends a restart interval, is checked
+ * against the 0..7 cycle and removed; the next interval is written at the next 4-byte boundary of dst.
+ * seg_off/seg_len receive the byte offset and length of every interval (one entry for a scan without
+ * restarts).  dst needs (end - src) + (end - src) / 2 bytes.  Returns the bytes used in dst. */
+long gjd_unstuff_segments(const uint8_t* src, const uint8_t* end, uint8_t* dst, std::vector<uint32_t>* seg_off,
+                          std::vector<uint32_t>* seg_len);
 
 #endif

@@ -4,7 +4,8 @@
  * HBM layout of one resident batch (all offsets 256-byte aligned, one arena per kind):
  *
  *   scan   u8    unstuffed entropy-coded bytes of every image, each image starting on a
- *                128-byte boundary and followed by >= 16 zero bytes.
+ *                128-byte boundary and followed by >= 16 zero bytes; restart intervals of an image
+ *                follow each other, each starting on a 4-byte boundary (RSTn markers removed).
  *   sinfo  u32x2 one state per subsequence (2^sub_log2 bits of one image's scan), padded per
  *                image to a multiple of GJD_SEQ_SUBS ("sequence" = the subsequences one thread
  *                block synchronises): {p, (n << 8) | pos}.
@@ -77,16 +78,28 @@ typedef struct GjdQuantSet {
     int32_t q[3][64];
 } GjdQuantSet;
 
-/* Per-image device descriptor. */
+/* One independently decodable piece of entropy-coded data: the whole scan of an image without restart
+ * markers, or one restart interval (the bytes between two RSTn markers; JPEG T.81 E.1.4: the decoder
+ * state — component, zigzag index, DC predictors — is reset at every restart).  The entropy kernels
+ * (k_huff_sync, k_huff_fix, k_seq_scan, k_huff_write) work on segments; sequences belong to a segment. */
+typedef struct GjdSegment {
+    uint64_t scan_off;      /* byte offset of the unstuffed bytes in the scan arena (4-byte aligned) */
+    uint32_t scan_bits;     /* unstuffed length in bits (a trailing partial byte of 1-padding included) */
+    uint32_t sub_count;     /* subsequences                                                    */
+    uint32_t seq_first;     /* global index of the segment's first sequence                    */
+    uint32_t seq_count;
+    uint32_t img;           /* owning image                                                    */
+    uint32_t blk_first;     /* first 8x8 block of the segment, counted from the image's first block (3 * first MCU) */
+    uint32_t blk_count;     /* 3 * MCUs in the segment                                         */
+    uint16_t lut_id;        /* index into the GjdLutSet array                                  */
+    uint16_t pad0;
+} GjdSegment;
+
+/* Per-image device descriptor (transform side). */
 typedef struct GjdImage {
-    uint64_t scan_off;      /* byte offset of the unstuffed scan in the scan arena            */
     uint64_t out_off;       /* byte offset in the rgb arena, or a raw device address           */
     uint64_t plane_stride;  /* bytes between planes                                            */
     uint32_t row_pitch;     /* bytes between rows                                              */
-    uint32_t scan_bits;     /* unstuffed scan length in bits                                   */
-    uint32_t sub_count;     /* subsequences                                                    */
-    uint32_t seq_first;     /* global index of the image's first sequence                      */
-    uint32_t seq_count;
     uint32_t tile_first;    /* global index of the image's first coefficient tile              */
     uint32_t tile_count;
     uint32_t tb_first;      /* global index of the image's first transform block               */
@@ -94,12 +107,12 @@ typedef struct GjdImage {
     uint32_t mcu_count;
     uint32_t mcus_x;
     uint32_t width, height;
-    uint16_t lut_id;        /* index into the GjdLutSet array                                  */
+    uint32_t restart_interval; /* MCUs per restart interval (DC predictors reset), 0 = none     */
+    uint32_t seg_first;     /* global index of the image's first segment                       */
+    uint32_t seg_count;
     uint16_t quant_id;      /* index into the GjdQuantSet array                                */
-    uint8_t  tabsel[8];     /* [c] = LUT slot of component c's DC table, [4+c] = AC table      */
-    uint8_t  qsel[4];       /* [c] = quant table (0/1) of component c                          */
+    uint16_t pad0;
     uint32_t out_is_ptr;    /* out_off is an absolute device address (caller-owned buffer)     */
-    uint32_t pad0, pad1, pad2;
 } GjdImage;
 
 /* Device-written status bits per image. */

@@ -121,6 +121,20 @@ def golden():
 
 
 @pytest.fixture(scope="session")
+def rst_golden():
+    out = {}
+    for f in sorted(glob.glob(os.path.join(GOLDEN, "rst", "*.jpg"))):
+        with open(f, "rb") as fh:
+            out[os.path.basename(f)[:-4]] = fh.read()
+    return out
+
+
+@pytest.fixture(scope="session")
+def ref_outputs_rst():
+    return np.load(os.path.join(GOLDEN, "ref_outputs_rst.npz"))
+
+
+@pytest.fixture(scope="session")
 def ref_outputs():
     return np.load(os.path.join(GOLDEN, "ref_outputs.npz"))
 

@@ -55,14 +55,21 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     if (rc) return rc;
     if (width) *width = p.width;
     if (height) *height = p.height;
-    std::vector<uint8_t> scanbuf((size_t)(p.file_end - p.scan_begin) + 64, 0);
-    long ulen = gjd_unstuff(p.scan_begin, p.file_end, scanbuf.data());
+    const size_t raw = (size_t)(p.file_end - p.scan_begin);
+    std::vector<uint8_t> scanbuf(raw + raw / 2 + 128, 0);
+    std::vector<uint32_t> seg_off, seg_len;
+    long ulen = gjd_unstuff_segments(p.scan_begin, p.file_end, scanbuf.data(), &seg_off, &seg_len);
     if (ulen < 0) return (int)ulen;
     memset(scanbuf.data() + ulen, 0, 16);
     /* word-aligned copy */
     std::vector<uint32_t> scanw((scanbuf.size() + 3) / 4 + 4, 0);
     memcpy(scanw.data(), scanbuf.data(), scanbuf.size());
-    const uint32_t* scan = scanw.data();
+    const uint32_t W = (uint32_t)p.width, H = (uint32_t)p.height;
+    const uint32_t mcus_x = (W + 7) / 8, mcu_count = mcus_x * ((H + 7) / 8);
+    const uint32_t tile_count = (mcu_count + 31) / 32;
+    const uint32_t ri = p.restart_interval;
+    if (!ri && seg_off.size() != 1) return GJD_E_UNSUPPORTED;          /* RSTn without DRI */
+    if (ri && seg_off.size() != (mcu_count + ri - 1) / ri) return GJD_E_CORRUPT;
 
     /* k_build_luts */
     GjdLutSet* lut = (GjdLutSet*)calloc(1, sizeof(GjdLutSet));
@@ -83,14 +90,20 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     GjdLutMem hlut;
     hlut.set = lut;
     hlut.badcode = &badcode;
-    const uint32_t scan_bits = (uint32_t)ulen * 8u;
+    uint32_t max_rounds = 0, fix_decodes = 0, nosync = 0, status = 0, sub_total = 0, seq_total = 0;
+    std::vector<int16_t> coef((size_t)tile_count * 96 * 64, (int16_t)0x7e7e);   /* stale garbage where nothing is written */
+    std::vector<uint32_t> meta((size_t)tile_count * 96, 0);
+    std::vector<uint8_t> written((size_t)tile_count * 96, 0);
+    /* the entropy kernels run per segment (restart interval); one segment without restarts */
+    for (size_t sgi = 0; sgi < seg_off.size(); sgi++) {
+    const uint32_t* scan = scanw.data() + seg_off[sgi] / 4;
+    const uint32_t scan_bits = seg_len[sgi] * 8u;
+    const uint32_t blk0 = 3u * ri * (uint32_t)sgi;
+    const uint32_t blk_count = 3u * (ri ? std::min(ri, mcu_count - ri * (uint32_t)sgi) : mcu_count);
     const uint32_t sub_count = std::max<uint32_t>(1u, (uint32_t)(((uint64_t)scan_bits + S - 1) / S));
     const uint32_t seq_count = (sub_count + GJD_SEQ_SUBS - 1) / GJD_SEQ_SUBS;
-    const uint32_t W = (uint32_t)p.width, H = (uint32_t)p.height;
-    const uint32_t mcus_x = (W + 7) / 8, mcu_count = mcus_x * ((H + 7) / 8);
-    const uint32_t tile_count = (mcu_count + 31) / 32;
+    sub_total += sub_count; seq_total += seq_count;
     std::vector<uint32_t> sp((size_t)seq_count * GJD_SEQ_SUBS, 0), sn((size_t)seq_count * GJD_SEQ_SUBS, 0);
-    uint32_t bad = 0, max_rounds = 0, fix_decodes = 0, nosync = 0, status = 0;
 
     /* k_huff_sync: one "block" per sequence */
     std::vector<uint32_t> seq_in_p(seq_count, 0), seq_in_pos(seq_count, 0);
@@ -175,11 +188,8 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
         for (uint32_t t = 0; t < cnt; t++) carry += sn[(size_t)g * GJD_SEQ_SUBS + t] >> 8;
     }
     badcode = 0;   /* only the write pass reports unassigned codes */
-    if (carry != 192u * mcu_count) status |= GJD_DEV_BADCOUNT;
+    if (carry != 64u * blk_count) status |= GJD_DEV_BADCOUNT;
     /* k_huff_write */
-    std::vector<int16_t> coef((size_t)tile_count * 96 * 64, (int16_t)0x7e7e);   /* stale garbage where nothing is written */
-    std::vector<uint32_t> meta((size_t)tile_count * 96, 0);
-    std::vector<uint8_t> written((size_t)tile_count * 96, 0);
     for (uint32_t g = 0; g < seq_count; g++) {
         uint32_t excl = 0;
         for (uint32_t tid = 0; tid < GJD_SEQ_SUBS; tid++) {
@@ -191,16 +201,17 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
             uint32_t tbad = 0;
             WriteSink sink;
             memset(sink.stage, 0, sizeof(sink.stage));
-            sink.coef = coef.data(); sink.meta = meta.data(); sink.written = written.data();
+            sink.coef = coef.data() + (size_t)blk0 * 64; sink.meta = meta.data() + blk0; sink.written = written.data() + blk0;
             uint32_t idx0 = seq_base[g] + excl;
             if (idx0 % 192u != st.pos && st.p < scan_bits) tbad |= GJD_DEV_BADSTATE;
             uint32_t end = std::min((sub + 1) << sub_log2, scan_bits);
-            gjd_write_span(scan, hlut, end, scan_bits, st, idx0, 3u * mcu_count, true, sink, tbad);
+            gjd_write_span(scan, hlut, end, scan_bits, st, idx0, blk_count, true, sink, tbad);
             for (int k = 0; k < 64; k++) if (sink.stage[k]) tbad |= GJD_DEV_BADSTATE;   /* staging must be left clean */
             status |= tbad;
             excl += sn[a] >> 8;
         }
     }
+    }   /* segments */
     for (uint32_t bk = 0; bk < 3u * mcu_count; bk++) if (written[bk] != 1) status |= GJD_DEV_BADCOUNT;
     if (badcode) status |= GJD_DEV_BADCODE;
     /* k_dc_tilebase + k_transform */
@@ -210,6 +221,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     int pred[3] = {0, 0, 0};
     for (uint32_t mcu = 0; mcu < mcu_count; mcu++) {
         int samples[3][64];
+        if (ri && mcu % ri == 0) pred[0] = pred[1] = pred[2] = 0;   /* T.81 E.1.4 */
         for (int c = 0; c < 3; c++) {
             size_t bk = (size_t)mcu * 3 + c;
             uint32_t m = meta[bk];
@@ -243,7 +255,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     }
     if (stats) {
         stats[0] = max_rounds; stats[1] = fix_decodes; stats[2] = status; stats[3] = nosync;
-        stats[4] = sub_count; stats[5] = seq_count;
+        stats[4] = sub_total; stats[5] = seq_total;
     }
     free(lut);
     return status ? GJD_E_CORRUPT : GJD_OK;

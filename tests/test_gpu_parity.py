@@ -196,3 +196,47 @@ def test_subsequence_lengths(golden, ref_outputs, oracle, sub_log2, monkeypatch)
             o, st = d.decode([f])
             rc, _, rgb, _, W, H = oracle.decode(f, want_coef=False)
             assert st == [0] and np.array_equal(o[0], rgb)
+
+
+def test_restart_intervals_bit_exact(decoder, golden, ref_outputs, rst_golden, ref_outputs_rst):
+    """DRI/RSTn (outside the reference's parser): the restart files, mixed into one batch
+    with ordinary files, must give exactly what the unmodified reference gives for the twins encoded
+    without restarts — coefficients and pixels."""
+    rn = sorted(rst_golden)
+    assert len(rn) >= 7
+    for n in rn:
+        coef, w, h = decoder.decode_coeffs(rst_golden[n])
+        assert np.array_equal(coef, ref_outputs_rst[n + "/coef"]), n
+    plain = NAMES[:5]
+    files, want = [], []
+    for i, n in enumerate(rn):            # interleave restart and ordinary images
+        files.append(rst_golden[n]); want.append(ref_outputs_rst[n + "/rgb"])
+        p = plain[i % len(plain)]
+        files.append(golden[p]); want.append(ref_outputs[p + "/rgb"])
+    outs, st = decoder.decode(files)
+    assert st == [0] * len(files)
+    for o, w_ in zip(outs, want):
+        assert np.array_equal(o, w_)
+
+
+def test_restart_stream_errors(decoder, golden, rst_golden):
+    good = golden["images/3_120x120"]
+    data = bytearray(rst_golden["r23_401x363_q75_o0_rst7B"])
+    i = data.index(b"\xff\xd1")
+    wrong_number = bytes(data[:i + 1]) + b"\xd3" + bytes(data[i + 2:])
+    j = data.index(b"\xff\xd2")
+    missing = bytes(data[:j]) + bytes(data[j + 2:])
+    outs, st = decoder.decode([good, wrong_number, missing, good])
+    assert st[0] == 0 and st[3] == 0 and st[1] == -4 and st[2] in (-4, -6)
+
+
+@pytest.mark.parametrize("sub_log2", [8, 10])
+def test_restart_intervals_subsequence_lengths(rst_golden, ref_outputs_rst, sub_log2, monkeypatch):
+    import gjd
+    monkeypatch.setenv("GJD_SUB_LOG2", str(sub_log2))
+    with gjd.Decoder(0) as d:
+        rn = sorted(rst_golden)
+        outs, st = d.decode([rst_golden[n] for n in rn])
+        assert st == [0] * len(rn)
+        for n, o in zip(rn, outs):
+            assert np.array_equal(o, ref_outputs_rst[n + "/rgb"]), n

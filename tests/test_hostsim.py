@@ -67,7 +67,7 @@ def test_parser_contract(hostsim, golden):
     assert hostsim.parse(enc("-sample", "2x2"))[0] == -5          # subsampled
     assert hostsim.parse(enc("-sample", "1x1", "-progressive"))[0] == -5
     assert hostsim.parse(enc("-grayscale"))[0] == -5
-    assert hostsim.parse(enc("-sample", "1x1", "-restart", "1"))[0] == -5   # DRI: SURVEY §8f-1
+    assert hostsim.parse(enc("-sample", "1x1", "-restart", "1"))[0] == 0    # DRI/RSTn accepted
     assert hostsim.parse(enc("-sample", "1x1", "-arithmetic"))[0] == -5
     assert hostsim.parse(ok[:100])[0] == -4                       # truncated header
     assert hostsim.parse(b"not a jpeg at all")[0] == -4
@@ -120,3 +120,25 @@ def test_two_level_lut_matches_canonical_tables(hostsim, golden):
         assert out[1] == 0, (name, out)
         long_codes += int(out[2])
     assert long_codes > 0
+
+
+def test_restart_intervals_match_reference_on_twin(hostsim, rst_golden, ref_outputs_rst):
+    """DRI/RSTn files (outside the reference's parser): coefficients and pixels must equal what the
+    unmodified reference gives for the same image encoded without restarts (tools/make_golden_rst.py)."""
+    assert len(rst_golden) >= 7
+    for name, data in sorted(rst_golden.items()):
+        for sub_log2 in (0, 8):
+            rc, coef, rgb, stats = hostsim.decode(data, sub_log2)
+            assert rc == 0 and stats[2] == 0, (name, rc, stats)
+            assert np.array_equal(coef, ref_outputs_rst[name + "/coef"]), name
+            assert np.array_equal(rgb, ref_outputs_rst[name + "/rgb"]), name
+
+
+def test_restart_stream_errors(hostsim, rst_golden):
+    data = bytearray(rst_golden["r23_401x363_q75_o0_rst7B"])
+    i = data.index(b"\xff\xd1")
+    bad = bytes(data[:i + 1]) + b"\xd3" + bytes(data[i + 2:])      # RST1 -> RST3: out of sequence
+    assert hostsim.decode(bad)[0] == -4
+    j = data.index(b"\xff\xd2")
+    cut = bytes(data[:j]) + bytes(data[j + 2:])                    # one marker removed: interval count is off
+    assert hostsim.decode(cut)[0] in (-4, -6)
