@@ -663,10 +663,14 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     }
     if (ev) GJD_CK(cudaEventRecord(ev->e[2], s));
     k_seq_scan<<<b.n_seg, 256, 0, s>>>(b); n++;
-    static bool write_attr = false;   /* opt in to > 48 KB of dynamic shared memory, once per process */
-    if (!write_attr) {
-        GJD_CK(cudaFuncSetAttribute(k_huff_write, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GJD_WRITE_SMEM));
-        write_attr = true;
+    {   /* opt in to > 48 KB of dynamic shared memory, once per device (function attributes are per context) */
+        static bool write_attr[64] = {false};
+        int dev = 0;
+        GJD_CK(cudaGetDevice(&dev));
+        if (dev < 0 || dev >= 64 || !write_attr[dev]) {
+            GJD_CK(cudaFuncSetAttribute(k_huff_write, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GJD_WRITE_SMEM));
+            if (dev >= 0 && dev < 64) write_attr[dev] = true;
+        }
     }
     k_huff_write<<<b.n_seq, GJD_WRITE_THREADS, GJD_WRITE_SMEM, s>>>(b); n++;
     k_dc_tilebase<<<b.n_img, 256, 0, s>>>(b); n++;

@@ -30,7 +30,7 @@ typedef enum gjd_status {
     GJD_E_NOMEM       = -3,  /* host or device allocation failed                            */
     GJD_E_FORMAT      = -4,  /* not a JPEG, truncated, or a marker segment is malformed     */
     GJD_E_UNSUPPORTED = -5,  /* valid JPEG outside the contract: progressive, arithmetic,
-                                12-bit, subsampled, != 3 components, multi-scan, DRI/RSTn    */
+                                12-bit, subsampled, != 3 components, multi-scan               */
     GJD_E_CORRUPT     = -6,  /* entropy-coded data is inconsistent (bad code / wrong count) */
     GJD_E_NODEVICE    = -7,  /* no usable CUDA device: the product has no CPU fallback      */
     GJD_E_IO          = -8   /* file could not be read / written (writers only)             */
@@ -70,6 +70,9 @@ int  gjd_peek(const uint8_t* jpg, size_t len, int32_t* width, int32_t* height);
 
 /* Decode n images end to end: marker parse + byte-unstuffing on the host, H2D, entropy decode,
  * dezigzag+dequant+IDCT+colour on the GPU, D2H into items[i].rgb (skipped for rgb_on_device).
+ * Restart markers (DRI/RSTn) are decoded (every restart interval is an independent segment for the
+ * entropy kernels; DC predictors restart) — a superset of the reference's parser, which keeps FF Dn as
+ * scan data (cpp-decoder/src/parser.cpp:84-96).
  * Synchronous on return.  Returns GJD_OK if the call itself worked; per-image failures are reported
  * in items[i].status and do not stop the batch.
  * Replaces extract()+allocate()+batchDecodeKernel<<<n,256>>>+D2H+clean()

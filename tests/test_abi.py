@@ -57,3 +57,20 @@ def test_array_writer_format(golden, ground_truth, tmp_path):
         p = str(tmp_path / (stem + ".array"))
         gjd.write_array(p, ground_truth[stem])
         assert hashlib.sha256(open(p, "rb").read()).hexdigest() == want
+
+
+def test_throughput_driver_without_gpu_fails_loudly():
+    """No CPU fallback: on a machine without a CUDA device the benchmark driver reports it and exits non-zero."""
+    import subprocess
+    exe = os.path.join(ROOT, "gjd-decoder", "gjd_bench")
+    if not os.path.exists(exe):
+        import pytest
+        pytest.skip("gjd_bench not built")
+    assert subprocess.run([exe], stderr=subprocess.PIPE).returncode == 1
+    import gjd
+    ctx = C.c_void_p()
+    if gjd.lib().gjd_create(C.byref(ctx), 0, 0) == 0:      # a GPU is present: nothing to check here
+        gjd.lib().gjd_destroy(ctx)
+        return
+    p = subprocess.run([exe, os.path.join(ROOT, "tests", "golden", "images")], stderr=subprocess.PIPE, text=True)
+    assert p.returncode == 3 and "CUDA device" in p.stderr

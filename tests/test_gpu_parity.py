@@ -240,3 +240,15 @@ def test_restart_intervals_subsequence_lengths(rst_golden, ref_outputs_rst, sub_
         assert st == [0] * len(rn)
         for n, o in zip(rn, outs):
             assert np.array_equal(o, ref_outputs_rst[n + "/rgb"]), n
+
+
+def test_throughput_driver_cli():
+    """gjd-decoder/gjd_bench = the reference's benchmark_thoughput driver over the C ABI: every fixture
+    decodes, in batches smaller than the directory, resident and end-to-end."""
+    exe = os.path.join(ROOT, "gjd-decoder", "gjd_bench")
+    assert os.path.exists(exe), "build it with make -C gpu-jpeg-decoder_b200"
+    out = subprocess.run([exe, os.path.join(GOLDEN, "images"), "--batch", "4", "--iters", "2", "--e2e"],
+                         check=True, stdout=subprocess.PIPE, text=True).stdout
+    r = json.loads(out.strip().splitlines()[-1])
+    assert r["images"] == 7 and r["failed"] == 0 and r["rejected"] == 0
+    assert r["MPixel_per_s"] > 0 and r["e2e_MPixel_per_s"] > 0 and r["compressed_MB_per_s"] > 0
