@@ -106,23 +106,28 @@ GJD_HD uint32_t gjd_bswap32(uint32_t x) {
 #endif
 }
 
-/* Two cached big-endian words of the scan; wi = index of w0. */
+/* Two cached big-endian words of the scan (wi = index of w0) plus the word after them, still in memory
+ * byte order: it is loaded one refill ahead of its use so that the load latency hides behind the symbols
+ * decoded in between (the byte swap waits for the data, so it is deferred to the next refill). */
 struct GjdWin {
-    uint32_t wi, w0, w1;
+    uint32_t wi, w0, w1, w2raw;
 };
 
 GJD_HD void gjd_win_init(GjdWin& c, const uint32_t* scan, uint32_t p) {
     c.wi = p >> 5;
     c.w0 = gjd_bswap32(scan[c.wi]);
     c.w1 = gjd_bswap32(scan[c.wi + 1]);
+    c.w2raw = scan[c.wi + 2];
 }
 
-/* 32 bits of the scan starting at bit p (MSB first).  p may advance by at most 32 bits per call. */
+/* 32 bits of the scan starting at bit p (MSB first).  p may advance by at most 32 bits per call.
+ * Reads up to 12 bytes past the word that holds p (the scan arena is padded). */
 GJD_HD uint32_t gjd_peek32(GjdWin& c, const uint32_t* scan, uint32_t p) {
     uint32_t wi = p >> 5;
     if (wi != c.wi) {
         c.w0 = c.w1;
-        c.w1 = gjd_bswap32(scan[wi + 1]);
+        c.w1 = gjd_bswap32(c.w2raw);
+        c.w2raw = scan[wi + 2];
         c.wi = wi;
     }
 #ifdef __CUDA_ARCH__
@@ -279,7 +284,7 @@ GJD_HD void gjd_write_span(const uint32_t* scan, const Lut& lut, uint32_t end_bi
                            GjdState s, uint32_t idx0, uint32_t nblocks, bool enable, Sink& sink, uint32_t& bad) {
     uint32_t run = (enable && s.p < end_bits) ? 1u : 0u;
     GjdWin win;
-    win.wi = 0; win.w0 = 0; win.w1 = 0;
+    win.wi = 0; win.w0 = 0; win.w1 = 0; win.w2raw = 0;
     if (run) gjd_win_init(win, scan, s.p);
     uint32_t p = s.p, z = s.pos & 63u, tb = gjd_ring_of_pos(s.pos);
     uint32_t blk = (idx0 + 63u) >> 6;
