@@ -143,6 +143,7 @@ struct ItemGeom {
     int32_t width = 0, height = 0;
     size_t out_bytes = 0;      /* bytes of the image's output region */
     size_t pitch = 0, pstride = 0;
+    int32_t layout = GJD_LAYOUT_PLANAR;
 };
 
 }  // namespace
@@ -296,6 +297,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         d.tb_count = (d.tile_count + GJD_TB_TILES - 1) / GJD_TB_TILES;
         d.row_pitch = (uint32_t)g.pitch;
         d.plane_stride = g.pstride;
+        d.layout = (uint16_t)g.layout;
         if (items[i].rgb_on_device && items[i].rgb && !own_output) {
             d.out_is_ptr = 1;
             d.out_off = (uint64_t)(uintptr_t)items[i].rgb;
@@ -379,6 +381,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     memset(&v, 0, sizeof(v));
     v.n_img = n_img;
     v.n_seg = (uint32_t)b->segs.size();
+    for (const GjdImage& im : b->imgs) v.any_interleaved |= im.layout == GJD_LAYOUT_INTERLEAVED;
     v.n_seq = seq;
     v.sub_log2 = sub_log2;
     v.n_tile = tile;
@@ -497,6 +500,15 @@ void parse_all(gjd_ctx* ctx, const gjd_item* items, int32_t n, std::vector<GjdPa
         g.width = parsed[i].width;
         g.height = parsed[i].height;
         if (rc) { g.status = rc; return; }
+        g.layout = items[i].layout;
+        if (g.layout == GJD_LAYOUT_INTERLEAVED) {
+            g.pitch = items[i].row_pitch ? items[i].row_pitch : 3 * (size_t)g.width;
+            g.pstride = 0;
+            if (g.pitch < 3 * (size_t)g.width || g.pitch > 0xffffffffull) { g.status = GJD_E_ARG; return; }
+            g.out_bytes = g.pitch * (size_t)g.height;
+            return;
+        }
+        if (g.layout != GJD_LAYOUT_PLANAR) { g.status = GJD_E_ARG; return; }
         g.pitch = items[i].row_pitch ? items[i].row_pitch : (size_t)g.width;
         g.pstride = items[i].plane_stride ? items[i].plane_stride : g.pitch * (size_t)g.height;
         if (g.pitch < (size_t)g.width || g.pstride < g.pitch * (size_t)g.height || g.pitch > 0xffffffffull) {
@@ -728,9 +740,14 @@ int gjd_batch_fetch(gjd_ctx* ctx, gjd_batch* b, int32_t i, uint8_t* rgb_host) {
     if (k < 0) return b->geom[i].status ? b->geom[i].status : GJD_E_ARG;
     const GjdImage& d = b->imgs[k];
     const uint8_t* src = d.out_is_ptr ? (const uint8_t*)(uintptr_t)d.out_off : (const uint8_t*)b->d_rgb.p + d.out_off;
-    for (int c = 0; c < 3; c++)
-        GJD_TRY(cudaMemcpy2DAsync(rgb_host + (size_t)c * d.width * d.height, d.width, src + (size_t)c * d.plane_stride,
-                                  d.row_pitch, d.width, d.height, cudaMemcpyDeviceToHost, b->stream));
+    if (d.layout == GJD_LAYOUT_INTERLEAVED) {
+        GJD_TRY(cudaMemcpy2DAsync(rgb_host, 3 * (size_t)d.width, src, d.row_pitch, 3 * (size_t)d.width, d.height,
+                                  cudaMemcpyDeviceToHost, b->stream));
+    } else {
+        for (int c = 0; c < 3; c++)
+            GJD_TRY(cudaMemcpy2DAsync(rgb_host + (size_t)c * d.width * d.height, d.width, src + (size_t)c * d.plane_stride,
+                                      d.row_pitch, d.width, d.height, cudaMemcpyDeviceToHost, b->stream));
+    }
     GJD_TRY(cudaStreamSynchronize(b->stream));
     return GJD_OK;
 }

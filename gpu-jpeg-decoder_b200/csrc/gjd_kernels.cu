@@ -18,6 +18,7 @@
 #include "gjd_kernels.h"
 
 #include "gjd_devfn.cuh"
+#include "../../include/gjd.h"
 
 #define GJD_SYNC_THREADS 256
 static_assert(GJD_SYNC_THREADS == GJD_SEQ_SUBS, "one thread per subsequence of a sequence");
@@ -471,7 +472,7 @@ __device__ __forceinline__ void gjd_block_to_samples(const uint32_t* w, const in
  * EXPORT = true is the coefficient test hook: blocks are written out in the reference layout
  * mcu*192 + comp*64 + k with the absolute DC in slot 0 instead of being transformed.
  */
-template <bool EXPORT, int MINB>
+template <bool EXPORT, int MINB, bool ILV>
 __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDevBatch b, int16_t* __restrict__ coef_out) {
     __shared__ int sq[3][64];
     __shared__ uint4 smp[2][3][8][32];
@@ -488,7 +489,9 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
     const uint32_t W = d.width, H = d.height;
     uint8_t* out = d.out_is_ptr ? reinterpret_cast<uint8_t*>(d.out_off) : b.rgb + d.out_off;
     const size_t pitch = d.row_pitch, pstride = d.plane_stride;
-    const bool aligned = (((size_t)out | pitch | pstride) & 7u) == 0;
+    /* ILV = false: the batch holds planar images only (the common case keeps the shorter kernel) */
+    const bool interleaved = ILV && d.layout == GJD_LAYOUT_INTERLEAVED;
+    const bool aligned = (((size_t)out | pitch | (interleaved ? 0 : pstride)) & 7u) == 0;
     const int* q = sq[c];
 
 #pragma unroll 1
@@ -575,6 +578,31 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
                     const uint64_t Ge = (uint64_t)gjd_color_g_exact((int)ys[x] - 256, (int)bs[x] - 256, (int)rs[x] - 256);
                     g8 = (g8 & ~(0xffull << (8u * x))) | (Ge << (8u * x));
                 }
+            }
+            if (interleaved) {   /* block-uniform: R,G,B,R,G,B,... 24 bytes per lane, 768 contiguous bytes per warp */
+                uint8_t* px = out + (size_t)(y0 + r) * pitch + (size_t)x0 * 3u;
+                const uint32_t g0 = (uint32_t)g8, g1 = (uint32_t)(g8 >> 32);
+                if (fast) {
+                    /* word j of the 24 bytes: __byte_perm picks from {a: bytes 0-3, b: bytes 4-7} */
+                    const uint32_t w0 = __byte_perm(__byte_perm(pr[0], g0, 0x1040), pb[0], 0x3410);   /* R0 G0 B0 R1 */
+                    const uint32_t w1 = __byte_perm(__byte_perm(g0, pb[0], 0x2051), pr[0], 0x3610);   /* G1 B1 R2 G2 */
+                    const uint32_t w2 = __byte_perm(__byte_perm(pb[0], pr[0], 0x3072), g0, 0x3710);   /* B2 R3 G3 B3 */
+                    const uint32_t w3 = __byte_perm(__byte_perm(pr[1], g1, 0x1040), pb[1], 0x3410);
+                    const uint32_t w4 = __byte_perm(__byte_perm(g1, pb[1], 0x2051), pr[1], 0x3610);
+                    const uint32_t w5 = __byte_perm(__byte_perm(pb[1], pr[1], 0x3072), g1, 0x3710);
+                    __stcs(reinterpret_cast<uint2*>(px), make_uint2(w0, w1));
+                    __stcs(reinterpret_cast<uint2*>(px + 8), make_uint2(w2, w3));
+                    __stcs(reinterpret_cast<uint2*>(px + 16), make_uint2(w4, w5));
+                } else {
+                    const uint64_t r8 = ((uint64_t)pr[1] << 32) | pr[0], b8 = ((uint64_t)pb[1] << 32) | pb[0];
+#pragma unroll 1
+                    for (uint32_t x = 0; x < 8u && x0 + x < W; x++) {
+                        px[3u * x] = (uint8_t)(r8 >> (8u * x));
+                        px[3u * x + 1u] = (uint8_t)(g8 >> (8u * x));
+                        px[3u * x + 2u] = (uint8_t)(b8 >> (8u * x));
+                    }
+                }
+                continue;
             }
             uint8_t* row = out + (size_t)(y0 + r) * pitch + x0;
             if (fast) {
@@ -675,8 +703,9 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     k_huff_write<<<b.n_seq, GJD_WRITE_THREADS, GJD_WRITE_SMEM, s>>>(b); n++;
     k_dc_tilebase<<<b.n_img, 256, 0, s>>>(b); n++;
     if (ev) GJD_CK(cudaEventRecord(ev->e[3], s));
-    if (transform_variant == 1) k_transform<false, 6><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
-    else k_transform<false, 8><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
+    if (b.any_interleaved) k_transform<false, 8, true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
+    else if (transform_variant == 1) k_transform<false, 6, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
+    else k_transform<false, 8, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
     n++;
     if (ev) GJD_CK(cudaEventRecord(ev->e[4], s));
     if (launches) *launches = n;
@@ -685,7 +714,7 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
 
 cudaError_t gjd_launch_export_coefs(const GjdDevBatch& b, int16_t* out, cudaStream_t s) {
     /* single-image batch: out is indexed by the image's own MCU numbers */
-    k_transform<true, 6><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, out);
+    k_transform<true, 6, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, out);
     return cudaGetLastError();
 }
 

@@ -111,7 +111,7 @@ typedef struct GjdImage {
     uint32_t seg_first;     /* global index of the image's first segment                       */
     uint32_t seg_count;
     uint16_t quant_id;      /* index into the GjdQuantSet array                                */
-    uint16_t pad0;
+    uint16_t layout;        /* GJD_LAYOUT_PLANAR / GJD_LAYOUT_INTERLEAVED (include/gjd.h)        */
     uint32_t out_is_ptr;    /* out_off is an absolute device address (caller-owned buffer)     */
 } GjdImage;
 

@@ -14,6 +14,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "build", "libgjd.so")
 
+PLANAR, INTERLEAVED = 0, 1
 OK, E_ARG, E_CUDA, E_NOMEM, E_FORMAT, E_UNSUPPORTED, E_CORRUPT, E_NODEVICE, E_IO = 0, -1, -2, -3, -4, -5, -6, -7, -8
 
 
@@ -28,6 +29,8 @@ class Item(C.Structure):
         ("width", C.c_int32),
         ("height", C.c_int32),
         ("status", C.c_int32),
+        ("layout", C.c_int32),
+        ("reserved", C.c_int32),
     ]
 
 
@@ -152,15 +155,17 @@ class Decoder:
             items[i].len = len(d)
         return items, hold
 
-    def decode(self, files):
-        """Decode a list of JPEG `bytes`; returns (list of (3,H,W) uint8 arrays or None, list of status)."""
+    def decode(self, files, layout=PLANAR):
+        """Decode a list of JPEG `bytes`; returns (list of uint8 arrays or None, list of status).
+        Arrays are (3,H,W) for the planar layout, (H,W,3) for the interleaved one."""
         n = len(files)
         items, hold = self.make_items(files)
         outs = []
         for i, d in enumerate(files):
             rc, w, h = peek(d)
+            items[i].layout = layout
             if rc == OK:
-                a = np.empty((3, h, w), np.uint8)
+                a = np.empty((3, h, w) if layout == PLANAR else (h, w, 3), np.uint8)
                 items[i].rgb = a.ctypes.data
                 outs.append(a)
             else:

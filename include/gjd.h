@@ -39,6 +39,16 @@ typedef enum gjd_status {
 typedef struct gjd_ctx   gjd_ctx;    /* streams + pinned staging + device arenas            */
 typedef struct gjd_batch gjd_batch;  /* a parsed batch resident in device memory            */
 
+/* Pixel layouts of gjd_item.rgb.
+ * PLANAR      three planes R, G, B of height rows, row_pitch bytes apart, plane_stride between planes —
+ *             the order of the reference's .array file (cpp-decoder/src/parser.cpp:203-208).
+ * INTERLEAVED R,G,B,R,G,B,... rows of 3*width bytes, row_pitch bytes apart (0 = 3*width); plane_stride is
+ *             ignored.  This is the pixel order of the reference's device buffer outputChannels
+ *             (cuda-decoder/src/parser.cu:571-573, read back at :715-717) narrowed from int16 to u8 and
+ *             cropped, and the body of a binary PPM (testing/jpeglib_output_ppm). */
+#define GJD_LAYOUT_PLANAR      0
+#define GJD_LAYOUT_INTERLEAVED 1
+
 /* One image of a batch.
  * Replaces the per-image HostData/DeviceData descriptor pair the reference fills with
  * ~26 CUDA calls per image (cuda-decoder/src/parser.h:21-39, benchmark_thoughput/benchmark.cu:49-60). */
@@ -49,11 +59,14 @@ typedef struct gjd_item {
                                  /*      (caller-owned; host memory unless rgb_on_device != 0).         */
                                  /*      NULL in gjd_batch_prepare = library-owned device buffer.       */
     size_t         plane_stride; /* in : bytes between the R, G and B planes; 0 = row_pitch * height    */
-    size_t         row_pitch;    /* in : bytes between rows; 0 = width                                  */
+    size_t         row_pitch;    /* in : bytes between rows; 0 = tight.  Bytes between rows/planes are   */
+                                 /*      unspecified after the call (regions are copied whole).         */
     int32_t        rgb_on_device;/* in : non-zero: rgb is a device pointer on the context's device      */
     int32_t        width;        /* out: image width  (SOF0)                                            */
     int32_t        height;       /* out: image height (SOF0)                                            */
     int32_t        status;       /* out: per-image gjd_status                                           */
+    int32_t        layout;       /* in : GJD_LAYOUT_PLANAR (0) or GJD_LAYOUT_INTERLEAVED                */
+    int32_t        reserved;     /* in : 0                                                              */
 } gjd_item;
 
 /* Context.  Replaces allocate()/clean() (cuda-decoder/src/parser.cu:324-358, 684-700): all device
@@ -89,7 +102,8 @@ int  gjd_decode_batch(gjd_ctx* ctx, gjd_item* items, int32_t n);
  *   run     : enqueue all GPU stages for the whole batch on the context stream (asynchronous).
  *   sync    : wait; returns GJD_E_CORRUPT if any image failed on the device (per-image detail via
  *             gjd_batch_status).
- *   fetch   : copy image i's pixels to host memory (tight planar R,G,B, W*H bytes per plane). */
+ *   fetch   : copy image i's pixels to host memory, tight, in the item's layout (planar: W*H bytes per
+ *             plane; interleaved: 3*W bytes per row). */
 int  gjd_batch_prepare(gjd_ctx* ctx, gjd_item* items, int32_t n, gjd_batch** out);
 int  gjd_batch_run(gjd_ctx* ctx, gjd_batch* b);
 int  gjd_batch_sync(gjd_ctx* ctx, gjd_batch* b);

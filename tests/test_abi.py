@@ -74,3 +74,14 @@ def test_throughput_driver_without_gpu_fails_loudly():
         return
     p = subprocess.run([exe, os.path.join(ROOT, "tests", "golden", "images")], stderr=subprocess.PIPE, text=True)
     assert p.returncode == 3 and "CUDA device" in p.stderr
+
+
+def test_item_struct_matches_header():
+    """The ctypes mirror of gjd_item has the header's fields, in order, and its size (64 bytes)."""
+    import gjd
+    src = open(os.path.join(ROOT, "include", "gjd.h")).read()
+    body = src[src.index("typedef struct gjd_item {"):src.index("} gjd_item;")]
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    fields = re.findall(r"\b(\w+);", body)
+    assert fields == [f[0] for f in gjd.Item._fields_]
+    assert C.sizeof(gjd.Item) == 64

@@ -252,3 +252,39 @@ def test_throughput_driver_cli():
     r = json.loads(out.strip().splitlines()[-1])
     assert r["images"] == 7 and r["failed"] == 0 and r["rejected"] == 0
     assert r["MPixel_per_s"] > 0 and r["e2e_MPixel_per_s"] > 0 and r["compressed_MB_per_s"] > 0
+
+
+def test_interleaved_layout_matches_planar(decoder, golden, ref_outputs, rst_golden, ref_outputs_rst):
+    """GJD_LAYOUT_INTERLEAVED (the pixel order of the reference's outputChannels / a PPM body) holds the
+    same pixels as the planar layout — aligned and ragged widths, restart files included."""
+    import gjd
+    names = NAMES
+    files = [golden[n] for n in names] + [rst_golden[n] for n in sorted(rst_golden)]
+    want = [ref_outputs[n + "/rgb"] for n in names] + [ref_outputs_rst[n + "/rgb"] for n in sorted(rst_golden)]
+    outs, st = decoder.decode(files, layout=gjd.INTERLEAVED)
+    assert st == [0] * len(files)
+    for o, w_ in zip(outs, want):
+        assert o.shape == (w_.shape[1], w_.shape[2], 3)
+        assert np.array_equal(o, w_.transpose(1, 2, 0))
+
+
+def test_interleaved_resident_fetch_and_pitch(decoder, golden, ref_outputs):
+    import ctypes as C
+    import gjd
+    name = "images/8_401x363"
+    data = golden[name]
+    want = ref_outputs[name + "/rgb"].transpose(1, 2, 0)
+    h, w, _ = want.shape
+    pitch = 3 * w + 13                                   # unaligned pitch: the byte-store path
+    items, hold = decoder.make_items([data])
+    buf = np.full(pitch * h, 0xAB, np.uint8)
+    items[0].rgb = buf.ctypes.data
+    items[0].row_pitch = pitch
+    items[0].layout = gjd.INTERLEAVED
+    decoder.decode_batch_raw(items, 1)
+    assert items[0].status == 0
+    rows = buf.reshape(h, pitch)
+    assert np.array_equal(rows[:, :3 * w].reshape(h, w, 3), want)
+    items[0].row_pitch = 3 * w - 1                       # too small
+    decoder.decode_batch_raw(items, 1)
+    assert items[0].status == gjd.E_ARG
