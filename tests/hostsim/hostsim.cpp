@@ -45,9 +45,10 @@ const int kZZ[64] = GJD_ZZ_TABLE;
 extern "C" {
 
 /* stats: [0] max synchronisation rounds inside a sequence, [1] fix-up subsequences decoded,
- *        [2] device status bits, [3] nosync count, [4] subsequences, [5] sequences */
+ *        [2] device status bits, [3] nosync count, [4] subsequences, [5] sequences,
+ *        [6] subsequences re-decoded in validation rounds (all rounds), [7] of those, in round 1 */
 int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* coef_out, uint8_t* rgb_out,
-                   int32_t* width, int32_t* height, uint32_t stats[6]) {
+                   int32_t* width, int32_t* height, uint32_t stats[8]) {
     const uint32_t sub_log2 = sub_log2_arg ? (uint32_t)sub_log2_arg : GJD_SUB_LOG2_MIN;
     const uint32_t S = 1u << sub_log2;
     GjdParsed p;
@@ -90,7 +91,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     GjdLutMem hlut;
     hlut.set = lut;
     hlut.badcode = &badcode;
-    uint32_t max_rounds = 0, fix_decodes = 0, nosync = 0, status = 0, sub_total = 0, seq_total = 0;
+    uint32_t max_rounds = 0, fix_decodes = 0, nosync = 0, status = 0, sub_total = 0, seq_total = 0, redec = 0, redec1 = 0;
     std::vector<int16_t> coef((size_t)tile_count * 96 * 64, (int16_t)0x7e7e);   /* stale garbage where nothing is written */
     std::vector<uint32_t> meta((size_t)tile_count * 96, 0);
     std::vector<uint8_t> written((size_t)tile_count * 96, 0);
@@ -143,7 +144,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                     GjdState st; st.p = in_p[tid] = pp; st.pos = in_pos[tid] = ppos; st.n = 0;
                     gjd_count_span(scan, hlut, endb[tid], scan_bits, st);
                     np[tid] = st.p; nn[tid] = (st.n << 8) | st.pos;
-                    badv[tid] = 1; any = true;
+                    badv[tid] = 1; any = true; redec++; if (r == 0) redec1++;
                 }
             }
             if (!any) break;
@@ -255,7 +256,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     }
     if (stats) {
         stats[0] = max_rounds; stats[1] = fix_decodes; stats[2] = status; stats[3] = nosync;
-        stats[4] = sub_total; stats[5] = seq_total;
+        stats[4] = sub_total; stats[5] = seq_total; stats[6] = redec; stats[7] = redec1;
     }
     free(lut);
     return status ? GJD_E_CORRUPT : GJD_OK;
