@@ -160,7 +160,7 @@ struct gjd_batch {
     std::vector<GjdDhtSet> dhts;
     std::vector<GjdQuantSet> quants;
     PinBuf h_scan, h_meta, h_status;
-    DevBuf d_scan, d_meta, d_luts, d_sinfo, d_seqmaps, d_coef, d_blkmeta, d_tilebase, d_tileimg, d_tbimg, d_rgb, d_status;
+    DevBuf d_scan, d_meta, d_luts, d_lutc, d_sinfo, d_seqmaps, d_coef, d_blkmeta, d_tilebase, d_tileimg, d_tbimg, d_rgb, d_status;
     GjdDevBatch view{};
     GjdStageEvents ev{};
     bool ev_ok = false;
@@ -172,7 +172,7 @@ struct gjd_batch {
 
     void release() {
         h_scan.release(); h_meta.release(); h_status.release();
-        d_scan.release(); d_meta.release(); d_luts.release(); d_sinfo.release(); d_seqmaps.release();
+        d_scan.release(); d_meta.release(); d_luts.release(); d_lutc.release(); d_sinfo.release(); d_seqmaps.release();
         d_coef.release(); d_blkmeta.release(); d_tilebase.release(); d_tileimg.release(); d_tbimg.release(); d_rgb.release();
         d_status.release();
         if (ev_ok) for (auto& e : ev.e) cudaEventDestroy(e);
@@ -403,6 +403,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     GJD_TRY(b->d_meta.ensure(meta));
     GJD_TRY(b->d_scan.ensure(b->scan_alloc));
     GJD_TRY(b->d_luts.ensure(sizeof(GjdLutSet) * b->dhts.size()));
+    GJD_TRY(b->d_lutc.ensure(sizeof(GjdLutCount) * b->dhts.size()));
     GJD_TRY(b->d_sinfo.ensure((size_t)seq * GJD_SEQ_SUBS * sizeof(uint2)));
     GJD_TRY(b->d_seqmaps.ensure((size_t)seq * 4 * sizeof(uint32_t)));
     GJD_TRY(b->d_coef.ensure((size_t)tile * 96 * 64 * sizeof(int16_t)));
@@ -418,6 +419,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     v.segs = (const GjdSegment*)((uint8_t*)b->d_meta.p + o_seg);
     v.scan = (const uint8_t*)b->d_scan.p;
     v.luts = (const GjdLutSet*)b->d_luts.p;
+    v.lutc = (const GjdLutCount*)b->d_lutc.p;
     v.quants = (const GjdQuantSet*)((uint8_t*)b->d_meta.p + o_q);
     v.sinfo = (uint2*)b->d_sinfo.p;
     v.seq_seg = (uint32_t*)b->d_seqmaps.p;
@@ -434,7 +436,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
 
     GJD_TRY(cudaMemcpyAsync(b->d_scan.p, b->h_scan.p, soff[n] + 16, cudaMemcpyHostToDevice, b->stream));
     GJD_TRY(cudaMemcpyAsync(b->d_meta.p, b->h_meta.p, meta, cudaMemcpyHostToDevice, b->stream));
-    GJD_TRY(gjd_launch_build_luts((const GjdDhtSet*)((uint8_t*)b->d_meta.p + o_dht), (GjdLutSet*)b->d_luts.p,
+    GJD_TRY(gjd_launch_build_luts((const GjdDhtSet*)((uint8_t*)b->d_meta.p + o_dht), (GjdLutSet*)b->d_luts.p, (GjdLutCount*)b->d_lutc.p,
                                   (uint32_t)b->dhts.size(), b->stream));
     GJD_TRY(gjd_launch_fill_maps(v, b->stream));
     return GJD_OK;

@@ -18,6 +18,10 @@
 #include <stdint.h>
 #include "gjd_types.h"
 
+#ifndef GJD_DBG_SYM
+#define GJD_DBG_SYM() ((void)0)   /* test harnesses may count decoded symbols */
+#endif
+
 #ifdef __CUDACC__
 #define GJD_HD __host__ __device__ __forceinline__
 #define GJD_HD_COLD __host__ __device__ __noinline__   /* rare paths: kept out of line (code size) */
@@ -35,6 +39,9 @@ GJD_HD uint32_t gjd_make_entry(uint32_t code_len, uint32_t sym, uint32_t isdc) {
     return (code_len + size) | (size << 5) | (adv << 9);
 }
 #define GJD_ENTRY_BAD 0x10000u   /* bit 16 (slow path only): no code assigned to these bits */
+/* what the decoders do with an unassigned code: consume 16 bits, no value, advance one slot — so that
+ * "zigzag index 0" and "the ring is at a DC table" stay equivalent even on garbage */
+#define GJD_ENTRY_UNASSIGNED (16u | (1u << 9))
 
 /* Canonical code tables from BITS[16]: lim[L] = first unused code of length L left-aligned to
  * 16 bits (non-decreasing in L), off[L] = valptr[L] - mincode[L].
@@ -89,6 +96,22 @@ GJD_HD uint16_t gjd_lut2_entry(const uint32_t* lim, const int32_t* off, const ui
     if (j >= (uint32_t)GJD_LUT_SIZE) return 0;
     uint32_t e = gjd_resolve(lim, off, vals, isdc, (j << 6) | (i2 & 63u), GJD_LUT_BITS + 1);
     return (e & GJD_ENTRY_BAD) ? (uint16_t)0 : (uint16_t)e;
+}
+
+/* Count-pass LUT entry for index i (GjdLutCount): the single-symbol entry without its size field, or — for an
+ * AC table, when the first symbol is not EOB and a second symbol of the same table fits completely into the
+ * remaining index bits — the pair entry. */
+GJD_HD uint16_t gjd_lutc_entry(const uint32_t* lim, const int32_t* off, const uint8_t* vals,
+                               uint32_t isdc, uint32_t i) {
+    const uint32_t e1 = gjd_lut_entry(lim, off, vals, isdc, i);
+    if ((e1 & 31u) == 0u) return (uint16_t)e1;
+    const uint32_t tot1 = e1 & 31u, adv1 = e1 >> 9;
+    const uint32_t single = tot1 | (adv1 << 9);
+    if (isdc || adv1 > 8u || tot1 >= (uint32_t)GJD_LUT_BITS) return (uint16_t)single;   /* EOB (64) and runs > 7: no pair */
+    const uint32_t e2 = gjd_lut_entry(lim, off, vals, 0u, (i << tot1) & (uint32_t)(GJD_LUT_SIZE - 1));
+    const uint32_t tot2 = e2 & 31u;
+    if (tot2 == 0u || tot1 + tot2 > (uint32_t)GJD_LUT_BITS) return (uint16_t)single;
+    return (uint16_t)((tot1 + tot2) | GJD_PAIR_FLAG | ((adv1 - 1u) << 6) | ((adv1 + (e2 >> 9)) << 9));
 }
 
 /* DHT slot behind ring position r (0..5): even = DC table, odd = AC table of component r/2. */
@@ -196,8 +219,8 @@ struct GjdLutSmem {
 };
 #endif
 
-/* Rare path: the code is longer than GJD_LUT_BITS, or unassigned.  An unassigned code consumes 16 bits
- * and comes back with advance 0 (no slot): the write pass flags it, and both passes treat it alike. */
+/* Rare path: the code is longer than GJD_LUT_BITS, or unassigned.  An unassigned code comes back as
+ * GJD_ENTRY_UNASSIGNED: the write pass flags it, and both passes treat it alike. */
 GJD_HD_COLD uint32_t gjd_lookup_slow(const GjdLutSet* lut, uint32_t tb, uint32_t w, uint32_t room, uint32_t* badcode) {
     uint32_t slot = lut->slot_of[tb / GJD_RING_STRIDE];
     uint32_t e = gjd_resolve(lut->lim[slot], lut->off[slot], lut->vals[slot], lut->isdc[slot], w >> 16, GJD_LUT_BITS + 1);
@@ -205,7 +228,7 @@ GJD_HD_COLD uint32_t gjd_lookup_slow(const GjdLutSet* lut, uint32_t tb, uint32_t
         /* only a symbol that lies inside the scan counts (the padding after the last MCU does not);
          * benign race: every writer stores the same value */
         if (badcode && room >= 16u) *badcode = 1u;
-        e = 16u;
+        e = GJD_ENTRY_UNASSIGNED;
     }
     return e;
 }
@@ -244,6 +267,7 @@ GJD_HD void gjd_count_span(const uint32_t* scan, const Lut& lut, uint32_t end_bi
     gjd_win_init(win, scan, s.p);
     uint32_t p = s.p, z = s.pos & 63u, tb = gjd_ring_of_pos(s.pos), nb = 0;
     while (p < end_bits) {
+        GJD_DBG_SYM();
         const uint32_t w = gjd_peek32(win, scan, p);
         const uint32_t e = gjd_lookup(lut, tb, w, scan_bits - p);
         const uint32_t pn = p + (e & 31u);
@@ -255,6 +279,69 @@ GJD_HD void gjd_count_span(const uint32_t* scan, const Lut& lut, uint32_t end_bi
         if (zn >= 64u) { z = 0u; nb++; }
     }
     const uint32_t adv = nb * 64u + z - (s.pos & 63u);      /* slots advanced (mod 2^32 arithmetic is exact) */
+    s.p = p;
+    s.n += adv;
+    s.pos = (s.pos + adv) % 192u;
+}
+
+/* Any single symbol from the canonical tables alone (code lengths 1..16): what gjd_lookup returns, without
+ * touching a LUT.  Rare paths of the pair-counting loop only. */
+GJD_HD_COLD uint32_t gjd_lookup_canonical(const GjdLutSet* lut, uint32_t tb, uint32_t w) {
+    const uint32_t slot = lut->slot_of[tb / GJD_RING_STRIDE];
+    const uint32_t e = gjd_resolve(lut->lim[slot], lut->off[slot], lut->vals[slot], lut->isdc[slot], w >> 16, 1);
+    return (e & GJD_ENTRY_BAD) ? GJD_ENTRY_UNASSIGNED : e;
+}
+
+/* gjd_count_span with the pair LUT (lut.entry() reads a GjdLutCount ring followed by lut2; lut.set gives the
+ * canonical tables).  Same states as gjd_count_span for every input:
+ *   - pairs are taken only while p + GJD_LUT_BITS <= end_bits, so the second symbol of a pair always STARTS
+ *     before end_bits; the last few symbols of the span are decoded one at a time from the canonical tables;
+ *   - when a pair would complete the block, the first symbol is checked alone: if it already completes the
+ *     block (a coefficient at index 63, or garbage), the second symbol belongs to the next block's DC table
+ *     and the pair is dropped. */
+template <class Lut>
+GJD_HD void gjd_count_span_pairs(const uint32_t* scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
+                                 GjdState& s) {
+    if (s.p >= end_bits) return;
+    GjdWin win;
+    gjd_win_init(win, scan, s.p);
+    uint32_t p = s.p, z = s.pos & 63u, tb = gjd_ring_of_pos(s.pos), nb = 0;
+    while (p + (uint32_t)GJD_LUT_BITS <= end_bits) {
+        GJD_DBG_SYM();
+        const uint32_t w = gjd_peek32(win, scan, p);
+        uint32_t e = lut.entry(tb + ((w >> (31 - GJD_LUT_BITS)) & (GJD_RING_STRIDE - 2u)));
+        if ((e & 31u) == 0u) {   /* long code: single-symbol entries (with a size field) from lut2 / the tables */
+            if (e) e = lut.entry((GJD_RING_BYTES - 128u) + (tb >> 1) + e * 4u + ((w >> 15) & 126u));
+            if ((e & 31u) == 0u) e = gjd_lookup_slow(lut.set, tb, w, scan_bits - p, lut.badcode);
+            e &= ~0x1E0u;
+        }
+        uint32_t pn = p + (e & 31u);
+        if (pn > scan_bits) break;
+        uint32_t zn = z + (e >> 9);
+        if (zn >= 64u && (e & GJD_PAIR_FLAG) && z + ((e >> 6) & 7u) >= 63u) {
+            /* the first symbol alone completes the block (rare): take it alone, from the canonical tables */
+            const uint32_t e1 = gjd_lookup_canonical(lut.set, tb, w);
+            pn = p + (e1 & 31u);
+            zn = z + (e1 >> 9);
+        }
+        p = pn;
+        tb = gjd_ring_next(tb, z, zn);
+        z = zn;
+        if (zn >= 64u) { z = 0u; nb++; }
+    }
+    while (p < end_bits) {
+        GJD_DBG_SYM();
+        const uint32_t w = gjd_peek32(win, scan, p);
+        const uint32_t e = gjd_lookup_canonical(lut.set, tb, w);
+        const uint32_t pn = p + (e & 31u);
+        if (pn > scan_bits) break;
+        p = pn;
+        const uint32_t zn = z + (e >> 9);
+        tb = gjd_ring_next(tb, z, zn);
+        z = zn;
+        if (zn >= 64u) { z = 0u; nb++; }
+    }
+    const uint32_t adv = nb * 64u + z - (s.pos & 63u);
     s.p = p;
     s.n += adv;
     s.pos = (s.pos + adv) % 192u;

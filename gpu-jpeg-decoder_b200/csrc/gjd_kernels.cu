@@ -52,6 +52,16 @@ __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* ws
     return base + incl - v;
 }
 
+/* The count pass's view: the pair LUT ring in place of the primary one, everything else as in the set. */
+__device__ __forceinline__ void copy_count_lut_to_smem(GjdLutSet* dst, const GjdLutSet* src, const GjdLutCount* cnt) {
+    static_assert(sizeof(GjdLutCount) == GJD_RING_BYTES && sizeof(GjdLutCount) % 16 == 0, "ring size");
+    const uint4* c = reinterpret_cast<const uint4*>(cnt);
+    const uint4* s = reinterpret_cast<const uint4*>(src);
+    uint4* d = reinterpret_cast<uint4*>(dst);
+    for (uint32_t i = threadIdx.x; i < sizeof(GjdLutSet) / 16; i += blockDim.x)
+        d[i] = __ldg(i < sizeof(GjdLutCount) / 16 ? c + i : s + i);
+}
+
 __device__ __forceinline__ void copy_lut_to_smem(GjdLutSet* dst, const GjdLutSet* src) {
     static_assert(sizeof(GjdLutSet) % 16 == 0, "GjdLutSet must be a multiple of 16 bytes");
     const uint4* s = reinterpret_cast<const uint4*>(src);
@@ -61,7 +71,8 @@ __device__ __forceinline__ void copy_lut_to_smem(GjdLutSet* dst, const GjdLutSet
 
 /* ------------------------------------------------------------------ tables and maps --- */
 
-__global__ void __launch_bounds__(256) k_build_luts(const GjdDhtSet* __restrict__ dht, GjdLutSet* __restrict__ luts) {
+__global__ void __launch_bounds__(256) k_build_luts(const GjdDhtSet* __restrict__ dht, GjdLutSet* __restrict__ luts,
+                                                    GjdLutCount* __restrict__ lutc) {
     const GjdDhtSet& in = dht[blockIdx.x];
     GjdLutSet& out = luts[blockIdx.x];
     __shared__ uint32_t lim[4][17];
@@ -81,6 +92,7 @@ __global__ void __launch_bounds__(256) k_build_luts(const GjdDhtSet* __restrict_
         uint32_t r = i / GJD_LUT_SIZE, j = i % GJD_LUT_SIZE;
         uint32_t t = gjd_ring_slot(in.tabsel, r);
         out.lut[r][j] = gjd_lut_entry(lim[t], off[t], in.vals[t], in.isdc[t], j);
+        lutc[blockIdx.x].lut[r][j] = gjd_lutc_entry(lim[t], off[t], in.vals[t], in.isdc[t], j);
     }
     for (uint32_t i = threadIdx.x; i < GJD_RING_TABLES * GJD_LUT2_SIZE; i += blockDim.x) {
         uint32_t r = i / GJD_LUT2_SIZE, j = i % GJD_LUT2_SIZE;
@@ -119,7 +131,7 @@ __global__ void __launch_bounds__(128) k_fill_maps(GjdDevBatch b) {
  * After the reference's parallelHuffManDecode (cuda-decoder/src/parser.cu:132-173), which continues
  * every thread through whole slices instead.
  */
-__global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
+__global__ void __launch_bounds__(GJD_SYNC_THREADS, 8) k_huff_sync(GjdDevBatch b) {
     __shared__ GjdLutSet lut;
     __shared__ uint32_t sp[GJD_SEQ_SUBS];
     __shared__ uint32_t sn[GJD_SEQ_SUBS];
@@ -131,7 +143,7 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
     const uint32_t sub_count = d.sub_count, scan_bits = d.scan_bits;
     const uint32_t S = 1u << b.sub_log2;
     const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
-    copy_lut_to_smem(&lut, b.luts + d.lut_id);
+    copy_count_lut_to_smem(&lut, b.luts + d.lut_id, b.lutc + d.lut_id);
     const GjdLutSmem slut(&lut);
     __syncthreads();
 
@@ -144,11 +156,11 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
     if (active) {
         if (sub != 0u) {
             st.p = start > GJD_LOOKBACK_BITS ? start - GJD_LOOKBACK_BITS : 0u;
-            gjd_count_span(scan, slut, start, scan_bits, st);
+            gjd_count_span_pairs(scan, slut, start, scan_bits, st);
         }
         in_p = st.p; in_pos = st.pos;
         st.n = 0;
-        gjd_count_span(scan, slut, end, scan_bits, st);
+        gjd_count_span_pairs(scan, slut, end, scan_bits, st);
     }
     sp[tid] = st.p;
     sn[tid] = (st.n << 8) | st.pos;
@@ -162,7 +174,7 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS) k_huff_sync(GjdDevBatch b) {
             bad = pp != in_p || ppos != in_pos;
             if (bad) {
                 st.p = in_p = pp; st.pos = in_pos = ppos; st.n = 0;
-                gjd_count_span(scan, slut, end, scan_bits, st);
+                gjd_count_span_pairs(scan, slut, end, scan_bits, st);
             }
         }
         if (!__syncthreads_or(bad)) break;
@@ -659,9 +671,9 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS) k_test_idct(const int16
 
 #define GJD_CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
 
-cudaError_t gjd_launch_build_luts(const GjdDhtSet* dht, GjdLutSet* luts, uint32_t n, cudaStream_t s) {
+cudaError_t gjd_launch_build_luts(const GjdDhtSet* dht, GjdLutSet* luts, GjdLutCount* lutc, uint32_t n, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
-    k_build_luts<<<n, 256, 0, s>>>(dht, luts);
+    k_build_luts<<<n, 256, 0, s>>>(dht, luts, lutc);
     return cudaGetLastError();
 }
 

@@ -18,6 +18,7 @@ struct GjdDevBatch {
     uint32_t n_seg;
     const uint8_t* scan;
     const GjdLutSet* luts;
+    const GjdLutCount* lutc;   /* pair LUT rings of the count pass, same index as luts */
     const GjdQuantSet* quants;
     uint2* sinfo;          /* [n_seq * GJD_SEQ_SUBS] */
     uint32_t* seq_seg;     /* [n_seq]  sequence -> segment */
@@ -45,7 +46,7 @@ struct GjdStageEvents {
     cudaEvent_t e[5];
 };
 
-cudaError_t gjd_launch_build_luts(const GjdDhtSet* dht, GjdLutSet* luts, uint32_t n, cudaStream_t s);
+cudaError_t gjd_launch_build_luts(const GjdDhtSet* dht, GjdLutSet* luts, GjdLutCount* lutc, uint32_t n, cudaStream_t s);
 cudaError_t gjd_launch_fill_maps(const GjdDevBatch& b, cudaStream_t s);
 /* Clears scratch and runs every decode stage. transform_variant selects the transform kernel
  * implementation (0 = default).  Returns the number of kernel launches in *launches. */

@@ -64,6 +64,17 @@ typedef struct GjdLutSet {
     uint8_t  pad[6];
 } GjdLutSet;
 
+/* The primary LUT ring as the COUNT pass (k_huff_sync) uses it: same index and the same [4:0] total bits and
+ * [15:9] slot advance, but no value size — instead bit 5 (GJD_PAIR_FLAG) marks an entry that covers TWO
+ * consecutive symbols of an AC table whose bits all lie inside the index (total and advance are the sums;
+ * an EOB as the second symbol contributes GJD_ADV_EOB; [8:6] = advance of the first symbol - 1, at most 7).
+ * Pairs cut the symbol loop's trip count by a third
+ * on photographic data.  Entries with [4:0] = 0 are the same links into lut2 as in GjdLutSet. */
+#define GJD_PAIR_FLAG 0x20u
+typedef struct GjdLutCount {
+    uint16_t lut[GJD_RING_TABLES][GJD_LUT_SIZE];
+} GjdLutCount;
+
 /* Raw DHT content + the scan's table selectors: what the LUT builder consumes (host -> device). */
 typedef struct GjdDhtSet {
     uint8_t bits[4][16];

@@ -8,12 +8,15 @@
  * It is not part of libgjd.so and nothing in the product can reach it.
  */
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
 #include <vector>
 
+static unsigned long long g_syms_dbg = 0;
+#define GJD_DBG_SYM() (g_syms_dbg++)
 #include "../../gpu-jpeg-decoder_b200/csrc/gjd_devfn.cuh"
 #include "../../gpu-jpeg-decoder_b200/csrc/gjd_parse.h"
 #include "../../include/gjd.h"
@@ -91,6 +94,17 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     GjdLutMem hlut;
     hlut.set = lut;
     hlut.badcode = &badcode;
+    /* k_huff_sync's view (copy_count_lut_to_smem): the pair LUT ring in place of the primary one */
+    GjdLutSet* lutS = (GjdLutSet*)malloc(sizeof(GjdLutSet));
+    memcpy(lutS, lut, sizeof(GjdLutSet));
+    for (uint32_t r = 0; r < GJD_RING_TABLES; r++) {
+        uint32_t t = lut->slot_of[r];
+        for (uint32_t i = 0; i < GJD_LUT_SIZE; i++)
+            lutS->lut[r][i] = gjd_lutc_entry(lut->lim[t], lut->off[t], lut->vals[t], lut->isdc[t], i);
+    }
+    GjdLutMem clut;
+    clut.set = lutS;
+    clut.badcode = nullptr;
     uint32_t max_rounds = 0, fix_decodes = 0, nosync = 0, status = 0, sub_total = 0, seq_total = 0, redec = 0, redec1 = 0;
     std::vector<int16_t> coef((size_t)tile_count * 96 * 64, (int16_t)0x7e7e);   /* stale garbage where nothing is written */
     std::vector<uint32_t> meta((size_t)tile_count * 96, 0);
@@ -122,11 +136,11 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                 endb[tid] = std::min(start + S, scan_bits);
                 if (sub != 0) {
                     st.p = start > GJD_LOOKBACK_BITS ? start - GJD_LOOKBACK_BITS : 0u;
-                    gjd_count_span(scan, hlut, start, scan_bits, st);
+                    gjd_count_span_pairs(scan, clut, start, scan_bits, st);
                 }
                 in_p[tid] = st.p; in_pos[tid] = st.pos;
                 st.n = 0;
-                gjd_count_span(scan, hlut, endb[tid], scan_bits, st);
+                gjd_count_span_pairs(scan, clut, endb[tid], scan_bits, st);
             }
             bp[tid] = st.p;
             bn[tid] = (st.n << 8) | st.pos;
@@ -142,7 +156,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                 uint32_t pp = bp[tid - 1], ppos = bn[tid - 1] & 255u;
                 if (pp != in_p[tid] || ppos != in_pos[tid]) {
                     GjdState st; st.p = in_p[tid] = pp; st.pos = in_pos[tid] = ppos; st.n = 0;
-                    gjd_count_span(scan, hlut, endb[tid], scan_bits, st);
+                    gjd_count_span_pairs(scan, clut, endb[tid], scan_bits, st);
                     np[tid] = st.p; nn[tid] = (st.n << 8) | st.pos;
                     badv[tid] = 1; any = true; redec++; if (r == 0) redec1++;
                 }
@@ -259,6 +273,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
         stats[4] = sub_total; stats[5] = seq_total; stats[6] = redec; stats[7] = redec1;
     }
     free(lut);
+    free(lutS);
     return status ? GJD_E_CORRUPT : GJD_OK;
 }
 
@@ -319,17 +334,83 @@ int hostsim_lut_check(const uint8_t* jpg, size_t len, uint32_t out[3]) {
         for (uint32_t win = 0; win < 65536u; win++) {
             const uint32_t w = win << 16, tb = r * GJD_RING_STRIDE;
             uint32_t want = gjd_resolve(lut->lim[t], lut->off[t], lut->vals[t], lut->isdc[t], win, 1);
-            if (want & GJD_ENTRY_BAD) want = 16u;
+            if (want & GJD_ENTRY_BAD) want = GJD_ENTRY_UNASSIGNED;
             if (gjd_lookup(m, tb, w, 64u) != want) out[0]++;
             uint32_t e = m.entry(tb + ((w >> (31 - GJD_LUT_BITS)) & (GJD_RING_STRIDE - 2u)));
             if ((e & 31u) == 0u) {
-                if (want != 16u) out[2]++;
+                if (want != GJD_ENTRY_UNASSIGNED) out[2]++;
                 uint32_t e2 = e ? m.entry((GJD_RING_BYTES - 128u) + (tb >> 1) + e * 4u + ((w >> 15) & 126u)) : 0u;
-                if ((e2 & 31u) == 0u && want != 16u) out[1]++;
+                if ((e2 & 31u) == 0u && want != GJD_ENTRY_UNASSIGNED) out[1]++;
             }
         }
     }
     free(lut);
+    return 0;
+}
+
+/* gjd_count_span_pairs against gjd_count_span: from every subsequence start of every segment, both from the
+ * true state (chained single-symbol decode) and from a cold state `lookback` bits earlier, for spans of
+ * 2^sub_log2 bits.  out[0] = spans compared, out[1] = spans whose exit state (p, n, pos) differs,
+ * out[2] = symbols decoded by the single-symbol walk, out[3] = loop trips of the pair walk. */
+static unsigned long long g_trips = 0;
+int hostsim_pair_check(const uint8_t* jpg, size_t len, int sub_log2, uint32_t lookback, unsigned long long out[4]) {
+    GjdParsed p;
+    int rc = gjd_parse_headers(jpg, len, &p);
+    if (rc) return rc;
+    const size_t raw = (size_t)(p.file_end - p.scan_begin);
+    std::vector<uint8_t> scanbuf(raw + raw / 2 + 128, 0);
+    std::vector<uint32_t> seg_off, seg_len;
+    long ulen = gjd_unstuff_segments(p.scan_begin, p.file_end, scanbuf.data(), &seg_off, &seg_len);
+    if (ulen < 0) return (int)ulen;
+    std::vector<uint32_t> scanw((scanbuf.size() + 3) / 4 + 4, 0);
+    memcpy(scanw.data(), scanbuf.data(), scanbuf.size());
+    GjdLutSet* lut = (GjdLutSet*)calloc(1, sizeof(GjdLutSet));
+    GjdLutSet* lutS = (GjdLutSet*)calloc(1, sizeof(GjdLutSet));
+    for (int t = 0; t < 4; t++) {
+        gjd_canonical(p.dht.bits[t], lut->lim[t], lut->off[t]);
+        memcpy(lut->vals[t], p.dht.vals[t], 256);
+        lut->isdc[t] = p.dht.isdc[t];
+    }
+    for (uint32_t r = 0; r < GJD_RING_TABLES; r++) {
+        uint32_t t = gjd_ring_slot(p.tabsel, r);
+        lut->slot_of[r] = (uint8_t)t;
+        for (uint32_t i = 0; i < GJD_LUT_SIZE; i++)
+            lut->lut[r][i] = gjd_lut_entry(lut->lim[t], lut->off[t], lut->vals[t], lut->isdc[t], i);
+        for (uint32_t i = 0; i < GJD_LUT2_SIZE; i++)
+            lut->lut2[r][i] = gjd_lut2_entry(lut->lim[t], lut->off[t], lut->vals[t], lut->isdc[t], i);
+    }
+    memcpy(lutS, lut, sizeof(GjdLutSet));
+    for (uint32_t r = 0; r < GJD_RING_TABLES; r++) {
+        uint32_t t = lut->slot_of[r];
+        for (uint32_t i = 0; i < GJD_LUT_SIZE; i++)
+            lutS->lut[r][i] = gjd_lutc_entry(lut->lim[t], lut->off[t], lut->vals[t], lut->isdc[t], i);
+    }
+    GjdLutMem one, two;
+    one.set = lut; one.badcode = nullptr;
+    two.set = lutS; two.badcode = nullptr;
+    const uint32_t S = 1u << sub_log2;
+    out[0] = out[1] = out[2] = out[3] = 0;
+    for (size_t sg = 0; sg < seg_off.size(); sg++) {
+        const uint32_t* scan = scanw.data() + seg_off[sg] / 4;
+        const uint32_t bits = seg_len[sg] * 8u;
+        GjdState truth; truth.p = 0; truth.n = 0; truth.pos = 0;
+        for (uint32_t start = 0; start < bits; start += S) {
+            const uint32_t end = std::min(start + S, bits);
+            for (int cold = 0; cold < 2; cold++) {
+                GjdState a, b;
+                if (cold) { a.p = start > lookback ? start - lookback : 0u; a.n = 0; a.pos = 0; }
+                else a = truth;
+                b = a;
+                g_syms_dbg = 0; gjd_count_span(scan, one, end, bits, a); out[2] += g_syms_dbg;
+                g_syms_dbg = 0; gjd_count_span_pairs(scan, two, end, bits, b); out[3] += g_syms_dbg;
+                out[0]++;
+                if (a.p != b.p || a.n != b.n || a.pos != b.pos) { out[1]++; if (getenv("GJD_PAIR_DEBUG")) fprintf(stderr, "seg %zu start %u end %u bits %u cold %d: single p=%u n=%u pos=%u  pair p=%u n=%u pos=%u\n", sg, start, end, bits, cold, a.p, a.n, a.pos, b.p, b.n, b.pos); }
+                if (!cold) truth = a;
+            }
+        }
+    }
+    (void)g_trips;
+    free(lut); free(lutS);
     return 0;
 }
 

@@ -142,3 +142,23 @@ def test_restart_stream_errors(hostsim, rst_golden):
     j = data.index(b"\xff\xd2")
     cut = bytes(data[:j]) + bytes(data[j + 2:])                    # one marker removed: interval count is off
     assert hostsim.decode(cut)[0] in (-4, -6)
+
+
+def test_pair_counting_equals_single_symbol_counting(hostsim, golden, rst_golden):
+    """k_huff_sync counts with the pair LUT (two AC symbols per trip); every span — from the true state and
+    from a cold start, three span lengths, every fixture incl. q100 (blocks ending exactly at index 63) and
+    restart files — must leave the decoder in the state the single-symbol walk leaves it in."""
+    import ctypes as C
+    trips = syms = 0
+    files = dict(golden)
+    files.update(rst_golden)
+    for name, data in sorted(files.items()):
+        for sub_log2, lookback in ((8, 100), (10, 512), (12, 512)):
+            out = np.zeros(4, np.uint64)
+            rc = hostsim.lib.hostsim_pair_check(C.cast(C.c_char_p(data), C.c_void_p), len(data), sub_log2, lookback,
+                                                out.ctypes.data)
+            assert rc == 0, name
+            assert out[0] > 0 and out[1] == 0, (name, sub_log2, list(out))
+            if sub_log2 == 12:
+                syms += int(out[2]); trips += int(out[3])
+    assert trips < 0.9 * syms        # the pairs do shorten the loop

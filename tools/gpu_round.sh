@@ -15,7 +15,7 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
     python tools/profile_run.py 3000 2 > $out/${tag}_ncu_launch.log 2>&1
 for k in k_transform k_huff_write k_huff_sync; do
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:$k -s 1 -c 1 -f -o $out/${tag}_$k \
-    python tools/profile_run.py 1000 2 > $out/${tag}_ncu_$k.log 2>&1
+    env GJD_SUB_LOG2=12 python tools/profile_run.py 1000 2 > $out/${tag}_ncu_$k.log 2>&1
 done
 fi
 ls -la $out | tail -20
