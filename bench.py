@@ -57,7 +57,7 @@ class ClockSampler:
         self.rows, self.proc = [], None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "20", "-i", str(index)], stdout=subprocess.PIPE, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
@@ -74,9 +74,12 @@ class ClockSampler:
         self.proc.terminate()
         sm, mx, reasons = [], 0.0, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ts, line in self.rows:
-            if ts < t0 or ts > t1 + 0.2:
-                continue
+        rows = [r for r in self.rows if t0 <= r[0] <= t1 + 0.2]
+        window = "timed region"
+        if not rows:   # a timed region shorter than the sampling period: the samples next to it
+            rows = [r for r in self.rows if t0 - 0.5 <= r[0] <= t1 + 0.5]
+            window = "timed region +-0.5 s"
+        for ts, line in rows:
             f = [x.strip() for x in line.split(",")]
             try:
                 sm.append(float(f[0]))
@@ -88,7 +91,8 @@ class ClockSampler:
                 pass
         if not sm:
             return None
-        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm),
+                "window": window}
 
 
 def ref_bench(threads, seconds, files_on_disk):
@@ -214,13 +218,13 @@ def main():
     dec = gjd.Decoder(local, scratch_bytes=int(os.environ.get("GJD_SCRATCH", str(4 << 30))))
 
     # ---- device-resident throughput ("value") ------------------------------------------------------
+    sampler = ClockSampler(local)     # started early: nvidia-smi needs a moment before its first sample
     batch = dec.prepare(files)
     info = None
     for _ in range(max(args.warmup, 3)):
         batch.run()
         assert batch.sync() == 0, "device reported a corrupt image"
     info = batch.info()
-    sampler = ClockSampler(local)
     stage = np.zeros(4)
     barrier()
     t0 = time.time()
