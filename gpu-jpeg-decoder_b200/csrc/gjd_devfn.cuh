@@ -616,6 +616,31 @@ GJD_HD uint32_t gjd_color_fast_frac(int yb, int cbb, int crb, int& R, int& G, in
     G = gjd_addmin_relu(tg >> 20, yb, 255);
     return (uint32_t)tg * 4096u;
 }
+/* d = sat_u8(b) | sat_u8(a) << 8 | (c & 0xffff) << 16  (PTX cvt.pack.sat.u8.s32.b32 = SASS I2IP.U8.S32.SAT):
+ * the 0..255 clamp of two pixels and their packing in one instruction. */
+GJD_HD uint32_t gjd_pack_sat_u8(int a, int b, uint32_t c) {
+#ifdef __CUDA_ARCH__
+    uint32_t d;
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+#else
+    const uint32_t sa = a < 0 ? 0u : (a > 255 ? 255u : (uint32_t)a), sb = b < 0 ? 0u : (b > 255 ? 255u : (uint32_t)b);
+    return sb | (sa << 8) | ((c & 0xffffu) << 16);
+#endif
+}
+
+/* gjd_color_fast_frac without the clamps: R, G, B before saturation (for gjd_pack_sat_u8). */
+GJD_HD uint32_t gjd_color_fast_raw(int yb, int cbb, int crb, int& R, int& G, int& B) {
+    int tr = crb * GJD_KR + GJD_CONST_R;
+    int tb = cbb * GJD_KB + GJD_CONST_B;
+    int tg = crb * (-GJD_KGR) + GJD_CONST_G;
+    tg = cbb * (-GJD_KGB) + tg;
+    R = (tr >> 20) + yb;
+    B = (tb >> 20) + yb;
+    G = (tg >> 20) + yb;
+    return (uint32_t)tg * 4096u;
+}
+
 GJD_HD bool gjd_color_fast(int yb, int cbb, int crb, int& R, int& G, int& B) {
     return gjd_color_fast_frac(yb, cbb, crb, R, G, B) < GJD_FRAC_DANGER;
 }

@@ -558,25 +558,31 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
         const uint32_t x0 = bx * 8u, y0 = by * 8u;
         const bool fast = aligned && (x0 + 8u <= W);
         /* rows 0-1 for the luma warp (its transform is the long one), 2-4 and 5-7 for the chroma warps */
-        const uint32_t r0 = c == 0u ? 0u : 3u * c - 1u, r1 = 3u * c + 2u;
+        const uint32_t r0 = c == 0u ? 0u : 3u * c - 1u;
+        /* rows of this warp that exist in the image (none for lanes past the last MCU) */
+        const uint32_t rows_left = (valid && y0 < H) ? H - y0 : 0u;
+        const uint32_t r1 = min(3u * c + 2u, rows_left);
+        uint8_t* rowp = out + (size_t)(y0 + r0) * pitch + (interleaved ? (size_t)x0 * 3u : (size_t)x0);
 #pragma unroll 1
-        for (uint32_t r = r0; r < r1; r++) {
-            if (!valid || y0 + r >= H) continue;
+        for (uint32_t r = r0; r < r1; r++, rowp += pitch) {
             const uint4 y4 = smp[t & 1u][0][r][lane], b4 = smp[t & 1u][1][r][lane], r4 = smp[t & 1u][2][r][lane];
             const uint32_t yw[4] = {y4.x, y4.y, y4.z, y4.w}, bw[4] = {b4.x, b4.y, b4.z, b4.w}, rw[4] = {r4.x, r4.y, r4.z, r4.w};
-            /* bytes are packed by multiply-add (values are 0..255, so + is |): one IMAD/LEA per pixel and
-             * channel; the danger test of the 8 pixels is one unsigned min over the fraction fields */
-            uint32_t pr[2] = {0, 0}, pg[2] = {0, 0}, pb[2] = {0, 0}, fmin = 0xffffffffu;
+            /* saturation and byte packing of two pixels in one I2IP (gjd_pack_sat_u8); the danger test of
+             * the 8 pixels is one unsigned min over the fraction fields */
+            int vr[8], vg[8], vb[8];
+            uint32_t fmin = 0xffffffffu;
 #pragma unroll
             for (int x = 0; x < 8; x++) {
                 const int sh = (x & 1) * 16;
-                int R, G, B;
-                const uint32_t frac = gjd_color_fast_frac((int)((yw[x >> 1] >> sh) & 0xffffu), (int)((bw[x >> 1] >> sh) & 0xffffu),
-                                                          (int)((rw[x >> 1] >> sh) & 0xffffu), R, G, B);
-                fmin = min(fmin, frac);
-                pr[x >> 2] = (uint32_t)R * (1u << (8 * (x & 3))) + pr[x >> 2];
-                pg[x >> 2] = (uint32_t)G * (1u << (8 * (x & 3))) + pg[x >> 2];
-                pb[x >> 2] = (uint32_t)B * (1u << (8 * (x & 3))) + pb[x >> 2];
+                fmin = min(fmin, gjd_color_fast_raw((int)((yw[x >> 1] >> sh) & 0xffffu), (int)((bw[x >> 1] >> sh) & 0xffffu),
+                                                    (int)((rw[x >> 1] >> sh) & 0xffffu), vr[x], vg[x], vb[x]));
+            }
+            uint32_t pr[2], pg[2], pb[2];
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                pr[h] = gjd_pack_sat_u8(vr[4 * h + 1], vr[4 * h], gjd_pack_sat_u8(vr[4 * h + 3], vr[4 * h + 2], 0u));
+                pg[h] = gjd_pack_sat_u8(vg[4 * h + 1], vg[4 * h], gjd_pack_sat_u8(vg[4 * h + 3], vg[4 * h + 2], 0u));
+                pb[h] = gjd_pack_sat_u8(vb[4 * h + 1], vb[4 * h], gjd_pack_sat_u8(vb[4 * h + 3], vb[4 * h + 2], 0u));
             }
             uint64_t g8 = ((uint64_t)pg[1] << 32) | pg[0];
             if (fmin < GJD_FRAC_DANGER) {   /* rare: G of the flagged pixels again with the reference's IEEE sequence */
@@ -592,7 +598,7 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
                 }
             }
             if (interleaved) {   /* block-uniform: R,G,B,R,G,B,... 24 bytes per lane, 768 contiguous bytes per warp */
-                uint8_t* px = out + (size_t)(y0 + r) * pitch + (size_t)x0 * 3u;
+                uint8_t* px = rowp;
                 const uint32_t g0 = (uint32_t)g8, g1 = (uint32_t)(g8 >> 32);
                 if (fast) {
                     /* word j of the 24 bytes: __byte_perm picks from {a: bytes 0-3, b: bytes 4-7} */
@@ -616,7 +622,7 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
                 }
                 continue;
             }
-            uint8_t* row = out + (size_t)(y0 + r) * pitch + x0;
+            uint8_t* row = rowp;
             if (fast) {
                 __stcs(reinterpret_cast<uint2*>(row), make_uint2(pr[0], pr[1]));
                 __stcs(reinterpret_cast<uint2*>(row + pstride), make_uint2((uint32_t)g8, (uint32_t)(g8 >> 32)));
