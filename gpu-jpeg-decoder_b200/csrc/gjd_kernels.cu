@@ -436,28 +436,37 @@ template <int I> struct GjdZz { static constexpr int value = gjd_zz_of_nat(I); }
  * compiler prunes the butterflies of gjd_idct8x8 that only see zeros (e.g. KLIM = 16: rows 5-7 vanish,
  * row 4 is DC-only).  Exactness is untouched: it is the same arithmetic on the same values. */
 template <int I, int KLIM> struct GjdUnpack {
-    static __device__ __forceinline__ void run(const uint32_t* w, const int* q, int* v) {
-        GjdUnpack<I - 1, KLIM>::run(w, q, v);
+    static __device__ __forceinline__ void run(const uint32_t* w, const uint32_t* qq, int* v) {
+        GjdUnpack<I - 1, KLIM>::run(w, qq, v);
         constexpr int k = GjdZz<I>::value;
         if (k < KLIM) {
-            const int c = (k & 1) ? ((int)w[k >> 1] >> 16) : (int)(int16_t)(w[k >> 1] & 0xffffu);
-            v[I] = c * q[k];
+            /* one IDP.2A (FMA pipe) selects the 16-bit half AND multiplies: qq[j] = q[2j] | q[2j+1] << 24, so
+             * dp2a.lo sees the bytes (q[2j], 0) against (lo, hi) and dp2a.hi sees (0, q[2j+1]) */
+            int r;
+            if (k & 1) asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(w[k >> 1]), "r"(qq[k >> 1]), "r"(0));
+            else asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(w[k >> 1]), "r"(qq[k >> 1]), "r"(0));
+            v[I] = r;
         } else {
             v[I] = 0;
         }
     }
 };
 template <int KLIM> struct GjdUnpack<0, KLIM> {
-    static __device__ __forceinline__ void run(const uint32_t*, const int*, int*) {}
+    static __device__ __forceinline__ void run(const uint32_t*, const uint32_t*, int*) {}
 };
+
+/* the quantisation table of one component as GjdUnpack wants it: 32 words q[2j] | q[2j+1] << 24 */
+__device__ __forceinline__ uint32_t gjd_pack_quant(const int* q, uint32_t j) {
+    return (uint32_t)q[2u * j] | ((uint32_t)q[2u * j + 1u] << 24);
+}
 
 /* dequantise + dezigzag + IDCT of one block (w: packed zigzag coefficients, dc: absolute DC), then park
  * the 64 samples (biased, u16) in shared memory rows dst[r * 32] */
 template <int KLIM>
-__device__ __forceinline__ void gjd_block_to_samples(const uint32_t* w, const int* q, int dc, uint4* dst) {
+__device__ __forceinline__ void gjd_block_to_samples(const uint32_t* w, const uint32_t* qq, int dc, uint4* dst) {
     int v[64];
-    GjdUnpack<63, KLIM>::run(w, q, v);
-    v[0] = dc * q[0];
+    GjdUnpack<63, KLIM>::run(w, qq, v);
+    v[0] = dc * (int)(qq[0] & 0xffu);
     gjd_idct8x8(v);
 #pragma unroll
     for (int r = 0; r < 8; r++)
@@ -486,7 +495,7 @@ __device__ __forceinline__ void gjd_block_to_samples(const uint32_t* w, const in
  */
 template <bool EXPORT, int MINB, bool ILV>
 __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDevBatch b, int16_t* __restrict__ coef_out) {
-    __shared__ int sq[3][64];
+    __shared__ uint32_t sq[3][32];
     __shared__ uint4 smp[2][3][8][32];
 
     const uint32_t tid = threadIdx.x, c = tid >> 5, lane = tid & 31u;
@@ -494,7 +503,7 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
     const uint32_t ltb = blockIdx.x - d.tb_first;
     {
         const int* qg = reinterpret_cast<const int*>(b.quants + d.quant_id);
-        for (uint32_t i = tid; i < 192; i += GJD_TRANSFORM_THREADS) sq[i / 64][i % 64] = __ldg(qg + i);
+        sq[c][lane] = gjd_pack_quant(qg + c * 64u, lane);
     }
     __syncthreads();
 
@@ -504,7 +513,7 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
     /* ILV = false: the batch holds planar images only (the common case keeps the shorter kernel) */
     const bool interleaved = ILV && d.layout == GJD_LAYOUT_INTERLEAVED;
     const bool aligned = (((size_t)out | pitch | (interleaved ? 0 : pstride)) & 7u) == 0;
-    const int* q = sq[c];
+    const uint32_t* q = sq[c];
 
 #pragma unroll 1
     for (uint32_t t = 0; t < GJD_TB_TILES; t++) {
@@ -656,8 +665,8 @@ __global__ void k_test_color(const int16_t* __restrict__ y, const int16_t* __res
 __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS) k_test_idct(const int16_t* __restrict__ coef, size_t nblocks,
                                                                       const int32_t* __restrict__ quant,
                                                                       int16_t* __restrict__ out) {
-    __shared__ int sq[64];
-    if (threadIdx.x < 64) sq[threadIdx.x] = quant[threadIdx.x];
+    __shared__ uint32_t sq[32];
+    if (threadIdx.x < 32) sq[threadIdx.x] = gjd_pack_quant(quant, threadIdx.x);
     __syncthreads();
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nblocks) return;
@@ -667,7 +676,7 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS) k_test_idct(const int16
     for (int j = 0; j < 32; j++) w[j] = src[j];
     int v[64];
     GjdUnpack<63, 64>::run(w, sq, v);
-    v[0] = (int)(int16_t)(w[0] & 0xffffu) * sq[0];
+    v[0] = (int)(int16_t)(w[0] & 0xffffu) * (int)(sq[0] & 0xffu);
     gjd_idct8x8(v);
 #pragma unroll
     for (int j = 0; j < 64; j++) out[i * 64 + j] = (int16_t)(v[j] - 256);

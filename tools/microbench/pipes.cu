@@ -21,6 +21,11 @@ __global__ void __launch_bounds__(256) k(int* out, int seed) {
             if (OP == 6) asm volatile("mul.hi.u32 %0, %0, 65536;" : "+r"(a[i]));
             if (OP == 7) asm volatile("prmt.b32 %0, %0, %1, 0x9910;" : "+r"(a[i]) : "r"(c));
             if (OP == 9) asm volatile("cvt.pack.sat.u8.s32.b32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c));
+            if (OP == 10) asm volatile("dp2a.lo.s32.u32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c));
+            if (OP == 11) { asm volatile("dp2a.lo.s32.u32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); asm volatile("lop3.b32 %0, %0, %1, %0, 0x96;" : "+r"(a[i]) : "r"(c)); }
+            if (OP == 12) { asm volatile("dp2a.lo.s32.u32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); asm volatile("mad.lo.s32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); }
+            if (OP == 13) { asm volatile("cvt.pack.sat.u8.s32.b32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); asm volatile("lop3.b32 %0, %0, %1, %0, 0x96;" : "+r"(a[i]) : "r"(c)); }
+            if (OP == 14) { asm volatile("cvt.pack.sat.u8.s32.b32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); asm volatile("mad.lo.s32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); }
             if (OP == 8) asm volatile("{.reg .s32 t; add.s32 t, %0, %1; min.s32 t, t, 511; max.s32 %0, t, 0;}" : "+r"(a[i]) : "r"(c));
         }
     }
@@ -43,5 +48,7 @@ int main() {
     run<0>("IMAD", 1); run<1>("IMAD.HI (s32, reg)", 1); run<2>("SHF.R.S32", 1); run<3>("LOP3", 1);
     run<4>("LEA.HI.SX32 (shr+add)", 1); run<5>("IMAD + SHF pair", 2); run<6>("IMAD.HI.U32 x 65536", 1);
     run<7>("PRMT", 1); run<8>("VIADDMNMX.RELU (add,min,max)", 1); run<9>("I2IP.U8.S32.SAT (cvt.pack.sat)", 1);
+    run<10>("IDP.2A (dp2a.lo)", 1); run<11>("IDP.2A + LOP3 pair", 2); run<12>("IDP.2A + IMAD pair", 2);
+    run<13>("I2IP + LOP3 pair", 2); run<14>("I2IP + IMAD pair", 2);
     return 0;
 }
