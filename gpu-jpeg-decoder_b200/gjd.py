@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "build", "libgjd.so")
+LIB_PATH = os.environ.get("GJD_LIB") or os.path.join(_HERE, "build", "libgjd.so")   # GJD_LIB: A/B builds
 
 PLANAR, INTERLEAVED = 0, 1
 OK, E_ARG, E_CUDA, E_NOMEM, E_FORMAT, E_UNSUPPORTED, E_CORRUPT, E_NODEVICE, E_IO = 0, -1, -2, -3, -4, -5, -6, -7, -8
