@@ -266,12 +266,12 @@ static_assert(GJD_WRITE_THREADS == GJD_SEQ_SUBS, "one thread per subsequence of 
  */
 struct GjdWriteSink {
     uint4* mine;       /* &buf[0][tid] */
-    uint4* coef;       /* the image's first coefficient line, 8 uint4 per block */
-    uint32_t* meta;    /* the image's first meta word */
+    uint4* dst;        /* coefficient line of the next block this thread flushes (blocks are flushed in order) */
+    uint32_t* mp;      /* its meta word */
     __device__ __forceinline__ void store(uint32_t k, int v) const {
         reinterpret_cast<int16_t*>(mine + (k >> 3) * GJD_WRITE_THREADS)[k & 7u] = (int16_t)v;
     }
-    __device__ __forceinline__ void sector(uint4* dst, uint32_t sct) const {
+    __device__ __forceinline__ void sector(uint32_t sct) const {
         uint4* s0 = mine + (2u * sct) * GJD_WRITE_THREADS;
         uint4* s1 = mine + (2u * sct + 1u) * GJD_WRITE_THREADS;
         const uint4 a = *s0, c = *s1;
@@ -280,18 +280,22 @@ struct GjdWriteSink {
         *s0 = make_uint4(0u, 0u, 0u, 0u);
         *s1 = make_uint4(0u, 0u, 0u, 0u);
     }
-    __device__ __forceinline__ void flush(uint32_t blk, int dcdiff, uint32_t kmax) const {
-        meta[blk] = ((uint32_t)dcdiff & 0xffffu) | (kmax << 16);
-        if (kmax == 0u) return;
-        uint4* dst = coef + (size_t)blk * 8u;
-        sector(dst, 0u);
-        if (kmax >= 16u) {
-            sector(dst, 1u);
-            if (kmax >= 32u) {
-                sector(dst, 2u);
-                if (kmax >= 48u) sector(dst, 3u);
+    /* gjd_write_span flushes consecutive blocks starting at (idx0 + 63) >> 6: running pointers replace the
+     * per-block address arithmetic (blk itself is only the caller's bound check) */
+    __device__ __forceinline__ void flush(uint32_t, int dcdiff, uint32_t kmax) {
+        *mp = ((uint32_t)dcdiff & 0xffffu) | (kmax << 16);
+        if (kmax != 0u) {
+            sector(0u);
+            if (kmax >= 16u) {
+                sector(1u);
+                if (kmax >= 32u) {
+                    sector(2u);
+                    if (kmax >= 48u) sector(3u);
+                }
             }
         }
+        mp += 1;
+        dst += 8;
     }
 };
 
@@ -337,9 +341,10 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, 4) k_huff_write(GjdDevBatch
     GjdWriteSink sink;
     sink.mine = &buf[0][tid];
     const size_t blk0 = (size_t)b.imgs[img].tile_first * 96u + d.blk_first;   /* the segment's first block */
-    sink.coef = reinterpret_cast<uint4*>(b.coef) + blk0 * 8u;
-    sink.meta = b.meta + blk0;
     const uint32_t idx0 = b.seq_base[g] + excl;
+    const size_t first = blk0 + ((idx0 + 63u) >> 6);          /* the first block this thread owns */
+    sink.dst = reinterpret_cast<uint4*>(b.coef) + first * 8u;
+    sink.mp = b.meta + first;
     if (active && idx0 % 192u != st.pos && st.p < scan_bits) bad |= GJD_DEV_BADSTATE;
     uint32_t end = min((sub + 1) << b.sub_log2, scan_bits);
     gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad);
