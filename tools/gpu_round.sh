@@ -11,8 +11,8 @@ timeout 600 python bench.py --steps 10 --warmup 3 > $out/${tag}_bench.json 2> $o
 cat $out/${tag}_bench.json
 if [ "$2" != "quick" ]; then
 timeout 300 python tools/profile_run.py 300 3 > $out/${tag}_profrun.log 2>&1 && \
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/${tag}_launches.csv \
-    python tools/profile_run.py 3000 2 > $out/${tag}_ncu_launch.log 2>&1
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/${tag}_launches.csv \
+    python bench.py --steps 2 --warmup 1 --e2e-steps 1 --no-cpu-baseline > $out/${tag}_ncu_launch.log 2>&1
 for k in k_transform k_huff_write k_huff_sync; do
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:$k -s 1 -c 1 -f -o $out/${tag}_$k \
     env GJD_SUB_LOG2=12 python tools/profile_run.py 1000 2 > $out/${tag}_ncu_$k.log 2>&1
