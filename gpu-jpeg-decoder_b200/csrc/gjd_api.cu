@@ -292,7 +292,9 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         d.mcus_x = (d.width + 7) / 8;
         d.mcu_count = d.mcus_x * ((d.height + 7) / 8);
         d.tile_first = tile;
-        d.tile_count = (d.mcu_count + GJD_TILE_MCUS - 1) / GJD_TILE_MCUS;
+        d.gray = p.components == 1 ? 1u : 0u;
+        const uint32_t bpm = d.gray ? 1u : 3u;                       /* 8x8 blocks per MCU */
+        d.tile_count = (d.mcu_count * bpm + 95u) / 96u;              /* a tile is 96 coefficient lines */
         d.tb_first = tb;
         d.tb_count = (d.tile_count + GJD_TB_TILES - 1) / GJD_TB_TILES;
         d.row_pitch = (uint32_t)g.pitch;
@@ -359,8 +361,8 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
             sg.seq_count = (sg.sub_count + GJD_SEQ_SUBS - 1) / GJD_SEQ_SUBS;
             sg.img = (uint32_t)b->imgs.size();
             const uint32_t mcu0 = k * p.restart_interval;
-            sg.blk_first = 3u * mcu0;
-            sg.blk_count = 3u * (p.restart_interval ? std::min(p.restart_interval, d.mcu_count - mcu0) : d.mcu_count);
+            sg.blk_first = bpm * mcu0;
+            sg.blk_count = bpm * (p.restart_interval ? std::min(p.restart_interval, d.mcu_count - mcu0) : d.mcu_count);
             sg.lut_id = lut_id;
             seq += sg.seq_count;
             b->subseqs += sg.sub_count;
@@ -371,7 +373,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         b->img_of[i] = (int32_t)b->imgs.size();
         b->imgs.push_back(d);
         b->pixels += (uint64_t)d.width * d.height;
-        b->padded_pixels += (uint64_t)d.mcu_count * 64;
+        b->padded_pixels += (uint64_t)d.mcu_count * 64;   /* per component plane */
         b->scan_bytes += (uint64_t)ulen[i];
     }
     b->rgb_alloc = rgb_off;
@@ -381,7 +383,10 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     memset(&v, 0, sizeof(v));
     v.n_img = n_img;
     v.n_seg = (uint32_t)b->segs.size();
-    for (const GjdImage& im : b->imgs) v.any_interleaved |= im.layout == GJD_LAYOUT_INTERLEAVED;
+    for (const GjdImage& im : b->imgs) {
+        v.any_interleaved |= im.layout == GJD_LAYOUT_INTERLEAVED;
+        v.any_gray |= im.gray;
+    }
     v.n_seq = seq;
     v.sub_log2 = sub_log2;
     v.n_tile = tile;
@@ -798,7 +803,7 @@ int gjd_decode_coeffs(gjd_ctx* ctx, const uint8_t* jpg, size_t len, int16_t* coe
     if (rc == GJD_OK) rc = gjd_batch_sync(ctx, b);
     if (rc == GJD_OK || rc == GJD_E_CORRUPT) {
         int rc0 = rc;
-        size_t ncoef = (size_t)b->imgs[0].mcu_count * 192;
+        size_t ncoef = (size_t)b->imgs[0].mcu_count * (b->imgs[0].gray ? 64 : 192);
         DevBuf tmp;
         cudaError_t e = tmp.ensure(ncoef * sizeof(int16_t));
         if (e == cudaSuccess) e = gjd_launch_export_coefs(b->view, (int16_t*)tmp.p, b->stream);

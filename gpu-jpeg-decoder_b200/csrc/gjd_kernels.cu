@@ -378,6 +378,7 @@ __global__ void __launch_bounds__(256) k_dc_tilebase(GjdDevBatch b) {
                 sum[(i * 4 + 3) % 3] += (int)(int16_t)(v.w & 0xffffu);
             }
         }
+        if (d.gray) { sum[0] += sum[1] + sum[2]; sum[1] = sum[2] = 0; }   /* one component: one DC chain over the 96 blocks */
         int excl[3];
 #pragma unroll
         for (int c = 0; c < 3; c++) {
@@ -505,6 +506,7 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
 
     const uint32_t tid = threadIdx.x, c = tid >> 5, lane = tid & 31u;
     const GjdImage& d = b.imgs[b.tb_img[blockIdx.x]];
+    if (d.gray) return;   /* k_transform_gray's */
     const uint32_t ltb = blockIdx.x - d.tb_first;
     {
         const int* qg = reinterpret_cast<const int*>(b.quants + d.quant_id);
@@ -654,6 +656,126 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
     }
 }
 
+/* ------------------------------------------------------------------ transform: grayscale -- */
+/*
+ * Single-component images (beyond the reference's parser, which wants three components).
+ * One thread per 8x8 block, 96 consecutive blocks (one "tile" of the coefficient layout) per pass:
+ * block-wide inclusive scan of the DC differences (one predictor chain, restarted every restart_interval
+ * blocks), dequantise + IDCT in registers, then the reference's colour formula with Cb = Cr = 0
+ * (cpp-decoder/utils/color.cpp:10-16 gives R = G = B = clamp(Y + 128) up to its float rounding, which
+ * gjd_color reproduces) and 8-byte stores to the three planes (or interleaved rows).
+ */
+template <bool EXPORT>
+__global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_gray(GjdDevBatch b, int16_t* __restrict__ coef_out) {
+    __shared__ uint32_t sq[32];
+    __shared__ int wsum[3];
+    __shared__ int sincl[GJD_TRANSFORM_THREADS];
+    __shared__ int s_red;
+    const uint32_t tid = threadIdx.x, wid = tid >> 5, lane = tid & 31u;
+    const GjdImage& d = b.imgs[b.tb_img[blockIdx.x]];
+    if (!d.gray) return;
+    const uint32_t ltb = blockIdx.x - d.tb_first;
+    if (tid < 32u) sq[tid] = gjd_pack_quant(reinterpret_cast<const int*>(b.quants + d.quant_id), tid);
+    const uint32_t W = d.width, H = d.height, ri = d.restart_interval;
+    uint8_t* out = d.out_is_ptr ? reinterpret_cast<uint8_t*>(d.out_off) : b.rgb + d.out_off;
+    const size_t pitch = d.row_pitch, pstride = d.plane_stride;
+    const bool interleaved = d.layout == GJD_LAYOUT_INTERLEAVED;
+    const bool aligned = (((size_t)out | pitch | (interleaved ? 0 : pstride)) & 7u) == 0;
+    const uint32_t* meta_img = b.meta + (size_t)d.tile_first * 96u;
+
+#pragma unroll 1
+    for (uint32_t t = 0; t < GJD_TB_TILES; t++) {
+        const uint32_t ltile = ltb * GJD_TB_TILES + t;
+        if (ltile >= d.tile_count) break;
+        const uint32_t m0 = ltile * 96u, blkno = m0 + tid;       /* block number inside the image */
+        const bool valid = blkno < d.mcu_count;
+        const size_t blk = (size_t)d.tile_first * 96u + blkno;
+        const uint32_t m = valid ? __ldg(b.meta + blk) : 0u;
+        const uint32_t kmax = (m >> 16) & 63u;
+        const uint32_t nsec = kmax ? (kmax >> 4) + 1u : 0u;
+        const uint4* src = reinterpret_cast<const uint4*>(b.coef) + blk * 8u;
+        uint32_t w[32];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            uint4 r = make_uint4(0u, 0u, 0u, 0u);
+            if ((uint32_t)(j >> 1) < nsec) r = __ldcs(src + j);
+            w[4 * j] = r.x; w[4 * j + 1] = r.y; w[4 * j + 2] = r.z; w[4 * j + 3] = r.w;
+        }
+        /* inclusive scan of the DC differences over the 96 blocks of the tile */
+        int incl = warp_incl_scan_i((int)(int16_t)(m & 0xffffu), lane);
+        __syncthreads();                       /* previous pass done with wsum / sincl */
+        if (lane == 31u) wsum[wid] = incl;
+        __syncthreads();
+        if (wid >= 1u) incl += wsum[0];
+        if (wid >= 2u) incl += wsum[1];
+        const int p_tile = b.tilebase[d.tile_first + ltile].x;    /* plain running sum at the tile start */
+        int dc = incl + p_tile;
+        if (ri != 0u) {                        /* T.81 E.1.4: the predictor restarts every ri blocks */
+            sincl[tid] = incl;
+            const uint32_t ms = blkno - blkno % ri, ms0 = m0 - m0 % ri;
+            int p_ms0 = p_tile;
+            if (ms0 != m0) {                   /* block-uniform: the running interval began in an earlier tile */
+                const uint32_t j = ms0 / 96u, r = ms0 % 96u;
+                int v = tid < r ? (int)(int16_t)(__ldg(meta_img + (size_t)j * 96u + tid) & 0xffffu) : 0;
+                v = __reduce_add_sync(0xffffffffu, v);
+                if (tid == 0u) s_red = 0;
+                __syncthreads();
+                if (lane == 0u) atomicAdd(&s_red, v);
+                __syncthreads();
+                p_ms0 = b.tilebase[d.tile_first + j].x + s_red;
+            } else {
+                __syncthreads();
+            }
+            if (ms > m0) dc = incl - sincl[ms - m0 - 1u];
+            else if (ms == m0) dc = incl;
+            else dc = incl + p_tile - p_ms0;
+        }
+        if (EXPORT) {
+            if (valid) {   /* blocks in the reference's slot layout, as if they were the Y blocks of an image */
+                uint4* o = reinterpret_cast<uint4*>(coef_out + (size_t)blkno * 64u);
+                w[0] = (w[0] & 0xffff0000u) | ((uint32_t)dc & 0xffffu);
+#pragma unroll
+                for (int j = 0; j < 8; j++) o[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+            }
+            continue;
+        }
+        int v[64];
+        GjdUnpack<63, 64>::run(w, sq, v);
+        v[0] = dc * (int)(sq[0] & 0xffu);
+        gjd_idct8x8(v);
+        if (!valid) continue;
+        const uint32_t by = blkno / d.mcus_x, bx = blkno - by * d.mcus_x;
+        const uint32_t x0 = bx * 8u, y0 = by * 8u;
+        const bool fast = aligned && (x0 + 8u <= W);
+        uint8_t* rowp = out + (size_t)y0 * pitch + (interleaved ? (size_t)x0 * 3u : (size_t)x0);
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+            if (y0 + (uint32_t)r < H) {
+                uint64_t r8 = 0, g8 = 0, b8 = 0;
+#pragma unroll
+                for (int x = 0; x < 8; x++) {
+                    int R, G, B;
+                    gjd_color(v[8 * r + x], 256, 256, R, G, B);
+                    r8 |= (uint64_t)R << (8 * x); g8 |= (uint64_t)G << (8 * x); b8 |= (uint64_t)B << (8 * x);
+                }
+                uint8_t* row = rowp + (size_t)r * pitch;
+                if (fast && !interleaved) {
+                    __stcs(reinterpret_cast<uint2*>(row), make_uint2((uint32_t)r8, (uint32_t)(r8 >> 32)));
+                    __stcs(reinterpret_cast<uint2*>(row + pstride), make_uint2((uint32_t)g8, (uint32_t)(g8 >> 32)));
+                    __stcs(reinterpret_cast<uint2*>(row + 2 * pstride), make_uint2((uint32_t)b8, (uint32_t)(b8 >> 32)));
+                } else {
+#pragma unroll 1
+                    for (uint32_t x = 0; x < 8u && x0 + x < W; x++) {
+                        const uint8_t R = (uint8_t)(r8 >> (8u * x)), G = (uint8_t)(g8 >> (8u * x)), B = (uint8_t)(b8 >> (8u * x));
+                        if (interleaved) { row[3u * x] = R; row[3u * x + 1u] = G; row[3u * x + 2u] = B; }
+                        else { row[x] = R; row[pstride + x] = G; row[2 * pstride + x] = B; }
+                    }
+                }
+            }
+        }
+    }
+}
+
 /* ------------------------------------------------------------------ test hooks -------- */
 
 __global__ void k_test_color(const int16_t* __restrict__ y, const int16_t* __restrict__ cb,
@@ -739,6 +861,7 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     else if (transform_variant == 1) k_transform<false, 6, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
     else k_transform<false, 8, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
     n++;
+    if (b.any_gray) { k_transform_gray<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr); n++; }
     if (ev) GJD_CK(cudaEventRecord(ev->e[4], s));
     if (launches) *launches = n;
     return cudaGetLastError();
@@ -746,7 +869,8 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
 
 cudaError_t gjd_launch_export_coefs(const GjdDevBatch& b, int16_t* out, cudaStream_t s) {
     /* single-image batch: out is indexed by the image's own MCU numbers */
-    k_transform<true, 6, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, out);
+    if (b.any_gray) k_transform_gray<true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, out);
+    else k_transform<true, 6, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, out);
     return cudaGetLastError();
 }
 

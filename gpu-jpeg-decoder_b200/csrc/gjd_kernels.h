@@ -34,6 +34,7 @@ struct GjdDevBatch {
     uint32_t* tb_img;      /* [n_tb] transform block -> image */
     uint32_t n_tb;
     uint8_t* rgb;          /* output arena (images with out_is_ptr == 0) */
+    uint32_t any_gray;        /* some image is single-component: k_transform_gray is launched too */
     uint32_t any_interleaved; /* some image wants GJD_LAYOUT_INTERLEAVED: selects the transform kernel variant */
     uint32_t* status;      /* [n_img] GJD_DEV_* bits */
     uint32_t* nosync;      /* [1] sequences whose boundary fix-up ran off the end of the sequence */

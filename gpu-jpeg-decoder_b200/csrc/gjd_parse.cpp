@@ -89,16 +89,19 @@ int gjd_parse_headers(const uint8_t* d, size_t len, GjdParsed* o) {
                 uint32_t prec = body[0], nf = body[5];
                 o->height = (int32_t)be16(body + 1);
                 o->width = (int32_t)be16(body + 3);
-                if (prec != 8 || nf != 3) return GJD_E_UNSUPPORTED;
+                if (prec != 8 || (nf != 3 && nf != 1)) return GJD_E_UNSUPPORTED;
                 if (blen < 6 + 3 * nf) return GJD_E_FORMAT;
                 if (o->width <= 0 || o->height <= 0) return GJD_E_UNSUPPORTED;   /* DNL-defined height */
-                for (uint32_t c = 0; c < 3; c++) {
+                o->components = nf;
+                for (uint32_t c = 0; c < nf; c++) {
                     comp_id[c] = body[6 + 3 * c];
-                    if (body[7 + 3 * c] != 0x11) return GJD_E_UNSUPPORTED;      /* 4:4:4 only */
+                    /* 4:4:4 only; a single component has one block per MCU whatever its factors say (T.81 A.2.2) */
+                    if (nf == 3 && body[7 + 3 * c] != 0x11) return GJD_E_UNSUPPORTED;
                     uint32_t tq = body[8 + 3 * c];
                     if (tq > 3) return GJD_E_FORMAT;
                     o->qsel[c] = (uint8_t)tq;
                 }
+                if (nf == 1) o->qsel[1] = o->qsel[2] = o->qsel[0];
                 have_sof = true;
                 break;
             }
@@ -113,15 +116,19 @@ int gjd_parse_headers(const uint8_t* d, size_t len, GjdParsed* o) {
                 if (!have_sof) return GJD_E_FORMAT;
                 if (blen < 1) return GJD_E_FORMAT;
                 uint32_t ns = body[0];
-                if (ns != 3) return GJD_E_UNSUPPORTED;   /* non-interleaved / multi-scan */
+                if (ns != o->components) return GJD_E_UNSUPPORTED;   /* non-interleaved / multi-scan */
                 if (blen < 1 + 2 * ns + 3) return GJD_E_FORMAT;
-                for (uint32_t c = 0; c < 3; c++) {
+                for (uint32_t c = 0; c < ns; c++) {
                     if (body[1 + 2 * c] != comp_id[c]) return GJD_E_UNSUPPORTED;
                     uint32_t td = body[2 + 2 * c] >> 4, ta = body[2 + 2 * c] & 15;
                     if (td > 1 || ta > 1) return GJD_E_UNSUPPORTED;
                     if (!o->dht_seen[td] || !o->dht_seen[2 + ta]) return GJD_E_FORMAT;
                     o->tabsel[c] = (uint8_t)td;
                     o->tabsel[4 + c] = (uint8_t)(2 + ta);
+                }
+                if (ns == 1) {   /* grayscale: the one table pair serves all three ring positions */
+                    o->tabsel[1] = o->tabsel[2] = o->tabsel[0];
+                    o->tabsel[5] = o->tabsel[6] = o->tabsel[4];
                 }
                 const uint8_t* sp = body + 1 + 2 * ns;
                 if (sp[0] != 0 || sp[1] != 63 || sp[2] != 0) return GJD_E_UNSUPPORTED;

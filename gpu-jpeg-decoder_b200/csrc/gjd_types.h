@@ -124,6 +124,10 @@ typedef struct GjdImage {
     uint16_t quant_id;      /* index into the GjdQuantSet array                                */
     uint16_t layout;        /* GJD_LAYOUT_PLANAR / GJD_LAYOUT_INTERLEAVED (include/gjd.h)        */
     uint32_t out_is_ptr;    /* out_off is an absolute device address (caller-owned buffer)     */
+    uint32_t gray;          /* single-component image: mcu_count blocks in one DC chain, tiles of 96 blocks,
+                               decoded by k_transform_gray (the entropy kernels see three ring positions that
+                               all use the one table pair)                                    */
+    uint32_t pad1;
 } GjdImage;
 
 /* Device-written status bits per image. */

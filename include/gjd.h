@@ -30,7 +30,7 @@ typedef enum gjd_status {
     GJD_E_NOMEM       = -3,  /* host or device allocation failed                            */
     GJD_E_FORMAT      = -4,  /* not a JPEG, truncated, or a marker segment is malformed     */
     GJD_E_UNSUPPORTED = -5,  /* valid JPEG outside the contract: progressive, arithmetic,
-                                12-bit, subsampled, != 3 components, multi-scan               */
+                                12-bit, subsampled, 2 or 4 components, multi-scan             */
     GJD_E_CORRUPT     = -6,  /* entropy-coded data is inconsistent (bad code / wrong count) */
     GJD_E_NODEVICE    = -7,  /* no usable CUDA device: the product has no CPU fallback      */
     GJD_E_IO          = -8   /* file could not be read / written (writers only)             */
@@ -83,6 +83,8 @@ int  gjd_peek(const uint8_t* jpg, size_t len, int32_t* width, int32_t* height);
 
 /* Decode n images end to end: marker parse + byte-unstuffing on the host, H2D, entropy decode,
  * dezigzag+dequant+IDCT+colour on the GPU, D2H into items[i].rgb (skipped for rgb_on_device).
+ * Single-component (grayscale) files are decoded too (R = G = B from the reference's colour formula with
+ * Cb = Cr = 0); the reference's parser wants exactly three components.
  * Restart markers (DRI/RSTn) are decoded (every restart interval is an independent segment for the
  * entropy kernels; DC predictors restart) — a superset of the reference's parser, which keeps FF Dn as
  * scan data (cpp-decoder/src/parser.cpp:84-96).
@@ -117,7 +119,7 @@ int  gjd_batch_info(gjd_ctx* ctx, gjd_batch* b, uint64_t info[5]);
 /* Quantised coefficients of one image, int16, zigzag order, absolute DC, layout
  * coeffs[mcu*192 + comp*64 + k] over ceil(W/8)*ceil(H/8) MCUs — the layout of the reference's device
  * buffer after parallelHuffManDecode (cuda-decoder/src/parser.cu:132-208, index at :538).
- * Test hook for the "bit-exact Huffman coefficients" gate. */
+ * Test hook for the "bit-exact Huffman coefficients" gate.  Grayscale files: coeffs[block*64 + k]. */
 int  gjd_decode_coeffs(gjd_ctx* ctx, const uint8_t* jpg, size_t len, int16_t* coeffs_host);
 
 /* Device times (ms, CUDA events on the context stream) of the last gjd_batch_run / the last sub-batch

@@ -88,7 +88,7 @@ class HostSim:
         if rc != 0:
             return rc, None, None, None
         nm = ((W + 7) // 8) * ((H + 7) // 8)
-        coef = np.zeros(nm * 192, np.int16)
+        coef = np.zeros(nm * 192, np.int16)      # grayscale files fill the first nm * 64
         rgb = np.zeros((3, H, W), np.uint8)
         stats = np.zeros(8, np.uint32)
         w, h = C.c_int32(), C.c_int32()
@@ -128,6 +128,20 @@ def rst_golden():
         with open(f, "rb") as fh:
             out[os.path.basename(f)[:-4]] = fh.read()
     return out
+
+
+@pytest.fixture(scope="session")
+def gray_golden():
+    out = {}
+    for f in sorted(glob.glob(os.path.join(GOLDEN, "gray", "*.jpg"))):
+        with open(f, "rb") as fh:
+            out[os.path.basename(f)[:-4]] = fh.read()
+    return out
+
+
+@pytest.fixture(scope="session")
+def ref_outputs_gray():
+    return np.load(os.path.join(GOLDEN, "ref_outputs_gray.npz"))
 
 
 @pytest.fixture(scope="session")

@@ -70,7 +70,9 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     memcpy(scanw.data(), scanbuf.data(), scanbuf.size());
     const uint32_t W = (uint32_t)p.width, H = (uint32_t)p.height;
     const uint32_t mcus_x = (W + 7) / 8, mcu_count = mcus_x * ((H + 7) / 8);
-    const uint32_t tile_count = (mcu_count + 31) / 32;
+    const bool gray = p.components == 1;
+    const uint32_t bpm = gray ? 1u : 3u;                       /* 8x8 blocks per MCU */
+    const uint32_t tile_count = (mcu_count * bpm + 95) / 96;
     const uint32_t ri = p.restart_interval;
     if (!ri && seg_off.size() != 1) return GJD_E_UNSUPPORTED;          /* RSTn without DRI */
     if (ri && seg_off.size() != (mcu_count + ri - 1) / ri) return GJD_E_CORRUPT;
@@ -113,8 +115,8 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     for (size_t sgi = 0; sgi < seg_off.size(); sgi++) {
     const uint32_t* scan = scanw.data() + seg_off[sgi] / 4;
     const uint32_t scan_bits = seg_len[sgi] * 8u;
-    const uint32_t blk0 = 3u * ri * (uint32_t)sgi;
-    const uint32_t blk_count = 3u * (ri ? std::min(ri, mcu_count - ri * (uint32_t)sgi) : mcu_count);
+    const uint32_t blk0 = bpm * ri * (uint32_t)sgi;
+    const uint32_t blk_count = bpm * (ri ? std::min(ri, mcu_count - ri * (uint32_t)sgi) : mcu_count);
     const uint32_t sub_count = std::max<uint32_t>(1u, (uint32_t)(((uint64_t)scan_bits + S - 1) / S));
     const uint32_t seq_count = (sub_count + GJD_SEQ_SUBS - 1) / GJD_SEQ_SUBS;
     sub_total += sub_count; seq_total += seq_count;
@@ -227,14 +229,44 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
         }
     }
     }   /* segments */
-    for (uint32_t bk = 0; bk < 3u * mcu_count; bk++) if (written[bk] != 1) status |= GJD_DEV_BADCOUNT;
+    for (uint32_t bk = 0; bk < bpm * mcu_count; bk++) if (written[bk] != 1) status |= GJD_DEV_BADCOUNT;
     if (badcode) status |= GJD_DEV_BADCODE;
     /* k_dc_tilebase + k_transform */
     int q[3][64];
     for (int c = 0; c < 3; c++)
         for (int k = 0; k < 64; k++) q[c][k] = p.quant[p.qsel[c]][k];
     int pred[3] = {0, 0, 0};
-    for (uint32_t mcu = 0; mcu < mcu_count; mcu++) {
+    /* k_transform_gray: one block per MCU, one DC chain, colour formula with Cb = Cr = 0 */
+    for (uint32_t bkn = 0; gray && bkn < mcu_count; bkn++) {
+        if (ri && bkn % ri == 0) pred[0] = 0;
+        uint32_t m = meta[bkn];
+        uint32_t kmax = (m >> 16) & 63u;
+        uint32_t nsec = kmax ? (kmax >> 4) + 1u : 0u;
+        int zq[64] = {0};
+        for (uint32_t k = 0; k < nsec * 16u; k++) zq[k] = coef[(size_t)bkn * 64 + k];
+        pred[0] += (int)(int16_t)(m & 0xffffu);
+        int v[64];
+        for (int i = 0; i < 64; i++) v[i] = zq[kZZ[i]] * q[0][kZZ[i]];
+        v[0] = pred[0] * q[0][0];
+        if (coef_out)
+            for (int k = 0; k < 64; k++) coef_out[(size_t)bkn * 64 + k] = (int16_t)(k == 0 ? pred[0] : zq[k]);
+        gjd_idct8x8(v);
+        if (rgb_out) {
+            uint32_t by = bkn / mcus_x, bx = bkn % mcus_x;
+            for (int r = 0; r < 8; r++)
+                for (int x = 0; x < 8; x++) {
+                    uint32_t py = by * 8 + r, px = bx * 8 + x;
+                    if (py >= H || px >= W) continue;
+                    int R, G, B;
+                    gjd_color(v[8 * r + x], 256, 256, R, G, B);
+                    size_t o = (size_t)py * W + px;
+                    rgb_out[o] = (uint8_t)R;
+                    rgb_out[(size_t)W * H + o] = (uint8_t)G;
+                    rgb_out[2 * (size_t)W * H + o] = (uint8_t)B;
+                }
+        }
+    }
+    for (uint32_t mcu = 0; !gray && mcu < mcu_count; mcu++) {
         int samples[3][64];
         if (ri && mcu % ri == 0) pred[0] = pred[1] = pred[2] = 0;   /* T.81 E.1.4 */
         for (int c = 0; c < 3; c++) {

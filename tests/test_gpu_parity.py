@@ -288,3 +288,29 @@ def test_interleaved_resident_fetch_and_pitch(decoder, golden, ref_outputs):
     items[0].row_pitch = 3 * w - 1                       # too small
     decoder.decode_batch_raw(items, 1)
     assert items[0].status == gjd.E_ARG
+
+
+def test_grayscale_bit_exact(decoder, golden, ref_outputs, gray_golden, ref_outputs_gray):
+    """Single-component files (outside the reference's parser), alone and mixed into a batch
+    with colour files, planar and interleaved: blocks = the Y blocks of the colour twin per the unmodified
+    reference, pixels = those blocks through the oracle's IDCT + colour formula with Cb = Cr = 0."""
+    import gjd
+    gn = sorted(gray_golden)
+    assert len(gn) >= 6
+    for n in gn:
+        coef, w, h = decoder.decode_coeffs(gray_golden[n])
+        want = ref_outputs_gray[n + "/coef"]
+        assert np.array_equal(coef[: want.size], want), n
+    files, want = [], []
+    for i, n in enumerate(gn):
+        files.append(gray_golden[n]); want.append(ref_outputs_gray[n + "/rgb"])
+        p = NAMES[i % len(NAMES)]
+        files.append(golden[p]); want.append(ref_outputs[p + "/rgb"])
+    outs, st = decoder.decode(files)
+    assert st == [0] * len(files)
+    for o, w_ in zip(outs, want):
+        assert np.array_equal(o, w_)
+    outs, st = decoder.decode(files, layout=gjd.INTERLEAVED)
+    assert st == [0] * len(files)
+    for o, w_ in zip(outs, want):
+        assert np.array_equal(o, w_.transpose(1, 2, 0))

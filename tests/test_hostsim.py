@@ -66,7 +66,7 @@ def test_parser_contract(hostsim, golden):
     assert hostsim.parse(ok)[0] == 0
     assert hostsim.parse(enc("-sample", "2x2"))[0] == -5          # subsampled
     assert hostsim.parse(enc("-sample", "1x1", "-progressive"))[0] == -5
-    assert hostsim.parse(enc("-grayscale"))[0] == -5
+    assert hostsim.parse(enc("-grayscale"))[0] == 0                 # single component accepted
     assert hostsim.parse(enc("-sample", "1x1", "-restart", "1"))[0] == 0    # DRI/RSTn accepted
     assert hostsim.parse(enc("-sample", "1x1", "-arithmetic"))[0] == -5
     assert hostsim.parse(ok[:100])[0] == -4                       # truncated header
@@ -162,3 +162,17 @@ def test_pair_counting_equals_single_symbol_counting(hostsim, golden, rst_golden
             if sub_log2 == 12:
                 syms += int(out[2]); trips += int(out[3])
     assert trips < 0.9 * syms        # the pairs do shorten the loop
+
+
+def test_grayscale_matches_reference_pieces(hostsim, gray_golden, ref_outputs_gray):
+    """Single-component files (outside the reference's parser): blocks equal the Y blocks the unmodified
+    reference reports for the colour twin, pixels equal those blocks through the oracle's IDCT and colour
+    formula with Cb = Cr = 0 (tools/make_golden_gray.py).  Restart files included."""
+    assert len(gray_golden) >= 6
+    for name, data in sorted(gray_golden.items()):
+        for sub_log2 in (0, 8):
+            rc, coef, rgb, stats = hostsim.decode(data, sub_log2)
+            assert rc == 0 and stats[2] == 0, (name, rc, list(stats))
+            want = ref_outputs_gray[name + "/coef"]
+            assert np.array_equal(coef[: want.size], want), name
+            assert np.array_equal(rgb, ref_outputs_gray[name + "/rgb"]), name

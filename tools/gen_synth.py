@@ -46,7 +46,7 @@ def make_image(seed, w, h):
     return np.clip(img, 0, 255).astype(np.uint8)
 
 
-def encode(img, quality=90, optimize=False, restart=0):
+def encode(img, quality=90, optimize=False, restart=0, grayscale=False):
     """RGB uint8 (H,W,3) -> JPEG bytes via vendored cjpeg."""
     h, w, _ = img.shape
     ppm = b"P6\n%d %d\n255\n" % (w, h) + img.tobytes()
@@ -55,6 +55,8 @@ def encode(img, quality=90, optimize=False, restart=0):
         cmd.append("-optimize")
     if restart:
         cmd += ["-restart", str(restart)]
+    if grayscale:
+        cmd.append("-grayscale")
     env = dict(os.environ, LD_LIBRARY_PATH=os.path.join(LIBJPEG, "lib"))
     return subprocess.run(cmd, input=ppm, stdout=subprocess.PIPE, check=True, env=env).stdout
 
