@@ -18,6 +18,9 @@ no data-path collective — torch.distributed is used for the barr
   cpu_baseline / --impl reference
             the UNMODIFIED reference cpp-decoder (oracle/_ref/ref_bench: JPEGParser::extract+decode, the
             timed region of cpp-decoder/benchmark/benchmark.cc:31-35) on all host cores, bounded sample.
+  cpu_baseline_jpeglib
+            the IJG libjpeg 9e the reference vendors, in process on all host cores (oracle/_ref/jpeglib_bench),
+            a second, reported-only baseline.
 """
 import argparse
 import json
@@ -97,6 +100,15 @@ class ClockSampler:
 
 def ref_bench(threads, seconds, files_on_disk):
     exe = os.path.join(ROOT, "oracle", "_ref", "ref_bench")
+    out = subprocess.run([exe, str(threads), str(seconds), *files_on_disk], stdout=subprocess.PIPE, check=True, text=True)
+    return json.loads(out.stdout.strip().splitlines()[-1])
+
+
+def jpeglib_bench(threads, seconds, files_on_disk):
+    """Second CPU baseline: the IJG libjpeg 9e the reference vendors, in process, all host cores."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "jpeglib_bench")
+    if not os.path.exists(exe):
+        return None
     out = subprocess.run([exe, str(threads), str(seconds), *files_on_disk], stdout=subprocess.PIPE, check=True, text=True)
     return json.loads(out.stdout.strip().splitlines()[-1])
 
@@ -308,6 +320,13 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             cb, _ = cpu_reference(float(os.environ.get("GJD_CPU_BASELINE_SECONDS", "12")), base, len(base))
             line["cpu_baseline"] = cb
+            paths = [os.path.join(gen_synth.CACHE, "s%d_1024x1024_q90_o0_r0.jpg" % s) for s in range(len(base))]
+            if all(os.path.exists(p) for p in paths):
+                jl = jpeglib_bench(cb["cores"], float(os.environ.get("GJD_JPEGLIB_BASELINE_SECONDS", "6")), paths)
+                if jl:
+                    line["cpu_baseline_jpeglib"] = {
+                        "value": round(jl["mpix_per_s"], 3), "unit": UNIT, "cores": cb["cores"], "kind": "reference-vendored libjpeg 9e",
+                        "sample": "%d images of the c3 set, %.1f s busy per thread, jpeg_read_header..jpeg_finish_decompress timed (RGB out, JDCT_ISLOW)" % (jl["images"], jl["busy_s_max"])}
         print(json.dumps(line), flush=True)
     pinned.free()
     dec.close()
