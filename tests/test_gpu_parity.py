@@ -314,3 +314,33 @@ def test_grayscale_bit_exact(decoder, golden, ref_outputs, gray_golden, ref_outp
     assert st == [0] * len(files)
     for o, w_ in zip(outs, want):
         assert np.array_equal(o, w_.transpose(1, 2, 0))
+
+
+def test_mixed_sizes_batch_independence(decoder, oracle):
+    """BASELINE config 5 shape at reduced count: sizes 256..2048 (one ragged), q 75..95, some with optimised
+    tables, sharded by gjd_partition into two parts.  Each part decoded as one batch must equal every image
+    decoded alone (no cross-image state), and a sample must equal the oracle."""
+    import gen_synth
+    import gjd
+    if not gen_synth.have_cjpeg():
+        pytest.skip("vendored cjpeg missing")
+    dims = [(256, 256), (512, 512), (2048, 2048), (1024, 1024), (640, 360), (1531, 1021), (2048, 1024), (384, 1536)]
+    files = [gen_synth.synth_jpeg(300 + i, w, h, 75 + 5 * (i % 5), i % 3 == 0) for i, (w, h) in enumerate(dims)] * 3
+    part, load, weight = gjd.partition(files, 2)
+    part, load = [int(q) for q in part], [int(v) for v in load]
+    assert sorted(set(part)) == [0, 1] and sum(load) == int(weight.sum())
+    assert max(load) - min(load) <= int(weight.max())          # LPT: imbalance below one item
+    whole = {}
+    for p in (0, 1):
+        idx = [i for i, q in enumerate(part) if q == p]
+        outs, st = decoder.decode([files[i] for i in idx])
+        assert st == [0] * len(idx)
+        whole.update(dict(zip(idx, outs)))
+    for i in range(len(dims)):
+        alone, st = decoder.decode([files[i]])
+        assert st == [0]
+        for rep in range(3):
+            assert np.array_equal(whole[i + rep * len(dims)], alone[0])
+    for i in (2, 5):
+        rc, _, rgb, _, W, H = oracle.decode(files[i], want_coef=False)
+        assert rc == 0 and np.array_equal(whole[i], rgb)
