@@ -344,3 +344,34 @@ def test_mixed_sizes_batch_independence(decoder, oracle):
     for i in (2, 5):
         rc, _, rgb, _, W, H = oracle.decode(files[i], want_coef=False)
         assert rc == 0 and np.array_equal(whole[i], rgb)
+
+
+def test_fuzz_differential_vs_hostsim(decoder, hostsim, golden, rst_golden, gray_golden):
+    """300 damaged files (bit flips, cuts, inserts, stray markers, truncation; headers and entropy data), decoded
+    in batches between two intact files: every status equals the one the same functions give when stepped on
+    the CPU (tests/hostsim), files that still decode give the same pixels, and the intact neighbours stay
+    bit-exact — damage never leaks across images."""
+    import fuzzlib
+    seeds = ([golden[n] for n in ("images/3_120x120", "images/5_200x200", "images/6_225x168")] + list(rst_golden.values())
+             + list(gray_golden.values()))
+    good = golden["images/3_120x120"]
+    want_good, st = decoder.decode([good])
+    assert st == [0]
+    bad = []
+    for f in fuzzlib.cases(seeds, 300, 23):
+        rc, w, h = hostsim.parse(f)
+        if rc != 0 or w * h <= 1 << 20:       # a damaged SOF may ask for gigapixels: not this test
+            bad.append(f)
+    seen = set()
+    for first in range(0, len(bad), 50):
+        part = bad[first : first + 50]
+        outs, st = decoder.decode([good] + part + [good])
+        assert st[0] == 0 and st[-1] == 0
+        assert np.array_equal(outs[0], want_good[0]) and np.array_equal(outs[-1], want_good[0])
+        for f, o, s in zip(part, outs[1:-1], st[1:-1]):
+            rc, _, rgb, _ = hostsim.decode(f)
+            assert s == rc, (s, rc)
+            seen.add(rc)
+            if rc == 0:
+                assert np.array_equal(o, rgb)
+    assert {0, -4, -6} <= seen

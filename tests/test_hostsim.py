@@ -1,10 +1,14 @@
 """CPU checks of the product's own arithmetic and algorithm (no GPU): the __host__ __device__
 functions of gpu-jpeg-decoder_b200/csrc/gjd_devfn.cuh and the host parser, stepped by tests/hostsim in the
 order the kernels run them, against the oracle and the golden vectors."""
+import glob
+import os
+import subprocess
+
 import numpy as np
 import pytest
 
-from conftest import golden_files
+from conftest import ROOT, golden_files
 
 NAMES = sorted(golden_files())
 
@@ -176,3 +180,47 @@ def test_grayscale_matches_reference_pieces(hostsim, gray_golden, ref_outputs_gr
             want = ref_outputs_gray[name + "/coef"]
             assert np.array_equal(coef[: want.size], want), name
             assert np.array_equal(rgb, ref_outputs_gray[name + "/rgb"]), name
+
+
+def _fuzz_seed_files(golden, rst_golden, gray_golden):
+    return ([golden[n] for n in ("images/3_120x120", "images/5_200x200", "images/6_225x168")] + list(rst_golden.values())
+            + list(gray_golden.values()))
+
+
+def test_fuzz_under_address_sanitizer(tmp_path):
+    """Mutation fuzzer over the parser and the device functions stepped on the CPU, built with
+    -fsanitize=address: a damaged file ends in a status code, never in an out-of-bounds access or a hang."""
+    d = os.path.join(ROOT, "tests", "hostsim")
+    exe = str(tmp_path / "fuzz_main")
+    r = subprocess.run(["g++", "-O1", "-g", "-std=c++17", "-ffp-contract=off", "-fsanitize=address", "-Wno-unknown-pragmas",
+                        "-o", exe, os.path.join(d, "fuzz_main.cpp"), os.path.join(d, "hostsim.cpp"),
+                        os.path.join(ROOT, "gpu-jpeg-decoder_b200", "csrc", "gjd_parse.cpp")], capture_output=True, text=True)
+    if r.returncode != 0 and "asan" in r.stderr.lower():
+        pytest.skip("libasan not installed")
+    assert r.returncode == 0, r.stderr[-2000:]
+    files = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "rst", "*.jpg")) +
+                   glob.glob(os.path.join(ROOT, "tests", "golden", "gray", "*.jpg")))
+    files += [os.path.join(ROOT, "tests", "golden", "images", n) for n in ("3_120x120.jpg", "5_200x200.jpg")]
+    r = subprocess.run([exe, "3000", "7", *files], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
+    words = r.stdout.split()
+    got = {words[i]: int(words[i + 1]) for i in range(0, len(words), 2)}
+    assert got["cases"] == 3000 and got["ok"] > 0 and got["corrupt"] > 0 and got["header"] > 0
+
+
+def test_fuzz_statuses_are_deterministic(hostsim, golden, rst_golden, gray_golden):
+    """The same damaged file gives the same status (and, when it still decodes, the same pixels) for two
+    subsequence lengths: flagged or not never depends on how the scan was cut up."""
+    import fuzzlib
+    n_ok = 0
+    for f in fuzzlib.cases(_fuzz_seed_files(golden, rst_golden, gray_golden), 150, 11):
+        rc, w, h = hostsim.parse(f)
+        if rc != 0 or w * h > 1 << 20:
+            continue
+        a = hostsim.decode(f, 8)
+        b = hostsim.decode(f, 11)
+        assert a[0] == b[0] and a[0] in (0, -4, -5, -6)     # -4/-5: the unstuffer met a stray marker
+        if a[0] == 0:
+            n_ok += 1
+            assert np.array_equal(a[2], b[2])
+    assert n_ok > 5
