@@ -18,6 +18,7 @@
 #include <functional>
 #include <mutex>
 #include <string>
+#include <chrono>
 #include <thread>
 #include <unordered_map>
 #include <vector>
@@ -640,18 +641,21 @@ int gjd_decode_batch(gjd_ctx* ctx, gjd_item* items, int32_t n) {
     std::vector<ItemGeom> geom;
     parse_all(ctx, items, n, parsed, geom);
 
-    /* sub-batches under the scratch budget, alternating between the two slots */
+    /* sub-batches under the scratch budget, alternating between the two slots.  The call is bound by the
+     * device-to-host link, which idles until the first sub-batch has been unstuffed, uploaded and decoded:
+     * the first sub-batch gets 1/16 of the budget and the following ones double up to the full budget. */
     struct Span { int32_t first, count; };
     std::vector<Span> spans;
     {
-        size_t acc = 0;
+        size_t acc = 0, cap = std::max<size_t>(ctx->scratch >> 4, (size_t)64 << 20);
         int32_t first = 0;
         for (int32_t i = 0; i < n; i++) {
             size_t need = geom[i].status == GJD_OK ? estimate_bytes(items[i], geom[i]) : 0;
-            if (i > first && acc + need > ctx->scratch) {
+            if (i > first && acc + need > std::min(cap, ctx->scratch)) {
                 spans.push_back({first, i - first});
                 first = i;
                 acc = 0;
+                cap *= 2;
             }
             acc += need;
         }
