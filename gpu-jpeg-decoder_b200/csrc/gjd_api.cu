@@ -149,6 +149,9 @@ struct ItemGeom {
 
 }  // namespace
 
+/* sub-batches in flight inside gjd_decode_batch: one being staged by the host, one uploading, one in the kernels */
+#define GJD_SLOTS 3
+
 /* ---------------------------------------------------------------- batch (one slot) ---- */
 
 struct gjd_batch {
@@ -187,7 +190,7 @@ struct gjd_ctx {
     int device = 0;
     size_t scratch = 0;
     Pool* pool = nullptr;
-    gjd_batch slot[2];
+    gjd_batch slot[GJD_SLOTS];
     gjd_batch* last = nullptr;     /* batch whose stage events gjd_stage_times reports */
     std::string cuda_err;
     int transform_variant = 0;
@@ -247,7 +250,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     std::vector<size_t> soff(n + 1, 0);
     for (int32_t i = 0; i < n; i++)
         soff[i + 1] = soff[i] + (b->geom[i].status == GJD_OK
-                                     ? align_up(items[i].len + 16 + (parsed[i].restart_interval ? items[i].len / 2 + 64 : 0), 128)
+                                     ? align_up(items[i].len + 64 + (parsed[i].restart_interval ? items[i].len / 2 + 64 : 0), 128)
                                      : 0);
     b->scan_alloc = soff[n] + 256;
     GJD_TRY(b->h_scan.ensure(b->scan_alloc));
@@ -641,7 +644,7 @@ int gjd_decode_batch(gjd_ctx* ctx, gjd_item* items, int32_t n) {
     std::vector<ItemGeom> geom;
     parse_all(ctx, items, n, parsed, geom);
 
-    /* sub-batches under the scratch budget, alternating between the two slots.  The call is bound by the
+    /* sub-batches under the scratch budget, rotating through the GJD_SLOTS slots.  The call is bound by the
      * device-to-host link, which idles until the first sub-batch has been unstuffed, uploaded and decoded:
      * the first sub-batch gets 1/16 of the budget and the following ones double up to the full budget. */
     struct Span { int32_t first, count; };
@@ -662,7 +665,8 @@ int gjd_decode_batch(gjd_ctx* ctx, gjd_item* items, int32_t n) {
         spans.push_back({first, n - first});
     }
     int rc = GJD_OK;
-    int32_t pending[2] = {-1, -1};   /* span index in flight on each slot */
+    int32_t pending[GJD_SLOTS];      /* span index in flight on each slot */
+    for (int s = 0; s < GJD_SLOTS; s++) pending[s] = -1;
     auto finish = [&](int s) -> int {
         if (pending[s] < 0) return GJD_OK;
         gjd_batch* b = &ctx->slot[s];
@@ -679,7 +683,7 @@ int gjd_decode_batch(gjd_ctx* ctx, gjd_item* items, int32_t n) {
         return GJD_OK;
     };
     for (size_t k = 0; k < spans.size() && rc == GJD_OK; k++) {
-        int s = (int)(k & 1);
+        int s = (int)(k % GJD_SLOTS);
         rc = finish(s);
         if (rc) break;
         gjd_batch* b = &ctx->slot[s];
@@ -691,7 +695,7 @@ int gjd_decode_batch(gjd_ctx* ctx, gjd_item* items, int32_t n) {
         rc = enqueue_d2h(ctx, b, items + sp.first);
         pending[s] = (int32_t)k;
     }
-    for (int s = 0; s < 2; s++) {
+    for (int s = 0; s < GJD_SLOTS; s++) {
         int r2 = finish(s);
         if (rc == GJD_OK) rc = r2;
     }

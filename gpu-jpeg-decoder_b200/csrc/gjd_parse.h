@@ -35,7 +35,8 @@ int gjd_parse_headers(const uint8_t* jpg, size_t len, GjdParsed* out);
 
 /* Copy the entropy-coded segment [src, end) to dst, removing the stuffed 0x00 after every 0xFF and
  * stopping at EOI (FF D9), exactly like the byte loop at cpp-decoder/src/parser.cpp:84-99 (and its
- * twin cuda-decoder/src/parser.cu:450-462).  dst needs (end - src) bytes.  Returns the unstuffed
+ * twin cuda-decoder/src/parser.cu:450-462).  dst needs (end - src) + 32 bytes (the copy runs 32 bytes at a time
+ * and stores before it tests).  Returns the unstuffed
  * length, or a negative gjd_status (truncated scan, RSTn, any other marker inside the scan). */
 long gjd_unstuff(const uint8_t* src, const uint8_t* end, uint8_t* dst);
 
@@ -43,7 +44,7 @@ long gjd_unstuff(const uint8_t* src, const uint8_t* end, uint8_t* dst);
  * keeps FF Dn as data, cpp-decoder/src/parser.cpp:84-96): every RSTn ends a restart interval, is checked
  * against the 0..7 cycle and removed; the next interval is written at the next 4-byte boundary of dst.
  * seg_off/seg_len receive the byte offset and length of every interval (one entry for a scan without
- * restarts).  dst needs (end - src) + (end - src) / 2 bytes.  Returns the bytes used in dst. */
+ * restarts).  dst needs (end - src) + (end - src) / 2 + 32 bytes.  Returns the bytes used in dst. */
 long gjd_unstuff_segments(const uint8_t* src, const uint8_t* end, uint8_t* dst, std::vector<uint32_t>* seg_off,
                           std::vector<uint32_t>* seg_len);
 
