@@ -274,8 +274,9 @@ def main():
     barrier()
     assert all(items[i].status == 0 for i in range(0, args.images, 97))
     assert int(pinned.array[-out_bytes:].max()) > 0
-    h2d = sum(len(f) for f in files)   # upper bound of the unstuffed scans + tables actually copied
-    d2h = out_bytes * args.images
+    # whole-job bytes per step, like the values they sit beside (every rank copies its own shard)
+    h2d = sum(len(f) for f in files) * world   # upper bound of the unstuffed scans + tables actually copied
+    d2h = out_bytes * args.images * world
 
     # ---- the same call with the pixels left in HBM (rgb_on_device: the data-loader use; extra key) ---
     dev_out = torch.zeros(out_bytes * args.images, dtype=torch.uint8, device="cuda")
