@@ -135,6 +135,14 @@ int gjd_parse_headers(const uint8_t* d, size_t len, GjdParsed* o) {
                 for (uint32_t c = 0; c < 3; c++)
                     if (!o->quant_seen[o->qsel[c]]) return GJD_E_FORMAT;
                 o->scan_begin = d + pos + seg;
+                {
+                    /* a block costs at least 2 bits (a 1-bit DC size code and a 1-bit EOB): a frame header that
+                     * announces more blocks than the remaining bytes can hold is damaged — refused here so that it
+                     * cannot ask for gigabytes of coefficient memory */
+                    const uint64_t mcus = (uint64_t)((o->width + 7) / 8) * (uint64_t)((o->height + 7) / 8);
+                    const uint64_t blocks = mcus * (o->components == 1 ? 1u : 3u);
+                    if (blocks * 2u > (uint64_t)(o->file_end - o->scan_begin) * 8u) return GJD_E_CORRUPT;
+                }
                 return GJD_OK;
             }
             default:

@@ -31,7 +31,8 @@ typedef enum gjd_status {
     GJD_E_FORMAT      = -4,  /* not a JPEG, truncated, or a marker segment is malformed     */
     GJD_E_UNSUPPORTED = -5,  /* valid JPEG outside the contract: progressive, arithmetic,
                                 12-bit, subsampled, 2 or 4 components, multi-scan             */
-    GJD_E_CORRUPT     = -6,  /* entropy-coded data is inconsistent (bad code / wrong count) */
+    GJD_E_CORRUPT     = -6,  /* entropy-coded data is inconsistent (bad code / wrong count /
+                                frame header announcing more blocks than the scan can hold) */
     GJD_E_NODEVICE    = -7,  /* no usable CUDA device: the product has no CPU fallback      */
     GJD_E_IO          = -8   /* file could not be read / written (writers only)             */
 } gjd_status;

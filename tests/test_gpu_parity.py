@@ -86,6 +86,11 @@ def test_error_statuses(decoder, golden):
     bad = bytes(data[:mid] + data[mid + 301 :])
     outs, st = decoder.decode([good, bad, good])
     assert st[0] == 0 and st[2] == 0 and st[1] in (-6, -4)
+    # a frame header announcing 65535 x 65535 over a 7 KB scan: refused per image, no arena is sized from it
+    at = good.find(b"\xff\xc0")
+    huge = good[: at + 5] + b"\xff\xff\xff\xff" + good[at + 9 :]
+    outs, st = decoder.decode([good, huge, good])
+    assert st == [0, -6, 0] and outs[1] is None and np.array_equal(outs[0], outs[2])
 
 
 def test_empty_batch(decoder):

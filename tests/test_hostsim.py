@@ -224,3 +224,20 @@ def test_fuzz_statuses_are_deterministic(hostsim, golden, rst_golden, gray_golde
             n_ok += 1
             assert np.array_equal(a[2], b[2])
     assert n_ok > 5
+
+
+def test_oversized_frame_header_is_refused(hostsim, golden):
+    """A SOF0 that announces more 8x8 blocks than the scan bytes could hold at 2 bits per block (a damaged or
+    hostile header) is refused by the parser, so it can never size a coefficient arena."""
+    import gjd
+    data = bytearray(golden["images/3_120x120"])
+    at = data.find(b"\xff\xc0")
+    assert at > 0
+    big = bytes(data[: at + 5] + b"\xff\xff\xff\xff" + data[at + 9 :])     # height, width = 65535
+    assert hostsim.parse(big)[0] == -6
+    assert gjd.peek(big)[0] == -6
+    # the largest frame the same scan could still pay for is accepted by the header check
+    n_bits = (len(data) - data.find(b"\xff\xda")) * 8
+    side = int((n_bits // 6) ** 0.5) * 8 // 2
+    ok = bytes(data[: at + 5] + side.to_bytes(2, "big") + side.to_bytes(2, "big") + data[at + 9 :])
+    assert hostsim.parse(ok)[0] == 0
