@@ -380,3 +380,48 @@ def test_fuzz_differential_vs_hostsim(decoder, hostsim, golden, rst_golden, gray
             if rc == 0:
                 assert np.array_equal(o, rgb)
     assert {0, -4, -6} <= seen
+
+
+def test_device_output_buffers(golden, ref_outputs, gray_golden, ref_outputs_gray):
+    """rgb_on_device = 1: the caller's DEVICE buffers receive the pixels (no read-back inside the call) — tight
+    planar, interleaved, and a padded pitch/plane stride — with the call forced through many sub-batches so that
+    all three staging slots rotate."""
+    import gjd
+    import torch
+    names = NAMES * 2
+    files = [golden[n] for n in names] + list(gray_golden.values())
+    want = [ref_outputs[n + "/rgb"] for n in names] + [ref_outputs_gray[k + "/rgb"] for k in gray_golden]
+    with gjd.Decoder(0, scratch_bytes=1 << 20) as d:
+        for layout, pad in ((gjd.PLANAR, 0), (gjd.INTERLEAVED, 0), (gjd.PLANAR, 24), (gjd.INTERLEAVED, 40)):
+            items, hold = d.make_items(files)
+            bufs = []
+            for i, w in enumerate(want):
+                _, H, W = w.shape
+                if layout == gjd.PLANAR:
+                    pitch = W + pad
+                    pstride = pitch * H + 8 * pad
+                    t = torch.full((3 * pstride + 64,), 0xAB, dtype=torch.uint8, device="cuda")
+                    items[i].plane_stride = pstride if pad else 0
+                else:
+                    pitch = 3 * W + pad
+                    t = torch.full((pitch * H + 64,), 0xAB, dtype=torch.uint8, device="cuda")
+                items[i].row_pitch = pitch if pad else 0
+                items[i].rgb = t.data_ptr()
+                items[i].rgb_on_device = 1
+                items[i].layout = layout
+                bufs.append((t, pitch, pstride if layout == gjd.PLANAR else 0))
+            d.decode_batch_raw(items, len(files))
+            torch.cuda.synchronize()
+            for i, w in enumerate(want):
+                assert items[i].status == 0
+                _, H, W = w.shape
+                t, pitch, pstride = bufs[i]
+                h = t.cpu().numpy()
+                if layout == gjd.PLANAR:
+                    got = np.stack([h[c * pstride : c * pstride + pitch * H].reshape(H, pitch)[:, :W] for c in range(3)])
+                    assert np.array_equal(got, w)
+                    assert (h[3 * pstride :] == 0xAB).all()          # nothing written past the third plane
+                else:
+                    got = h[: pitch * H].reshape(H, pitch)[:, : 3 * W].reshape(H, W, 3)
+                    assert np.array_equal(got, w.transpose(1, 2, 0))
+                    assert (h[pitch * H :] == 0xAB).all()
