@@ -73,7 +73,9 @@ typedef struct gjd_item {
 /* Context.  Replaces allocate()/clean() (cuda-decoder/src/parser.cu:324-358, 684-700): all device
  * and pinned memory is arena-allocated once per context and reused across batches.
  * scratch_bytes_hint: device bytes the context may keep for one in-flight sub-batch
- * (0 = default, 6 GiB); batches larger than that are processed as pipelined sub-batches. */
+ * (0 = default, 6 GiB); batches larger than that are processed as pipelined sub-batches, up to
+ * three in flight inside gjd_decode_batch (one being unstuffed by the host threads, one uploading,
+ * one in the kernels / reading back), so the context may hold three times the hint. */
 int  gjd_create(gjd_ctx** out, int cuda_device, size_t scratch_bytes_hint);
 void gjd_destroy(gjd_ctx* ctx);
 
