@@ -8,7 +8,8 @@
  *   k_seq_scan      exclusive scan of per-sequence coefficient counts (per image)
  *   k_huff_write    re-decode from the synchronised states; every thread stages the blocks it owns in
  *                   shared memory and writes them as whole 32-byte sectors (+ DC difference, kmax)
- *   k_dc_tilebase   DC predictor at the start of every 32-MCU tile
+ *   k_dc_tilesum    DC differences summed per 32-MCU tile
+ *   k_dc_tilebase   DC predictor at the start of every tile (scan of the tile sums per image)
  *   k_transform     per 8x8 block: load the coefficient sectors, DC prefix, dequantise, dezigzag, integer
  *                   IDCT in registers; samples meet in shared memory for colour conversion + RGB store
  *
@@ -355,30 +356,40 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, 4) k_huff_write(GjdDevBatch
 
 /* ------------------------------------------------------------------ DC predictors ----- */
 /*
- * One block per image.  Thread t sums the DC differences of tile t (32 MCUs x 3 components =
- * 96 meta words, contiguous), the block scans the sums: tilebase[tile] = predictors at the tile start
- * (cpp-decoder/src/parser.cpp:108-111,141: three running predictors, never reset).
+ * tilebase[tile] = the three DC predictors at the start of the tile (cpp-decoder/src/parser.cpp:108-111,141:
+ * three running predictors, never reset; restart intervals are applied in the transform).  Two steps so that
+ * one huge image (BASELINE config 4: 32768 tiles) is not summed by a single block:
+ *   k_dc_tilesum   one thread per tile of the batch: sums the DC differences of the tile's 96 meta words
+ *                  (32 MCUs x 3 components, or 96 blocks of a single-component image)
+ *   k_dc_tilebase  one block per image: exclusive scan of its tile sums, in place
  */
+__global__ void __launch_bounds__(256) k_dc_tilesum(GjdDevBatch b) {
+    const uint32_t t = blockIdx.x * 256u + threadIdx.x;
+    if (t >= b.n_tile) return;
+    const uint4* mt = reinterpret_cast<const uint4*>(b.meta) + (size_t)t * 24u;
+    int sum[3] = {0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < 24; i++) {
+        const uint4 v = __ldg(mt + i);
+        sum[(i * 4) % 3] += (int)(int16_t)(v.x & 0xffffu);
+        sum[(i * 4 + 1) % 3] += (int)(int16_t)(v.y & 0xffffu);
+        sum[(i * 4 + 2) % 3] += (int)(int16_t)(v.z & 0xffffu);
+        sum[(i * 4 + 3) % 3] += (int)(int16_t)(v.w & 0xffffu);
+    }
+    if (b.imgs[b.tile_img[t]].gray) { sum[0] += sum[1] + sum[2]; sum[1] = sum[2] = 0; }   /* one DC chain over the 96 blocks */
+    b.tilebase[t] = make_int4(sum[0], sum[1], sum[2], 0);
+}
+
 __global__ void __launch_bounds__(256) k_dc_tilebase(GjdDevBatch b) {
     __shared__ uint32_t ws[8];
     const uint32_t tid = threadIdx.x;
     const GjdImage& d = b.imgs[blockIdx.x];
-    const uint4* mt = reinterpret_cast<const uint4*>(b.meta + (size_t)d.tile_first * 96u);
+    int4* tbase = b.tilebase + d.tile_first;
     int carry[3] = {0, 0, 0};
     for (uint32_t base = 0; base < d.tile_count; base += 256) {
-        uint32_t t = base + tid;
-        int sum[3] = {0, 0, 0};
-        if (t < d.tile_count) {
-#pragma unroll
-            for (int i = 0; i < 24; i++) {
-                uint4 v = __ldg(mt + (size_t)t * 24 + i);
-                sum[(i * 4) % 3] += (int)(int16_t)(v.x & 0xffffu);
-                sum[(i * 4 + 1) % 3] += (int)(int16_t)(v.y & 0xffffu);
-                sum[(i * 4 + 2) % 3] += (int)(int16_t)(v.z & 0xffffu);
-                sum[(i * 4 + 3) % 3] += (int)(int16_t)(v.w & 0xffffu);
-            }
-        }
-        if (d.gray) { sum[0] += sum[1] + sum[2]; sum[1] = sum[2] = 0; }   /* one component: one DC chain over the 96 blocks */
+        const uint32_t t = base + tid;
+        const int4 v = t < d.tile_count ? tbase[t] : make_int4(0, 0, 0, 0);
+        const int sum[3] = {v.x, v.y, v.z};
         int excl[3];
 #pragma unroll
         for (int c = 0; c < 3; c++) {
@@ -386,7 +397,7 @@ __global__ void __launch_bounds__(256) k_dc_tilebase(GjdDevBatch b) {
             excl[c] = (int)block_excl_scan_256((uint32_t)sum[c], ws, &tot) + carry[c];
             carry[c] += (int)tot;
         }
-        if (t < d.tile_count) b.tilebase[d.tile_first + t] = make_int4(excl[0], excl[1], excl[2], 0);
+        if (t < d.tile_count) tbase[t] = make_int4(excl[0], excl[1], excl[2], 0);
     }
 }
 
@@ -855,6 +866,7 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
         }
     }
     k_huff_write<<<b.n_seq, GJD_WRITE_THREADS, GJD_WRITE_SMEM, s>>>(b); n++;
+    k_dc_tilesum<<<(b.n_tile + 255u) / 256u, 256, 0, s>>>(b); n++;
     k_dc_tilebase<<<b.n_img, 256, 0, s>>>(b); n++;
     if (ev) GJD_CK(cudaEventRecord(ev->e[3], s));
     if (b.any_interleaved) k_transform<false, 8, true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
