@@ -53,6 +53,15 @@ __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* ws
     return base + incl - v;
 }
 
+__device__ __forceinline__ int warp_incl_scan_i(int v, uint32_t lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, v, o);
+        if ((int)lane >= o) v += t;
+    }
+    return v;
+}
+
 /* The count pass's view: the pair LUT ring in place of the primary one, everything else as in the set. */
 __device__ __forceinline__ void copy_count_lut_to_smem(GjdLutSet* dst, const GjdLutSet* src, const GjdLutCount* cnt) {
     static_assert(sizeof(GjdLutCount) == GJD_RING_BYTES && sizeof(GjdLutCount) % 16 == 0, "ring size");
@@ -235,21 +244,31 @@ __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
  */
 __global__ void __launch_bounds__(256) k_seq_scan(GjdDevBatch b) {
     __shared__ uint32_t ws[8];
-    const uint32_t tid = threadIdx.x;
+    __shared__ uint32_t tot_s[256];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
     const GjdSegment& d = b.segs[blockIdx.x];
     const uint32_t img = d.img;
     uint32_t carry = 0;
     for (uint32_t base = 0; base < d.seq_count; base += 256) {
-        uint32_t s = base + tid, total = 0;
-        if (s < d.seq_count) {
+        /* totals of up to 256 sequences: a warp per sequence, coalesced over its 256 subsequence records */
+        for (uint32_t i = wid; i < 256u; i += 8u) {
+            const uint32_t s = base + i;
+            if (s >= d.seq_count) break;                      /* warp-uniform */
             const uint2* si = b.sinfo + (size_t)(d.seq_first + s) * GJD_SEQ_SUBS;
-            uint32_t cnt = min(GJD_SEQ_SUBS, d.sub_count - s * GJD_SEQ_SUBS);
-            for (uint32_t t = 0; t < cnt; t++) total += si[t].y >> 8;
+            const uint32_t cnt = min(GJD_SEQ_SUBS, d.sub_count - s * GJD_SEQ_SUBS);
+            uint32_t t = 0;
+            for (uint32_t k = lane; k < cnt; k += 32u) t += si[k].y >> 8;
+            t = __reduce_add_sync(0xffffffffu, t);
+            if (lane == 0) tot_s[i] = t;
         }
+        __syncthreads();
+        const uint32_t s = base + tid;
+        const uint32_t total = s < d.seq_count ? tot_s[tid] : 0u;
         uint32_t blocksum;
         uint32_t excl = block_excl_scan_256(total, ws, &blocksum);
         if (s < d.seq_count) b.seq_base[d.seq_first + s] = carry + excl;
         carry += blocksum;
+        __syncthreads();                                      /* tot_s is rewritten by the next chunk */
     }
     if (tid == 0 && carry != 64u * d.blk_count) atomicOr(b.status + img, GJD_DEV_BADCOUNT);
 }
@@ -381,36 +400,49 @@ __global__ void __launch_bounds__(256) k_dc_tilesum(GjdDevBatch b) {
 }
 
 __global__ void __launch_bounds__(256) k_dc_tilebase(GjdDevBatch b) {
-    __shared__ uint32_t ws[8];
-    const uint32_t tid = threadIdx.x;
+    __shared__ int ws[3][8];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
     const GjdImage& d = b.imgs[blockIdx.x];
     int4* tbase = b.tilebase + d.tile_first;
     int carry[3] = {0, 0, 0};
-    for (uint32_t base = 0; base < d.tile_count; base += 256) {
-        const uint32_t t = base + tid;
-        const int4 v = t < d.tile_count ? tbase[t] : make_int4(0, 0, 0, 0);
-        const int sum[3] = {v.x, v.y, v.z};
-        int excl[3];
+    /* 2048 tiles per round: a thread takes 8 consecutive tiles, the block scans the three per-thread sums at once */
+    for (uint32_t base = 0; base < d.tile_count; base += 2048u) {
+        const uint32_t t0 = base + tid * 8u;
+        int4 v[8];
+        int sum[3] = {0, 0, 0};
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            v[j] = t0 + j < d.tile_count ? tbase[t0 + j] : make_int4(0, 0, 0, 0);
+            sum[0] += v[j].x; sum[1] += v[j].y; sum[2] += v[j].z;
+        }
+        int incl[3];
+#pragma unroll
+        for (int c = 0; c < 3; c++) incl[c] = warp_incl_scan_i(sum[c], lane);
+        __syncthreads();   /* ws may still be read from the previous round */
+        if (lane == 31u) { ws[0][wid] = incl[0]; ws[1][wid] = incl[1]; ws[2][wid] = incl[2]; }
+        __syncthreads();
+        int run[3];
 #pragma unroll
         for (int c = 0; c < 3; c++) {
-            uint32_t tot;
-            excl[c] = (int)block_excl_scan_256((uint32_t)sum[c], ws, &tot) + carry[c];
-            carry[c] += (int)tot;
+            int before = 0, tot = 0;
+#pragma unroll
+            for (int w = 0; w < 8; w++) {
+                const int x = ws[c][w];
+                if (w < (int)wid) before += x;
+                tot += x;
+            }
+            run[c] = carry[c] + before + incl[c] - sum[c];
+            carry[c] += tot;
         }
-        if (t < d.tile_count) tbase[t] = make_int4(excl[0], excl[1], excl[2], 0);
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            if (t0 + j < d.tile_count) tbase[t0 + j] = make_int4(run[0], run[1], run[2], 0);
+            run[0] += v[j].x; run[1] += v[j].y; run[2] += v[j].z;
+        }
     }
 }
 
 /* ------------------------------------------------------------------ transform --------- */
-
-__device__ __forceinline__ int warp_incl_scan_i(int v, uint32_t lane) {
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        int t = __shfl_up_sync(0xffffffffu, v, o);
-        if ((int)lane >= o) v += t;
-    }
-    return v;
-}
 
 #define GJD_TRANSFORM_THREADS 96
 
