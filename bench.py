@@ -227,6 +227,10 @@ def main():
 
     base = gen_synth.c3_files()
     files = [base[i % len(base)] for i in range(args.images)]
+    # the ranks of one node share its cores: each rank's host pool (header parse, unstuffing) gets its share
+    local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
+    if local_world > 1 and "GJD_HOST_THREADS" not in os.environ:
+        os.environ["GJD_HOST_THREADS"] = str(max(2, (os.cpu_count() or 2) // local_world))
     dec = gjd.Decoder(local, scratch_bytes=int(os.environ.get("GJD_SCRATCH", str(4 << 30))))
 
     # ---- device-resident throughput ("value") ------------------------------------------------------
