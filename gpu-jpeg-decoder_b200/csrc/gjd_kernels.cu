@@ -581,13 +581,13 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
         }
         const uint32_t m = valid ? __ldg(b.meta + blk) : 0u;
         const uint32_t kmax = (m >> 16) & 63u;
-        const uint32_t nsec = kmax ? (kmax >> 4) + 1u : 0u;
+        const uint32_t nchunk = kmax ? (kmax >> 3) + 1u : 0u;   /* 16-byte chunks up to the last coefficient */
         const uint4* src = reinterpret_cast<const uint4*>(b.coef) + blk * 8u;
         uint32_t w[32];
 #pragma unroll
         for (int j = 0; j < 8; j++) {
             uint4 r = make_uint4(0u, 0u, 0u, 0u);
-            if ((uint32_t)(j >> 1) < nsec) r = __ldcs(src + j);
+            if ((uint32_t)j < nchunk) r = __ldcs(src + j);
             w[4 * j] = r.x; w[4 * j + 1] = r.y; w[4 * j + 2] = r.z; w[4 * j + 3] = r.w;
         }
         const int4 tb = b.tilebase[d.tile_first + ltile];
