@@ -214,6 +214,11 @@ def main():
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; gjd has no CPU path (use --impl reference for the CPU arm)")
+    # stdout carries the ONE JSON line and nothing else: libraries that write to fd 1 (NCCL prints its version
+    # there when NCCL_DEBUG is set) are sent to stderr for the length of the run
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     torch.cuda.set_device(local)
     dist = None
     if world > 1:
@@ -352,7 +357,7 @@ def main():
                     line["cpu_baseline_jpeglib"] = {
                         "value": round(jl["mpix_per_s"], 3), "unit": UNIT, "cores": cb["cores"], "kind": "reference-vendored libjpeg 9e",
                         "sample": "%d images of the c3 set, %.1f s busy per thread, jpeg_read_header..jpeg_finish_decompress timed (RGB out, JDCT_ISLOW)" % (jl["images"], jl["busy_s_max"])}
-        print(json.dumps(line), flush=True)
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     pinned.free()
     dec.close()
     if dist:
