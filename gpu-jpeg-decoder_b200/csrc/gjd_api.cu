@@ -279,6 +279,19 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     }
     const uint64_t sub_bits = 1ull << sub_log2;
 
+    /* tiles per transform block: GJD_TB_TILES for big batches (one cold, unprefetched tile in 32); halved while
+     * the batch would give the 148 SMs x 8 resident blocks fewer than four waves of blocks */
+    uint32_t tb_tiles = GJD_TB_TILES;
+    {
+        uint64_t tiles = 0;
+        for (int32_t i = 0; i < n; i++) {
+            if (b->geom[i].status != GJD_OK) continue;
+            const uint64_t mc = (uint64_t)((b->geom[i].width + 7) / 8) * (uint64_t)((b->geom[i].height + 7) / 8);
+            tiles += (mc * (parsed[i].components == 1 ? 1u : 3u) + 95u) / 96u;
+        }
+        while (tb_tiles > 4u && tiles / tb_tiles < 4u * 148u * 8u) tb_tiles >>= 1;
+    }
+
     /* descriptors */
     std::unordered_map<uint64_t, std::vector<uint32_t>> lut_index, quant_index;
     uint32_t seq = 0, tile = 0, tb = 0;
@@ -300,7 +313,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         const uint32_t bpm = d.gray ? 1u : 3u;                       /* 8x8 blocks per MCU */
         d.tile_count = (d.mcu_count * bpm + 95u) / 96u;              /* a tile is 96 coefficient lines */
         d.tb_first = tb;
-        d.tb_count = (d.tile_count + GJD_TB_TILES - 1) / GJD_TB_TILES;
+        d.tb_count = (d.tile_count + tb_tiles - 1) / tb_tiles;
         d.row_pitch = (uint32_t)g.pitch;
         d.plane_stride = g.pstride;
         d.layout = (uint16_t)g.layout;
@@ -395,6 +408,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     v.sub_log2 = sub_log2;
     v.n_tile = tile;
     v.n_tb = tb;
+    v.tb_tiles = tb_tiles;
     if (n_img == 0) return GJD_OK;
 
     /* one pinned block for descriptors + DHT sets + quant sets, one H2D copy */

@@ -526,7 +526,7 @@ __device__ __forceinline__ void gjd_block_to_samples(const uint32_t* w, const ui
 }
 
 /*
- * One thread block (3 warps) per GJD_TB_TILES tiles of one image; per tile, warp c takes component c
+ * One thread block (3 warps) per b.tb_tiles (<= GJD_TB_TILES) tiles of one image; per tile, warp c takes component c
  * and lane l the 8x8 block of MCU l:
  *   transform phase  load the block's coefficient sectors (only those the write pass produced: kmax from
  *                    meta), warp-scan the DC differences onto the tile's DC base, dequantise + dezigzag
@@ -566,15 +566,15 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
     const uint32_t* q = sq[c];
 
 #pragma unroll 1
-    for (uint32_t t = 0; t < GJD_TB_TILES; t++) {
-        const uint32_t ltile = ltb * GJD_TB_TILES + t;
+    for (uint32_t t = 0; t < b.tb_tiles; t++) {
+        const uint32_t ltile = ltb * b.tb_tiles + t;
         if (ltile >= d.tile_count) break;
         const uint32_t mcu = ltile * GJD_TILE_MCUS + lane;
         const bool valid = mcu < d.mcu_count;
         const size_t blk = (size_t)(d.tile_first + ltile) * 96u + lane * 3u + c;
 
         /* ---- transform phase: component c of MCU `lane` ---- */
-        if (t + 1u < GJD_TB_TILES && ltile + 1u < d.tile_count) {
+        if (t + 1u < b.tb_tiles && ltile + 1u < d.tile_count) {
             /* the next tile's coefficient line and meta word on their way to L2 while this tile computes */
             asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const uint4*>(b.coef) + (blk + 96u) * 8u));
             if (lane < 12u && c == 0u) asm volatile("prefetch.global.L2 [%0];" ::"l"(b.meta + blk + 96u - lane * 3u + lane * 8u));
@@ -727,8 +727,8 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_gray(Gjd
     const uint32_t* meta_img = b.meta + (size_t)d.tile_first * 96u;
 
 #pragma unroll 1
-    for (uint32_t t = 0; t < GJD_TB_TILES; t++) {
-        const uint32_t ltile = ltb * GJD_TB_TILES + t;
+    for (uint32_t t = 0; t < b.tb_tiles; t++) {
+        const uint32_t ltile = ltb * b.tb_tiles + t;
         if (ltile >= d.tile_count) break;
         const uint32_t m0 = ltile * 96u, blkno = m0 + tid;       /* block number inside the image */
         const bool valid = blkno < d.mcu_count;

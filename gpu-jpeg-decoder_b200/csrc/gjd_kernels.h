@@ -33,6 +33,7 @@ struct GjdDevBatch {
     uint32_t n_tile;
     uint32_t* tb_img;      /* [n_tb] transform block -> image */
     uint32_t n_tb;
+    uint32_t tb_tiles;     /* tiles per transform block (1..GJD_TB_TILES, per batch: small batches get more blocks) */
     uint8_t* rgb;          /* output arena (images with out_is_ptr == 0) */
     uint32_t any_gray;        /* some image is single-component: k_transform_gray is launched too */
     uint32_t any_interleaved; /* some image wants GJD_LAYOUT_INTERLEAVED: selects the transform kernel variant */

@@ -34,7 +34,7 @@
 #define GJD_LUT2_PREFIXES  8       /* secondary LUT: 64-entry sub-tables for the first 8 unresolved prefixes */
 #define GJD_LUT2_SIZE     (GJD_LUT2_PREFIXES * 64)
 #define GJD_TILE_MCUS     32u      /* MCUs per coefficient tile (one warp)         */
-#define GJD_TB_TILES      32u      /* tiles per transform thread block (one image)  */
+#define GJD_TB_TILES      32u      /* most tiles per transform thread block (one image; GjdDevBatch.tb_tiles) */
 
 /* LUT entry (u16):  [4:0]  total bits = code length + value size (1..27); 0 = code longer than
  *                          GJD_LUT_BITS (or unassigned): then [15:5] = 1 + rank of this prefix among the
@@ -114,7 +114,7 @@ typedef struct GjdImage {
     uint32_t tile_first;    /* global index of the image's first coefficient tile              */
     uint32_t tile_count;
     uint32_t tb_first;      /* global index of the image's first transform block               */
-    uint32_t tb_count;      /* ceil(tile_count / GJD_TB_TILES)                                 */
+    uint32_t tb_count;      /* ceil(tile_count / tiles per transform block of the batch)       */
     uint32_t mcu_count;
     uint32_t mcus_x;
     uint32_t width, height;
