@@ -18,6 +18,10 @@
 #include <stdint.h>
 #include "gjd_types.h"
 
+#ifndef GJD_WRITE_SYMS
+#define GJD_WRITE_SYMS 2          /* symbols per trip of the write pass's warp-voted loop */
+#endif
+
 #ifndef GJD_DBG_SYM
 #define GJD_DBG_SYM() ((void)0)   /* test harnesses may count decoded symbols */
 #endif
@@ -407,8 +411,9 @@ GJD_HD void gjd_write_span(const uint32_t* scan, const Lut& lut, uint32_t end_bi
 #ifdef __CUDACC__
 #pragma unroll
 #endif
-        for (int half = 0; half < 2; half++) {
-            if (run) {
+        for (int half = 0; half < GJD_WRITE_SYMS; half++) {
+            /* (more than two symbols per trip: past a completed block only the next DC symbol may be taken) */
+            if (run && !(GJD_WRITE_SYMS > 2 && fl && z != 0u)) {
                 const uint32_t w = gjd_peek32(win, scan, p);     /* (reads at most one word into the padding) */
                 const uint32_t e = gjd_lookup(lut, tb, w, scan_bits - p);
                 const uint32_t total = e & 31u;

@@ -735,13 +735,13 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_gray(Gjd
         const size_t blk = (size_t)d.tile_first * 96u + blkno;
         const uint32_t m = valid ? __ldg(b.meta + blk) : 0u;
         const uint32_t kmax = (m >> 16) & 63u;
-        const uint32_t nsec = kmax ? (kmax >> 4) + 1u : 0u;
+        const uint32_t nchunk = kmax ? (kmax >> 3) + 1u : 0u;   /* 16-byte chunks up to the last coefficient */
         const uint4* src = reinterpret_cast<const uint4*>(b.coef) + blk * 8u;
         uint32_t w[32];
 #pragma unroll
         for (int j = 0; j < 8; j++) {
             uint4 r = make_uint4(0u, 0u, 0u, 0u);
-            if ((uint32_t)(j >> 1) < nsec) r = __ldcs(src + j);
+            if ((uint32_t)j < nchunk) r = __ldcs(src + j);
             w[4 * j] = r.x; w[4 * j + 1] = r.y; w[4 * j + 2] = r.z; w[4 * j + 3] = r.w;
         }
         /* inclusive scan of the DC differences over the 96 blocks of the tile */
