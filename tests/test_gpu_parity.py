@@ -425,3 +425,28 @@ def test_device_output_buffers(golden, ref_outputs, gray_golden, ref_outputs_gra
                     got = h[: pitch * H].reshape(H, pitch)[:, : 3 * W].reshape(H, W, 3)
                     assert np.array_equal(got, w.transpose(1, 2, 0))
                     assert (h[pitch * H :] == 0xAB).all()
+
+
+@pytest.mark.gpu
+def test_transform_block_tiling_all_sizes(decoder, oracle):
+    """batch_stage picks the tiles per transform block from the batch size (4, 8, 16 or 32: small batches get more
+    blocks).  Resident batches of 1, 96, 160 and 320 images of 1024x1024 land on each value; every image of every
+    batch must equal the oracle's pixels for its file."""
+    import gen_synth
+    if not gen_synth.have_cjpeg():
+        pytest.skip("vendored cjpeg missing")
+    base = [gen_synth.synth_jpeg(s, 1024, 1024, 90) for s in range(4)]
+    want = []
+    for f in base:
+        rc, _, rgb, _, W, H = oracle.decode(f, want_coef=False)
+        assert rc == 0
+        want.append(hashlib.md5(rgb.tobytes()).hexdigest())
+    for n in (1, 96, 160, 320):
+        files = [base[i % 4] for i in range(n)]
+        b = decoder.prepare(files)
+        b.run()
+        assert b.sync() == 0
+        for i in range(n):
+            assert b.status(i) == 0
+            assert hashlib.md5(b.fetch(i).tobytes()).hexdigest() == want[i % 4], (n, i)
+        b.free()
