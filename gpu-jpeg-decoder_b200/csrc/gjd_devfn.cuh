@@ -62,10 +62,10 @@ GJD_HD void gjd_canonical(const uint8_t bits[16], uint32_t lim[17], int32_t off[
     }
 }
 
-/* Resolve a 16-bit window against the canonical tables, lengths from..16. */
+/* Resolve a 16-bit window against the canonical tables, lengths from..to (16 unless fewer bits are known). */
 GJD_HD uint32_t gjd_resolve(const uint32_t* lim, const int32_t* off, const uint8_t* vals,
-                            uint32_t isdc, uint32_t win16, int from) {
-    for (int L = from; L <= 16; L++) {
+                            uint32_t isdc, uint32_t win16, int from, int to = 16) {
+    for (int L = from; L <= to; L++) {
         if (win16 < lim[L]) {
             uint32_t idx = (uint32_t)(off[L] + (int32_t)(win16 >> (16 - L))) & 255u;
             return gjd_make_entry((uint32_t)L, vals[idx], isdc);
@@ -92,13 +92,15 @@ GJD_HD uint16_t gjd_lut_entry(const uint32_t* lim, const int32_t* off, const uin
     return rank < (uint32_t)GJD_LUT2_PREFIXES ? (uint16_t)((rank + 1u) << 5) : (uint16_t)0;
 }
 
-/* Secondary LUT entry i2 = rank * 64 + (the 6 bits after the primary index): the whole 16-bit window is
- * known, so every assigned code resolves; 0 = unassigned code (left to gjd_lookup_slow, which flags it). */
+/* Secondary LUT entry i2 = rank * 64 + (the 6 bits after the primary index): GJD_LUT_BITS + 6 bits of the
+ * window are known (all 16 with a 10-bit index, so every assigned code resolves);
+ * 0 = longer or unassigned code (left to gjd_lookup_slow, which flags the latter). */
 GJD_HD uint16_t gjd_lut2_entry(const uint32_t* lim, const int32_t* off, const uint8_t* vals,
                                uint32_t isdc, uint32_t i2) {
     uint32_t j = (lim[GJD_LUT_BITS] >> (16 - GJD_LUT_BITS)) + (i2 >> 6);
     if (j >= (uint32_t)GJD_LUT_SIZE) return 0;
-    uint32_t e = gjd_resolve(lim, off, vals, isdc, (j << 6) | (i2 & 63u), GJD_LUT_BITS + 1);
+    uint32_t e = gjd_resolve(lim, off, vals, isdc, ((j << 6) | (i2 & 63u)) << (10 - GJD_LUT_BITS), GJD_LUT_BITS + 1,
+                             GJD_LUT_BITS + 6);
     return (e & GJD_ENTRY_BAD) ? (uint16_t)0 : (uint16_t)e;
 }
 
@@ -211,7 +213,9 @@ struct GjdLutSmem {
     const GjdLutSet* set;
     uint32_t* badcode;
     uint32_t base;
-    __device__ __forceinline__ explicit GjdLutSmem(const GjdLutSet* s, uint32_t* bc = nullptr) : set(s), badcode(bc) {
+    /* cold: where the slow path finds the canonical tables when s holds only the LUT levels */
+    __device__ __forceinline__ explicit GjdLutSmem(const GjdLutSet* s, uint32_t* bc = nullptr, const GjdLutSet* cold = nullptr)
+        : set(cold ? cold : s), badcode(bc) {
         /* opaque move: keeps the window offset in a register instead of re-deriving it per symbol */
         asm volatile("mov.u32 %0, %1;" : "=r"(base) : "r"((uint32_t)__cvta_generic_to_shared(s->lut)));
     }
@@ -244,7 +248,7 @@ GJD_HD uint32_t gjd_lookup(const Lut& lut, uint32_t tb, uint32_t w, uint32_t roo
     uint32_t e = lut.entry(tb + ((w >> (31 - GJD_LUT_BITS)) & (GJD_RING_STRIDE - 2u)));
     if ((e & 31u) == 0u) {
         /* sub-table ((e >> 5) - 1) of secondary table tb / RING_STRIDE, entry = next 6 bits */
-        if (e) e = lut.entry((GJD_RING_BYTES - 128u) + (tb >> 1) + e * 4u + ((w >> 15) & 126u));
+        if (e) e = lut.entry(GJD_LUT2_OFF(tb, e, w));
         if ((e & 31u) == 0u) e = gjd_lookup_slow(lut.set, tb, w, room, lut.badcode);
     }
     return e;
@@ -315,7 +319,7 @@ GJD_HD void gjd_count_span_pairs(const uint32_t* scan, const Lut& lut, uint32_t 
         const uint32_t w = gjd_peek32(win, scan, p);
         uint32_t e = lut.entry(tb + ((w >> (31 - GJD_LUT_BITS)) & (GJD_RING_STRIDE - 2u)));
         if ((e & 31u) == 0u) {   /* long code: single-symbol entries (with a size field) from lut2 / the tables */
-            if (e) e = lut.entry((GJD_RING_BYTES - 128u) + (tb >> 1) + e * 4u + ((w >> 15) & 126u));
+            if (e) e = lut.entry(GJD_LUT2_OFF(tb, e, w));
             if ((e & 31u) == 0u) e = gjd_lookup_slow(lut.set, tb, w, scan_bits - p, lut.badcode);
             e &= ~0x1E0u;
         }

@@ -72,11 +72,12 @@ __device__ __forceinline__ void copy_count_lut_to_smem(GjdLutSet* dst, const Gjd
         d[i] = __ldg(i < sizeof(GjdLutCount) / 16 ? c + i : s + i);
 }
 
-__device__ __forceinline__ void copy_lut_to_smem(GjdLutSet* dst, const GjdLutSet* src) {
+/* the first `bytes` of the set: all of it, or only the two LUT levels (the canonical tables then stay in global memory) */
+__device__ __forceinline__ void copy_lut_to_smem(GjdLutSet* dst, const GjdLutSet* src, uint32_t bytes = sizeof(GjdLutSet)) {
     static_assert(sizeof(GjdLutSet) % 16 == 0, "GjdLutSet must be a multiple of 16 bytes");
     const uint4* s = reinterpret_cast<const uint4*>(src);
     uint4* d = reinterpret_cast<uint4*>(dst);
-    for (uint32_t i = threadIdx.x; i < sizeof(GjdLutSet) / 16; i += blockDim.x) d[i] = __ldg(s + i);
+    for (uint32_t i = threadIdx.x; i < bytes / 16; i += blockDim.x) d[i] = __ldg(s + i);
 }
 
 /* ------------------------------------------------------------------ tables and maps --- */
@@ -324,11 +325,21 @@ struct GjdWriteSink {
  * coefficient index seq_base + (block-exclusive scan of the counts), and writes the blocks it owns
  * (gjd_write_span).
  */
-#define GJD_WRITE_SMEM (sizeof(GjdLutSet) + 8u * GJD_WRITE_THREADS * sizeof(uint4))   /* dynamic: > 48 KB */
-__global__ void __launch_bounds__(GJD_WRITE_THREADS, 4) k_huff_write(GjdDevBatch b) {
+#if GJD_LUT_BITS < 10
+/* experiment: a 9-bit primary LUT, only the two LUT levels in shared memory (12 KB; the canonical tables of
+ * the rare slow path are read from global memory) -> 44 KB per block, five blocks per SM */
+#define GJD_WRITE_LUT_BYTES (GJD_RING_BYTES + GJD_RING_TABLES * GJD_LUT2_STRIDE)
+#define GJD_WRITE_MINB 5
+#else
+#define GJD_WRITE_LUT_BYTES sizeof(GjdLutSet)
+#define GJD_WRITE_MINB 4
+#endif
+#define GJD_WRITE_SMEM (GJD_WRITE_LUT_BYTES + 8u * GJD_WRITE_THREADS * sizeof(uint4))   /* dynamic: > 48 KB with the whole set */
+__global__ void __launch_bounds__(GJD_WRITE_THREADS, GJD_WRITE_MINB) k_huff_write(GjdDevBatch b) {
     extern __shared__ uint4 dyn_smem[];
+    static_assert(GJD_WRITE_LUT_BYTES % 16 == 0 && GJD_WRITE_LUT_BYTES <= sizeof(GjdLutSet), "LUT part of the set");
     GjdLutSet& lut = *reinterpret_cast<GjdLutSet*>(dyn_smem);
-    uint4 (*buf)[GJD_WRITE_THREADS] = reinterpret_cast<uint4 (*)[GJD_WRITE_THREADS]>(dyn_smem + sizeof(GjdLutSet) / 16);
+    uint4 (*buf)[GJD_WRITE_THREADS] = reinterpret_cast<uint4 (*)[GJD_WRITE_THREADS]>(dyn_smem + GJD_WRITE_LUT_BYTES / 16);
     __shared__ uint32_t ws[8];
     __shared__ uint32_t badcode;
     const uint32_t g = blockIdx.x, tid = threadIdx.x;
@@ -340,8 +351,8 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, 4) k_huff_write(GjdDevBatch
     const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
     const bool active = sub < d.sub_count;
     const uint2* si = b.sinfo + (size_t)g * GJD_SEQ_SUBS;
-    copy_lut_to_smem(&lut, b.luts + d.lut_id);
-    const GjdLutSmem slut(&lut, &badcode);
+    copy_lut_to_smem(&lut, b.luts + d.lut_id, GJD_WRITE_LUT_BYTES);
+    const GjdLutSmem slut(&lut, &badcode, GJD_WRITE_LUT_BYTES < sizeof(GjdLutSet) ? b.luts + d.lut_id : &lut);
     if (tid == 0) badcode = 0u;
 #pragma unroll
     for (int j = 0; j < 8; j++) buf[j][tid] = make_uint4(0u, 0u, 0u, 0u);

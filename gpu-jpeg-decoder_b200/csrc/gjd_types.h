@@ -29,7 +29,9 @@
 #define GJD_SUB_LOG2_MAX   13u      /* long enough to amortise the look-back, short enough to fill the GPU */
 #define GJD_LOOKBACK_BITS 512u     /* cold-start distance before a subsequence (k_huff_sync)          */
 #define GJD_SEQ_SUBS      256u     /* subsequences per sequence (one thread block) */
-#define GJD_LUT_BITS      10       /* primary Huffman LUT index width              */
+#ifndef GJD_LUT_BITS
+#define GJD_LUT_BITS      10       /* primary Huffman LUT index width (9 or 10: the secondary LUT covers 6 more bits) */
+#endif
 #define GJD_LUT_SIZE      (1 << GJD_LUT_BITS)
 #define GJD_LUT2_PREFIXES  8       /* secondary LUT: 64-entry sub-tables for the first 8 unresolved prefixes */
 #define GJD_LUT2_SIZE     (GJD_LUT2_PREFIXES * 64)
@@ -46,7 +48,12 @@
 #define GJD_RING_TABLES 6
 #define GJD_RING_STRIDE (GJD_LUT_SIZE * 2u)                  /* bytes per table of the ring        */
 #define GJD_RING_BYTES  (GJD_RING_TABLES * GJD_RING_STRIDE)
-#define GJD_LUT2_STRIDE  (GJD_LUT2_SIZE * 2u)                 /* bytes per secondary table (= RING_STRIDE / 2) */
+#define GJD_LUT2_STRIDE  (GJD_LUT2_SIZE * 2u)                 /* bytes per secondary table (= RING_STRIDE / 2, or RING_STRIDE with a 9-bit index) */
+/* Offset (from the start of the ring) of the secondary-LUT entry behind link e = (rank + 1) << 5 of the table at
+ * ring offset tb, for the window w: sub-table rank of secondary table tb / RING_STRIDE, entry = the 6 bits after
+ * the primary index. */
+#define GJD_LUT2_OFF(tb, e, w) ((GJD_RING_BYTES - 128u) + (GJD_LUT2_STRIDE == GJD_RING_STRIDE ? (tb) : (tb) >> 1) + \
+                                (e) * 4u + (((w) >> (25 - GJD_LUT_BITS)) & 126u))
 
 /* One Huffman table set as the decoders use it, device-resident, built by k_build_luts from a
  * GjdDhtSet: the primary LUTs laid out as a RING in scan order — DC(comp 0), AC(comp 0), DC(comp 1),

@@ -62,13 +62,15 @@ class HostSim:
 
     def __init__(self):
         d = os.path.join(ROOT, "tests", "hostsim")
-        so = os.path.join(d, "_build", "libgjd_hostsim.so")
+        bits = os.environ.get("GJD_LUT_BITS")       # A/B of the primary LUT width (csrc/gjd_types.h), default build otherwise
+        so = os.path.join(d, "_build", "libgjd_hostsim%s.so" % ("_lut" + bits if bits else ""))
         srcs = [os.path.join(d, "hostsim.cpp"), os.path.join(PKG, "csrc", "gjd_parse.cpp")]
         deps = srcs + glob.glob(os.path.join(PKG, "csrc", "*.h")) + glob.glob(os.path.join(PKG, "csrc", "*.cuh"))
         if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(s) for s in deps):
             os.makedirs(os.path.dirname(so), exist_ok=True)
             subprocess.run(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared",
-                            "-Wno-unknown-pragmas", "-o", so, *srcs], check=True)
+                            "-Wno-unknown-pragmas", *(["-DGJD_LUT_BITS=" + bits] if bits else []),
+                            "-o", so, *srcs], check=True)
         self.lib = C.CDLL(so)
         self.lib.hostsim_decode.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p,
                                             C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_void_p]

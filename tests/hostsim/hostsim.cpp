@@ -371,7 +371,7 @@ int hostsim_lut_check(const uint8_t* jpg, size_t len, uint32_t out[3]) {
             uint32_t e = m.entry(tb + ((w >> (31 - GJD_LUT_BITS)) & (GJD_RING_STRIDE - 2u)));
             if ((e & 31u) == 0u) {
                 if (want != GJD_ENTRY_UNASSIGNED) out[2]++;
-                uint32_t e2 = e ? m.entry((GJD_RING_BYTES - 128u) + (tb >> 1) + e * 4u + ((w >> 15) & 126u)) : 0u;
+                uint32_t e2 = e ? m.entry(GJD_LUT2_OFF(tb, e, w)) : 0u;
                 if ((e2 & 31u) == 0u && want != GJD_ENTRY_UNASSIGNED) out[1]++;
             }
         }

@@ -121,7 +121,8 @@ def test_two_level_lut_matches_canonical_tables(hostsim, golden):
         rc = hostsim.lib.hostsim_lut_check(C.cast(C.c_char_p(data), C.c_void_p), len(data), out.ctypes.data)
         assert rc == 0, name
         assert out[0] == 0, (name, out)
-        assert out[1] == 0, (name, out)
+        if int(os.environ.get("GJD_LUT_BITS", "10")) == 10:   # a narrower index leaves 16-bit codes to the slow path
+            assert out[1] == 0, (name, out)
         long_codes += int(out[2])
     assert long_codes > 0
 
