@@ -195,6 +195,7 @@ struct gjd_ctx {
     std::string cuda_err;
     int transform_variant = 0;
     uint64_t min_subseqs = 1200000;   /* ~4 waves of 148 SMs x 2048 threads */
+    uint32_t max_tb_tiles = GJD_TB_TILES;   /* GJD_TB_TILES_MAX: measurement knob (power of two, 4..128) */
     int force_sub_log2 = 0;           /* GJD_SUB_LOG2: fixed subsequence length (tests, experiments) */
 };
 
@@ -281,7 +282,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
 
     /* tiles per transform block: GJD_TB_TILES for big batches (one cold, unprefetched tile in 32); halved while
      * the batch would give the 148 SMs x 8 resident blocks fewer than four waves of blocks */
-    uint32_t tb_tiles = GJD_TB_TILES;
+    uint32_t tb_tiles = ctx->max_tb_tiles;
     {
         uint64_t tiles = 0;
         for (int32_t i = 0; i < n; i++) {
@@ -593,6 +594,10 @@ int gjd_create(gjd_ctx** out, int device, size_t scratch_bytes_hint) {
     if (const char* e = getenv("GJD_SUB_LOG2")) {
         int k = atoi(e);
         if (k >= 8 && k <= 16) ctx->force_sub_log2 = k;
+    }
+    if (const char* e = getenv("GJD_TB_TILES_MAX")) {
+        const int v = atoi(e);
+        if (v >= 4 && v <= 128 && (v & (v - 1)) == 0) ctx->max_tb_tiles = (uint32_t)v;
     }
     if (const char* e = getenv("GJD_MIN_SUBSEQS")) ctx->min_subseqs = (uint64_t)std::max(1ll, atoll(e));
     *out = ctx;
