@@ -352,6 +352,9 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
             GjdQuantSet q;
             for (int c = 0; c < 3; c++)
                 for (int k = 0; k < 64; k++) q.q[c][k] = p.quant[p.qsel[c]][k];
+            for (int c = 0; c < 3; c++)
+                for (int j = 0; j < 32; j++)
+                    q.packed[c][j] = (uint32_t)q.q[c][2 * j] | ((uint32_t)q.q[c][2 * j + 1] << 24);
             uint64_t h = fnv1a(&q, sizeof(q));
             auto& cand = quant_index[h];
             int found = -1;

@@ -553,9 +553,18 @@ __device__ __forceinline__ void gjd_block_to_samples(const uint32_t* w, const ui
  * EXPORT = true is the coefficient test hook: blocks are written out in the reference layout
  * mcu*192 + comp*64 + k with the absolute DC in slot 0 instead of being transformed.
  */
+#ifndef GJD_TRANSFORM_MINB
+#define GJD_TRANSFORM_MINB 9       /* resident blocks per SM of the planar transform: 72 registers, 24 KB of shared memory */
+#endif
+#ifndef GJD_TRANSFORM_MINB_ALT
+#define GJD_TRANSFORM_MINB_ALT 8   /* the GJD_TRANSFORM_VARIANT=1 instantiation (A/B): 80 registers, quantisation words in shared memory */
+#endif
 template <bool EXPORT, int MINB, bool ILV>
 __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDevBatch b, int16_t* __restrict__ coef_out) {
-    __shared__ uint32_t sq[3][32];
+    /* MINB >= 9 (A/B builds): the packed quantisation words are read from global memory (GjdQuantSet.packed) — the
+     * 384 bytes of sq are what keeps a ninth block off the SM */
+    constexpr bool QGLOBAL = MINB >= 9;
+    __shared__ uint32_t sq[QGLOBAL ? 1 : 3][32];
     __shared__ uint4 smp[2][3][8][32];
 
     const uint32_t tid = threadIdx.x, c = tid >> 5, lane = tid & 31u;
@@ -564,7 +573,7 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
     const uint32_t ltb = blockIdx.x - d.tb_first;
     {
         const int* qg = reinterpret_cast<const int*>(b.quants + d.quant_id);
-        sq[c][lane] = gjd_pack_quant(qg + c * 64u, lane);
+        if (!QGLOBAL) sq[c][lane] = gjd_pack_quant(qg + c * 64u, lane);
     }
     __syncthreads();
 
@@ -574,7 +583,7 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
     /* ILV = false: the batch holds planar images only (the common case keeps the shorter kernel) */
     const bool interleaved = ILV && d.layout == GJD_LAYOUT_INTERLEAVED;
     const bool aligned = (((size_t)out | pitch | (interleaved ? 0 : pstride)) & 7u) == 0;
-    const uint32_t* q = sq[c];
+    const uint32_t* q = QGLOBAL ? b.quants[d.quant_id].packed[c] : sq[c];
 
 #pragma unroll 1
     for (uint32_t t = 0; t < b.tb_tiles; t++) {
@@ -913,8 +922,8 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     k_dc_tilebase<<<b.n_img, 256, 0, s>>>(b); n++;
     if (ev) GJD_CK(cudaEventRecord(ev->e[3], s));
     if (b.any_interleaved) k_transform<false, 8, true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
-    else if (transform_variant == 1) k_transform<false, 6, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
-    else k_transform<false, 8, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
+    else if (transform_variant == 1) k_transform<false, GJD_TRANSFORM_MINB_ALT, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
+    else k_transform<false, GJD_TRANSFORM_MINB, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
     n++;
     if (b.any_gray) { k_transform_gray<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr); n++; }
     if (ev) GJD_CK(cudaEventRecord(ev->e[4], s));

@@ -94,6 +94,7 @@ typedef struct GjdDhtSet {
 /* The quantisation table of each component, zigzag order, widened to i32 for broadcast loads. */
 typedef struct GjdQuantSet {
     int32_t q[3][64];
+    uint32_t packed[3][32];          /* q[c][2j] | q[c][2j+1] << 24: the words the transform's dp2a dequantisation takes */
 } GjdQuantSet;
 
 /* One independently decodable piece of entropy-coded data: the whole scan of an image without restart
