@@ -1,18 +1,32 @@
 #!/usr/bin/env python
 """bench.py — decoded MPixel/s of the 4:4:4 baseline-JPEG decode path (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--images 3000]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--config c3|c5] [--images M]
 
-Workload (BASELINE.json configs[2], SURVEY §8d "C3"): a batch of 3000 synthetic 1024x1024 q90 4:4:4
-JPEGs per GPU (64 distinct files, seeds 0..63, tiled), encoded with the reference's vendored IJG cjpeg.
-One "step" = one pass of the whole decode path over that batch.  Weak scaling: every rank (one process
-per GPU, launched by torch.distributed.run for N > 1) decodes its own batch of the same size; there is
-no data-path collective — torch.distributed is used for the barrier and the max-over-ranks.
+Workloads:
+  c3 (default; BASELINE.json configs[2], the shape `metric` is quoted on): a batch of 3000 synthetic
+      1024x1024 q90 4:4:4 JPEGs PER GPU (64 distinct files, seeds 0..63, tiled).  Weak scaling: every rank
+      decodes its own batch of the same size.
+  c5 (BASELINE.json configs[4]): ONE global list of 24000 mixed-size images (256 distinct files,
+      default_rng(2024): sizes {256..2048}^2 + 10 % ragged, q in {75,90,95}), sharded over the N ranks with
+      gjd_partition (greedy LPT on padded pixels, include/gjd.h); rank r decodes part_of == r.  Strong scaling.
+Both are encoded with the reference's vendored IJG cjpeg.  One "step" = one pass of the whole decode path
+over the rank's images.  There is no data-path collective — torch.distributed carries the
+barrier, the max-over-ranks of the times and the sum of the parity counts.
 
   value     device-resident: parsed + unstuffed scans already in HBM, outputs stay in HBM, timed with
-            CUDA events on the launching stream around every GPU stage (scratch clears included).
-  e2e       gjd_decode_batch() through the C ABI with HOST buffers: header parse, unstuffing into pinned
-            staging, H2D, all GPU stages, D2H of the pixels into pinned host memory, all timed.
+            CUDA events on the launching stream around every GPU stage (scratch clears included).  A shard
+            that does not fit in HBM at once (c5 at small N) is decoded as successive resident chunks; a
+            chunk's preparation (the reference's untimed extract()/allocate() loop,
+            cuda-decoder/benchmark_thoughput/benchmark.cu:49-60) is outside the event-timed region.
+  e2e       gjd_decode_batch() through the C ABI with HOST buffers: header parse, unstuffing, H2D, all GPU
+            stages, D2H of the pixels into pinned host memory, all timed (wall clock around the calls).
+  e2e_device_output
+            the same call with the pixels left in device memory (rgb_on_device).
+  parity_checked
+            after EACH of the three timed loops, one image per distinct file (spread over the batch) is
+            compared byte for byte with the oracle's output for that file (oracle/gjd_oracle.c, hashed once
+            outside every timed region); a mismatch fails the run.
   roofline  the transform kernel (dequant+IDCT+colour+store), algorithmic bytes 6 B/padded px + 3 B/px,
             against the measured HBM copy peak of MEASURED_PEAKS.json.
   cpu_baseline / --impl reference
@@ -23,6 +37,7 @@ no data-path collective — torch.distributed is used for the barr
             a second, reported-only baseline.
 """
 import argparse
+import hashlib
 import json
 import os
 import statistics
@@ -39,7 +54,7 @@ for p in (PKG, os.path.join(ROOT, "tools")):
 
 METRIC = "decoded MPixel/s (4:4:4 batch)"
 UNIT = "MPixel/s"
-WORKLOAD = "c3: synthetic 1024x1024 q90 4:4:4 baseline JPEG, batch of %d per GPU (64 distinct files tiled)"
+CHUNK_PIXELS = int(float(os.environ.get("GJD_BENCH_CHUNK_GPIX", "3.3")) * 1e9)   # padded pixels resident at once
 
 
 def measured_peak():
@@ -98,6 +113,43 @@ class ClockSampler:
                 "window": window}
 
 
+# ---------------------------------------------------------------------------------------- workloads ----
+
+def load_workload(config, images):
+    """(distinct files as bytes, their paths on disk, file id of every image of the GLOBAL list)."""
+    import gen_synth
+    if config == "c3":
+        base = gen_synth.c3_files()
+        paths = [os.path.join(gen_synth.CACHE, "s%d_1024x1024_q90_o0_r0.jpg" % s) for s in range(len(base))]
+    elif config == "c5":
+        specs = gen_synth.c5_specs(256)
+        base = gen_synth.c5_files(256)
+        paths = [os.path.join(gen_synth.CACHE, "s%d_%dx%d_q%d_o0_r0.jpg" % s) for s in specs]
+    else:
+        raise SystemExit("bench.py: unknown --config %r" % config)
+    return base, paths, [i % len(base) for i in range(images)]
+
+
+def config_dict(config, images, world):
+    """The static description of the workload — identical in the gjd arm and in the --impl reference arm."""
+    if config == "c3":
+        return {"workload": "c3: synthetic 1024x1024 q90 4:4:4 baseline JPEG, batch of %d per GPU (64 distinct files tiled)" % images,
+                "config": "c3", "images_per_gpu": images, "distinct_files": 64, "scaling": "weak",
+                "parallelism": "replicas: one batch per GPU, no collective",
+                "l2": "inputs+outputs larger than L2 (0.75 GB of scans read 3x, 9.4 GB of RGB written per step and GPU)"}
+    return {"workload": "c5: synthetic mixed-size 4:4:4 baseline JPEG ({256..2048}^2 + 10%% ragged, q 75/90/95), %d images "
+                        "(256 distinct files tiled) sharded over the GPUs by gjd_partition" % images,
+            "config": "c5", "images_total": images, "distinct_files": 256, "scaling": "strong",
+            "parallelism": "shards: gjd_partition (greedy LPT on padded pixels), one shard per GPU, no collective",
+            "l2": "inputs+outputs larger than L2 (every resident chunk holds > 1 GPixel)"}
+
+
+def default_images(config):
+    return int(os.environ.get("GJD_BENCH_IMAGES", "3000" if config == "c3" else "24000"))
+
+
+# ---------------------------------------------------------------------------------------- CPU arms -----
+
 def ref_bench(threads, seconds, files_on_disk):
     exe = os.path.join(ROOT, "oracle", "_ref", "ref_bench")
     out = subprocess.run([exe, str(threads), str(seconds), *files_on_disk], stdout=subprocess.PIPE, check=True, text=True)
@@ -113,15 +165,21 @@ def jpeglib_bench(threads, seconds, files_on_disk):
     return json.loads(out.stdout.strip().splitlines()[-1])
 
 
-def port_bench(threads, seconds, files):
-    """Fallback CPU baseline: the oracle restatement (kind "port") on `threads` Python threads (ctypes drops the GIL)."""
+def oracle_lib():
     import ctypes as C
     so = os.path.join(ROOT, "oracle", "_build", "libgjd_oracle.so")
     if not os.path.exists(so):
         subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "oracle"], check=True, stdout=subprocess.DEVNULL)
     lib = C.CDLL(so)
     lib.gjdo_decode.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_void_p, C.c_void_p, C.c_void_p]
+    return lib
+
+
+def port_bench(threads, seconds, files):
+    """Fallback CPU baseline: the oracle restatement (kind "port") on `threads` Python threads (ctypes drops the GIL)."""
+    import ctypes as C
     import numpy as np
+    lib = oracle_lib()
     busy, pixels, images = [0.0] * threads, [0] * threads, [0] * threads
 
     def work(t):
@@ -144,49 +202,98 @@ def port_bench(threads, seconds, files):
             "mpix_per_s": sum(pixels) / max(busy) / 1e6}
 
 
-def cpu_reference(seconds, files, n_distinct):
+def cpu_reference(seconds, base, paths, config):
     """Time the reference CPU decoder on all host cores over a bounded sample of the workload."""
     cores = os.cpu_count() or 1
-    import gen_synth
-    paths = [os.path.join(gen_synth.CACHE, "s%d_1024x1024_q90_o0_r0.jpg" % s) for s in range(n_distinct)]
     if os.path.exists(os.path.join(ROOT, "oracle", "_ref", "ref_bench")) and all(os.path.exists(p) for p in paths):
         r = ref_bench(cores, seconds, paths)
         kind = "reference"
     else:
-        r = port_bench(cores, seconds, files)
+        r = port_bench(cores, seconds, base)
         kind = "port"
-    sample = "%d images of the c3 set (1024x1024 q90), %.1f s busy per thread, extract()+decode() timed" % (r["images"], r["busy_s_max"])
+    sample = "%d images of the %s set, %.1f s busy per thread, extract()+decode() timed" % (r["images"], config, r["busy_s_max"])
     return {"value": round(r["mpix_per_s"], 3), "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}, r
 
 
 def run_reference_arm(args, rank, world):
     if rank != 0:
         return
-    import gen_synth
-    files = gen_synth.c3_files()
+    base, paths, _ = load_workload(args.config, 1)
     per_step = float(os.environ.get("GJD_REF_STEP_SECONDS", "3"))
     for _ in range(args.warmup):
-        cpu_reference(min(per_step, 1.0), files, len(files))
+        cpu_reference(min(per_step, 1.0), base, paths, args.config)
     pixels, busy, images = 0, 0.0, 0
     t0 = time.time()
     for _ in range(args.steps):
-        cb, r = cpu_reference(per_step, files, len(files))
+        cb, r = cpu_reference(per_step, base, paths, args.config)
         pixels += r["pixels"]
         busy += r["busy_s_max"]
         images += r["images"]
     value = pixels / busy / 1e6
+    cfg = config_dict(args.config, args.images, world)
     line = {
         "impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(busy / args.steps * 1e3, 3),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-        "config": {"workload": WORKLOAD % args.images, "step": "bounded sample: every host thread decodes c3 images for %.1f s" % per_step},
+        "higher_is_better": True, "scaling": cfg["scaling"], "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+        "config": cfg,
         "cpu_baseline": {"value": round(value, 3), "unit": UNIT, "cores": cb["cores"], "kind": cb["kind"],
-                         "sample": "%d images over %d steps, extract()+decode() timed per image as cpp-decoder/benchmark/benchmark.cc:31-35" % (images, args.steps)},
+                         "sample": "bounded sample: every host thread decodes %s images for %.1f s per step; %d images over %d steps, "
+                                   "extract()+decode() timed per image as cpp-decoder/benchmark/benchmark.cc:31-35"
+                                   % (args.config, per_step, images, args.steps)},
         "e2e": {"value": round(value, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0, "wall_s": round(time.time() - t0, 2),
+        "gpu_launches": 0, "host_cores": cb["cores"], "wall_s": round(time.time() - t0, 2),
     }
     print(json.dumps(line), flush=True)
 
+
+# ---------------------------------------------------------------------------------------- parity -------
+
+def oracle_digests(base, ids, threads):
+    """md5 of the oracle's planar R,G,B output (oracle/gjd_oracle.c) for the distinct files in `ids`."""
+    import ctypes as C
+    import numpy as np
+    from concurrent.futures import ThreadPoolExecutor
+    lib = oracle_lib()
+
+    def one(i):
+        d = base[i]
+        w, h = C.c_int(), C.c_int()
+        buf = C.cast(C.c_char_p(d), C.c_void_p)
+        rc = lib.gjdo_decode(buf, len(d), C.byref(w), C.byref(h), None, None, None)
+        assert rc == 0, "oracle rejected file %d" % i
+        rgb = np.empty(3 * w.value * h.value, np.uint8)
+        rc = lib.gjdo_decode(buf, len(d), C.byref(w), C.byref(h), None, None, rgb.ctypes.data)
+        assert rc == 0
+        return i, hashlib.md5(rgb.tobytes()).digest()
+
+    with ThreadPoolExecutor(max(1, threads)) as ex:
+        return dict(ex.map(one, sorted(set(ids))))
+
+
+def pick_samples(ids):
+    """One position per distinct file id present in `ids`, spread over the list."""
+    occ = {}
+    for pos, fid in enumerate(ids):
+        occ.setdefault(fid, []).append(pos)
+    return sorted(v[(fid * 7 + 3) % len(v)] for fid, v in occ.items())
+
+
+def make_chunks(ids, weight_of):
+    """Split the rank's image list into resident chunks of at most CHUNK_PIXELS padded pixels."""
+    chunks, cur, acc = [], [], 0
+    for pos, fid in enumerate(ids):
+        w = weight_of[fid]
+        if cur and acc + w > CHUNK_PIXELS:
+            chunks.append(cur)
+            cur, acc = [], 0
+        cur.append(pos)
+        acc += w
+    if cur:
+        chunks.append(cur)
+    return chunks
+
+
+# ---------------------------------------------------------------------------------------- main ---------
 
 def main():
     ap = argparse.ArgumentParser()
@@ -194,10 +301,13 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="gjd")
-    ap.add_argument("--images", type=int, default=int(os.environ.get("GJD_BENCH_IMAGES", "3000")))
+    ap.add_argument("--config", default=os.environ.get("GJD_BENCH_CONFIG", "c3"), choices=["c3", "c5"])
+    ap.add_argument("--images", type=int, default=0, help="c3: images per GPU (3000); c5: images in the global list (24000)")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    if args.images <= 0:
+        args.images = default_images(args.config)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -206,10 +316,8 @@ def main():
         run_reference_arm(args, rank, world)
         return
 
-    import ctypes as C
     import numpy as np
     import torch
-    import gen_synth
     import gjd
 
     if not torch.cuda.is_available():
@@ -230,133 +338,192 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    base = gen_synth.c3_files()
-    files = [base[i % len(base)] for i in range(args.images)]
+    # ---- the rank's images --------------------------------------------------------------------------
+    base, paths, gids = load_workload(args.config, args.images)
+    imbalance, loads = 0.0, None
+    if args.config == "c5":
+        part_of, load, weight = gjd.partition([base[g] for g in gids], world)     # every rank computes the same partition
+        ids = [gids[i] for i in np.nonzero(part_of == rank)[0]]
+        loads = [int(x) for x in load]
+        imbalance = float(max(loads) / (sum(loads) / world) - 1.0)
+    else:
+        ids = gids
+    n_local = len(ids)
+    dims = {}
+    for fid in set(ids):
+        rc, w, h = gjd.peek(base[fid])
+        assert rc == 0
+        dims[fid] = (w, h)
+    weight_of = {fid: (8 * ((w + 7) // 8)) * (8 * ((h + 7) // 8)) for fid, (w, h) in dims.items()}
+    out_bytes = {fid: 3 * w * h for fid, (w, h) in dims.items()}
+    chunks = make_chunks(ids, weight_of)
+    samples = set(pick_samples(ids))
     # the ranks of one node share its cores: each rank's host pool (header parse, unstuffing) gets its share
     local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
+    host_threads = max(2, (os.cpu_count() or 2) // local_world)
     if local_world > 1 and "GJD_HOST_THREADS" not in os.environ:
-        os.environ["GJD_HOST_THREADS"] = str(max(2, (os.cpu_count() or 2) // local_world))
+        os.environ["GJD_HOST_THREADS"] = str(host_threads)
+    want = oracle_digests(base, [ids[p] for p in samples], host_threads)      # the checker, outside every timed region
     dec = gjd.Decoder(local, scratch_bytes=int(os.environ.get("GJD_SCRATCH", str(4 << 30))))
+
+    def check(pos, pixels, leg):
+        got = hashlib.md5(np.ascontiguousarray(pixels).tobytes()).digest()
+        if got != want[ids[pos]]:
+            raise SystemExit("bench.py: PARITY FAILURE in the %s leg: image %d (file %d) differs from the oracle" % (leg, pos, ids[pos]))
 
     # ---- device-resident throughput ("value") ------------------------------------------------------
     sampler = ClockSampler(local)     # started early: nvidia-smi needs a moment before its first sample
-    batch = dec.prepare(files)
-    info = None
-    for _ in range(max(args.warmup, 3)):
-        batch.run()
-        assert batch.sync() == 0, "device reported a corrupt image"
-    info = batch.info()
     stage = np.zeros(4)
+    info_sum = dict(pixels=0, padded_pixels=0, scan_bytes=0, subseqs=0, launches=0)
+    checked = {"value": 0, "e2e": 0, "e2e_device_output": 0}
+    wall = 0.0
     barrier()
     t0 = time.time()
-    w0 = time.perf_counter()
-    for _ in range(args.steps):
-        batch.run()
-        batch.sync()
-        stage += np.array(dec.stage_times())
-    torch.cuda.synchronize()
-    wall = time.perf_counter() - w0
+    for ci, chunk in enumerate(chunks):
+        batch = dec.prepare([base[ids[p]] for p in chunk])
+        for _ in range(max(args.warmup, 3) if ci == 0 else 1):
+            batch.run()
+            assert batch.sync() == 0, "device reported a corrupt image"
+        if ci == 0:
+            barrier()
+            t0 = time.time()
+        w0 = time.perf_counter()
+        for _ in range(args.steps):
+            batch.run()
+            batch.sync()
+            stage += np.array(dec.stage_times())
+        torch.cuda.synchronize()
+        wall += time.perf_counter() - w0
+        info = batch.info()
+        for k in info_sum:
+            info_sum[k] += info[k]
+        for j, p in enumerate(chunk):       # parity of what was just timed: the batch's own output buffers
+            if p in samples:
+                assert batch.status(j) == 0
+                check(p, batch.fetch(j), "value")
+                checked["value"] += 1
+        batch.free()
     t1 = time.time()
     barrier()
     clocks = sampler.stop(t0, t1)
-    dev_ms = float(stage[3])          # CUDA-event time of all K steps on this rank
-    pixels = info["pixels"]
-    # one spot check that the timed path produced real pixels
-    chk = batch.fetch(args.images - 1)
-    assert chk.shape == (3, 1024, 1024) and int(chk.max()) > 0
-    batch.free()
+    dev_ms = float(stage[3])          # CUDA-event time of all K steps over all chunks on this rank
+    pixels = info_sum["pixels"]
 
     # ---- end to end through the C ABI with host buffers ("e2e") -------------------------------------
-    out_bytes = 3 * 1024 * 1024
-    pinned = gjd.PinnedBuffer(out_bytes * args.images)
-    items, hold = dec.make_items(files)
-    for i in range(args.images):
-        items[i].rgb = pinned.ptr + i * out_bytes
+    chunk_out = [sum(out_bytes[ids[p]] for p in c) for c in chunks]
+    pinned = gjd.PinnedBuffer(max(chunk_out))
+    citems = []
+    for c in chunks:
+        items, hold = dec.make_items([base[ids[p]] for p in c])
+        off, offs = 0, []
+        for j, p in enumerate(c):
+            items[j].rgb = pinned.ptr + off
+            offs.append(off)
+            off += out_bytes[ids[p]]
+        citems.append((items, hold, offs))
     e2e_steps = max(1, min(args.e2e_steps, args.steps))
-    dec.decode_batch_raw(items, args.images)      # warm-up: grows the staging/arena buffers
-    barrier()
-    e0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        dec.decode_batch_raw(items, args.images)
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - e0
-    barrier()
-    assert all(items[i].status == 0 for i in range(0, args.images, 97))
-    assert int(pinned.array[-out_bytes:].max()) > 0
-    # whole-job bytes per step, like the values they sit beside (every rank copies its own shard)
-    h2d = sum(len(f) for f in files) * world   # upper bound of the unstuffed scans + tables actually copied
-    d2h = out_bytes * args.images * world
+
+    def e2e_loop(leg, fetch):
+        for items, hold, offs in citems:      # warm-up: grows the staging/arena buffers
+            dec.decode_batch_raw(items, len(offs))
+        barrier()
+        total = 0.0
+        for step in range(e2e_steps):
+            for c, (items, hold, offs) in zip(chunks, citems):
+                e0 = time.perf_counter()
+                dec.decode_batch_raw(items, len(offs))
+                torch.cuda.synchronize()
+                total += time.perf_counter() - e0
+                if step == e2e_steps - 1:     # parity of the last timed step (clock stopped)
+                    for j, p in enumerate(c):
+                        if p in samples:
+                            assert items[j].status == 0
+                            check(p, fetch(offs[j], out_bytes[ids[p]]), leg)
+                            checked[leg] += 1
+                    assert all(items[j].status == 0 for j in range(0, len(offs), 97))
+        barrier()
+        return total
+
+    e2e_s = e2e_loop("e2e", lambda off, n: pinned.array[off:off + n])
+    # whole-job bytes per step, like the values they sit beside
+    h2d_local = sum(len(base[f]) for f in ids)   # upper bound of the unstuffed scans + tables actually copied
+    d2h_local = sum(chunk_out)
 
     # ---- the same call with the pixels left in HBM (rgb_on_device: the data-loader use; extra key) ---
-    dev_out = torch.zeros(out_bytes * args.images, dtype=torch.uint8, device="cuda")
-    for i in range(args.images):
-        items[i].rgb = dev_out.data_ptr() + i * out_bytes
-        items[i].rgb_on_device = 1
-    dec.decode_batch_raw(items, args.images)
-    barrier()
-    e0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        dec.decode_batch_raw(items, args.images)
-    torch.cuda.synchronize()
-    dout_s = time.perf_counter() - e0
-    barrier()
-    assert int(dev_out[-out_bytes:].max()) > 0
+    dev_out = torch.zeros(max(chunk_out), dtype=torch.uint8, device="cuda")
+    for items, hold, offs in citems:
+        for j, off in enumerate(offs):
+            items[j].rgb = dev_out.data_ptr() + off
+            items[j].rgb_on_device = 1
+    dout_s = e2e_loop("e2e_device_output", lambda off, n: dev_out[off:off + n].cpu().numpy())
     del dev_out
 
     # ---- reduce over ranks ---------------------------------------------------------------------------
     t = torch.tensor([dev_ms, e2e_s, wall, dout_s], dtype=torch.float64, device="cuda")
+    s = torch.tensor([pixels, h2d_local, d2h_local, checked["value"], checked["e2e"], checked["e2e_device_output"],
+                      info_sum["launches"] * args.steps, n_local, info_sum["scan_bytes"], info_sum["subseqs"]],
+                     dtype=torch.float64, device="cuda")
     if dist:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(s, op=dist.ReduceOp.SUM)
     dev_ms_max, e2e_s_max, wall_max, dout_s_max = (float(x) for x in t.cpu())
-    total_pixels = pixels * world
+    total_pixels, h2d, d2h, chk_v, chk_e, chk_d, launches, n_total, scan_total, subs_total = (int(x) for x in s.cpu())
     value = total_pixels * args.steps / (dev_ms_max * 1e-3) / 1e6
     e2e_value = total_pixels * e2e_steps / e2e_s_max / 1e6
 
     if rank == 0:
         peak, peak_src = measured_peak()
         t_tr = stage[2] / args.steps * 1e-3
-        algo = info["padded_pixels"] * 6 + info["pixels"] * 3
+        algo = info_sum["padded_pixels"] * 6 + info_sum["pixels"] * 3
         achieved = algo / t_tr / 1e9
-        traffic = None
+        traffic, traffic_src = None, None
         try:
             with open(os.path.join(ROOT, "profiles", "transform_traffic.json")) as f:
-                traffic = json.load(f).get("dram_bytes_per_launch")
+                tj = json.load(f)
+            if args.config == "c3" and args.images == 3000:
+                traffic, traffic_src = tj.get("dram_bytes_per_launch"), tj.get("source")
         except Exception:
             pass
+        cfg = config_dict(args.config, args.images, world)
         line = {
             "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": round(dev_ms_max / args.steps, 3), "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-            "config": {"workload": WORKLOAD % args.images, "images_per_gpu": args.images,
-                       "scan_bytes_per_gpu": info["scan_bytes"], "subsequences_per_gpu": info["subseqs"],
-                       "l2": "inputs+outputs larger than L2 (scans %.2f GB read 3x, RGB %.1f GB written per step)" % (info["scan_bytes"] / 1e9, info["pixels"] * 3 / 1e9),
-                       "timing": "CUDA events on the launching stream per step (value); wall clock around gjd_decode_batch (e2e, %d steps)" % e2e_steps,
-                       "parallelism": "replicas: one sub-batch per GPU, no collective"},
+            "scaling": cfg["scaling"], "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+            "config": cfg,
+            "workload_detail": {"images_decoded_per_step": n_total, "pixels_per_step": total_pixels, "scan_bytes": scan_total,
+                                "subsequences": subs_total, "resident_chunks_rank0": len(chunks),
+                                "timing": "CUDA events on the launching stream per step (value); wall clock around gjd_decode_batch (e2e, %d steps)" % e2e_steps},
+            "parity_checked": min(chk_v, chk_e, chk_d),
+            "parity_detail": {"value": chk_v, "e2e": chk_e, "e2e_device_output": chk_d,
+                              "how": "one image per distinct file and rank, spread over the batch, md5 of the planar pixels vs the oracle's (oracle/gjd_oracle.c) after each timed loop"},
             "stages_ms": {"entropy_sync": round(stage[0] / args.steps, 3), "entropy_write": round(stage[1] / args.steps, 3),
                           "transform": round(stage[2] / args.steps, 3), "pipeline": round(stage[3] / args.steps, 3),
                           "wall_per_step": round(wall_max / args.steps * 1e3, 3)},
             "roofline": {"kernel": "k_transform", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                         "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": algo},
+                         "frac": round(achieved / peak, 4), "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": algo, "launches_per_step_rank0": len(chunks)},
             "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps, "ms_per_step": round(e2e_s_max / e2e_steps * 1e3, 2)},
             "e2e_device_output": {"value": round(total_pixels * e2e_steps / dout_s_max / 1e6, 1), "unit": UNIT,
                                   "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 0, "steps": e2e_steps,
                                   "ms_per_step": round(dout_s_max / e2e_steps * 1e3, 2),
                                   "note": "gjd_decode_batch with host JPEG bytes in, pixels left in device memory (no read-back)"},
-            "gpu_launches": int(info["launches"]) * args.steps,
+            "gpu_launches": launches, "host_cores": os.cpu_count(), "host_threads_per_rank": int(os.environ.get("GJD_HOST_THREADS", os.cpu_count() or 1)),
             "clocks": clocks,
         }
+        if loads is not None:
+            line["shards"] = {"padded_pixels_per_rank": loads, "imbalance": round(imbalance, 6)}
         if world == 1 and not args.no_cpu_baseline:
-            cb, _ = cpu_reference(float(os.environ.get("GJD_CPU_BASELINE_SECONDS", "12")), base, len(base))
+            cb, _ = cpu_reference(float(os.environ.get("GJD_CPU_BASELINE_SECONDS", "12")), base, paths, args.config)
             line["cpu_baseline"] = cb
-            paths = [os.path.join(gen_synth.CACHE, "s%d_1024x1024_q90_o0_r0.jpg" % s) for s in range(len(base))]
+            line["e2e_vs_cpu_baseline"] = round(e2e_value / cb["value"], 2)       # the like-for-like ratio (host bytes in, host pixels out)
+            line["value_vs_cpu_baseline_kernels_only"] = round(value / cb["value"], 1)
             if all(os.path.exists(p) for p in paths):
                 jl = jpeglib_bench(cb["cores"], float(os.environ.get("GJD_JPEGLIB_BASELINE_SECONDS", "6")), paths)
                 if jl:
                     line["cpu_baseline_jpeglib"] = {
                         "value": round(jl["mpix_per_s"], 3), "unit": UNIT, "cores": cb["cores"], "kind": "reference-vendored libjpeg 9e",
-                        "sample": "%d images of the c3 set, %.1f s busy per thread, jpeg_read_header..jpeg_finish_decompress timed (RGB out, JDCT_ISLOW)" % (jl["images"], jl["busy_s_max"])}
+                        "sample": "%d images of the %s set, %.1f s busy per thread, jpeg_read_header..jpeg_finish_decompress timed (RGB out, JDCT_ISLOW)" % (jl["images"], args.config, jl["busy_s_max"])}
         os.write(json_fd, (json.dumps(line) + "\n").encode())
     pinned.free()
     dec.close()

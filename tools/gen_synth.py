@@ -96,6 +96,14 @@ def c5_specs(n_distinct=256):
     return specs
 
 
+def c5_files(n_distinct=256):
+    """The distinct files of config 5 (missing ones are encoded on a thread pool: cjpeg runs as a subprocess)."""
+    from concurrent.futures import ThreadPoolExecutor
+    specs = c5_specs(n_distinct)
+    with ThreadPoolExecutor(max(1, min(16, os.cpu_count() or 1))) as ex:
+        return list(ex.map(lambda s: synth_jpeg(*s), specs))
+
+
 def digest(files):
     m = hashlib.sha256()
     for f in files:
