@@ -62,7 +62,7 @@ bool read_file(const std::string& path, std::vector<uint8_t>& out) {
 struct ShardResult {
     int rc = 0;
     double dev_ms = 0, e2e_s = 0;      /* summed over iterations */
-    uint64_t pixels = 0, bytes = 0, images = 0, failed = 0;
+    uint64_t pixels = 0, bytes = 0, images = 0, failed = 0, e2e_failed = 0;
     std::string err;
 };
 
@@ -106,21 +106,29 @@ void run_shard(int device, const std::vector<const std::vector<uint8_t>*>& files
         r->bytes += bytes;
         r->images += (uint64_t)n;
         if (e2e) {
-            uint8_t* host = (uint8_t*)gjd_host_alloc((size_t)info[0] * 3 + 16);
-            if (!host) { r->rc = GJD_E_NOMEM; r->err = "gjd_host_alloc"; break; }
-            size_t off = 0;
+            /* output offsets and the buffer size come from the SAME loop over the items whose header parses: an image
+             * that parses but later fails to unstuff still owns its region */
+            std::vector<size_t> off((size_t)n, (size_t)-1);
+            size_t total = 0;
             for (int32_t i = 0; i < n; i++) {
                 int32_t w = 0, h = 0;
                 if (gjd_peek(items[i].jpg, items[i].len, &w, &h) == GJD_OK) {
-                    items[i].rgb = host + off;
-                    off += (size_t)w * h * 3;
+                    off[(size_t)i] = total;
+                    total += (size_t)w * h * 3;
                 }
             }
-            gjd_decode_batch(ctx, items.data(), n);     /* warm-up: sizes the staging buffers */
+            uint8_t* host = (uint8_t*)gjd_host_alloc(total + 16);
+            if (!host) { r->rc = GJD_E_NOMEM; r->err = "gjd_host_alloc"; break; }
+            for (int32_t i = 0; i < n; i++) items[i].rgb = off[(size_t)i] == (size_t)-1 ? nullptr : host + off[(size_t)i];
+            int rc = gjd_decode_batch(ctx, items.data(), n);     /* warm-up: sizes the staging buffers */
             auto t0 = std::chrono::steady_clock::now();
-            for (int it = 0; it < iters; it++) r->rc = gjd_decode_batch(ctx, items.data(), n);
+            for (int it = 0; it < iters && rc == GJD_OK; it++) rc = gjd_decode_batch(ctx, items.data(), n);
             r->e2e_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
             gjd_host_free(host);
+            if (rc != GJD_OK) { r->rc = rc; r->err = std::string("e2e: ") + gjd_strerror(rc) + " " + gjd_last_cuda_error(ctx); break; }
+            uint64_t bad = 0;
+            for (int32_t i = 0; i < n; i++) bad += items[i].status != GJD_OK;
+            r->e2e_failed += bad;
         }
     }
     gjd_destroy(ctx);
@@ -182,19 +190,20 @@ int main(int argc, char** argv) {
     double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count();
 
     double dev_ms_max = 0, e2e_max = 0;
-    uint64_t pixels = 0, bytes = 0, images = 0, failed = 0;
+    uint64_t pixels = 0, bytes = 0, images = 0, failed = 0, e2e_failed = 0;
     for (int g = 0; g < gpus; g++) {
         if (res[(size_t)g].rc) { fprintf(stderr, "gjd_bench: device %d: %s\n", g, res[(size_t)g].err.c_str()); return 3; }
         dev_ms_max = std::max(dev_ms_max, res[(size_t)g].dev_ms);
         e2e_max = std::max(e2e_max, res[(size_t)g].e2e_s);
         pixels += res[(size_t)g].pixels; bytes += res[(size_t)g].bytes; images += res[(size_t)g].images; failed += res[(size_t)g].failed;
+        e2e_failed += res[(size_t)g].e2e_failed;
     }
     const double s = dev_ms_max * 1e-3;   /* all devices run concurrently: the slowest shard bounds the job */
     printf("{\"images\": %llu, \"failed\": %llu, \"rejected\": %zu, \"gpus\": %d, \"batch\": %d, \"iters\": %d, "
            "\"device_ms_per_iter\": %.3f, \"images_per_s\": %.1f, \"compressed_MB_per_s\": %.1f, \"MPixel_per_s\": %.1f",
            (unsigned long long)images, (unsigned long long)failed, rejected, gpus, batch, iters, dev_ms_max / iters,
            images * (double)iters / s, bytes * (double)iters / s / 1e6, pixels * (double)iters / s / 1e6);
-    if (e2e) printf(", \"e2e_MPixel_per_s\": %.1f", pixels * (double)iters / e2e_max / 1e6);
+    if (e2e) printf(", \"e2e_MPixel_per_s\": %.1f, \"e2e_failed\": %llu", pixels * (double)iters / e2e_max / 1e6, (unsigned long long)e2e_failed);
     printf(", \"wall_s\": %.2f}\n", wall);
     return 0;
 }

@@ -8,6 +8,7 @@
  * per sub-batch: one staging copy, one descriptor upload, one pipeline of launches, merged D2H copies.
  */
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>   /* header-only; ranges cost nothing unless a profiler is attached */
 
 #include <algorithm>
 #include <atomic>
@@ -17,6 +18,7 @@
 #include <cstring>
 #include <functional>
 #include <mutex>
+#include <new>
 #include <string>
 #include <chrono>
 #include <thread>
@@ -33,6 +35,30 @@
 #define GJD_STR(x) GJD_STR2(x)
 
 namespace {
+
+/* NVTX range per stage of a call (parse / stage+unstuff / H2D / GPU stages / D2H), after the reference's
+ * nvtxRangePush around its decode (cuda-decoder/benchmark/benchmark.cu:9,41,70; README.md:147-166). */
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
+
+/* Every entry point runs on the context's device and leaves the caller's current device as it found it
+ * (a multi-GPU host such as PyTorch keeps its own notion of the current device). */
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = false;
+    explicit DeviceGuard(int device) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        ok = (prev == device) || cudaSetDevice(device) == cudaSuccess;
+        if (prev == device) prev = -1;   /* nothing to restore */
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+/* No C++ exception crosses the C ABI: allocation failures of the host containers become GJD_E_NOMEM. */
+#define GJD_API_TRY try {
+#define GJD_API_CATCH } catch (const std::bad_alloc&) { return GJD_E_NOMEM; } catch (...) { return GJD_E_CUDA; }
 
 /* ---------------------------------------------------------------- worker pool --------- */
 
@@ -62,9 +88,12 @@ public:
         }
         cv_.notify_all();
         work();
-        std::unique_lock<std::mutex> l(m_);
-        done_.wait(l, [this] { return pending_ == 0; });
-        fn_ = nullptr;
+        {
+            std::unique_lock<std::mutex> l(m_);
+            done_.wait(l, [this] { return pending_ == 0; });
+            fn_ = nullptr;
+        }
+        if (failed_.exchange(false)) throw std::bad_alloc();   /* a worker ran out of memory: reported by the caller's thread */
     }
     int size() const { return (int)th_.size() + 1; }
 
@@ -74,7 +103,9 @@ private:
             size_t b = next_.fetch_add(chunk_);
             if (b >= n_) break;
             size_t e = std::min(n_, b + chunk_);
-            for (size_t i = b; i < e; i++) (*fn_)(i);
+            for (size_t i = b; i < e; i++) {
+                try { (*fn_)(i); } catch (...) { failed_.store(true); }
+            }
         }
     }
     void loop() {
@@ -99,6 +130,7 @@ private:
     const std::function<void(size_t)>* fn_ = nullptr;
     size_t n_ = 0, chunk_ = 1;
     std::atomic<size_t> next_{0};
+    std::atomic<bool> failed_{false};
     int pending_ = 0;
     uint64_t gen_ = 0;
     bool stop_ = false;
@@ -106,20 +138,23 @@ private:
 
 /* ---------------------------------------------------------------- buffers ------------- */
 
+/* Device arena that only grows.  Stream-ordered (cudaMallocAsync / cudaFreeAsync on the owning slot's stream): growing
+ * one slot's arena does not synchronise the device while the other slots' kernels and copies are in flight, which a
+ * cudaFree would.  The context raises the pool's release threshold so freed blocks stay with the process. */
 struct DevBuf {
     void* p = nullptr;
     size_t cap = 0;
-    cudaError_t ensure(size_t bytes) {
+    cudaError_t ensure(size_t bytes, cudaStream_t s) {
         if (bytes <= cap) return cudaSuccess;
-        if (p) cudaFree(p);
+        if (p) cudaFreeAsync(p, s);
         p = nullptr; cap = 0;
         size_t want = bytes + bytes / 8 + 4096;
-        cudaError_t e = cudaMalloc(&p, want);
-        if (e != cudaSuccess) { e = cudaMalloc(&p, bytes); want = bytes; }
-        if (e == cudaSuccess) cap = want;
+        cudaError_t e = cudaMallocAsync(&p, want, s);
+        if (e != cudaSuccess) { cudaGetLastError(); e = cudaMallocAsync(&p, bytes, s); want = bytes; }
+        if (e == cudaSuccess) cap = want; else p = nullptr;
         return e;
     }
-    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    void release(cudaStream_t s) { if (p) cudaFreeAsync(p, s); p = nullptr; cap = 0; }
 };
 
 struct PinBuf {
@@ -176,12 +211,12 @@ struct gjd_batch {
 
     void release() {
         h_scan.release(); h_meta.release(); h_status.release();
-        d_scan.release(); d_meta.release(); d_luts.release(); d_lutc.release(); d_sinfo.release(); d_seqmaps.release();
-        d_coef.release(); d_blkmeta.release(); d_tilebase.release(); d_tileimg.release(); d_tbimg.release(); d_rgb.release();
-        d_status.release();
+        for (DevBuf* d : {&d_scan, &d_meta, &d_luts, &d_lutc, &d_sinfo, &d_seqmaps, &d_coef, &d_blkmeta, &d_tilebase, &d_tileimg,
+                          &d_tbimg, &d_rgb, &d_status})
+            d->release(stream);
         if (ev_ok) for (auto& e : ev.e) cudaEventDestroy(e);
         ev_ok = false;
-        if (stream) cudaStreamDestroy(stream);
+        if (stream) { cudaStreamSynchronize(stream); cudaStreamDestroy(stream); }
         stream = nullptr;
     }
 };
@@ -197,6 +232,7 @@ struct gjd_ctx {
     uint64_t min_subseqs = 1200000;   /* ~4 waves of 148 SMs x 2048 threads */
     uint32_t max_tb_tiles = GJD_TB_TILES;   /* GJD_TB_TILES_MAX: measurement knob (power of two, 4..128) */
     int force_sub_log2 = 0;           /* GJD_SUB_LOG2: fixed subsequence length (tests, experiments) */
+    bool kernel_attrs_set = false;    /* the > 48 KB dynamic shared memory opt-in of k_huff_write (per context) */
 };
 
 namespace {
@@ -235,7 +271,7 @@ size_t estimate_bytes(const gjd_item& it, const ItemGeom& g) {
  * pre: parsed/geom for the items are already filled by parse_all (indexed from `first`).
  */
 int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* parsed, const ItemGeom* geom,
-                int32_t n, bool own_output) {
+                int32_t n) {
     int rc = batch_init(ctx, b);
     if (rc) return rc;
     b->n = n;
@@ -259,6 +295,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
 
     std::vector<long> ulen(n, 0);
     std::vector<std::vector<uint32_t>> rst_off(n), rst_len(n);   /* restart intervals (images with DRI only) */
+    nvtxRangePushA("gjd: unstuff scans into pinned staging");
     ctx->pool->parallel_for((size_t)n, 4, [&](size_t i) {
         if (b->geom[i].status != GJD_OK) return;
         const GjdParsed& p = parsed[i];
@@ -269,6 +306,8 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         memset(dst + m, 0, 16);
         ulen[i] = m;
     });
+    nvtxRangePop();
+    NvtxRange r_desc("gjd: descriptors + H2D + table kernels");
 
     /* subsequence length for this batch: the longest that still leaves >= GJD_MIN_SUBSEQS threads */
     uint32_t sub_log2 = GJD_SUB_LOG2_MIN;
@@ -303,6 +342,10 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         if (g.status != GJD_OK) continue;
         const GjdParsed& p = parsed[i];
         if ((uint64_t)ulen[i] * 8 >= 0xffff0000ull) { g.status = GJD_E_UNSUPPORTED; continue; }
+        {   /* coefficient slot indices (sinfo counts, seq_base, the write pass's idx0) are 32-bit */
+            const uint64_t mc = (uint64_t)((g.width + 7) / 8) * (uint64_t)((g.height + 7) / 8);
+            if (mc * (p.components == 1 ? 1u : 3u) * 64u >= 0xffffffffull) { g.status = GJD_E_UNSUPPORTED; continue; }
+        }
         GjdImage d;
         memset(&d, 0, sizeof(d));
         d.width = (uint32_t)g.width;
@@ -318,7 +361,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         d.row_pitch = (uint32_t)g.pitch;
         d.plane_stride = g.pstride;
         d.layout = (uint16_t)g.layout;
-        if (items[i].rgb_on_device && items[i].rgb && !own_output) {
+        if (items[i].rgb_on_device && items[i].rgb) {
             d.out_is_ptr = 1;
             d.out_off = (uint64_t)(uintptr_t)items[i].rgb;
         } else {
@@ -405,7 +448,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     v.n_img = n_img;
     v.n_seg = (uint32_t)b->segs.size();
     for (const GjdImage& im : b->imgs) {
-        v.any_interleaved |= im.layout == GJD_LAYOUT_INTERLEAVED;
+        v.any_interleaved |= im.layout != GJD_LAYOUT_PLANAR;
         v.any_gray |= im.gray;
     }
     v.n_seq = seq;
@@ -427,19 +470,19 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     memcpy((uint8_t*)b->h_meta.p + o_dht, b->dhts.data(), sizeof(GjdDhtSet) * b->dhts.size());
     memcpy((uint8_t*)b->h_meta.p + o_q, b->quants.data(), sizeof(GjdQuantSet) * b->quants.size());
 
-    GJD_TRY(b->d_meta.ensure(meta));
-    GJD_TRY(b->d_scan.ensure(b->scan_alloc));
-    GJD_TRY(b->d_luts.ensure(sizeof(GjdLutSet) * b->dhts.size()));
-    GJD_TRY(b->d_lutc.ensure(sizeof(GjdLutCount) * b->dhts.size()));
-    GJD_TRY(b->d_sinfo.ensure((size_t)seq * GJD_SEQ_SUBS * sizeof(uint2)));
-    GJD_TRY(b->d_seqmaps.ensure((size_t)seq * 4 * sizeof(uint32_t)));
-    GJD_TRY(b->d_coef.ensure((size_t)tile * 96 * 64 * sizeof(int16_t)));
-    GJD_TRY(b->d_tbimg.ensure((size_t)tb * sizeof(uint32_t)));
-    GJD_TRY(b->d_blkmeta.ensure((size_t)tile * 96 * sizeof(uint32_t)));
-    GJD_TRY(b->d_tilebase.ensure((size_t)tile * sizeof(int4)));
-    GJD_TRY(b->d_tileimg.ensure((size_t)tile * sizeof(uint32_t)));
-    GJD_TRY(b->d_rgb.ensure(std::max<size_t>(b->rgb_alloc, 256)));
-    GJD_TRY(b->d_status.ensure((size_t)(n_img + 1) * sizeof(uint32_t)));
+    GJD_TRY(b->d_meta.ensure(meta, b->stream));
+    GJD_TRY(b->d_scan.ensure(b->scan_alloc, b->stream));
+    GJD_TRY(b->d_luts.ensure(sizeof(GjdLutSet) * b->dhts.size(), b->stream));
+    GJD_TRY(b->d_lutc.ensure(sizeof(GjdLutCount) * b->dhts.size(), b->stream));
+    GJD_TRY(b->d_sinfo.ensure((size_t)seq * GJD_SEQ_SUBS * sizeof(uint2), b->stream));
+    GJD_TRY(b->d_seqmaps.ensure((size_t)seq * 4 * sizeof(uint32_t), b->stream));
+    GJD_TRY(b->d_coef.ensure((size_t)tile * 96 * 64 * sizeof(int16_t), b->stream));
+    GJD_TRY(b->d_tbimg.ensure((size_t)tb * sizeof(uint32_t), b->stream));
+    GJD_TRY(b->d_blkmeta.ensure((size_t)tile * 96 * sizeof(uint32_t), b->stream));
+    GJD_TRY(b->d_tilebase.ensure((size_t)tile * sizeof(int4), b->stream));
+    GJD_TRY(b->d_tileimg.ensure((size_t)tile * sizeof(uint32_t), b->stream));
+    GJD_TRY(b->d_rgb.ensure(std::max<size_t>(b->rgb_alloc, 256), b->stream));
+    GJD_TRY(b->d_status.ensure((size_t)(n_img + 1) * sizeof(uint32_t), b->stream));
     GJD_TRY(b->h_status.ensure((size_t)(n_img + 1) * sizeof(uint32_t)));
 
     v.imgs = (const GjdImage*)((uint8_t*)b->d_meta.p + o_img);
@@ -471,7 +514,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
 
 int batch_enqueue_run(gjd_ctx* ctx, gjd_batch* b) {
     if (b->view.n_img == 0) { b->launches = 0; b->ran = true; return GJD_OK; }
-    GJD_TRY(gjd_launch_pipeline(b->view, b->stream, &b->ev, ctx->transform_variant, &b->launches));
+    GJD_TRY(gjd_launch_pipeline(b->view, b->stream, &b->ev, ctx->transform_variant, &b->launches, false, &ctx->kernel_attrs_set));
     GJD_TRY(cudaMemcpyAsync(b->h_status.p, b->d_status.p, (size_t)(b->view.n_img + 1) * sizeof(uint32_t),
                             cudaMemcpyDeviceToHost, b->stream));
     b->ran = true;
@@ -484,6 +527,7 @@ int batch_enqueue_run(gjd_ctx* ctx, gjd_batch* b) {
  * streams, kept for correctness), iterate the fix-up to its fixed point and redo the later stages. */
 int batch_wait(gjd_ctx* ctx, gjd_batch* b) {
     if (!b->stream) return GJD_OK;
+    NvtxRange r("gjd: wait for the sub-batch");
     GJD_TRY(cudaStreamSynchronize(b->stream));
     if (!b->ran || b->view.n_img == 0) return GJD_OK;
     uint32_t* hst = (uint32_t*)b->h_status.p;
@@ -496,7 +540,7 @@ int batch_wait(gjd_ctx* ctx, gjd_batch* b) {
         GJD_TRY(cudaStreamSynchronize(b->stream));
     }
     int launches = 0;
-    GJD_TRY(gjd_launch_pipeline(b->view, b->stream, nullptr, ctx->transform_variant, &launches, true));
+    GJD_TRY(gjd_launch_pipeline(b->view, b->stream, nullptr, ctx->transform_variant, &launches, true, &ctx->kernel_attrs_set));
     GJD_TRY(cudaMemcpyAsync(b->h_status.p, b->d_status.p, (size_t)(b->view.n_img + 1) * sizeof(uint32_t),
                             cudaMemcpyDeviceToHost, b->stream));
     GJD_TRY(cudaStreamSynchronize(b->stream));
@@ -520,6 +564,7 @@ void set_item_status(gjd_batch* b, gjd_item* items) {
 /* Header parse of every item (parallel). */
 void parse_all(gjd_ctx* ctx, const gjd_item* items, int32_t n, std::vector<GjdParsed>& parsed,
                std::vector<ItemGeom>& geom) {
+    NvtxRange r("gjd: parse headers");
     parsed.resize(n);
     geom.assign(n, ItemGeom());
     ctx->pool->parallel_for((size_t)n, 16, [&](size_t i) {
@@ -530,10 +575,12 @@ void parse_all(gjd_ctx* ctx, const gjd_item* items, int32_t n, std::vector<GjdPa
         g.height = parsed[i].height;
         if (rc) { g.status = rc; return; }
         g.layout = items[i].layout;
-        if (g.layout == GJD_LAYOUT_INTERLEAVED) {
-            g.pitch = items[i].row_pitch ? items[i].row_pitch : 3 * (size_t)g.width;
+        if (g.layout == GJD_LAYOUT_INTERLEAVED || g.layout == GJD_LAYOUT_INTERLEAVED_I16) {
+            const size_t bpp = g.layout == GJD_LAYOUT_INTERLEAVED ? 3 : 6;        /* bytes per pixel */
+            g.pitch = items[i].row_pitch ? items[i].row_pitch : bpp * (size_t)g.width;
             g.pstride = 0;
-            if (g.pitch < 3 * (size_t)g.width || g.pitch > 0xffffffffull) { g.status = GJD_E_ARG; return; }
+            if (g.pitch < bpp * (size_t)g.width || g.pitch > 0xffffffffull) { g.status = GJD_E_ARG; return; }
+            if (bpp == 6 && ((g.pitch & 1u) || ((uintptr_t)items[i].rgb & 1u))) { g.status = GJD_E_ARG; return; }   /* int16 elements */
             g.out_bytes = g.pitch * (size_t)g.height;
             return;
         }
@@ -581,7 +628,9 @@ int gjd_create(gjd_ctx** out, int device, size_t scratch_bytes_hint) {
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) return GJD_E_NODEVICE;
     if (device < 0 || device >= count) return GJD_E_ARG;
-    if (cudaSetDevice(device) != cudaSuccess) return GJD_E_NODEVICE;
+    DeviceGuard guard(device);
+    if (!guard.ok) return GJD_E_NODEVICE;
+    GJD_API_TRY
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return GJD_E_NODEVICE;
     if (prop.major < 10) return GJD_E_NODEVICE;   /* kernels are built for sm_100a only */
@@ -594,7 +643,7 @@ int gjd_create(gjd_ctx** out, int device, size_t scratch_bytes_hint) {
     threads = std::max(1, std::min(threads, 64));
     ctx->pool = new Pool(threads - 1);
     if (const char* e = getenv("GJD_TRANSFORM_VARIANT")) ctx->transform_variant = atoi(e);
-    if (const char* e = getenv("GJD_SUB_LOG2")) {
+    if (const char* e = getenv("GJD_SUB_LOG2")) {   /* 8..16: beyond the 10..13 the library picks from, for the tests */
         int k = atoi(e);
         if (k >= 8 && k <= 16) ctx->force_sub_log2 = k;
     }
@@ -603,13 +652,21 @@ int gjd_create(gjd_ctx** out, int device, size_t scratch_bytes_hint) {
         if (v >= 4 && v <= 128 && (v & (v - 1)) == 0) ctx->max_tb_tiles = (uint32_t)v;
     }
     if (const char* e = getenv("GJD_MIN_SUBSEQS")) ctx->min_subseqs = (uint64_t)std::max(1ll, atoll(e));
+    {   /* the arenas are stream-ordered allocations: keep what they free inside the process */
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+            uint64_t keep = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+    }
     *out = ctx;
     return GJD_OK;
+    GJD_API_CATCH
 }
 
 void gjd_destroy(gjd_ctx* ctx) {
     if (!ctx) return;
-    cudaSetDevice(ctx->device);
+    DeviceGuard guard(ctx->device);
     for (auto& s : ctx->slot) {
         if (s.stream) cudaStreamSynchronize(s.stream);
         s.release();
@@ -620,11 +677,13 @@ void gjd_destroy(gjd_ctx* ctx) {
 
 int gjd_peek(const uint8_t* jpg, size_t len, int32_t* width, int32_t* height) {
     if (!jpg) return GJD_E_ARG;
+    GJD_API_TRY
     GjdParsed p;
     int rc = gjd_parse_headers(jpg, len, &p);
     if (width) *width = p.width;
     if (height) *height = p.height;
     return rc;
+    GJD_API_CATCH
 }
 
 void* gjd_host_alloc(size_t bytes) {
@@ -636,6 +695,7 @@ void gjd_host_free(void* p) { if (p) cudaFreeHost(p); }
 
 /* D2H of every image of a staged+run batch into the callers' buffers; adjacent regions merge. */
 static int enqueue_d2h(gjd_ctx* ctx, gjd_batch* b, gjd_item* items) {
+    NvtxRange r("gjd: D2H pixels");
     const uint8_t* dbase = (const uint8_t*)b->d_rgb.p;
     uint8_t* run_dst = nullptr;
     const uint8_t* run_src = nullptr;
@@ -660,8 +720,11 @@ static int enqueue_d2h(gjd_ctx* ctx, gjd_batch* b, gjd_item* items) {
 
 int gjd_decode_batch(gjd_ctx* ctx, gjd_item* items, int32_t n) {
     if (!ctx || (n > 0 && !items) || n < 0) return GJD_E_ARG;
-    if (cudaSetDevice(ctx->device) != cudaSuccess) return GJD_E_NODEVICE;
+    DeviceGuard guard(ctx->device);
+    if (!guard.ok) return GJD_E_NODEVICE;
     if (n == 0) return GJD_OK;
+    GJD_API_TRY
+    NvtxRange whole("gjd_decode_batch");
     std::vector<GjdParsed> parsed;
     std::vector<ItemGeom> geom;
     parse_all(ctx, items, n, parsed, geom);
@@ -710,7 +773,7 @@ int gjd_decode_batch(gjd_ctx* ctx, gjd_item* items, int32_t n) {
         if (rc) break;
         gjd_batch* b = &ctx->slot[s];
         const Span& sp = spans[k];
-        rc = batch_stage(ctx, b, items + sp.first, parsed.data() + sp.first, geom.data() + sp.first, sp.count, false);
+        rc = batch_stage(ctx, b, items + sp.first, parsed.data() + sp.first, geom.data() + sp.first, sp.count);
         if (rc) break;
         rc = batch_enqueue_run(ctx, b);
         if (rc) break;
@@ -725,18 +788,22 @@ int gjd_decode_batch(gjd_ctx* ctx, gjd_item* items, int32_t n) {
         for (int32_t i = 0; i < n; i++)
             if (items[i].status == GJD_OK && geom[i].status != GJD_OK) items[i].status = geom[i].status;
     return rc;
+    GJD_API_CATCH
 }
 
 int gjd_batch_prepare(gjd_ctx* ctx, gjd_item* items, int32_t n, gjd_batch** out) {
     if (!ctx || !out || (n > 0 && !items) || n < 0) return GJD_E_ARG;
     *out = nullptr;
-    if (cudaSetDevice(ctx->device) != cudaSuccess) return GJD_E_NODEVICE;
+    DeviceGuard guard(ctx->device);
+    if (!guard.ok) return GJD_E_NODEVICE;
     gjd_batch* b = new (std::nothrow) gjd_batch();
     if (!b) return GJD_E_NOMEM;
+    try {
+    NvtxRange whole("gjd_batch_prepare");
     std::vector<ItemGeom> geom;
     parse_all(ctx, items, n, b->parsed, geom);
-    /* items without a caller buffer get a tight library-owned device buffer */
-    int rc = batch_stage(ctx, b, items, b->parsed.data(), geom.data(), n, false);
+    /* items[i].rgb == NULL (or a host pointer): the pixels land in the batch's own device arena, read with gjd_batch_fetch */
+    int rc = batch_stage(ctx, b, items, b->parsed.data(), geom.data(), n);
     if (rc == GJD_OK && cudaStreamSynchronize(b->stream) != cudaSuccess) rc = cuda_fail(ctx, cudaGetLastError(), "prepare");
     if (rc != GJD_OK) {
         b->release();
@@ -748,16 +815,24 @@ int gjd_batch_prepare(gjd_ctx* ctx, gjd_item* items, int32_t n, gjd_batch** out)
     b->parsed.shrink_to_fit();
     *out = b;
     return GJD_OK;
+    } catch (...) {
+        b->release();
+        delete b;
+        return GJD_E_NOMEM;
+    }
 }
 
 int gjd_batch_run(gjd_ctx* ctx, gjd_batch* b) {
     if (!ctx || !b) return GJD_E_ARG;
-    if (cudaSetDevice(ctx->device) != cudaSuccess) return GJD_E_NODEVICE;
+    DeviceGuard guard(ctx->device);
+    if (!guard.ok) return GJD_E_NODEVICE;
     return batch_enqueue_run(ctx, b);
 }
 
 int gjd_batch_sync(gjd_ctx* ctx, gjd_batch* b) {
     if (!ctx || !b) return GJD_E_ARG;
+    DeviceGuard guard(ctx->device);
+    if (!guard.ok) return GJD_E_NODEVICE;
     int w = batch_wait(ctx, b);
     if (w < 0) return w;
     set_item_status(b, nullptr);
@@ -773,13 +848,15 @@ int gjd_batch_status(gjd_ctx* ctx, gjd_batch* b, int32_t i) {
 
 int gjd_batch_fetch(gjd_ctx* ctx, gjd_batch* b, int32_t i, uint8_t* rgb_host) {
     if (!ctx || !b || !rgb_host || i < 0 || i >= b->n) return GJD_E_ARG;
+    DeviceGuard guard(ctx->device);
+    if (!guard.ok) return GJD_E_NODEVICE;
     int32_t k = b->img_of[i];
     if (k < 0) return b->geom[i].status ? b->geom[i].status : GJD_E_ARG;
     const GjdImage& d = b->imgs[k];
     const uint8_t* src = d.out_is_ptr ? (const uint8_t*)(uintptr_t)d.out_off : (const uint8_t*)b->d_rgb.p + d.out_off;
-    if (d.layout == GJD_LAYOUT_INTERLEAVED) {
-        GJD_TRY(cudaMemcpy2DAsync(rgb_host, 3 * (size_t)d.width, src, d.row_pitch, 3 * (size_t)d.width, d.height,
-                                  cudaMemcpyDeviceToHost, b->stream));
+    if (d.layout != GJD_LAYOUT_PLANAR) {
+        const size_t row = (d.layout == GJD_LAYOUT_INTERLEAVED ? 3 : 6) * (size_t)d.width;
+        GJD_TRY(cudaMemcpy2DAsync(rgb_host, row, src, d.row_pitch, row, d.height, cudaMemcpyDeviceToHost, b->stream));
     } else {
         for (int c = 0; c < 3; c++)
             GJD_TRY(cudaMemcpy2DAsync(rgb_host + (size_t)c * d.width * d.height, d.width, src + (size_t)c * d.plane_stride,
@@ -791,10 +868,8 @@ int gjd_batch_fetch(gjd_ctx* ctx, gjd_batch* b, int32_t i, uint8_t* rgb_host) {
 
 void gjd_batch_free(gjd_ctx* ctx, gjd_batch* b) {
     if (!b) return;
-    if (ctx) {
-        cudaSetDevice(ctx->device);
-        if (ctx->last == b) ctx->last = nullptr;
-    }
+    DeviceGuard guard(ctx ? ctx->device : 0);
+    if (ctx && ctx->last == b) ctx->last = nullptr;
     if (b->stream) cudaStreamSynchronize(b->stream);
     b->release();
     delete b;
@@ -811,6 +886,8 @@ int gjd_stage_times(gjd_ctx* ctx, float ms[4]) {
     if (!ctx || !ms) return GJD_E_ARG;
     gjd_batch* b = ctx->last;
     if (!b || !b->ev_ok || !b->ran || b->view.n_img == 0) return GJD_E_ARG;
+    DeviceGuard guard(ctx->device);
+    if (!guard.ok) return GJD_E_NODEVICE;
     GJD_TRY(cudaEventSynchronize(b->ev.e[4]));
     GJD_TRY(cudaEventElapsedTime(&ms[0], b->ev.e[1], b->ev.e[2]));
     GJD_TRY(cudaEventElapsedTime(&ms[1], b->ev.e[2], b->ev.e[3]));
@@ -821,6 +898,8 @@ int gjd_stage_times(gjd_ctx* ctx, float ms[4]) {
 
 int gjd_decode_coeffs(gjd_ctx* ctx, const uint8_t* jpg, size_t len, int16_t* coeffs_host) {
     if (!ctx || !jpg || !coeffs_host) return GJD_E_ARG;
+    DeviceGuard guard(ctx->device);
+    if (!guard.ok) return GJD_E_NODEVICE;
     gjd_item it;
     memset(&it, 0, sizeof(it));
     it.jpg = jpg;
@@ -835,11 +914,11 @@ int gjd_decode_coeffs(gjd_ctx* ctx, const uint8_t* jpg, size_t len, int16_t* coe
         int rc0 = rc;
         size_t ncoef = (size_t)b->imgs[0].mcu_count * (b->imgs[0].gray ? 64 : 192);
         DevBuf tmp;
-        cudaError_t e = tmp.ensure(ncoef * sizeof(int16_t));
+        cudaError_t e = tmp.ensure(ncoef * sizeof(int16_t), b->stream);
         if (e == cudaSuccess) e = gjd_launch_export_coefs(b->view, (int16_t*)tmp.p, b->stream);
         if (e == cudaSuccess) e = cudaMemcpyAsync(coeffs_host, tmp.p, ncoef * sizeof(int16_t), cudaMemcpyDeviceToHost, b->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
-        tmp.release();
+        tmp.release(b->stream);
         rc = e == cudaSuccess ? rc0 : cuda_fail(ctx, e, "export_coefs");
     }
     gjd_batch_free(ctx, b);
@@ -849,11 +928,12 @@ int gjd_decode_coeffs(gjd_ctx* ctx, const uint8_t* jpg, size_t len, int16_t* coe
 int gjd_test_color(gjd_ctx* ctx, const int16_t* y, const int16_t* cb, const int16_t* cr, size_t n,
                    uint8_t* r, uint8_t* g, uint8_t* bl) {
     if (!ctx || !y || !cb || !cr || !r || !g || !bl) return GJD_E_ARG;
-    if (cudaSetDevice(ctx->device) != cudaSuccess) return GJD_E_NODEVICE;
+    DeviceGuard guard(ctx->device);
+    if (!guard.ok) return GJD_E_NODEVICE;
     if (n == 0) return GJD_OK;
     DevBuf in, out;
-    GJD_TRY(in.ensure(n * 6));
-    GJD_TRY(out.ensure(n * 3));
+    GJD_TRY(in.ensure(n * 6, 0));
+    GJD_TRY(out.ensure(n * 3, 0));
     int16_t* di = (int16_t*)in.p;
     uint8_t* dout = (uint8_t*)out.p;
     int rc = GJD_OK;
@@ -865,19 +945,20 @@ int gjd_test_color(gjd_ctx* ctx, const int16_t* y, const int16_t* cb, const int1
     if (e == cudaSuccess) e = cudaMemcpy(g, dout + n, n, cudaMemcpyDeviceToHost);
     if (e == cudaSuccess) e = cudaMemcpy(bl, dout + 2 * n, n, cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) rc = cuda_fail(ctx, e, "gjd_test_color");
-    in.release();
-    out.release();
+    in.release(0);
+    out.release(0);
     return rc;
 }
 
 int gjd_test_idct(gjd_ctx* ctx, const int16_t* coef_zz, size_t nblocks, const uint8_t quant_zz[64], int16_t* samples) {
     if (!ctx || !coef_zz || !quant_zz || !samples) return GJD_E_ARG;
-    if (cudaSetDevice(ctx->device) != cudaSuccess) return GJD_E_NODEVICE;
+    DeviceGuard guard(ctx->device);
+    if (!guard.ok) return GJD_E_NODEVICE;
     if (nblocks == 0) return GJD_OK;
     DevBuf in, out, q;
-    GJD_TRY(in.ensure(nblocks * 128));
-    GJD_TRY(out.ensure(nblocks * 128));
-    GJD_TRY(q.ensure(256));
+    GJD_TRY(in.ensure(nblocks * 128, 0));
+    GJD_TRY(out.ensure(nblocks * 128, 0));
+    GJD_TRY(q.ensure(256, 0));
     int32_t hq[64];
     for (int i = 0; i < 64; i++) hq[i] = quant_zz[i];
     int rc = GJD_OK;
@@ -886,7 +967,7 @@ int gjd_test_idct(gjd_ctx* ctx, const int16_t* coef_zz, size_t nblocks, const ui
     if (e == cudaSuccess) e = gjd_launch_test_idct((const int16_t*)in.p, nblocks, (const int32_t*)q.p, (int16_t*)out.p, 0);
     if (e == cudaSuccess) e = cudaMemcpy(samples, out.p, nblocks * 128, cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) rc = cuda_fail(ctx, e, "gjd_test_idct");
-    in.release(); out.release(); q.release();
+    in.release(0); out.release(0); q.release(0);
     return rc;
 }
 

@@ -18,6 +18,8 @@
  */
 #include "gjd_kernels.h"
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "gjd_devfn.cuh"
 #include "../../include/gjd.h"
 
@@ -536,6 +538,31 @@ __device__ __forceinline__ void gjd_block_to_samples(const uint32_t* w, const ui
                                  (uint32_t)v[8 * r + 7] * 65536u + (uint32_t)v[8 * r + 6]);
 }
 
+/* 8 pixels of one row as int16 R,G,B triples (GJD_LAYOUT_INTERLEAVED_I16: element type and order of the reference's
+ * outputChannels, cuda-decoder/src/parser.cu:571-573): 48 bytes per lane.  r8/g8/b8 hold the 8 clamped bytes of each
+ * channel; n = pixels of this row inside the image (1..8); vec = the 48 bytes are 16-byte aligned and n == 8. */
+__device__ __forceinline__ void gjd_store_row_i16(uint8_t* px, uint64_t r8, uint64_t g8, uint64_t b8, uint32_t n, bool vec) {
+    if (vec) {
+        uint32_t w[12];
+#pragma unroll
+        for (int e = 0; e < 24; e += 2) {   /* element e = pixel e / 3, channel e % 3 */
+            const uint64_t lo = (e % 3 == 0 ? r8 : e % 3 == 1 ? g8 : b8) >> (8 * (e / 3));
+            const uint64_t hi = ((e + 1) % 3 == 0 ? r8 : (e + 1) % 3 == 1 ? g8 : b8) >> (8 * ((e + 1) / 3));
+            w[e / 2] = ((uint32_t)lo & 0xffu) | (((uint32_t)hi & 0xffu) << 16);
+        }
+#pragma unroll
+        for (int j = 0; j < 3; j++) __stcs(reinterpret_cast<uint4*>(px) + j, make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]));
+    } else {
+        int16_t* o = reinterpret_cast<int16_t*>(px);
+#pragma unroll 1
+        for (uint32_t x = 0; x < n; x++) {
+            o[3u * x] = (int16_t)((r8 >> (8u * x)) & 0xffu);
+            o[3u * x + 1u] = (int16_t)((g8 >> (8u * x)) & 0xffu);
+            o[3u * x + 2u] = (int16_t)((b8 >> (8u * x)) & 0xffu);
+        }
+    }
+}
+
 /*
  * One thread block (3 warps) per b.tb_tiles (<= GJD_TB_TILES) tiles of one image; per tile, warp c takes component c
  * and lane l the 8x8 block of MCU l:
@@ -581,8 +608,9 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
     uint8_t* out = d.out_is_ptr ? reinterpret_cast<uint8_t*>(d.out_off) : b.rgb + d.out_off;
     const size_t pitch = d.row_pitch, pstride = d.plane_stride;
     /* ILV = false: the batch holds planar images only (the common case keeps the shorter kernel) */
-    const bool interleaved = ILV && d.layout == GJD_LAYOUT_INTERLEAVED;
-    const bool aligned = (((size_t)out | pitch | (interleaved ? 0 : pstride)) & 7u) == 0;
+    const bool interleaved = ILV && d.layout != GJD_LAYOUT_PLANAR;
+    const bool wide = ILV && d.layout == GJD_LAYOUT_INTERLEAVED_I16;      /* int16 elements: 6 bytes per pixel */
+    const bool aligned = (((size_t)out | pitch | (interleaved ? 0 : pstride)) & (wide ? 15u : 7u)) == 0;
     const uint32_t* q = QGLOBAL ? b.quants[d.quant_id].packed[c] : sq[c];
 
 #pragma unroll 1
@@ -641,7 +669,7 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
         /* rows of this warp that exist in the image (none for lanes past the last MCU) */
         const uint32_t rows_left = (valid && y0 < H) ? H - y0 : 0u;
         const uint32_t r1 = min(3u * c + 2u, rows_left);
-        uint8_t* rowp = out + (size_t)(y0 + r0) * pitch + (interleaved ? (size_t)x0 * 3u : (size_t)x0);
+        uint8_t* rowp = out + (size_t)(y0 + r0) * pitch + (interleaved ? (size_t)x0 * (wide ? 6u : 3u) : (size_t)x0);
 #pragma unroll 1
         for (uint32_t r = r0; r < r1; r++, rowp += pitch) {
             const uint4 y4 = smp[t & 1u][0][r][lane], b4 = smp[t & 1u][1][r][lane], r4 = smp[t & 1u][2][r][lane];
@@ -675,6 +703,10 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
                     const uint64_t Ge = (uint64_t)gjd_color_g_exact((int)ys[x] - 256, (int)bs[x] - 256, (int)rs[x] - 256);
                     g8 = (g8 & ~(0xffull << (8u * x))) | (Ge << (8u * x));
                 }
+            }
+            if (wide) {          /* block-uniform: int16 R,G,B triples, 48 bytes per lane */
+                gjd_store_row_i16(rowp, ((uint64_t)pr[1] << 32) | pr[0], g8, ((uint64_t)pb[1] << 32) | pb[0], min(8u, W - x0), fast);
+                continue;
             }
             if (interleaved) {   /* block-uniform: R,G,B,R,G,B,... 24 bytes per lane, 768 contiguous bytes per warp */
                 uint8_t* px = rowp;
@@ -742,8 +774,9 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_gray(Gjd
     const uint32_t W = d.width, H = d.height, ri = d.restart_interval;
     uint8_t* out = d.out_is_ptr ? reinterpret_cast<uint8_t*>(d.out_off) : b.rgb + d.out_off;
     const size_t pitch = d.row_pitch, pstride = d.plane_stride;
-    const bool interleaved = d.layout == GJD_LAYOUT_INTERLEAVED;
-    const bool aligned = (((size_t)out | pitch | (interleaved ? 0 : pstride)) & 7u) == 0;
+    const bool interleaved = d.layout != GJD_LAYOUT_PLANAR;
+    const bool wide = d.layout == GJD_LAYOUT_INTERLEAVED_I16;
+    const bool aligned = (((size_t)out | pitch | (interleaved ? 0 : pstride)) & (wide ? 15u : 7u)) == 0;
     const uint32_t* meta_img = b.meta + (size_t)d.tile_first * 96u;
 
 #pragma unroll 1
@@ -810,7 +843,7 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_gray(Gjd
         const uint32_t by = blkno / d.mcus_x, bx = blkno - by * d.mcus_x;
         const uint32_t x0 = bx * 8u, y0 = by * 8u;
         const bool fast = aligned && (x0 + 8u <= W);
-        uint8_t* rowp = out + (size_t)y0 * pitch + (interleaved ? (size_t)x0 * 3u : (size_t)x0);
+        uint8_t* rowp = out + (size_t)y0 * pitch + (interleaved ? (size_t)x0 * (wide ? 6u : 3u) : (size_t)x0);
 #pragma unroll
         for (int r = 0; r < 8; r++) {
             if (y0 + (uint32_t)r < H) {
@@ -822,7 +855,9 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_gray(Gjd
                     r8 |= (uint64_t)R << (8 * x); g8 |= (uint64_t)G << (8 * x); b8 |= (uint64_t)B << (8 * x);
                 }
                 uint8_t* row = rowp + (size_t)r * pitch;
-                if (fast && !interleaved) {
+                if (wide) {
+                    gjd_store_row_i16(row, r8, g8, b8, min(8u, W - x0), fast);
+                } else if (fast && !interleaved) {
                     __stcs(reinterpret_cast<uint2*>(row), make_uint2((uint32_t)r8, (uint32_t)(r8 >> 32)));
                     __stcs(reinterpret_cast<uint2*>(row + pstride), make_uint2((uint32_t)g8, (uint32_t)(g8 >> 32)));
                     __stcs(reinterpret_cast<uint2*>(row + 2 * pstride), make_uint2((uint32_t)b8, (uint32_t)(b8 >> 32)));
@@ -894,7 +929,7 @@ cudaError_t gjd_launch_fix(const GjdDevBatch& b, cudaStream_t s) {
 }
 
 cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdStageEvents* ev,
-                                int transform_variant, int* launches, bool skip_sync) {
+                                int transform_variant, int* launches, bool skip_sync, bool* attrs_set) {
     (void)transform_variant;
     int n = 0;
     if (b.n_img == 0) { if (launches) *launches = 0; return cudaSuccess; }
@@ -902,30 +937,32 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     GJD_CK(cudaMemsetAsync(b.meta, 0, (size_t)b.n_tile * 96 * sizeof(uint32_t), s));
     GJD_CK(cudaMemsetAsync(b.status, 0, (size_t)(b.n_img + 1) * sizeof(uint32_t), s));
     if (ev) GJD_CK(cudaEventRecord(ev->e[1], s));
+    /* NVTX ranges bracket the launches of each stage (host side, like the reference's range around its kernel) */
     if (!skip_sync) {
+        nvtxRangePushA("gjd stage 1: entropy sync");
         k_huff_sync<<<b.n_seq, GJD_SYNC_THREADS, 0, s>>>(b); n++;
         k_huff_fix<<<(b.n_seq + 127) / 128, 128, 0, s>>>(b); n++;
+        nvtxRangePop();
     }
     if (ev) GJD_CK(cudaEventRecord(ev->e[2], s));
+    nvtxRangePushA("gjd stage 2: count scan + coefficient write + DC bases");
     k_seq_scan<<<b.n_seg, 256, 0, s>>>(b); n++;
-    {   /* opt in to > 48 KB of dynamic shared memory, once per device (function attributes are per context) */
-        static bool write_attr[64] = {false};
-        int dev = 0;
-        GJD_CK(cudaGetDevice(&dev));
-        if (dev < 0 || dev >= 64 || !write_attr[dev]) {
-            GJD_CK(cudaFuncSetAttribute(k_huff_write, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GJD_WRITE_SMEM));
-            if (dev >= 0 && dev < 64) write_attr[dev] = true;
-        }
+    if (!attrs_set || !*attrs_set) {   /* opt in to > 48 KB of dynamic shared memory; the caller's gjd_ctx remembers it */
+        GJD_CK(cudaFuncSetAttribute(k_huff_write, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GJD_WRITE_SMEM));
+        if (attrs_set) *attrs_set = true;
     }
     k_huff_write<<<b.n_seq, GJD_WRITE_THREADS, GJD_WRITE_SMEM, s>>>(b); n++;
     k_dc_tilesum<<<(b.n_tile + 255u) / 256u, 256, 0, s>>>(b); n++;
     k_dc_tilebase<<<b.n_img, 256, 0, s>>>(b); n++;
+    nvtxRangePop();
     if (ev) GJD_CK(cudaEventRecord(ev->e[3], s));
+    nvtxRangePushA("gjd stage 3: dequant + IDCT + colour");
     if (b.any_interleaved) k_transform<false, 8, true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
     else if (transform_variant == 1) k_transform<false, GJD_TRANSFORM_MINB_ALT, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
     else k_transform<false, GJD_TRANSFORM_MINB, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
     n++;
     if (b.any_gray) { k_transform_gray<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr); n++; }
+    nvtxRangePop();
     if (ev) GJD_CK(cudaEventRecord(ev->e[4], s));
     if (launches) *launches = n;
     return cudaGetLastError();

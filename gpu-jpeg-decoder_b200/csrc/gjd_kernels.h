@@ -53,7 +53,7 @@ cudaError_t gjd_launch_fill_maps(const GjdDevBatch& b, cudaStream_t s);
 /* Clears scratch and runs every decode stage. transform_variant selects the transform kernel
  * implementation (0 = default).  Returns the number of kernel launches in *launches. */
 cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdStageEvents* ev,
-                                int transform_variant, int* launches, bool skip_sync = false);
+                                int transform_variant, int* launches, bool skip_sync = false, bool* attrs_set = nullptr);
 /* Re-run of the boundary fix-up only (slow path when *nosync != 0). */
 cudaError_t gjd_launch_fix(const GjdDevBatch& b, cudaStream_t s);
 cudaError_t gjd_launch_export_coefs(const GjdDevBatch& b, int16_t* out, cudaStream_t s);

@@ -14,7 +14,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GJD_LIB") or os.path.join(_HERE, "build", "libgjd.so")   # GJD_LIB: A/B builds
 
-PLANAR, INTERLEAVED = 0, 1
+PLANAR, INTERLEAVED, INTERLEAVED_I16 = 0, 1, 2
 OK, E_ARG, E_CUDA, E_NOMEM, E_FORMAT, E_UNSUPPORTED, E_CORRUPT, E_NODEVICE, E_IO = 0, -1, -2, -3, -4, -5, -6, -7, -8
 
 
@@ -156,8 +156,9 @@ class Decoder:
         return items, hold
 
     def decode(self, files, layout=PLANAR):
-        """Decode a list of JPEG `bytes`; returns (list of uint8 arrays or None, list of status).
-        Arrays are (3,H,W) for the planar layout, (H,W,3) for the interleaved one."""
+        """Decode a list of JPEG `bytes`; returns (list of arrays or None, list of status).
+        Arrays are uint8 (3,H,W) for the planar layout, uint8 (H,W,3) for the interleaved one and int16 (H,W,3)
+        for INTERLEAVED_I16 (element type and order of the reference's outputChannels)."""
         n = len(files)
         items, hold = self.make_items(files)
         outs = []
@@ -165,7 +166,7 @@ class Decoder:
             rc, w, h = peek(d)
             items[i].layout = layout
             if rc == OK:
-                a = np.empty((3, h, w) if layout == PLANAR else (h, w, 3), np.uint8)
+                a = np.empty((3, h, w) if layout == PLANAR else (h, w, 3), np.int16 if layout == INTERLEAVED_I16 else np.uint8)
                 items[i].rgb = a.ctypes.data
                 outs.append(a)
             else:
@@ -200,8 +201,10 @@ class Decoder:
         return list(ms)
 
     # -- resident batch -----------------------------------------------------------------------
-    def prepare(self, files):
+    def prepare(self, files, layout=PLANAR):
         items, hold = self.make_items(files)
+        for i in range(len(files)):
+            items[i].layout = layout
         b = C.c_void_p()
         rc = lib().gjd_batch_prepare(self._ctx, items, len(files), C.byref(b))
         if rc != OK:
@@ -253,7 +256,8 @@ class ResidentBatch:
 
     def fetch(self, i):
         w, h = self.items[i].width, self.items[i].height
-        out = np.empty((3, h, w), np.uint8)
+        layout = self.items[i].layout
+        out = np.empty((3, h, w) if layout == PLANAR else (h, w, 3), np.int16 if layout == INTERLEAVED_I16 else np.uint8)
         rc = lib().gjd_batch_fetch(self.dec._ctx, self.h, i, out.ctypes.data)
         if rc != OK:
             raise GjdError(rc, self.dec._detail())
@@ -269,6 +273,14 @@ def write_array(path, rgb):
     """rgb: (3,H,W) uint8."""
     rgb = np.ascontiguousarray(rgb, np.uint8)
     rc = lib().gjd_write_array(path.encode(), rgb.shape[2], rgb.shape[1], rgb.ctypes.data)
+    if rc != OK:
+        raise GjdError(rc)
+
+
+def write_ppm(path, rgb):
+    """rgb: (3,H,W) uint8 -> binary P6."""
+    rgb = np.ascontiguousarray(rgb, np.uint8)
+    rc = lib().gjd_write_ppm(path.encode(), rgb.shape[2], rgb.shape[1], rgb.ctypes.data)
     if rc != OK:
         raise GjdError(rc)
 

@@ -46,9 +46,15 @@ typedef struct gjd_batch gjd_batch;  /* a parsed batch resident in device memory
  * INTERLEAVED R,G,B,R,G,B,... rows of 3*width bytes, row_pitch bytes apart (0 = 3*width); plane_stride is
  *             ignored.  This is the pixel order of the reference's device buffer outputChannels
  *             (cuda-decoder/src/parser.cu:571-573, read back at :715-717) narrowed from int16 to u8 and
- *             cropped, and the body of a binary PPM (testing/jpeglib_output_ppm). */
-#define GJD_LAYOUT_PLANAR      0
-#define GJD_LAYOUT_INTERLEAVED 1
+ *             cropped, and the body of a binary PPM (testing/jpeglib_output_ppm).
+ * INTERLEAVED_I16
+ *             the same order with int16 elements (6 bytes per pixel; row_pitch in bytes, 0 = 6*width): element type AND
+ *             order of outputChannels (cuda-decoder/src/parser.cu:571-573), for callers that read that buffer as the
+ *             reference's write() does (:702-724).  A caller that wants the reference's padded geometry passes
+ *             row_pitch = 6 * 8*ceil(width/8); only the width x height pixels are written. */
+#define GJD_LAYOUT_PLANAR          0
+#define GJD_LAYOUT_INTERLEAVED     1
+#define GJD_LAYOUT_INTERLEAVED_I16 2
 
 /* One image of a batch.
  * Replaces the per-image HostData/DeviceData descriptor pair the reference fills with
@@ -66,7 +72,7 @@ typedef struct gjd_item {
     int32_t        width;        /* out: image width  (SOF0)                                            */
     int32_t        height;       /* out: image height (SOF0)                                            */
     int32_t        status;       /* out: per-image gjd_status                                           */
-    int32_t        layout;       /* in : GJD_LAYOUT_PLANAR (0) or GJD_LAYOUT_INTERLEAVED                */
+    int32_t        layout;       /* in : GJD_LAYOUT_PLANAR (0), GJD_LAYOUT_INTERLEAVED or _INTERLEAVED_I16 */
     int32_t        reserved;     /* in : 0                                                              */
 } gjd_item;
 
@@ -108,7 +114,7 @@ int  gjd_decode_batch(gjd_ctx* ctx, gjd_item* items, int32_t n);
  *   sync    : wait; returns GJD_E_CORRUPT if any image failed on the device (per-image detail via
  *             gjd_batch_status).
  *   fetch   : copy image i's pixels to host memory, tight, in the item's layout (planar: W*H bytes per
- *             plane; interleaved: 3*W bytes per row). */
+ *             plane; interleaved: 3*W bytes per row; interleaved int16: 6*W bytes per row). */
 int  gjd_batch_prepare(gjd_ctx* ctx, gjd_item* items, int32_t n, gjd_batch** out);
 int  gjd_batch_run(gjd_ctx* ctx, gjd_batch* b);
 int  gjd_batch_sync(gjd_ctx* ctx, gjd_batch* b);

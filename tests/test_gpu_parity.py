@@ -450,3 +450,48 @@ def test_transform_block_tiling_all_sizes(decoder, oracle):
             assert b.status(i) == 0
             assert hashlib.md5(b.fetch(i).tobytes()).hexdigest() == want[i % 4], (n, i)
         b.free()
+
+
+def test_int16_interleaved_layout(decoder, golden, ref_outputs, gray_golden, ref_outputs_gray, rst_golden, ref_outputs_rst):
+    """GJD_LAYOUT_INTERLEAVED_I16: element type and order of the reference's outputChannels
+    (cuda-decoder/src/parser.cu:571-573) — same pixels as the planar layout, as int16; tight, with the reference's
+    padded pitch (6 * 8*ceil(W/8), the geometry write() reads back at :702-724), with an unaligned pitch, resident."""
+    import gjd
+    files = [golden[n] for n in NAMES] + list(gray_golden.values()) + [rst_golden[n] for n in sorted(rst_golden)]
+    want = ([ref_outputs[n + "/rgb"] for n in NAMES] + [ref_outputs_gray[k + "/rgb"] for k in gray_golden]
+            + [ref_outputs_rst[n + "/rgb"] for n in sorted(rst_golden)])
+    outs, st = decoder.decode(files, layout=gjd.INTERLEAVED_I16)
+    assert st == [0] * len(files)
+    for o, w_ in zip(outs, want):
+        assert o.dtype == np.int16 and np.array_equal(o, w_.transpose(1, 2, 0).astype(np.int16))
+    for extra in (0, 10):      # the reference's padded pitch, then the same + 10 bytes (no 16-byte alignment)
+        items, hold = decoder.make_items(files)
+        bufs = []
+        for i, w_ in enumerate(want):
+            _, H, W = w_.shape
+            pitch = 6 * 8 * ((W + 7) // 8) + extra
+            buf = np.full(pitch * H // 2 + 8, -21846, np.int16)
+            items[i].rgb = buf.ctypes.data
+            items[i].row_pitch = pitch
+            items[i].layout = gjd.INTERLEAVED_I16
+            bufs.append((buf, pitch))
+        decoder.decode_batch_raw(items, len(files))
+        for i, w_ in enumerate(want):
+            assert items[i].status == 0
+            _, H, W = w_.shape
+            buf, pitch = bufs[i]
+            rows = buf[: pitch * H // 2].reshape(H, pitch // 2)
+            assert np.array_equal(rows[:, : 3 * W].reshape(H, W, 3), w_.transpose(1, 2, 0).astype(np.int16))
+            assert (rows[:, 3 * W:] == -21846).all()          # nothing written outside W x H
+    b = decoder.prepare(files[:4], layout=gjd.INTERLEAVED_I16)
+    b.run()
+    assert b.sync() == 0
+    for i in range(4):
+        assert np.array_equal(b.fetch(i), want[i].transpose(1, 2, 0).astype(np.int16))
+    b.free()
+    items, hold = decoder.make_items(files[:1])
+    buf = np.zeros(6 * 400 * 400 + 8, np.uint8)
+    items[0].rgb = buf.ctypes.data + 1                         # odd address: not an int16 buffer
+    items[0].layout = gjd.INTERLEAVED_I16
+    decoder.decode_batch_raw(items, 1)
+    assert items[0].status == gjd.E_ARG

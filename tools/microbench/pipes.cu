@@ -26,6 +26,14 @@ __global__ void __launch_bounds__(256) k(int* out, int seed) {
             if (OP == 12) { asm volatile("dp2a.lo.s32.u32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); asm volatile("mad.lo.s32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); }
             if (OP == 13) { asm volatile("cvt.pack.sat.u8.s32.b32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); asm volatile("lop3.b32 %0, %0, %1, %0, 0x96;" : "+r"(a[i]) : "r"(c)); }
             if (OP == 14) { asm volatile("cvt.pack.sat.u8.s32.b32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); asm volatile("mad.lo.s32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); }
+            if (OP == 15) asm volatile("cvt.pack.sat.s16.s32 %0, %0, %1;" : "+r"(a[i]) : "r"(c));                       // I2IP.S16.S32.SAT
+            if (OP == 16) a[i] = (int)__viaddmin_s16x2_relu((unsigned)a[i], (unsigned)c, 0x01ff01ffu);                      // VIADDMNMX.S16x2.RELU
+            if (OP == 17) { asm volatile("mad.lo.s32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); a[i] = (int)__viaddmin_s16x2_relu((unsigned)a[i], (unsigned)c, 0x01ff01ffu); }
+            if (OP == 18) { asm volatile("prmt.b32 %0, %0, %1, 0x7632;" : "+r"(a[i]) : "r"(c)); asm volatile("mad.lo.s32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); }
+            if (OP == 19) { asm volatile("shr.s32 %0, %0, 3;" : "+r"(a[i])); asm volatile("mad.lo.s32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); asm volatile("mad.lo.s32 %0, %0, %1, %0;" : "+r"(a[i]) : "r"(c)); }
+            if (OP == 20) asm volatile("{.reg .s64 t; mad.wide.s32 t, %0, %1, 5; cvt.u32.u64 %0, t;}" : "+r"(a[i]) : "r"(c));   // IMAD.WIDE
+            if (OP == 21) asm volatile("shf.l.wrap.b32 %0, %0, %1, 7;" : "+r"(a[i]) : "r"(c));                               // SHF funnel
+            if (OP == 22) a[i] = (int)__vimax3_s16x2((unsigned)a[i], (unsigned)c, 0x00100010u);                             // VIMNMX3.S16x2
             if (OP == 8) asm volatile("{.reg .s32 t; add.s32 t, %0, %1; min.s32 t, t, 511; max.s32 %0, t, 0;}" : "+r"(a[i]) : "r"(c));
         }
     }
@@ -50,5 +58,8 @@ int main() {
     run<7>("PRMT", 1); run<8>("VIADDMNMX.RELU (add,min,max)", 1); run<9>("I2IP.U8.S32.SAT (cvt.pack.sat)", 1);
     run<10>("IDP.2A (dp2a.lo)", 1); run<11>("IDP.2A + LOP3 pair", 2); run<12>("IDP.2A + IMAD pair", 2);
     run<13>("I2IP + LOP3 pair", 2); run<14>("I2IP + IMAD pair", 2);
+    run<15>("I2IP.S16.S32.SAT", 1); run<16>("VIADDMNMX.S16x2.RELU", 1); run<17>("IMAD + VIADDMNMX.S16x2 pair", 2);
+    run<18>("PRMT + IMAD pair", 2); run<19>("SHF + 2 IMAD (1 ALU : 2 FMA)", 3); run<20>("IMAD.WIDE", 1);
+    run<21>("SHF.L.W (funnel)", 1); run<22>("VIMNMX3.S16x2", 1);
     return 0;
 }
