@@ -19,8 +19,9 @@ barrier, the max-over-ranks of the times and the sum of the parity counts.
             that does not fit in HBM at once (c5 at small N) is decoded as successive resident chunks; a
             chunk's preparation (the reference's untimed extract()/allocate() loop,
             cuda-decoder/benchmark_thoughput/benchmark.cu:49-60) is outside the event-timed region.
-  e2e       gjd_decode_batch() through the C ABI with HOST buffers: header parse, unstuffing, H2D, all GPU
-            stages, D2H of the pixels into pinned host memory, all timed (wall clock around the calls).
+  e2e       gjd_decode_batch() through the C ABI with HOST buffers: JPEG files in page-locked host memory in, header
+            parse, H2D of the raw scans, unstuffing + all GPU stages, D2H of the pixels into page-locked host memory,
+            all timed (wall clock around the calls).
   e2e_device_output
             the same call with the pixels left in device memory (rgb_on_device).
   parity_checked
@@ -414,7 +415,8 @@ def main():
     pinned = gjd.PinnedBuffer(max(chunk_out))
     citems = []
     for c in chunks:
-        items, hold = dec.make_items([base[ids[p]] for p in c])
+        # the step's inputs lie in page-locked host memory (gjd_host_alloc), files back to back
+        items, hold = dec.make_items_pinned([base[ids[p]] for p in c])
         off, offs = 0, []
         for j, p in enumerate(c):
             items[j].rgb = pinned.ptr + off

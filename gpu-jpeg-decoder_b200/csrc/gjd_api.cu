@@ -180,6 +180,7 @@ struct ItemGeom {
     size_t out_bytes = 0;      /* bytes of the image's output region */
     size_t pitch = 0, pstride = 0;
     int32_t layout = GJD_LAYOUT_PLANAR;
+    bool jpg_pinned = false;   /* the caller's JPEG bytes lie in page-locked memory: DMA straight from them */
 };
 
 }  // namespace
@@ -198,7 +199,9 @@ struct gjd_batch {
     std::vector<int32_t> img_of;     /* item -> index into imgs, or -1 */
     std::vector<GjdDhtSet> dhts;
     std::vector<GjdQuantSet> quants;
-    PinBuf h_scan, h_meta, h_status;
+    std::vector<GjdRaw> raws;        /* scans unstuffed on the device */
+    PinBuf h_scan, h_raw, h_meta, h_status;
+    DevBuf d_raw, d_uchunk, d_rawmeta, d_ustatus;
     DevBuf d_scan, d_meta, d_luts, d_lutc, d_sinfo, d_seqmaps, d_coef, d_blkmeta, d_tilebase, d_tileimg, d_tbimg, d_rgb, d_status;
     GjdDevBatch view{};
     GjdStageEvents ev{};
@@ -206,12 +209,12 @@ struct gjd_batch {
     cudaStream_t stream = nullptr;
     size_t scan_alloc = 0, rgb_alloc = 0;
     uint64_t pixels = 0, padded_pixels = 0, scan_bytes = 0, subseqs = 0;
-    int launches = 0;
+    int launches = 0, unstuff_launches = 0;
     bool ran = false;
 
     void release() {
-        h_scan.release(); h_meta.release(); h_status.release();
-        for (DevBuf* d : {&d_scan, &d_meta, &d_luts, &d_lutc, &d_sinfo, &d_seqmaps, &d_coef, &d_blkmeta, &d_tilebase, &d_tileimg,
+        h_scan.release(); h_raw.release(); h_meta.release(); h_status.release();
+        for (DevBuf* d : {&d_raw, &d_uchunk, &d_rawmeta, &d_ustatus, &d_scan, &d_meta, &d_luts, &d_lutc, &d_sinfo, &d_seqmaps, &d_coef, &d_blkmeta, &d_tilebase, &d_tileimg,
                           &d_tbimg, &d_rgb, &d_status})
             d->release(stream);
         if (ev_ok) for (auto& e : ev.e) cudaEventDestroy(e);
@@ -232,6 +235,7 @@ struct gjd_ctx {
     uint64_t min_subseqs = 1200000;   /* ~4 waves of 148 SMs x 2048 threads */
     uint32_t max_tb_tiles = GJD_TB_TILES;   /* GJD_TB_TILES_MAX: measurement knob (power of two, 4..128) */
     int force_sub_log2 = 0;           /* GJD_SUB_LOG2: fixed subsequence length (tests, experiments) */
+    bool device_unstuff = true;       /* GJD_DEVICE_UNSTUFF=0: unstuff every scan on the host (A/B, tests) */
     bool kernel_attrs_set = false;    /* the > 48 KB dynamic shared memory opt-in of k_huff_write (per context) */
 };
 
@@ -262,7 +266,7 @@ uint64_t fnv1a(const void* p, size_t n) {
 /* Estimated device bytes one image needs (scan + sinfo + coefficient lines + block meta + rgb). */
 size_t estimate_bytes(const gjd_item& it, const ItemGeom& g) {
     size_t pw = align_up((size_t)g.width, 8), ph = align_up((size_t)g.height, 8);
-    return pw * ph * 6 + pw * ph / 4 + g.out_bytes + it.len * 3 + 65536;
+    return pw * ph * 6 + pw * ph / 4 + g.out_bytes + it.len * 4 + 65536;
 }
 
 /*
@@ -283,23 +287,66 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     b->dhts.clear();
     b->quants.clear();
 
-    /* scan staging offsets from file sizes (upper bound of the unstuffed scan) */
-    std::vector<size_t> soff(n + 1, 0);
-    for (int32_t i = 0; i < n; i++)
-        soff[i + 1] = soff[i] + (b->geom[i].status == GJD_OK
-                                     ? align_up(items[i].len + 64 + (parsed[i].restart_interval ? items[i].len / 2 + 64 : 0), 128)
-                                     : 0);
+    /* Where each scan is unstuffed.  On the device (k_unstuff_*): every scan without restart intervals — the raw bytes from
+     * the first scan byte to the end of the file are uploaded, straight from the caller's buffer when that is page-locked
+     * (adjacent files merge into one copy), through the pinned h_raw staging otherwise.  On the host
+     * (gjd_unstuff_segments): scans with restart intervals, whose intervals become segments the host has to size. */
+    b->raws.clear();
+    std::vector<uint8_t> mode(n, 0);                 /* 1 = device-unstuffed */
+    std::vector<size_t> soff(n + 1, 0);              /* scan arena (device) */
+    std::vector<size_t> hoff(n + 1, 0);              /* h_scan staging: host-unstuffed scans only */
+    std::vector<size_t> roff(n, 0);                  /* raw arena: first scan byte of device-unstuffed scans */
+    struct Copy { const uint8_t* src; size_t dst, len; };
+    std::vector<Copy> dma;                           /* user buffer -> raw arena */
+    size_t raw_staged = 16, raw_total = 0;           /* 16 bytes of slack in front of the arena */
+    for (int32_t i = 0; i < n; i++) {
+        size_t room = 0, hroom = 0;
+        if (b->geom[i].status == GJD_OK) {
+            const size_t rawlen = (size_t)(parsed[i].file_end - parsed[i].scan_begin);
+            mode[i] = ctx->device_unstuff && parsed[i].restart_interval == 0;
+            if (mode[i]) {
+                room = align_up(rawlen + 64, 128);
+                if (!b->geom[i].jpg_pinned) { roff[i] = raw_staged; raw_staged += align_up(rawlen, 16) + 16; }
+            } else {
+                room = hroom = align_up(items[i].len + 64 + (parsed[i].restart_interval ? items[i].len / 2 + 64 : 0), 128);
+            }
+        }
+        soff[i + 1] = soff[i] + room;
+        hoff[i + 1] = hoff[i] + hroom;
+    }
+    raw_total = raw_staged;
+    for (int32_t i = 0; i < n; i++) {                /* page-locked inputs: runs of files that follow each other in memory */
+        if (!mode[i] || !b->geom[i].jpg_pinned) continue;
+        const bool joins = !dma.empty() && i > 0 && mode[i - 1] && b->geom[i - 1].jpg_pinned &&
+                           items[i].jpg == items[i - 1].jpg + items[i - 1].len;
+        if (!joins) {
+            raw_total = align_up(raw_total, 16) + 16;
+            dma.push_back({parsed[i].scan_begin, raw_total, 0});
+        }
+        Copy& c = dma.back();
+        roff[i] = c.dst + (size_t)(parsed[i].scan_begin - c.src);
+        c.len = (size_t)(parsed[i].file_end - c.src);
+        raw_total = c.dst + c.len;
+    }
+    raw_total += 64;
     b->scan_alloc = soff[n] + 256;
-    GJD_TRY(b->h_scan.ensure(b->scan_alloc));
+    GJD_TRY(b->h_scan.ensure(hoff[n] + 256));
+    GJD_TRY(b->h_raw.ensure(raw_staged + 64));
     uint8_t* hs = (uint8_t*)b->h_scan.p;
+    uint8_t* hr = (uint8_t*)b->h_raw.p;
 
-    std::vector<long> ulen(n, 0);
+    std::vector<long> ulen(n, 0);                    /* unstuffed length (device-unstuffed scans: the raw length, an upper bound) */
     std::vector<std::vector<uint32_t>> rst_off(n), rst_len(n);   /* restart intervals (images with DRI only) */
-    nvtxRangePushA("gjd: unstuff scans into pinned staging");
+    nvtxRangePushA("gjd: stage scans (host unstuffing / raw copies into pinned staging)");
     ctx->pool->parallel_for((size_t)n, 4, [&](size_t i) {
         if (b->geom[i].status != GJD_OK) return;
         const GjdParsed& p = parsed[i];
-        uint8_t* dst = hs + soff[i];
+        if (mode[i]) {
+            ulen[i] = (long)(p.file_end - p.scan_begin);
+            if (!b->geom[i].jpg_pinned) memcpy(hr + roff[i], p.scan_begin, (size_t)ulen[i]);
+            return;
+        }
+        uint8_t* dst = hs + hoff[i];
         long m = p.restart_interval ? gjd_unstuff_segments(p.scan_begin, p.file_end, dst, &rst_off[i], &rst_len[i])
                                     : gjd_unstuff(p.scan_begin, p.file_end, dst);
         if (m < 0) { b->geom[i].status = (int32_t)m; return; }
@@ -334,8 +381,9 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
 
     /* descriptors */
     std::unordered_map<uint64_t, std::vector<uint32_t>> lut_index, quant_index;
-    uint32_t seq = 0, tile = 0, tb = 0;
+    uint32_t seq = 0, tile = 0, tb = 0, uchunk = 0;
     size_t rgb_off = 0;
+    int last_lut = -1, last_quant = -1;            /* most images of a batch share their tables with the one before */
     b->pixels = b->padded_pixels = b->scan_bytes = b->subseqs = 0;
     for (int32_t i = 0; i < n; i++) {
         ItemGeom& g = b->geom[i];
@@ -378,11 +426,12 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
             GjdDhtSet key = p.dht;              /* the LUT ring depends on the scan's table selectors too */
             memcpy(key.tabsel, p.tabsel, 8);
             memset(key.pad, 0, sizeof(key.pad));
-            uint64_t h = fnv1a(&key, sizeof(GjdDhtSet));
+            int found = last_lut >= 0 && memcmp(&b->dhts[last_lut], &key, sizeof(GjdDhtSet)) == 0 ? last_lut : -1;
+            uint64_t h = found < 0 ? fnv1a(&key, sizeof(GjdDhtSet)) : 0;
             auto& cand = lut_index[h];
-            int found = -1;
-            for (uint32_t id : cand)
-                if (memcmp(&b->dhts[id], &key, sizeof(GjdDhtSet)) == 0) { found = (int)id; break; }
+            if (found < 0)
+                for (uint32_t id : cand)
+                    if (memcmp(&b->dhts[id], &key, sizeof(GjdDhtSet)) == 0) { found = (int)id; break; }
             if (found < 0) {
                 if (b->dhts.size() >= 65535) { g.status = GJD_E_NOMEM; continue; }
                 found = (int)b->dhts.size();
@@ -390,6 +439,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
                 cand.push_back((uint32_t)found);
             }
             lut_id = (uint16_t)found;
+            last_lut = found;
         }
         {
             GjdQuantSet q;
@@ -398,11 +448,12 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
             for (int c = 0; c < 3; c++)
                 for (int j = 0; j < 32; j++)
                     q.packed[c][j] = (uint32_t)q.q[c][2 * j] | ((uint32_t)q.q[c][2 * j + 1] << 24);
-            uint64_t h = fnv1a(&q, sizeof(q));
+            int found = last_quant >= 0 && memcmp(&b->quants[last_quant], &q, sizeof(q)) == 0 ? last_quant : -1;
+            uint64_t h = found < 0 ? fnv1a(&q, sizeof(q)) : 0;
             auto& cand = quant_index[h];
-            int found = -1;
-            for (uint32_t id : cand)
-                if (memcmp(&b->quants[id], &q, sizeof(q)) == 0) { found = (int)id; break; }
+            if (found < 0)
+                for (uint32_t id : cand)
+                    if (memcmp(&b->quants[id], &q, sizeof(q)) == 0) { found = (int)id; break; }
             if (found < 0) {
                 if (b->quants.size() >= 65535) { g.status = GJD_E_NOMEM; continue; }
                 found = (int)b->quants.size();
@@ -410,6 +461,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
                 cand.push_back((uint32_t)found);
             }
             d.quant_id = (uint16_t)found;
+            last_quant = found;
         }
         d.seg_first = (uint32_t)b->segs.size();
         d.seg_count = nseg;
@@ -428,6 +480,19 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
             sg.blk_first = bpm * mcu0;
             sg.blk_count = bpm * (p.restart_interval ? std::min(p.restart_interval, d.mcu_count - mcu0) : d.mcu_count);
             sg.lut_id = lut_id;
+            if (mode[i]) {
+                GjdRaw r;
+                memset(&r, 0, sizeof(r));
+                r.raw_off = roff[i];
+                r.raw_len = (uint32_t)ulen[i];
+                r.chunk_first = uchunk;
+                r.chunk_count = (uint32_t)(((roff[i] & 15u) + (size_t)ulen[i] + GJD_UCHUNK - 1) / GJD_UCHUNK);
+                if (r.chunk_count == 0) r.chunk_count = 1;
+                r.seg = (uint32_t)b->segs.size();
+                r.img = (uint32_t)b->imgs.size();
+                uchunk += r.chunk_count;
+                b->raws.push_back(r);
+            }
             seq += sg.seq_count;
             b->subseqs += sg.sub_count;
             b->segs.push_back(sg);
@@ -463,8 +528,10 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     size_t o_seg = align_up(o_img + sizeof(GjdImage) * n_img, 256);
     size_t o_dht = align_up(o_seg + sizeof(GjdSegment) * b->segs.size(), 256);
     size_t o_q = align_up(o_dht + sizeof(GjdDhtSet) * b->dhts.size(), 256);
-    size_t meta = align_up(o_q + sizeof(GjdQuantSet) * b->quants.size(), 256);
+    size_t o_raw = align_up(o_q + sizeof(GjdQuantSet) * b->quants.size(), 256);
+    size_t meta = align_up(o_raw + sizeof(GjdRaw) * b->raws.size(), 256);
     GJD_TRY(b->h_meta.ensure(meta));
+    if (!b->raws.empty()) memcpy((uint8_t*)b->h_meta.p + o_raw, b->raws.data(), sizeof(GjdRaw) * b->raws.size());
     memcpy((uint8_t*)b->h_meta.p + o_img, b->imgs.data(), sizeof(GjdImage) * n_img);
     memcpy((uint8_t*)b->h_meta.p + o_seg, b->segs.data(), sizeof(GjdSegment) * b->segs.size());
     memcpy((uint8_t*)b->h_meta.p + o_dht, b->dhts.data(), sizeof(GjdDhtSet) * b->dhts.size());
@@ -483,11 +550,24 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     GJD_TRY(b->d_tileimg.ensure((size_t)tile * sizeof(uint32_t), b->stream));
     GJD_TRY(b->d_rgb.ensure(std::max<size_t>(b->rgb_alloc, 256), b->stream));
     GJD_TRY(b->d_status.ensure((size_t)(n_img + 1) * sizeof(uint32_t), b->stream));
+    GJD_TRY(b->d_ustatus.ensure((size_t)(n_img + 1) * sizeof(uint32_t), b->stream));
+    GJD_TRY(b->d_raw.ensure(raw_total + 64, b->stream));
+    GJD_TRY(b->d_uchunk.ensure((size_t)(uchunk + 1) * 2 * sizeof(uint32_t), b->stream));
+    GJD_TRY(b->d_rawmeta.ensure((b->raws.size() + 1) * 2 * sizeof(uint32_t), b->stream));
     GJD_TRY(b->h_status.ensure((size_t)(n_img + 1) * sizeof(uint32_t)));
 
     v.imgs = (const GjdImage*)((uint8_t*)b->d_meta.p + o_img);
-    v.segs = (const GjdSegment*)((uint8_t*)b->d_meta.p + o_seg);
-    v.scan = (const uint8_t*)b->d_scan.p;
+    v.segs = (GjdSegment*)((uint8_t*)b->d_meta.p + o_seg);
+    v.scan = (uint8_t*)b->d_scan.p;
+    v.raws = (const GjdRaw*)((uint8_t*)b->d_meta.p + o_raw);
+    v.n_raw = (uint32_t)b->raws.size();
+    v.n_uchunk = uchunk;
+    v.raw = (const uint8_t*)b->d_raw.p;
+    v.uchunk_raw = (uint32_t*)b->d_uchunk.p;
+    v.uchunk_cnt = (uint32_t*)b->d_uchunk.p + uchunk;
+    v.raw_eoi = (uint32_t*)b->d_rawmeta.p;
+    v.raw_err = (uint32_t*)b->d_rawmeta.p + b->raws.size();
+    v.ustatus = (uint32_t*)b->d_ustatus.p;
     v.luts = (const GjdLutSet*)b->d_luts.p;
     v.lutc = (const GjdLutCount*)b->d_lutc.p;
     v.quants = (const GjdQuantSet*)((uint8_t*)b->d_meta.p + o_q);
@@ -504,11 +584,25 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     v.status = (uint32_t*)b->d_status.p;
     v.nosync = (uint32_t*)b->d_status.p + n_img;
 
-    GJD_TRY(cudaMemcpyAsync(b->d_scan.p, b->h_scan.p, soff[n] + 16, cudaMemcpyHostToDevice, b->stream));
+    {   /* host-unstuffed scans: staging -> scan arena, runs of neighbours in one copy */
+        int32_t i = 0;
+        while (i < n) {
+            if (hoff[i + 1] == hoff[i]) { i++; continue; }
+            int32_t j = i + 1;
+            while (j < n && hoff[j + 1] != hoff[j] && soff[j] - soff[i] == hoff[j] - hoff[i]) j++;
+            GJD_TRY(cudaMemcpyAsync((uint8_t*)b->d_scan.p + soff[i], hs + hoff[i], hoff[j] - hoff[i], cudaMemcpyHostToDevice, b->stream));
+            i = j;
+        }
+    }
+    if (raw_staged > 16)
+        GJD_TRY(cudaMemcpyAsync(b->d_raw.p, b->h_raw.p, raw_staged, cudaMemcpyHostToDevice, b->stream));
+    for (const auto& c : dma)   /* page-locked JPEG bytes: no staging copy at all */
+        GJD_TRY(cudaMemcpyAsync((uint8_t*)b->d_raw.p + c.dst, c.src, c.len, cudaMemcpyHostToDevice, b->stream));
     GJD_TRY(cudaMemcpyAsync(b->d_meta.p, b->h_meta.p, meta, cudaMemcpyHostToDevice, b->stream));
     GJD_TRY(gjd_launch_build_luts((const GjdDhtSet*)((uint8_t*)b->d_meta.p + o_dht), (GjdLutSet*)b->d_luts.p, (GjdLutCount*)b->d_lutc.p,
                                   (uint32_t)b->dhts.size(), b->stream));
     GJD_TRY(gjd_launch_fill_maps(v, b->stream));
+    GJD_TRY(gjd_launch_unstuff(v, b->stream, &b->unstuff_launches));
     return GJD_OK;
 }
 
@@ -551,7 +645,11 @@ void set_item_status(gjd_batch* b, gjd_item* items) {
     const uint32_t* hst = (const uint32_t*)b->h_status.p;
     for (int32_t i = 0; i < b->n; i++) {
         int32_t st = b->geom[i].status;
-        if (st == GJD_OK && b->img_of[i] >= 0 && b->ran && hst[b->img_of[i]] != 0) st = GJD_E_CORRUPT;
+        if (st == GJD_OK && b->img_of[i] >= 0 && b->ran && hst[b->img_of[i]] != 0) {
+            /* what the device unstuffing found comes first, with the codes the host loop gives (gjd_unstuff_segments) */
+            const uint32_t bits = hst[b->img_of[i]];
+            st = (bits & GJD_DEV_UFORMAT) ? GJD_E_FORMAT : (bits & GJD_DEV_UUNSUP) ? GJD_E_UNSUPPORTED : GJD_E_CORRUPT;
+        }
         b->geom[i].status = st;
         if (items) {
             items[i].status = st;
@@ -571,6 +669,11 @@ void parse_all(gjd_ctx* ctx, const gjd_item* items, int32_t n, std::vector<GjdPa
         ItemGeom& g = geom[i];
         if (!items[i].jpg) { g.status = GJD_E_ARG; return; }
         int rc = gjd_parse_headers(items[i].jpg, items[i].len, &parsed[i]);
+        if (rc == GJD_OK && ctx->device_unstuff) {
+            cudaPointerAttributes at;
+            if (cudaPointerGetAttributes(&at, items[i].jpg) == cudaSuccess) g.jpg_pinned = at.type == cudaMemoryTypeHost;
+            else cudaGetLastError();
+        }
         g.width = parsed[i].width;
         g.height = parsed[i].height;
         if (rc) { g.status = rc; return; }
@@ -651,6 +754,7 @@ int gjd_create(gjd_ctx** out, int device, size_t scratch_bytes_hint) {
         const int v = atoi(e);
         if (v >= 4 && v <= 128 && (v & (v - 1)) == 0) ctx->max_tb_tiles = (uint32_t)v;
     }
+    if (const char* e = getenv("GJD_DEVICE_UNSTUFF")) ctx->device_unstuff = atoi(e) != 0;
     if (const char* e = getenv("GJD_MIN_SUBSEQS")) ctx->min_subseqs = (uint64_t)std::max(1ll, atoll(e));
     {   /* the arenas are stream-ordered allocations: keep what they free inside the process */
         cudaMemPool_t pool;
@@ -805,6 +909,15 @@ int gjd_batch_prepare(gjd_ctx* ctx, gjd_item* items, int32_t n, gjd_batch** out)
     /* items[i].rgb == NULL (or a host pointer): the pixels land in the batch's own device arena, read with gjd_batch_fetch */
     int rc = batch_stage(ctx, b, items, b->parsed.data(), geom.data(), n);
     if (rc == GJD_OK && cudaStreamSynchronize(b->stream) != cudaSuccess) rc = cuda_fail(ctx, cudaGetLastError(), "prepare");
+    if (rc == GJD_OK && b->view.n_raw) {   /* what the device unstuffing found is known already: report it from prepare */
+        cudaError_t e = cudaMemcpyAsync(b->h_status.p, b->view.ustatus, (size_t)b->view.n_img * sizeof(uint32_t), cudaMemcpyDeviceToHost, b->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
+        if (e != cudaSuccess) rc = cuda_fail(ctx, e, "prepare");
+        const uint32_t* hst = (const uint32_t*)b->h_status.p;
+        for (int32_t i = 0; rc == GJD_OK && i < n; i++)
+            if (b->geom[i].status == GJD_OK && b->img_of[i] >= 0 && hst[b->img_of[i]])
+                b->geom[i].status = (hst[b->img_of[i]] & GJD_DEV_UFORMAT) ? GJD_E_FORMAT : GJD_E_UNSUPPORTED;
+    }
     if (rc != GJD_OK) {
         b->release();
         delete b;

@@ -125,6 +125,114 @@ GJD_HD uint32_t gjd_ring_slot(const uint8_t tabsel[8], uint32_t r) {
     return (uint32_t)tabsel[(r & 1u) * 4u + (r >> 1)] & 3u;
 }
 
+/* ------------------------------------------------------------------ byte unstuffing --- */
+/*
+ * On-device FF00 unstuffing with marker detection.  The byte loop it replaces
+ * (cpp-decoder/src/parser.cpp:78-99, cuda-decoder/src/parser.cu:446-464, host twin gjd_unstuff_segments) walks the scan
+ * once, serially; what it does to a byte depends only on the byte and its two neighbours:
+ *     00 after FF                 -> dropped (stuffing)
+ *     FF before FF                -> dropped (fill byte, T.81 B.1.1.2)
+ *     FF before D9                -> the scan ends here (EOI)
+ *     FF before D0..D7            -> restart marker
+ *     FF before anything else     -> a marker that has no business inside a scan
+ * so 16 bytes per thread can be classified independently.  Masks have bit i = byte i of the 16 (memory order).
+ */
+struct GjdUnstuffMasks {
+    uint32_t drop;   /* stuffed zeros and fill FFs                                   */
+    uint32_t mark;   /* FFs followed by a byte that is neither 00 nor FF (marker)     */
+};
+
+/* bit 7 of every byte of w that equals 0xFF / 0x00, gathered into a 4-bit mask (bit i = byte i) */
+GJD_HD uint32_t gjd_bytes_ff4(uint32_t w) {
+    const uint32_t m = (((w & 0x7f7f7f7fu) + 0x01010101u) & w & 0x80808080u) >> 7;
+    return ((m * 0x01020408u) >> 24) & 15u;
+}
+GJD_HD uint32_t gjd_bytes_004(uint32_t w) {
+    const uint32_t m = (~(((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w) & 0x80808080u) >> 7;
+    return ((m * 0x01020408u) >> 24) & 15u;
+}
+
+/* w[4] = 16 bytes in memory order (little-endian words); valid = mask of the bytes that belong to the scan;
+ * prev_ff = the byte before them is a scan byte equal to FF; next = the scan byte after them, next_valid = it exists
+ * (an FF that is the last byte of the data is no marker: gjd_unstuff_segments stops there with "no EOI"). */
+GJD_HD GjdUnstuffMasks gjd_unstuff_classify(const uint32_t w[4], uint32_t valid, uint32_t prev_ff, uint32_t next,
+                                            uint32_t next_valid) {
+    uint32_t ff = 0, z = 0;
+    for (int j = 0; j < 4; j++) {
+        ff |= gjd_bytes_ff4(w[j]) << (4 * j);
+        z |= gjd_bytes_004(w[j]) << (4 * j);
+    }
+    ff &= valid;
+    z &= valid;
+    const uint32_t nv = next_valid ? 1u : 0u;
+    const uint32_t ff_next = (ff >> 1) | ((nv && next == 0xffu ? 1u : 0u) << 15);   /* byte i+1 is FF */
+    const uint32_t z_next = (z >> 1) | ((nv && next == 0x00u ? 1u : 0u) << 15);     /* byte i+1 is 00 */
+    const uint32_t has_next = (valid >> 1) | (nv << 15);                            /* byte i+1 exists */
+    const uint32_t ff_prev = ((ff << 1) | (prev_ff ? 1u : 0u)) & 0xffffu;           /* byte i-1 is FF */
+    GjdUnstuffMasks m;
+    m.drop = (z & ff_prev) | (ff & ff_next);
+    m.mark = ff & ~ff_next & ~z_next & has_next;
+    return m;
+}
+
+/* One thread's share of a raw scan: 16 bytes at arena offset a (a multiple of 16).  raw_off / raw_len: where the scan's
+ * first byte lies in the arena and how many bytes follow it to the end of the file.  limit: positions >= limit are
+ * outside the scan for this pass (raw_len in the counting pass; the EOI position once it is known). */
+struct GjdUnstuffLane {
+    uint32_t w[4];      /* the 16 raw bytes */
+    uint32_t valid;     /* those of them that are scan bytes at a position < limit */
+    uint32_t pos0;      /* position in the scan of byte 0 (wraps for the bytes in front of the scan) */
+    uint32_t next;      /* the byte after the 16 (0 when the file ends there) */
+    GjdUnstuffMasks m;
+};
+
+#ifdef __CUDA_ARCH__
+#define GJD_LDG8(p) ((uint32_t)__ldg(p))
+#else
+#define GJD_LDG8(p) ((uint32_t)*(p))
+#endif
+
+GJD_HD GjdUnstuffLane gjd_unstuff_lane_at(const uint8_t* raw, uint64_t raw_off, uint32_t raw_len, uint64_t a, uint32_t limit) {
+    GjdUnstuffLane L;
+    const int64_t p0 = (int64_t)a - (int64_t)raw_off;                                 /* position in the scan of byte 0 */
+    L.pos0 = (uint32_t)p0;
+    L.valid = 0;
+    L.next = 0;
+    L.w[0] = L.w[1] = L.w[2] = L.w[3] = 0;
+    L.m.drop = L.m.mark = 0;
+    if (p0 >= (int64_t)limit || p0 + 16 <= 0) return L;
+#ifdef __CUDA_ARCH__
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(raw + a));
+    L.w[0] = v.x; L.w[1] = v.y; L.w[2] = v.z; L.w[3] = v.w;
+#else
+    for (int j = 0; j < 4; j++)
+        L.w[j] = (uint32_t)raw[a + 4 * j] | ((uint32_t)raw[a + 4 * j + 1] << 8) | ((uint32_t)raw[a + 4 * j + 2] << 16) |
+                 ((uint32_t)raw[a + 4 * j + 3] << 24);
+#endif
+    const uint32_t lo = p0 < 0 ? (uint32_t)(-p0) : 0u;                                /* first byte of the scan among the 16 */
+    const uint32_t hi = (int64_t)limit - p0 < 16 ? (uint32_t)((int64_t)limit - p0) : 16u;
+    L.valid = (0xffffu >> (16u - hi)) & (0xffffu << lo) & 0xffffu;
+    const uint32_t prev_ff = (p0 > 0 && GJD_LDG8(raw + a - 1) == 0xffu) ? 1u : 0u;
+    /* neighbours are bytes of the FILE, also at or past `limit` (the D9 of the EOI itself lies there) */
+    const uint32_t next_valid = p0 + 16 < (int64_t)raw_len ? 1u : 0u;
+    L.next = next_valid ? GJD_LDG8(raw + a + 16) : 0u;
+    const uint32_t hi_file = (int64_t)raw_len - p0 < 16 ? (uint32_t)((int64_t)raw_len - p0) : 16u;
+    const uint32_t valid_file = (0xffffu >> (16u - hi_file)) & (0xffffu << lo) & 0xffffu;
+    L.m = gjd_unstuff_classify(L.w, valid_file, prev_ff, L.next, next_valid);
+    L.m.drop &= L.valid;
+    L.m.mark &= L.valid;
+    return L;
+}
+
+GJD_HD uint32_t gjd_lane_byte(const GjdUnstuffLane& L, uint32_t i) {
+    return (L.w[i >> 2] >> (8u * (i & 3u))) & 0xffu;
+}
+
+/* the raw_err word of a marker with second byte nb at scan position pos (not an EOI) */
+GJD_HD uint32_t gjd_unstuff_err_word(uint32_t pos, uint32_t nb) {
+    return (pos << 2) | ((nb >= 0xd0u && nb <= 0xd7u) ? GJD_UERR_UNSUPPORTED : GJD_UERR_FORMAT);
+}
+
 /* ------------------------------------------------------------------ bit reader -------- */
 
 GJD_HD uint32_t gjd_bswap32(uint32_t x) {

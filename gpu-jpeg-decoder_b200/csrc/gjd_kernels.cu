@@ -121,11 +121,144 @@ __global__ void __launch_bounds__(128) k_fill_maps(GjdDevBatch b) {
         const GjdImage& d = b.imgs[img];
         for (uint32_t i = threadIdx.x; i < d.tile_count; i += blockDim.x) b.tile_img[d.tile_first + i] = img;
         for (uint32_t i = threadIdx.x; i < d.tb_count; i += blockDim.x) b.tb_img[d.tb_first + i] = img;
-    } else {
+    } else if (blockIdx.x < b.n_img + b.n_seg) {
         uint32_t sg = blockIdx.x - b.n_img;
         const GjdSegment& d = b.segs[sg];
         for (uint32_t i = threadIdx.x; i < d.seq_count; i += blockDim.x) b.seq_seg[d.seq_first + i] = sg;
+    } else {
+        uint32_t r = blockIdx.x - b.n_img - b.n_seg;
+        const GjdRaw& d = b.raws[r];
+        for (uint32_t i = threadIdx.x; i < d.chunk_count; i += blockDim.x) b.uchunk_raw[d.chunk_first + i] = r;
     }
+}
+
+/* ------------------------------------------------------------------ device unstuffing -- */
+/*
+ * FF00 unstuffing with marker detection on the device, replacing the host's byte loop
+ * (cpp-decoder/src/parser.cpp:78-99, cuda-decoder/src/parser.cu:446-464; host twin gjd_unstuff_segments) for scans
+ * without restart intervals.  The host uploads the raw bytes from the first scan byte to the end of the file.
+ *   k_unstuff_count  one block per 4 KB chunk, 16 bytes per thread: bytes kept per chunk; position of every EOI and of
+ *                    every marker that does not belong in the scan (atomicMin per scan)
+ *   k_unstuff_scan   one block per scan: the first EOI ends the scan (everything after it is ignored, including
+ *                    markers); an offending marker before it, or no EOI, fails the image with the status the host loop
+ *                    gives; exclusive scan of the chunk counts; unstuffed length -> scan_bits / sub_count of the segment
+ *                    (the host sized the sequences from the raw length, an upper bound); 16 zero bytes behind the scan
+ *   k_unstuff_write  one block per chunk: the kept bytes, compacted in shared memory, go to the scan arena as whole
+ *                    32-bit words (byte stores only at the chunk's unaligned ends)
+ */
+/* limit: positions >= limit are outside the scan (raw_len, or the EOI position in the write pass) */
+__device__ __forceinline__ GjdUnstuffLane gjd_unstuff_lane(const GjdDevBatch& b, const GjdRaw& r, uint32_t chunk, uint32_t limit) {
+    const uint64_t a = (r.raw_off & ~(uint64_t)15) + (uint64_t)chunk * GJD_UCHUNK + threadIdx.x * 16u;   /* arena offset of byte 0 */
+    return gjd_unstuff_lane_at(b.raw, r.raw_off, r.raw_len, a, limit);
+}
+
+__global__ void __launch_bounds__(256) k_unstuff_count(GjdDevBatch b) {
+    __shared__ uint32_t ws[8];
+    const uint32_t ri = b.uchunk_raw[blockIdx.x];
+    const GjdRaw& r = b.raws[ri];
+    const uint32_t chunk = blockIdx.x - r.chunk_first;
+    const GjdUnstuffLane L = gjd_unstuff_lane(b, r, chunk, r.raw_len);
+    uint32_t mk = L.m.mark;
+    while (mk) {                                   /* rare: a marker inside the scan */
+        const uint32_t i = __ffs(mk) - 1u;
+        mk &= mk - 1u;
+        const uint32_t nb = i < 15u ? gjd_lane_byte(L, i + 1u) : L.next;
+        const uint32_t pos = L.pos0 + i;
+        if (nb == 0xd9u) atomicMin(b.raw_eoi + ri, pos);
+        else atomicMin(b.raw_err + ri, gjd_unstuff_err_word(pos, nb));
+    }
+    uint32_t kept = __popc(L.valid & ~L.m.drop);
+    kept = __reduce_add_sync(0xffffffffu, kept);
+    if ((threadIdx.x & 31u) == 0u) ws[threadIdx.x >> 5] = kept;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int w = 0; w < 8; w++) t += ws[w];
+        b.uchunk_cnt[blockIdx.x] = t;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_unstuff_scan(GjdDevBatch b, uint32_t* __restrict__ ustatus) {
+    __shared__ uint32_t ws[8];
+    const uint32_t ri = blockIdx.x, tid = threadIdx.x;
+    const GjdRaw& r = b.raws[ri];
+    GjdSegment& sg = b.segs[r.seg];
+    uint32_t eoi = b.raw_eoi[ri];
+    const uint32_t err = b.raw_err[ri];
+    __syncthreads();                                /* every thread has read raw_eoi before it is rewritten below */
+    const bool failed = eoi == 0xffffffffu || (err != 0xffffffffu && (err >> 2) < eoi);
+    if (failed) {
+        if (tid == 0) {
+            const bool unsup = err != 0xffffffffu && (eoi == 0xffffffffu || (err >> 2) < eoi) && (err & 3u) == GJD_UERR_UNSUPPORTED;
+            ustatus[r.img] = unsup ? GJD_DEV_UUNSUP : GJD_DEV_UFORMAT;
+            sg.scan_bits = 0;
+            sg.sub_count = 1;
+            b.raw_eoi[ri] = 0;                      /* k_unstuff_write: nothing to write */
+        }
+        if (tid < 16) b.scan[sg.scan_off + tid] = 0;
+        return;
+    }
+    /* exclusive scan of the chunk counts up to the chunk that holds the EOI */
+    const uint32_t ce = (uint32_t)(((r.raw_off & 15u) + eoi) / GJD_UCHUNK);
+    uint32_t* cnt = b.uchunk_cnt + r.chunk_first;
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < ce; base += 256u) {
+        const uint32_t c = base + tid;
+        const uint32_t v = c < ce ? cnt[c] : 0u;
+        uint32_t blocksum;
+        const uint32_t excl = block_excl_scan_256(v, ws, &blocksum);
+        if (c < ce) cnt[c] = carry + excl;
+        carry += blocksum;
+    }
+    /* the chunk with the EOI keeps only what lies before it */
+    const GjdUnstuffLane L = gjd_unstuff_lane(b, r, ce, eoi);
+    uint32_t blocksum;
+    block_excl_scan_256(__popc(L.valid & ~L.m.drop), ws, &blocksum);
+    const uint32_t total = carry + blocksum;
+    if (tid == 0) {
+        cnt[ce] = carry;
+        sg.scan_bits = total * 8u;
+        const uint32_t S = 1u << b.sub_log2;
+        sg.sub_count = max(1u, (total * 8u + S - 1u) >> b.sub_log2);
+    }
+    if (tid < 16) b.scan[sg.scan_off + total + tid] = 0;     /* the bit window reads up to 12 bytes past the end */
+}
+
+__global__ void __launch_bounds__(256) k_unstuff_write(GjdDevBatch b) {
+    __shared__ uint32_t ws[8];
+    __shared__ __align__(16) uint8_t stage[GJD_UCHUNK + 16];
+    const uint32_t ri = b.uchunk_raw[blockIdx.x], tid = threadIdx.x;
+    const GjdRaw& r = b.raws[ri];
+    const uint32_t chunk = blockIdx.x - r.chunk_first;
+    const uint32_t eoi = b.raw_eoi[ri];
+    const int64_t cstart = (int64_t)chunk * GJD_UCHUNK - (int64_t)(r.raw_off & 15u);    /* position of the chunk's first byte */
+    if (cstart >= (int64_t)eoi) return;             /* block-uniform: behind the end of the scan (or a failed image) */
+    const GjdUnstuffLane L = gjd_unstuff_lane(b, r, chunk, eoi);
+    uint32_t keep = L.valid & ~L.m.drop;
+    uint32_t total;
+    uint32_t o = block_excl_scan_256(__popc(keep), ws, &total);
+    if (keep == 0xffffu && (o & 3u) == 0u) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) *reinterpret_cast<uint32_t*>(stage + o + 4 * j) = L.w[j];
+    } else {
+        while (keep) {
+            const uint32_t i = __ffs(keep) - 1u;
+            keep &= keep - 1u;
+            stage[o++] = (uint8_t)gjd_lane_byte(L, i);
+        }
+    }
+    __syncthreads();
+    uint8_t* dst = b.scan + b.segs[r.seg].scan_off + b.uchunk_cnt[blockIdx.x];
+    const uint32_t head = min(total, (uint32_t)(-(intptr_t)dst) & 3u);      /* bytes up to the first aligned word of dst */
+    const uint32_t nword = (total - head) >> 2;
+    if (tid < head) dst[tid] = stage[tid];
+    const uint32_t tail0 = head + 4u * nword;
+    if (tid >= 32u && tid - 32u < total - tail0) dst[tail0 + tid - 32u] = stage[tail0 + tid - 32u];
+    uint32_t* dw = reinterpret_cast<uint32_t*>(dst + head);
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>(stage);
+    const uint32_t sel = 0x3210u + 0x1111u * head;                          /* bytes head..head+3 of the pair (lo, hi) */
+    for (uint32_t k = tid; k < nword; k += 256u) dw[k] = __byte_perm(sw[k], sw[k + 1], sel);
 }
 
 /* ------------------------------------------------------------------ entropy: sync ----- */
@@ -919,7 +1052,21 @@ cudaError_t gjd_launch_build_luts(const GjdDhtSet* dht, GjdLutSet* luts, GjdLutC
 
 cudaError_t gjd_launch_fill_maps(const GjdDevBatch& b, cudaStream_t s) {
     if (b.n_img == 0) return cudaSuccess;
-    k_fill_maps<<<b.n_img + b.n_seg, 128, 0, s>>>(b);
+    k_fill_maps<<<b.n_img + b.n_seg + b.n_raw, 128, 0, s>>>(b);
+    return cudaGetLastError();
+}
+
+cudaError_t gjd_launch_unstuff(const GjdDevBatch& b, cudaStream_t s, int* launches) {
+    if (launches) *launches = 0;
+    GJD_CK(cudaMemsetAsync(b.ustatus, 0, (size_t)(b.n_img + 1) * sizeof(uint32_t), s));
+    if (b.n_raw == 0) return cudaSuccess;
+    nvtxRangePushA("gjd stage 0: unstuff scans on the device");
+    GJD_CK(cudaMemsetAsync(b.raw_eoi, 0xff, (size_t)b.n_raw * 2 * sizeof(uint32_t), s));    /* raw_eoi and raw_err */
+    k_unstuff_count<<<b.n_uchunk, 256, 0, s>>>(b);
+    k_unstuff_scan<<<b.n_raw, 256, 0, s>>>(b, b.ustatus);
+    k_unstuff_write<<<b.n_uchunk, 256, 0, s>>>(b);
+    nvtxRangePop();
+    if (launches) *launches = 3;
     return cudaGetLastError();
 }
 
@@ -935,7 +1082,8 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     if (b.n_img == 0) { if (launches) *launches = 0; return cudaSuccess; }
     if (ev) GJD_CK(cudaEventRecord(ev->e[0], s));
     GJD_CK(cudaMemsetAsync(b.meta, 0, (size_t)b.n_tile * 96 * sizeof(uint32_t), s));
-    GJD_CK(cudaMemsetAsync(b.status, 0, (size_t)(b.n_img + 1) * sizeof(uint32_t), s));
+    /* status starts from what the device unstuffing found (all zero for host-unstuffed batches); nosync = 0 */
+    GJD_CK(cudaMemcpyAsync(b.status, b.ustatus, (size_t)(b.n_img + 1) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
     if (ev) GJD_CK(cudaEventRecord(ev->e[1], s));
     /* NVTX ranges bracket the launches of each stage (host side, like the reference's range around its kernel) */
     if (!skip_sync) {

@@ -14,9 +14,9 @@
 struct GjdDevBatch {
     const GjdImage* imgs;
     uint32_t n_img;
-    const GjdSegment* segs;
+    GjdSegment* segs;      /* scan_bits / sub_count of device-unstuffed scans are written by k_unstuff_scan */
     uint32_t n_seg;
-    const uint8_t* scan;
+    uint8_t* scan;
     const GjdLutSet* luts;
     const GjdLutCount* lutc;   /* pair LUT rings of the count pass, same index as luts */
     const GjdQuantSet* quants;
@@ -37,6 +37,16 @@ struct GjdDevBatch {
     uint8_t* rgb;          /* output arena (images with out_is_ptr == 0) */
     uint32_t any_gray;        /* some image is single-component: k_transform_gray is launched too */
     uint32_t any_interleaved; /* some image wants GJD_LAYOUT_INTERLEAVED: selects the transform kernel variant */
+    /* device-side unstuffing (images whose raw scan bytes were uploaded instead of host-unstuffed ones) */
+    const GjdRaw* raws;    /* [n_raw] */
+    uint32_t n_raw;
+    uint32_t n_uchunk;     /* chunks of GJD_UCHUNK raw bytes over all raws */
+    const uint8_t* raw;    /* raw arena (>= 16 bytes of slack on both sides of every scan) */
+    uint32_t* uchunk_raw;  /* [n_uchunk] chunk -> raw */
+    uint32_t* uchunk_cnt;  /* [n_uchunk] bytes the chunk keeps; then (k_unstuff_scan) its exclusive prefix inside the scan */
+    uint32_t* raw_eoi;     /* [n_raw] position of the first EOI in the scan (0xffffffff: none) */
+    uint32_t* raw_err;     /* [n_raw] smallest (position << 2 | GJD_UERR_*) (0xffffffff: none) */
+    uint32_t* ustatus;     /* [n_img + 1] GJD_DEV_U* bits from the unstuffing (kept across runs of a resident batch), then 0 */
     uint32_t* status;      /* [n_img] GJD_DEV_* bits */
     uint32_t* nosync;      /* [1] sequences whose boundary fix-up ran off the end of the sequence */
 };
@@ -50,6 +60,9 @@ struct GjdStageEvents {
 
 cudaError_t gjd_launch_build_luts(const GjdDhtSet* dht, GjdLutSet* luts, GjdLutCount* lutc, uint32_t n, cudaStream_t s);
 cudaError_t gjd_launch_fill_maps(const GjdDevBatch& b, cudaStream_t s);
+/* Device-side unstuffing of the batch's raw scans into the scan arena (no-op when n_raw == 0).  Runs once per staged
+ * batch, before the first gjd_launch_pipeline; clears the status words it may set. */
+cudaError_t gjd_launch_unstuff(const GjdDevBatch& b, cudaStream_t s, int* launches);
 /* Clears scratch and runs every decode stage. transform_variant selects the transform kernel
  * implementation (0 = default).  Returns the number of kernel launches in *launches. */
 cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdStageEvents* ev,

@@ -114,6 +114,23 @@ typedef struct GjdSegment {
     uint16_t pad0;
 } GjdSegment;
 
+/* A scan that is unstuffed ON THE DEVICE (k_unstuff_*): the raw entropy-coded bytes as they stand in the file, from the
+ * first byte after the SOS header to the end of the file (stuffed FF00 pairs, the EOI marker, whatever follows it).
+ * Work is cut into chunks of GJD_UCHUNK bytes counted from the 16-byte boundary at or below raw_off. */
+#define GJD_UCHUNK 4096u
+typedef struct GjdRaw {
+    uint64_t raw_off;       /* byte offset of the first scan byte in the raw arena                    */
+    uint32_t raw_len;       /* bytes from there to the end of the file                                 */
+    uint32_t chunk_first;   /* global index of its first chunk                                         */
+    uint32_t chunk_count;
+    uint32_t seg;           /* its segment: scan_bits and sub_count are written by k_unstuff_scan      */
+    uint32_t img;
+    uint32_t pad;
+} GjdRaw;
+/* raw_err word: (position in the scan) << 2 | code; the smallest one before the EOI decides the image's status */
+#define GJD_UERR_FORMAT 1u       /* a marker other than RSTn / EOI inside the scan, or no EOI at all   */
+#define GJD_UERR_UNSUPPORTED 2u  /* RSTn in a file without DRI                                          */
+
 /* Per-image device descriptor (transform side). */
 typedef struct GjdImage {
     uint64_t out_off;       /* byte offset in the rgb arena, or a raw device address           */
@@ -143,5 +160,7 @@ typedef struct GjdImage {
 #define GJD_DEV_BADSTATE  2u   /* synchronised state disagrees with the coefficient index       */
 #define GJD_DEV_BADCOUNT  4u   /* decoded coefficient count != 192 * MCUs                       */
 #define GJD_DEV_NOSYNC    8u   /* a sequence boundary did not converge in one fix-up round      */
+#define GJD_DEV_UFORMAT   16u  /* device unstuffing: stray marker inside the scan / no EOI (GJD_E_FORMAT)       */
+#define GJD_DEV_UUNSUP    32u  /* device unstuffing: RSTn without DRI (GJD_E_UNSUPPORTED)                        */
 
 #endif

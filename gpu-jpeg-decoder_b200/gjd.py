@@ -155,12 +155,26 @@ class Decoder:
             items[i].len = len(d)
         return items, hold
 
-    def decode(self, files, layout=PLANAR):
+    def make_items_pinned(self, files):
+        """The same, with the JPEG bytes packed back to back in ONE page-locked buffer (gjd_host_alloc): the library
+        then DMAs straight from it.  Returns (items, PinnedBuffer)."""
+        n = len(files)
+        items = (Item * max(n, 1))()
+        pin = PinnedBuffer(sum(len(d) for d in files) + 16)
+        off = 0
+        for i, d in enumerate(files):
+            pin.array[off:off + len(d)] = np.frombuffer(d, np.uint8)
+            items[i].jpg = pin.ptr + off
+            items[i].len = len(d)
+            off += len(d)
+        return items, pin
+
+    def decode(self, files, layout=PLANAR, pinned=False):
         """Decode a list of JPEG `bytes`; returns (list of arrays or None, list of status).
         Arrays are uint8 (3,H,W) for the planar layout, uint8 (H,W,3) for the interleaved one and int16 (H,W,3)
         for INTERLEAVED_I16 (element type and order of the reference's outputChannels)."""
         n = len(files)
-        items, hold = self.make_items(files)
+        items, hold = self.make_items_pinned(files) if pinned else self.make_items(files)
         outs = []
         for i, d in enumerate(files):
             rc, w, h = peek(d)

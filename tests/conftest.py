@@ -79,11 +79,24 @@ class HostSim:
         self.lib.hostsim_pair_check.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_uint32, C.c_void_p]
         self.lib.hostsim_lut_check.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
         self.lib.hostsim_parse.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+        self.lib.hostsim_unstuff_device.argtypes = [C.c_void_p, C.c_size_t, C.c_uint32, C.c_void_p]
+        self.lib.hostsim_unstuff_device.restype = C.c_long
+        self.lib.hostsim_unstuff_host.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
+        self.lib.hostsim_unstuff_host.restype = C.c_long
 
     def parse(self, data):
         w, h = C.c_int32(), C.c_int32()
         rc = self.lib.hostsim_parse(C.cast(C.c_char_p(data), C.c_void_p), len(data), C.byref(w), C.byref(h))
         return rc, w.value, h.value
+
+    def unstuff_both(self, data, misalign=0):
+        """(host loop result, device-style result): each (length or negative status, bytes)."""
+        buf = C.cast(C.c_char_p(data), C.c_void_p)
+        a = np.zeros(len(data) + 128, np.uint8)
+        b = np.zeros(len(data) + 128, np.uint8)
+        ra = self.lib.hostsim_unstuff_host(buf, len(data), a.ctypes.data)
+        rb = self.lib.hostsim_unstuff_device(buf, len(data), misalign, b.ctypes.data)
+        return (ra, a[: max(ra, 0)].tobytes()), (rb, b[: max(rb, 0)].tobytes())
 
     def decode(self, data, sub_log2=0):
         rc, W, H = self.parse(data)

@@ -446,4 +446,70 @@ int hostsim_pair_check(const uint8_t* jpg, size_t len, int sub_log2, uint32_t lo
     return 0;
 }
 
+/* The device unstuffing (k_unstuff_count / k_unstuff_scan / k_unstuff_write, gjd_kernels.cu) stepped on the CPU with the
+ * product's own lane functions: the scan bytes of `jpg` are placed at arena offset 32 + misalign, classified 16 bytes per
+ * "thread", 4 KB per "block", and compacted.  Returns the unstuffed length (bytes in out, which needs the raw length + 64)
+ * or the negative gjd_status the kernels would report.  Must equal gjd_unstuff() for every input without DRI. */
+long hostsim_unstuff_device(const uint8_t* jpg, size_t len, uint32_t misalign, uint8_t* out) {
+    GjdParsed p;
+    int rc = gjd_parse_headers(jpg, len, &p);
+    if (rc) return rc;
+    const uint32_t raw_len = (uint32_t)(p.file_end - p.scan_begin);
+    const uint64_t raw_off = 32 + (misalign & 15u);
+    std::vector<uint8_t> arena(raw_off + raw_len + 64, 0xff);       /* slack filled with FF: must never be looked at */
+    memcpy(arena.data() + raw_off, p.scan_begin, raw_len);
+    const uint64_t base16 = raw_off & ~(uint64_t)15;
+    const uint32_t chunks = std::max<uint32_t>(1u, (uint32_t)(((raw_off & 15u) + raw_len + GJD_UCHUNK - 1) / GJD_UCHUNK));
+    uint32_t eoi = 0xffffffffu, err = 0xffffffffu;
+    std::vector<uint32_t> cnt(chunks, 0);
+    for (uint32_t c = 0; c < chunks; c++)                            /* k_unstuff_count */
+        for (uint32_t tid = 0; tid < 256; tid++) {
+            const GjdUnstuffLane L = gjd_unstuff_lane_at(arena.data(), raw_off, raw_len, base16 + (uint64_t)c * GJD_UCHUNK + tid * 16u, raw_len);
+            for (uint32_t mk = L.m.mark; mk; mk &= mk - 1u) {
+                const uint32_t i = (uint32_t)__builtin_ctz(mk);
+                const uint32_t nb = i < 15u ? gjd_lane_byte(L, i + 1u) : L.next;
+                const uint32_t pos = L.pos0 + i;
+                if (nb == 0xd9u) eoi = std::min(eoi, pos);
+                else err = std::min(err, gjd_unstuff_err_word(pos, nb));
+            }
+            cnt[c] += (uint32_t)__builtin_popcount(L.valid & ~L.m.drop);
+        }
+    /* k_unstuff_scan */
+    if (eoi == 0xffffffffu || (err != 0xffffffffu && (err >> 2) < eoi)) {
+        const bool unsup = err != 0xffffffffu && (eoi == 0xffffffffu || (err >> 2) < eoi) && (err & 3u) == GJD_UERR_UNSUPPORTED;
+        return unsup ? GJD_E_UNSUPPORTED : GJD_E_FORMAT;
+    }
+    const uint32_t ce = (uint32_t)(((raw_off & 15u) + eoi) / GJD_UCHUNK);
+    std::vector<uint32_t> base(chunks, 0);
+    uint32_t carry = 0;
+    for (uint32_t c = 0; c < ce; c++) { base[c] = carry; carry += cnt[c]; }
+    base[ce] = carry;
+    uint32_t total = carry;
+    for (uint32_t tid = 0; tid < 256; tid++) {
+        const GjdUnstuffLane L = gjd_unstuff_lane_at(arena.data(), raw_off, raw_len, base16 + (uint64_t)ce * GJD_UCHUNK + tid * 16u, eoi);
+        total += (uint32_t)__builtin_popcount(L.valid & ~L.m.drop);
+    }
+    /* k_unstuff_write */
+    for (uint32_t c = 0; c < chunks; c++) {
+        const int64_t cstart = (int64_t)c * GJD_UCHUNK - (int64_t)(raw_off & 15u);
+        if (cstart >= (int64_t)eoi) continue;
+        uint32_t o = base[c];
+        for (uint32_t tid = 0; tid < 256; tid++) {
+            const GjdUnstuffLane L = gjd_unstuff_lane_at(arena.data(), raw_off, raw_len, base16 + (uint64_t)c * GJD_UCHUNK + tid * 16u, eoi);
+            for (uint32_t keep = L.valid & ~L.m.drop; keep; keep &= keep - 1u) out[o++] = (uint8_t)gjd_lane_byte(L, (uint32_t)__builtin_ctz(keep));
+        }
+        if (c < ce && o != base[c + 1]) return -100;                 /* the count pass and the write pass disagree */
+    }
+    memset(out + total, 0, 16);
+    return (long)total;
+}
+
+/* the host byte loop on the same input (what the device path has to reproduce) */
+long hostsim_unstuff_host(const uint8_t* jpg, size_t len, uint8_t* out) {
+    GjdParsed p;
+    int rc = gjd_parse_headers(jpg, len, &p);
+    if (rc) return rc;
+    return gjd_unstuff(p.scan_begin, p.file_end, out);
+}
+
 }  /* extern "C" */

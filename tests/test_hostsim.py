@@ -242,3 +242,55 @@ def test_oversized_frame_header_is_refused(hostsim, golden):
     side = int((n_bits // 6) ** 0.5) * 8 // 2
     ok = bytes(data[: at + 5] + side.to_bytes(2, "big") + side.to_bytes(2, "big") + data[at + 9 :])
     assert hostsim.parse(ok)[0] == 0
+
+
+def test_device_unstuffing_equals_host_loop(hostsim, golden, gray_golden, rst_golden):
+    """k_unstuff_* stepped on the CPU (the product's lane functions, 16 bytes per thread, 4 KB per block) against the
+    host byte loop gjd_unstuff (the twin of cpp-decoder/src/parser.cpp:78-99): same bytes, same length, and for damaged
+    scans the same status — every fixture at every arena alignment, hand-made marker sequences, 600 mutated files."""
+    import fuzzlib
+
+    def has_dri(f):
+        at = f.find(b"\xff\xda")
+        return at >= 0 and b"\xff\xdd" in f[:at]
+
+    files = [f for f in list(golden.values()) + list(gray_golden.values()) if not has_dri(f)]
+    assert len(files) >= 20
+    for f in files:
+        for mis in range(16):
+            (ra, a), (rb, b) = hostsim.unstuff_both(f, mis)
+            assert ra > 0 and ra == rb and a == b
+    # restart markers without DRI, stray markers, fill bytes, FF at the very end, EOI followed by junk with markers
+    base = golden["images/3_120x120"]
+    sos = base.index(b"\xff\xda")
+    head = base[: sos + 2 + int.from_bytes(base[sos + 2: sos + 4], "big")]
+    body = base[len(head):-2]
+    cases = [head + body + b"\xff\xd9",
+             head + body[:100] + b"\xff\xff\xff" + body[100:] + b"\xff\xd9",            # fill bytes
+             head + body[:4090 - len(head) % 16] + b"\xff\x00" + body[4090:] + b"\xff\xd9",   # a stuffed pair near a chunk edge
+             head + body + b"\xff\xd9" + b"\xff\xc4junk\xff\xd0" * 5,                   # markers after the EOI are ignored
+             head + body[:50] + b"\xff\xd0" + body[50:] + b"\xff\xd9",                    # RSTn without DRI
+             head + body[:50] + b"\xff\xc4" + body[50:60] + b"\xff\xd0" + body[60:] + b"\xff\xd9",   # stray marker first
+             head + body[:50] + b"\xff\xd3" + body[50:60] + b"\xff\xe1" + body[60:] + b"\xff\xd9",   # RSTn first
+             head + body,                                                                # no EOI
+             head + body + b"\xff",                                                      # FF as the last byte
+             head + body + b"\xff\xff",
+             head + b"\xff\xd9",                                                         # empty scan
+             head + body[:7] + b"\xff\xd9" + body]                                       # early EOI
+    for k in range(16):                                                                   # marker pairs straddling 16-byte and 4 KB edges
+        cases.append(head + body[:4096 * 2 - len(head) - 8 + k] + b"\xff\x00\xff\x00\xff\xff\x00" + body[9000:] + b"\xff\xd9")
+    seen = set()
+    for f in cases + list(fuzzlib.cases([golden[n] for n in ("images/3_120x120", "images/5_200x200", "synth/s6_256x256_q90_o1")] , 600, 99)):
+        for mis in (0, 5, 15):
+            (ra, a), (rb, b) = hostsim.unstuff_both(f, mis)
+            rc, w, h = hostsim.parse(f)
+            if rc != 0:
+                assert ra == rc and rb == rc
+                continue
+            if has_dri(f):
+                continue                                  # scans with restart intervals stay on the host path
+            assert ra == rb, (ra, rb, mis)
+            if ra >= 0:
+                assert a == b
+            seen.add(ra if ra < 0 else 0)
+    assert {0, -4, -5} <= seen
