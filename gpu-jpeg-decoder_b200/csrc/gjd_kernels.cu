@@ -391,7 +391,9 @@ __global__ void __launch_bounds__(256) k_seq_scan(GjdDevBatch b) {
             const uint32_t s = base + i;
             if (s >= d.seq_count) break;                      /* warp-uniform */
             const uint2* si = b.sinfo + (size_t)(d.seq_first + s) * GJD_SEQ_SUBS;
-            const uint32_t cnt = min(GJD_SEQ_SUBS, d.sub_count - s * GJD_SEQ_SUBS);
+            /* (a device-unstuffed scan may be shorter than the raw length its sequences were sized from: the last
+             * sequences can be empty) */
+            const uint32_t cnt = s * GJD_SEQ_SUBS < d.sub_count ? min(GJD_SEQ_SUBS, d.sub_count - s * GJD_SEQ_SUBS) : 0u;
             uint32_t t = 0;
             for (uint32_t k = lane; k < cnt; k += 32u) t += si[k].y >> 8;
             t = __reduce_add_sync(0xffffffffu, t);

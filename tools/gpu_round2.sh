@@ -8,7 +8,7 @@ nproc >> $out/${tag}_gpu.txt; free -g | head -2 >> $out/${tag}_gpu.txt
 for what in "$@"; do
 case $what in
 tests)
-  timeout 1200 python -m pytest tests -m gpu -x -q > $out/${tag}_pytest_gpu.txt 2>&1; echo "pytest rc=$?" >> $out/${tag}_pytest_gpu.txt
+  timeout 1200 python -m pytest tests -m gpu -q > $out/${tag}_pytest_gpu.txt 2>&1; echo "pytest rc=$?" >> $out/${tag}_pytest_gpu.txt
   tail -5 $out/${tag}_pytest_gpu.txt ;;
 bench)
   timeout 600 python bench.py --steps 10 --warmup 3 > $out/${tag}_bench.json 2> $out/${tag}_bench.err; echo "bench rc=$?"
