@@ -576,11 +576,16 @@ GJD_HD void gjd_write_span(const uint32_t* scan, const Lut& lut, uint32_t end_bi
 #define GJD_C7 565
 
 /* Row pass on b[0..7] (stride 1); general path only — the reference's all-zero shortcut
- * (idct.cpp:38-41) is value-identical: ((b0<<11)+128)>>8 == b0<<3. */
-GJD_HD void gjd_idct_row(int& b0, int& b1, int& b2, int& b3, int& b4, int& b5, int& b6, int& b7) {
+ * (idct.cpp:38-41) is value-identical: ((b0<<11)+128)>>8 == b0<<3.
+ * PRE: what the column pass is handed for this row.  0: the reference's b >> 8.  1 (row 0) and 2 (row 4): the column
+ * pass only ever uses these rows as b*256 (x0 = b0*256 + 8192, x1 = b4*256, idct.cpp:83-88), and (s >> 8) * 256 is
+ * s & ~255 for every 32-bit s; row 0 also carries the 8192, which is a multiple of 256 and enters all eight sums of
+ * the row once: ((s + 8192) >> 8) * 256 = (s >> 8) * 256 + 8192.  Same values, one instruction less per sample. */
+template <int PRE>
+GJD_HD void gjd_idct_row_t(int& b0, int& b1, int& b2, int& b3, int& b4, int& b5, int& b6, int& b7) {
     int x0, x1, x2, x3, x4, x5, x6, x7, x8;
     x1 = b4 * 2048; x2 = b6; x3 = b2; x4 = b1; x5 = b7; x6 = b5; x7 = b3;
-    x0 = b0 * 2048 + 128;
+    x0 = b0 * 2048 + (PRE == 1 ? 128 + 8192 : 128);
     x8 = GJD_C7 * (x4 + x5);
     x4 = x8 + (GJD_C1 - GJD_C7) * x4;
     x5 = x8 - (GJD_C1 + GJD_C7) * x5;
@@ -602,14 +607,16 @@ GJD_HD void gjd_idct_row(int& b0, int& b1, int& b2, int& b3, int& b4, int& b5, i
     x0 -= x2;
     x2 = (181 * (x4 + x5) + 128) >> 8;
     x4 = (181 * (x4 - x5) + 128) >> 8;
-    b0 = (x7 + x1) >> 8;
-    b1 = (x3 + x2) >> 8;
-    b2 = (x0 + x4) >> 8;
-    b3 = (x8 + x6) >> 8;
-    b4 = (x8 - x6) >> 8;
-    b5 = (x0 - x4) >> 8;
-    b6 = (x3 - x2) >> 8;
-    b7 = (x7 - x1) >> 8;
+    if (PRE == 0) {
+        b0 = (x7 + x1) >> 8; b1 = (x3 + x2) >> 8; b2 = (x0 + x4) >> 8; b3 = (x8 + x6) >> 8;
+        b4 = (x8 - x6) >> 8; b5 = (x0 - x4) >> 8; b6 = (x3 - x2) >> 8; b7 = (x7 - x1) >> 8;
+    } else {
+        b0 = (x7 + x1) & ~255; b1 = (x3 + x2) & ~255; b2 = (x0 + x4) & ~255; b3 = (x8 + x6) & ~255;
+        b4 = (x8 - x6) & ~255; b5 = (x0 - x4) & ~255; b6 = (x3 - x2) & ~255; b7 = (x7 - x1) & ~255;
+    }
+}
+GJD_HD void gjd_idct_row(int& b0, int& b1, int& b2, int& b3, int& b4, int& b5, int& b6, int& b7) {
+    gjd_idct_row_t<0>(b0, b1, b2, b3, b4, b5, b6, b7);
 }
 
 /* clip(v >> 14) to [-256,255] (idct.cpp:20-22), returned with a +256 bias: [0,511]. */
@@ -624,11 +631,14 @@ GJD_HD int gjd_descale_clip_biased(int v) {
 }
 
 /* Column pass (idct.cpp:79-122; shortcut :83-86 is value-identical to the general path).
- * Outputs are clip(.)+256, i.e. in [0,511]. */
-GJD_HD void gjd_idct_col(int& b0, int& b1, int& b2, int& b3, int& b4, int& b5, int& b6, int& b7) {
+ * RAW = false: outputs are clip(.)+256, i.e. in [0,511], from rows as the reference hands them over.
+ * RAW = true : b0 and b4 come pre-multiplied from gjd_idct_row_t<1> / <2> (b0*256 + 8192, b4*256), and the outputs are
+ *              the eight sums BEFORE the final >> 14 and clip (gjd_pack_samples finishes two of them at a time). */
+template <bool RAW>
+GJD_HD void gjd_idct_col_t(int& b0, int& b1, int& b2, int& b3, int& b4, int& b5, int& b6, int& b7) {
     int x0, x1, x2, x3, x4, x5, x6, x7, x8;
-    x1 = b4 * 256; x2 = b6; x3 = b2; x4 = b1; x5 = b7; x6 = b5; x7 = b3;
-    x0 = b0 * 256 + 8192;
+    x1 = RAW ? b4 : b4 * 256; x2 = b6; x3 = b2; x4 = b1; x5 = b7; x6 = b5; x7 = b3;
+    x0 = RAW ? b0 : b0 * 256 + 8192;
     x8 = GJD_C7 * (x4 + x5) + 4;
     x4 = (x8 + (GJD_C1 - GJD_C7) * x4) >> 3;
     x5 = (x8 - (GJD_C1 + GJD_C7) * x5) >> 3;
@@ -650,14 +660,85 @@ GJD_HD void gjd_idct_col(int& b0, int& b1, int& b2, int& b3, int& b4, int& b5, i
     x0 -= x2;
     x2 = (181 * (x4 + x5) + 128) >> 8;
     x4 = (181 * (x4 - x5) + 128) >> 8;
-    b0 = gjd_descale_clip_biased(x7 + x1);
-    b1 = gjd_descale_clip_biased(x3 + x2);
-    b2 = gjd_descale_clip_biased(x0 + x4);
-    b3 = gjd_descale_clip_biased(x8 + x6);
-    b4 = gjd_descale_clip_biased(x8 - x6);
-    b5 = gjd_descale_clip_biased(x0 - x4);
-    b6 = gjd_descale_clip_biased(x3 - x2);
-    b7 = gjd_descale_clip_biased(x7 - x1);
+    if (RAW) {
+        b0 = x7 + x1; b1 = x3 + x2; b2 = x0 + x4; b3 = x8 + x6;
+        b4 = x8 - x6; b5 = x0 - x4; b6 = x3 - x2; b7 = x7 - x1;
+    } else {
+        b0 = gjd_descale_clip_biased(x7 + x1);
+        b1 = gjd_descale_clip_biased(x3 + x2);
+        b2 = gjd_descale_clip_biased(x0 + x4);
+        b3 = gjd_descale_clip_biased(x8 + x6);
+        b4 = gjd_descale_clip_biased(x8 - x6);
+        b5 = gjd_descale_clip_biased(x0 - x4);
+        b6 = gjd_descale_clip_biased(x3 - x2);
+        b7 = gjd_descale_clip_biased(x7 - x1);
+    }
+}
+GJD_HD void gjd_idct_col(int& b0, int& b1, int& b2, int& b3, int& b4, int& b5, int& b6, int& b7) {
+    gjd_idct_col_t<false>(b0, b1, b2, b3, b4, b5, b6, b7);
+}
+
+/* ---- packed 16-bit helpers (sm_100a: PRMT, I2IP.S16.S32.SAT, VIADDMNMX.S16x2.RELU; plain C on the host) ---- */
+GJD_HD uint32_t gjd_prmt(uint32_t a, uint32_t b, uint32_t sel) {
+#ifdef __CUDA_ARCH__
+    return __byte_perm(a, b, sel);
+#else
+    const uint64_t ab = ((uint64_t)b << 32) | a;
+    uint32_t r = 0;
+    for (int i = 0; i < 4; i++) r |= (uint32_t)((ab >> (8 * ((sel >> (4 * i)) & 7u))) & 0xffu) << (8 * i);
+    return r;
+#endif
+}
+/* per 16-bit lane: max(min(a + b, c), 0), signed lanes that wrap like the hardware's */
+GJD_HD uint32_t gjd_viaddmin_s16x2_relu(uint32_t a, uint32_t b, uint32_t c) {
+#ifdef __CUDA_ARCH__
+    return __viaddmin_s16x2_relu(a, b, c);
+#else
+    uint32_t r = 0;
+    for (int h = 0; h < 2; h++) {
+        int16_t t = (int16_t)((a >> (16 * h)) + (b >> (16 * h)));
+        const int16_t m = (int16_t)(c >> (16 * h));
+        t = t > m ? m : t;
+        t = t < 0 ? (int16_t)0 : t;
+        r |= (uint32_t)(uint16_t)t << (16 * h);
+    }
+    return r;
+#endif
+}
+/* (sat_s16(hi) << 16) | (sat_s16(lo) & 0xffff) */
+GJD_HD uint32_t gjd_pack_sat_s16(int hi, int lo) {
+#ifdef __CUDA_ARCH__
+    uint32_t d;
+    asm("cvt.pack.sat.s16.s32 %0, %1, %2;" : "=r"(d) : "r"(hi), "r"(lo));
+    return d;
+#else
+    const int h = hi > 32767 ? 32767 : (hi < -32768 ? -32768 : hi), l = lo > 32767 ? 32767 : (lo < -32768 ? -32768 : lo);
+    return ((uint32_t)(uint16_t)(int16_t)h << 16) | (uint32_t)(uint16_t)(int16_t)l;
+#endif
+}
+
+/* per 16-bit lane: max(min(a, c), 0) */
+GJD_HD uint32_t gjd_vimin_s16x2_relu(uint32_t a, uint32_t c) {
+#ifdef __CUDA_ARCH__
+    return __vimin_s16x2_relu(a, c);
+#else
+    uint32_t r = 0;
+    for (int h = 0; h < 2; h++) {
+        int16_t t = (int16_t)(a >> (16 * h));
+        const int16_t m = (int16_t)(c >> (16 * h));
+        t = t > m ? m : t;
+        t = t < 0 ? (int16_t)0 : t;
+        r |= (uint32_t)(uint16_t)t << (16 * h);
+    }
+    return r;
+#endif
+}
+
+/* Two column-pass sums -> two finished samples in one word: clip(s >> 14) + 256 for both (idct.cpp:20-22, 113-120),
+ * s1 in the high half.  (s >> 14) + 256 is one LEA.HI each; the saturation to 16 bits cannot change a value that is
+ * clamped to [0,511] next, and no 16-bit lane ever adds (a lane add after the saturation could wrap). */
+GJD_HD uint32_t gjd_pack_samples(int s1, int s0) {
+    return gjd_vimin_s16x2_relu(gjd_pack_sat_s16((s1 >> 14) + 256, (s0 >> 14) + 256), 0x01ff01ffu);
 }
 
 /* Full 8x8: v[] natural order, dequantised in, biased samples (clip+256) out. */
@@ -669,6 +750,20 @@ GJD_HD void gjd_idct8x8(int v[64]) {
 #pragma unroll
     for (int c = 0; c < 8; c++)
         gjd_idct_col(v[c], v[8 + c], v[16 + c], v[24 + c], v[32 + c], v[40 + c], v[48 + c], v[56 + c]);
+}
+
+/* The same with the shortcuts of gjd_idct_row_t<1,2> / gjd_idct_col_t<true>: v[] holds the 64 column-pass sums before
+ * the final >> 14 and clip (natural order); gjd_pack_samples turns them into samples. */
+GJD_HD void gjd_idct8x8_raw(int v[64]) {
+    gjd_idct_row_t<1>(v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7]);
+#pragma unroll
+    for (int r = 1; r < 8; r++) {
+        if (r == 4) gjd_idct_row_t<2>(v[32], v[33], v[34], v[35], v[36], v[37], v[38], v[39]);
+        else gjd_idct_row_t<0>(v[8 * r], v[8 * r + 1], v[8 * r + 2], v[8 * r + 3], v[8 * r + 4], v[8 * r + 5], v[8 * r + 6], v[8 * r + 7]);
+    }
+#pragma unroll
+    for (int c = 0; c < 8; c++)
+        gjd_idct_col_t<true>(v[c], v[8 + c], v[16 + c], v[24 + c], v[32 + c], v[40 + c], v[48 + c], v[56 + c]);
 }
 
 /* ------------------------------------------------------------------ colour ------------ */
@@ -778,6 +873,77 @@ GJD_HD bool gjd_color_fast(int yb, int cbb, int crb, int& R, int& G, int& B) {
 
 GJD_HD void gjd_color(int yb, int cbb, int crb, int& R, int& G, int& B) {
     if (gjd_color_fast(yb, cbb, crb, R, G, B)) G = gjd_color_g_exact(yb - 256, cbb - 256, crb - 256);
+}
+
+/* ------------------------------------------------------------------ colour, 8 pixels of a row at a time ----------
+ * What k_transform runs (the scalar gjd_color above stays as the per-pixel statement of the same function).
+ * Samples arrive as the IDCT parks them: two biased 9-bit samples per word (x odd in the high half).
+ *   R, B   2^-16 fixed point: hi16(Cr' * KR16 + CR16) = floor(1.402 Cr) - 128 for every Cr' = Cr + 256 in [0,511]
+ *          (all 512 values checked against the 2^-20 form above, tests/test_hostsim.py), so the two high halves of
+ *          two pixels are ONE byte permute away from a packed pair that a single VIADDMNMX.S16x2.RELU adds to the
+ *          packed Y pair and clamps to [0,255].
+ *   G      2^-32 fixed point in 64 bits: the offset's integer part is the high word, no shift; the fraction is the low
+ *          word.  At this precision (|error| < 2^-23) the fast value can differ from the reference's float sequence
+ *          only when the exact rational lies within 12/587000 BELOW an integer (4 of the 2^18 (Cb,Cr) pairs; 12 of the
+ *          2^27 triples really differ) — those re-run the reference's IEEE sequence (gjd_color_g_exact).  Exact integers
+ *          (Cb = Cr = 0: every neutral pixel) are not in that zone, unlike the symmetric zone of the 2^-20 form.
+ *          0.299*1.402/0.587 * 2^32 does not fit a signed 32-bit multiplier: -c*Cr' = -Cr' + (1 - c)*Cr', and the
+ *          -Cr' goes into the packed Y pair (one IADD3 for two pixels).
+ * Proven against cpp-decoder/utils/color.cpp:3-18 for all 2^27 triples on the CPU (tests/test_hostsim.py::
+ * test_colour_exhaustive) and on the GPU (tests/test_gpu_parity.py::test_colour_exhaustive_on_device). */
+#define GJD_KR16 91881
+#define GJD_CR16 (-31910037)
+#define GJD_KB16 116130
+#define GJD_CB16 (-38117862)
+#define GJD_GA32 1478054095ll          /* round(0.114*1.772/0.587 * 2^32)                          */
+#define GJD_GC32 3067191994ll          /* round(0.299*1.402/0.587 * 2^32)                          */
+#define GJD_GC32P 1227775302ll         /* 2^32 - GJD_GC32                                           */
+#define GJD_G_DELTA 859ll              /* keeps exact integers (and values above them) on the right side of floor() */
+#define GJD_G_ZONE 94489u              /* 2.2e-5 * 2^32: fraction >= 2^32 - ZONE -> re-run the IEEE sequence */
+/* constant term: -128 (level shift relative to the +256 bias of Y), the +256 bias of both chroma samples, and -512 for
+ * the (+512 - Cr') that rides in the packed Y pair */
+#define GJD_G_C64 (256ll * (GJD_GA32 + GJD_GC32) - (128ll << 32) + GJD_G_DELTA - (512ll << 32))
+#define GJD_G_DANGER (0u - GJD_G_ZONE)
+
+/* the G offset of one pixel: high word = floor(-a*Cb - c*Cr) - 128 + Cr' - 512, low word = the fraction */
+GJD_HD long long gjd_color_g64(uint32_t cbb, uint32_t crb) {
+    long long t = (long long)(int)cbb * (-GJD_GA32) + GJD_G_C64;
+    return t + (long long)(int)crb * GJD_GC32P;
+}
+
+/* yw, bw, rw: four words each = the 8 samples of one row of Y, Cb, Cr.  r, g, b: two words each = 8 clamped bytes. */
+GJD_HD void gjd_color_row8(const uint32_t yw[4], const uint32_t bw[4], const uint32_t rw[4], uint32_t r[2], uint32_t g[2], uint32_t b[2]) {
+    uint32_t r2[4], g2[4], b2[4], fmax = 0;
+#ifdef __CUDACC__
+#pragma unroll
+#endif
+    for (int j = 0; j < 4; j++) {
+        const uint32_t cb0 = bw[j] & 0xffffu, cb1 = bw[j] >> 16, cr0 = rw[j] & 0xffffu, cr1 = rw[j] >> 16;
+        const uint32_t tr0 = cr0 * (uint32_t)GJD_KR16 + (uint32_t)GJD_CR16, tr1 = cr1 * (uint32_t)GJD_KR16 + (uint32_t)GJD_CR16;
+        const uint32_t tb0 = cb0 * (uint32_t)GJD_KB16 + (uint32_t)GJD_CB16, tb1 = cb1 * (uint32_t)GJD_KB16 + (uint32_t)GJD_CB16;
+        r2[j] = gjd_viaddmin_s16x2_relu(gjd_prmt(tr0, tr1, 0x7632u), yw[j], 0x00ff00ffu);
+        b2[j] = gjd_viaddmin_s16x2_relu(gjd_prmt(tb0, tb1, 0x7632u), yw[j], 0x00ff00ffu);
+        const long long t0 = gjd_color_g64(cb0, cr0), t1 = gjd_color_g64(cb1, cr1);
+        const uint32_t ywr = yw[j] + 0x02000200u - rw[j];      /* per half: Y' + 512 - Cr' in [1,1023]: no borrow between the halves */
+        g2[j] = gjd_viaddmin_s16x2_relu(gjd_prmt((uint32_t)(t0 >> 32), (uint32_t)(t1 >> 32), 0x5410u), ywr, 0x00ff00ffu);
+        const uint32_t f0 = (uint32_t)t0, f1 = (uint32_t)t1;
+        fmax = fmax > f0 ? fmax : f0;
+        fmax = fmax > f1 ? fmax : f1;
+    }
+    if (fmax >= GJD_G_DANGER) {          /* rare (4 chroma pairs): G of the flagged pixels from the reference's IEEE sequence */
+        for (int x = 0; x < 8; x++) {
+            const uint32_t sh = (uint32_t)(x & 1) * 16u;
+            const uint32_t yb = (yw[x >> 1] >> sh) & 0xffffu, cbb = (bw[x >> 1] >> sh) & 0xffffu, crb = (rw[x >> 1] >> sh) & 0xffffu;
+            if ((uint32_t)gjd_color_g64(cbb, crb) < GJD_G_DANGER) continue;
+            const uint32_t G = (uint32_t)gjd_color_g_exact((int)yb - 256, (int)cbb - 256, (int)crb - 256);
+            g2[x >> 1] = (g2[x >> 1] & ~(0xffffu << sh)) | (G << sh);
+        }
+    }
+    for (int h = 0; h < 2; h++) {        /* bytes 0 and 2 of two words -> four pixels in one word */
+        r[h] = gjd_prmt(r2[2 * h], r2[2 * h + 1], 0x6420u);
+        g[h] = gjd_prmt(g2[2 * h], g2[2 * h + 1], 0x6420u);
+        b[h] = gjd_prmt(b2[2 * h], b2[2 * h + 1], 0x6420u);
+    }
 }
 
 #endif /* GJD_DEVFN_CUH */

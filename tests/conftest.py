@@ -76,6 +76,8 @@ class HostSim:
                                             C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_void_p]
         self.lib.hostsim_color_plane.argtypes = [C.c_int, C.c_void_p]
         self.lib.hostsim_idct.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        self.lib.hostsim_idct_packed.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        self.lib.hostsim_color_plane_row8.argtypes = [C.c_int, C.c_void_p]
         self.lib.hostsim_pair_check.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_uint32, C.c_void_p]
         self.lib.hostsim_lut_check.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
         self.lib.hostsim_parse.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]

@@ -267,7 +267,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
         }
     }
     for (uint32_t mcu = 0; !gray && mcu < mcu_count; mcu++) {
-        int samples[3][64];
+        uint32_t samples[3][32];   /* as k_transform parks them: two biased samples per word, row r = words 4r..4r+3 */
         if (ri && mcu % ri == 0) pred[0] = pred[1] = pred[2] = 0;   /* T.81 E.1.4 */
         for (int c = 0; c < 3; c++) {
             size_t bk = (size_t)mcu * 3 + c;
@@ -282,22 +282,23 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
             v[0] = pred[c] * q[c][0];
             if (coef_out)
                 for (int k = 0; k < 64; k++) coef_out[(size_t)mcu * 192 + c * 64 + k] = (int16_t)(k == 0 ? pred[c] : zq[k]);
-            gjd_idct8x8(v);
-            memcpy(samples[c], v, sizeof(v));
+            gjd_idct8x8_raw(v);
+            for (int j = 0; j < 32; j++) samples[c][j] = gjd_pack_samples(v[2 * j + 1], v[2 * j]);
         }
         if (rgb_out) {
             uint32_t by = mcu / mcus_x, bx = mcu % mcus_x;
-            for (int r = 0; r < 8; r++)
+            for (int r = 0; r < 8; r++) {
+                uint32_t pr[2], pg[2], pb[2];
+                gjd_color_row8(&samples[0][4 * r], &samples[1][4 * r], &samples[2][4 * r], pr, pg, pb);
                 for (int x = 0; x < 8; x++) {
                     uint32_t py = by * 8 + r, px = bx * 8 + x;
                     if (py >= H || px >= W) continue;
-                    int R, G, B;
-                    gjd_color(samples[0][8 * r + x], samples[1][8 * r + x], samples[2][8 * r + x], R, G, B);
                     size_t o = (size_t)py * W + px;
-                    rgb_out[o] = (uint8_t)R;
-                    rgb_out[(size_t)W * H + o] = (uint8_t)G;
-                    rgb_out[2 * (size_t)W * H + o] = (uint8_t)B;
+                    rgb_out[o] = (uint8_t)(pr[x >> 2] >> (8 * (x & 3)));
+                    rgb_out[(size_t)W * H + o] = (uint8_t)(pg[x >> 2] >> (8 * (x & 3)));
+                    rgb_out[2 * (size_t)W * H + o] = (uint8_t)(pb[x >> 2] >> (8 * (x & 3)));
                 }
+            }
         }
     }
     if (stats) {
@@ -320,6 +321,24 @@ void hostsim_color_plane(int y, uint8_t* out) {
         }
 }
 
+/* the same plane through gjd_color_row8, the packed 8-pixels-per-call form k_transform runs */
+void hostsim_color_plane_row8(int y, uint8_t* out) {
+    for (int cb = -256; cb < 256; cb++)
+        for (int cr0 = -256; cr0 < 256; cr0 += 8) {
+            uint32_t yw[4], bw[4], rw[4], r[2], g[2], b[2];
+            for (int j = 0; j < 4; j++) {
+                yw[j] = (uint32_t)(y + 256) * 0x10001u;
+                bw[j] = (uint32_t)(cb + 256) * 0x10001u;
+                rw[j] = (uint32_t)(cr0 + 2 * j + 256) | ((uint32_t)(cr0 + 2 * j + 1 + 256) << 16);
+            }
+            gjd_color_row8(yw, bw, rw, r, g, b);
+            for (int x = 0; x < 8; x++) {
+                uint8_t* o = out + ((size_t)(cb + 256) * 512 + (cr0 + x + 256)) * 3;
+                o[0] = (uint8_t)(r[x >> 2] >> (8 * (x & 3))); o[1] = (uint8_t)(g[x >> 2] >> (8 * (x & 3))); o[2] = (uint8_t)(b[x >> 2] >> (8 * (x & 3)));
+            }
+        }
+}
+
 /* dequantised natural-order block in, clip(.) samples (unbiased) out */
 void hostsim_idct(const int32_t* in, int32_t* out, size_t nblocks) {
     for (size_t b = 0; b < nblocks; b++) {
@@ -327,6 +346,20 @@ void hostsim_idct(const int32_t* in, int32_t* out, size_t nblocks) {
         for (int i = 0; i < 64; i++) v[i] = in[b * 64 + i];
         gjd_idct8x8(v);
         for (int i = 0; i < 64; i++) out[b * 64 + i] = v[i] - 256;
+    }
+}
+
+/* the same through gjd_idct8x8_raw + gjd_pack_samples (the form k_transform runs) */
+void hostsim_idct_packed(const int32_t* in, int32_t* out, size_t nblocks) {
+    for (size_t b = 0; b < nblocks; b++) {
+        int v[64];
+        for (int i = 0; i < 64; i++) v[i] = in[b * 64 + i];
+        gjd_idct8x8_raw(v);
+        for (int j = 0; j < 32; j++) {
+            const uint32_t w = gjd_pack_samples(v[2 * j + 1], v[2 * j]);
+            out[b * 64 + 2 * j] = (int)(w & 0xffffu) - 256;
+            out[b * 64 + 2 * j + 1] = (int)(w >> 16) - 256;
+        }
     }
 }
 

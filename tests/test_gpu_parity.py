@@ -502,8 +502,9 @@ def _marker_cases(base):
     sos = base.index(b"\xff\xda")
     head = base[: sos + 2 + int.from_bytes(base[sos + 2: sos + 4], "big")]
     body = base[len(head):-2]
+    k = body.index(b"\xff\x00")
     return [head + body + b"\xff\xd9" + b"\xff\xc4junk\xff\xd0" * 5,      # markers behind the EOI are ignored
-            head + body[:100] + b"\xff\xff\xff" + body[100:] + b"\xff\xd9",   # fill bytes
+            head + body[:k] + b"\xff\xff\xff" + body[k:] + b"\xff\xd9",       # fill bytes in front of a stuffed FF
             head + body[:50] + b"\xff\xd0" + body[50:] + b"\xff\xd9",       # RSTn without DRI      -> -5
             head + body[:50] + b"\xff\xc4" + body[50:] + b"\xff\xd9",       # stray marker          -> -4
             head + body,                                                     # no EOI                -> -4

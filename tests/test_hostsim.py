@@ -34,6 +34,17 @@ def test_colour_exhaustive(hostsim, oracle):
         assert np.array_equal(a, b), f"colour mismatch at y={y}"
 
 
+def test_colour_exhaustive_packed_rows(hostsim, oracle):
+    """gjd_color_row8 — the packed form k_transform runs (R/B in 2^-16 fixed point on 16-bit lanes, G in 2^-32 fixed
+    point with the one-sided danger zone) == cpp-decoder/utils/color.cpp on all 2^27 triples."""
+    a = np.empty((512, 512, 3), np.uint8)
+    b = np.empty((512, 512, 3), np.uint8)
+    for y in range(-256, 256):
+        hostsim.lib.hostsim_color_plane_row8(y, a.ctypes.data)
+        oracle.lib.gjdo_color_plane(y, b.ctypes.data)
+        assert np.array_equal(a, b), f"colour mismatch at y={y}"
+
+
 def test_idct_random_blocks(hostsim, oracle):
     rng = np.random.default_rng(7)
     n = 4000
@@ -51,6 +62,10 @@ def test_idct_random_blocks(hostsim, oracle):
     for i in range(n):
         oracle.lib.gjdo_idct_block(want[i].ctypes.data)
     assert np.array_equal(out, want)
+    # the form k_transform runs: rows 0/4 handed over pre-multiplied, two samples finished per packed operation
+    out2 = np.zeros_like(blocks)
+    hostsim.lib.hostsim_idct_packed(blocks.ctypes.data, out2.ctypes.data, n)
+    assert np.array_equal(out2, want)
 
 
 def test_parser_contract(hostsim, golden):
