@@ -905,10 +905,19 @@ GJD_HD void gjd_color(int yb, int cbb, int crb, int& R, int& G, int& B) {
 #define GJD_G_C64 (256ll * (GJD_GA32 + GJD_GC32) - (128ll << 32) + GJD_G_DELTA - (512ll << 32))
 #define GJD_G_DANGER (0u - GJD_G_ZONE)
 
-/* the G offset of one pixel: high word = floor(-a*Cb - c*Cr) - 128 + Cr' - 512, low word = the fraction */
+/* the G offset of one pixel: high word = floor(-a*Cb - c*Cr) - 128 + Cr' - 512, low word = the fraction.
+ * (mad.wide.s32 by hand: from the C expression the compiler makes an unsigned product plus a correction of the high
+ * word, three instructions more per pixel.) */
 GJD_HD long long gjd_color_g64(uint32_t cbb, uint32_t crb) {
+#ifdef __CUDA_ARCH__
+    long long t;
+    asm("{.reg .s64 u; mad.wide.s32 u, %1, %3, %5; mad.wide.s32 %0, %2, %4, u;}"
+        : "=l"(t) : "r"(cbb), "r"(crb), "n"((int)(-GJD_GA32)), "n"((int)GJD_GC32P), "l"(GJD_G_C64));
+    return t;
+#else
     long long t = (long long)(int)cbb * (-GJD_GA32) + GJD_G_C64;
     return t + (long long)(int)crb * GJD_GC32P;
+#endif
 }
 
 /* yw, bw, rw: four words each = the 8 samples of one row of Y, Cb, Cr.  r, g, b: two words each = 8 clamped bytes. */
@@ -931,12 +940,17 @@ GJD_HD void gjd_color_row8(const uint32_t yw[4], const uint32_t bw[4], const uin
         fmax = fmax > f1 ? fmax : f1;
     }
     if (fmax >= GJD_G_DANGER) {          /* rare (4 chroma pairs): G of the flagged pixels from the reference's IEEE sequence */
-        for (int x = 0; x < 8; x++) {
-            const uint32_t sh = (uint32_t)(x & 1) * 16u;
-            const uint32_t yb = (yw[x >> 1] >> sh) & 0xffffu, cbb = (bw[x >> 1] >> sh) & 0xffffu, crb = (rw[x >> 1] >> sh) & 0xffffu;
-            if ((uint32_t)gjd_color_g64(cbb, crb) < GJD_G_DANGER) continue;
-            const uint32_t G = (uint32_t)gjd_color_g_exact((int)yb - 256, (int)cbb - 256, (int)crb - 256);
-            g2[x >> 1] = (g2[x >> 1] & ~(0xffffu << sh)) | (G << sh);
+#ifdef __CUDACC__
+#pragma unroll
+#endif
+        for (int x = 0; x < 8; x++) {    /* (unrolled: run-time indices would push the arrays into local memory) */
+            const int sh = (x & 1) * 16;
+            const uint32_t cbb = (bw[x >> 1] >> sh) & 0xffffu, crb = (rw[x >> 1] >> sh) & 0xffffu;
+            if ((uint32_t)gjd_color_g64(cbb, crb) >= GJD_G_DANGER) {
+                const uint32_t yb = (yw[x >> 1] >> sh) & 0xffffu;
+                const uint32_t G = (uint32_t)gjd_color_g_exact((int)yb - 256, (int)cbb - 256, (int)crb - 256);
+                g2[x >> 1] = (g2[x >> 1] & ~(0xffffu << sh)) | (G << sh);
+            }
         }
     }
     for (int h = 0; h < 2; h++) {        /* bytes 0 and 2 of two words -> four pixels in one word */

@@ -886,6 +886,252 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
     }
 }
 
+/* ------------------------------------------------------------------ transform, round 2 -- */
+/*
+ * k_transform2 — the shipped transform (k_transform above stays as GJD_TRANSFORM_VARIANT=1 for A/B runs and as the
+ * coefficient export of gjd_decode_coeffs).  Same result, fewer instructions (profiles/r02a_k_transform.*: the round-1
+ * kernel is issue-bound, 64 thread-instructions per pixel):
+ *
+ *  1. Blocks are SORTED BY COST before they are transformed.  A lane used to own the block of its MCU, so a warp paid
+ *     for the most expensive of its 32 blocks: every luma warp ran the full 64-coefficient butterfly, every chroma
+ *     warp the 16-coefficient one although 93 % of the chroma blocks of the benchmark images end before zigzag index
+ *     10.  Now a thread block takes a WINDOW of two tiles (192 blocks): phase A reads the meta words in natural order
+ *     (warp c = component c, lane = MCU: the DC prefix scan needs that order), classes every block by kmax
+ *     (< 10, < 28, the rest) and appends it to the class's queue in shared memory (warp-aggregated atomics); phase B
+ *     hands the concatenated queues out 32 at a time, so a warp gets blocks of one class and runs the butterfly pruned
+ *     for it (gjd_block_transform<10|28|64>: ~450 / ~690 / ~920 instructions).  The samples go to the block's own
+ *     place in shared memory, wherever it was transformed; the colour phase reads them in MCU order as before.
+ *  2. Two finished samples per packed operation at the end of the column pass, rows 0 and 4 handed over without shifts
+ *     (gjd_idct8x8_raw, gjd_pack_samples).
+ *  3. Colour conversion on 16-bit lanes, 8 pixels per call (gjd_color_row8): no per-pixel shift/add/clamp, and neutral
+ *     pixels (Cb = Cr = 0) no longer take the IEEE path — round 1's symmetric danger zone sent 8.7 % of the rows of
+ *     the benchmark images through it.
+ *  4. MCU coordinates advance incrementally (one division per thread block instead of one per tile).
+ * Shared memory: 24 KB of samples (two tiles, single-buffered: the barriers of the sort separate the phases anyway)
+ * + 1.5 KB of queues -> 8 blocks per SM.
+ */
+#define GJD_TW 2u                      /* tiles per sort window */
+#define GJD_WIN_BLOCKS (GJD_TW * 96u)
+#define GJD_CLS0_KLIM 10
+#define GJD_CLS1_KLIM 28
+
+/* dequantise + dezigzag + IDCT of one block whose coefficients all lie below zigzag index KLIM, samples parked at
+ * dst[r * 32] (r = row).  Lanes without a block (active = false) run along with kmax = 0 and store nothing. */
+template <int KLIM>
+__device__ __forceinline__ void gjd_block_transform(const uint4* __restrict__ src, uint32_t kmax, int dc,
+                                                    const uint32_t* __restrict__ qq, uint4* dst, bool active) {
+    constexpr int NCH = (KLIM + 7) / 8;            /* 16-byte chunks that can hold a coefficient below KLIM */
+    const uint32_t nchunk = kmax ? (kmax >> 3) + 1u : 0u;
+    uint32_t w[4 * NCH];
+#pragma unroll
+    for (int j = 0; j < NCH; j++) {
+        uint4 r = make_uint4(0u, 0u, 0u, 0u);
+        if ((uint32_t)j < nchunk) r = __ldcs(src + j);
+        w[4 * j] = r.x; w[4 * j + 1] = r.y; w[4 * j + 2] = r.z; w[4 * j + 3] = r.w;
+    }
+    int v[64];
+    GjdUnpack<63, KLIM>::run(w, qq, v);
+    v[0] = dc * (int)(qq[0] & 0xffu);
+    gjd_idct8x8_raw(v);
+    if (active) {
+#pragma unroll
+        for (int r = 0; r < 8; r++)
+            dst[r * 32] = make_uint4(gjd_pack_samples(v[8 * r + 1], v[8 * r]), gjd_pack_samples(v[8 * r + 3], v[8 * r + 2]),
+                                     gjd_pack_samples(v[8 * r + 5], v[8 * r + 4]), gjd_pack_samples(v[8 * r + 7], v[8 * r + 6]));
+    }
+}
+
+/* (bx, by) of an MCU `n` further on in raster order; block-uniform branch */
+__device__ __forceinline__ void gjd_mcu_advance(uint32_t& bx, uint32_t& by, uint32_t n, uint32_t mcus_x) {
+    bx += n;
+    if (mcus_x >= n) {
+        if (bx >= mcus_x) { bx -= mcus_x; by++; }
+    } else {
+        const uint32_t q = bx / mcus_x;
+        by += q;
+        bx -= q * mcus_x;
+    }
+}
+
+template <int MINB, bool ILV>
+__global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform2(GjdDevBatch b) {
+    __shared__ uint4 smp[GJD_TW][3][8][32];
+    __shared__ int s_dc[GJD_WIN_BLOCKS];           /* absolute DC of every block of the window, natural order */
+    __shared__ uint8_t s_km[GJD_WIN_BLOCKS];       /* its kmax */
+    __shared__ uint8_t s_q[3][GJD_WIN_BLOCKS];     /* per class: the blocks (natural index) in arrival order */
+    __shared__ uint32_t s_cnt[2][4];               /* queue lengths, double-buffered over the windows */
+
+    const uint32_t tid = threadIdx.x, c = tid >> 5, lane = tid & 31u;
+    const GjdImage& d = b.imgs[b.tb_img[blockIdx.x]];
+    if (d.gray) return;   /* k_transform_gray's */
+    const uint32_t ltb = blockIdx.x - d.tb_first;
+    if (tid < 8u) (&s_cnt[0][0])[tid] = 0u;
+    __syncthreads();
+
+    const uint32_t W = d.width, H = d.height, mcus_x = d.mcus_x;
+    uint8_t* out = d.out_is_ptr ? reinterpret_cast<uint8_t*>(d.out_off) : b.rgb + d.out_off;
+    const size_t pitch = d.row_pitch, pstride = d.plane_stride;
+    const bool interleaved = ILV && d.layout != GJD_LAYOUT_PLANAR;
+    const bool wide = ILV && d.layout == GJD_LAYOUT_INTERLEAVED_I16;      /* int16 elements: 6 bytes per pixel */
+    const bool aligned = (((size_t)out | pitch | (interleaved ? 0 : pstride)) & (wide ? 15u : 7u)) == 0;
+    const uint32_t bpp = interleaved ? (wide ? 6u : 3u) : 1u;
+    const GjdQuantSet& qs = b.quants[d.quant_id];
+    const uint4* coef4 = reinterpret_cast<const uint4*>(b.coef) + (size_t)d.tile_first * 96u * 8u;   /* the image's first line */
+    const uint32_t* meta_img = b.meta + (size_t)d.tile_first * 96u;
+    const int4* tilebase_img = b.tilebase + d.tile_first;
+
+    const uint32_t tile0 = ltb * b.tb_tiles;
+    const uint32_t tile_end = min(tile0 + b.tb_tiles, d.tile_count);
+    /* raster position of this lane's MCU in the first tile of the window */
+    uint32_t by0 = (tile0 * GJD_TILE_MCUS + lane) / mcus_x, bx0 = tile0 * GJD_TILE_MCUS + lane - by0 * mcus_x;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+
+#pragma unroll 1
+    for (uint32_t wt = tile0, win = 0; wt < tile_end; wt += GJD_TW, win++) {
+        const uint32_t nt = min(GJD_TW, tile_end - wt);
+        uint32_t* cnt = s_cnt[win & 1u];
+
+        /* ---- phase A: natural order.  DC prefix, class, queue ---- */
+        uint32_t cls_t[GJD_TW], in_t[GJD_TW], cm[GJD_TW][3];    /* per tile: class, has a block, ballot of every class */
+#pragma unroll
+        for (uint32_t t = 0; t < GJD_TW; t++) {
+            const uint32_t ltile = wt + t;
+            const bool tvalid = t < nt;
+            const uint32_t mcu = ltile * GJD_TILE_MCUS + lane;
+            const bool valid = tvalid && mcu < d.mcu_count;
+            const uint32_t lblk = ltile * 96u + lane * 3u + c;            /* block number inside the image */
+            if (ltile + GJD_TW < tile_end) {
+                /* the lines and meta words of the next window on their way to L2 while this one computes */
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(coef4 + (size_t)(lblk + GJD_WIN_BLOCKS) * 8u));
+                if (lane < 12u && c == 0u) asm volatile("prefetch.global.L2 [%0];" ::"l"(meta_img + (ltile + GJD_TW) * 96u + lane * 8u));
+            }
+            const uint32_t m = valid ? __ldg(meta_img + lblk) : 0u;
+            const uint32_t kmax = (m >> 16) & 63u;
+            int dc = warp_incl_scan_i((int)(int16_t)(m & 0xffffu), lane);
+            if (tvalid) {                                                   /* block-uniform */
+                const int4 tb = tilebase_img[ltile];
+                if (d.restart_interval == 0u) dc += c == 0u ? tb.x : c == 1u ? tb.y : tb.z;
+                else dc = gjd_restart_dc(tilebase_img, meta_img, d.restart_interval, ltile, mcu, c, lane, dc, tb);
+            }
+            s_dc[t * 96u + tid] = dc;
+            s_km[t * 96u + tid] = (uint8_t)kmax;
+            cls_t[t] = kmax < (uint32_t)GJD_CLS0_KLIM ? 0u : kmax < (uint32_t)GJD_CLS1_KLIM ? 1u : 2u;
+            in_t[t] = valid ? 1u : 0u;
+#pragma unroll
+            for (uint32_t k = 0; k < 3u; k++) cm[t][k] = __ballot_sync(0xffffffffu, valid && cls_t[t] == k);
+        }
+        {   /* one shared-memory atomic per warp and window: lane k reserves the warp's blocks of class k (both tiles) */
+            const uint32_t n0 = __popc(cm[0][0]) + __popc(cm[1][0]), n1 = __popc(cm[0][1]) + __popc(cm[1][1]),
+                           n2 = __popc(cm[0][2]) + __popc(cm[1][2]);
+            uint32_t base = 0;
+            if (lane < 3u) base = atomicAdd(&cnt[lane], lane == 0u ? n0 : lane == 1u ? n1 : n2);
+#pragma unroll
+            for (uint32_t t = 0; t < GJD_TW; t++) {
+                const uint32_t k = cls_t[t];
+                const uint32_t mine = k == 0u ? cm[t][0] : k == 1u ? cm[t][1] : cm[t][2];
+                const uint32_t before = t == 0u ? 0u : __popc(k == 0u ? cm[0][0] : k == 1u ? cm[0][1] : cm[0][2]);
+                const uint32_t at = __shfl_sync(0xffffffffu, base, k) + before + __popc(mine & lt_mask);
+                if (in_t[t]) s_q[k][at] = (uint8_t)(t * 96u + tid);
+            }
+        }
+        if (tid < 4u) s_cnt[(win + 1u) & 1u][tid] = 0u;    /* the next window's counters: idle since the barrier before last */
+        __syncthreads();
+
+        /* ---- phase B: the queues, cheapest class first, 32 blocks per warp and round ---- */
+        {
+            const uint32_t n0 = cnt[0], n1 = cnt[1], total = n0 + n1 + cnt[2];
+#pragma unroll 1
+            for (uint32_t r = 0; r < GJD_TW; r++) {
+                const uint32_t slot = r * 96u + tid;
+                const bool act = slot < total;
+                const uint32_t cls = slot < n0 ? 0u : slot < n0 + n1 ? 1u : 2u;
+                const uint32_t vmax = __reduce_max_sync(0xffffffffu, act ? cls + 1u : 0u);
+                if (vmax == 0u) continue;                                   /* warp-uniform: this warp has no block in this round */
+                const uint32_t item = act ? s_q[cls][slot - (cls == 0u ? 0u : cls == 1u ? n0 : n0 + n1)] : 0u;
+                const uint32_t t = item >= 96u ? 1u : 0u, ci = (item - t * 96u) >> 5, li = item & 31u;
+                const uint32_t kmax = act ? s_km[item] : 0u;
+                const int dc = s_dc[item];
+                const uint4* src = coef4 + (size_t)((wt + t) * 96u + li * 3u + ci) * 8u;
+                const uint32_t* q = qs.packed[ci];
+                uint4* dst = &smp[t][ci][0][li];
+                if (vmax == 1u) gjd_block_transform<GJD_CLS0_KLIM>(src, kmax, dc, q, dst, act);
+                else if (vmax == 2u) gjd_block_transform<GJD_CLS1_KLIM>(src, kmax, dc, q, dst, act);
+                else gjd_block_transform<64>(src, kmax, dc, q, dst, act);
+            }
+        }
+        __syncthreads();
+
+        /* ---- phase C: colour, in MCU order.  The window's 16 tile rows are dealt out as runs of consecutive rows of one
+         * tile: warp 0 rows 0-5 of tile 0, warp 1 rows 6-7 of tile 0 and 0-3 of tile 1, warp 2 rows 4-7 of tile 1 (in
+         * phase B warp 2 ends up with the most expensive class, so it gets the fewest rows) ---- */
+        {
+            uint32_t by1 = by0, bx1 = bx0;
+            gjd_mcu_advance(bx1, by1, GJD_TILE_MCUS, mcus_x);
+#pragma unroll 1
+            for (uint32_t seg = 0; seg < 2u; seg++) {
+                /* (tile, first row, one past the last row) of this warp's run number `seg`; empty runs have rb >= re */
+                const uint32_t t = c == 0u ? 0u : c == 1u ? seg : 1u;
+                const uint32_t rb = c == 0u ? (seg ? 8u : 0u) : c == 1u ? (seg ? 0u : 6u) : (seg ? 8u : 4u);
+                const uint32_t re = c == 0u ? (seg ? 8u : 6u) : c == 1u ? (seg ? 4u : 8u) : 8u;
+                if (rb >= re || t >= nt) continue;                          /* warp-uniform */
+                const uint32_t bx = t ? bx1 : bx0, by = t ? by1 : by0;
+                const uint32_t x0 = bx * 8u, y0 = by * 8u;
+                const bool mvalid = (wt + t) * GJD_TILE_MCUS + lane < d.mcu_count && y0 < H;
+                const uint32_t rows_left = mvalid ? H - y0 : 0u;            /* rows of this MCU that exist in the image */
+                const uint32_t r1 = min(re, rows_left);
+                const bool fast = aligned && (x0 + 8u <= W);
+                uint8_t* rowp = out + (size_t)(y0 + rb) * pitch + (size_t)x0 * bpp;
+                const uint4* sp = &smp[t][0][rb][lane];
+#pragma unroll 1
+                for (uint32_t r = rb; r < r1; r++, rowp += pitch, sp += 32) {
+                    const uint4 y4 = sp[0], b4 = sp[8 * 32], r4 = sp[16 * 32];
+                    const uint32_t yw[4] = {y4.x, y4.y, y4.z, y4.w}, bw[4] = {b4.x, b4.y, b4.z, b4.w}, rw[4] = {r4.x, r4.y, r4.z, r4.w};
+                    uint32_t pr[2], pg[2], pb[2];
+                    gjd_color_row8(yw, bw, rw, pr, pg, pb);
+                    if (ILV && wide) {       /* block-uniform: int16 R,G,B triples, 48 bytes per lane */
+                        gjd_store_row_i16(rowp, ((uint64_t)pr[1] << 32) | pr[0], ((uint64_t)pg[1] << 32) | pg[0], ((uint64_t)pb[1] << 32) | pb[0],
+                                          min(8u, W - x0), fast);
+                    } else if (ILV && interleaved) {   /* block-uniform: R,G,B,R,G,B,... 24 bytes per lane, 768 contiguous bytes per warp */
+                        if (fast) {
+                            /* word j of the 24 bytes: __byte_perm picks from {a: bytes 0-3, b: bytes 4-7} */
+                            const uint32_t w0 = __byte_perm(__byte_perm(pr[0], pg[0], 0x1040), pb[0], 0x3410);   /* R0 G0 B0 R1 */
+                            const uint32_t w1 = __byte_perm(__byte_perm(pg[0], pb[0], 0x2051), pr[0], 0x3610);   /* G1 B1 R2 G2 */
+                            const uint32_t w2 = __byte_perm(__byte_perm(pb[0], pr[0], 0x3072), pg[0], 0x3710);   /* B2 R3 G3 B3 */
+                            const uint32_t w3 = __byte_perm(__byte_perm(pr[1], pg[1], 0x1040), pb[1], 0x3410);
+                            const uint32_t w4 = __byte_perm(__byte_perm(pg[1], pb[1], 0x2051), pr[1], 0x3610);
+                            const uint32_t w5 = __byte_perm(__byte_perm(pb[1], pr[1], 0x3072), pg[1], 0x3710);
+                            __stcs(reinterpret_cast<uint2*>(rowp), make_uint2(w0, w1));
+                            __stcs(reinterpret_cast<uint2*>(rowp + 8), make_uint2(w2, w3));
+                            __stcs(reinterpret_cast<uint2*>(rowp + 16), make_uint2(w4, w5));
+                        } else {
+                            const uint64_t r8 = ((uint64_t)pr[1] << 32) | pr[0], g8 = ((uint64_t)pg[1] << 32) | pg[0], b8 = ((uint64_t)pb[1] << 32) | pb[0];
+#pragma unroll 1
+                            for (uint32_t x = 0; x < 8u && x0 + x < W; x++) {
+                                rowp[3u * x] = (uint8_t)(r8 >> (8u * x));
+                                rowp[3u * x + 1u] = (uint8_t)(g8 >> (8u * x));
+                                rowp[3u * x + 2u] = (uint8_t)(b8 >> (8u * x));
+                            }
+                        }
+                    } else if (fast) {
+                        __stcs(reinterpret_cast<uint2*>(rowp), make_uint2(pr[0], pr[1]));
+                        __stcs(reinterpret_cast<uint2*>(rowp + pstride), make_uint2(pg[0], pg[1]));
+                        __stcs(reinterpret_cast<uint2*>(rowp + 2 * pstride), make_uint2(pb[0], pb[1]));
+                    } else {
+                        const uint64_t r8 = ((uint64_t)pr[1] << 32) | pr[0], g8 = ((uint64_t)pg[1] << 32) | pg[0], b8 = ((uint64_t)pb[1] << 32) | pb[0];
+#pragma unroll 1
+                        for (uint32_t x = 0; x < 8u && x0 + x < W; x++) {
+                            rowp[x] = (uint8_t)(r8 >> (8u * x));
+                            rowp[pstride + x] = (uint8_t)(g8 >> (8u * x));
+                            rowp[2 * pstride + x] = (uint8_t)(b8 >> (8u * x));
+                        }
+                    }
+                }
+            }
+            gjd_mcu_advance(bx0, by0, GJD_TW * GJD_TILE_MCUS, mcus_x);
+        }
+    }
+}
+
 /* ------------------------------------------------------------------ transform: grayscale -- */
 /*
  * Single-component images (beyond the reference's parser, which wants three components).
@@ -1107,9 +1353,11 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     nvtxRangePop();
     if (ev) GJD_CK(cudaEventRecord(ev->e[3], s));
     nvtxRangePushA("gjd stage 3: dequant + IDCT + colour");
-    if (b.any_interleaved) k_transform<false, 8, true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
-    else if (transform_variant == 1) k_transform<false, GJD_TRANSFORM_MINB_ALT, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
-    else k_transform<false, GJD_TRANSFORM_MINB, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
+    if (transform_variant == 1) {   /* round 1's kernel, kept for A/B runs */
+        if (b.any_interleaved) k_transform<false, 8, true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
+        else k_transform<false, GJD_TRANSFORM_MINB, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
+    } else if (b.any_interleaved) k_transform2<8, true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b);
+    else k_transform2<8, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b);
     n++;
     if (b.any_gray) { k_transform_gray<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr); n++; }
     nvtxRangePop();

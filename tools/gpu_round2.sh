@@ -25,7 +25,7 @@ launches)
   timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/${tag}_launches.csv \
       python bench.py --steps 2 --warmup 1 --e2e-steps 1 --no-cpu-baseline > $out/${tag}_ncu_launch.log 2>&1; echo "launch list rc=$?" ;;
 ncu)
-  for k in k_transform k_huff_write k_huff_sync; do
+  for k in ${NCU_KERNELS:-k_transform k_huff_write k_huff_sync}; do
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:$k -s 1 -c 1 -f -o $out/${tag}_$k \
       env GJD_SUB_LOG2=12 python tools/profile_run.py 1000 2 > $out/${tag}_ncu_$k.log 2>&1; echo "ncu $k rc=$?"
   done ;;
@@ -40,6 +40,9 @@ san)
       -k "pixels_bit_exact_batch or restart_intervals_bit_exact or grayscale_bit_exact" \
       > $out/${tag}_sanitizer_racecheck_tests.txt 2>&1; echo "racecheck rc=$?" | tee -a $out/${tag}_sanitizer_racecheck_tests.txt
   tail -4 $out/${tag}_sanitizer_*.txt ;;
+ab)
+  # A/B of the two transform kernels on the resident c3 batch (round 1's k_transform = variant 1)
+  timeout 600 python tools/stage_bench.py 3000 10 0,1,0,1 > $out/${tag}_transform_ab.txt 2>&1; cat $out/${tag}_transform_ab.txt ;;
 micro)
   ./tools/microbench/pipes > $out/${tag}_pipes.txt 2>&1; cat $out/${tag}_pipes.txt ;;
 *) echo "unknown step $what" ;;
