@@ -752,18 +752,35 @@ GJD_HD void gjd_idct8x8(int v[64]) {
         gjd_idct_col(v[c], v[8 + c], v[16 + c], v[24 + c], v[32 + c], v[40 + c], v[48 + c], v[56 + c]);
 }
 
-/* The same with the shortcuts of gjd_idct_row_t<1,2> / gjd_idct_col_t<true>: v[] holds the 64 column-pass sums before
- * the final >> 14 and clip (natural order); gjd_pack_samples turns them into samples. */
-GJD_HD void gjd_idct8x8_raw(int v[64]) {
+/* The same with the shortcuts of gjd_idct_row_t<1,2> / gjd_idct_col_t<true>, in two steps so that k_transform2 can share one
+ * column pass between its classes: after both, v[] holds the 64 column-pass sums before the final >> 14 and clip (natural
+ * order); gjd_pack_samples turns them into samples. */
+GJD_HD void gjd_idct_rows_raw(int v[64]) {
     gjd_idct_row_t<1>(v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7]);
 #pragma unroll
     for (int r = 1; r < 8; r++) {
         if (r == 4) gjd_idct_row_t<2>(v[32], v[33], v[34], v[35], v[36], v[37], v[38], v[39]);
         else gjd_idct_row_t<0>(v[8 * r], v[8 * r + 1], v[8 * r + 2], v[8 * r + 3], v[8 * r + 4], v[8 * r + 5], v[8 * r + 6], v[8 * r + 7]);
     }
+}
+/* TOP4: rows 4-7 are known to be zero (no coefficient at or past zigzag index 10): their inputs are literal zeros here, so the
+ * butterflies that only see zeros fall away at compile time — same values as the general pass on the same data */
+template <bool TOP4>
+GJD_HD void gjd_idct_cols_raw(int v[64]) {
 #pragma unroll
-    for (int c = 0; c < 8; c++)
-        gjd_idct_col_t<true>(v[c], v[8 + c], v[16 + c], v[24 + c], v[32 + c], v[40 + c], v[48 + c], v[56 + c]);
+    for (int c = 0; c < 8; c++) {
+        if (TOP4) {
+            int z4 = 0, z5 = 0, z6 = 0, z7 = 0;
+            gjd_idct_col_t<true>(v[c], v[8 + c], v[16 + c], v[24 + c], z4, z5, z6, z7);
+            v[32 + c] = z4; v[40 + c] = z5; v[48 + c] = z6; v[56 + c] = z7;
+        } else {
+            gjd_idct_col_t<true>(v[c], v[8 + c], v[16 + c], v[24 + c], v[32 + c], v[40 + c], v[48 + c], v[56 + c]);
+        }
+    }
+}
+GJD_HD void gjd_idct8x8_raw(int v[64]) {
+    gjd_idct_rows_raw(v);
+    gjd_idct_cols_raw<false>(v);
 }
 
 /* ------------------------------------------------------------------ colour ------------ */

@@ -915,11 +915,12 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
 #define GJD_CLS0_KLIM 10
 #define GJD_CLS1_KLIM 28
 
-/* dequantise + dezigzag + IDCT of one block whose coefficients all lie below zigzag index KLIM, samples parked at
- * dst[r * 32] (r = row).  Lanes without a block (active = false) run along with kmax = 0 and store nothing. */
+/* First half of a block's transform: load the coefficient chunks that can hold a coefficient below zigzag index KLIM,
+ * dequantise + dezigzag (GjdUnpack), row pass.  One instantiation per class: the row pass prunes itself on the literal
+ * zeros.  Lanes without a block run along with kmax = 0. */
 template <int KLIM>
-__device__ __forceinline__ void gjd_block_transform(const uint4* __restrict__ src, uint32_t kmax, int dc,
-                                                    const uint32_t* __restrict__ qq, uint4* dst, bool active) {
+__device__ __forceinline__ void gjd_block_rows(const uint4* __restrict__ src, uint32_t kmax, int dc,
+                                               const uint32_t* __restrict__ qq, int v[64]) {
     constexpr int NCH = (KLIM + 7) / 8;            /* 16-byte chunks that can hold a coefficient below KLIM */
     const uint32_t nchunk = kmax ? (kmax >> 3) + 1u : 0u;
     uint32_t w[4 * NCH];
@@ -929,10 +930,13 @@ __device__ __forceinline__ void gjd_block_transform(const uint4* __restrict__ sr
         if ((uint32_t)j < nchunk) r = __ldcs(src + j);
         w[4 * j] = r.x; w[4 * j + 1] = r.y; w[4 * j + 2] = r.z; w[4 * j + 3] = r.w;
     }
-    int v[64];
     GjdUnpack<63, KLIM>::run(w, qq, v);
     v[0] = dc * (int)(qq[0] & 0xffu);
-    gjd_idct8x8_raw(v);
+    gjd_idct_rows_raw(v);
+}
+
+/* samples of a finished block, parked at dst[r * 32] (r = row) */
+__device__ __forceinline__ void gjd_block_park(const int v[64], uint4* dst, bool active) {
     if (active) {
 #pragma unroll
         for (int r = 0; r < 8; r++)
@@ -992,13 +996,11 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform2(GjdD
         uint32_t* cnt = s_cnt[win & 1u];
 
         /* ---- phase A: natural order.  DC prefix, class, queue ---- */
-        uint32_t cls_t[GJD_TW], in_t[GJD_TW], cm[GJD_TW][3];    /* per tile: class, has a block, ballot of every class */
-#pragma unroll
-        for (uint32_t t = 0; t < GJD_TW; t++) {
+#pragma unroll 1
+        for (uint32_t t = 0; t < nt; t++) {
             const uint32_t ltile = wt + t;
-            const bool tvalid = t < nt;
             const uint32_t mcu = ltile * GJD_TILE_MCUS + lane;
-            const bool valid = tvalid && mcu < d.mcu_count;
+            const bool valid = mcu < d.mcu_count;
             const uint32_t lblk = ltile * 96u + lane * 3u + c;            /* block number inside the image */
             if (ltile + GJD_TW < tile_end) {
                 /* the lines and meta words of the next window on their way to L2 while this one computes */
@@ -1008,31 +1010,20 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform2(GjdD
             const uint32_t m = valid ? __ldg(meta_img + lblk) : 0u;
             const uint32_t kmax = (m >> 16) & 63u;
             int dc = warp_incl_scan_i((int)(int16_t)(m & 0xffffu), lane);
-            if (tvalid) {                                                   /* block-uniform */
-                const int4 tb = tilebase_img[ltile];
-                if (d.restart_interval == 0u) dc += c == 0u ? tb.x : c == 1u ? tb.y : tb.z;
-                else dc = gjd_restart_dc(tilebase_img, meta_img, d.restart_interval, ltile, mcu, c, lane, dc, tb);
-            }
+            const int4 tb = tilebase_img[ltile];
+            if (d.restart_interval == 0u) dc += c == 0u ? tb.x : c == 1u ? tb.y : tb.z;
+            else dc = gjd_restart_dc(tilebase_img, meta_img, d.restart_interval, ltile, mcu, c, lane, dc, tb);
             s_dc[t * 96u + tid] = dc;
             s_km[t * 96u + tid] = (uint8_t)kmax;
-            cls_t[t] = kmax < (uint32_t)GJD_CLS0_KLIM ? 0u : kmax < (uint32_t)GJD_CLS1_KLIM ? 1u : 2u;
-            in_t[t] = valid ? 1u : 0u;
-#pragma unroll
-            for (uint32_t k = 0; k < 3u; k++) cm[t][k] = __ballot_sync(0xffffffffu, valid && cls_t[t] == k);
-        }
-        {   /* one shared-memory atomic per warp and window: lane k reserves the warp's blocks of class k (both tiles) */
-            const uint32_t n0 = __popc(cm[0][0]) + __popc(cm[1][0]), n1 = __popc(cm[0][1]) + __popc(cm[1][1]),
-                           n2 = __popc(cm[0][2]) + __popc(cm[1][2]);
+            const uint32_t cls = kmax < (uint32_t)GJD_CLS0_KLIM ? 0u : kmax < (uint32_t)GJD_CLS1_KLIM ? 1u : 2u;
+            const uint32_t m0 = __ballot_sync(0xffffffffu, valid && cls == 0u), m1 = __ballot_sync(0xffffffffu, valid && cls == 1u),
+                           m2 = __ballot_sync(0xffffffffu, valid && cls == 2u);
+            /* one shared-memory atomic per warp and tile: lane k reserves the warp's blocks of class k */
             uint32_t base = 0;
-            if (lane < 3u) base = atomicAdd(&cnt[lane], lane == 0u ? n0 : lane == 1u ? n1 : n2);
-#pragma unroll
-            for (uint32_t t = 0; t < GJD_TW; t++) {
-                const uint32_t k = cls_t[t];
-                const uint32_t mine = k == 0u ? cm[t][0] : k == 1u ? cm[t][1] : cm[t][2];
-                const uint32_t before = t == 0u ? 0u : __popc(k == 0u ? cm[0][0] : k == 1u ? cm[0][1] : cm[0][2]);
-                const uint32_t at = __shfl_sync(0xffffffffu, base, k) + before + __popc(mine & lt_mask);
-                if (in_t[t]) s_q[k][at] = (uint8_t)(t * 96u + tid);
-            }
+            if (lane < 3u) base = atomicAdd(&cnt[lane], __popc(lane == 0u ? m0 : lane == 1u ? m1 : m2));
+            const uint32_t mine = cls == 0u ? m0 : cls == 1u ? m1 : m2;
+            const uint32_t at = __shfl_sync(0xffffffffu, base, cls) + __popc(mine & lt_mask);
+            if (valid) s_q[cls][at] = (uint8_t)(t * 96u + tid);
         }
         if (tid < 4u) s_cnt[(win + 1u) & 1u][tid] = 0u;    /* the next window's counters: idle since the barrier before last */
         __syncthreads();
@@ -1054,9 +1045,18 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform2(GjdD
                 const uint4* src = coef4 + (size_t)((wt + t) * 96u + li * 3u + ci) * 8u;
                 const uint32_t* q = qs.packed[ci];
                 uint4* dst = &smp[t][ci][0][li];
-                if (vmax == 1u) gjd_block_transform<GJD_CLS0_KLIM>(src, kmax, dc, q, dst, act);
-                else if (vmax == 2u) gjd_block_transform<GJD_CLS1_KLIM>(src, kmax, dc, q, dst, act);
-                else gjd_block_transform<64>(src, kmax, dc, q, dst, act);
+                /* the row pass is per class; the two expensive classes share ONE column pass (code size: the instruction
+                 * cache holds 32 KB, r02d measured 2.2 stall cycles per issue on instruction fetch with three full copies) */
+                int v[64];
+                if (vmax == 1u) {
+                    gjd_block_rows<GJD_CLS0_KLIM>(src, kmax, dc, q, v);
+                    gjd_idct_cols_raw<true>(v);
+                } else {
+                    if (vmax == 2u) gjd_block_rows<GJD_CLS1_KLIM>(src, kmax, dc, q, v);
+                    else gjd_block_rows<64>(src, kmax, dc, q, v);
+                    gjd_idct_cols_raw<false>(v);
+                }
+                gjd_block_park(v, dst, act);
             }
         }
         __syncthreads();
