@@ -250,21 +250,92 @@ struct GjdWin {
     uint32_t wi, w0, w1, w2raw;
 };
 
-GJD_HD void gjd_win_init(GjdWin& c, const uint32_t* scan, uint32_t p) {
+/* Where the words of the scan come from.  The decoders are templates over the source: a plain pointer (global memory on
+ * the device, the test harness's buffer on the host), or GjdScanRing, the TMA-staged variant of the A/B build
+ * -DGJD_SCAN_TMA=1 (profiles/r02_tma_scan_ab.txt). */
+GJD_HD uint32_t gjd_scan_word(const uint32_t*& scan, uint32_t i) { return scan[i]; }
+
+#if defined(__CUDACC__) && defined(GJD_SCAN_TMA)
+/* Per-thread double-buffered ring in shared memory, filled by 1-D TMA bulk copies (cp.async.bulk ... mbarrier::
+ * complete_tx::bytes; SASS UBLKCP) of GJD_RING_CHUNK bytes: BASELINE.json's "compressed scans staged into shared memory by
+ * TMA bulk copies".  Every thread walks its own subsequence, so every thread owns two chunks and two mbarriers; the copy
+ * of chunk c+1 is issued when the reader enters chunk c (the words of chunk c-1 are all in registers by then: GjdWin
+ * holds three), so it has a whole chunk's worth of symbols to land. */
+#ifndef GJD_RING_CHUNK
+#define GJD_RING_CHUNK 32u
+#endif
+struct GjdScanRing {
+    const uint8_t* arena;     /* scan arena (256-byte aligned) */
+    uint64_t base;            /* byte offset of the segment's first scan byte in the arena (4-byte aligned) */
+    uint32_t slots;           /* shared address of this thread's two chunks (slot s at slots + s * GJD_RING_CHUNK * blockDim.x) */
+    uint32_t bars;            /* shared address of this thread's two mbarriers (8 bytes each, adjacent) */
+    uint32_t stride;          /* bytes between the two slots */
+    uint32_t cur;             /* chunk the reader is in (arena byte offset / GJD_RING_CHUNK), 0xffffffff = none */
+    uint32_t phase;           /* bit s = parity the next wait on slot s uses */
+    uint32_t inflight;        /* bit s = a copy into slot s has been issued and not waited for */
+    __device__ __forceinline__ void issue(uint32_t chunk) {
+        const uint32_t s = chunk & 1u;
+        const uint32_t bar = bars + 8u * s, dst = slots + s * stride;
+        const uint8_t* src = arena + (uint64_t)chunk * GJD_RING_CHUNK;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(GJD_RING_CHUNK) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(dst), "l"(src), "r"(GJD_RING_CHUNK), "r"(bar) : "memory");
+        inflight |= 1u << s;
+    }
+    __device__ __forceinline__ void wait(uint32_t s) {
+        const uint32_t bar = bars + 8u * s, par = (phase >> s) & 1u;
+        uint32_t done;
+        do {
+            asm volatile("{.reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p;}"
+                         : "=r"(done) : "r"(bar), "r"(par) : "memory");
+        } while (!done);
+        phase ^= 1u << s;
+        inflight &= ~(1u << s);
+    }
+    __device__ __forceinline__ uint32_t word(uint32_t i) {
+        const uint64_t a = base + 4ull * i;
+        const uint32_t chunk = (uint32_t)(a / GJD_RING_CHUNK);
+        if (chunk != cur) {
+            if (chunk != cur + 1u || !((inflight >> (chunk & 1u)) & 1u)) {
+                /* a jump (start of a span): drain what is in flight, fetch this chunk */
+                if (inflight & 1u) wait(0u);
+                if (inflight & 2u) wait(1u);
+                issue(chunk);
+            }
+            wait(chunk & 1u);
+            cur = chunk;
+            issue(chunk + 1u);
+        }
+        uint32_t v;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(slots + (chunk & 1u) * stride + (uint32_t)(a % GJD_RING_CHUNK)));
+        return v;
+    }
+    /* leave nothing in flight (before the thread block's shared memory goes away) */
+    __device__ __forceinline__ void drain() {
+        if (inflight & 1u) wait(0u);
+        if (inflight & 2u) wait(1u);
+    }
+};
+__device__ __forceinline__ uint32_t gjd_scan_word(GjdScanRing& r, uint32_t i) { return r.word(i); }
+#endif
+
+template <class Src>
+GJD_HD void gjd_win_init(GjdWin& c, Src& scan, uint32_t p) {
     c.wi = p >> 5;
-    c.w0 = gjd_bswap32(scan[c.wi]);
-    c.w1 = gjd_bswap32(scan[c.wi + 1]);
-    c.w2raw = scan[c.wi + 2];
+    c.w0 = gjd_bswap32(gjd_scan_word(scan, c.wi));
+    c.w1 = gjd_bswap32(gjd_scan_word(scan, c.wi + 1));
+    c.w2raw = gjd_scan_word(scan, c.wi + 2);
 }
 
 /* 32 bits of the scan starting at bit p (MSB first).  p may advance by at most 32 bits per call.
  * Reads up to 12 bytes past the word that holds p (the scan arena is padded). */
-GJD_HD uint32_t gjd_peek32(GjdWin& c, const uint32_t* scan, uint32_t p) {
+template <class Src>
+GJD_HD uint32_t gjd_peek32(GjdWin& c, Src& scan, uint32_t p) {
     uint32_t wi = p >> 5;
     if (wi != c.wi) {
         c.w0 = c.w1;
         c.w1 = gjd_bswap32(c.w2raw);
-        c.w2raw = scan[wi + 2];
+        c.w2raw = gjd_scan_word(scan, wi + 2);
         c.wi = wi;
     }
 #ifdef __CUDA_ARCH__
@@ -375,8 +446,8 @@ GJD_HD uint32_t gjd_ring_next(uint32_t tb, uint32_t z, uint32_t zn) {
  * scan_bits is padding and is not counted.
  * Follows JPEGParser::buildMCU (cpp-decoder/src/parser.cpp:105-134): DC size/diff; AC run/size with
  * EOB = 0x00, "length += run", value bits always consumed, coefficient kept only if index < 64. */
-template <class Lut>
-GJD_HD void gjd_count_span(const uint32_t* scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
+template <class Src, class Lut>
+GJD_HD void gjd_count_span(Src& scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
                            GjdState& s) {
     if (s.p >= end_bits) return;
     GjdWin win;
@@ -415,8 +486,8 @@ GJD_HD_COLD uint32_t gjd_lookup_canonical(const GjdLutSet* lut, uint32_t tb, uin
  *   - when a pair would complete the block, the first symbol is checked alone: if it already completes the
  *     block (a coefficient at index 63, or garbage), the second symbol belongs to the next block's DC table
  *     and the pair is dropped. */
-template <class Lut>
-GJD_HD void gjd_count_span_pairs(const uint32_t* scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
+template <class Src, class Lut>
+GJD_HD void gjd_count_span_pairs(Src& scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
                                  GjdState& s) {
     if (s.p >= end_bits) return;
     GjdWin win;
@@ -482,8 +553,8 @@ GJD_HD void gjd_count_span_pairs(const uint32_t* scan, const Lut& lut, uint32_t 
  * lanes of a warp stay converged: ALL 32 lanes call this (enable = false for lanes without a
  * subsequence).  Same buildMCU semantics as gjd_count_span (cpp-decoder/src/parser.cpp:105-134).
  */
-template <class Lut, class Sink>
-GJD_HD void gjd_write_span(const uint32_t* scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
+template <class Src, class Lut, class Sink>
+GJD_HD void gjd_write_span(Src& scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
                            GjdState s, uint32_t idx0, uint32_t nblocks, bool enable, Sink& sink, uint32_t& bad) {
     uint32_t run = (enable && s.p < end_bits) ? 1u : 0u;
     GjdWin win;

@@ -82,6 +82,26 @@ __device__ __forceinline__ void copy_lut_to_smem(GjdLutSet* dst, const GjdLutSet
     for (uint32_t i = threadIdx.x; i < bytes / 16; i += blockDim.x) d[i] = __ldg(s + i);
 }
 
+#ifdef GJD_SCAN_TMA
+/* A/B build: the entropy kernels read the scan through per-thread TMA rings (GjdScanRing, gjd_devfn.cuh) */
+#define GJD_RING_BYTES_PER_BLOCK (2u * GJD_SEQ_SUBS * GJD_RING_CHUNK)
+__device__ __forceinline__ GjdScanRing gjd_ring_setup(uint8_t* ring, uint64_t* bars, const uint8_t* arena, uint64_t seg_off) {
+    GjdScanRing r;
+    r.arena = arena;
+    r.base = seg_off;
+    r.slots = (uint32_t)__cvta_generic_to_shared(ring + threadIdx.x * GJD_RING_CHUNK);
+    r.stride = GJD_SEQ_SUBS * GJD_RING_CHUNK;
+    r.bars = (uint32_t)__cvta_generic_to_shared(bars + 2u * threadIdx.x);
+    r.cur = 0xffffffffu;
+    r.phase = 0u;
+    r.inflight = 0u;
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(r.bars));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(r.bars + 8u));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    return r;
+}
+#endif
+
 /* ------------------------------------------------------------------ tables and maps --- */
 
 __global__ void __launch_bounds__(256) k_build_luts(const GjdDhtSet* __restrict__ dht, GjdLutSet* __restrict__ luts,
@@ -288,7 +308,13 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS, 8) k_huff_sync(GjdDevBatch b
     const uint32_t sub = ls * GJD_SEQ_SUBS + tid;
     const uint32_t sub_count = d.sub_count, scan_bits = d.scan_bits;
     const uint32_t S = 1u << b.sub_log2;
+#ifdef GJD_SCAN_TMA
+    __shared__ __align__(128) uint8_t ring[GJD_RING_BYTES_PER_BLOCK];
+    __shared__ uint64_t ring_bars[2 * GJD_SEQ_SUBS];
+    GjdScanRing scan = gjd_ring_setup(ring, ring_bars, b.scan, d.scan_off);
+#else
     const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
+#endif
     copy_count_lut_to_smem(&lut, b.luts + d.lut_id, b.lutc + d.lut_id);
     const GjdLutSmem slut(&lut);
     __syncthreads();
@@ -330,6 +356,9 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS, 8) k_huff_sync(GjdDevBatch b
         }
     }
     if (active) b.sinfo[(size_t)g * GJD_SEQ_SUBS + tid] = make_uint2(sp[tid], sn[tid]);
+#ifdef GJD_SCAN_TMA
+    scan.drain();
+#endif
 }
 
 /*
@@ -471,7 +500,11 @@ struct GjdWriteSink {
 #define GJD_WRITE_LUT_BYTES sizeof(GjdLutSet)
 #define GJD_WRITE_MINB 4
 #endif
+#ifdef GJD_SCAN_TMA
+#define GJD_WRITE_SMEM (GJD_WRITE_LUT_BYTES + 8u * GJD_WRITE_THREADS * sizeof(uint4) + 2u * GJD_SEQ_SUBS * GJD_RING_CHUNK + 16u * GJD_SEQ_SUBS)
+#else
 #define GJD_WRITE_SMEM (GJD_WRITE_LUT_BYTES + 8u * GJD_WRITE_THREADS * sizeof(uint4))   /* dynamic: > 48 KB with the whole set */
+#endif
 __global__ void __launch_bounds__(GJD_WRITE_THREADS, GJD_WRITE_MINB) k_huff_write(GjdDevBatch b) {
     extern __shared__ uint4 dyn_smem[];
     static_assert(GJD_WRITE_LUT_BYTES % 16 == 0 && GJD_WRITE_LUT_BYTES <= sizeof(GjdLutSet), "LUT part of the set");
@@ -485,7 +518,12 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, GJD_WRITE_MINB) k_huff_writ
     const uint32_t ls = g - d.seq_first;
     const uint32_t sub = ls * GJD_SEQ_SUBS + tid;
     const uint32_t scan_bits = d.scan_bits;
+#ifdef GJD_SCAN_TMA
+    uint8_t* ring = reinterpret_cast<uint8_t*>(dyn_smem) + GJD_WRITE_LUT_BYTES + 8u * GJD_WRITE_THREADS * sizeof(uint4);
+    GjdScanRing scan = gjd_ring_setup(ring, reinterpret_cast<uint64_t*>(ring + GJD_RING_BYTES_PER_BLOCK), b.scan, d.scan_off);
+#else
     const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
+#endif
     const bool active = sub < d.sub_count;
     const uint2* si = b.sinfo + (size_t)g * GJD_SEQ_SUBS;
     copy_lut_to_smem(&lut, b.luts + d.lut_id, GJD_WRITE_LUT_BYTES);
@@ -516,6 +554,9 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, GJD_WRITE_MINB) k_huff_writ
     if (active && idx0 % 192u != st.pos && st.p < scan_bits) bad |= GJD_DEV_BADSTATE;
     uint32_t end = min((sub + 1) << b.sub_log2, scan_bits);
     gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad);
+#ifdef GJD_SCAN_TMA
+    scan.drain();
+#endif
     if (bad) atomicOr(b.status + img, bad);
     __syncthreads();
     if (tid == 0 && badcode) atomicOr(b.status + img, GJD_DEV_BADCODE);
@@ -809,36 +850,11 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
         for (uint32_t r = r0; r < r1; r++, rowp += pitch) {
             const uint4 y4 = smp[t & 1u][0][r][lane], b4 = smp[t & 1u][1][r][lane], r4 = smp[t & 1u][2][r][lane];
             const uint32_t yw[4] = {y4.x, y4.y, y4.z, y4.w}, bw[4] = {b4.x, b4.y, b4.z, b4.w}, rw[4] = {r4.x, r4.y, r4.z, r4.w};
-            /* saturation and byte packing of two pixels in one I2IP (gjd_pack_sat_u8); the danger test of
-             * the 8 pixels is one unsigned min over the fraction fields */
-            int vr[8], vg[8], vb[8];
-            uint32_t fmin = 0xffffffffu;
-#pragma unroll
-            for (int x = 0; x < 8; x++) {
-                const int sh = (x & 1) * 16;
-                fmin = min(fmin, gjd_color_fast_raw((int)((yw[x >> 1] >> sh) & 0xffffu), (int)((bw[x >> 1] >> sh) & 0xffffu),
-                                                    (int)((rw[x >> 1] >> sh) & 0xffffu), vr[x], vg[x], vb[x]));
-            }
+            /* 8 pixels on 16-bit lanes (gjd_color_row8): R/B in 2^-16, G in 2^-32 fixed point with the one-sided danger zone —
+             * round 1's symmetric zone sent every neutral pixel (Cb = Cr = 0) through the IEEE sequence */
             uint32_t pr[2], pg[2], pb[2];
-#pragma unroll
-            for (int h = 0; h < 2; h++) {
-                pr[h] = gjd_pack_sat_u8(vr[4 * h + 1], vr[4 * h], gjd_pack_sat_u8(vr[4 * h + 3], vr[4 * h + 2], 0u));
-                pg[h] = gjd_pack_sat_u8(vg[4 * h + 1], vg[4 * h], gjd_pack_sat_u8(vg[4 * h + 3], vg[4 * h + 2], 0u));
-                pb[h] = gjd_pack_sat_u8(vb[4 * h + 1], vb[4 * h], gjd_pack_sat_u8(vb[4 * h + 3], vb[4 * h + 2], 0u));
-            }
-            uint64_t g8 = ((uint64_t)pg[1] << 32) | pg[0];
-            if (fmin < GJD_FRAC_DANGER) {   /* rare: G of the flagged pixels again with the reference's IEEE sequence */
-                const uint16_t* ys = reinterpret_cast<const uint16_t*>(&smp[t & 1u][0][r][lane]);
-                const uint16_t* bs = reinterpret_cast<const uint16_t*>(&smp[t & 1u][1][r][lane]);
-                const uint16_t* rs = reinterpret_cast<const uint16_t*>(&smp[t & 1u][2][r][lane]);
-#pragma unroll 1
-                for (uint32_t x = 0; x < 8u; x++) {
-                    int R, G, B;
-                    if (gjd_color_fast_frac((int)ys[x], (int)bs[x], (int)rs[x], R, G, B) >= GJD_FRAC_DANGER) continue;
-                    const uint64_t Ge = (uint64_t)gjd_color_g_exact((int)ys[x] - 256, (int)bs[x] - 256, (int)rs[x] - 256);
-                    g8 = (g8 & ~(0xffull << (8u * x))) | (Ge << (8u * x));
-                }
-            }
+            gjd_color_row8(yw, bw, rw, pr, pg, pb);
+            const uint64_t g8 = ((uint64_t)pg[1] << 32) | pg[0];
             if (wide) {          /* block-uniform: int16 R,G,B triples, 48 bytes per lane */
                 gjd_store_row_i16(rowp, ((uint64_t)pr[1] << 32) | pr[0], g8, ((uint64_t)pb[1] << 32) | pb[0], min(8u, W - x0), fast);
                 continue;
