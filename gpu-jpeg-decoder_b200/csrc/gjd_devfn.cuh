@@ -964,53 +964,29 @@ GJD_HD void gjd_color(int yb, int cbb, int crb, int& R, int& G, int& B) {
 }
 
 /* ------------------------------------------------------------------ colour, 8 pixels of a row at a time ----------
- * What k_transform runs (the scalar gjd_color above stays as the per-pixel statement of the same function).
+ * What the transform kernels run (the scalar gjd_color above stays as the per-pixel statement of the same function).
  * Samples arrive as the IDCT parks them: two biased 9-bit samples per word (x odd in the high half).
  *   R, B   2^-16 fixed point: hi16(Cr' * KR16 + CR16) = floor(1.402 Cr) - 128 for every Cr' = Cr + 256 in [0,511]
- *          (all 512 values checked against the 2^-20 form above, tests/test_hostsim.py), so the two high halves of
- *          two pixels are ONE byte permute away from a packed pair that a single VIADDMNMX.S16x2.RELU adds to the
- *          packed Y pair and clamps to [0,255].
- *   G      2^-32 fixed point in 64 bits: the offset's integer part is the high word, no shift; the fraction is the low
- *          word.  At this precision (|error| < 2^-23) the fast value can differ from the reference's float sequence
- *          only when the exact rational lies within 12/587000 BELOW an integer (4 of the 2^18 (Cb,Cr) pairs; 12 of the
- *          2^27 triples really differ) — those re-run the reference's IEEE sequence (gjd_color_g_exact).  Exact integers
- *          (Cb = Cr = 0: every neutral pixel) are not in that zone, unlike the symmetric zone of the 2^-20 form.
- *          0.299*1.402/0.587 * 2^32 does not fit a signed 32-bit multiplier: -c*Cr' = -Cr' + (1 - c)*Cr', and the
- *          -Cr' goes into the packed Y pair (one IADD3 for two pixels).
+ *          (all 512 values equal the 2^-20 form above), so the two high halves of two pixels are ONE byte permute away
+ *          from a packed pair that a single VIADDMNMX.S16x2.RELU adds to the packed Y pair and clamps to [0,255]: no
+ *          per-pixel shift, add or clamp, and Y is never unpacked.
+ *   G      the 2^-20 fixed point of gjd_color_fast_raw (two IMADs per pixel), its integer parts packed the same way; the
+ *          fractions' unsigned minimum over the row flags the danger zone.  A flagged row re-runs the reference's IEEE
+ *          sequence (gjd_color_g_exact) for its flagged pixels — EXCEPT neutral ones (Cb = Cr = 0): their exact G is the
+ *          integer Y + 128 the fast path already gives, and they sit in the middle of the zone by construction, so round 1
+ *          sent every gray pixel through the double-precision divide.
+ *   A 2^-32 form of G in 64 bits (no shifts, a one-sided zone that excludes the integers) was measured and is slower: the
+ *   kernels are bound by the ALU pipe, and the 64-bit carries are ALU instructions (profiles/r02f_transform_ab.txt).
  * Proven against cpp-decoder/utils/color.cpp:3-18 for all 2^27 triples on the CPU (tests/test_hostsim.py::
- * test_colour_exhaustive) and on the GPU (tests/test_gpu_parity.py::test_colour_exhaustive_on_device). */
+ * test_colour_exhaustive_packed_rows) and on the GPU (tests/test_gpu_parity.py::test_colour_exhaustive_on_device). */
 #define GJD_KR16 91881
 #define GJD_CR16 (-31910037)
 #define GJD_KB16 116130
 #define GJD_CB16 (-38117862)
-#define GJD_GA32 1478054095ll          /* round(0.114*1.772/0.587 * 2^32)                          */
-#define GJD_GC32 3067191994ll          /* round(0.299*1.402/0.587 * 2^32)                          */
-#define GJD_GC32P 1227775302ll         /* 2^32 - GJD_GC32                                           */
-#define GJD_G_DELTA 859ll              /* keeps exact integers (and values above them) on the right side of floor() */
-#define GJD_G_ZONE 94489u              /* 2.2e-5 * 2^32: fraction >= 2^32 - ZONE -> re-run the IEEE sequence */
-/* constant term: -128 (level shift relative to the +256 bias of Y), the +256 bias of both chroma samples, and -512 for
- * the (+512 - Cr') that rides in the packed Y pair */
-#define GJD_G_C64 (256ll * (GJD_GA32 + GJD_GC32) - (128ll << 32) + GJD_G_DELTA - (512ll << 32))
-#define GJD_G_DANGER (0u - GJD_G_ZONE)
-
-/* the G offset of one pixel: high word = floor(-a*Cb - c*Cr) - 128 + Cr' - 512, low word = the fraction.
- * (mad.wide.s32 by hand: from the C expression the compiler makes an unsigned product plus a correction of the high
- * word, three instructions more per pixel.) */
-GJD_HD long long gjd_color_g64(uint32_t cbb, uint32_t crb) {
-#ifdef __CUDA_ARCH__
-    long long t;
-    asm("{.reg .s64 u; mad.wide.s32 u, %1, %3, %5; mad.wide.s32 %0, %2, %4, u;}"
-        : "=l"(t) : "r"(cbb), "r"(crb), "n"((int)(-GJD_GA32)), "n"((int)GJD_GC32P), "l"(GJD_G_C64));
-    return t;
-#else
-    long long t = (long long)(int)cbb * (-GJD_GA32) + GJD_G_C64;
-    return t + (long long)(int)crb * GJD_GC32P;
-#endif
-}
 
 /* yw, bw, rw: four words each = the 8 samples of one row of Y, Cb, Cr.  r, g, b: two words each = 8 clamped bytes. */
 GJD_HD void gjd_color_row8(const uint32_t yw[4], const uint32_t bw[4], const uint32_t rw[4], uint32_t r[2], uint32_t g[2], uint32_t b[2]) {
-    uint32_t r2[4], g2[4], b2[4], fmax = 0;
+    uint32_t r2[4], g2[4], b2[4], fmin = 0xffffffffu;
 #ifdef __CUDACC__
 #pragma unroll
 #endif
@@ -1020,21 +996,23 @@ GJD_HD void gjd_color_row8(const uint32_t yw[4], const uint32_t bw[4], const uin
         const uint32_t tb0 = cb0 * (uint32_t)GJD_KB16 + (uint32_t)GJD_CB16, tb1 = cb1 * (uint32_t)GJD_KB16 + (uint32_t)GJD_CB16;
         r2[j] = gjd_viaddmin_s16x2_relu(gjd_prmt(tr0, tr1, 0x7632u), yw[j], 0x00ff00ffu);
         b2[j] = gjd_viaddmin_s16x2_relu(gjd_prmt(tb0, tb1, 0x7632u), yw[j], 0x00ff00ffu);
-        const long long t0 = gjd_color_g64(cb0, cr0), t1 = gjd_color_g64(cb1, cr1);
-        const uint32_t ywr = yw[j] + 0x02000200u - rw[j];      /* per half: Y' + 512 - Cr' in [1,1023]: no borrow between the halves */
-        g2[j] = gjd_viaddmin_s16x2_relu(gjd_prmt((uint32_t)(t0 >> 32), (uint32_t)(t1 >> 32), 0x5410u), ywr, 0x00ff00ffu);
-        const uint32_t f0 = (uint32_t)t0, f1 = (uint32_t)t1;
-        fmax = fmax > f0 ? fmax : f0;
-        fmax = fmax > f1 ? fmax : f1;
+        int tg0 = (int)cr0 * (-GJD_KGR) + GJD_CONST_G, tg1 = (int)cr1 * (-GJD_KGR) + GJD_CONST_G;
+        tg0 = (int)cb0 * (-GJD_KGB) + tg0;
+        tg1 = (int)cb1 * (-GJD_KGB) + tg1;
+        g2[j] = gjd_viaddmin_s16x2_relu(gjd_prmt((uint32_t)(tg0 >> 20), (uint32_t)(tg1 >> 20), 0x5410u), yw[j], 0x00ff00ffu);
+        const uint32_t f0 = (uint32_t)tg0 * 4096u, f1 = (uint32_t)tg1 * 4096u;
+        fmin = fmin < f0 ? fmin : f0;
+        fmin = fmin < f1 ? fmin : f1;
     }
-    if (fmax >= GJD_G_DANGER) {          /* rare (4 chroma pairs): G of the flagged pixels from the reference's IEEE sequence */
+    if (fmin < GJD_FRAC_DANGER) {        /* some pixel's G is within 2^-14 of an integer */
 #ifdef __CUDACC__
 #pragma unroll
 #endif
         for (int x = 0; x < 8; x++) {    /* (unrolled: run-time indices would push the arrays into local memory) */
             const int sh = (x & 1) * 16;
             const uint32_t cbb = (bw[x >> 1] >> sh) & 0xffffu, crb = (rw[x >> 1] >> sh) & 0xffffu;
-            if ((uint32_t)gjd_color_g64(cbb, crb) >= GJD_G_DANGER) {
+            const uint32_t f = (uint32_t)((int)crb * (-GJD_KGR) + (int)cbb * (-GJD_KGB) + GJD_CONST_G) * 4096u;
+            if (f < GJD_FRAC_DANGER && (cbb != 256u || crb != 256u)) {
                 const uint32_t yb = (yw[x >> 1] >> sh) & 0xffffu;
                 const uint32_t G = (uint32_t)gjd_color_g_exact((int)yb - 256, (int)cbb - 256, (int)crb - 256);
                 g2[x >> 1] = (g2[x >> 1] & ~(0xffffu << sh)) | (G << sh);
