@@ -904,9 +904,12 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
 
 /* ------------------------------------------------------------------ transform, round 2 -- */
 /*
- * k_transform2 — the shipped transform (k_transform above stays as GJD_TRANSFORM_VARIANT=1 for A/B runs and as the
- * coefficient export of gjd_decode_coeffs).  Same result, fewer instructions (profiles/r02a_k_transform.*: the round-1
- * kernel is issue-bound, 64 thread-instructions per pixel):
+ * k_transform2 — GJD_TRANSFORM_VARIANT=2, a measured alternative to k_transform above (which ships).  Same result, 8 % fewer
+ * instructions, and slower: 7.32 ms against 7.07 ms on C3 (profiles/r02g_transform_ab.txt).  Both kernels are bound by the
+ * ALU pipe (70 % of its peak at 68-76 % issue-active, profiles/r02e_k_transform2.summary.txt), and what the sort saves are
+ * mostly IMADs of pruned butterflies (FMA pipe), while its queue bookkeeping, votes and selects are ALU instructions.
+ * Kept because it is the variant that wins once the shifts and clamps stop dominating (e.g. low-quality images whose
+ * blocks end before zigzag index 10).  What it does differently:
  *
  *  1. Blocks are SORTED BY COST before they are transformed.  A lane used to own the block of its MCU, so a warp paid
  *     for the most expensive of its 32 blocks: every luma warp ran the full 64-coefficient butterfly, every chroma
@@ -1369,11 +1372,11 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     nvtxRangePop();
     if (ev) GJD_CK(cudaEventRecord(ev->e[3], s));
     nvtxRangePushA("gjd stage 3: dequant + IDCT + colour");
-    if (transform_variant == 1) {   /* round 1's kernel, kept for A/B runs */
-        if (b.any_interleaved) k_transform<false, 8, true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
-        else k_transform<false, GJD_TRANSFORM_MINB, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
-    } else if (b.any_interleaved) k_transform2<8, true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b);
-    else k_transform2<8, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b);
+    if (transform_variant == 2) {   /* the cost-sorted kernel (measured: 7.32 ms against 7.07 ms on C3, profiles/r02g_transform_ab.txt) */
+        if (b.any_interleaved) k_transform2<8, true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b);
+        else k_transform2<8, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b);
+    } else if (b.any_interleaved) k_transform<false, 8, true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
+    else k_transform<false, GJD_TRANSFORM_MINB, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
     n++;
     if (b.any_gray) { k_transform_gray<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr); n++; }
     nvtxRangePop();

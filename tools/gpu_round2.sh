@@ -41,8 +41,8 @@ san)
       > $out/${tag}_sanitizer_racecheck_tests.txt 2>&1; echo "racecheck rc=$?" | tee -a $out/${tag}_sanitizer_racecheck_tests.txt
   tail -4 $out/${tag}_sanitizer_*.txt ;;
 ab)
-  # A/B of the two transform kernels on the resident c3 batch (round 1's k_transform = variant 1)
-  timeout 600 python tools/stage_bench.py 3000 10 0,1,0,1 > $out/${tag}_transform_ab.txt 2>&1; cat $out/${tag}_transform_ab.txt ;;
+  # A/B of the two transform kernels on the resident c3 batch (0 = k_transform, 2 = the cost-sorted k_transform2)
+  timeout 600 python tools/stage_bench.py 3000 10 ${AB_VARIANTS:-0,2,0,2} > $out/${tag}_transform_ab.txt 2>&1; cat $out/${tag}_transform_ab.txt ;;
 micro)
   ./tools/microbench/pipes > $out/${tag}_pipes.txt 2>&1; cat $out/${tag}_pipes.txt ;;
 *) echo "unknown step $what" ;;
