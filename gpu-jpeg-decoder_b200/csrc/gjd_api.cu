@@ -201,7 +201,7 @@ struct gjd_batch {
     std::vector<GjdQuantSet> quants;
     std::vector<GjdRaw> raws;        /* scans unstuffed on the device */
     PinBuf h_scan, h_raw, h_meta, h_status;
-    DevBuf d_raw, d_uchunk, d_rawmeta, d_ustatus;
+    DevBuf d_raw, d_uchunk, d_rawmeta, d_ustatus, d_dcabs;
     DevBuf d_scan, d_meta, d_luts, d_lutc, d_sinfo, d_seqmaps, d_coef, d_blkmeta, d_tilebase, d_tileimg, d_tbimg, d_rgb, d_status;
     GjdDevBatch view{};
     GjdStageEvents ev{};
@@ -214,7 +214,7 @@ struct gjd_batch {
 
     void release() {
         h_scan.release(); h_raw.release(); h_meta.release(); h_status.release();
-        for (DevBuf* d : {&d_raw, &d_uchunk, &d_rawmeta, &d_ustatus, &d_scan, &d_meta, &d_luts, &d_lutc, &d_sinfo, &d_seqmaps, &d_coef, &d_blkmeta, &d_tilebase, &d_tileimg,
+        for (DevBuf* d : {&d_raw, &d_uchunk, &d_rawmeta, &d_ustatus, &d_dcabs, &d_scan, &d_meta, &d_luts, &d_lutc, &d_sinfo, &d_seqmaps, &d_coef, &d_blkmeta, &d_tilebase, &d_tileimg,
                           &d_tbimg, &d_rgb, &d_status})
             d->release(stream);
         if (ev_ok) for (auto& e : ev.e) cudaEventDestroy(e);
@@ -265,8 +265,8 @@ uint64_t fnv1a(const void* p, size_t n) {
 
 /* Estimated device bytes one image needs (scan + sinfo + coefficient lines + block meta + rgb). */
 size_t estimate_bytes(const gjd_item& it, const ItemGeom& g) {
-    size_t pw = align_up((size_t)g.width, 8), ph = align_up((size_t)g.height, 8);
-    return pw * ph * 6 + pw * ph / 4 + g.out_bytes + it.len * 4 + 65536;
+    size_t pw = align_up((size_t)g.width, 16), ph = align_up((size_t)g.height, 16);
+    return pw * ph * 6 + pw * ph / 8 + pw * ph / 4 + g.out_bytes + it.len * 4 + 65536;
 }
 
 /*
@@ -373,8 +373,9 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         uint64_t tiles = 0;
         for (int32_t i = 0; i < n; i++) {
             if (b->geom[i].status != GJD_OK) continue;
-            const uint64_t mc = (uint64_t)((b->geom[i].width + 7) / 8) * (uint64_t)((b->geom[i].height + 7) / 8);
-            tiles += (mc * (parsed[i].components == 1 ? 1u : 3u) + 95u) / 96u;
+            const uint32_t mw = 8u * parsed[i].hs, mh = 8u * parsed[i].vs;
+            const uint64_t mc = (uint64_t)((b->geom[i].width + mw - 1) / mw) * (uint64_t)((b->geom[i].height + mh - 1) / mh);
+            tiles += (mc * (parsed[i].components == 1 ? 1u : parsed[i].hs * parsed[i].vs + 2u) + 95u) / 96u;
         }
         while (tb_tiles > 4u && tiles / tb_tiles < 4u * 148u * 8u) tb_tiles >>= 1;
     }
@@ -391,18 +392,21 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         const GjdParsed& p = parsed[i];
         if ((uint64_t)ulen[i] * 8 >= 0xffff0000ull) { g.status = GJD_E_UNSUPPORTED; continue; }
         {   /* coefficient slot indices (sinfo counts, seq_base, the write pass's idx0) are 32-bit */
-            const uint64_t mc = (uint64_t)((g.width + 7) / 8) * (uint64_t)((g.height + 7) / 8);
-            if (mc * (p.components == 1 ? 1u : 3u) * 64u >= 0xffffffffull) { g.status = GJD_E_UNSUPPORTED; continue; }
+            const uint32_t mw = 8u * p.hs, mh = 8u * p.vs;
+            const uint64_t mc = (uint64_t)((g.width + mw - 1) / mw) * (uint64_t)((g.height + mh - 1) / mh);
+            if (mc * (p.components == 1 ? 1u : p.hs * p.vs + 2u) * 64u >= 0xffffffffull) { g.status = GJD_E_UNSUPPORTED; continue; }
         }
         GjdImage d;
         memset(&d, 0, sizeof(d));
         d.width = (uint32_t)g.width;
         d.height = (uint32_t)g.height;
-        d.mcus_x = (d.width + 7) / 8;
-        d.mcu_count = d.mcus_x * ((d.height + 7) / 8);
-        d.tile_first = tile;
         d.gray = p.components == 1 ? 1u : 0u;
-        const uint32_t bpm = d.gray ? 1u : 3u;                       /* 8x8 blocks per MCU */
+        d.hs = (uint8_t)(d.gray ? 1u : p.hs);
+        d.vs = (uint8_t)(d.gray ? 1u : p.vs);
+        d.mcus_x = (d.width + 8u * d.hs - 1u) / (8u * d.hs);
+        d.mcu_count = d.mcus_x * ((d.height + 8u * d.vs - 1u) / (8u * d.vs));
+        d.tile_first = tile;
+        const uint32_t bpm = d.gray ? 1u : (uint32_t)d.hs * d.vs + 2u;   /* 8x8 blocks per MCU */
         d.tile_count = (d.mcu_count * bpm + 95u) / 96u;              /* a tile is 96 coefficient lines */
         d.tb_first = tb;
         d.tb_count = (d.tile_count + tb_tiles - 1) / tb_tiles;
@@ -480,6 +484,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
             sg.blk_first = bpm * mcu0;
             sg.blk_count = bpm * (p.restart_interval ? std::min(p.restart_interval, d.mcu_count - mcu0) : d.mcu_count);
             sg.lut_id = lut_id;
+            sg.ny = (uint8_t)(d.gray ? 1u : (uint32_t)d.hs * d.vs);
             if (mode[i]) {
                 GjdRaw r;
                 memset(&r, 0, sizeof(r));
@@ -502,7 +507,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         b->img_of[i] = (int32_t)b->imgs.size();
         b->imgs.push_back(d);
         b->pixels += (uint64_t)d.width * d.height;
-        b->padded_pixels += (uint64_t)d.mcu_count * 64;   /* per component plane */
+        b->padded_pixels += (uint64_t)d.mcu_count * 64 * d.hs * d.vs;   /* per full-resolution plane */
         b->scan_bytes += (uint64_t)ulen[i];
     }
     b->rgb_alloc = rgb_off;
@@ -515,6 +520,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     for (const GjdImage& im : b->imgs) {
         v.any_interleaved |= im.layout != GJD_LAYOUT_PLANAR;
         v.any_gray |= im.gray;
+        v.any_sub |= (uint32_t)im.hs * im.vs > 1u;
     }
     v.n_seq = seq;
     v.sub_log2 = sub_log2;
@@ -548,6 +554,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     GJD_TRY(b->d_blkmeta.ensure((size_t)tile * 96 * sizeof(uint32_t), b->stream));
     GJD_TRY(b->d_tilebase.ensure((size_t)tile * sizeof(int4), b->stream));
     GJD_TRY(b->d_tileimg.ensure((size_t)tile * sizeof(uint32_t), b->stream));
+    if (v.any_sub) GJD_TRY(b->d_dcabs.ensure((size_t)tile * 96 * sizeof(int), b->stream));
     GJD_TRY(b->d_rgb.ensure(std::max<size_t>(b->rgb_alloc, 256), b->stream));
     GJD_TRY(b->d_status.ensure((size_t)(n_img + 1) * sizeof(uint32_t), b->stream));
     GJD_TRY(b->d_ustatus.ensure((size_t)(n_img + 1) * sizeof(uint32_t), b->stream));
@@ -580,6 +587,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     v.meta = (uint32_t*)b->d_blkmeta.p;
     v.tilebase = (int4*)b->d_tilebase.p;
     v.tile_img = (uint32_t*)b->d_tileimg.p;
+    v.dcabs = (int*)b->d_dcabs.p;
     v.rgb = (uint8_t*)b->d_rgb.p;
     v.status = (uint32_t*)b->d_status.p;
     v.nosync = (uint32_t*)b->d_status.p + n_img;
@@ -715,7 +723,7 @@ const char* gjd_strerror(int st) {
         case GJD_E_CUDA: return "CUDA runtime error";
         case GJD_E_NOMEM: return "out of memory";
         case GJD_E_FORMAT: return "not a JPEG or malformed/truncated marker segment";
-        case GJD_E_UNSUPPORTED: return "JPEG outside the 8-bit 4:4:4 baseline single-scan contract";
+        case GJD_E_UNSUPPORTED: return "JPEG outside the 8-bit baseline single-scan contract (4:4:4, 4:2:2, 4:4:0, 4:2:0 or grayscale)";
         case GJD_E_CORRUPT: return "corrupt entropy-coded data";
         case GJD_E_NODEVICE: return "no usable CUDA device (libgjd has no CPU decode path)";
         case GJD_E_IO: return "file I/O error";
@@ -1025,7 +1033,7 @@ int gjd_decode_coeffs(gjd_ctx* ctx, const uint8_t* jpg, size_t len, int16_t* coe
     if (rc == GJD_OK) rc = gjd_batch_sync(ctx, b);
     if (rc == GJD_OK || rc == GJD_E_CORRUPT) {
         int rc0 = rc;
-        size_t ncoef = (size_t)b->imgs[0].mcu_count * (b->imgs[0].gray ? 64 : 192);
+        size_t ncoef = (size_t)b->imgs[0].mcu_count * (b->imgs[0].gray ? 64 : ((size_t)b->imgs[0].hs * b->imgs[0].vs + 2) * 64);
         DevBuf tmp;
         cudaError_t e = tmp.ensure(ncoef * sizeof(int16_t), b->stream);
         if (e == cudaSuccess) e = gjd_launch_export_coefs(b->view, (int16_t*)tmp.p, b->stream);

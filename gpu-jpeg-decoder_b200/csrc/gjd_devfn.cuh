@@ -348,12 +348,15 @@ GJD_HD uint32_t gjd_peek32(GjdWin& c, Src& scan, uint32_t p) {
 
 /* ------------------------------------------------------------------ entropy decode ---- */
 
-/* Decoder state between symbols as stored in sinfo: p = bit position in the image's unstuffed scan,
- * n = coefficient slots advanced so far, pos = comp*64 + zigzag index (0..191) of the next slot.
+/* Decoder state between symbols as stored in sinfo ({p, n << GJD_POS_BITS | pos}): p = bit position in the image's unstuffed
+ * scan, n = coefficient slots advanced so far, pos = block-in-MCU * 64 + zigzag index of the next slot (0..191 for
+ * 4:4:4, where the block in the MCU is the component; up to 383 for 4:2:0).
  * This is the (p, n, c, z) state of the reference's decodeSequence (cuda-decoder/src/parser.cu:50-121). */
 struct GjdState {
     uint32_t p, n, pos;
 };
+#define GJD_POS_BITS 9u
+#define GJD_POS_MASK 511u
 
 /* Inside the loops the state is (p, q, tb): q = slot counter with q & 63 = zigzag index (starts at
  * pos, never wraps), tb = byte offset of the current table in the LUT ring. */
@@ -442,17 +445,51 @@ GJD_HD uint32_t gjd_ring_next(uint32_t tb, uint32_t z, uint32_t zn) {
     return tb;
 }
 
+/* How the table ring moves from block to block.  The decoders are templates over it.
+ *   GjdRing444  one block of every component per MCU (4:4:4; also single-component scans, whose one table pair fills all
+ *               three ring positions): DC -> AC -> next component's DC, the stepping above.  Stateless.
+ *   GjdRingSub  chroma-subsampled scans (T.81 A.2.3): an MCU is ny = H*V luma blocks, then Cb, then Cr.  The ring
+ *               still holds six tables; after a luma block the ring goes BACK to the luma DC table while luma blocks of
+ *               the MCU remain (yl counts them).  pos = block-in-MCU * 64 + zigzag index, up to (ny + 2) * 64 - 1.
+ * Only whole blocks change anything, so the per-symbol path of the 4:4:4 decoders is untouched by the second one. */
+struct GjdRing444 {
+    GJD_HD uint32_t of_pos(uint32_t pos) { return gjd_ring_of_pos(pos); }
+    GJD_HD uint32_t next(uint32_t tb, uint32_t z, uint32_t zn) { return gjd_ring_next(tb, z, zn); }
+    GJD_HD uint32_t slots() const { return 192u; }
+};
+struct GjdRingSub {
+    uint32_t ny, yl;
+    GJD_HD explicit GjdRingSub(uint32_t ny_) : ny(ny_), yl(0) {}
+    GJD_HD uint32_t of_pos(uint32_t pos) {
+        const uint32_t bp = pos >> 6;
+        const uint32_t comp = bp < ny ? 0u : bp - ny + 1u;
+        yl = bp < ny ? ny - 1u - bp : 0u;
+        return (comp * 2u + ((pos & 63u) ? 1u : 0u)) * GJD_RING_STRIDE;
+    }
+    GJD_HD uint32_t next(uint32_t tb, uint32_t z, uint32_t zn) {
+        if (zn >= 64u) {                                    /* block complete */
+            if (tb <= GJD_RING_STRIDE && yl != 0u) { yl--; return 0u; }   /* another luma block of this MCU */
+            tb = (tb | GJD_RING_STRIDE) + GJD_RING_STRIDE;  /* the next component's DC table (a block that ends on its DC symbol
+                                                               cannot happen: a DC symbol advances one slot) */
+            if (tb == GJD_RING_BYTES) { tb = 0u; yl = ny - 1u; }
+            return tb;
+        }
+        return z == 0u ? tb + GJD_RING_STRIDE : tb;
+    }
+    GJD_HD uint32_t slots() const { return (ny + 2u) * 64u; }
+};
+
 /* Decode symbols that START before end_bits, beginning at state s.  A symbol that would run past
  * scan_bits is padding and is not counted.
  * Follows JPEGParser::buildMCU (cpp-decoder/src/parser.cpp:105-134): DC size/diff; AC run/size with
  * EOB = 0x00, "length += run", value bits always consumed, coefficient kept only if index < 64. */
-template <class Src, class Lut>
+template <class Src, class Lut, class Ring = GjdRing444>
 GJD_HD void gjd_count_span(Src& scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
-                           GjdState& s) {
+                           GjdState& s, Ring ring = Ring()) {
     if (s.p >= end_bits) return;
     GjdWin win;
     gjd_win_init(win, scan, s.p);
-    uint32_t p = s.p, z = s.pos & 63u, tb = gjd_ring_of_pos(s.pos), nb = 0;
+    uint32_t p = s.p, z = s.pos & 63u, tb = ring.of_pos(s.pos), nb = 0;
     while (p < end_bits) {
         GJD_DBG_SYM();
         const uint32_t w = gjd_peek32(win, scan, p);
@@ -461,14 +498,14 @@ GJD_HD void gjd_count_span(Src& scan, const Lut& lut, uint32_t end_bits, uint32_
         if (pn > scan_bits) break;
         p = pn;
         const uint32_t zn = z + (e >> 9);
-        tb = gjd_ring_next(tb, z, zn);
+        tb = ring.next(tb, z, zn);
         z = zn;
         if (zn >= 64u) { z = 0u; nb++; }
     }
     const uint32_t adv = nb * 64u + z - (s.pos & 63u);      /* slots advanced (mod 2^32 arithmetic is exact) */
     s.p = p;
     s.n += adv;
-    s.pos = (s.pos + adv) % 192u;
+    s.pos = (s.pos + adv) % ring.slots();
 }
 
 /* Any single symbol from the canonical tables alone (code lengths 1..16): what gjd_lookup returns, without
@@ -486,13 +523,13 @@ GJD_HD_COLD uint32_t gjd_lookup_canonical(const GjdLutSet* lut, uint32_t tb, uin
  *   - when a pair would complete the block, the first symbol is checked alone: if it already completes the
  *     block (a coefficient at index 63, or garbage), the second symbol belongs to the next block's DC table
  *     and the pair is dropped. */
-template <class Src, class Lut>
+template <class Src, class Lut, class Ring = GjdRing444>
 GJD_HD void gjd_count_span_pairs(Src& scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
-                                 GjdState& s) {
+                                 GjdState& s, Ring ring = Ring()) {
     if (s.p >= end_bits) return;
     GjdWin win;
     gjd_win_init(win, scan, s.p);
-    uint32_t p = s.p, z = s.pos & 63u, tb = gjd_ring_of_pos(s.pos), nb = 0;
+    uint32_t p = s.p, z = s.pos & 63u, tb = ring.of_pos(s.pos), nb = 0;
     while (p + (uint32_t)GJD_LUT_BITS <= end_bits) {
         GJD_DBG_SYM();
         const uint32_t w = gjd_peek32(win, scan, p);
@@ -512,7 +549,7 @@ GJD_HD void gjd_count_span_pairs(Src& scan, const Lut& lut, uint32_t end_bits, u
             zn = z + (e1 >> 9);
         }
         p = pn;
-        tb = gjd_ring_next(tb, z, zn);
+        tb = ring.next(tb, z, zn);
         z = zn;
         if (zn >= 64u) { z = 0u; nb++; }
     }
@@ -524,14 +561,14 @@ GJD_HD void gjd_count_span_pairs(Src& scan, const Lut& lut, uint32_t end_bits, u
         if (pn > scan_bits) break;
         p = pn;
         const uint32_t zn = z + (e >> 9);
-        tb = gjd_ring_next(tb, z, zn);
+        tb = ring.next(tb, z, zn);
         z = zn;
         if (zn >= 64u) { z = 0u; nb++; }
     }
     const uint32_t adv = nb * 64u + z - (s.pos & 63u);
     s.p = p;
     s.n += adv;
-    s.pos = (s.pos + adv) % 192u;
+    s.pos = (s.pos + adv) % ring.slots();
 }
 
 /* Warp-wide "any lane still running": keeps the 32 lanes of a warp in one converged loop on the GPU
@@ -553,14 +590,14 @@ GJD_HD void gjd_count_span_pairs(Src& scan, const Lut& lut, uint32_t end_bits, u
  * lanes of a warp stay converged: ALL 32 lanes call this (enable = false for lanes without a
  * subsequence).  Same buildMCU semantics as gjd_count_span (cpp-decoder/src/parser.cpp:105-134).
  */
-template <class Src, class Lut, class Sink>
+template <class Src, class Lut, class Sink, class Ring = GjdRing444>
 GJD_HD void gjd_write_span(Src& scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
-                           GjdState s, uint32_t idx0, uint32_t nblocks, bool enable, Sink& sink, uint32_t& bad) {
+                           GjdState s, uint32_t idx0, uint32_t nblocks, bool enable, Sink& sink, uint32_t& bad, Ring ring = Ring()) {
     uint32_t run = (enable && s.p < end_bits) ? 1u : 0u;
     GjdWin win;
     win.wi = 0; win.w0 = 0; win.w1 = 0; win.w2raw = 0;
     if (run) gjd_win_init(win, scan, s.p);
-    uint32_t p = s.p, z = s.pos & 63u, tb = gjd_ring_of_pos(s.pos);
+    uint32_t p = s.p, z = s.pos & 63u, tb = ring.of_pos(s.pos);
     uint32_t blk = (idx0 + 63u) >> 6;
 
     /* phase A: the tail of a block that belongs to the previous thread */
@@ -575,7 +612,7 @@ GJD_HD void gjd_write_span(Src& scan, const Lut& lut, uint32_t end_bits, uint32_
             } else {
                 p = pn;
                 const uint32_t zn = z + (e >> 9);
-                tb = gjd_ring_next(tb, z, zn);
+                tb = ring.next(tb, z, zn);
                 z = zn >= 64u ? 0u : zn;
                 if (z == 0u) skip = 0u;
             }
@@ -612,7 +649,7 @@ GJD_HD void gjd_write_span(Src& scan, const Lut& lut, uint32_t end_bits, uint32_
                     const int v = gjd_extend(w, total - size, size);
                     if (z == 0u) dcdiff = v;
                     else if (size != 0u && zn <= 64u) { sink.store(zn - 1u, v); kmax = zn - 1u; }
-                    tb = gjd_ring_next(tb, z, zn);
+                    tb = ring.next(tb, z, zn);
                     z = zn;
                     if (zn >= 64u) {
                         z = 0u;

@@ -322,39 +322,43 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS, 8) k_huff_sync(GjdDevBatch b
     const bool active = sub < sub_count;
     const uint32_t start = sub << b.sub_log2;
     const uint32_t end = active ? min(start + S, scan_bits) : 0u;
-    GjdState st;
-    st.p = 0; st.n = 0; st.pos = 0;
-    uint32_t in_p = 0, in_pos = 0;
-    if (active) {
-        if (sub != 0u) {
-            st.p = start > GJD_LOOKBACK_BITS ? start - GJD_LOOKBACK_BITS : 0u;
-            gjd_count_span_pairs(scan, slut, start, scan_bits, st);
+    /* the same code for both MCU shapes (block-uniform choice): 4:4:4 / single-component, or ny luma blocks + Cb + Cr */
+    auto body = [&](auto ring) {
+        GjdState st;
+        st.p = 0; st.n = 0; st.pos = 0;
+        uint32_t in_p = 0, in_pos = 0;
+        if (active) {
+            if (sub != 0u) {
+                st.p = start > GJD_LOOKBACK_BITS ? start - GJD_LOOKBACK_BITS : 0u;
+                gjd_count_span_pairs(scan, slut, start, scan_bits, st, ring);
+            }
+            in_p = st.p; in_pos = st.pos;
+            st.n = 0;
+            gjd_count_span_pairs(scan, slut, end, scan_bits, st, ring);
         }
-        in_p = st.p; in_pos = st.pos;
-        st.n = 0;
-        gjd_count_span_pairs(scan, slut, end, scan_bits, st);
-    }
-    sp[tid] = st.p;
-    sn[tid] = (st.n << 8) | st.pos;
-    if (tid == 0 && ls != 0u) b.seq_in[g] = make_uint2(in_p, in_pos);
+        sp[tid] = st.p;
+        sn[tid] = (st.n << GJD_POS_BITS) | st.pos;
+        if (tid == 0 && ls != 0u) b.seq_in[g] = make_uint2(in_p, in_pos);
 
-    for (uint32_t r = 0; r < GJD_SEQ_SUBS; r++) {
-        __syncthreads();
-        bool bad = false;
-        if (active && tid != 0u) {
-            const uint32_t pp = sp[tid - 1], ppos = sn[tid - 1] & 255u;
-            bad = pp != in_p || ppos != in_pos;
+        for (uint32_t r = 0; r < GJD_SEQ_SUBS; r++) {
+            __syncthreads();
+            bool bad = false;
+            if (active && tid != 0u) {
+                const uint32_t pp = sp[tid - 1], ppos = sn[tid - 1] & GJD_POS_MASK;
+                bad = pp != in_p || ppos != in_pos;
+                if (bad) {
+                    st.p = in_p = pp; st.pos = in_pos = ppos; st.n = 0;
+                    gjd_count_span_pairs(scan, slut, end, scan_bits, st, ring);
+                }
+            }
+            if (!__syncthreads_or(bad)) break;
             if (bad) {
-                st.p = in_p = pp; st.pos = in_pos = ppos; st.n = 0;
-                gjd_count_span_pairs(scan, slut, end, scan_bits, st);
+                sp[tid] = st.p;
+                sn[tid] = (st.n << GJD_POS_BITS) | st.pos;
             }
         }
-        if (!__syncthreads_or(bad)) break;
-        if (bad) {
-            sp[tid] = st.p;
-            sn[tid] = (st.n << 8) | st.pos;
-        }
-    }
+    };
+    if (d.ny > 1u) body(GjdRingSub(d.ny)); else body(GjdRing444());
     if (active) b.sinfo[(size_t)g * GJD_SEQ_SUBS + tid] = make_uint2(sp[tid], sn[tid]);
 #ifdef GJD_SCAN_TMA
     scan.drain();
@@ -376,8 +380,8 @@ __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
     uint2* si = b.sinfo + (size_t)g * GJD_SEQ_SUBS;
     const uint2 prev = si[-1];
     const uint2 ein = b.seq_in[g];
-    if (prev.x == ein.x && (prev.y & 255u) == ein.y) return;
-    b.seq_in[g] = make_uint2(prev.x, prev.y & 255u);
+    if (prev.x == ein.x && (prev.y & GJD_POS_MASK) == ein.y) return;
+    b.seq_in[g] = make_uint2(prev.x, prev.y & GJD_POS_MASK);
     const uint32_t* scan = reinterpret_cast<const uint32_t*>(b.scan + d.scan_off);
     GjdLutMem glut;
     glut.set = b.luts + d.lut_id;
@@ -385,17 +389,18 @@ __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
     const uint32_t scan_bits = d.scan_bits;
     GjdState st;
     st.p = prev.x;
-    st.pos = prev.y & 255u;
+    st.pos = prev.y & GJD_POS_MASK;
     bool merged = false;
     for (uint32_t t = 0; t < GJD_SEQ_SUBS; t++) {
         uint32_t sub = ls * GJD_SEQ_SUBS + t;
         if (sub >= d.sub_count) { merged = true; break; }
         st.n = 0;
         uint32_t end = min((sub + 1) << b.sub_log2, scan_bits);
-        gjd_count_span(scan, glut, end, scan_bits, st);
+        if (d.ny > 1u) gjd_count_span(scan, glut, end, scan_bits, st, GjdRingSub(d.ny));
+        else gjd_count_span(scan, glut, end, scan_bits, st);
         uint2 old = si[t];
-        si[t] = make_uint2(st.p, (st.n << 8) | st.pos);
-        if (old.x == st.p && (old.y & 255u) == st.pos) { merged = true; break; }
+        si[t] = make_uint2(st.p, (st.n << GJD_POS_BITS) | st.pos);
+        if (old.x == st.p && (old.y & GJD_POS_MASK) == st.pos) { merged = true; break; }
     }
     if (!merged && ls + 1 < d.seq_count) {
         atomicAdd(b.nosync, 1u);
@@ -424,7 +429,7 @@ __global__ void __launch_bounds__(256) k_seq_scan(GjdDevBatch b) {
              * sequences can be empty) */
             const uint32_t cnt = s * GJD_SEQ_SUBS < d.sub_count ? min(GJD_SEQ_SUBS, d.sub_count - s * GJD_SEQ_SUBS) : 0u;
             uint32_t t = 0;
-            for (uint32_t k = lane; k < cnt; k += 32u) t += si[k].y >> 8;
+            for (uint32_t k = lane; k < cnt; k += 32u) t += si[k].y >> GJD_POS_BITS;
             t = __reduce_add_sync(0xffffffffu, t);
             if (lane == 0) tot_s[i] = t;
         }
@@ -532,7 +537,7 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, GJD_WRITE_MINB) k_huff_writ
 #pragma unroll
     for (int j = 0; j < 8; j++) buf[j][tid] = make_uint4(0u, 0u, 0u, 0u);
 
-    uint32_t n = active ? (si[tid].y >> 8) : 0u;
+    uint32_t n = active ? (si[tid].y >> GJD_POS_BITS) : 0u;
     uint32_t blocksum;
     uint32_t excl = block_excl_scan_256(n, ws, &blocksum);   /* has the __syncthreads the LUT copy needs */
 
@@ -541,7 +546,7 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, GJD_WRITE_MINB) k_huff_writ
     if (active && sub != 0u) {
         uint2 prev = si[(int)tid - 1];
         st.p = prev.x;
-        st.pos = prev.y & 255u;
+        st.pos = prev.y & GJD_POS_MASK;
     }
     uint32_t bad = 0;
     GjdWriteSink sink;
@@ -551,9 +556,11 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, GJD_WRITE_MINB) k_huff_writ
     const size_t first = blk0 + ((idx0 + 63u) >> 6);          /* the first block this thread owns */
     sink.dst = reinterpret_cast<uint4*>(b.coef) + first * 8u;
     sink.mp = b.meta + first;
-    if (active && idx0 % 192u != st.pos && st.p < scan_bits) bad |= GJD_DEV_BADSTATE;
+    const uint32_t mcu_slots = ((uint32_t)d.ny + 2u) * 64u;       /* coefficient slots per MCU: 192 for 4:4:4 and single-component scans */
+    if (active && idx0 % mcu_slots != st.pos && st.p < scan_bits) bad |= GJD_DEV_BADSTATE;
     uint32_t end = min((sub + 1) << b.sub_log2, scan_bits);
-    gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad);
+    if (d.ny > 1u) gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad, GjdRingSub(d.ny));   /* block-uniform */
+    else gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad);
 #ifdef GJD_SCAN_TMA
     scan.drain();
 #endif
@@ -772,7 +779,7 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
 
     const uint32_t tid = threadIdx.x, c = tid >> 5, lane = tid & 31u;
     const GjdImage& d = b.imgs[b.tb_img[blockIdx.x]];
-    if (d.gray) return;   /* k_transform_gray's */
+    if (d.gray || (uint32_t)d.hs * d.vs > 1u) return;   /* k_transform_gray's / k_transform_sub's */
     const uint32_t ltb = blockIdx.x - d.tb_first;
     {
         const int* qg = reinterpret_cast<const int*>(b.quants + d.quant_id);
@@ -986,7 +993,7 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform2(GjdD
 
     const uint32_t tid = threadIdx.x, c = tid >> 5, lane = tid & 31u;
     const GjdImage& d = b.imgs[b.tb_img[blockIdx.x]];
-    if (d.gray) return;   /* k_transform_gray's */
+    if (d.gray || (uint32_t)d.hs * d.vs > 1u) return;   /* k_transform_gray's / k_transform_sub's */
     const uint32_t ltb = blockIdx.x - d.tb_first;
     if (tid < 8u) (&s_cnt[0][0])[tid] = 0u;
     __syncthreads();
@@ -1274,6 +1281,151 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_gray(Gjd
     }
 }
 
+/* ------------------------------------------------------------------ chroma-subsampled images -- */
+/*
+ * 4:2:2, 4:4:0 and 4:2:0 (what data_preprocessing/image_converter.py:14-19 exists to avoid; the reference's
+ * parser ignores the sampling factors and garbles such files).  An MCU is hs*vs luma blocks (row-major inside the MCU),
+ * then Cb, then Cr (T.81 A.2.3); the entropy kernels run unchanged apart from the ring stepper (GjdRingSub) and write one
+ * 128-byte coefficient line per block in scan order, so line = mcu * (hs*vs + 2) + block-in-MCU.  Two more kernels:
+ *   k_dc_sub         one block per segment (restart interval, or the whole scan): the three DC chains — luma blocks in
+ *                    scan order, Cb, Cr — by block-wide scans, absolute DC of every line -> dcabs
+ *   k_transform_sub  one thread per line: dequantise, dezigzag, IDCT (the same gjd_idct8x8 as everything else), samples
+ *                    parked in shared memory; then 8-pixel row pieces: luma sample + the chroma sample that covers it
+ *                    (sample replication, i.e. libjpeg's h2v1 / h2v2 "non-fancy" upsampling), the reference's colour
+ *                    formula (gjd_color), 8-byte stores.
+ * Pin (no reference output exists): coefficients against jpeg_read_coefficients of the reference's vendored libjpeg 9e,
+ * pixels against the oracle's IDCT + replication + the oracle's colour function (tools/make_golden_sub.py).
+ * Correct first: these kernels are not tuned.
+ */
+__global__ void __launch_bounds__(256) k_dc_sub(GjdDevBatch b, int* __restrict__ dcabs) {
+    __shared__ uint32_t ws[8];
+    const GjdSegment& sg = b.segs[blockIdx.x];
+    const GjdImage& d = b.imgs[sg.img];
+    const uint32_t ny = (uint32_t)d.hs * d.vs;
+    if (d.gray || ny == 1u) return;
+    const uint32_t nblk = ny + 2u, tid = threadIdx.x;
+    const size_t line0 = (size_t)d.tile_first * 96u;
+    int pred[3] = {0, 0, 0};                                /* T.81 E.1.4: the predictors restart with the interval */
+    for (uint32_t base = 0; base < sg.blk_count; base += 256u) {
+        const uint32_t j = sg.blk_first + base + tid;       /* line inside the image */
+        const bool valid = base + tid < sg.blk_count;
+        const uint32_t bp = j % nblk, c = bp < ny ? 0u : bp - ny + 1u;
+        const int diff = valid ? (int)(int16_t)(__ldg(b.meta + line0 + j) & 0xffffu) : 0;
+        int mine = 0;
+#pragma unroll
+        for (uint32_t k = 0; k < 3u; k++) {
+            uint32_t total;
+            const uint32_t v = c == k ? (uint32_t)diff : 0u;
+            const uint32_t excl = block_excl_scan_256(v, ws, &total);
+            if (c == k) mine = pred[k] + (int)(excl + v);
+            pred[k] += (int)total;
+        }
+        if (valid) dcabs[line0 + j] = mine;
+    }
+}
+
+template <bool EXPORT>
+__global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_sub(GjdDevBatch b, const int* __restrict__ dcabs,
+                                                                             int16_t* __restrict__ coef_out) {
+    __shared__ uint16_t smp[96][64];                        /* samples (biased, 9 bits) of the tile's 96 blocks */
+    const uint32_t tid = threadIdx.x;
+    const GjdImage& d = b.imgs[b.tb_img[blockIdx.x]];
+    const uint32_t hs = d.hs, vs = d.vs, ny = hs * vs;
+    if (d.gray || ny == 1u) return;
+    const uint32_t nblk = ny + 2u;
+    const uint32_t ltb = blockIdx.x - d.tb_first;
+    const uint32_t W = d.width, H = d.height;
+    uint8_t* out = d.out_is_ptr ? reinterpret_cast<uint8_t*>(d.out_off) : b.rgb + d.out_off;
+    const size_t pitch = d.row_pitch, pstride = d.plane_stride;
+    const bool interleaved = d.layout != GJD_LAYOUT_PLANAR;
+    const bool wide = d.layout == GJD_LAYOUT_INTERLEAVED_I16;
+    const bool aligned = (((size_t)out | pitch | (interleaved ? 0 : pstride)) & (wide ? 15u : 7u)) == 0;
+    const uint32_t nlines = d.mcu_count * nblk;
+    const size_t line0 = (size_t)d.tile_first * 96u;
+    const GjdQuantSet& qs = b.quants[d.quant_id];
+    const uint32_t mcus_tile = 96u / nblk;                  /* 96 = 24 x 4 = 16 x 6: a tile holds whole MCUs */
+
+#pragma unroll 1
+    for (uint32_t t = 0; t < b.tb_tiles; t++) {
+        const uint32_t ltile = ltb * b.tb_tiles + t;
+        if (ltile >= d.tile_count) break;
+        const uint32_t j = ltile * 96u + tid;               /* line inside the image */
+        const bool valid = j < nlines;
+        const uint32_t bp = j % nblk, c = bp < ny ? 0u : bp - ny + 1u;
+        const uint32_t m = valid ? __ldg(b.meta + line0 + j) : 0u;
+        const uint32_t kmax = (m >> 16) & 63u;
+        const uint32_t nchunk = kmax ? (kmax >> 3) + 1u : 0u;
+        const uint4* src = reinterpret_cast<const uint4*>(b.coef) + (line0 + j) * 8u;
+        uint32_t w[32];
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            uint4 r = make_uint4(0u, 0u, 0u, 0u);
+            if ((uint32_t)q < nchunk) r = __ldcs(src + q);
+            w[4 * q] = r.x; w[4 * q + 1] = r.y; w[4 * q + 2] = r.z; w[4 * q + 3] = r.w;
+        }
+        const int dc = valid ? dcabs[line0 + j] : 0;
+        if (EXPORT) {                                       /* gjd_decode_coeffs: lines in scan order, absolute DC in slot 0 */
+            if (valid) {
+                uint4* o = reinterpret_cast<uint4*>(coef_out + (size_t)j * 64u);
+                w[0] = (w[0] & 0xffff0000u) | ((uint32_t)dc & 0xffffu);
+#pragma unroll
+                for (int q = 0; q < 8; q++) o[q] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+            }
+            continue;
+        }
+        {
+            int v[64];
+            const uint32_t* qq = qs.packed[c];
+            GjdUnpack<63, 64>::run(w, qq, v);
+            v[0] = dc * (int)(qq[0] & 0xffu);
+            gjd_idct8x8(v);
+            __syncthreads();                                /* the previous tile's colour phase is done with smp */
+#pragma unroll
+            for (int i = 0; i < 64; i += 2) *reinterpret_cast<uint32_t*>(&smp[tid][i]) = (uint32_t)v[i] | ((uint32_t)v[i + 1] << 16);
+        }
+        __syncthreads();
+        /* colour: pieces of 8 pixels = one row of one luma block */
+        const uint32_t pieces = mcus_tile * ny * 8u;
+        for (uint32_t pc = tid; pc < pieces; pc += GJD_TRANSFORM_THREADS) {
+            const uint32_t ml = pc / (ny * 8u), rem = pc - ml * (ny * 8u), yb = rem >> 3, r = rem & 7u;
+            const uint32_t mcu = ltile * mcus_tile + ml;
+            if (mcu >= d.mcu_count) continue;
+            const uint32_t my = mcu / d.mcus_x, mx = mcu - my * d.mcus_x;
+            const uint32_t bx = yb % hs, byy = yb / hs;                         /* the luma block's place in the MCU */
+            const uint32_t x0 = (mx * hs + bx) * 8u, y = (my * vs + byy) * 8u + r;
+            if (y >= H || x0 >= W) continue;
+            const uint16_t* ys = &smp[ml * nblk + yb][r * 8u];
+            const uint16_t* cbs = &smp[ml * nblk + ny][0];
+            const uint16_t* crs = &smp[ml * nblk + ny + 1u][0];
+            const uint32_t cy = (byy * 8u + r) / vs;                            /* chroma row that covers this luma row */
+            uint64_t r8 = 0, g8 = 0, b8 = 0;
+#pragma unroll
+            for (uint32_t x = 0; x < 8u; x++) {
+                const uint32_t cx = (bx * 8u + x) / hs;
+                int R, G, B;
+                gjd_color((int)ys[x], (int)cbs[cy * 8u + cx], (int)crs[cy * 8u + cx], R, G, B);
+                r8 |= (uint64_t)R << (8u * x); g8 |= (uint64_t)G << (8u * x); b8 |= (uint64_t)B << (8u * x);
+            }
+            const bool fast = aligned && x0 + 8u <= W;
+            uint8_t* row = out + (size_t)y * pitch + (size_t)x0 * (interleaved ? (wide ? 6u : 3u) : 1u);
+            if (wide) {
+                gjd_store_row_i16(row, r8, g8, b8, min(8u, W - x0), fast);
+            } else if (fast && !interleaved) {
+                __stcs(reinterpret_cast<uint2*>(row), make_uint2((uint32_t)r8, (uint32_t)(r8 >> 32)));
+                __stcs(reinterpret_cast<uint2*>(row + pstride), make_uint2((uint32_t)g8, (uint32_t)(g8 >> 32)));
+                __stcs(reinterpret_cast<uint2*>(row + 2 * pstride), make_uint2((uint32_t)b8, (uint32_t)(b8 >> 32)));
+            } else {
+#pragma unroll 1
+                for (uint32_t x = 0; x < 8u && x0 + x < W; x++) {
+                    const uint8_t R = (uint8_t)(r8 >> (8u * x)), G = (uint8_t)(g8 >> (8u * x)), B = (uint8_t)(b8 >> (8u * x));
+                    if (interleaved) { row[3u * x] = R; row[3u * x + 1u] = G; row[3u * x + 2u] = B; }
+                    else { row[x] = R; row[pstride + x] = G; row[2 * pstride + x] = B; }
+                }
+            }
+        }
+    }
+}
+
 /* ------------------------------------------------------------------ test hooks -------- */
 
 __global__ void k_test_color(const int16_t* __restrict__ y, const int16_t* __restrict__ cb,
@@ -1379,6 +1531,10 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     else k_transform<false, GJD_TRANSFORM_MINB, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr);
     n++;
     if (b.any_gray) { k_transform_gray<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr); n++; }
+    if (b.any_sub) {
+        k_dc_sub<<<b.n_seg, 256, 0, s>>>(b, b.dcabs); n++;
+        k_transform_sub<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, b.dcabs, nullptr); n++;
+    }
     nvtxRangePop();
     if (ev) GJD_CK(cudaEventRecord(ev->e[4], s));
     if (launches) *launches = n;
@@ -1388,6 +1544,7 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
 cudaError_t gjd_launch_export_coefs(const GjdDevBatch& b, int16_t* out, cudaStream_t s) {
     /* single-image batch: out is indexed by the image's own MCU numbers */
     if (b.any_gray) k_transform_gray<true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, out);
+    else if (b.any_sub) k_transform_sub<true><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, b.dcabs, out);
     else k_transform<true, 6, false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, out);
     return cudaGetLastError();
 }

@@ -95,8 +95,18 @@ int gjd_parse_headers(const uint8_t* d, size_t len, GjdParsed* o) {
                 o->components = nf;
                 for (uint32_t c = 0; c < nf; c++) {
                     comp_id[c] = body[6 + 3 * c];
-                    /* 4:4:4 only; a single component has one block per MCU whatever its factors say (T.81 A.2.2) */
-                    if (nf == 3 && body[7 + 3 * c] != 0x11) return GJD_E_UNSUPPORTED;
+                    /* luma 1x1, 2x1, 1x2 or 2x2 over 1x1 chroma; a single component has one block per MCU whatever its
+                     * factors say (T.81 A.2.2) */
+                    if (nf == 3) {
+                        const uint32_t h = body[7 + 3 * c] >> 4, v = body[7 + 3 * c] & 15u;
+                        if (c == 0) {
+                            if (h < 1 || h > 2 || v < 1 || v > 2) return GJD_E_UNSUPPORTED;
+                            o->hs = h;
+                            o->vs = v;
+                        } else if (h != 1 || v != 1) {
+                            return GJD_E_UNSUPPORTED;
+                        }
+                    }
                     uint32_t tq = body[8 + 3 * c];
                     if (tq > 3) return GJD_E_FORMAT;
                     o->qsel[c] = (uint8_t)tq;
@@ -139,8 +149,9 @@ int gjd_parse_headers(const uint8_t* d, size_t len, GjdParsed* o) {
                     /* a block costs at least 2 bits (a 1-bit DC size code and a 1-bit EOB): a frame header that
                      * announces more blocks than the remaining bytes can hold is damaged — refused here so that it
                      * cannot ask for gigabytes of coefficient memory */
-                    const uint64_t mcus = (uint64_t)((o->width + 7) / 8) * (uint64_t)((o->height + 7) / 8);
-                    const uint64_t blocks = mcus * (o->components == 1 ? 1u : 3u);
+                    const uint32_t mw = 8u * o->hs, mh = 8u * o->vs;
+                    const uint64_t mcus = (uint64_t)((o->width + mw - 1) / mw) * (uint64_t)((o->height + mh - 1) / mh);
+                    const uint64_t blocks = mcus * (o->components == 1 ? 1u : o->hs * o->vs + 2u);
                     if (blocks * 2u > (uint64_t)(o->file_end - o->scan_begin) * 8u) return GJD_E_CORRUPT;
                 }
                 return GJD_OK;
@@ -255,8 +266,10 @@ extern "C" int gjd_partition_weights(const gjd_item* items, int32_t n, uint64_t*
     for (int32_t i = 0; i < n; i++) {
         GjdParsed p;
         weight[i] = 0;
-        if (items[i].jpg && gjd_parse_headers(items[i].jpg, items[i].len, &p) == GJD_OK)
-            weight[i] = (uint64_t)(8 * ((p.width + 7) / 8)) * (uint64_t)(8 * ((p.height + 7) / 8));
+        if (items[i].jpg && gjd_parse_headers(items[i].jpg, items[i].len, &p) == GJD_OK) {
+            const uint32_t mw = 8u * p.hs, mh = 8u * p.vs;       /* MCU size: the padded frame is whole MCUs */
+            weight[i] = (uint64_t)(mw * ((p.width + mw - 1) / mw)) * (uint64_t)(mh * ((p.height + mh - 1) / mh));
+        }
     }
     return GJD_OK;
 }

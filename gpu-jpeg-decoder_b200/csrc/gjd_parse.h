@@ -22,14 +22,16 @@ struct GjdParsed {
     uint8_t tabsel[8] = {0};               /* [c] DC slot, [4+c] AC slot of component c             */
     uint8_t qsel[4] = {0};                 /* [c] Tq of component c                                 */
     uint32_t restart_interval = 0;
-    uint32_t components = 3;               /* 3 (Y, Cb, Cr at 4:4:4) or 1 (grayscale)               */
+    uint32_t components = 3;               /* 3 (Y, Cb, Cr) or 1 (grayscale)                         */
+    uint32_t hs = 1, vs = 1;               /* luma sampling factors (1 or 2 each; chroma is always 1x1): 1x1 = 4:4:4,
+                                              2x1 = 4:2:2, 1x2 = 4:4:0, 2x2 = 4:2:0                   */
 };
 
 /* Parse every marker segment up to and including the SOS header.  Returns a gjd_status.
  * A superset of what the reference parser accepts: APPn/COM/unknown segments are
  * skipped by length, DQT/DHT may hold several tables in any order, selectors in SOF0/SOS are
- * honoured; single-component (grayscale) frames are accepted; everything else outside the 8-bit 4:4:4 baseline
- * single-scan contract is rejected with
+ * honoured; single-component (grayscale) frames and luma sampling factors of 1 or 2 (4:2:2, 4:4:0, 4:2:0) are accepted;
+ * everything else outside the 8-bit baseline single-scan contract is rejected with
  * GJD_E_UNSUPPORTED instead of being mis-decoded.  DRI is accepted: restart_interval = MCUs per interval. */
 int gjd_parse_headers(const uint8_t* jpg, size_t len, GjdParsed* out);
 

@@ -108,10 +108,12 @@ typedef struct GjdSegment {
     uint32_t seq_first;     /* global index of the segment's first sequence                    */
     uint32_t seq_count;
     uint32_t img;           /* owning image                                                    */
-    uint32_t blk_first;     /* first 8x8 block of the segment, counted from the image's first block (3 * first MCU) */
-    uint32_t blk_count;     /* 3 * MCUs in the segment                                         */
+    uint32_t blk_first;     /* first 8x8 block of the segment, counted from the image's first block (blocks per MCU * first MCU) */
+    uint32_t blk_count;     /* blocks per MCU * MCUs in the segment                            */
     uint16_t lut_id;        /* index into the GjdLutSet array                                  */
-    uint16_t pad0;
+    uint8_t  ny;            /* luma blocks per MCU: 1 (4:4:4, single-component), 2 (4:2:2, 4:4:0) or 4 (4:2:0); an MCU is
+                               ny luma blocks + Cb + Cr, i.e. ny + 2 blocks (three for the single-component trick)      */
+    uint8_t  pad0;
 } GjdSegment;
 
 /* A scan that is unstuffed ON THE DEVICE (k_unstuff_*): the raw entropy-coded bytes as they stand in the file, from the
@@ -152,7 +154,9 @@ typedef struct GjdImage {
     uint32_t gray;          /* single-component image: mcu_count blocks in one DC chain, tiles of 96 blocks,
                                decoded by k_transform_gray (the entropy kernels see three ring positions that
                                all use the one table pair)                                    */
-    uint32_t pad1;
+    uint8_t  hs, vs;        /* luma sampling factors (1 or 2 each); chroma is 1x1.  hs * vs > 1: a chroma-subsampled image —
+                               MCUs of 8*hs x 8*vs pixels and hs*vs + 2 blocks, decoded by k_dc_sub + k_transform_sub        */
+    uint16_t pad1;
 } GjdImage;
 
 /* Device-written status bits per image. */

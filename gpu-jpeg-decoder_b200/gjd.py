@@ -90,6 +90,26 @@ class GjdError(RuntimeError):
         super().__init__(f"gjd status {status}: {msg} {detail}".strip())
 
 
+def sof_sampling(data: bytes):
+    """(components, luma h, luma v) from the SOF0 segment (host-side helper for sizing coefficient buffers)."""
+    i = 2
+    while i + 4 <= len(data):
+        if data[i] != 0xFF:
+            break
+        m = data[i + 1]
+        if m == 0xFF:
+            i += 1
+            continue
+        seg = (data[i + 2] << 8) | data[i + 3]
+        if m == 0xC0:
+            nf = data[i + 9]
+            return nf, (data[i + 11] >> 4) if nf == 3 else 1, (data[i + 11] & 15) if nf == 3 else 1
+        if m == 0xDA:
+            break
+        i += 2 + seg
+    return 3, 1, 1
+
+
 def peek(data: bytes):
     w, h = C.c_int32(), C.c_int32()
     rc = lib().gjd_peek(C.cast(C.c_char_p(data), C.c_void_p), len(data), C.byref(w), C.byref(h))
@@ -197,11 +217,14 @@ class Decoder:
             raise GjdError(rc, self._detail())
 
     def decode_coeffs(self, data: bytes):
+        """Quantised coefficients (gjd_decode_coeffs): 4:4:4 files mcu*192 + comp*64 + k; single-component files
+        block*64 + k; chroma-subsampled files line*64 + k with line = mcu*(hs*vs + 2) + block-in-MCU (scan order)."""
         rc, w, h = peek(data)
         if rc != OK:
             raise GjdError(rc)
-        nm = ((w + 7) // 8) * ((h + 7) // 8)
-        out = np.empty(nm * 192, np.int16)
+        nc, hs, vs = sof_sampling(data)
+        nm = ((w + 8 * hs - 1) // (8 * hs)) * ((h + 8 * vs - 1) // (8 * vs))
+        out = np.empty(nm * (hs * vs + 2) * 64 if nc == 3 else nm * 192, np.int16)
         rc = lib().gjd_decode_coeffs(self._ctx, C.cast(C.c_char_p(data), C.c_void_p), len(data), out.ctypes.data)
         if rc != OK:
             raise GjdError(rc, self._detail())

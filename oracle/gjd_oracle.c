@@ -336,6 +336,16 @@ void gjdo_color_plane(int y, uint8_t* out) {
         }
 }
 
+/* Bulk form for composed pins (tools/make_golden_gray.py, make_golden_sub.py): n (y, cb, cr) triples through
+ * gjdo_color, out = planar R, G, B (n bytes each). */
+void gjdo_color_pixels(const int16_t* y, const int16_t* cb, const int16_t* cr, size_t n, uint8_t* out) {
+    for (size_t i = 0; i < n; i++) {
+        int r, g, b;
+        gjdo_color(y[i], cb[i], cr[i], &r, &g, &b);
+        out[i] = (uint8_t)r; out[n + i] = (uint8_t)g; out[2 * n + i] = (uint8_t)b;
+    }
+}
+
 /* ---- decode: cpp-decoder/src/parser.cpp:105-195 ----------------------------------------- */
 
 static int build_block(bitreader* br, const hufftab* dc, const hufftab* ac, const uint8_t* q,

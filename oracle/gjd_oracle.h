@@ -53,6 +53,7 @@ void gjdo_idct_block(int blk[64]);                    /* in: natural order dequa
 void gjdo_dezigzag(const int zz[64], int nat[64]);    /* idct.cpp:7-32  */
 void gjdo_color(int y, int cb, int cr, int* r, int* g, int* b);   /* color.cpp:3-18 */
 void gjdo_color_plane(int y, uint8_t* out);            /* all (cb,cr) at one y; see .c */
+void gjdo_color_pixels(const int16_t* y, const int16_t* cb, const int16_t* cr, size_t n, uint8_t* out);   /* bulk gjdo_color */
 extern const uint8_t gjdo_zigzag_of_natural[64];      /* table[x][y] at idct.cpp:7-18 */
 
 /* `.array` text writer, parser.cpp:197-210.  Returns bytes written or <0. */

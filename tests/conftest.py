@@ -100,18 +100,21 @@ class HostSim:
         rb = self.lib.hostsim_unstuff_device(buf, len(data), misalign, b.ctypes.data)
         return (ra, a[: max(ra, 0)].tobytes()), (rb, b[: max(rb, 0)].tobytes())
 
-    def decode(self, data, sub_log2=0):
+    def decode(self, data, sub_log2=0, ncoef=None):
+        """ncoef: int16 coefficients to return (default: the 4:4:4 count, ceil(W/8)*ceil(H/8)*192; chroma-subsampled
+        files have 64 * blocks-per-MCU * MCUs, in scan order)."""
         rc, W, H = self.parse(data)
         if rc != 0:
             return rc, None, None, None
-        nm = ((W + 7) // 8) * ((H + 7) // 8)
+        # room for the subsampled layouts too (up to 6 blocks per 16x16 MCU < 3 blocks per 8x8 one)
+        nm = ((W + 15) // 8) * ((H + 15) // 8)
         coef = np.zeros(nm * 192, np.int16)      # grayscale files fill the first nm * 64
         rgb = np.zeros((3, H, W), np.uint8)
         stats = np.zeros(8, np.uint32)
         w, h = C.c_int32(), C.c_int32()
         rc = self.lib.hostsim_decode(C.cast(C.c_char_p(data), C.c_void_p), len(data), sub_log2, coef.ctypes.data,
                                      rgb.ctypes.data, C.byref(w), C.byref(h), stats.ctypes.data)
-        return rc, coef, rgb, stats
+        return rc, coef[: (ncoef if ncoef is not None else ((W + 7) // 8) * ((H + 7) // 8) * 192)], rgb, stats
 
 
 @pytest.fixture(scope="session")
@@ -154,6 +157,20 @@ def gray_golden():
         with open(f, "rb") as fh:
             out[os.path.basename(f)[:-4]] = fh.read()
     return out
+
+
+@pytest.fixture(scope="session")
+def sub_golden():
+    out = {}
+    for f in sorted(glob.glob(os.path.join(GOLDEN, "sub", "*.jpg"))):
+        with open(f, "rb") as fh:
+            out[os.path.basename(f)[:-4]] = fh.read()
+    return out
+
+
+@pytest.fixture(scope="session")
+def ref_outputs_sub():
+    return np.load(os.path.join(GOLDEN, "ref_outputs_sub.npz"))
 
 
 @pytest.fixture(scope="session")

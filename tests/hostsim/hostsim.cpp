@@ -69,9 +69,12 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     std::vector<uint32_t> scanw((scanbuf.size() + 3) / 4 + 4, 0);
     memcpy(scanw.data(), scanbuf.data(), scanbuf.size());
     const uint32_t W = (uint32_t)p.width, H = (uint32_t)p.height;
-    const uint32_t mcus_x = (W + 7) / 8, mcu_count = mcus_x * ((H + 7) / 8);
     const bool gray = p.components == 1;
-    const uint32_t bpm = gray ? 1u : 3u;                       /* 8x8 blocks per MCU */
+    const uint32_t hs = gray ? 1u : p.hs, vs = gray ? 1u : p.vs, ny = hs * vs;
+    const bool subsamp = ny > 1u;                                  /* chroma-subsampled: ny luma blocks + Cb + Cr per MCU */
+    const uint32_t mcus_x = (W + 8 * hs - 1) / (8 * hs), mcu_count = mcus_x * ((H + 8 * vs - 1) / (8 * vs));
+    const uint32_t bpm = gray ? 1u : ny + 2u;                  /* 8x8 blocks per MCU */
+    const uint32_t mcu_slots = (gray ? 3u : bpm) * 64u;
     const uint32_t tile_count = (mcu_count * bpm + 95) / 96;
     const uint32_t ri = p.restart_interval;
     if (!ri && seg_off.size() != 1) return GJD_E_UNSUPPORTED;          /* RSTn without DRI */
@@ -138,14 +141,14 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                 endb[tid] = std::min(start + S, scan_bits);
                 if (sub != 0) {
                     st.p = start > GJD_LOOKBACK_BITS ? start - GJD_LOOKBACK_BITS : 0u;
-                    gjd_count_span_pairs(scan, clut, start, scan_bits, st);
+                    if (subsamp) gjd_count_span_pairs(scan, clut, start, scan_bits, st, GjdRingSub(ny)); else gjd_count_span_pairs(scan, clut, start, scan_bits, st);
                 }
                 in_p[tid] = st.p; in_pos[tid] = st.pos;
                 st.n = 0;
-                gjd_count_span_pairs(scan, clut, endb[tid], scan_bits, st);
+                if (subsamp) gjd_count_span_pairs(scan, clut, endb[tid], scan_bits, st, GjdRingSub(ny)); else gjd_count_span_pairs(scan, clut, endb[tid], scan_bits, st);
             }
             bp[tid] = st.p;
-            bn[tid] = (st.n << 8) | st.pos;
+            bn[tid] = (st.n << GJD_POS_BITS) | st.pos;
         }
         seq_in_p[g] = in_p[0]; seq_in_pos[g] = in_pos[0];
         for (uint32_t r = 0; r < GJD_SEQ_SUBS; r++) {
@@ -155,11 +158,11 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
             bool any = false;
             for (uint32_t tid = 1; tid < GJD_SEQ_SUBS; tid++) {
                 if (!active[tid]) continue;
-                uint32_t pp = bp[tid - 1], ppos = bn[tid - 1] & 255u;
+                uint32_t pp = bp[tid - 1], ppos = bn[tid - 1] & GJD_POS_MASK;
                 if (pp != in_p[tid] || ppos != in_pos[tid]) {
                     GjdState st; st.p = in_p[tid] = pp; st.pos = in_pos[tid] = ppos; st.n = 0;
-                    gjd_count_span_pairs(scan, clut, endb[tid], scan_bits, st);
-                    np[tid] = st.p; nn[tid] = (st.n << 8) | st.pos;
+                    if (subsamp) gjd_count_span_pairs(scan, clut, endb[tid], scan_bits, st, GjdRingSub(ny)); else gjd_count_span_pairs(scan, clut, endb[tid], scan_bits, st);
+                    np[tid] = st.p; nn[tid] = (st.n << GJD_POS_BITS) | st.pos;
                     badv[tid] = 1; any = true; redec++; if (r == 0) redec1++;
                 }
             }
@@ -174,7 +177,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
         uint32_t ns = 0;
         for (uint32_t g = 1; g < seq_count; g++) {
             size_t base = (size_t)g * GJD_SEQ_SUBS;
-            uint32_t pp = sp[base - 1], ppos = sn[base - 1] & 255u;
+            uint32_t pp = sp[base - 1], ppos = sn[base - 1] & GJD_POS_MASK;
             if (pp == seq_in_p[g] && ppos == seq_in_pos[g]) continue;
             seq_in_p[g] = pp; seq_in_pos[g] = ppos;
             GjdState st; st.p = pp; st.pos = ppos;
@@ -184,11 +187,11 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                 if (sub >= sub_count) { merged = true; break; }
                 st.n = 0;
                 uint32_t end = std::min((sub + 1) << sub_log2, scan_bits);
-                gjd_count_span(scan, hlut, end, scan_bits, st);
+                if (subsamp) gjd_count_span(scan, hlut, end, scan_bits, st, GjdRingSub(ny)); else gjd_count_span(scan, hlut, end, scan_bits, st);
                 fix_decodes++;
-                bool match = sp[base + t] == st.p && (sn[base + t] & 255u) == st.pos;
+                bool match = sp[base + t] == st.p && (sn[base + t] & GJD_POS_MASK) == st.pos;
                 sp[base + t] = st.p;
-                sn[base + t] = (st.n << 8) | st.pos;
+                sn[base + t] = (st.n << GJD_POS_BITS) | st.pos;
                 if (match) { merged = true; break; }
             }
             if (!merged && g + 1 < seq_count) ns++;
@@ -202,7 +205,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     for (uint32_t g = 0; g < seq_count; g++) {
         seq_base[g] = carry;
         uint32_t cnt = std::min<uint32_t>(GJD_SEQ_SUBS, sub_count - g * GJD_SEQ_SUBS);
-        for (uint32_t t = 0; t < cnt; t++) carry += sn[(size_t)g * GJD_SEQ_SUBS + t] >> 8;
+        for (uint32_t t = 0; t < cnt; t++) carry += sn[(size_t)g * GJD_SEQ_SUBS + t] >> GJD_POS_BITS;
     }
     badcode = 0;   /* only the write pass reports unassigned codes */
     if (carry != 64u * blk_count) status |= GJD_DEV_BADCOUNT;
@@ -214,18 +217,18 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
             if (sub >= sub_count) break;
             size_t a = (size_t)g * GJD_SEQ_SUBS + tid;
             GjdState st; st.p = 0; st.n = 0; st.pos = 0;
-            if (sub != 0) { st.p = sp[a - 1]; st.pos = sn[a - 1] & 255u; }
+            if (sub != 0) { st.p = sp[a - 1]; st.pos = sn[a - 1] & GJD_POS_MASK; }
             uint32_t tbad = 0;
             WriteSink sink;
             memset(sink.stage, 0, sizeof(sink.stage));
             sink.coef = coef.data() + (size_t)blk0 * 64; sink.meta = meta.data() + blk0; sink.written = written.data() + blk0;
             uint32_t idx0 = seq_base[g] + excl;
-            if (idx0 % 192u != st.pos && st.p < scan_bits) tbad |= GJD_DEV_BADSTATE;
+            if (idx0 % mcu_slots != st.pos && st.p < scan_bits) tbad |= GJD_DEV_BADSTATE;
             uint32_t end = std::min((sub + 1) << sub_log2, scan_bits);
-            gjd_write_span(scan, hlut, end, scan_bits, st, idx0, blk_count, true, sink, tbad);
+            if (subsamp) gjd_write_span(scan, hlut, end, scan_bits, st, idx0, blk_count, true, sink, tbad, GjdRingSub(ny)); else gjd_write_span(scan, hlut, end, scan_bits, st, idx0, blk_count, true, sink, tbad);
             for (int k = 0; k < 64; k++) if (sink.stage[k]) tbad |= GJD_DEV_BADSTATE;   /* staging must be left clean */
             status |= tbad;
-            excl += sn[a] >> 8;
+            excl += sn[a] >> GJD_POS_BITS;
         }
     }
     }   /* segments */
@@ -266,7 +269,44 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                 }
         }
     }
-    for (uint32_t mcu = 0; !gray && mcu < mcu_count; mcu++) {
+    /* k_dc_sub + k_transform_sub: ny luma blocks + Cb + Cr per MCU, chroma samples replicated over hs x vs pixels */
+    for (uint32_t mcu = 0; subsamp && mcu < mcu_count; mcu++) {
+        int smp[6][64];
+        if (ri && mcu % ri == 0) pred[0] = pred[1] = pred[2] = 0;
+        for (uint32_t bpos = 0; bpos < bpm; bpos++) {
+            const uint32_t c = bpos < ny ? 0u : bpos - ny + 1u;
+            size_t bk = (size_t)mcu * bpm + bpos;
+            uint32_t m = meta[bk];
+            uint32_t kmax = (m >> 16) & 63u;
+            uint32_t nsec = kmax ? (kmax >> 4) + 1u : 0u;
+            int zq[64] = {0};
+            for (uint32_t k = 0; k < nsec * 16u; k++) zq[k] = coef[bk * 64 + k];
+            pred[c] += (int)(int16_t)(m & 0xffffu);
+            int v[64];
+            for (int i = 0; i < 64; i++) v[i] = zq[kZZ[i]] * q[c][kZZ[i]];
+            v[0] = pred[c] * q[c][0];
+            if (coef_out)
+                for (int k = 0; k < 64; k++) coef_out[bk * 64 + k] = (int16_t)(k == 0 ? pred[c] : zq[k]);
+            gjd_idct8x8(v);
+            memcpy(smp[bpos], v, sizeof(v));
+        }
+        if (rgb_out) {
+            uint32_t my = mcu / mcus_x, mx = mcu % mcus_x;
+            for (uint32_t yy = 0; yy < 8 * vs; yy++)
+                for (uint32_t xx = 0; xx < 8 * hs; xx++) {
+                    uint32_t py = my * 8 * vs + yy, px = mx * 8 * hs + xx;
+                    if (py >= H || px >= W) continue;
+                    const int* yb = smp[(yy / 8) * hs + xx / 8];
+                    int R, G, B;
+                    gjd_color(yb[(yy % 8) * 8 + xx % 8], smp[ny][(yy / vs) * 8 + xx / hs], smp[ny + 1][(yy / vs) * 8 + xx / hs], R, G, B);
+                    size_t o = (size_t)py * W + px;
+                    rgb_out[o] = (uint8_t)R;
+                    rgb_out[(size_t)W * H + o] = (uint8_t)G;
+                    rgb_out[2 * (size_t)W * H + o] = (uint8_t)B;
+                }
+        }
+    }
+    for (uint32_t mcu = 0; !gray && !subsamp && mcu < mcu_count; mcu++) {
         uint32_t samples[3][32];   /* as k_transform parks them: two biased samples per word, row r = words 4r..4r+3 */
         if (ri && mcu % ri == 0) pred[0] = pred[1] = pred[2] = 0;   /* T.81 E.1.4 */
         for (int c = 0; c < 3; c++) {

@@ -564,3 +564,68 @@ def test_pinned_input_large_batch(decoder, oracle):
         rc, _, rgb, _, W, H = oracle.decode(base[i], want_coef=False)
         for j in range(i, 64, 4):
             assert np.array_equal(outs[j], rgb)
+
+
+def test_subsampled_bit_exact(decoder, golden, ref_outputs, sub_golden, ref_outputs_sub):
+    """4:2:0 / 4:2:2 / 4:4:0 on the GPU (k_dc_sub + k_transform_sub behind the same entropy kernels): coefficients =
+    jpeg_read_coefficients of the reference's vendored libjpeg, pixels = the oracle's IDCT + sample replication + the
+    oracle's colour formula (tools/make_golden_sub.py) — alone, mixed into one batch with 4:4:4 files, in every layout,
+    and the reference's own testing/image.jpeg, which none of its decoders can read."""
+    import gjd
+    names = sorted(sub_golden)
+    assert len(names) >= 8 and "ref_testing_image" in names
+    for n in names:
+        coef, w, h = decoder.decode_coeffs(sub_golden[n])
+        assert np.array_equal(coef, ref_outputs_sub[n + "/coef"]), n
+    files, want = [], []
+    for i, n in enumerate(names):
+        files.append(sub_golden[n]); want.append(ref_outputs_sub[n + "/rgb"])
+        p = NAMES[i % len(NAMES)]
+        files.append(golden[p]); want.append(ref_outputs[p + "/rgb"])
+    for pinned in (False, True):
+        outs, st = decoder.decode(files, pinned=pinned)
+        assert st == [0] * len(files)
+        for o, w_ in zip(outs, want):
+            assert np.array_equal(o, w_)
+    outs, st = decoder.decode(files, layout=gjd.INTERLEAVED)
+    assert st == [0] * len(files)
+    for o, w_ in zip(outs, want):
+        assert np.array_equal(o, w_.transpose(1, 2, 0))
+    outs, st = decoder.decode(files, layout=gjd.INTERLEAVED_I16)
+    assert st == [0] * len(files)
+    for o, w_ in zip(outs, want):
+        assert np.array_equal(o, w_.transpose(1, 2, 0).astype(np.int16))
+    for n in names[:3]:
+        outs, st = decoder.decode([sub_golden[n]])
+        assert st == [0] and np.array_equal(outs[0], ref_outputs_sub[n + "/rgb"])
+
+
+@pytest.mark.parametrize("sub_log2", [8, 13])
+def test_subsampled_subsequence_lengths(sub_golden, ref_outputs_sub, sub_log2, monkeypatch):
+    import gjd
+    monkeypatch.setenv("GJD_SUB_LOG2", str(sub_log2))
+    monkeypatch.setenv("GJD_DEVICE_UNSTUFF", "0" if sub_log2 == 13 else "1")
+    with gjd.Decoder(0) as d:
+        names = sorted(sub_golden)
+        outs, st = d.decode([sub_golden[n] for n in names])
+        assert st == [0] * len(names)
+        for n, o in zip(names, outs):
+            assert np.array_equal(o, ref_outputs_sub[n + "/rgb"]), n
+
+
+def test_subsampled_large_vs_hostsim(decoder, hostsim):
+    """A 4:2:0 file big enough for many sequences and transform blocks (2048x1536), against the CPU stepping of the same
+    functions (itself pinned to the libjpeg/oracle composition by tests/test_hostsim.py::test_subsampled_bit_exact)."""
+    import gen_synth
+    import subprocess
+    if not gen_synth.have_cjpeg():
+        pytest.skip("vendored cjpeg missing")
+    img = gen_synth.make_image(77, 2048, 1536)
+    ppm = b"P6\n2048 1536\n255\n" + img.tobytes()
+    env = dict(os.environ, LD_LIBRARY_PATH=os.path.join(gen_synth.LIBJPEG, "lib"))
+    data = subprocess.run([os.path.join(gen_synth.LIBJPEG, "bin", "cjpeg"), "-quality", "90", "-sample", "2x2", "-baseline"],
+                          input=ppm, stdout=subprocess.PIPE, check=True, env=env).stdout
+    outs, st = decoder.decode([data, data])
+    assert st == [0, 0]
+    rc, _, rgb, _ = hostsim.decode(data)
+    assert rc == 0 and np.array_equal(outs[0], rgb) and np.array_equal(outs[1], rgb)

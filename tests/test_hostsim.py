@@ -83,7 +83,11 @@ def test_parser_contract(hostsim, golden):
 
     ok = enc("-quality", "90", "-sample", "1x1", "-baseline")
     assert hostsim.parse(ok)[0] == 0
-    assert hostsim.parse(enc("-sample", "2x2"))[0] == -5          # subsampled
+    assert hostsim.parse(enc("-sample", "2x2"))[0] == 0           # 4:2:0, 4:2:2, 4:4:0 are decoded
+    assert hostsim.parse(enc("-sample", "2x1"))[0] == 0
+    assert hostsim.parse(enc("-sample", "1x2"))[0] == 0
+    assert hostsim.parse(enc("-sample", "4x1"))[0] == -5          # luma factors beyond 2
+    assert hostsim.parse(enc("-sample", "2x2,2x1,1x1"))[0] == -5  # subsampling that leaves chroma above 1x1
     assert hostsim.parse(enc("-sample", "1x1", "-progressive"))[0] == -5
     assert hostsim.parse(enc("-grayscale"))[0] == 0                 # single component accepted
     assert hostsim.parse(enc("-sample", "1x1", "-restart", "1"))[0] == 0    # DRI/RSTn accepted
@@ -309,3 +313,19 @@ def test_device_unstuffing_equals_host_loop(hostsim, golden, gray_golden, rst_go
                 assert a == b
             seen.add(ra if ra < 0 else 0)
     assert {0, -4, -5} <= seen
+
+
+def test_subsampled_bit_exact(hostsim, sub_golden, ref_outputs_sub):
+    """4:2:0, 4:2:2 and 4:4:0 (outside the reference's decoders): coefficients = jpeg_read_coefficients of the
+    reference's vendored libjpeg, pixels = those through the oracle's IDCT + sample replication + the oracle's colour
+    formula (tools/make_golden_sub.py) — ragged sizes, restart intervals, optimised tables, the reference's own
+    testing/image.jpeg; default subsequences and ones shorter than the look-back."""
+    assert len(sub_golden) >= 8
+    for name, data in sub_golden.items():
+        want_c, want_p = ref_outputs_sub[name + "/coef"], ref_outputs_sub[name + "/rgb"]
+        for sub_log2 in (0, 8, 12):
+            rc, coef, rgb, stats = hostsim.decode(data, sub_log2, ncoef=want_c.size)
+            assert rc == 0, name
+            assert np.array_equal(coef, want_c), name
+            assert np.array_equal(rgb, want_p), name
+            assert stats[2] == 0 and stats[3] == 0
