@@ -200,6 +200,7 @@ struct gjd_batch {
     std::vector<GjdDhtSet> dhts;
     std::vector<GjdQuantSet> quants;
     std::vector<GjdRaw> raws;        /* scans unstuffed on the device */
+    std::vector<uint32_t> rst;       /* restart-interval start positions (bits) of all segments */
     PinBuf h_scan, h_raw, h_meta, h_status;
     DevBuf d_raw, d_uchunk, d_rawmeta, d_ustatus, d_dcabs;
     DevBuf d_scan, d_meta, d_luts, d_lutc, d_sinfo, d_seqmaps, d_coef, d_blkmeta, d_tilebase, d_tileimg, d_tbimg, d_rgb, d_status;
@@ -292,6 +293,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
      * (adjacent files merge into one copy), through the pinned h_raw staging otherwise.  On the host
      * (gjd_unstuff_segments): scans with restart intervals, whose intervals become segments the host has to size. */
     b->raws.clear();
+    b->rst.clear();
     std::vector<uint8_t> mode(n, 0);                 /* 1 = device-unstuffed */
     std::vector<size_t> soff(n + 1, 0);              /* scan arena (device) */
     std::vector<size_t> hoff(n + 1, 0);              /* h_scan staging: host-unstuffed scans only */
@@ -308,7 +310,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
                 room = align_up(rawlen + 64, 128);
                 if (!b->geom[i].jpg_pinned) { roff[i] = raw_staged; raw_staged += align_up(rawlen, 16) + 16; }
             } else {
-                room = hroom = align_up(items[i].len + 64 + (parsed[i].restart_interval ? items[i].len / 2 + 64 : 0), 128);
+                room = hroom = align_up(items[i].len + 64, 128);
             }
         }
         soff[i + 1] = soff[i] + room;
@@ -468,21 +470,24 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
             last_quant = found;
         }
         d.seg_first = (uint32_t)b->segs.size();
-        d.seg_count = nseg;
-        for (uint32_t k = 0; k < nseg; k++) {
+        d.seg_count = 1;
+        {   /* one segment per image; its restart intervals lie back to back inside it (table of their start positions) */
             GjdSegment sg;
             memset(&sg, 0, sizeof(sg));
-            const uint32_t off = p.restart_interval ? rst_off[i][k] : 0u;
-            const uint32_t len = p.restart_interval ? rst_len[i][k] : (uint32_t)ulen[i];
-            sg.scan_off = soff[i] + off;
-            sg.scan_bits = len * 8u;
+            sg.scan_off = soff[i];
+            sg.scan_bits = (uint32_t)ulen[i] * 8u;
             sg.sub_count = std::max<uint32_t>(1u, (uint32_t)(((uint64_t)sg.scan_bits + sub_bits - 1) / sub_bits));
             sg.seq_first = seq;
             sg.seq_count = (sg.sub_count + GJD_SEQ_SUBS - 1) / GJD_SEQ_SUBS;
             sg.img = (uint32_t)b->imgs.size();
-            const uint32_t mcu0 = k * p.restart_interval;
-            sg.blk_first = bpm * mcu0;
-            sg.blk_count = bpm * (p.restart_interval ? std::min(p.restart_interval, d.mcu_count - mcu0) : d.mcu_count);
+            sg.blk_first = 0;
+            sg.blk_count = bpm * d.mcu_count;
+            if (p.restart_interval && nseg > 1) {
+                sg.rst_first = (uint32_t)b->rst.size();
+                sg.rst_count = nseg - 1;
+                sg.rst_blocks = bpm * p.restart_interval;
+                for (uint32_t k = 1; k < nseg; k++) b->rst.push_back(rst_off[i][k] * 8u);
+            }
             sg.lut_id = lut_id;
             sg.ny = (uint8_t)(d.gray ? 1u : (uint32_t)d.hs * d.vs);
             if (mode[i]) {
@@ -535,9 +540,11 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     size_t o_dht = align_up(o_seg + sizeof(GjdSegment) * b->segs.size(), 256);
     size_t o_q = align_up(o_dht + sizeof(GjdDhtSet) * b->dhts.size(), 256);
     size_t o_raw = align_up(o_q + sizeof(GjdQuantSet) * b->quants.size(), 256);
-    size_t meta = align_up(o_raw + sizeof(GjdRaw) * b->raws.size(), 256);
+    size_t o_rst = align_up(o_raw + sizeof(GjdRaw) * b->raws.size(), 256);
+    size_t meta = align_up(o_rst + sizeof(uint32_t) * b->rst.size(), 256);
     GJD_TRY(b->h_meta.ensure(meta));
     if (!b->raws.empty()) memcpy((uint8_t*)b->h_meta.p + o_raw, b->raws.data(), sizeof(GjdRaw) * b->raws.size());
+    if (!b->rst.empty()) memcpy((uint8_t*)b->h_meta.p + o_rst, b->rst.data(), sizeof(uint32_t) * b->rst.size());
     memcpy((uint8_t*)b->h_meta.p + o_img, b->imgs.data(), sizeof(GjdImage) * n_img);
     memcpy((uint8_t*)b->h_meta.p + o_seg, b->segs.data(), sizeof(GjdSegment) * b->segs.size());
     memcpy((uint8_t*)b->h_meta.p + o_dht, b->dhts.data(), sizeof(GjdDhtSet) * b->dhts.size());
@@ -566,6 +573,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     v.imgs = (const GjdImage*)((uint8_t*)b->d_meta.p + o_img);
     v.segs = (GjdSegment*)((uint8_t*)b->d_meta.p + o_seg);
     v.scan = (uint8_t*)b->d_scan.p;
+    v.rst = (const uint32_t*)((uint8_t*)b->d_meta.p + o_rst);
     v.raws = (const GjdRaw*)((uint8_t*)b->d_meta.p + o_raw);
     v.n_raw = (uint32_t)b->raws.size();
     v.n_uchunk = uchunk;

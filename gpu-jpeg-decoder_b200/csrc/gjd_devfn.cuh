@@ -479,23 +479,69 @@ struct GjdRingSub {
     GJD_HD uint32_t slots() const { return (ny + 2u) * 64u; }
 };
 
+/* Restart intervals inside one scan (T.81 B.2.4.4, E.1.4; outside the reference's parser, which keeps FF Dn as data).
+ * The unstuffed scan of an image holds its intervals back to back, RSTn markers removed: interval k >= 1 starts at the
+ * bit position start[k - 1] (a byte boundary); the 0-7 one-bits in front of it pad the previous interval.  A decoder
+ * — synchronised or not — that reaches such a position, or whose next symbol would run across it, drops what is left
+ * of the interval and restarts there at block 0 of an MCU, zigzag index 0: restart positions are hard synchronisation
+ * points.  The decoders are templates over this policy: GjdNoRst compiles to exactly the code without restart intervals
+ * (limit == scan_bits), GjdRstTable carries the table.  A block cut short by a restart counts as ended (corrupt data;
+ * the write pass flags it). */
+struct GjdNoRst {
+    static constexpr bool enabled = false;
+    GJD_HD uint32_t seek(uint32_t, uint32_t scan_bits) { return scan_bits; }
+    GJD_HD uint32_t advance(uint32_t scan_bits) { return scan_bits; }
+    GJD_HD uint32_t interval() const { return 0u; }
+};
+struct GjdRstTable {
+    static constexpr bool enabled = true;
+    const uint32_t* start;      /* start[k - 1] = bit position of interval k */
+    uint32_t count;             /* restart markers = intervals - 1 */
+    uint32_t next;              /* start[next] = the boundary in front of the decoder (next == count: the end of the scan) */
+    GJD_HD GjdRstTable(const uint32_t* s, uint32_t n) : start(s), count(n), next(0) {}
+    /* the first boundary > p: the decoder at p is inside the interval that ends there */
+    GJD_HD uint32_t seek(uint32_t p, uint32_t scan_bits) {
+        uint32_t lo = 0, hi = count;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (start[mid] <= p) lo = mid + 1u; else hi = mid;
+        }
+        next = lo;
+        return lo < count ? start[lo] : scan_bits;
+    }
+    GJD_HD uint32_t advance(uint32_t scan_bits) {
+        next++;
+        return next < count ? start[next] : scan_bits;
+    }
+    GJD_HD uint32_t interval() const { return next; }   /* index of the interval the decoder is in */
+};
+
 /* Decode symbols that START before end_bits, beginning at state s.  A symbol that would run past
  * scan_bits is padding and is not counted.
  * Follows JPEGParser::buildMCU (cpp-decoder/src/parser.cpp:105-134): DC size/diff; AC run/size with
  * EOB = 0x00, "length += run", value bits always consumed, coefficient kept only if index < 64. */
-template <class Src, class Lut, class Ring = GjdRing444>
+template <class Src, class Lut, class Ring = GjdRing444, class Rst = GjdNoRst>
 GJD_HD void gjd_count_span(Src& scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
-                           GjdState& s, Ring ring = Ring()) {
+                           GjdState& s, Ring ring = Ring(), Rst rst = Rst()) {
     if (s.p >= end_bits) return;
     GjdWin win;
     gjd_win_init(win, scan, s.p);
     uint32_t p = s.p, z = s.pos & 63u, tb = ring.of_pos(s.pos), nb = 0;
+    uint32_t limit = rst.seek(p, scan_bits);
     while (p < end_bits) {
         GJD_DBG_SYM();
         const uint32_t w = gjd_peek32(win, scan, p);
-        const uint32_t e = gjd_lookup(lut, tb, w, scan_bits - p);
+        const uint32_t e = gjd_lookup(lut, tb, w, limit - p);
         const uint32_t pn = p + (e & 31u);
-        if (pn > scan_bits) break;
+        if (pn > limit) {
+            if (!Rst::enabled || limit >= scan_bits) break;
+            p = limit;                                  /* restart: the rest of the interval is padding */
+            if (z != 0u) nb++;
+            z = 0u;
+            tb = ring.of_pos(0u);
+            limit = rst.advance(scan_bits);
+            continue;
+        }
         p = pn;
         const uint32_t zn = z + (e >> 9);
         tb = ring.next(tb, z, zn);
@@ -523,47 +569,65 @@ GJD_HD_COLD uint32_t gjd_lookup_canonical(const GjdLutSet* lut, uint32_t tb, uin
  *   - when a pair would complete the block, the first symbol is checked alone: if it already completes the
  *     block (a coefficient at index 63, or garbage), the second symbol belongs to the next block's DC table
  *     and the pair is dropped. */
-template <class Src, class Lut, class Ring = GjdRing444>
+template <class Src, class Lut, class Ring = GjdRing444, class Rst = GjdNoRst>
 GJD_HD void gjd_count_span_pairs(Src& scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
-                                 GjdState& s, Ring ring = Ring()) {
+                                 GjdState& s, Ring ring = Ring(), Rst rst = Rst()) {
     if (s.p >= end_bits) return;
     GjdWin win;
     gjd_win_init(win, scan, s.p);
     uint32_t p = s.p, z = s.pos & 63u, tb = ring.of_pos(s.pos), nb = 0;
-    while (p + (uint32_t)GJD_LUT_BITS <= end_bits) {
-        GJD_DBG_SYM();
-        const uint32_t w = gjd_peek32(win, scan, p);
-        uint32_t e = lut.entry(tb + ((w >> (31 - GJD_LUT_BITS)) & (GJD_RING_STRIDE - 2u)));
-        if ((e & 31u) == 0u) {   /* long code: single-symbol entries (with a size field) from lut2 / the tables */
-            if (e) e = lut.entry(GJD_LUT2_OFF(tb, e, w));
-            if ((e & 31u) == 0u) e = gjd_lookup_slow(lut.set, tb, w, scan_bits - p, lut.badcode);
-            e &= ~0x1E0u;
+    uint32_t limit = rst.seek(p, scan_bits);
+    for (;;) {
+        /* fast steps: only where a whole LUT index lies in front of both the end of the span and the next restart */
+        const uint32_t fence = (Rst::enabled && limit < end_bits) ? limit : end_bits;
+        while (p + (uint32_t)GJD_LUT_BITS <= fence) {
+            GJD_DBG_SYM();
+            const uint32_t w = gjd_peek32(win, scan, p);
+            uint32_t e = lut.entry(tb + ((w >> (31 - GJD_LUT_BITS)) & (GJD_RING_STRIDE - 2u)));
+            if ((e & 31u) == 0u) {   /* long code: single-symbol entries (with a size field) from lut2 / the tables */
+                if (e) e = lut.entry(GJD_LUT2_OFF(tb, e, w));
+                if ((e & 31u) == 0u) e = gjd_lookup_slow(lut.set, tb, w, limit - p, lut.badcode);
+                e &= ~0x1E0u;
+            }
+            uint32_t pn = p + (e & 31u);
+            if (pn > limit) break;   /* (a long code only) left to the single steps below */
+            uint32_t zn = z + (e >> 9);
+            if (zn >= 64u && (e & GJD_PAIR_FLAG) && z + ((e >> 6) & 7u) >= 63u) {
+                /* the first symbol alone completes the block (rare): take it alone, from the canonical tables */
+                const uint32_t e1 = gjd_lookup_canonical(lut.set, tb, w);
+                pn = p + (e1 & 31u);
+                zn = z + (e1 >> 9);
+            }
+            p = pn;
+            tb = ring.next(tb, z, zn);
+            z = zn;
+            if (zn >= 64u) { z = 0u; nb++; }
         }
-        uint32_t pn = p + (e & 31u);
-        if (pn > scan_bits) break;
-        uint32_t zn = z + (e >> 9);
-        if (zn >= 64u && (e & GJD_PAIR_FLAG) && z + ((e >> 6) & 7u) >= 63u) {
-            /* the first symbol alone completes the block (rare): take it alone, from the canonical tables */
-            const uint32_t e1 = gjd_lookup_canonical(lut.set, tb, w);
-            pn = p + (e1 & 31u);
-            zn = z + (e1 >> 9);
+        /* single steps from the canonical tables: the last symbols of the span, or of a restart interval */
+        bool again = false;
+        while (p < end_bits) {
+            GJD_DBG_SYM();
+            const uint32_t w = gjd_peek32(win, scan, p);
+            const uint32_t e = gjd_lookup_canonical(lut.set, tb, w);
+            const uint32_t pn = p + (e & 31u);
+            if (pn > limit) {
+                if (!Rst::enabled || limit >= scan_bits) break;
+                p = limit;                              /* restart: the rest of the interval is padding */
+                if (z != 0u) nb++;
+                z = 0u;
+                tb = ring.of_pos(0u);
+                limit = rst.advance(scan_bits);
+                again = true;
+                break;
+            }
+            p = pn;
+            const uint32_t zn = z + (e >> 9);
+            tb = ring.next(tb, z, zn);
+            z = zn;
+            if (zn >= 64u) { z = 0u; nb++; }
+            if (Rst::enabled && p + (uint32_t)GJD_LUT_BITS <= fence) { again = true; break; }   /* a long code sent us here */
         }
-        p = pn;
-        tb = ring.next(tb, z, zn);
-        z = zn;
-        if (zn >= 64u) { z = 0u; nb++; }
-    }
-    while (p < end_bits) {
-        GJD_DBG_SYM();
-        const uint32_t w = gjd_peek32(win, scan, p);
-        const uint32_t e = gjd_lookup_canonical(lut.set, tb, w);
-        const uint32_t pn = p + (e & 31u);
-        if (pn > scan_bits) break;
-        p = pn;
-        const uint32_t zn = z + (e >> 9);
-        tb = ring.next(tb, z, zn);
-        z = zn;
-        if (zn >= 64u) { z = 0u; nb++; }
+        if (!Rst::enabled || !again) break;
     }
     const uint32_t adv = nb * 64u + z - (s.pos & 63u);
     s.p = p;
@@ -590,24 +654,31 @@ GJD_HD void gjd_count_span_pairs(Src& scan, const Lut& lut, uint32_t end_bits, u
  * lanes of a warp stay converged: ALL 32 lanes call this (enable = false for lanes without a
  * subsequence).  Same buildMCU semantics as gjd_count_span (cpp-decoder/src/parser.cpp:105-134).
  */
-template <class Src, class Lut, class Sink, class Ring = GjdRing444>
+template <class Src, class Lut, class Sink, class Ring = GjdRing444, class Rst = GjdNoRst>
 GJD_HD void gjd_write_span(Src& scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
-                           GjdState s, uint32_t idx0, uint32_t nblocks, bool enable, Sink& sink, uint32_t& bad, Ring ring = Ring()) {
+                           GjdState s, uint32_t idx0, uint32_t nblocks, bool enable, Sink& sink, uint32_t& bad, Ring ring = Ring(),
+                           Rst rst = Rst(), uint32_t rst_blocks = 0) {
     uint32_t run = (enable && s.p < end_bits) ? 1u : 0u;
     GjdWin win;
     win.wi = 0; win.w0 = 0; win.w1 = 0; win.w2raw = 0;
     if (run) gjd_win_init(win, scan, s.p);
     uint32_t p = s.p, z = s.pos & 63u, tb = ring.of_pos(s.pos);
     uint32_t blk = (idx0 + 63u) >> 6;
+    uint32_t limit = run ? rst.seek(p, scan_bits) : scan_bits;
 
     /* phase A: the tail of a block that belongs to the previous thread */
     uint32_t skip = (run && z != 0u) ? 1u : 0u;
     while (GJD_WARP_ANY(skip != 0u)) {
         if (skip) {
             const uint32_t w = gjd_peek32(win, scan, p);
-            const uint32_t e = gjd_lookup(lut, tb, w, scan_bits - p);
+            const uint32_t e = gjd_lookup(lut, tb, w, limit - p);
             const uint32_t pn = p + (e & 31u);
-            if (p >= end_bits || pn > scan_bits) {
+            if (Rst::enabled && p < end_bits && pn > limit && limit < scan_bits) {
+                /* the block was cut short by a restart (corrupt data; its owner flags it): this thread starts with the interval */
+                p = limit; z = 0u; tb = ring.of_pos(0u);
+                limit = rst.advance(scan_bits);
+                skip = 0u;
+            } else if (p >= end_bits || pn > limit) {
                 skip = 0u; run = 0u;                 /* owns nothing (a truncated block is its owner's to report) */
             } else {
                 p = pn;
@@ -624,7 +695,8 @@ GJD_HD void gjd_write_span(Src& scan, const Lut& lut, uint32_t end_bits, uint32_
      * runs its ~45 instructions for 2-3 active lanes on 95 % of the trips (ncu source page, r01m: 37 % of the
      * pass's warp instructions).  A lane completes at most one block per trip: the symbol after a completed
      * block is the next block's DC, which neither completes a block nor touches the staging buffer, so the
-     * completed block can wait there (DC difference parked in fdc, kmax left alone) until the end of the trip. */
+     * completed block can wait there (DC difference parked in fdc, kmax left alone) until the end of the trip.
+     * (A restart counts as a step that completes the block it cuts short, if any.) */
     int dcdiff = 0, fdc = 0;
     uint32_t kmax = 0, fl = 0;
     while (GJD_WARP_ANY(run != 0u)) {
@@ -635,11 +707,22 @@ GJD_HD void gjd_write_span(Src& scan, const Lut& lut, uint32_t end_bits, uint32_
             /* (more than two symbols per trip: past a completed block only the next DC symbol may be taken) */
             if (run && !(GJD_WRITE_SYMS > 2 && fl && z != 0u)) {
                 const uint32_t w = gjd_peek32(win, scan, p);     /* (reads at most one word into the padding) */
-                const uint32_t e = gjd_lookup(lut, tb, w, scan_bits - p);
+                const uint32_t e = gjd_lookup(lut, tb, w, limit - p);
                 const uint32_t total = e & 31u;
                 const uint32_t pn = p + total;
                 const bool stop = z == 0u && p >= end_bits;
-                if (stop || pn > scan_bits) {                    /* padding at a block start is the normal end */
+                if (Rst::enabled && !stop && pn > limit && limit < scan_bits) {
+                    /* restart: what is left of the interval is padding; the next interval starts a new MCU, and it must
+                     * start at the block the restart interval says (T.81 E.1.4) */
+                    if (z != 0u) {                               /* a block cut short: corrupt, still flushed (staging stays clean) */
+                        bad |= GJD_DEV_BADCOUNT;
+                        if (fl || blk >= nblocks) run = 0u;      /* (one flush per trip; cannot happen on valid data) */
+                        else { fl = 1u; fdc = dcdiff; blk++; }
+                    }
+                    p = limit; z = 0u; tb = ring.of_pos(0u);
+                    limit = rst.advance(scan_bits);
+                    if (blk != rst.interval() * rst_blocks) { bad |= GJD_DEV_BADCOUNT; run = 0u; }
+                } else if (stop || pn > limit) {                 /* padding at a block start is the normal end */
                     if (z != 0u) bad |= GJD_DEV_BADCOUNT;
                     run = 0u;
                 } else {

@@ -323,18 +323,18 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS, 8) k_huff_sync(GjdDevBatch b
     const uint32_t start = sub << b.sub_log2;
     const uint32_t end = active ? min(start + S, scan_bits) : 0u;
     /* the same code for both MCU shapes (block-uniform choice): 4:4:4 / single-component, or ny luma blocks + Cb + Cr */
-    auto body = [&](auto ring) {
+    auto body = [&](auto ring, auto rst) {
         GjdState st;
         st.p = 0; st.n = 0; st.pos = 0;
         uint32_t in_p = 0, in_pos = 0;
         if (active) {
             if (sub != 0u) {
                 st.p = start > GJD_LOOKBACK_BITS ? start - GJD_LOOKBACK_BITS : 0u;
-                gjd_count_span_pairs(scan, slut, start, scan_bits, st, ring);
+                gjd_count_span_pairs(scan, slut, start, scan_bits, st, ring, rst);
             }
             in_p = st.p; in_pos = st.pos;
             st.n = 0;
-            gjd_count_span_pairs(scan, slut, end, scan_bits, st, ring);
+            gjd_count_span_pairs(scan, slut, end, scan_bits, st, ring, rst);
         }
         sp[tid] = st.p;
         sn[tid] = (st.n << GJD_POS_BITS) | st.pos;
@@ -348,7 +348,7 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS, 8) k_huff_sync(GjdDevBatch b
                 bad = pp != in_p || ppos != in_pos;
                 if (bad) {
                     st.p = in_p = pp; st.pos = in_pos = ppos; st.n = 0;
-                    gjd_count_span_pairs(scan, slut, end, scan_bits, st, ring);
+                    gjd_count_span_pairs(scan, slut, end, scan_bits, st, ring, rst);
                 }
             }
             if (!__syncthreads_or(bad)) break;
@@ -358,7 +358,11 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS, 8) k_huff_sync(GjdDevBatch b
             }
         }
     };
-    if (d.ny > 1u) body(GjdRingSub(d.ny)); else body(GjdRing444());
+    /* block-uniform: with or without restart intervals inside the scan */
+    auto with_rst = [&](auto ring) {
+        if (d.rst_count) body(ring, GjdRstTable(b.rst + d.rst_first, d.rst_count)); else body(ring, GjdNoRst());
+    };
+    if (d.ny > 1u) with_rst(GjdRingSub(d.ny)); else with_rst(GjdRing444());
     if (active) b.sinfo[(size_t)g * GJD_SEQ_SUBS + tid] = make_uint2(sp[tid], sn[tid]);
 #ifdef GJD_SCAN_TMA
     scan.drain();
@@ -396,7 +400,11 @@ __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
         if (sub >= d.sub_count) { merged = true; break; }
         st.n = 0;
         uint32_t end = min((sub + 1) << b.sub_log2, scan_bits);
-        if (d.ny > 1u) gjd_count_span(scan, glut, end, scan_bits, st, GjdRingSub(d.ny));
+        if (d.rst_count) {
+            const GjdRstTable rst(b.rst + d.rst_first, d.rst_count);
+            if (d.ny > 1u) gjd_count_span(scan, glut, end, scan_bits, st, GjdRingSub(d.ny), rst);
+            else gjd_count_span(scan, glut, end, scan_bits, st, GjdRing444(), rst);
+        } else if (d.ny > 1u) gjd_count_span(scan, glut, end, scan_bits, st, GjdRingSub(d.ny));
         else gjd_count_span(scan, glut, end, scan_bits, st);
         uint2 old = si[t];
         si[t] = make_uint2(st.p, (st.n << GJD_POS_BITS) | st.pos);
@@ -559,7 +567,12 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, GJD_WRITE_MINB) k_huff_writ
     const uint32_t mcu_slots = ((uint32_t)d.ny + 2u) * 64u;       /* coefficient slots per MCU: 192 for 4:4:4 and single-component scans */
     if (active && idx0 % mcu_slots != st.pos && st.p < scan_bits) bad |= GJD_DEV_BADSTATE;
     uint32_t end = min((sub + 1) << b.sub_log2, scan_bits);
-    if (d.ny > 1u) gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad, GjdRingSub(d.ny));   /* block-uniform */
+    /* block-uniform choices: the MCU shape, and restart intervals inside the scan */
+    if (d.rst_count) {
+        const GjdRstTable rst(b.rst + d.rst_first, d.rst_count);
+        if (d.ny > 1u) gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad, GjdRingSub(d.ny), rst, d.rst_blocks);
+        else gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad, GjdRing444(), rst, d.rst_blocks);
+    } else if (d.ny > 1u) gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad, GjdRingSub(d.ny));
     else gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad);
 #ifdef GJD_SCAN_TMA
     scan.drain();
@@ -1297,28 +1310,55 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_gray(Gjd
  * pixels against the oracle's IDCT + replication + the oracle's colour function (tools/make_golden_sub.py).
  * Correct first: these kernels are not tuned.
  */
+/* Inclusive SEGMENTED scan over a 256-thread block: v summed from the nearest thread at or below with head = true (from
+ * `carry`, the running value in front of the block, when there is none).  Returns the thread's value; *carry_out = the
+ * running value behind the block.  wv / wf: 8 words of shared memory each. */
+__device__ __forceinline__ int block_seg_scan_256(int v, bool head, int carry, int* wv, uint32_t* wf, int* carry_out) {
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    const uint32_t heads = __ballot_sync(0xffffffffu, head);
+    const uint32_t below = heads & (0xffffffffu >> (31u - lane));           /* heads at lanes <= lane */
+    const int first = below ? 31 - __clz(below) : 0;                        /* this lane's head (lane 0 stands in when none) */
+    const int incl = warp_incl_scan_i(v, lane);
+    const int before = __shfl_sync(0xffffffffu, incl, first > 0 ? first - 1 : 0);
+    const int seg = incl - (first > 0 ? before : 0);                        /* sum since the head / since the warp's first lane */
+    __syncthreads();                                                         /* wv / wf may still be read from the previous call */
+    if (lane == 31u) { wv[wid] = seg; wf[wid] = heads != 0u; }
+    __syncthreads();
+    int run = carry, mine = carry;
+#pragma unroll
+    for (uint32_t w = 0; w < 8u; w++) {
+        if (w == wid) mine = run;
+        run = wf[w] ? wv[w] : run + wv[w];
+    }
+    *carry_out = run;
+    return below ? seg : mine + seg;
+}
+
 __global__ void __launch_bounds__(256) k_dc_sub(GjdDevBatch b, int* __restrict__ dcabs) {
-    __shared__ uint32_t ws[8];
+    __shared__ int wv[8];
+    __shared__ uint32_t wf[8];
     const GjdSegment& sg = b.segs[blockIdx.x];
     const GjdImage& d = b.imgs[sg.img];
     const uint32_t ny = (uint32_t)d.hs * d.vs;
     if (d.gray || ny == 1u) return;
     const uint32_t nblk = ny + 2u, tid = threadIdx.x;
     const size_t line0 = (size_t)d.tile_first * 96u;
-    int pred[3] = {0, 0, 0};                                /* T.81 E.1.4: the predictors restart with the interval */
+    const uint32_t rb = d.restart_interval * nblk;          /* lines per restart interval (0: none) */
+    int pred[3] = {0, 0, 0};
     for (uint32_t base = 0; base < sg.blk_count; base += 256u) {
         const uint32_t j = sg.blk_first + base + tid;       /* line inside the image */
         const bool valid = base + tid < sg.blk_count;
         const uint32_t bp = j % nblk, c = bp < ny ? 0u : bp - ny + 1u;
+        /* T.81 E.1.4: the predictors restart with the interval — at the first block of each chain in it */
+        const bool head = rb != 0u && (j % rb) == (c == 0u ? 0u : ny + c - 1u);
         const int diff = valid ? (int)(int16_t)(__ldg(b.meta + line0 + j) & 0xffffu) : 0;
         int mine = 0;
 #pragma unroll
         for (uint32_t k = 0; k < 3u; k++) {
-            uint32_t total;
-            const uint32_t v = c == k ? (uint32_t)diff : 0u;
-            const uint32_t excl = block_excl_scan_256(v, ws, &total);
-            if (c == k) mine = pred[k] + (int)(excl + v);
-            pred[k] += (int)total;
+            int next;
+            const int r = block_seg_scan_256(c == k ? diff : 0, c == k && head, pred[k], wv, wf, &next);
+            if (c == k) mine = r;
+            pred[k] = next;
         }
         if (valid) dcabs[line0 + j] = mine;
     }

@@ -16,6 +16,7 @@ struct GjdDevBatch {
     uint32_t n_img;
     GjdSegment* segs;      /* scan_bits / sub_count of device-unstuffed scans are written by k_unstuff_scan */
     uint32_t n_seg;
+    const uint32_t* rst;   /* restart-interval start positions of all segments (GjdSegment.rst_first / rst_count) */
     uint8_t* scan;
     const GjdLutSet* luts;
     const GjdLutCount* lutc;   /* pair LUT rings of the count pass, same index as luts */

@@ -219,7 +219,6 @@ long gjd_unstuff_segments(const uint8_t* p, const uint8_t* end, uint8_t* dst, st
             expect = (expect + 1u) & 7u;
             seg_off->push_back((uint32_t)(seg - dst));
             if (seg_len) seg_len->push_back((uint32_t)(o - seg));
-            while ((size_t)(o - dst) & 3u) *o++ = 0;         /* the next interval starts on a 4-byte boundary */
             seg = o;
             p = q + 2;
         } else {

@@ -44,9 +44,9 @@ long gjd_unstuff(const uint8_t* src, const uint8_t* end, uint8_t* dst);
 
 /* The same with restart markers (DRI/RSTn, T.81 B.2.4.4 + E.1.4; outside the reference's parser, which
  * keeps FF Dn as data, cpp-decoder/src/parser.cpp:84-96): every RSTn ends a restart interval, is checked
- * against the 0..7 cycle and removed; the next interval is written at the next 4-byte boundary of dst.
+ * against the 0..7 cycle and removed; the intervals follow each other without gaps in dst.
  * seg_off/seg_len receive the byte offset and length of every interval (one entry for a scan without
- * restarts).  dst needs (end - src) + (end - src) / 2 + 32 bytes.  Returns the bytes used in dst. */
+ * restarts).  dst needs (end - src) + 32 bytes.  Returns the bytes used in dst. */
 long gjd_unstuff_segments(const uint8_t* src, const uint8_t* end, uint8_t* dst, std::vector<uint32_t>* seg_off,
                           std::vector<uint32_t>* seg_len);
 

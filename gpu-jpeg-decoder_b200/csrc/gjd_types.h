@@ -97,10 +97,11 @@ typedef struct GjdQuantSet {
     uint32_t packed[3][32];          /* q[c][2j] | q[c][2j+1] << 24: the words the transform's dp2a dequantisation takes */
 } GjdQuantSet;
 
-/* One independently decodable piece of entropy-coded data: the whole scan of an image without restart
- * markers, or one restart interval (the bytes between two RSTn markers; JPEG T.81 E.1.4: the decoder
- * state — component, zigzag index, DC predictors — is reset at every restart).  The entropy kernels
- * (k_huff_sync, k_huff_fix, k_seq_scan, k_huff_write) work on segments; sequences belong to a segment. */
+/* The entropy-coded data of one image's scan.  The entropy kernels (k_huff_sync, k_huff_fix, k_seq_scan, k_huff_write) work
+ * on segments; sequences belong to a segment.  Restart intervals (T.81 E.1.4: the decoder state — block in the MCU, zigzag
+ * index, DC predictors — is reset at every RSTn) lie back to back inside the segment, markers removed; the table of their
+ * start positions makes every restart a hard synchronisation point for the decoders (GjdRstTable, gjd_devfn.cuh).  (Round 1
+ * made every interval a segment of its own: one 256-thread block and one LUT copy per interval, most of it idle.) */
 typedef struct GjdSegment {
     uint64_t scan_off;      /* byte offset of the unstuffed bytes in the scan arena (4-byte aligned) */
     uint32_t scan_bits;     /* unstuffed length in bits (a trailing partial byte of 1-padding included) */
@@ -114,6 +115,11 @@ typedef struct GjdSegment {
     uint8_t  ny;            /* luma blocks per MCU: 1 (4:4:4, single-component), 2 (4:2:2, 4:4:0) or 4 (4:2:0); an MCU is
                                ny luma blocks + Cb + Cr, i.e. ny + 2 blocks (three for the single-component trick)      */
     uint8_t  pad0;
+    uint32_t rst_first;     /* restart intervals inside the scan: index of the segment's first entry in the rst arena ...     */
+    uint32_t rst_count;     /* ... and the number of entries = restart markers = intervals - 1 (0: no restart intervals);
+                               entry k - 1 = bit position in the unstuffed scan where interval k starts            */
+    uint32_t rst_blocks;    /* blocks per restart interval (restart_interval * blocks per MCU)                       */
+    uint32_t pad1;
 } GjdSegment;
 
 /* A scan that is unstuffed ON THE DEVICE (k_unstuff_*): the raw entropy-coded bytes as they stand in the file, from the

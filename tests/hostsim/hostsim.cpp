@@ -115,11 +115,26 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     std::vector<uint32_t> meta((size_t)tile_count * 96, 0);
     std::vector<uint8_t> written((size_t)tile_count * 96, 0);
     /* the entropy kernels run per segment (restart interval); one segment without restarts */
-    for (size_t sgi = 0; sgi < seg_off.size(); sgi++) {
-    const uint32_t* scan = scanw.data() + seg_off[sgi] / 4;
-    const uint32_t scan_bits = seg_len[sgi] * 8u;
-    const uint32_t blk0 = bpm * ri * (uint32_t)sgi;
-    const uint32_t blk_count = bpm * (ri ? std::min(ri, mcu_count - ri * (uint32_t)sgi) : mcu_count);
+    /* one segment per image; restart intervals lie back to back inside it (GjdRstTable: their start positions) */
+    std::vector<uint32_t> rst_bits;
+    for (size_t k = 1; k < seg_off.size(); k++) rst_bits.push_back(seg_off[k] * 8u);
+    const GjdRstTable rstt(rst_bits.data(), (uint32_t)rst_bits.size());
+    const uint32_t rst_blocks = bpm * ri;
+    const bool has_rst = !rst_bits.empty();
+    /* the four instantiations the kernels choose from (MCU shape x restart intervals) */
+    auto count_pairs = [&](const uint32_t*& sc, const GjdLutMem& l, uint32_t end, uint32_t bits, GjdState& st) {
+        if (has_rst) { if (subsamp) gjd_count_span_pairs(sc, l, end, bits, st, GjdRingSub(ny), rstt); else gjd_count_span_pairs(sc, l, end, bits, st, GjdRing444(), rstt); }
+        else if (subsamp) gjd_count_span_pairs(sc, l, end, bits, st, GjdRingSub(ny)); else gjd_count_span_pairs(sc, l, end, bits, st);
+    };
+    auto count_one = [&](const uint32_t*& sc, const GjdLutMem& l, uint32_t end, uint32_t bits, GjdState& st) {
+        if (has_rst) { if (subsamp) gjd_count_span(sc, l, end, bits, st, GjdRingSub(ny), rstt); else gjd_count_span(sc, l, end, bits, st, GjdRing444(), rstt); }
+        else if (subsamp) gjd_count_span(sc, l, end, bits, st, GjdRingSub(ny)); else gjd_count_span(sc, l, end, bits, st);
+    };
+    {
+    const uint32_t* scan = scanw.data();
+    const uint32_t scan_bits = (uint32_t)ulen * 8u;
+    const uint32_t blk0 = 0;
+    const uint32_t blk_count = bpm * mcu_count;
     const uint32_t sub_count = std::max<uint32_t>(1u, (uint32_t)(((uint64_t)scan_bits + S - 1) / S));
     const uint32_t seq_count = (sub_count + GJD_SEQ_SUBS - 1) / GJD_SEQ_SUBS;
     sub_total += sub_count; seq_total += seq_count;
@@ -141,11 +156,11 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                 endb[tid] = std::min(start + S, scan_bits);
                 if (sub != 0) {
                     st.p = start > GJD_LOOKBACK_BITS ? start - GJD_LOOKBACK_BITS : 0u;
-                    if (subsamp) gjd_count_span_pairs(scan, clut, start, scan_bits, st, GjdRingSub(ny)); else gjd_count_span_pairs(scan, clut, start, scan_bits, st);
+                    count_pairs(scan, clut, start, scan_bits, st);
                 }
                 in_p[tid] = st.p; in_pos[tid] = st.pos;
                 st.n = 0;
-                if (subsamp) gjd_count_span_pairs(scan, clut, endb[tid], scan_bits, st, GjdRingSub(ny)); else gjd_count_span_pairs(scan, clut, endb[tid], scan_bits, st);
+                count_pairs(scan, clut, endb[tid], scan_bits, st);
             }
             bp[tid] = st.p;
             bn[tid] = (st.n << GJD_POS_BITS) | st.pos;
@@ -161,7 +176,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                 uint32_t pp = bp[tid - 1], ppos = bn[tid - 1] & GJD_POS_MASK;
                 if (pp != in_p[tid] || ppos != in_pos[tid]) {
                     GjdState st; st.p = in_p[tid] = pp; st.pos = in_pos[tid] = ppos; st.n = 0;
-                    if (subsamp) gjd_count_span_pairs(scan, clut, endb[tid], scan_bits, st, GjdRingSub(ny)); else gjd_count_span_pairs(scan, clut, endb[tid], scan_bits, st);
+                    count_pairs(scan, clut, endb[tid], scan_bits, st);
                     np[tid] = st.p; nn[tid] = (st.n << GJD_POS_BITS) | st.pos;
                     badv[tid] = 1; any = true; redec++; if (r == 0) redec1++;
                 }
@@ -187,7 +202,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                 if (sub >= sub_count) { merged = true; break; }
                 st.n = 0;
                 uint32_t end = std::min((sub + 1) << sub_log2, scan_bits);
-                if (subsamp) gjd_count_span(scan, hlut, end, scan_bits, st, GjdRingSub(ny)); else gjd_count_span(scan, hlut, end, scan_bits, st);
+                count_one(scan, hlut, end, scan_bits, st);
                 fix_decodes++;
                 bool match = sp[base + t] == st.p && (sn[base + t] & GJD_POS_MASK) == st.pos;
                 sp[base + t] = st.p;
@@ -225,13 +240,17 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
             uint32_t idx0 = seq_base[g] + excl;
             if (idx0 % mcu_slots != st.pos && st.p < scan_bits) tbad |= GJD_DEV_BADSTATE;
             uint32_t end = std::min((sub + 1) << sub_log2, scan_bits);
-            if (subsamp) gjd_write_span(scan, hlut, end, scan_bits, st, idx0, blk_count, true, sink, tbad, GjdRingSub(ny)); else gjd_write_span(scan, hlut, end, scan_bits, st, idx0, blk_count, true, sink, tbad);
+            if (has_rst) {
+                if (subsamp) gjd_write_span(scan, hlut, end, scan_bits, st, idx0, blk_count, true, sink, tbad, GjdRingSub(ny), rstt, rst_blocks);
+                else gjd_write_span(scan, hlut, end, scan_bits, st, idx0, blk_count, true, sink, tbad, GjdRing444(), rstt, rst_blocks);
+            } else if (subsamp) gjd_write_span(scan, hlut, end, scan_bits, st, idx0, blk_count, true, sink, tbad, GjdRingSub(ny));
+            else gjd_write_span(scan, hlut, end, scan_bits, st, idx0, blk_count, true, sink, tbad);
             for (int k = 0; k < 64; k++) if (sink.stage[k]) tbad |= GJD_DEV_BADSTATE;   /* staging must be left clean */
             status |= tbad;
             excl += sn[a] >> GJD_POS_BITS;
         }
     }
-    }   /* segments */
+    }   /* the segment */
     for (uint32_t bk = 0; bk < bpm * mcu_count; bk++) if (written[bk] != 1) status |= GJD_DEV_BADCOUNT;
     if (badcode) status |= GJD_DEV_BADCODE;
     /* k_dc_tilebase + k_transform */
@@ -495,9 +514,14 @@ int hostsim_pair_check(const uint8_t* jpg, size_t len, int sub_log2, uint32_t lo
     two.set = lutS; two.badcode = nullptr;
     const uint32_t S = 1u << sub_log2;
     out[0] = out[1] = out[2] = out[3] = 0;
-    for (size_t sg = 0; sg < seg_off.size(); sg++) {
-        const uint32_t* scan = scanw.data() + seg_off[sg] / 4;
-        const uint32_t bits = seg_len[sg] * 8u;
+    {   /* the whole scan, its restart intervals inside it: both walks must make the same restart transitions */
+        const size_t sg = 0;
+        const uint32_t* scan = scanw.data();
+        const uint32_t bits = (uint32_t)ulen * 8u;
+        std::vector<uint32_t> rst_bits;
+        for (size_t k = 1; k < seg_off.size(); k++) rst_bits.push_back(seg_off[k] * 8u);
+        const GjdRstTable rstt(rst_bits.data(), (uint32_t)rst_bits.size());
+        const uint32_t ny = p.components == 1 ? 1u : p.hs * p.vs;
         GjdState truth; truth.p = 0; truth.n = 0; truth.pos = 0;
         for (uint32_t start = 0; start < bits; start += S) {
             const uint32_t end = std::min(start + S, bits);
@@ -506,8 +530,12 @@ int hostsim_pair_check(const uint8_t* jpg, size_t len, int sub_log2, uint32_t lo
                 if (cold) { a.p = start > lookback ? start - lookback : 0u; a.n = 0; a.pos = 0; }
                 else a = truth;
                 b = a;
-                g_syms_dbg = 0; gjd_count_span(scan, one, end, bits, a); out[2] += g_syms_dbg;
-                g_syms_dbg = 0; gjd_count_span_pairs(scan, two, end, bits, b); out[3] += g_syms_dbg;
+                g_syms_dbg = 0;
+                if (ny > 1u) gjd_count_span(scan, one, end, bits, a, GjdRingSub(ny), rstt); else gjd_count_span(scan, one, end, bits, a, GjdRing444(), rstt);
+                out[2] += g_syms_dbg;
+                g_syms_dbg = 0;
+                if (ny > 1u) gjd_count_span_pairs(scan, two, end, bits, b, GjdRingSub(ny), rstt); else gjd_count_span_pairs(scan, two, end, bits, b, GjdRing444(), rstt);
+                out[3] += g_syms_dbg;
                 out[0]++;
                 if (a.p != b.p || a.n != b.n || a.pos != b.pos) { out[1]++; if (getenv("GJD_PAIR_DEBUG")) fprintf(stderr, "seg %zu start %u end %u bits %u cold %d: single p=%u n=%u pos=%u  pair p=%u n=%u pos=%u\n", sg, start, end, bits, cold, a.p, a.n, a.pos, b.p, b.n, b.pos); }
                 if (!cold) truth = a;

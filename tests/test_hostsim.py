@@ -168,14 +168,16 @@ def test_restart_stream_errors(hostsim, rst_golden):
     assert hostsim.decode(cut)[0] in (-4, -6)
 
 
-def test_pair_counting_equals_single_symbol_counting(hostsim, golden, rst_golden):
+def test_pair_counting_equals_single_symbol_counting(hostsim, golden, rst_golden, sub_golden, gray_golden):
     """k_huff_sync counts with the pair LUT (two AC symbols per trip); every span — from the true state and
     from a cold start, three span lengths, every fixture incl. q100 (blocks ending exactly at index 63) and
     restart files — must leave the decoder in the state the single-symbol walk leaves it in."""
     import ctypes as C
     trips = syms = 0
     files = dict(golden)
-    files.update(rst_golden)
+    files.update(rst_golden)          # restart intervals inside the scan: both walks make the same transitions
+    files.update(sub_golden)          # 4:2:0 / 4:2:2 / 4:4:0 ring, with and without restarts
+    files.update(gray_golden)
     for name, data in sorted(files.items()):
         for sub_log2, lookback in ((8, 100), (10, 512), (12, 512)):
             out = np.zeros(4, np.uint64)

@@ -61,6 +61,16 @@ with gjd.Decoder(0) as dec:
                       "stages_ms": [round(x, 3) for x in med[:3]],
                       "MPixel_per_s": round(info["pixels"] / med[3] / 1e3, 1)}), flush=True)
 
+    # ---- C3 with restart intervals (one MCU row per interval, the usual camera setting): ADVICE r1 ----
+    rbase = [gen_synth.synth_jpeg(s, 1024, 1024, 90, False, 1) for s in range(16)]
+    nbase = [gen_synth.synth_jpeg(s, 1024, 1024, 90) for s in range(16)]
+    for label, base_files in (("c3 shape, 1000 x 1024x1024 q90, no restart markers", nbase),
+                              ("c3 shape, 1000 x 1024x1024 q90, DRI = one MCU row (128 intervals per image)", rbase)):
+        med, info = resident(dec, [base_files[i % 16] for i in range(1000)], 10)
+        print(json.dumps({"config": label, "subsequences": info["subseqs"], "device_ms": round(med[3], 3),
+                          "stages_ms": [round(x, 3) for x in med[:3]],
+                          "MPixel_per_s": round(info["pixels"] / med[3] / 1e3, 1)}), flush=True)
+
     # ---- C5 ----
     if n5 <= 0:
         sys.exit(0)
