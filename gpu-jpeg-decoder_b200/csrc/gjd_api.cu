@@ -288,10 +288,10 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     b->dhts.clear();
     b->quants.clear();
 
-    /* Where each scan is unstuffed.  On the device (k_unstuff_*): every scan without restart intervals — the raw bytes from
-     * the first scan byte to the end of the file are uploaded, straight from the caller's buffer when that is page-locked
-     * (adjacent files merge into one copy), through the pinned h_raw staging otherwise.  On the host
-     * (gjd_unstuff_segments): scans with restart intervals, whose intervals become segments the host has to size. */
+    /* Where each scan is unstuffed.  On the device (k_unstuff_*), the default: the raw bytes from the first scan byte to
+     * the end of the file are uploaded, straight from the caller's buffer when that is page-locked (adjacent files merge
+     * into one copy), through the pinned h_raw staging otherwise.  On the host (gjd_unstuff_segments) with
+     * GJD_DEVICE_UNSTUFF=0. */
     b->raws.clear();
     b->rst.clear();
     std::vector<uint8_t> mode(n, 0);                 /* 1 = device-unstuffed */
@@ -305,7 +305,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         size_t room = 0, hroom = 0;
         if (b->geom[i].status == GJD_OK) {
             const size_t rawlen = (size_t)(parsed[i].file_end - parsed[i].scan_begin);
-            mode[i] = ctx->device_unstuff && parsed[i].restart_interval == 0;
+            mode[i] = ctx->device_unstuff;
             if (mode[i]) {
                 room = align_up(rawlen + 64, 128);
                 if (!b->geom[i].jpg_pinned) { roff[i] = raw_staged; raw_staged += align_up(rawlen, 16) + 16; }
@@ -425,7 +425,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         }
         d.restart_interval = p.restart_interval;
         const uint32_t nseg = p.restart_interval ? (d.mcu_count + p.restart_interval - 1) / p.restart_interval : 1u;
-        if (p.restart_interval && rst_off[i].size() != nseg) { g.status = GJD_E_CORRUPT; continue; }
+        if (p.restart_interval && !mode[i] && rst_off[i].size() != nseg) { g.status = GJD_E_CORRUPT; continue; }
         uint16_t lut_id = 0;
         /* Huffman table set: dedup by content */
         {
@@ -486,7 +486,8 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
                 sg.rst_first = (uint32_t)b->rst.size();
                 sg.rst_count = nseg - 1;
                 sg.rst_blocks = bpm * p.restart_interval;
-                for (uint32_t k = 1; k < nseg; k++) b->rst.push_back(rst_off[i][k] * 8u);
+                /* (device-unstuffed scans: k_unstuff_write fills the table in) */
+                for (uint32_t k = 1; k < nseg; k++) b->rst.push_back(mode[i] ? 0u : rst_off[i][k] * 8u);
             }
             sg.lut_id = lut_id;
             sg.ny = (uint8_t)(d.gray ? 1u : (uint32_t)d.hs * d.vs);
@@ -500,6 +501,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
                 if (r.chunk_count == 0) r.chunk_count = 1;
                 r.seg = (uint32_t)b->segs.size();
                 r.img = (uint32_t)b->imgs.size();
+                r.dri = p.restart_interval != 0;
                 uchunk += r.chunk_count;
                 b->raws.push_back(r);
             }
@@ -566,20 +568,21 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     GJD_TRY(b->d_status.ensure((size_t)(n_img + 1) * sizeof(uint32_t), b->stream));
     GJD_TRY(b->d_ustatus.ensure((size_t)(n_img + 1) * sizeof(uint32_t), b->stream));
     GJD_TRY(b->d_raw.ensure(raw_total + 64, b->stream));
-    GJD_TRY(b->d_uchunk.ensure((size_t)(uchunk + 1) * 2 * sizeof(uint32_t), b->stream));
+    GJD_TRY(b->d_uchunk.ensure((size_t)(uchunk + 1) * 3 * sizeof(uint32_t), b->stream));
     GJD_TRY(b->d_rawmeta.ensure((b->raws.size() + 1) * 2 * sizeof(uint32_t), b->stream));
     GJD_TRY(b->h_status.ensure((size_t)(n_img + 1) * sizeof(uint32_t)));
 
     v.imgs = (const GjdImage*)((uint8_t*)b->d_meta.p + o_img);
     v.segs = (GjdSegment*)((uint8_t*)b->d_meta.p + o_seg);
     v.scan = (uint8_t*)b->d_scan.p;
-    v.rst = (const uint32_t*)((uint8_t*)b->d_meta.p + o_rst);
+    v.rst = (uint32_t*)((uint8_t*)b->d_meta.p + o_rst);
     v.raws = (const GjdRaw*)((uint8_t*)b->d_meta.p + o_raw);
     v.n_raw = (uint32_t)b->raws.size();
     v.n_uchunk = uchunk;
     v.raw = (const uint8_t*)b->d_raw.p;
     v.uchunk_raw = (uint32_t*)b->d_uchunk.p;
     v.uchunk_cnt = (uint32_t*)b->d_uchunk.p + uchunk;
+    v.uchunk_rst = (uint32_t*)b->d_uchunk.p + 2 * (size_t)uchunk;
     v.raw_eoi = (uint32_t*)b->d_rawmeta.p;
     v.raw_err = (uint32_t*)b->d_rawmeta.p + b->raws.size();
     v.ustatus = (uint32_t*)b->d_ustatus.p;
@@ -932,7 +935,8 @@ int gjd_batch_prepare(gjd_ctx* ctx, gjd_item* items, int32_t n, gjd_batch** out)
         const uint32_t* hst = (const uint32_t*)b->h_status.p;
         for (int32_t i = 0; rc == GJD_OK && i < n; i++)
             if (b->geom[i].status == GJD_OK && b->img_of[i] >= 0 && hst[b->img_of[i]])
-                b->geom[i].status = (hst[b->img_of[i]] & GJD_DEV_UFORMAT) ? GJD_E_FORMAT : GJD_E_UNSUPPORTED;
+                b->geom[i].status = (hst[b->img_of[i]] & GJD_DEV_UFORMAT) ? GJD_E_FORMAT
+                                    : (hst[b->img_of[i]] & GJD_DEV_UUNSUP) ? GJD_E_UNSUPPORTED : GJD_E_CORRUPT;
     }
     if (rc != GJD_OK) {
         b->release();

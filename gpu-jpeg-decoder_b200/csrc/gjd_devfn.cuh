@@ -138,8 +138,10 @@ GJD_HD uint32_t gjd_ring_slot(const uint8_t tabsel[8], uint32_t r) {
  * so 16 bytes per thread can be classified independently.  Masks have bit i = byte i of the 16 (memory order).
  */
 struct GjdUnstuffMasks {
-    uint32_t drop;   /* stuffed zeros and fill FFs                                   */
-    uint32_t mark;   /* FFs followed by a byte that is neither 00 nor FF (marker)     */
+    uint32_t drop;   /* stuffed zeros, fill FFs and (scans with restart intervals) both bytes of every RSTn   */
+    uint32_t mark;   /* FFs followed by a byte that is neither 00 nor FF: EOI or a stray marker (RSTn: only in
+                        scans without restart intervals, where it is an error)                                */
+    uint32_t rst;    /* scans with restart intervals: FFs that start an RSTn marker                            */
 };
 
 /* bit 7 of every byte of w that equals 0xFF / 0x00, gathered into a 4-bit mask (bit i = byte i) */
@@ -156,14 +158,16 @@ GJD_HD uint32_t gjd_bytes_004(uint32_t w) {
  * prev_ff = the byte before them is a scan byte equal to FF; next = the scan byte after them, next_valid = it exists
  * (an FF that is the last byte of the data is no marker: gjd_unstuff_segments stops there with "no EOI"). */
 GJD_HD GjdUnstuffMasks gjd_unstuff_classify(const uint32_t w[4], uint32_t valid, uint32_t prev_ff, uint32_t next,
-                                            uint32_t next_valid) {
-    uint32_t ff = 0, z = 0;
+                                            uint32_t next_valid, bool allow_rst = false) {
+    uint32_t ff = 0, z = 0, dn = 0;
     for (int j = 0; j < 4; j++) {
         ff |= gjd_bytes_ff4(w[j]) << (4 * j);
         z |= gjd_bytes_004(w[j]) << (4 * j);
+        dn |= gjd_bytes_004((w[j] ^ 0xd0d0d0d0u) & 0xf8f8f8f8u) << (4 * j);      /* bytes D0..D7 */
     }
     ff &= valid;
     z &= valid;
+    dn &= valid;
     const uint32_t nv = next_valid ? 1u : 0u;
     const uint32_t ff_next = (ff >> 1) | ((nv && next == 0xffu ? 1u : 0u) << 15);   /* byte i+1 is FF */
     const uint32_t z_next = (z >> 1) | ((nv && next == 0x00u ? 1u : 0u) << 15);     /* byte i+1 is 00 */
@@ -172,6 +176,13 @@ GJD_HD GjdUnstuffMasks gjd_unstuff_classify(const uint32_t w[4], uint32_t valid,
     GjdUnstuffMasks m;
     m.drop = (z & ff_prev) | (ff & ff_next);
     m.mark = ff & ~ff_next & ~z_next & has_next;
+    m.rst = 0;
+    if (allow_rst) {
+        const uint32_t dn_next = (dn >> 1) | ((nv && (next & 0xf8u) == 0xd0u ? 1u : 0u) << 15);   /* byte i+1 is D0..D7 */
+        m.rst = m.mark & dn_next;
+        m.mark &= ~dn_next;
+        m.drop |= m.rst | (dn & ff_prev);
+    }
     return m;
 }
 
@@ -192,14 +203,15 @@ struct GjdUnstuffLane {
 #define GJD_LDG8(p) ((uint32_t)*(p))
 #endif
 
-GJD_HD GjdUnstuffLane gjd_unstuff_lane_at(const uint8_t* raw, uint64_t raw_off, uint32_t raw_len, uint64_t a, uint32_t limit) {
+GJD_HD GjdUnstuffLane gjd_unstuff_lane_at(const uint8_t* raw, uint64_t raw_off, uint32_t raw_len, uint64_t a, uint32_t limit,
+                                          bool allow_rst = false) {
     GjdUnstuffLane L;
     const int64_t p0 = (int64_t)a - (int64_t)raw_off;                                 /* position in the scan of byte 0 */
     L.pos0 = (uint32_t)p0;
     L.valid = 0;
     L.next = 0;
     L.w[0] = L.w[1] = L.w[2] = L.w[3] = 0;
-    L.m.drop = L.m.mark = 0;
+    L.m.drop = L.m.mark = L.m.rst = 0;
     if (p0 >= (int64_t)limit || p0 + 16 <= 0) return L;
 #ifdef __CUDA_ARCH__
     const uint4 v = __ldg(reinterpret_cast<const uint4*>(raw + a));
@@ -218,9 +230,10 @@ GJD_HD GjdUnstuffLane gjd_unstuff_lane_at(const uint8_t* raw, uint64_t raw_off, 
     L.next = next_valid ? GJD_LDG8(raw + a + 16) : 0u;
     const uint32_t hi_file = (int64_t)raw_len - p0 < 16 ? (uint32_t)((int64_t)raw_len - p0) : 16u;
     const uint32_t valid_file = (0xffffu >> (16u - hi_file)) & (0xffffu << lo) & 0xffffu;
-    L.m = gjd_unstuff_classify(L.w, valid_file, prev_ff, L.next, next_valid);
+    L.m = gjd_unstuff_classify(L.w, valid_file, prev_ff, L.next, next_valid, allow_rst);
     L.m.drop &= L.valid;
     L.m.mark &= L.valid;
+    L.m.rst &= L.valid;
     return L;
 }
 

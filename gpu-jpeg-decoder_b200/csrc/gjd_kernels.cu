@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(128) k_fill_maps(GjdDevBatch b) {
 /* limit: positions >= limit are outside the scan (raw_len, or the EOI position in the write pass) */
 __device__ __forceinline__ GjdUnstuffLane gjd_unstuff_lane(const GjdDevBatch& b, const GjdRaw& r, uint32_t chunk, uint32_t limit) {
     const uint64_t a = (r.raw_off & ~(uint64_t)15) + (uint64_t)chunk * GJD_UCHUNK + threadIdx.x * 16u;   /* arena offset of byte 0 */
-    return gjd_unstuff_lane_at(b.raw, r.raw_off, r.raw_len, a, limit);
+    return gjd_unstuff_lane_at(b.raw, r.raw_off, r.raw_len, a, limit, r.dri != 0u);
 }
 
 __global__ void __launch_bounds__(256) k_unstuff_count(GjdDevBatch b) {
@@ -187,7 +187,8 @@ __global__ void __launch_bounds__(256) k_unstuff_count(GjdDevBatch b) {
         if (nb == 0xd9u) atomicMin(b.raw_eoi + ri, pos);
         else atomicMin(b.raw_err + ri, gjd_unstuff_err_word(pos, nb));
     }
-    uint32_t kept = __popc(L.valid & ~L.m.drop);
+    /* bytes kept (<= 4096 per chunk) and restart markers (<= 2048) in one sum: kept | markers << 16 */
+    uint32_t kept = __popc(L.valid & ~L.m.drop) | ((uint32_t)__popc(L.m.rst) << 16);
     kept = __reduce_add_sync(0xffffffffu, kept);
     if ((threadIdx.x & 31u) == 0u) ws[threadIdx.x >> 5] = kept;
     __syncthreads();
@@ -195,7 +196,8 @@ __global__ void __launch_bounds__(256) k_unstuff_count(GjdDevBatch b) {
         uint32_t t = 0;
 #pragma unroll
         for (int w = 0; w < 8; w++) t += ws[w];
-        b.uchunk_cnt[blockIdx.x] = t;
+        b.uchunk_cnt[blockIdx.x] = t & 0xffffu;
+        b.uchunk_rst[blockIdx.x] = t >> 16;
     }
 }
 
@@ -222,25 +224,31 @@ __global__ void __launch_bounds__(256) k_unstuff_scan(GjdDevBatch b, uint32_t* _
     /* exclusive scan of the chunk counts up to the chunk that holds the EOI */
     const uint32_t ce = (uint32_t)(((r.raw_off & 15u) + eoi) / GJD_UCHUNK);
     uint32_t* cnt = b.uchunk_cnt + r.chunk_first;
-    uint32_t carry = 0;
+    uint32_t* rcnt = b.uchunk_rst + r.chunk_first;
+    uint32_t carry = 0, rcarry = 0;
     for (uint32_t base = 0; base < ce; base += 256u) {
         const uint32_t c = base + tid;
-        const uint32_t v = c < ce ? cnt[c] : 0u;
-        uint32_t blocksum;
+        const uint32_t v = c < ce ? cnt[c] : 0u, rv = c < ce ? rcnt[c] : 0u;
+        uint32_t blocksum, rsum;
         const uint32_t excl = block_excl_scan_256(v, ws, &blocksum);
-        if (c < ce) cnt[c] = carry + excl;
+        const uint32_t rexcl = block_excl_scan_256(rv, ws, &rsum);
+        if (c < ce) { cnt[c] = carry + excl; rcnt[c] = rcarry + rexcl; }
         carry += blocksum;
+        rcarry += rsum;
     }
     /* the chunk with the EOI keeps only what lies before it */
     const GjdUnstuffLane L = gjd_unstuff_lane(b, r, ce, eoi);
     uint32_t blocksum;
-    block_excl_scan_256(__popc(L.valid & ~L.m.drop), ws, &blocksum);
-    const uint32_t total = carry + blocksum;
+    block_excl_scan_256(__popc(L.valid & ~L.m.drop) | ((uint32_t)__popc(L.m.rst) << 16), ws, &blocksum);
+    const uint32_t total = carry + (blocksum & 0xffffu), markers = rcarry + (blocksum >> 16);
     if (tid == 0) {
         cnt[ce] = carry;
+        rcnt[ce] = rcarry;
         sg.scan_bits = total * 8u;
         const uint32_t S = 1u << b.sub_log2;
         sg.sub_count = max(1u, (total * 8u + S - 1u) >> b.sub_log2);
+        /* as many RSTn as the frame size and DRI call for (the host loop: GJD_E_CORRUPT otherwise) */
+        if (markers != sg.rst_count) ustatus[r.img] = GJD_DEV_BADCOUNT;
     }
     if (tid < 16) b.scan[sg.scan_off + total + tid] = 0;     /* the bit window reads up to 12 bytes past the end */
 }
@@ -257,7 +265,21 @@ __global__ void __launch_bounds__(256) k_unstuff_write(GjdDevBatch b) {
     const GjdUnstuffLane L = gjd_unstuff_lane(b, r, chunk, eoi);
     uint32_t keep = L.valid & ~L.m.drop;
     uint32_t total;
-    uint32_t o = block_excl_scan_256(__popc(keep), ws, &total);
+    uint32_t o = block_excl_scan_256(__popc(keep) | ((uint32_t)__popc(L.m.rst) << 16), ws, &total);
+    total &= 0xffffu;
+    if (L.m.rst) {                                  /* restart markers: number them, check the 0..7 cycle, note where the
+                                                       next interval starts in the unstuffed scan */
+        const GjdSegment& sg = b.segs[r.seg];
+        uint32_t ord = b.uchunk_rst[blockIdx.x] + (o >> 16);
+        const uint32_t at0 = b.uchunk_cnt[blockIdx.x] + (o & 0xffffu);
+        for (uint32_t mk = L.m.rst; mk; mk &= mk - 1u, ord++) {
+            const uint32_t i = __ffs(mk) - 1u;
+            const uint32_t nb = i < 15u ? gjd_lane_byte(L, i + 1u) : L.next;
+            if (((nb - 0xd0u) & 7u) != (ord & 7u)) atomicOr(b.ustatus + r.img, GJD_DEV_UFORMAT);
+            if (ord < sg.rst_count) b.rst[sg.rst_first + ord] = (at0 + __popc(keep & ((1u << i) - 1u))) * 8u;
+        }
+    }
+    o &= 0xffffu;
     if (keep == 0xffffu && (o & 3u) == 0u) {
 #pragma unroll
         for (int j = 0; j < 4; j++) *reinterpret_cast<uint32_t*>(stage + o + 4 * j) = L.w[j];

@@ -16,7 +16,8 @@ struct GjdDevBatch {
     uint32_t n_img;
     GjdSegment* segs;      /* scan_bits / sub_count of device-unstuffed scans are written by k_unstuff_scan */
     uint32_t n_seg;
-    const uint32_t* rst;   /* restart-interval start positions of all segments (GjdSegment.rst_first / rst_count) */
+    uint32_t* rst;         /* restart-interval start positions of all segments (GjdSegment.rst_first / rst_count); written by the host
+                              for host-unstuffed scans and by k_unstuff_write for the others */
     uint8_t* scan;
     const GjdLutSet* luts;
     const GjdLutCount* lutc;   /* pair LUT rings of the count pass, same index as luts */
@@ -47,6 +48,7 @@ struct GjdDevBatch {
     const uint8_t* raw;    /* raw arena (>= 16 bytes of slack on both sides of every scan) */
     uint32_t* uchunk_raw;  /* [n_uchunk] chunk -> raw */
     uint32_t* uchunk_cnt;  /* [n_uchunk] bytes the chunk keeps; then (k_unstuff_scan) its exclusive prefix inside the scan */
+    uint32_t* uchunk_rst;  /* [n_uchunk] the same for the chunk's restart markers */
     uint32_t* raw_eoi;     /* [n_raw] position of the first EOI in the scan (0xffffffff: none) */
     uint32_t* raw_err;     /* [n_raw] smallest (position << 2 | GJD_UERR_*) (0xffffffff: none) */
     uint32_t* ustatus;     /* [n_img + 1] GJD_DEV_U* bits from the unstuffing (kept across runs of a resident batch), then 0 */

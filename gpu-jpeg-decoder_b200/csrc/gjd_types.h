@@ -133,7 +133,7 @@ typedef struct GjdRaw {
     uint32_t chunk_count;
     uint32_t seg;           /* its segment: scan_bits and sub_count are written by k_unstuff_scan      */
     uint32_t img;
-    uint32_t pad;
+    uint32_t dri;           /* the file has a DRI segment: RSTn markers are expected (and removed) instead of being an error */
 } GjdRaw;
 /* raw_err word: (position in the scan) << 2 | code; the smallest one before the EOI decides the image's status */
 #define GJD_UERR_FORMAT 1u       /* a marker other than RSTn / EOI inside the scan, or no EOI at all   */

@@ -81,9 +81,9 @@ class HostSim:
         self.lib.hostsim_pair_check.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_uint32, C.c_void_p]
         self.lib.hostsim_lut_check.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
         self.lib.hostsim_parse.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
-        self.lib.hostsim_unstuff_device.argtypes = [C.c_void_p, C.c_size_t, C.c_uint32, C.c_void_p]
+        self.lib.hostsim_unstuff_device.argtypes = [C.c_void_p, C.c_size_t, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
         self.lib.hostsim_unstuff_device.restype = C.c_long
-        self.lib.hostsim_unstuff_host.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
+        self.lib.hostsim_unstuff_host.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]
         self.lib.hostsim_unstuff_host.restype = C.c_long
 
     def parse(self, data):
@@ -92,13 +92,17 @@ class HostSim:
         return rc, w.value, h.value
 
     def unstuff_both(self, data, misalign=0):
-        """(host loop result, device-style result): each (length or negative status, bytes)."""
+        """(host loop result, device-style result): each (length or negative status, bytes + restart table)."""
         buf = C.cast(C.c_char_p(data), C.c_void_p)
         a = np.zeros(len(data) + 128, np.uint8)
         b = np.zeros(len(data) + 128, np.uint8)
-        ra = self.lib.hostsim_unstuff_host(buf, len(data), a.ctypes.data)
-        rb = self.lib.hostsim_unstuff_device(buf, len(data), misalign, b.ctypes.data)
-        return (ra, a[: max(ra, 0)].tobytes()), (rb, b[: max(rb, 0)].tobytes())
+        ta = np.zeros(len(data) // 2 + 8, np.uint32)
+        tb = np.zeros(len(data) // 2 + 8, np.uint32)
+        na, nb = C.c_uint32(0), C.c_uint32(0)
+        ra = self.lib.hostsim_unstuff_host(buf, len(data), a.ctypes.data, ta.ctypes.data, C.byref(na))
+        rb = self.lib.hostsim_unstuff_device(buf, len(data), misalign, b.ctypes.data, tb.ctypes.data, C.byref(nb))
+        return ((ra, a[: max(ra, 0)].tobytes() + ta[: na.value].tobytes() if ra >= 0 else b""),
+                (rb, b[: max(rb, 0)].tobytes() + tb[: nb.value].tobytes() if rb >= 0 else b""))
 
     def decode(self, data, sub_log2=0, ncoef=None):
         """ncoef: int16 coefficients to return (default: the 4:4:4 count, ceil(W/8)*ceil(H/8)*192; chroma-subsampled

@@ -551,10 +551,11 @@ int hostsim_pair_check(const uint8_t* jpg, size_t len, int sub_log2, uint32_t lo
  * product's own lane functions: the scan bytes of `jpg` are placed at arena offset 32 + misalign, classified 16 bytes per
  * "thread", 4 KB per "block", and compacted.  Returns the unstuffed length (bytes in out, which needs the raw length + 64)
  * or the negative gjd_status the kernels would report.  Must equal gjd_unstuff() for every input without DRI. */
-long hostsim_unstuff_device(const uint8_t* jpg, size_t len, uint32_t misalign, uint8_t* out) {
+long hostsim_unstuff_device(const uint8_t* jpg, size_t len, uint32_t misalign, uint8_t* out, uint32_t* rst_out, uint32_t* nrst_out) {
     GjdParsed p;
     int rc = gjd_parse_headers(jpg, len, &p);
     if (rc) return rc;
+    const bool dri = p.restart_interval != 0;
     const uint32_t raw_len = (uint32_t)(p.file_end - p.scan_begin);
     const uint64_t raw_off = 32 + (misalign & 15u);
     std::vector<uint8_t> arena(raw_off + raw_len + 64, 0xff);       /* slack filled with FF: must never be looked at */
@@ -562,10 +563,10 @@ long hostsim_unstuff_device(const uint8_t* jpg, size_t len, uint32_t misalign, u
     const uint64_t base16 = raw_off & ~(uint64_t)15;
     const uint32_t chunks = std::max<uint32_t>(1u, (uint32_t)(((raw_off & 15u) + raw_len + GJD_UCHUNK - 1) / GJD_UCHUNK));
     uint32_t eoi = 0xffffffffu, err = 0xffffffffu;
-    std::vector<uint32_t> cnt(chunks, 0);
+    std::vector<uint32_t> cnt(chunks, 0), rcnt(chunks, 0);
     for (uint32_t c = 0; c < chunks; c++)                            /* k_unstuff_count */
         for (uint32_t tid = 0; tid < 256; tid++) {
-            const GjdUnstuffLane L = gjd_unstuff_lane_at(arena.data(), raw_off, raw_len, base16 + (uint64_t)c * GJD_UCHUNK + tid * 16u, raw_len);
+            const GjdUnstuffLane L = gjd_unstuff_lane_at(arena.data(), raw_off, raw_len, base16 + (uint64_t)c * GJD_UCHUNK + tid * 16u, raw_len, dri);
             for (uint32_t mk = L.m.mark; mk; mk &= mk - 1u) {
                 const uint32_t i = (uint32_t)__builtin_ctz(mk);
                 const uint32_t nb = i < 15u ? gjd_lane_byte(L, i + 1u) : L.next;
@@ -574,6 +575,7 @@ long hostsim_unstuff_device(const uint8_t* jpg, size_t len, uint32_t misalign, u
                 else err = std::min(err, gjd_unstuff_err_word(pos, nb));
             }
             cnt[c] += (uint32_t)__builtin_popcount(L.valid & ~L.m.drop);
+            rcnt[c] += (uint32_t)__builtin_popcount(L.m.rst);
         }
     /* k_unstuff_scan */
     if (eoi == 0xffffffffu || (err != 0xffffffffu && (err >> 2) < eoi)) {
@@ -581,36 +583,59 @@ long hostsim_unstuff_device(const uint8_t* jpg, size_t len, uint32_t misalign, u
         return unsup ? GJD_E_UNSUPPORTED : GJD_E_FORMAT;
     }
     const uint32_t ce = (uint32_t)(((raw_off & 15u) + eoi) / GJD_UCHUNK);
-    std::vector<uint32_t> base(chunks, 0);
-    uint32_t carry = 0;
-    for (uint32_t c = 0; c < ce; c++) { base[c] = carry; carry += cnt[c]; }
+    std::vector<uint32_t> base(chunks, 0), rbase(chunks, 0);
+    uint32_t carry = 0, rcarry = 0;
+    for (uint32_t c = 0; c < ce; c++) { base[c] = carry; carry += cnt[c]; rbase[c] = rcarry; rcarry += rcnt[c]; }
     base[ce] = carry;
-    uint32_t total = carry;
+    rbase[ce] = rcarry;
+    uint32_t total = carry, markers = rcarry;
     for (uint32_t tid = 0; tid < 256; tid++) {
-        const GjdUnstuffLane L = gjd_unstuff_lane_at(arena.data(), raw_off, raw_len, base16 + (uint64_t)ce * GJD_UCHUNK + tid * 16u, eoi);
+        const GjdUnstuffLane L = gjd_unstuff_lane_at(arena.data(), raw_off, raw_len, base16 + (uint64_t)ce * GJD_UCHUNK + tid * 16u, eoi, dri);
         total += (uint32_t)__builtin_popcount(L.valid & ~L.m.drop);
+        markers += (uint32_t)__builtin_popcount(L.m.rst);
     }
     /* k_unstuff_write */
+    bool bad_cycle = false;
+    uint32_t nrst = 0;
     for (uint32_t c = 0; c < chunks; c++) {
         const int64_t cstart = (int64_t)c * GJD_UCHUNK - (int64_t)(raw_off & 15u);
         if (cstart >= (int64_t)eoi) continue;
-        uint32_t o = base[c];
+        uint32_t o = base[c], ord = rbase[c];
         for (uint32_t tid = 0; tid < 256; tid++) {
-            const GjdUnstuffLane L = gjd_unstuff_lane_at(arena.data(), raw_off, raw_len, base16 + (uint64_t)c * GJD_UCHUNK + tid * 16u, eoi);
-            for (uint32_t keep = L.valid & ~L.m.drop; keep; keep &= keep - 1u) out[o++] = (uint8_t)gjd_lane_byte(L, (uint32_t)__builtin_ctz(keep));
+            const GjdUnstuffLane L = gjd_unstuff_lane_at(arena.data(), raw_off, raw_len, base16 + (uint64_t)c * GJD_UCHUNK + tid * 16u, eoi, dri);
+            const uint32_t keep0 = L.valid & ~L.m.drop;
+            for (uint32_t mk = L.m.rst; mk; mk &= mk - 1u, ord++) {
+                const uint32_t i = (uint32_t)__builtin_ctz(mk);
+                const uint32_t nb = i < 15u ? gjd_lane_byte(L, i + 1u) : L.next;
+                if (((nb - 0xd0u) & 7u) != (ord & 7u)) bad_cycle = true;
+                if (rst_out) rst_out[ord] = (o + (uint32_t)__builtin_popcount(keep0 & ((1u << i) - 1u))) * 8u;
+                nrst = std::max(nrst, ord + 1u);
+            }
+            for (uint32_t keep = keep0; keep; keep &= keep - 1u) out[o++] = (uint8_t)gjd_lane_byte(L, (uint32_t)__builtin_ctz(keep));
         }
         if (c < ce && o != base[c + 1]) return -100;                 /* the count pass and the write pass disagree */
     }
+    if (bad_cycle) return GJD_E_FORMAT;
+    if (nrst != markers) return -101;
+    if (nrst_out) *nrst_out = nrst;
     memset(out + total, 0, 16);
     return (long)total;
 }
 
-/* the host byte loop on the same input (what the device path has to reproduce) */
-long hostsim_unstuff_host(const uint8_t* jpg, size_t len, uint8_t* out) {
+/* the host byte loop on the same input (what the device path has to reproduce); restart intervals: their start
+ * positions in bits, like the device's table */
+long hostsim_unstuff_host(const uint8_t* jpg, size_t len, uint8_t* out, uint32_t* rst_out, uint32_t* nrst_out) {
     GjdParsed p;
     int rc = gjd_parse_headers(jpg, len, &p);
     if (rc) return rc;
-    return gjd_unstuff(p.scan_begin, p.file_end, out);
+    if (!p.restart_interval) { if (nrst_out) *nrst_out = 0; return gjd_unstuff(p.scan_begin, p.file_end, out); }
+    std::vector<uint32_t> so, sl;
+    long m = gjd_unstuff_segments(p.scan_begin, p.file_end, out, &so, &sl);
+    if (m >= 0) {
+        for (size_t k = 1; k < so.size(); k++) if (rst_out) rst_out[k - 1] = so[k] * 8u;
+        if (nrst_out) *nrst_out = (uint32_t)so.size() - 1u;
+    }
+    return m;
 }
 
 }  /* extern "C" */

@@ -275,8 +275,8 @@ def test_device_unstuffing_equals_host_loop(hostsim, golden, gray_golden, rst_go
         at = f.find(b"\xff\xda")
         return at >= 0 and b"\xff\xdd" in f[:at]
 
-    files = [f for f in list(golden.values()) + list(gray_golden.values()) if not has_dri(f)]
-    assert len(files) >= 20
+    files = list(golden.values()) + list(gray_golden.values()) + list(rst_golden.values())     # with and without DRI
+    assert len(files) >= 30 and sum(has_dri(f) for f in files) >= 9
     for f in files:
         for mis in range(16):
             (ra, a), (rb, b) = hostsim.unstuff_both(f, mis)
@@ -301,15 +301,14 @@ def test_device_unstuffing_equals_host_loop(hostsim, golden, gray_golden, rst_go
     for k in range(16):                                                                   # marker pairs straddling 16-byte and 4 KB edges
         cases.append(head + body[:4096 * 2 - len(head) - 8 + k] + b"\xff\x00\xff\x00\xff\xff\x00" + body[9000:] + b"\xff\xd9")
     seen = set()
-    for f in cases + list(fuzzlib.cases([golden[n] for n in ("images/3_120x120", "images/5_200x200", "synth/s6_256x256_q90_o1")] , 600, 99)):
+    rst_seeds = [rst_golden[n] for n in sorted(rst_golden)[:3]]     # damaged restart files: wrong cycle, missing / extra markers
+    for f in cases + list(fuzzlib.cases([golden[n] for n in ("images/3_120x120", "images/5_200x200", "synth/s6_256x256_q90_o1")] + rst_seeds, 900, 99)):
         for mis in (0, 5, 15):
             (ra, a), (rb, b) = hostsim.unstuff_both(f, mis)
             rc, w, h = hostsim.parse(f)
             if rc != 0:
                 assert ra == rc and rb == rc
                 continue
-            if has_dri(f):
-                continue                                  # scans with restart intervals stay on the host path
             assert ra == rb, (ra, rb, mis)
             if ra >= 0:
                 assert a == b
