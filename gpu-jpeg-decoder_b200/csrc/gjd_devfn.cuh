@@ -259,8 +259,14 @@ GJD_HD uint32_t gjd_bswap32(uint32_t x) {
 /* Two cached big-endian words of the scan (wi = index of w0) plus the word after them, still in memory
  * byte order: it is loaded one refill ahead of its use so that the load latency hides behind the symbols
  * decoded in between (the byte swap waits for the data, so it is deferred to the next refill). */
+#ifndef GJD_WIN_AHEAD
+#define GJD_WIN_AHEAD 2            /* refills between the load of a word and its first use (1 or 2; A/B: profiles/r02l_win_ahead_ab.txt) */
+#endif
 struct GjdWin {
     uint32_t wi, w0, w1, w2raw;
+#if GJD_WIN_AHEAD > 1
+    uint32_t w3raw;                /* the word after w2raw: loaded two refills (64 bits of symbols) ahead of its use */
+#endif
 };
 
 /* Where the words of the scan come from.  The decoders are templates over the source: a plain pointer (global memory on
@@ -338,17 +344,25 @@ GJD_HD void gjd_win_init(GjdWin& c, Src& scan, uint32_t p) {
     c.w0 = gjd_bswap32(gjd_scan_word(scan, c.wi));
     c.w1 = gjd_bswap32(gjd_scan_word(scan, c.wi + 1));
     c.w2raw = gjd_scan_word(scan, c.wi + 2);
+#if GJD_WIN_AHEAD > 1
+    c.w3raw = gjd_scan_word(scan, c.wi + 3);
+#endif
 }
 
 /* 32 bits of the scan starting at bit p (MSB first).  p may advance by at most 32 bits per call.
- * Reads up to 12 bytes past the word that holds p (the scan arena is padded). */
+ * Reads up to 4 * (GJD_WIN_AHEAD + 2) bytes past the start of the word that holds p (the scan arena is padded). */
 template <class Src>
 GJD_HD uint32_t gjd_peek32(GjdWin& c, Src& scan, uint32_t p) {
     uint32_t wi = p >> 5;
     if (wi != c.wi) {
         c.w0 = c.w1;
         c.w1 = gjd_bswap32(c.w2raw);
+#if GJD_WIN_AHEAD > 1
+        c.w2raw = c.w3raw;
+        c.w3raw = gjd_scan_word(scan, wi + 3);
+#else
         c.w2raw = gjd_scan_word(scan, wi + 2);
+#endif
         c.wi = wi;
     }
 #ifdef __CUDA_ARCH__
@@ -673,7 +687,7 @@ GJD_HD void gjd_write_span(Src& scan, const Lut& lut, uint32_t end_bits, uint32_
                            Rst rst = Rst(), uint32_t rst_blocks = 0) {
     uint32_t run = (enable && s.p < end_bits) ? 1u : 0u;
     GjdWin win;
-    win.wi = 0; win.w0 = 0; win.w1 = 0; win.w2raw = 0;
+    win = GjdWin();
     if (run) gjd_win_init(win, scan, s.p);
     uint32_t p = s.p, z = s.pos & 63u, tb = ring.of_pos(s.pos);
     uint32_t blk = (idx0 + 63u) >> 6;

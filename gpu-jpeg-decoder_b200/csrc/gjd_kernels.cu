@@ -319,7 +319,10 @@ __global__ void __launch_bounds__(256) k_unstuff_write(GjdDevBatch b) {
  * After the reference's parallelHuffManDecode (cuda-decoder/src/parser.cu:132-173), which continues
  * every thread through whole slices instead.
  */
-__global__ void __launch_bounds__(GJD_SYNC_THREADS, 8) k_huff_sync(GjdDevBatch b) {
+#ifndef GJD_SYNC_MINB
+#define GJD_SYNC_MINB 8            /* resident blocks per SM of the count pass: 8 x 256 threads = every thread slot, 32 registers */
+#endif
+__global__ void __launch_bounds__(GJD_SYNC_THREADS, GJD_SYNC_MINB) k_huff_sync(GjdDevBatch b) {
     __shared__ GjdLutSet lut;
     __shared__ uint32_t sp[GJD_SEQ_SUBS];
     __shared__ uint32_t sn[GJD_SEQ_SUBS];
