@@ -260,7 +260,7 @@ GJD_HD uint32_t gjd_bswap32(uint32_t x) {
  * byte order: it is loaded one refill ahead of its use so that the load latency hides behind the symbols
  * decoded in between (the byte swap waits for the data, so it is deferred to the next refill). */
 #ifndef GJD_WIN_AHEAD
-#define GJD_WIN_AHEAD 2            /* refills between the load of a word and its first use (1 or 2; A/B: profiles/r02l_win_ahead_ab.txt) */
+#define GJD_WIN_AHEAD 1            /* refills between the load of a word and its first use; 2 was measured: write 6.30 -> 6.92 ms (profiles/r02l_win_ahead_ab.txt) */
 #endif
 struct GjdWin {
     uint32_t wi, w0, w1, w2raw;

@@ -320,7 +320,7 @@ __global__ void __launch_bounds__(256) k_unstuff_write(GjdDevBatch b) {
  * every thread through whole slices instead.
  */
 #ifndef GJD_SYNC_MINB
-#define GJD_SYNC_MINB 8            /* resident blocks per SM of the count pass: 8 x 256 threads = every thread slot, 32 registers */
+#define GJD_SYNC_MINB 6            /* resident blocks per SM of the count pass: 40 registers; 8 (32 registers) spills since the decoders carry ring and restart state: 1.95 vs 2.00 ms (profiles/r02l_win_ahead_ab.txt) */
 #endif
 __global__ void __launch_bounds__(GJD_SYNC_THREADS, GJD_SYNC_MINB) k_huff_sync(GjdDevBatch b) {
     __shared__ GjdLutSet lut;
