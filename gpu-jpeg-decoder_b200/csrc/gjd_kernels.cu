@@ -538,10 +538,13 @@ struct GjdWriteSink {
 #define GJD_WRITE_LUT_BYTES sizeof(GjdLutSet)
 #define GJD_WRITE_MINB 4
 #endif
+#ifndef GJD_WRITE_SMEM_EXTRA
+#define GJD_WRITE_SMEM_EXTRA 0u    /* experiment knob: unused shared memory per block, lowers the resident blocks per SM (4 -> 3 at 20 KB, -> 2 at 56 KB) */
+#endif
 #ifdef GJD_SCAN_TMA
 #define GJD_WRITE_SMEM (GJD_WRITE_LUT_BYTES + 8u * GJD_WRITE_THREADS * sizeof(uint4) + 2u * GJD_SEQ_SUBS * GJD_RING_CHUNK + 16u * GJD_SEQ_SUBS)
 #else
-#define GJD_WRITE_SMEM (GJD_WRITE_LUT_BYTES + 8u * GJD_WRITE_THREADS * sizeof(uint4))   /* dynamic: > 48 KB with the whole set */
+#define GJD_WRITE_SMEM (GJD_WRITE_LUT_BYTES + 8u * GJD_WRITE_THREADS * sizeof(uint4) + GJD_WRITE_SMEM_EXTRA)   /* dynamic: > 48 KB with the whole set */
 #endif
 __global__ void __launch_bounds__(GJD_WRITE_THREADS, GJD_WRITE_MINB) k_huff_write(GjdDevBatch b) {
     extern __shared__ uint4 dyn_smem[];
