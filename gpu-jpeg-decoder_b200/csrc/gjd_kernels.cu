@@ -1630,3 +1630,126 @@ cudaError_t gjd_launch_test_idct(const int16_t* coef, size_t nblocks, const int3
     k_test_idct<<<(unsigned)((nblocks + GJD_TRANSFORM_THREADS - 1) / GJD_TRANSFORM_THREADS), GJD_TRANSFORM_THREADS, 0, s>>>(coef, nblocks, quant, out);
     return cudaGetLastError();
 }
+
+/* ------------------------------------------------------------------ no-allocation entry point ---- */
+/*
+ * gjd_idct_blocks_static (include/gjd.h): what gjd_test_idct does, for callers that cannot call cudaMalloc.
+ * gjd_test_idct keeps its device-side scratch (the staged coefficients, the expanded quantisation table, the staged
+ * samples) in three stream-ordered allocations; here that scratch is one file-scope device array, so the call allocates
+ * nothing.  Every GPU that loads libgjd.so holds the array until the process exits.
+ *
+ *   [0, 256)                     header; word 0 = blocks the kernel finished (cleared by every call, checked after it)
+ *   [256, 512)                   the quantisation table, 64 int32 in zigzag order
+ *   [512, 512 + MAX*128)         coefficients, int16 zigzag, 128 bytes per block
+ *   [512 + MAX*128, +MAX*128)    samples, int16 natural order
+ *
+ * The array keeps the last call's contents; the one thing that must start at zero (the header word) is cleared per call.
+ * All calls share it: two calls that overlap on the GPU would race, so the entry point holds a process-wide lock and is
+ * synchronous on return.  In host code g_idct_static is only the host-side stand-in of the symbol — the device address
+ * comes from cudaGetSymbolAddress, once per device, with that device current.
+ */
+#define GJD_STATIC_HDR   256u
+#define GJD_STATIC_QOFF  256u
+#define GJD_STATIC_COEF  512u
+#define GJD_STATIC_BYTES (GJD_STATIC_COEF + 2u * (size_t)GJD_STATIC_IDCT_MAX_BLOCKS * 128u)
+#define GJD_STATIC_MAX_DEVICES 64
+
+static __device__ __align__(256) unsigned char g_idct_static[GJD_STATIC_BYTES];
+
+/* k_test_idct with the quantisation table and the finished-blocks word in the static array (named directly: device code
+ * may); coef and out are addresses inside the same array, handed in by the host from cudaGetSymbolAddress */
+__global__ void __launch_bounds__(GJD_TRANSFORM_THREADS) k_idct_blocks_static(const int16_t* __restrict__ coef, uint32_t nblocks,
+                                                                               int16_t* __restrict__ out) {
+    __shared__ uint32_t sq[32];
+    __shared__ uint32_t finished;
+    if (threadIdx.x < 32) sq[threadIdx.x] = gjd_pack_quant(reinterpret_cast<const int*>(g_idct_static + GJD_STATIC_QOFF), threadIdx.x);
+    if (threadIdx.x == 0) finished = 0u;
+    __syncthreads();
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nblocks) {
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(coef + (size_t)i * 64);
+        uint32_t w[32];
+#pragma unroll
+        for (int j = 0; j < 32; j++) w[j] = src[j];
+        int v[64];
+        GjdUnpack<63, 64>::run(w, sq, v);
+        v[0] = (int)(int16_t)(w[0] & 0xffffu) * (int)(sq[0] & 0xffu);
+        gjd_idct8x8(v);
+#pragma unroll
+        for (int j = 0; j < 64; j++) out[(size_t)i * 64 + j] = (int16_t)(v[j] - 256);
+        atomicAdd(&finished, 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && finished) atomicAdd(reinterpret_cast<uint32_t*>(g_idct_static), finished);
+}
+
+#include <cstdio>
+#include <mutex>
+
+namespace {
+std::mutex g_static_mu;                                        /* one call at a time: the array is shared */
+unsigned char* g_static_dev[GJD_STATIC_MAX_DEVICES] = {};      /* device address of g_idct_static, per device */
+
+int static_fail(char* errbuf, size_t errbuf_len, int rc, const char* what, cudaError_t e) {
+    if (errbuf && errbuf_len)
+        snprintf(errbuf, errbuf_len, "gjd_idct_blocks_static: %s%s%s", what, e != cudaSuccess ? ": " : "",
+                 e != cudaSuccess ? cudaGetErrorString(e) : "");
+    return rc;
+}
+}  /* namespace */
+
+extern "C" int gjd_idct_blocks_static(int cuda_device, const int16_t* coef_zz, size_t nblocks, const uint8_t quant_zz[64],
+                                      int16_t* samples, char* errbuf, size_t errbuf_len) {
+    if (errbuf && errbuf_len) errbuf[0] = 0;
+    if (!coef_zz || !quant_zz || !samples) return static_fail(errbuf, errbuf_len, GJD_E_ARG, "NULL argument", cudaSuccess);
+    if (cuda_device < 0 || cuda_device >= GJD_STATIC_MAX_DEVICES)
+        return static_fail(errbuf, errbuf_len, GJD_E_ARG, "device index out of range", cudaSuccess);
+    if (nblocks > (size_t)GJD_STATIC_IDCT_MAX_BLOCKS) {
+        if (errbuf && errbuf_len)
+            snprintf(errbuf, errbuf_len, "gjd_idct_blocks_static: %zu blocks exceed the static scratch, GJD_STATIC_IDCT_MAX_BLOCKS = %d "
+                     "(split the call, or use gjd_test_idct, which allocates)", nblocks, (int)GJD_STATIC_IDCT_MAX_BLOCKS);
+        return GJD_E_ARG;
+    }
+    if (nblocks == 0) return GJD_OK;
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    int prev = -1;
+    cudaError_t e = cudaGetDevice(&prev);
+    if (e != cudaSuccess) return static_fail(errbuf, errbuf_len, GJD_E_NODEVICE, "no usable CUDA device", e);
+    if (prev != cuda_device && (e = cudaSetDevice(cuda_device)) != cudaSuccess)
+        return static_fail(errbuf, errbuf_len, GJD_E_NODEVICE, "cudaSetDevice", e);
+    int rc = GJD_OK;
+    const char* what = "";
+    do {
+        unsigned char*& base = g_static_dev[cuda_device];
+        if (!base) {   /* set-up, once per device, with that device current */
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_idct_static);
+            if (e != cudaSuccess || !p) { what = "cudaGetSymbolAddress"; break; }
+            base = static_cast<unsigned char*>(p);
+        }
+        int16_t* d_coef = reinterpret_cast<int16_t*>(base + GJD_STATIC_COEF);
+        int16_t* d_out = d_coef + (size_t)GJD_STATIC_IDCT_MAX_BLOCKS * 64;
+        int32_t hq[64];
+        for (int i = 0; i < 64; i++) hq[i] = quant_zz[i];
+        /* everything on the legacy default stream, synchronous copies: no stream, event or buffer is created */
+        what = "clear header";
+        if ((e = cudaMemset(base, 0, GJD_STATIC_HDR)) != cudaSuccess) break;
+        what = "copy quantisation table";
+        if ((e = cudaMemcpy(base + GJD_STATIC_QOFF, hq, sizeof hq, cudaMemcpyHostToDevice)) != cudaSuccess) break;
+        what = "copy coefficients";
+        if ((e = cudaMemcpy(d_coef, coef_zz, nblocks * 128, cudaMemcpyDefault)) != cudaSuccess) break;
+        what = "launch";
+        k_idct_blocks_static<<<(unsigned)((nblocks + GJD_TRANSFORM_THREADS - 1) / GJD_TRANSFORM_THREADS), GJD_TRANSFORM_THREADS>>>(
+            d_coef, (uint32_t)nblocks, d_out);
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        what = "copy samples";
+        if ((e = cudaMemcpy(samples, d_out, nblocks * 128, cudaMemcpyDefault)) != cudaSuccess) break;
+        what = "read header";
+        uint32_t finished = 0;
+        if ((e = cudaMemcpy(&finished, base, sizeof finished, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if (finished != (uint32_t)nblocks) { rc = static_fail(errbuf, errbuf_len, GJD_E_CUDA, "the kernel did not finish every block", cudaSuccess); }
+    } while (0);
+    if (e != cudaSuccess) rc = static_fail(errbuf, errbuf_len, GJD_E_CUDA, what, e);
+    if (prev != cuda_device && prev >= 0) cudaSetDevice(prev);
+    return rc;
+}

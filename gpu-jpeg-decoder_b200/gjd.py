@@ -66,6 +66,7 @@ def lib():
     L.gjd_stage_times.argtypes = [vp, C.POINTER(C.c_float)]
     L.gjd_test_color.argtypes = [vp, vp, vp, vp, sz, vp, vp, vp]
     L.gjd_test_idct.argtypes = [vp, vp, sz, vp, vp]
+    L.gjd_idct_blocks_static.argtypes = [C.c_int, vp, sz, vp, vp, C.c_char_p, sz]
     L.gjd_host_alloc.argtypes = [sz]
     L.gjd_host_alloc.restype = vp
     L.gjd_host_free.argtypes = [vp]
@@ -304,6 +305,29 @@ class ResidentBatch:
         if self.h:
             lib().gjd_batch_free(self.dec._ctx, self.h)
             self.h = None
+
+
+STATIC_IDCT_MAX_BLOCKS = 8192   # GJD_STATIC_IDCT_MAX_BLOCKS (include/gjd.h)
+
+
+def idct_blocks_static(coef_zz, quant_zz, device=0, out=None):
+    """gjd_idct_blocks_static: Decoder.test_idct without a context and without any device allocation (the scratch is a
+    static device array inside libgjd.so).  coef_zz / out may also be integer device addresses (then pass nblocks rows
+    through `coef_zz=(ptr, nblocks)` and `out=ptr`); numpy arrays are host memory."""
+    q = np.ascontiguousarray(quant_zz, np.uint8)
+    if isinstance(coef_zz, tuple):
+        src, n = coef_zz
+        result = dst = out
+    else:
+        coef_zz = np.ascontiguousarray(coef_zz, np.int16).reshape(-1, 64)
+        src, n = coef_zz.ctypes.data, coef_zz.shape[0]
+        result = np.empty_like(coef_zz) if out is None else out
+        dst = result if isinstance(result, int) else result.ctypes.data
+    err = C.create_string_buffer(256)
+    rc = lib().gjd_idct_blocks_static(device, src, n, q.ctypes.data, dst, err, len(err))
+    if rc != OK:
+        raise GjdError(rc, err.value.decode())
+    return result
 
 
 def write_array(path, rgb):

@@ -149,6 +149,23 @@ int  gjd_test_color(gjd_ctx* ctx, const int16_t* y, const int16_t* cb, const int
 int  gjd_test_idct(gjd_ctx* ctx, const int16_t* coef_zz, size_t nblocks, const uint8_t quant_zz[64],
                    int16_t* samples);
 
+/* gjd_test_idct for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid allocation).  It has NO counterpart in the reference.
+ * Same arithmetic and same results as gjd_test_idct, but the device-side scratch (staged
+ * coefficients, expanded quantisation table, staged samples, a finished-blocks word) lives in one file-scope
+ * `static __device__` array of 512 + 256 * GJD_STATIC_IDCT_MAX_BLOCKS bytes (2 MiB + 512 B), which every GPU that
+ * loads the library holds until the process exits.  The call uses no gjd_ctx, runs on the legacy default stream of
+ * `cuda_device`, and calls no cudaMalloc / cudaFree / cudaMallocAsync, creates no stream or event.
+ *   coef_zz, samples : caller-owned, host or device memory (copied with cudaMemcpyDefault), 64 int16 per block.
+ *   nblocks          : at most GJD_STATIC_IDCT_MAX_BLOCKS; more is rejected with GJD_E_ARG and a message in errbuf.
+ *   errbuf           : optional (may be NULL): receives a one-line description of any failure.
+ * The array is shared by every call and keeps the last call's contents (the word that must start at zero is cleared
+ * by each call).  Calls that overlapped on the GPU would race on it: the entry point therefore takes a process-wide
+ * lock and is synchronous on return; this is the one piece of process-global state behind this ABI. */
+#define GJD_STATIC_IDCT_MAX_BLOCKS 8192
+int  gjd_idct_blocks_static(int cuda_device, const int16_t* coef_zz, size_t nblocks, const uint8_t quant_zz[64],
+                            int16_t* samples, char* errbuf, size_t errbuf_len);
+
 /* Multi-GPU sharding (host-only, no CUDA): assign n independent images to `parts` devices by greedy
  * longest-processing-time on the padded pixel count 8*ceil(W/8) * 8*ceil(H/8) (the unit both the
  * coefficient traffic and, roughly, the scan bits follow).  Deterministic: ties go to the lower image
