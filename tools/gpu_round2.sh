@@ -10,6 +10,12 @@ case $what in
 tests)
   timeout 1200 python -m pytest tests -m gpu -q > $out/${tag}_pytest_gpu.txt 2>&1; echo "pytest rc=$?" >> $out/${tag}_pytest_gpu.txt
   tail -5 $out/${tag}_pytest_gpu.txt ;;
+zz)
+  # the allocation-free entry point alone, in a fresh process (it must not depend on what the other tests left behind)
+  timeout 600 python -m pytest tests/test_zz_no_alloc.py -m gpu -q > $out/${tag}_pytest_zz_alone.txt 2>&1; echo "zz alone rc=$?" >> $out/${tag}_pytest_zz_alone.txt
+  tail -3 $out/${tag}_pytest_zz_alone.txt ;;
+ablibs)
+  bash tools/ab_libs.sh $tag ${AB_LIBS:-default} ;;
 bench)
   timeout 600 python bench.py --steps 10 --warmup 3 > $out/${tag}_bench.json 2> $out/${tag}_bench.err; echo "bench rc=$?"
   cat $out/${tag}_bench.json; tail -3 $out/${tag}_bench.err ;;
