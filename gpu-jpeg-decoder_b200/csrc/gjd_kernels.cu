@@ -804,6 +804,20 @@ __device__ __forceinline__ void gjd_store_row_i16(uint8_t* px, uint64_t r8, uint
  * EXPORT = true is the coefficient test hook: blocks are written out in the reference layout
  * mcu*192 + comp*64 + k with the absolute DC in slot 0 instead of being transformed.
  */
+/* Rows of the colour phase per warp: [0, B1) for the luma warp, [B1, B2) and [B2, 8) for the chroma warps.  The three warps
+ * meet at one barrier per tile, so a tile takes as long as its slowest warp, and on photographic tiles that is the luma
+ * warp (full 64-coefficient transform, ~6 colour rows' worth of instructions, against ~3 for the pruned chroma one): 16 % of
+ * the kernel's warp time was barrier wait with the 2/3/3 split (profiles/r02n_k_transform.hotspots.txt).  Measured on C3
+ * (profiles/r02p_transform_split_ab.txt): 3/3/2 6.85 ms, 2/3/3 6.82, 1/3/4 6.77, 0/4/4 6.72.  A per-tile choice from the
+ * classes the warps actually took (a byte per warp in shared memory) cost 0.4 ms: one more live value across the butterfly
+ * spills 28 bytes inside it at the 72-register cap. */
+#ifndef GJD_COLOR_ROWS_B1
+#define GJD_COLOR_ROWS_B1 0u
+#define GJD_COLOR_ROWS_B2 4u
+#endif
+#ifndef GJD_TRANSFORM_HOIST
+#define GJD_TRANSFORM_HOIST 1      /* image geometry in registers + reciprocal multiply for the MCU row (0: re-read per tile, divide) */
+#endif
 #ifndef GJD_TRANSFORM_MINB
 #define GJD_TRANSFORM_MINB 9       /* resident blocks per SM of the planar transform: 72 registers, 24 KB of shared memory */
 #endif
@@ -836,17 +850,26 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
     const bool wide = ILV && d.layout == GJD_LAYOUT_INTERLEAVED_I16;      /* int16 elements: 6 bytes per pixel */
     const bool aligned = (((size_t)out | pitch | (interleaved ? 0 : pstride)) & (wide ? 15u : 7u)) == 0;
     const uint32_t* q = QGLOBAL ? b.quants[d.quant_id].packed[c] : sq[c];
+#if GJD_TRANSFORM_HOIST
+    /* the image's geometry in registers: behind the per-tile __syncthreads the compiler has to re-read d.* from memory, and
+     * the division by mcus_x (I2F/MUFU/fix-up, 20 instructions per tile and lane) becomes a multiply-high and one fix-up */
+    const uint32_t mcus_x = d.mcus_x, tile_count = d.tile_count, mcu_count = d.mcu_count, tile_first = d.tile_first;
+    const uint32_t mcus_x_inv = 0xffffffffu / mcus_x;
+#else
+    const uint32_t& mcus_x = d.mcus_x; const uint32_t& tile_count = d.tile_count; const uint32_t& mcu_count = d.mcu_count;
+    const uint32_t& tile_first = d.tile_first;
+#endif
 
 #pragma unroll 1
     for (uint32_t t = 0; t < b.tb_tiles; t++) {
         const uint32_t ltile = ltb * b.tb_tiles + t;
-        if (ltile >= d.tile_count) break;
+        if (ltile >= tile_count) break;
         const uint32_t mcu = ltile * GJD_TILE_MCUS + lane;
-        const bool valid = mcu < d.mcu_count;
-        const size_t blk = (size_t)(d.tile_first + ltile) * 96u + lane * 3u + c;
+        const bool valid = mcu < mcu_count;
+        const size_t blk = (size_t)(tile_first + ltile) * 96u + lane * 3u + c;
 
         /* ---- transform phase: component c of MCU `lane` ---- */
-        if (t + 1u < b.tb_tiles && ltile + 1u < d.tile_count) {
+        if (t + 1u < b.tb_tiles && ltile + 1u < tile_count) {
             /* the next tile's coefficient line and meta word on their way to L2 while this tile computes */
             asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const uint4*>(b.coef) + (blk + 96u) * 8u));
             if (lane < 12u && c == 0u) asm volatile("prefetch.global.L2 [%0];" ::"l"(b.meta + blk + 96u - lane * 3u + lane * 8u));
@@ -862,12 +885,12 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
             if ((uint32_t)j < nchunk) r = __ldcs(src + j);
             w[4 * j] = r.x; w[4 * j + 1] = r.y; w[4 * j + 2] = r.z; w[4 * j + 3] = r.w;
         }
-        const int4 tb = b.tilebase[d.tile_first + ltile];
+        const int4 tb = b.tilebase[tile_first + ltile];
         int dc = warp_incl_scan_i((int)(int16_t)(m & 0xffffu), lane);
         if (d.restart_interval == 0u) {
             dc += c == 0 ? tb.x : c == 1 ? tb.y : tb.z;
         } else {
-            dc = gjd_restart_dc(b.tilebase + d.tile_first, b.meta + (size_t)d.tile_first * 96u, d.restart_interval,
+            dc = gjd_restart_dc(b.tilebase + tile_first, b.meta + (size_t)tile_first * 96u, d.restart_interval,
                                 ltile, mcu, c, lane, dc, tb);
         }
         if (EXPORT) {
@@ -884,15 +907,20 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
         else gjd_block_to_samples<64>(w, q, dc, &smp[t & 1u][c][0][lane]);
         __syncthreads();
 
-        /* ---- colour phase: rows c, c+3, c+6 of MCU `lane` ---- */
-        const uint32_t by = mcu / d.mcus_x, bx = mcu - by * d.mcus_x;
+        /* ---- colour phase: some of the 8 rows of MCU `lane` ---- */
+#if GJD_TRANSFORM_HOIST
+        uint32_t by = __umulhi(mcu, mcus_x_inv), bx = mcu - by * mcus_x;     /* floor or floor - 1 (mcu < 2^27) */
+        if (bx >= mcus_x) { by++; bx -= mcus_x; }
+#else
+        const uint32_t by = mcu / mcus_x, bx = mcu - by * mcus_x;
+#endif
         const uint32_t x0 = bx * 8u, y0 = by * 8u;
         const bool fast = aligned && (x0 + 8u <= W);
-        /* rows 0-1 for the luma warp (its transform is the long one), 2-4 and 5-7 for the chroma warps */
-        const uint32_t r0 = c == 0u ? 0u : 3u * c - 1u;
+        const uint32_t r0 = c == 0u ? 0u : c == 1u ? GJD_COLOR_ROWS_B1 : GJD_COLOR_ROWS_B2;
+        const uint32_t rend = c == 0u ? GJD_COLOR_ROWS_B1 : c == 1u ? GJD_COLOR_ROWS_B2 : 8u;
         /* rows of this warp that exist in the image (none for lanes past the last MCU) */
         const uint32_t rows_left = (valid && y0 < H) ? H - y0 : 0u;
-        const uint32_t r1 = min(3u * c + 2u, rows_left);
+        const uint32_t r1 = min(rend, rows_left);
         uint8_t* rowp = out + (size_t)(y0 + r0) * pitch + (interleaved ? (size_t)x0 * (wide ? 6u : 3u) : (size_t)x0);
 #pragma unroll 1
         for (uint32_t r = r0; r < r1; r++, rowp += pitch) {

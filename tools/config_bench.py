@@ -71,6 +71,14 @@ with gjd.Decoder(0) as dec:
                           "stages_ms": [round(x, 3) for x in med[:3]],
                           "MPixel_per_s": round(info["pixels"] / med[3] / 1e3, 1)}), flush=True)
 
+    # ---- C3 shape, chroma-subsampled: the same 16 pictures encoded 4:2:2 and 4:2:0 ----
+    for label, sample in (("4:2:2 (-sample 2x1)", "2x1"), ("4:2:0 (-sample 2x2)", "2x2")):
+        sbase = [gen_synth.synth_jpeg(s, 1024, 1024, 90, False, 0, sample) for s in range(16)]
+        med, info = resident(dec, [sbase[i % 16] for i in range(1000)], 10)
+        print(json.dumps({"config": "c3 shape, 1000 x 1024x1024 q90, " + label, "subsequences": info["subseqs"],
+                          "scan_bytes": info["scan_bytes"], "device_ms": round(med[3], 3), "stages_ms": [round(x, 3) for x in med[:3]],
+                          "MPixel_per_s": round(info["pixels"] / med[3] / 1e3, 1)}), flush=True)
+
     # ---- C5 ----
     if n5 <= 0:
         sys.exit(0)

@@ -46,11 +46,11 @@ def make_image(seed, w, h):
     return np.clip(img, 0, 255).astype(np.uint8)
 
 
-def encode(img, quality=90, optimize=False, restart=0, grayscale=False):
-    """RGB uint8 (H,W,3) -> JPEG bytes via vendored cjpeg."""
+def encode(img, quality=90, optimize=False, restart=0, grayscale=False, sample="1x1"):
+    """RGB uint8 (H,W,3) -> JPEG bytes via vendored cjpeg (sample: the luma sampling factors, "2x2" = 4:2:0, "2x1" = 4:2:2)."""
     h, w, _ = img.shape
     ppm = b"P6\n%d %d\n255\n" % (w, h) + img.tobytes()
-    cmd = [os.path.join(LIBJPEG, "bin", "cjpeg"), "-quality", str(quality), "-sample", "1x1", "-baseline"]
+    cmd = [os.path.join(LIBJPEG, "bin", "cjpeg"), "-quality", str(quality), "-sample", sample, "-baseline"]
     if optimize:
         cmd.append("-optimize")
     if restart:
@@ -61,13 +61,13 @@ def encode(img, quality=90, optimize=False, restart=0, grayscale=False):
     return subprocess.run(cmd, input=ppm, stdout=subprocess.PIPE, check=True, env=env).stdout
 
 
-def synth_jpeg(seed, w, h, quality=90, optimize=False, restart=0):
-    key = f"s{seed}_{w}x{h}_q{quality}_o{int(optimize)}_r{restart}"
+def synth_jpeg(seed, w, h, quality=90, optimize=False, restart=0, sample="1x1"):
+    key = f"s{seed}_{w}x{h}_q{quality}_o{int(optimize)}_r{restart}" + ("" if sample == "1x1" else "_" + sample)
     path = os.path.join(CACHE, key + ".jpg")
     if os.path.exists(path):
         with open(path, "rb") as f:
             return f.read()
-    data = encode(make_image(seed, w, h), quality, optimize, restart)
+    data = encode(make_image(seed, w, h), quality, optimize, restart, False, sample)
     os.makedirs(CACHE, exist_ok=True)
     tmp = path + ".%d.tmp" % os.getpid()
     with open(tmp, "wb") as f:

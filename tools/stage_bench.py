@@ -1,5 +1,5 @@
 """A/B of kernel variants on a resident c3 batch: median CUDA-event stage times per GJD_TRANSFORM_VARIANT.
-usage: python tools/stage_bench.py [images] [runs] [variants, comma separated]"""
+usage: python tools/stage_bench.py [images] [runs] [variants, comma separated] [c3|c5 = which synthetic set is tiled]"""
 import os
 import statistics
 import sys
@@ -13,7 +13,7 @@ import gjd
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 3000
 runs = int(sys.argv[2]) if len(sys.argv) > 2 else 10
 variants = [int(v) for v in (sys.argv[3] if len(sys.argv) > 3 else "0").split(",")]
-base = gen_synth.c3_files()
+base = gen_synth.c5_files(256) if (len(sys.argv) > 4 and sys.argv[4] == "c5") else gen_synth.c3_files()
 files = [base[i % len(base)] for i in range(n)]
 for v in variants:
     os.environ["GJD_TRANSFORM_VARIANT"] = str(v)
