@@ -480,11 +480,13 @@ GJD_HD uint32_t gjd_ring_next(uint32_t tb, uint32_t z, uint32_t zn) {
  *               the MCU remain (yl counts them).  pos = block-in-MCU * 64 + zigzag index, up to (ny + 2) * 64 - 1.
  * Only whole blocks change anything, so the per-symbol path of the 4:4:4 decoders is untouched by the second one. */
 struct GjdRing444 {
+    static constexpr bool sub = false;
     GJD_HD uint32_t of_pos(uint32_t pos) { return gjd_ring_of_pos(pos); }
     GJD_HD uint32_t next(uint32_t tb, uint32_t z, uint32_t zn) { return gjd_ring_next(tb, z, zn); }
     GJD_HD uint32_t slots() const { return 192u; }
 };
 struct GjdRingSub {
+    static constexpr bool sub = true;
     uint32_t ny, yl;
     GJD_HD explicit GjdRingSub(uint32_t ny_) : ny(ny_), yl(0) {}
     GJD_HD uint32_t of_pos(uint32_t pos) {

@@ -354,7 +354,8 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS, GJD_SYNC_MINB) k_huff_sync(G
         uint32_t in_p = 0, in_pos = 0;
         if (active) {
             if (sub != 0u) {
-                st.p = start > GJD_LOOKBACK_BITS ? start - GJD_LOOKBACK_BITS : 0u;
+                const uint32_t lookback = decltype(ring)::sub ? GJD_LOOKBACK_SUB_BITS : GJD_LOOKBACK_BITS;
+                st.p = start > lookback ? start - lookback : 0u;
                 gjd_count_span_pairs(scan, slut, start, scan_bits, st, ring, rst);
             }
             in_p = st.p; in_pos = st.pos;
@@ -747,8 +748,8 @@ __device__ __forceinline__ uint32_t gjd_pack_quant(const int* q, uint32_t j) {
 }
 
 /* dequantise + dezigzag + IDCT of one block (w: packed zigzag coefficients, dc: absolute DC), then park
- * the 64 samples (biased, u16) in shared memory rows dst[r * 32] */
-template <int KLIM>
+ * the 64 samples (biased, u16) in shared memory rows dst[r * RSTRIDE] */
+template <int KLIM, int RSTRIDE = 32>
 __device__ __forceinline__ void gjd_block_to_samples(const uint32_t* w, const uint32_t* qq, int dc, uint4* dst) {
     int v[64];
     GjdUnpack<63, KLIM>::run(w, qq, v);
@@ -756,7 +757,7 @@ __device__ __forceinline__ void gjd_block_to_samples(const uint32_t* w, const ui
     gjd_idct8x8(v);
 #pragma unroll
     for (int r = 0; r < 8; r++)
-        dst[r * 32] = make_uint4((uint32_t)v[8 * r + 1] * 65536u + (uint32_t)v[8 * r],
+        dst[r * RSTRIDE] = make_uint4((uint32_t)v[8 * r + 1] * 65536u + (uint32_t)v[8 * r],
                                  (uint32_t)v[8 * r + 3] * 65536u + (uint32_t)v[8 * r + 2],
                                  (uint32_t)v[8 * r + 5] * 65536u + (uint32_t)v[8 * r + 4],
                                  (uint32_t)v[8 * r + 7] * 65536u + (uint32_t)v[8 * r + 6]);
@@ -794,7 +795,7 @@ __device__ __forceinline__ void gjd_store_row_i16(uint8_t* px, uint64_t r8, uint
  *                    meta), warp-scan the DC differences onto the tile's DC base, dequantise + dezigzag
  *                    into 64 registers, integer IDCT in registers, park the 64 samples (biased, 9 bits,
  *                    as u16) in shared memory [comp][row][lane] — conflict-free 128-bit stores.
- *   colour phase     the warps split the 8 rows (2/3/3): lane l reads row r of Y, Cb, Cr of MCU l (three
+ *   colour phase     the warps split the 8 rows (GJD_COLOR_ROWS_*): lane l reads row r of Y, Cb, Cr of MCU l (three
  *                    128-bit loads), converts 8 pixels and stores 8 bytes per plane; a warp covers 256
  *                    contiguous bytes of an image row.
  * The sample buffer is double-buffered, so one __syncthreads per tile separates the phases.
@@ -1361,10 +1362,9 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_gray(Gjd
  *   k_transform_sub  one thread per line: dequantise, dezigzag, IDCT (the same gjd_idct8x8 as everything else), samples
  *                    parked in shared memory; then 8-pixel row pieces: luma sample + the chroma sample that covers it
  *                    (sample replication, i.e. libjpeg's h2v1 / h2v2 "non-fancy" upsampling), the reference's colour
- *                    formula (gjd_color), 8-byte stores.
+ *                    formula (gjd_color_row8, the packed form of the 4:4:4 kernel), 8-byte stores.
  * Pin (no reference output exists): coefficients against jpeg_read_coefficients of the reference's vendored libjpeg 9e,
  * pixels against the oracle's IDCT + replication + the oracle's colour function (tools/make_golden_sub.py).
- * Correct first: these kernels are not tuned.
  */
 /* Inclusive SEGMENTED scan over a 256-thread block: v summed from the nearest thread at or below with head = true (from
  * `carry`, the running value in front of the block, when there is none).  Returns the thread's value; *carry_out = the
@@ -1420,10 +1420,55 @@ __global__ void __launch_bounds__(256) k_dc_sub(GjdDevBatch b, int* __restrict__
     }
 }
 
+/* 8 pixels of one image row, R/G/B as 8 clamped bytes each (two words), in any of the three layouts */
+__device__ __forceinline__ void gjd_store_pixels8(uint8_t* rowp, size_t pstride, const uint32_t* pr, const uint32_t* pg, const uint32_t* pb,
+                                                  uint32_t n, bool fast, bool interleaved, bool wide) {
+    const uint64_t r8 = ((uint64_t)pr[1] << 32) | pr[0], g8 = ((uint64_t)pg[1] << 32) | pg[0], b8 = ((uint64_t)pb[1] << 32) | pb[0];
+    if (wide) {
+        gjd_store_row_i16(rowp, r8, g8, b8, n, fast);
+    } else if (fast && !interleaved) {
+        __stcs(reinterpret_cast<uint2*>(rowp), make_uint2(pr[0], pr[1]));
+        __stcs(reinterpret_cast<uint2*>(rowp + pstride), make_uint2(pg[0], pg[1]));
+        __stcs(reinterpret_cast<uint2*>(rowp + 2 * pstride), make_uint2(pb[0], pb[1]));
+    } else if (fast) {
+        /* word j of the 24 bytes: __byte_perm picks from {a: bytes 0-3, b: bytes 4-7} */
+        const uint32_t w0 = __byte_perm(__byte_perm(pr[0], pg[0], 0x1040), pb[0], 0x3410);   /* R0 G0 B0 R1 */
+        const uint32_t w1 = __byte_perm(__byte_perm(pg[0], pb[0], 0x2051), pr[0], 0x3610);   /* G1 B1 R2 G2 */
+        const uint32_t w2 = __byte_perm(__byte_perm(pb[0], pr[0], 0x3072), pg[0], 0x3710);   /* B2 R3 G3 B3 */
+        const uint32_t w3 = __byte_perm(__byte_perm(pr[1], pg[1], 0x1040), pb[1], 0x3410);
+        const uint32_t w4 = __byte_perm(__byte_perm(pg[1], pb[1], 0x2051), pr[1], 0x3610);
+        const uint32_t w5 = __byte_perm(__byte_perm(pb[1], pr[1], 0x3072), pg[1], 0x3710);
+        __stcs(reinterpret_cast<uint2*>(rowp), make_uint2(w0, w1));
+        __stcs(reinterpret_cast<uint2*>(rowp + 8), make_uint2(w2, w3));
+        __stcs(reinterpret_cast<uint2*>(rowp + 16), make_uint2(w4, w5));
+    } else {
+#pragma unroll 1
+        for (uint32_t x = 0; x < n; x++) {
+            const uint8_t R = (uint8_t)(r8 >> (8u * x)), G = (uint8_t)(g8 >> (8u * x)), B = (uint8_t)(b8 >> (8u * x));
+            if (interleaved) { rowp[3u * x] = R; rowp[3u * x + 1u] = G; rowp[3u * x + 2u] = B; }
+            else { rowp[x] = R; rowp[pstride + x] = G; rowp[2 * pstride + x] = B; }
+        }
+    }
+}
+
+/*
+ * One thread block (3 warps) per b.tb_tiles tiles of one image; a tile is 96 coefficient lines = 16 MCUs of 6 blocks (4:2:0)
+ * or 24 MCUs of 4 (4:2:2, 4:4:0).
+ *   transform phase  thread -> line: the tile's luma lines first, then its Cb lines, then its Cr lines, so that whole warps
+ *                    hold chroma blocks and take the pruned transform (4:2:0: warps 0-1 luma, warp 2 chroma); samples parked
+ *                    as rows of 8 (uint4) at smp[row][line in scan order], double-buffered: one barrier per tile.
+ *   colour phase     thread -> 8-pixel column of the tile's pixel rows (MCU, luma block column): consecutive lanes write
+ *                    consecutive 8-byte pieces of an image row; per row the luma row of its block and the half (hs = 2) or
+ *                    whole chroma row that covers it, replicated on 16-bit lanes (PRMT), through the packed colour function
+ *                    of the 4:4:4 kernel (gjd_color_row8) and the same stores.
+ */
+#ifndef GJD_SUB_MINB
+#define GJD_SUB_MINB 8
+#endif
 template <bool EXPORT>
-__global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_sub(GjdDevBatch b, const int* __restrict__ dcabs,
-                                                                             int16_t* __restrict__ coef_out) {
-    __shared__ uint16_t smp[96][64];                        /* samples (biased, 9 bits) of the tile's 96 blocks */
+__global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, GJD_SUB_MINB) k_transform_sub(GjdDevBatch b, const int* __restrict__ dcabs,
+                                                                                        int16_t* __restrict__ coef_out) {
+    __shared__ uint4 smp[2][8][96];                         /* [tile parity][row][line of the tile]: 8 samples (biased, 9 bits, u16) */
     const uint32_t tid = threadIdx.x;
     const GjdImage& d = b.imgs[b.tb_img[blockIdx.x]];
     const uint32_t hs = d.hs, vs = d.vs, ny = hs * vs;
@@ -1436,18 +1481,31 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_sub(GjdD
     const bool interleaved = d.layout != GJD_LAYOUT_PLANAR;
     const bool wide = d.layout == GJD_LAYOUT_INTERLEAVED_I16;
     const bool aligned = (((size_t)out | pitch | (interleaved ? 0 : pstride)) & (wide ? 15u : 7u)) == 0;
-    const uint32_t nlines = d.mcu_count * nblk;
+    const uint32_t mcu_count = d.mcu_count, tile_count = d.tile_count, mcus_x = d.mcus_x;
+    const uint32_t mcus_x_inv = 0xffffffffu / mcus_x;
+    const uint32_t nlines = mcu_count * nblk;
     const size_t line0 = (size_t)d.tile_first * 96u;
-    const GjdQuantSet& qs = b.quants[d.quant_id];
     const uint32_t mcus_tile = 96u / nblk;                  /* 96 = 24 x 4 = 16 x 6: a tile holds whole MCUs */
+    /* transform phase: this thread's line of the tile */
+    const uint32_t nluma = mcus_tile * ny;
+    uint32_t tml, tbp;                                      /* MCU in the tile, block in the MCU */
+    if (tid < nluma) { tml = tid / ny; tbp = tid - tml * ny; }
+    else { const uint32_t k = tid - nluma, cc = k >= mcus_tile ? 1u : 0u; tml = k - cc * mcus_tile; tbp = ny + cc; }
+    const uint32_t tline = tml * nblk + tbp;
+    const uint32_t c = tbp < ny ? 0u : tbp - ny + 1u;
+    const uint32_t* qq = b.quants[d.quant_id].packed[c];
+    /* colour phase: this thread's column of 8 pixels and its first row */
+    const uint32_t cols = mcus_tile * hs, rpi = GJD_TRANSFORM_THREADS / cols;   /* 32/3 (4:2:0), 48/2 (4:2:2), 24/4 (4:4:0) */
+    const uint32_t row0 = tid / cols, col = tid - row0 * cols;
+    const uint32_t cml = hs == 2u ? col >> 1 : col, cbx = hs == 2u ? col & 1u : 0u;
+    const uint32_t vshift = vs - 1u;                        /* chroma row = pixel row of the MCU >> vshift */
 
 #pragma unroll 1
     for (uint32_t t = 0; t < b.tb_tiles; t++) {
         const uint32_t ltile = ltb * b.tb_tiles + t;
-        if (ltile >= d.tile_count) break;
-        const uint32_t j = ltile * 96u + tid;               /* line inside the image */
+        if (ltile >= tile_count) break;
+        const uint32_t j = ltile * 96u + tline;             /* line inside the image */
         const bool valid = j < nlines;
-        const uint32_t bp = j % nblk, c = bp < ny ? 0u : bp - ny + 1u;
         const uint32_t m = valid ? __ldg(b.meta + line0 + j) : 0u;
         const uint32_t kmax = (m >> 16) & 63u;
         const uint32_t nchunk = kmax ? (kmax >> 3) + 1u : 0u;
@@ -1469,55 +1527,39 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_sub(GjdD
             }
             continue;
         }
-        {
-            int v[64];
-            const uint32_t* qq = qs.packed[c];
-            GjdUnpack<63, 64>::run(w, qq, v);
-            v[0] = dc * (int)(qq[0] & 0xffu);
-            gjd_idct8x8(v);
-            __syncthreads();                                /* the previous tile's colour phase is done with smp */
-#pragma unroll
-            for (int i = 0; i < 64; i += 2) *reinterpret_cast<uint32_t*>(&smp[tid][i]) = (uint32_t)v[i] | ((uint32_t)v[i + 1] << 16);
-        }
+        if (__reduce_max_sync(0xffffffffu, kmax) < 16u) gjd_block_to_samples<16, 96>(w, qq, dc, &smp[t & 1u][0][tline]);
+        else gjd_block_to_samples<64, 96>(w, qq, dc, &smp[t & 1u][0][tline]);
         __syncthreads();
-        /* colour: pieces of 8 pixels = one row of one luma block */
-        const uint32_t pieces = mcus_tile * ny * 8u;
-        for (uint32_t pc = tid; pc < pieces; pc += GJD_TRANSFORM_THREADS) {
-            const uint32_t ml = pc / (ny * 8u), rem = pc - ml * (ny * 8u), yb = rem >> 3, r = rem & 7u;
-            const uint32_t mcu = ltile * mcus_tile + ml;
-            if (mcu >= d.mcu_count) continue;
-            const uint32_t my = mcu / d.mcus_x, mx = mcu - my * d.mcus_x;
-            const uint32_t bx = yb % hs, byy = yb / hs;                         /* the luma block's place in the MCU */
-            const uint32_t x0 = (mx * hs + bx) * 8u, y = (my * vs + byy) * 8u + r;
-            if (y >= H || x0 >= W) continue;
-            const uint16_t* ys = &smp[ml * nblk + yb][r * 8u];
-            const uint16_t* cbs = &smp[ml * nblk + ny][0];
-            const uint16_t* crs = &smp[ml * nblk + ny + 1u][0];
-            const uint32_t cy = (byy * 8u + r) / vs;                            /* chroma row that covers this luma row */
-            uint64_t r8 = 0, g8 = 0, b8 = 0;
-#pragma unroll
-            for (uint32_t x = 0; x < 8u; x++) {
-                const uint32_t cx = (bx * 8u + x) / hs;
-                int R, G, B;
-                gjd_color((int)ys[x], (int)cbs[cy * 8u + cx], (int)crs[cy * 8u + cx], R, G, B);
-                r8 |= (uint64_t)R << (8u * x); g8 |= (uint64_t)G << (8u * x); b8 |= (uint64_t)B << (8u * x);
-            }
-            const bool fast = aligned && x0 + 8u <= W;
-            uint8_t* row = out + (size_t)y * pitch + (size_t)x0 * (interleaved ? (wide ? 6u : 3u) : 1u);
-            if (wide) {
-                gjd_store_row_i16(row, r8, g8, b8, min(8u, W - x0), fast);
-            } else if (fast && !interleaved) {
-                __stcs(reinterpret_cast<uint2*>(row), make_uint2((uint32_t)r8, (uint32_t)(r8 >> 32)));
-                __stcs(reinterpret_cast<uint2*>(row + pstride), make_uint2((uint32_t)g8, (uint32_t)(g8 >> 32)));
-                __stcs(reinterpret_cast<uint2*>(row + 2 * pstride), make_uint2((uint32_t)b8, (uint32_t)(b8 >> 32)));
-            } else {
+
+        const uint32_t mcu = ltile * mcus_tile + cml;
+        if (row0 >= rpi || mcu >= mcu_count) continue;      /* (96 = rpi * cols for the three shapes: no thread is left over) */
+        uint32_t my = __umulhi(mcu, mcus_x_inv), mx = mcu - my * mcus_x;     /* floor or floor - 1 (mcu < 2^27) */
+        if (mx >= mcus_x) { my++; mx -= mcus_x; }
+        const uint32_t x0 = (mx * hs + cbx) * 8u, ytop = my * vs * 8u;
+        if (x0 >= W) continue;
+        const bool fast = aligned && x0 + 8u <= W;
+        const uint32_t npx = min(8u, W - x0);
+        const uint4* sm = &smp[t & 1u][0][cml * nblk];
+        uint8_t* rowp = out + (size_t)(ytop + row0) * pitch + (size_t)x0 * (interleaved ? (wide ? 6u : 3u) : 1u);
 #pragma unroll 1
-                for (uint32_t x = 0; x < 8u && x0 + x < W; x++) {
-                    const uint8_t R = (uint8_t)(r8 >> (8u * x)), G = (uint8_t)(g8 >> (8u * x)), B = (uint8_t)(b8 >> (8u * x));
-                    if (interleaved) { row[3u * x] = R; row[3u * x + 1u] = G; row[3u * x + 2u] = B; }
-                    else { row[x] = R; row[pstride + x] = G; row[2 * pstride + x] = B; }
-                }
+        for (uint32_t row = row0; row < vs * 8u && ytop + row < H; row += rpi, rowp += (size_t)rpi * pitch) {
+            const uint32_t r = row & 7u, yb = (row >> 3) * hs + cbx, cy = row >> vshift;
+            const uint4 y4 = sm[r * 96u + yb], b4 = sm[cy * 96u + ny], r4 = sm[cy * 96u + ny + 1u];
+            const uint32_t yw[4] = {y4.x, y4.y, y4.z, y4.w};
+            uint32_t bw[4], rw[4];
+            if (hs == 2u) {     /* block-uniform: each chroma sample covers two pixels; this luma block sees one half of the chroma row */
+                const uint32_t bl = cbx ? b4.z : b4.x, bh = cbx ? b4.w : b4.y, rl = cbx ? r4.z : r4.x, rh = cbx ? r4.w : r4.y;
+                bw[0] = __byte_perm(bl, 0u, 0x1010); bw[1] = __byte_perm(bl, 0u, 0x3232);
+                bw[2] = __byte_perm(bh, 0u, 0x1010); bw[3] = __byte_perm(bh, 0u, 0x3232);
+                rw[0] = __byte_perm(rl, 0u, 0x1010); rw[1] = __byte_perm(rl, 0u, 0x3232);
+                rw[2] = __byte_perm(rh, 0u, 0x1010); rw[3] = __byte_perm(rh, 0u, 0x3232);
+            } else {
+                bw[0] = b4.x; bw[1] = b4.y; bw[2] = b4.z; bw[3] = b4.w;
+                rw[0] = r4.x; rw[1] = r4.y; rw[2] = r4.z; rw[3] = r4.w;
             }
+            uint32_t pr[2], pg[2], pb[2];
+            gjd_color_row8(yw, bw, rw, pr, pg, pb);
+            gjd_store_pixels8(rowp, pstride, pr, pg, pb, npx, fast, interleaved, wide);
         }
     }
 }

@@ -28,6 +28,9 @@
 #define GJD_SUB_LOG2_MIN   10u      /* subsequence (one thread) = 2^k bits, k chosen per batch:        */
 #define GJD_SUB_LOG2_MAX   13u      /* long enough to amortise the look-back, short enough to fill the GPU */
 #define GJD_LOOKBACK_BITS 512u     /* cold-start distance before a subsequence (k_huff_sync)          */
+#ifndef GJD_LOOKBACK_SUB_BITS
+#define GJD_LOOKBACK_SUB_BITS 512u /* the same for chroma-subsampled scans (MCUs of 4 or 6 blocks)    */
+#endif
 #define GJD_SEQ_SUBS      256u     /* subsequences per sequence (one thread block) */
 #ifndef GJD_LUT_BITS
 #define GJD_LUT_BITS      10       /* primary Huffman LUT index width (9 or 10: the secondary LUT covers 6 more bits) */

@@ -155,7 +155,8 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                 uint32_t start = sub << sub_log2;
                 endb[tid] = std::min(start + S, scan_bits);
                 if (sub != 0) {
-                    st.p = start > GJD_LOOKBACK_BITS ? start - GJD_LOOKBACK_BITS : 0u;
+                    const uint32_t lookback = subsamp ? GJD_LOOKBACK_SUB_BITS : GJD_LOOKBACK_BITS;
+                    st.p = start > lookback ? start - lookback : 0u;
                     count_pairs(scan, clut, start, scan_bits, st);
                 }
                 in_p[tid] = st.p; in_pos[tid] = st.pos;

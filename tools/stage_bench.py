@@ -1,5 +1,5 @@
 """A/B of kernel variants on a resident c3 batch: median CUDA-event stage times per GJD_TRANSFORM_VARIANT.
-usage: python tools/stage_bench.py [images] [runs] [variants, comma separated] [c3|c5 = which synthetic set is tiled]"""
+usage: python tools/stage_bench.py [images] [runs] [variants, comma separated] [c3|c5|422|420 = which synthetic set is tiled]"""
 import os
 import statistics
 import sys
@@ -13,7 +13,13 @@ import gjd
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 3000
 runs = int(sys.argv[2]) if len(sys.argv) > 2 else 10
 variants = [int(v) for v in (sys.argv[3] if len(sys.argv) > 3 else "0").split(",")]
-base = gen_synth.c5_files(256) if (len(sys.argv) > 4 and sys.argv[4] == "c5") else gen_synth.c3_files()
+which = sys.argv[4] if len(sys.argv) > 4 else "c3"
+if which == "c5":
+    base = gen_synth.c5_files(256)
+elif which in ("422", "420"):    # the 16 pictures of tools/config_bench.py's subsampled lines
+    base = [gen_synth.synth_jpeg(s, 1024, 1024, 90, False, 0, "2x1" if which == "422" else "2x2") for s in range(16)]
+else:
+    base = gen_synth.c3_files()
 files = [base[i % len(base)] for i in range(n)]
 for v in variants:
     os.environ["GJD_TRANSFORM_VARIANT"] = str(v)
