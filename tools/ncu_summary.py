@@ -12,7 +12,7 @@ WANT = re.compile(
     r"sm__issue_active\.avg\.pct_of_peak_sustained_elapsed|launch__registers_per_thread|launch__occupancy_limit_\w+|"
     r"launch__grid_size|launch__block_size|smsp__average_warps_issue_stalled_\w+_per_issue_active\.ratio|"
     r"l1tex__data_bank_conflicts_pipe_lsu_mem_shared\.sum|smsp__thread_inst_executed_per_inst_executed\.ratio|"
-    r"sm__inst_executed_pipe_(alu|fma|lsu)\.avg\.pct_of_peak_sustained_active|l1tex__t_sector_hit_rate\.pct|"
+    r"sm__inst_executed_pipe_(alu|fma|lsu)\.avg\.pct_of_peak_sustained_active|sm__pipe_fmaheavy_cycles_active\.avg\.pct_of_peak_sustained_elapsed|l1tex__t_sector_hit_rate\.pct|"
     r"lts__t_sector_hit_rate\.pct|lts__t_bytes\.sum|l1tex__t_bytes\.sum|lts__throughput\.avg\.pct_of_peak_sustained_elapsed|"
     r"l1tex__throughput\.avg\.pct_of_peak_sustained_elapsed|smsp__inst_executed_op_(shared|global)_(ld|st)\.sum|"
     r"sm__sass_inst_executed_op_(shared|global)_(ld|st)\.sum|l1tex__lsu_writeback_active\.avg\.pct_of_peak_sustained_elapsed)$")
