@@ -22,6 +22,9 @@
 #define GJD_WRITE_SYMS 2          /* symbols per trip of the write pass's warp-voted loop */
 #endif
 
+#ifndef GJD_DBG_SLOW
+#define GJD_DBG_SLOW() ((void)0)  /* ... and the symbols that leave the LUTs for the canonical tables */
+#endif
 #ifndef GJD_DBG_SYM
 #define GJD_DBG_SYM() ((void)0)   /* test harnesses may count decoded symbols */
 #endif
@@ -439,6 +442,7 @@ struct GjdLutSmem {
 /* Rare path: the code is longer than GJD_LUT_BITS, or unassigned.  An unassigned code comes back as
  * GJD_ENTRY_UNASSIGNED: the write pass flags it, and both passes treat it alike. */
 GJD_HD_COLD uint32_t gjd_lookup_slow(const GjdLutSet* lut, uint32_t tb, uint32_t w, uint32_t room, uint32_t* badcode) {
+    GJD_DBG_SLOW();
     uint32_t slot = lut->slot_of[tb / GJD_RING_STRIDE];
     uint32_t e = gjd_resolve(lut->lim[slot], lut->off[slot], lut->vals[slot], lut->isdc[slot], w >> 16, GJD_LUT_BITS + 1);
     if (e & GJD_ENTRY_BAD) {
@@ -496,14 +500,15 @@ struct GjdRingSub {
         return (comp * 2u + ((pos & 63u) ? 1u : 0u)) * GJD_RING_STRIDE;
     }
     GJD_HD uint32_t next(uint32_t tb, uint32_t z, uint32_t zn) {
-        if (zn >= 64u) {                                    /* block complete */
-            if (tb <= GJD_RING_STRIDE && yl != 0u) { yl--; return 0u; }   /* another luma block of this MCU */
-            tb = (tb | GJD_RING_STRIDE) + GJD_RING_STRIDE;  /* the next component's DC table (a block that ends on its DC symbol
-                                                               cannot happen: a DC symbol advances one slot) */
-            if (tb == GJD_RING_BYTES) { tb = 0u; yl = ny - 1u; }
-            return tb;
-        }
-        return z == 0u ? tb + GJD_RING_STRIDE : tb;
+        /* straight-line (selects): in a warp some lane completes a block on nearly every trip of the symbol loop, so a branch
+         * here would run both of its sides every time */
+        const bool done = zn >= 64u;                        /* block complete (never on its DC symbol: that advances one slot) */
+        const bool more = done && tb <= GJD_RING_STRIDE && yl != 0u;      /* another luma block of this MCU follows */
+        uint32_t nxt = (tb | GJD_RING_STRIDE) + GJD_RING_STRIDE;          /* the next component's DC table */
+        const bool wrap = nxt == GJD_RING_BYTES;
+        nxt = wrap ? 0u : nxt;
+        yl = more ? yl - 1u : (done && wrap) ? ny - 1u : yl;
+        return more ? 0u : done ? nxt : z == 0u ? tb + GJD_RING_STRIDE : tb;
     }
     GJD_HD uint32_t slots() const { return (ny + 2u) * 64u; }
 };
@@ -586,6 +591,7 @@ GJD_HD void gjd_count_span(Src& scan, const Lut& lut, uint32_t end_bits, uint32_
 /* Any single symbol from the canonical tables alone (code lengths 1..16): what gjd_lookup returns, without
  * touching a LUT.  Rare paths of the pair-counting loop only. */
 GJD_HD_COLD uint32_t gjd_lookup_canonical(const GjdLutSet* lut, uint32_t tb, uint32_t w) {
+    GJD_DBG_SLOW();
     const uint32_t slot = lut->slot_of[tb / GJD_RING_STRIDE];
     const uint32_t e = gjd_resolve(lut->lim[slot], lut->off[slot], lut->vals[slot], lut->isdc[slot], w >> 16, 1);
     return (e & GJD_ENTRY_BAD) ? GJD_ENTRY_UNASSIGNED : e;
@@ -598,9 +604,66 @@ GJD_HD_COLD uint32_t gjd_lookup_canonical(const GjdLutSet* lut, uint32_t tb, uin
  *   - when a pair would complete the block, the first symbol is checked alone: if it already completes the
  *     block (a coefficient at index 63, or garbage), the second symbol belongs to the next block's DC table
  *     and the pair is dropped. */
-template <class Src, class Lut, class Ring = GjdRing444, class Rst = GjdNoRst>
+/* Checkpoints inside a span (k_huff_sync).  A thread that has to decode its subsequence again, from the state its
+ * predecessor really ended in, almost always falls back into the path of its first decode within a few hundred bits; what
+ * follows would be the same symbols again.  So the first decode leaves its state at a few fixed places of the span, and a
+ * repeat stops at the first of them it reaches in the same state (same bit position, same slot in the MCU).  The places
+ * cost the symbol loop nothing: a checkpoint is one more fence of the loop that is already there for the end of the span
+ * and for restart boundaries, and the loop leaves at "the first symbol boundary less than GJD_LUT_BITS in front of the
+ * fence" — the same boundary for every decode that is on the same path.
+ *   GjdNoChk   no checkpoints: exactly the code without them.
+ *   visit(k, p, n, pos) -> true: stop here (the caller finishes the state from what the first decode left). */
+struct GjdNoChk {
+    static constexpr bool enabled = false;
+    GJD_HD uint32_t fence(uint32_t f) const { return f; }
+    GJD_HD bool visit(uint32_t, uint32_t, uint32_t) { return false; }
+};
+
+/* The checkpoints of k_huff_sync: the quarter points of a subsequence, {p, n << GJD_POS_BITS | pos} like sinfo, checkpoint k
+ * of a thread at cp[k * GJD_SEQ_SUBS]. */
+#ifndef GJD_SYNC_CHK
+#define GJD_SYNC_CHK 3
+#endif
+struct GjdChkPt { uint32_t x, y; };
+struct GjdChkRecord {            /* first decode: leave the state at every checkpoint */
+    static constexpr bool enabled = true;
+    GjdChkPt* cp;
+    uint32_t next, step, k;
+    GJD_HD uint32_t fence(uint32_t f) const { return (k < (uint32_t)GJD_SYNC_CHK && next < f) ? next : f; }
+    GJD_HD bool visit(uint32_t p, uint32_t n, uint32_t pos) {
+        cp[k * GJD_SEQ_SUBS].x = p; cp[k * GJD_SEQ_SUBS].y = (n << GJD_POS_BITS) | pos;
+        k++; next += step;
+        return false;
+    }
+};
+struct GjdChkCompare {           /* repeat decode: stop at the first checkpoint reached in the state the earlier decode had there */
+    static constexpr bool enabled = true;
+    GjdChkPt* cp;
+    uint32_t next, step, k;
+    uint32_t n_old;              /* slots the earlier decode had counted at the checkpoint that matched */
+    bool hit;
+    GJD_HD uint32_t fence(uint32_t f) const { return (k < (uint32_t)GJD_SYNC_CHK && next < f) ? next : f; }
+    GJD_HD bool visit(uint32_t p, uint32_t n, uint32_t pos) {
+        const uint32_t ox = cp[k * GJD_SEQ_SUBS].x, oy = cp[k * GJD_SEQ_SUBS].y;
+        cp[k * GJD_SEQ_SUBS].x = p; cp[k * GJD_SEQ_SUBS].y = (n << GJD_POS_BITS) | pos;     /* (the same place, the new count) */
+        if (ox == p && (oy & GJD_POS_MASK) == pos) { n_old = oy >> GJD_POS_BITS; hit = true; return true; }
+        k++; next += step;
+        return false;
+    }
+};
+/* After a repeat decode that stopped at checkpoint c.k with st = its state there: the rest of the earlier decode stands —
+ * its exit {exit_p, exit_n_pos} and its later checkpoints — with the slot counts shifted by what the new start changed. */
+GJD_HD void gjd_chk_finish(const GjdChkCompare& c, GjdState& st, uint32_t exit_p, uint32_t exit_n_pos) {
+    const uint32_t delta = st.n - c.n_old;
+    for (uint32_t k = c.k + 1u; k < (uint32_t)GJD_SYNC_CHK; k++) c.cp[k * GJD_SEQ_SUBS].y += delta << GJD_POS_BITS;
+    st.p = exit_p;
+    st.pos = exit_n_pos & GJD_POS_MASK;
+    st.n = (exit_n_pos >> GJD_POS_BITS) + delta;
+}
+
+template <class Src, class Lut, class Ring = GjdRing444, class Rst = GjdNoRst, class Chk = GjdNoChk>
 GJD_HD void gjd_count_span_pairs(Src& scan, const Lut& lut, uint32_t end_bits, uint32_t scan_bits,
-                                 GjdState& s, Ring ring = Ring(), Rst rst = Rst()) {
+                                 GjdState& s, Ring ring = Ring(), Rst rst = Rst(), Chk* chk = nullptr) {
     if (s.p >= end_bits) return;
     GjdWin win;
     gjd_win_init(win, scan, s.p);
@@ -608,7 +671,17 @@ GJD_HD void gjd_count_span_pairs(Src& scan, const Lut& lut, uint32_t end_bits, u
     uint32_t limit = rst.seek(p, scan_bits);
     for (;;) {
         /* fast steps: only where a whole LUT index lies in front of both the end of the span and the next restart */
-        const uint32_t fence = (Rst::enabled && limit < end_bits) ? limit : end_bits;
+        const uint32_t fence0 = (Rst::enabled && limit < end_bits) ? limit : end_bits;
+        const uint32_t fence = Chk::enabled ? chk->fence(fence0) : fence0;
+        if (Chk::enabled && fence < fence0 && p + (uint32_t)GJD_LUT_BITS > fence) {
+            /* at a checkpoint (the loop below left because of it, or the span starts this close to it) */
+            const uint32_t adv = nb * 64u + z - (s.pos & 63u);
+            if (chk->visit(p, s.n + adv, (s.pos + adv) % ring.slots())) {
+                s.p = p; s.n += adv; s.pos = (s.pos + adv) % ring.slots();
+                return;
+            }
+            continue;
+        }
         while (p + (uint32_t)GJD_LUT_BITS <= fence) {
             GJD_DBG_SYM();
             const uint32_t w = gjd_peek32(win, scan, p);
@@ -632,6 +705,7 @@ GJD_HD void gjd_count_span_pairs(Src& scan, const Lut& lut, uint32_t end_bits, u
             z = zn;
             if (zn >= 64u) { z = 0u; nb++; }
         }
+        if (Chk::enabled && fence < fence0 && p + (uint32_t)GJD_LUT_BITS > fence) continue;   /* a checkpoint, not the end */
         /* single steps from the canonical tables: the last symbols of the span, or of a restart interval */
         bool again = false;
         while (p < end_bits) {

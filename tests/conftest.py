@@ -114,7 +114,7 @@ class HostSim:
         nm = ((W + 15) // 8) * ((H + 15) // 8)
         coef = np.zeros(nm * 192, np.int16)      # grayscale files fill the first nm * 64
         rgb = np.zeros((3, H, W), np.uint8)
-        stats = np.zeros(8, np.uint32)
+        stats = np.zeros(9, np.uint32)   # [8] = repeat decodes cut short at a checkpoint
         w, h = C.c_int32(), C.c_int32()
         rc = self.lib.hostsim_decode(C.cast(C.c_char_p(data), C.c_void_p), len(data), sub_log2, coef.ctypes.data,
                                      rgb.ctypes.data, C.byref(w), C.byref(h), stats.ctypes.data)

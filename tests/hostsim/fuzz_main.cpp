@@ -13,7 +13,7 @@
 #include <vector>
 
 extern "C" int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* coef_out, uint8_t* rgb_out,
-                              int32_t* width, int32_t* height, uint32_t stats[8]);
+                              int32_t* width, int32_t* height, uint32_t stats[9]);
 extern "C" int hostsim_parse(const uint8_t* jpg, size_t len, int32_t* w, int32_t* h);
 
 static uint64_t rng_state;
@@ -95,7 +95,7 @@ int main(int argc, char** argv) {
             const size_t pw = ((size_t)w + 7) / 8 * 8, ph = ((size_t)h + 7) / 8 * 8;
             std::vector<int16_t> coef(pw * ph * 3);
             std::vector<uint8_t> rgb((size_t)w * h * 3);
-            uint32_t stats[8];
+            uint32_t stats[9];
             rc = hostsim_decode(exact.data(), exact.size(), (it & 1) ? 8 : 10, coef.data(), rgb.data(), &w, &h, stats);
         }
         switch (rc) {

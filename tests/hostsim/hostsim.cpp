@@ -15,8 +15,9 @@
 #include <algorithm>
 #include <vector>
 
-static unsigned long long g_syms_dbg = 0;
+static unsigned long long g_syms_dbg = 0, g_slow_dbg = 0;
 #define GJD_DBG_SYM() (g_syms_dbg++)
+#define GJD_DBG_SLOW() (g_slow_dbg++)
 #include "../../gpu-jpeg-decoder_b200/csrc/gjd_devfn.cuh"
 #include "../../gpu-jpeg-decoder_b200/csrc/gjd_parse.h"
 #include "../../include/gjd.h"
@@ -51,7 +52,7 @@ extern "C" {
  *        [2] device status bits, [3] nosync count, [4] subsequences, [5] sequences,
  *        [6] subsequences re-decoded in validation rounds (all rounds), [7] of those, in round 1 */
 int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* coef_out, uint8_t* rgb_out,
-                   int32_t* width, int32_t* height, uint32_t stats[8]) {
+                   int32_t* width, int32_t* height, uint32_t stats[9]) {
     const uint32_t sub_log2 = sub_log2_arg ? (uint32_t)sub_log2_arg : GJD_SUB_LOG2_MIN;
     const uint32_t S = 1u << sub_log2;
     GjdParsed p;
@@ -110,7 +111,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     GjdLutMem clut;
     clut.set = lutS;
     clut.badcode = nullptr;
-    uint32_t max_rounds = 0, fix_decodes = 0, nosync = 0, status = 0, sub_total = 0, seq_total = 0, redec = 0, redec1 = 0;
+    uint32_t max_rounds = 0, fix_decodes = 0, nosync = 0, status = 0, sub_total = 0, seq_total = 0, redec = 0, redec1 = 0, chk_hits = 0;
     std::vector<int16_t> coef((size_t)tile_count * 96 * 64, (int16_t)0x7e7e);   /* stale garbage where nothing is written */
     std::vector<uint32_t> meta((size_t)tile_count * 96, 0);
     std::vector<uint8_t> written((size_t)tile_count * 96, 0);
@@ -126,6 +127,17 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
         if (has_rst) { if (subsamp) gjd_count_span_pairs(sc, l, end, bits, st, GjdRingSub(ny), rstt); else gjd_count_span_pairs(sc, l, end, bits, st, GjdRing444(), rstt); }
         else if (subsamp) gjd_count_span_pairs(sc, l, end, bits, st, GjdRingSub(ny)); else gjd_count_span_pairs(sc, l, end, bits, st);
     };
+#if GJD_SYNC_CHK
+    /* the checkpointed forms k_huff_sync uses for a thread's own subsequence (first decode / repeat) */
+    auto count_pairs_rec = [&](const uint32_t*& sc, const GjdLutMem& l, uint32_t end, uint32_t bits, GjdState& st, GjdChkRecord* c) {
+        if (has_rst) { if (subsamp) gjd_count_span_pairs(sc, l, end, bits, st, GjdRingSub(ny), rstt, c); else gjd_count_span_pairs(sc, l, end, bits, st, GjdRing444(), rstt, c); }
+        else if (subsamp) gjd_count_span_pairs(sc, l, end, bits, st, GjdRingSub(ny), GjdNoRst(), c); else gjd_count_span_pairs(sc, l, end, bits, st, GjdRing444(), GjdNoRst(), c);
+    };
+    auto count_pairs_cmp = [&](const uint32_t*& sc, const GjdLutMem& l, uint32_t end, uint32_t bits, GjdState& st, GjdChkCompare* c) {
+        if (has_rst) { if (subsamp) gjd_count_span_pairs(sc, l, end, bits, st, GjdRingSub(ny), rstt, c); else gjd_count_span_pairs(sc, l, end, bits, st, GjdRing444(), rstt, c); }
+        else if (subsamp) gjd_count_span_pairs(sc, l, end, bits, st, GjdRingSub(ny), GjdNoRst(), c); else gjd_count_span_pairs(sc, l, end, bits, st, GjdRing444(), GjdNoRst(), c);
+    };
+#endif
     auto count_one = [&](const uint32_t*& sc, const GjdLutMem& l, uint32_t end, uint32_t bits, GjdState& st) {
         if (has_rst) { if (subsamp) gjd_count_span(sc, l, end, bits, st, GjdRingSub(ny), rstt); else gjd_count_span(sc, l, end, bits, st, GjdRing444(), rstt); }
         else if (subsamp) gjd_count_span(sc, l, end, bits, st, GjdRingSub(ny)); else gjd_count_span(sc, l, end, bits, st);
@@ -141,12 +153,16 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     std::vector<uint32_t> sp((size_t)seq_count * GJD_SEQ_SUBS, 0), sn((size_t)seq_count * GJD_SEQ_SUBS, 0);
 
     /* k_huff_sync: one "block" per sequence */
+    g_syms_dbg = 0; g_slow_dbg = 0;
     std::vector<uint32_t> seq_in_p(seq_count, 0), seq_in_pos(seq_count, 0);
     for (uint32_t g = 0; g < seq_count; g++) {
         uint32_t* bp = &sp[(size_t)g * GJD_SEQ_SUBS];
         uint32_t* bn = &sn[(size_t)g * GJD_SEQ_SUBS];
         std::vector<uint32_t> in_p(GJD_SEQ_SUBS, 0), in_pos(GJD_SEQ_SUBS, 0), endb(GJD_SEQ_SUBS, 0);
         std::vector<char> active(GJD_SEQ_SUBS, 0);
+#if GJD_SYNC_CHK
+        std::vector<GjdChkPt> cps((size_t)GJD_SYNC_CHK * GJD_SEQ_SUBS);     /* [checkpoint][thread], like the kernel's shared array */
+#endif
         for (uint32_t tid = 0; tid < GJD_SEQ_SUBS; tid++) {
             uint32_t sub = g * GJD_SEQ_SUBS + tid;
             active[tid] = sub < sub_count;
@@ -161,6 +177,12 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                 }
                 in_p[tid] = st.p; in_pos[tid] = st.pos;
                 st.n = 0;
+#if GJD_SYNC_CHK
+                if (subsamp) {      /* like the kernel: checkpoints for chroma-subsampled scans only */
+                    GjdChkRecord rec = {&cps[tid], start + (S >> 2), S >> 2, 0u};
+                    count_pairs_rec(scan, clut, endb[tid], scan_bits, st, &rec);
+                } else
+#endif
                 count_pairs(scan, clut, endb[tid], scan_bits, st);
             }
             bp[tid] = st.p;
@@ -177,7 +199,24 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                 uint32_t pp = bp[tid - 1], ppos = bn[tid - 1] & GJD_POS_MASK;
                 if (pp != in_p[tid] || ppos != in_pos[tid]) {
                     GjdState st; st.p = in_p[tid] = pp; st.pos = in_pos[tid] = ppos; st.n = 0;
+#if GJD_SYNC_CHK
+                    if (!subsamp) count_pairs(scan, clut, endb[tid], scan_bits, st);
+                    else {
+                    const uint32_t start = (g * GJD_SEQ_SUBS + tid) << sub_log2;
+                    GjdChkCompare cmp = {&cps[tid], start + (S >> 2), S >> 2, 0u, 0u, false};
+                    count_pairs_cmp(scan, clut, endb[tid], scan_bits, st, &cmp);
+                    if (cmp.hit) {
+                        gjd_chk_finish(cmp, st, bp[tid], bn[tid]);
+                        /* the short cut must give what the whole repeat gives */
+                        GjdState full; full.p = pp; full.pos = ppos; full.n = 0;
+                        count_pairs(scan, clut, endb[tid], scan_bits, full);
+                        if (full.p != st.p || full.pos != st.pos || full.n != st.n) { fprintf(stderr, "hostsim: checkpoint short cut differs\n"); abort(); }
+                        chk_hits++;
+                    }
+                    }
+#else
                     count_pairs(scan, clut, endb[tid], scan_bits, st);
+#endif
                     np[tid] = st.p; nn[tid] = (st.n << GJD_POS_BITS) | st.pos;
                     badv[tid] = 1; any = true; redec++; if (r == 0) redec1++;
                 }
@@ -188,6 +227,9 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                 if (badv[tid]) { bp[tid] = np[tid]; bn[tid] = nn[tid]; }
         }
     }
+    if (getenv("HOSTSIM_DEBUG"))
+        fprintf(stderr, "hostsim sync pass: %u subsequences, %llu loop trips, %llu of them through the canonical tables, %u repeats (%u cut short)\n",
+                sub_count, g_syms_dbg, g_slow_dbg, redec, chk_hits);
     /* k_huff_fix, iterated to its fixed point like batch_wait does */
     for (int iter = 0; iter < 65536; iter++) {
         uint32_t ns = 0;
@@ -363,7 +405,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     }
     if (stats) {
         stats[0] = max_rounds; stats[1] = fix_decodes; stats[2] = status; stats[3] = nosync;
-        stats[4] = sub_total; stats[5] = seq_total; stats[6] = redec; stats[7] = redec1;
+        stats[4] = sub_total; stats[5] = seq_total; stats[6] = redec; stats[7] = redec1; stats[8] = chk_hits;
     }
     free(lut);
     free(lutS);

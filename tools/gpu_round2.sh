@@ -33,7 +33,7 @@ launches)
 ncu)
   for k in ${NCU_KERNELS:-k_transform k_huff_write k_huff_sync}; do
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:$k -s 1 -c 1 -f -o $out/${tag}_$k \
-      env GJD_SUB_LOG2=12 python tools/profile_run.py 1000 2 > $out/${tag}_ncu_$k.log 2>&1; echo "ncu $k rc=$?"
+      env GJD_SUB_LOG2=12 python tools/profile_run.py 1000 2 ${NCU_SET:-c3} > $out/${tag}_ncu_$k.log 2>&1; echo "ncu $k rc=$?"
   done ;;
 san)
   # compute-sanitizer over the small-image parity tests and the damaged-file fuzzer
