@@ -835,9 +835,6 @@ __device__ __forceinline__ void gjd_store_row_i16(uint8_t* px, uint64_t r8, uint
 #define GJD_COLOR_ROWS_B1 0u
 #define GJD_COLOR_ROWS_B2 4u
 #endif
-#ifndef GJD_TRANSFORM_PREMETA
-#define GJD_TRANSFORM_PREMETA 0    /* next tile's meta word and DC base loaded during the colour phase */
-#endif
 #ifndef GJD_TRANSFORM_HOIST
 #define GJD_TRANSFORM_HOIST 1      /* image geometry in registers + reciprocal multiply for the MCU row (0: re-read per tile, divide) */
 #endif
@@ -885,17 +882,6 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
     const uint32_t& tile_first = d.tile_first;
 #endif
 
-#if GJD_TRANSFORM_PREMETA
-    /* the meta word and the DC base of a tile are fetched during the colour phase of the tile before it, so that the chain
-     * meta -> kmax -> coefficient loads does not start with a trip to L2 */
-    uint32_t m_next = 0u;
-    int base_next = 0;
-    if (!EXPORT && ltb * b.tb_tiles < tile_count) {
-        const uint32_t lt0 = ltb * b.tb_tiles;
-        if (lt0 * GJD_TILE_MCUS + lane < mcu_count) m_next = __ldg(b.meta + (size_t)(tile_first + lt0) * 96u + lane * 3u + c);
-        base_next = reinterpret_cast<const int*>(b.tilebase + tile_first + lt0)[c];
-    }
-#endif
 
 #pragma unroll 1
     for (uint32_t t = 0; t < b.tb_tiles; t++) {
@@ -911,11 +897,7 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
             asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const uint4*>(b.coef) + (blk + 96u) * 8u));
             if (lane < 12u && c == 0u) asm volatile("prefetch.global.L2 [%0];" ::"l"(b.meta + blk + 96u - lane * 3u + lane * 8u));
         }
-#if GJD_TRANSFORM_PREMETA
-        const uint32_t m = !EXPORT ? m_next : valid ? __ldg(b.meta + blk) : 0u;
-#else
         const uint32_t m = valid ? __ldg(b.meta + blk) : 0u;
-#endif
         const uint32_t kmax = (m >> 16) & 63u;
         const uint32_t nchunk = kmax ? (kmax >> 3) + 1u : 0u;   /* 16-byte chunks up to the last coefficient */
         const uint4* src = reinterpret_cast<const uint4*>(b.coef) + blk * 8u;
@@ -926,27 +908,11 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
             if ((uint32_t)j < nchunk) r = __ldcs(src + j);
             w[4 * j] = r.x; w[4 * j + 1] = r.y; w[4 * j + 2] = r.z; w[4 * j + 3] = r.w;
         }
-#if GJD_TRANSFORM_PREMETA
-        int dc = warp_incl_scan_i((int)(int16_t)(m & 0xffffu), lane);
-        const int base = base_next;
-#if GJD_TRANSFORM_PREMETA == 2
-        /* (a whole tile ahead: the luma warp has no colour phase to hide the fetch behind) */
-        if (!EXPORT && t + 1u < b.tb_tiles && ltile + 1u < tile_count) {
-            m_next = mcu + GJD_TILE_MCUS < mcu_count ? __ldg(b.meta + blk + 96u) : 0u;
-            base_next = reinterpret_cast<const int*>(b.tilebase + tile_first + ltile + 1u)[c];
-        }
-#endif
-        if (d.restart_interval == 0u) {
-            dc += !EXPORT ? base : reinterpret_cast<const int*>(b.tilebase + tile_first + ltile)[c];
-        } else {
-            const int4 tb = b.tilebase[tile_first + ltile];
-#else
         const int4 tb = b.tilebase[tile_first + ltile];
         int dc = warp_incl_scan_i((int)(int16_t)(m & 0xffffu), lane);
         if (d.restart_interval == 0u) {
             dc += c == 0 ? tb.x : c == 1 ? tb.y : tb.z;
         } else {
-#endif
             dc = gjd_restart_dc(b.tilebase + tile_first, b.meta + (size_t)tile_first * 96u, d.restart_interval,
                                 ltile, mcu, c, lane, dc, tb);
         }
@@ -963,12 +929,6 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, MINB) k_transform(GjdDe
         if (__reduce_max_sync(0xffffffffu, kmax) < 16u) gjd_block_to_samples<16>(w, q, dc, &smp[t & 1u][c][0][lane]);
         else gjd_block_to_samples<64>(w, q, dc, &smp[t & 1u][c][0][lane]);
         __syncthreads();
-#if GJD_TRANSFORM_PREMETA == 1
-        if (t + 1u < b.tb_tiles && ltile + 1u < tile_count) {
-            m_next = mcu + GJD_TILE_MCUS < mcu_count ? __ldg(b.meta + blk + 96u) : 0u;
-            base_next = reinterpret_cast<const int*>(b.tilebase + tile_first + ltile + 1u)[c];
-        }
-#endif
 
         /* ---- colour phase: some of the 8 rows of MCU `lane` ---- */
 #if GJD_TRANSFORM_HOIST

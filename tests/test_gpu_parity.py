@@ -629,3 +629,38 @@ def test_subsampled_large_vs_hostsim(decoder, hostsim):
     assert st == [0, 0]
     rc, _, rgb, _ = hostsim.decode(data)
     assert rc == 0 and np.array_equal(outs[0], rgb) and np.array_equal(outs[1], rgb)
+
+
+@pytest.mark.parametrize("sub_log2", [0, 12])
+def test_subsampled_bench_sets_vs_pin(oracle, sub_log2, monkeypatch):
+    """The 4:2:2 / 4:2:0 sets of tools/config_bench.py (1024x1024 q90: long scans, where half of the cold decodes of a 4:2:0
+    subsequence start in the wrong block of the MCU and are repeated up to a checkpoint) against the pin itself, composed
+    at run time as tools/make_golden_sub.py does: jpeg_read_coefficients of the vendored libjpeg + the oracle's IDCT,
+    sample replication and the oracle's colour function."""
+    import ctypes as C
+    import gen_synth
+    import gjd
+    import make_golden_sub as mgs
+    if not gen_synth.have_cjpeg() or not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "jpeg_coefs")):
+        pytest.skip("vendored cjpeg / jpeg_coefs missing")
+    if sub_log2:
+        monkeypatch.setenv("GJD_SUB_LOG2", str(sub_log2))
+    orc = oracle.lib
+    orc.gjdo_idct_block.argtypes = [C.c_void_p]
+    orc.gjdo_color_pixels.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    zz_of_nat = np.ctypeslib.as_array((C.c_uint8 * 64).in_dll(orc, "gjdo_zigzag_of_natural")).astype(np.int64)
+    files, want = [], []
+    for sample in ("2x1", "2x2"):
+        for seed in range(3):
+            data = gen_synth.synth_jpeg(seed, 1024, 1024, 90, False, 0, sample)
+            coef, rgb, _ = mgs.compose(data, orc, zz_of_nat)
+            files.append(data); want.append((coef, rgb))
+    with gjd.Decoder(0) as d:
+        for i in (0, 3):
+            got, _, _ = d.decode_coeffs(files[i])
+            assert np.array_equal(got, want[i][0])
+        batch = [files[i % len(files)] for i in range(30)]
+        outs, st = d.decode(batch)
+        assert st == [0] * len(batch)
+        for i, o in enumerate(outs):
+            assert np.array_equal(o, want[i % len(files)][1]), i
