@@ -1,5 +1,5 @@
 """A/B of kernel variants on a resident c3 batch: median CUDA-event stage times per GJD_TRANSFORM_VARIANT.
-usage: python tools/stage_bench.py [images] [runs] [variants, comma separated] [c3|c5|422|420 = which synthetic set is tiled]"""
+usage: python tools/stage_bench.py [images] [runs] [variants, comma separated] [c3|c5|422|420|dri = which synthetic set is tiled]"""
 import os
 import statistics
 import sys
@@ -18,6 +18,8 @@ if which == "c5":
     base = gen_synth.c5_files(256)
 elif which in ("422", "420"):    # the 16 pictures of tools/config_bench.py's subsampled lines
     base = [gen_synth.synth_jpeg(s, 1024, 1024, 90, False, 0, "2x1" if which == "422" else "2x2") for s in range(16)]
+elif which == "dri":               # the restart-interval line of tools/config_bench.py (one MCU row per interval)
+    base = [gen_synth.synth_jpeg(s, 1024, 1024, 90, False, 1) for s in range(16)]
 else:
     base = gen_synth.c3_files()
 files = [base[i % len(base)] for i in range(n)]
