@@ -636,23 +636,43 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, GJD_WRITE_MINB) k_huff_writ
  * three running predictors, never reset; restart intervals are applied in the transform).  Two steps so that
  * one huge image (BASELINE config 4: 32768 tiles) is not summed by a single block:
  *   k_dc_tilesum   one thread per tile of the batch: sums the DC differences of the tile's 96 meta words
- *                  (32 MCUs x 3 components, or 96 blocks of a single-component image)
+ *                  (32 MCUs x 3 components, 96 blocks of a single-component image, or 16 / 24 MCUs of a chroma-subsampled one)
  *   k_dc_tilebase  one block per image: exclusive scan of its tile sums, in place
  */
 __global__ void __launch_bounds__(256) k_dc_tilesum(GjdDevBatch b) {
     const uint32_t t = blockIdx.x * 256u + threadIdx.x;
     if (t >= b.n_tile) return;
     const uint4* mt = reinterpret_cast<const uint4*>(b.meta) + (size_t)t * 24u;
+    const GjdImage& im = b.imgs[b.tile_img[t]];
+    const uint32_t ny = im.gray ? 1u : (uint32_t)im.hs * im.vs;
     int sum[3] = {0, 0, 0};
+    if (ny == 4u) {            /* 4:2:0: lines Y Y Y Y Cb Cr, 16 MCUs per tile */
 #pragma unroll
-    for (int i = 0; i < 24; i++) {
-        const uint4 v = __ldg(mt + i);
-        sum[(i * 4) % 3] += (int)(int16_t)(v.x & 0xffffu);
-        sum[(i * 4 + 1) % 3] += (int)(int16_t)(v.y & 0xffffu);
-        sum[(i * 4 + 2) % 3] += (int)(int16_t)(v.z & 0xffffu);
-        sum[(i * 4 + 3) % 3] += (int)(int16_t)(v.w & 0xffffu);
+        for (int i = 0; i < 24; i++) {
+            const uint4 v = __ldg(mt + i);
+            const int d4[4] = {(int)(int16_t)(v.x & 0xffffu), (int)(int16_t)(v.y & 0xffffu), (int)(int16_t)(v.z & 0xffffu), (int)(int16_t)(v.w & 0xffffu)};
+#pragma unroll
+            for (int k = 0; k < 4; k++) sum[(i * 4 + k) % 6 < 4 ? 0 : (i * 4 + k) % 6 - 3] += d4[k];
+        }
+    } else if (ny == 2u) {     /* 4:2:2 / 4:4:0: lines Y Y Cb Cr, 24 MCUs per tile */
+#pragma unroll
+        for (int i = 0; i < 24; i++) {
+            const uint4 v = __ldg(mt + i);
+            sum[0] += (int)(int16_t)(v.x & 0xffffu) + (int)(int16_t)(v.y & 0xffffu);
+            sum[1] += (int)(int16_t)(v.z & 0xffffu);
+            sum[2] += (int)(int16_t)(v.w & 0xffffu);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 24; i++) {
+            const uint4 v = __ldg(mt + i);
+            sum[(i * 4) % 3] += (int)(int16_t)(v.x & 0xffffu);
+            sum[(i * 4 + 1) % 3] += (int)(int16_t)(v.y & 0xffffu);
+            sum[(i * 4 + 2) % 3] += (int)(int16_t)(v.z & 0xffffu);
+            sum[(i * 4 + 3) % 3] += (int)(int16_t)(v.w & 0xffffu);
+        }
+        if (im.gray) { sum[0] += sum[1] + sum[2]; sum[1] = sum[2] = 0; }   /* one DC chain over the 96 blocks */
     }
-    if (b.imgs[b.tile_img[t]].gray) { sum[0] += sum[1] + sum[2]; sum[1] = sum[2] = 0; }   /* one DC chain over the 96 blocks */
     b.tilebase[t] = make_int4(sum[0], sum[1], sum[2], 0);
 }
 
@@ -1379,8 +1399,9 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_gray(Gjd
  * parser ignores the sampling factors and garbles such files).  An MCU is hs*vs luma blocks (row-major inside the MCU),
  * then Cb, then Cr (T.81 A.2.3); the entropy kernels run unchanged apart from the ring stepper (GjdRingSub) and write one
  * 128-byte coefficient line per block in scan order, so line = mcu * (hs*vs + 2) + block-in-MCU.  Two more kernels:
- *   k_dc_sub         one block per segment (restart interval, or the whole scan): the three DC chains — luma blocks in
- *                    scan order, Cb, Cr — by block-wide scans, absolute DC of every line -> dcabs
+ *   k_dc_sub         images with restart intervals: one block per image, the three DC chains — luma blocks in scan order, Cb,
+ *                    Cr — by block-wide segmented scans (heads at the restart intervals), absolute DC of every line -> dcabs
+ *   k_dc_sub_tiles   images without: the same per tile, in parallel, on top of the tile bases of k_dc_tilebase
  *   k_transform_sub  one thread per line: dequantise, dezigzag, IDCT (the same gjd_idct8x8 as everything else), samples
  *                    parked in shared memory; then 8-pixel row pieces: luma sample + the chroma sample that covers it
  *                    (sample replication, i.e. libjpeg's h2v1 / h2v2 "non-fancy" upsampling), the reference's colour
@@ -1388,10 +1409,11 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_gray(Gjd
  * Pin (no reference output exists): coefficients against jpeg_read_coefficients of the reference's vendored libjpeg 9e,
  * pixels against the oracle's IDCT + replication + the oracle's colour function (tools/make_golden_sub.py).
  */
-/* Inclusive SEGMENTED scan over a 256-thread block: v summed from the nearest thread at or below with head = true (from
+/* Inclusive SEGMENTED scan over a block of WARPS warps (256 threads: block_seg_scan_256): v summed from the nearest thread at or below with head = true (from
  * `carry`, the running value in front of the block, when there is none).  Returns the thread's value; *carry_out = the
  * running value behind the block.  wv / wf: 8 words of shared memory each. */
-__device__ __forceinline__ int block_seg_scan_256(int v, bool head, int carry, int* wv, uint32_t* wf, int* carry_out) {
+template <uint32_t WARPS>
+__device__ __forceinline__ int block_seg_scan(int v, bool head, int carry, int* wv, uint32_t* wf, int* carry_out) {
     const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
     const uint32_t heads = __ballot_sync(0xffffffffu, head);
     const uint32_t below = heads & (0xffffffffu >> (31u - lane));           /* heads at lanes <= lane */
@@ -1404,12 +1426,46 @@ __device__ __forceinline__ int block_seg_scan_256(int v, bool head, int carry, i
     __syncthreads();
     int run = carry, mine = carry;
 #pragma unroll
-    for (uint32_t w = 0; w < 8u; w++) {
+    for (uint32_t w = 0; w < WARPS; w++) {
         if (w == wid) mine = run;
         run = wf[w] ? wv[w] : run + wv[w];
     }
     *carry_out = run;
     return below ? seg : mine + seg;
+}
+__device__ __forceinline__ int block_seg_scan_256(int v, bool head, int carry, int* wv, uint32_t* wf, int* carry_out) {
+    return block_seg_scan<8u>(v, head, carry, wv, wf, carry_out);
+}
+
+/* The same without restart intervals, in parallel over the tiles (one huge 4:2:0 image is 16384 tiles, which one block would
+ * walk in 6144 rounds): the DC base of each chain at the start of a tile comes from k_dc_tilesum / k_dc_tilebase (as for
+ * 4:4:4), and the 96 lines of a tile are a segmented scan over three warps — threads in the order luma lines, Cb lines, Cr
+ * lines (the order of k_transform_sub), which is the order of each chain. */
+#define GJD_DCSUB_TILES 8u
+__global__ void __launch_bounds__(GJD_TRANSFORM_THREADS) k_dc_sub_tiles(GjdDevBatch b, int* __restrict__ dcabs) {
+    __shared__ int wv[3];
+    __shared__ uint32_t wf[3];
+    const uint32_t tid = threadIdx.x;
+    for (uint32_t k = 0; k < GJD_DCSUB_TILES; k++) {
+        const uint32_t t = blockIdx.x * GJD_DCSUB_TILES + k;
+        if (t >= b.n_tile) break;                               /* block-uniform */
+        const GjdImage& d = b.imgs[b.tile_img[t]];
+        const uint32_t ny = (uint32_t)d.hs * d.vs;
+        if (d.gray || ny == 1u || d.restart_interval != 0u) continue;   /* block-uniform: k_transform's, or k_dc_sub's */
+        const uint32_t nblk = ny + 2u, mcus_tile = 96u / nblk, nluma = mcus_tile * ny;
+        uint32_t ml, bp;
+        if (tid < nluma) { ml = tid / ny; bp = tid - ml * ny; }
+        else { const uint32_t q = tid - nluma, cc = q >= mcus_tile ? 1u : 0u; ml = q - cc * mcus_tile; bp = ny + cc; }
+        const uint32_t c = bp < ny ? 0u : bp - ny + 1u;
+        const uint32_t j = (t - d.tile_first) * 96u + ml * nblk + bp;             /* line inside the image */
+        const size_t line = (size_t)d.tile_first * 96u + j;
+        const bool valid = j < d.mcu_count * nblk;
+        const int diff = valid ? (int)(int16_t)(__ldg(b.meta + line) & 0xffffu) : 0;
+        int unused;
+        const int pre = block_seg_scan<3u>(diff, tid == 0u || tid == nluma || tid == nluma + mcus_tile, 0, wv, wf, &unused);
+        const int4 tb = b.tilebase[t];
+        if (valid) dcabs[line] = pre + (c == 0u ? tb.x : c == 1u ? tb.y : tb.z);
+    }
 }
 
 __global__ void __launch_bounds__(256) k_dc_sub(GjdDevBatch b, int* __restrict__ dcabs) {
@@ -1418,7 +1474,7 @@ __global__ void __launch_bounds__(256) k_dc_sub(GjdDevBatch b, int* __restrict__
     const GjdSegment& sg = b.segs[blockIdx.x];
     const GjdImage& d = b.imgs[sg.img];
     const uint32_t ny = (uint32_t)d.hs * d.vs;
-    if (d.gray || ny == 1u) return;
+    if (d.gray || ny == 1u || d.restart_interval == 0u) return;   /* (without restart intervals: k_dc_sub_tiles) */
     const uint32_t nblk = ny + 2u, tid = threadIdx.x;
     const size_t line0 = (size_t)d.tile_first * 96u;
     const uint32_t rb = d.restart_interval * nblk;          /* lines per restart interval (0: none) */
@@ -1693,6 +1749,7 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     if (b.any_gray) { k_transform_gray<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr); n++; }
     if (b.any_sub) {
         k_dc_sub<<<b.n_seg, 256, 0, s>>>(b, b.dcabs); n++;
+        k_dc_sub_tiles<<<(b.n_tile + GJD_DCSUB_TILES - 1u) / GJD_DCSUB_TILES, GJD_TRANSFORM_THREADS, 0, s>>>(b, b.dcabs); n++;
         k_transform_sub<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, b.dcabs, nullptr); n++;
     }
     nvtxRangePop();

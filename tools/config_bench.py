@@ -61,6 +61,14 @@ with gjd.Decoder(0) as dec:
                       "stages_ms": [round(x, 3) for x in med[:3]],
                       "MPixel_per_s": round(info["pixels"] / med[3] / 1e3, 1)}), flush=True)
 
+    # ---- C4 shape, 4:2:0: intra-image parallelism of the chroma-subsampled path (DC chains per tile, not per image) ----
+    big420 = gen_synth.synth_jpeg(1000, 8192, 8192, 90, False, 0, "2x2")
+    med, info = resident(dec, [big420], 10)
+    print(json.dumps({"config": "c4 shape 8192x8192 q90 4:2:0, no restart markers", "scan_bytes": info["scan_bytes"],
+                      "subsequences": info["subseqs"], "device_ms": round(med[3], 3),
+                      "stages_ms": [round(x, 3) for x in med[:3]],
+                      "MPixel_per_s": round(info["pixels"] / med[3] / 1e3, 1)}), flush=True)
+
     # ---- C3 with restart intervals (one MCU row per interval, the usual camera setting): ADVICE r1 ----
     rbase = [gen_synth.synth_jpeg(s, 1024, 1024, 90, False, 1) for s in range(16)]
     nbase = [gen_synth.synth_jpeg(s, 1024, 1024, 90) for s in range(16)]
