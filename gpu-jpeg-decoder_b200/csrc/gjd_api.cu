@@ -358,12 +358,21 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
     nvtxRangePop();
     NvtxRange r_desc("gjd: descriptors + H2D + table kernels");
 
-    /* subsequence length for this batch: the longest that still leaves >= GJD_MIN_SUBSEQS threads */
+    /* subsequence length for this batch: the longest that still leaves >= GJD_MIN_SUBSEQS threads.  Where most of the bits
+     * are chroma-subsampled scans an eighth of that is enough: half of the cold decodes of a 4:2:0 subsequence start in the
+     * wrong block of the MCU and are repeated, which costs less the fewer subsequence boundaries there are (1000 x 1024^2
+     * 4:2:0: sync pass 1.93 ms at 2^10 bits, 0.92 ms at 2^13; the 4:4:4 set of the same size is fastest at 2^10-2^11;
+     * profiles/r02I_sub_log2.txt) */
     uint32_t sub_log2 = GJD_SUB_LOG2_MIN;
     {
-        uint64_t total_bits = 0;
-        for (int32_t i = 0; i < n; i++) total_bits += (uint64_t)std::max<long>(ulen[i], 0) * 8;
-        while (sub_log2 < GJD_SUB_LOG2_MAX && (total_bits >> (sub_log2 + 1)) >= ctx->min_subseqs) sub_log2++;
+        uint64_t total_bits = 0, sub_bits_total = 0;
+        for (int32_t i = 0; i < n; i++) {
+            const uint64_t bits = (uint64_t)std::max<long>(ulen[i], 0) * 8;
+            total_bits += bits;
+            if (b->geom[i].status == GJD_OK && (uint32_t)parsed[i].hs * parsed[i].vs > 1u) sub_bits_total += bits;
+        }
+        const uint64_t want = sub_bits_total * 2 > total_bits ? std::max<uint64_t>(ctx->min_subseqs / 8, 1) : ctx->min_subseqs;
+        while (sub_log2 < GJD_SUB_LOG2_MAX && (total_bits >> (sub_log2 + 1)) >= want) sub_log2++;
         if (ctx->force_sub_log2) sub_log2 = (uint32_t)ctx->force_sub_log2;
     }
     const uint64_t sub_bits = 1ull << sub_log2;

@@ -619,7 +619,7 @@ struct GjdNoChk {
     GJD_HD bool visit(uint32_t, uint32_t, uint32_t) { return false; }
 };
 
-/* The checkpoints of k_huff_sync: the quarter points of a subsequence, {p, n << GJD_POS_BITS | pos} like sinfo, checkpoint k
+/* The checkpoints of k_huff_sync: GJD_SYNC_CHK evenly spaced places inside a subsequence (3: its quarter points), {p, n << GJD_POS_BITS | pos} like sinfo, checkpoint k
  * of a thread at cp[k * GJD_SEQ_SUBS]. */
 #ifndef GJD_SYNC_CHK
 #define GJD_SYNC_CHK 3

@@ -368,7 +368,7 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS, GJD_SYNC_MINB) k_huff_sync(G
              * block of the MCU half of the time (10 % for 4:2:2, never on the 4:4:4 benchmark images), and all but 2 % of the
              * repeats are back on the first decode's path at the first checkpoint (tests/hostsim stats) */
             if constexpr (decltype(ring)::sub) {
-                GjdChkRecord rec = {&cps[0][tid], start + (S >> 2), S >> 2, 0u};
+                GjdChkRecord rec = {&cps[0][tid], start + S / (GJD_SYNC_CHK + 1u), S / (GJD_SYNC_CHK + 1u), 0u};
                 gjd_count_span_pairs(scan, slut, end, scan_bits, st, ring, rst, &rec);
             } else
 #endif
@@ -388,7 +388,7 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS, GJD_SYNC_MINB) k_huff_sync(G
                     st.p = in_p = pp; st.pos = in_pos = ppos; st.n = 0;
 #if GJD_SYNC_CHK
                     if constexpr (decltype(ring)::sub) {
-                        GjdChkCompare cmp = {&cps[0][tid], start + (S >> 2), S >> 2, 0u, 0u, false};
+                        GjdChkCompare cmp = {&cps[0][tid], start + S / (GJD_SYNC_CHK + 1u), S / (GJD_SYNC_CHK + 1u), 0u, 0u, false};
                         gjd_count_span_pairs(scan, slut, end, scan_bits, st, ring, rst, &cmp);
                         if (cmp.hit) gjd_chk_finish(cmp, st, sp[tid], sn[tid]);
                     } else

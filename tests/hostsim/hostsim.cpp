@@ -179,7 +179,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                 st.n = 0;
 #if GJD_SYNC_CHK
                 if (subsamp) {      /* like the kernel: checkpoints for chroma-subsampled scans only */
-                    GjdChkRecord rec = {&cps[tid], start + (S >> 2), S >> 2, 0u};
+                    GjdChkRecord rec = {&cps[tid], start + S / (GJD_SYNC_CHK + 1u), S / (GJD_SYNC_CHK + 1u), 0u};
                     count_pairs_rec(scan, clut, endb[tid], scan_bits, st, &rec);
                 } else
 #endif
@@ -203,7 +203,7 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
                     if (!subsamp) count_pairs(scan, clut, endb[tid], scan_bits, st);
                     else {
                     const uint32_t start = (g * GJD_SEQ_SUBS + tid) << sub_log2;
-                    GjdChkCompare cmp = {&cps[tid], start + (S >> 2), S >> 2, 0u, 0u, false};
+                    GjdChkCompare cmp = {&cps[tid], start + S / (GJD_SYNC_CHK + 1u), S / (GJD_SYNC_CHK + 1u), 0u, 0u, false};
                     count_pairs_cmp(scan, clut, endb[tid], scan_bits, st, &cmp);
                     if (cmp.hit) {
                         gjd_chk_finish(cmp, st, bp[tid], bn[tid]);
