@@ -537,6 +537,10 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         v.any_interleaved |= im.layout != GJD_LAYOUT_PLANAR;
         v.any_gray |= im.gray;
         v.any_sub |= (uint32_t)im.hs * im.vs > 1u;
+        v.any_rst |= im.restart_interval != 0u;
+        /* an image with restart intervals may still hold a segment without a restart table (one interval): both kernels */
+        const uint32_t sub = !im.gray && (uint32_t)im.hs * im.vs > 1u ? 2u : 0u;
+        v.entropy_mask |= (1u << sub) | (im.restart_interval != 0u ? 1u << (sub + 1u) : 0u);
     }
     v.n_seq = seq;
     v.sub_log2 = sub_log2;

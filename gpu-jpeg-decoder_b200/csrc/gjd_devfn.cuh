@@ -669,6 +669,57 @@ GJD_HD void gjd_count_span_pairs(Src& scan, const Lut& lut, uint32_t end_bits, u
     gjd_win_init(win, scan, s.p);
     uint32_t p = s.p, z = s.pos & 63u, tb = ring.of_pos(s.pos), nb = 0;
     uint32_t limit = rst.seek(p, scan_bits);
+    if (Rst::enabled) {
+        /* Scans with restart intervals: ONE flat loop, a pair step or a single step per trip.  The nest of loops below sends
+         * a lane that reaches a restart boundary through the single steps and back into the fast loop on its own, and the
+         * lanes of a warp do not meet again until the span ends: 17 of 32 lanes were active per instruction on images with
+         * one MCU row per interval (profiles/r02Kdri_k_huff_sync.hotspots.txt).  Here they meet at the end of every trip.
+         * Same states as the nest for every input (tests/test_hostsim.py: pair counting against the single-symbol walk). */
+        bool run = true;
+        while (run) {
+            GJD_DBG_SYM();
+            const uint32_t fence = limit < end_bits ? limit : end_bits;
+            const uint32_t w = gjd_peek32(win, scan, p);
+            uint32_t pn = p, zn = z;
+            bool single = true, step = false;
+            if (p + (uint32_t)GJD_LUT_BITS <= fence) {
+                uint32_t e = lut.entry(tb + ((w >> (31 - GJD_LUT_BITS)) & (GJD_RING_STRIDE - 2u)));
+                if ((e & 31u) == 0u) {
+                    if (e) e = lut.entry(GJD_LUT2_OFF(tb, e, w));
+                    if ((e & 31u) == 0u) e = gjd_lookup_slow(lut.set, tb, w, limit - p, lut.badcode);
+                    e &= ~0x1E0u;
+                }
+                pn = p + (e & 31u);
+                if (pn <= limit) {       /* (else: a long code across the boundary, left to the single step) */
+                    zn = z + (e >> 9);
+                    single = zn >= 64u && (e & GJD_PAIR_FLAG) && z + ((e >> 6) & 7u) >= 63u;   /* the first symbol alone completes the block */
+                    step = !single;
+                }
+            }
+            if (single) {
+                if (p >= end_bits) run = false;
+                else {
+                    const uint32_t e = gjd_lookup_canonical(lut.set, tb, w);
+                    pn = p + (e & 31u);
+                    if (pn <= limit) { zn = z + (e >> 9); step = true; }
+                    else if (limit >= scan_bits) run = false;     /* padding at the end of the scan */
+                    else {                                       /* restart: the rest of the interval is padding */
+                        p = limit;
+                        if (z != 0u) nb++;
+                        z = 0u;
+                        tb = ring.of_pos(0u);
+                        limit = rst.advance(scan_bits);
+                    }
+                }
+            }
+            if (step) {
+                p = pn;
+                tb = ring.next(tb, z, zn);
+                z = zn;
+                if (zn >= 64u) { z = 0u; nb++; }
+            }
+        }
+    } else
     for (;;) {
         /* fast steps: only where a whole LUT index lies in front of both the end of the span and the next restart */
         const uint32_t fence0 = (Rst::enabled && limit < end_bits) ? limit : end_bits;

@@ -322,16 +322,21 @@ __global__ void __launch_bounds__(256) k_unstuff_write(GjdDevBatch b) {
 #ifndef GJD_SYNC_MINB
 #define GJD_SYNC_MINB 6            /* resident blocks per SM of the count pass: 40 registers; 8 (32 registers) spills since the decoders carry ring and restart state: 1.95 vs 2.00 ms (profiles/r02l_win_ahead_ab.txt) */
 #endif
+/* RST: segments with restart intervals inside the scan; SUB: chroma-subsampled scans (MCUs of 4 or 6 blocks, checkpoints).
+ * Four kernels instead of four paths in one (launched only for batches that hold such images), so that the registers and
+ * spills of one instantiation are not the others': the 4:4:4 kernel without restarts is the one the benchmark runs. */
+template <bool RST, bool SUB>
 __global__ void __launch_bounds__(GJD_SYNC_THREADS, GJD_SYNC_MINB) k_huff_sync(GjdDevBatch b) {
     __shared__ GjdLutSet lut;
     __shared__ uint32_t sp[GJD_SEQ_SUBS];
     __shared__ uint32_t sn[GJD_SEQ_SUBS];
 #if GJD_SYNC_CHK
-    __shared__ GjdChkPt cps[GJD_SYNC_CHK][GJD_SEQ_SUBS];
+    __shared__ GjdChkPt cps[SUB ? GJD_SYNC_CHK : 1][SUB ? GJD_SEQ_SUBS : 1];
 #endif
 
     const uint32_t g = blockIdx.x, tid = threadIdx.x;
     const GjdSegment& d = b.segs[b.seq_seg[g]];
+    if ((d.rst_count != 0u) != RST || (d.ny > 1u) != SUB) return;    /* block-uniform: another instantiation's */
     const uint32_t ls = g - d.seq_first;
     const uint32_t sub = ls * GJD_SEQ_SUBS + tid;
     const uint32_t sub_count = d.sub_count, scan_bits = d.scan_bits;
@@ -405,9 +410,9 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS, GJD_SYNC_MINB) k_huff_sync(G
     };
     /* block-uniform: with or without restart intervals inside the scan */
     auto with_rst = [&](auto ring) {
-        if (d.rst_count) body(ring, GjdRstTable(b.rst + d.rst_first, d.rst_count)); else body(ring, GjdNoRst());
+        if constexpr (RST) body(ring, GjdRstTable(b.rst + d.rst_first, d.rst_count)); else body(ring, GjdNoRst());
     };
-    if (d.ny > 1u) with_rst(GjdRingSub(d.ny)); else with_rst(GjdRing444());
+    if constexpr (SUB) with_rst(GjdRingSub(d.ny)); else with_rst(GjdRing444());
     if (active) b.sinfo[(size_t)g * GJD_SEQ_SUBS + tid] = make_uint2(sp[tid], sn[tid]);
 #ifdef GJD_SCAN_TMA
     scan.drain();
@@ -566,6 +571,8 @@ struct GjdWriteSink {
 #else
 #define GJD_WRITE_SMEM (GJD_WRITE_LUT_BYTES + 8u * GJD_WRITE_THREADS * sizeof(uint4) + GJD_WRITE_SMEM_EXTRA)   /* dynamic: > 48 KB with the whole set */
 #endif
+/* (RST, SUB: as for k_huff_sync — one kernel per combination, launched where the batch holds such images) */
+template <bool RST, bool SUB>
 __global__ void __launch_bounds__(GJD_WRITE_THREADS, GJD_WRITE_MINB) k_huff_write(GjdDevBatch b) {
     extern __shared__ uint4 dyn_smem[];
     static_assert(GJD_WRITE_LUT_BYTES % 16 == 0 && GJD_WRITE_LUT_BYTES <= sizeof(GjdLutSet), "LUT part of the set");
@@ -575,6 +582,7 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, GJD_WRITE_MINB) k_huff_writ
     __shared__ uint32_t badcode;
     const uint32_t g = blockIdx.x, tid = threadIdx.x;
     const GjdSegment& d = b.segs[b.seq_seg[g]];
+    if ((d.rst_count != 0u) != RST || (d.ny > 1u) != SUB) return;    /* block-uniform: another instantiation's */
     const uint32_t img = d.img;
     const uint32_t ls = g - d.seq_first;
     const uint32_t sub = ls * GJD_SEQ_SUBS + tid;
@@ -616,11 +624,11 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, GJD_WRITE_MINB) k_huff_writ
     if (active && idx0 % mcu_slots != st.pos && st.p < scan_bits) bad |= GJD_DEV_BADSTATE;
     uint32_t end = min((sub + 1) << b.sub_log2, scan_bits);
     /* block-uniform choices: the MCU shape, and restart intervals inside the scan */
-    if (d.rst_count) {
+    if constexpr (RST) {
         const GjdRstTable rst(b.rst + d.rst_first, d.rst_count);
-        if (d.ny > 1u) gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad, GjdRingSub(d.ny), rst, d.rst_blocks);
+        if constexpr (SUB) gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad, GjdRingSub(d.ny), rst, d.rst_blocks);
         else gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad, GjdRing444(), rst, d.rst_blocks);
-    } else if (d.ny > 1u) gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad, GjdRingSub(d.ny));
+    } else if constexpr (SUB) gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad, GjdRingSub(d.ny));
     else gjd_write_span(scan, slut, end, scan_bits, st, idx0, d.blk_count, active, sink, bad);
 #ifdef GJD_SCAN_TMA
     scan.drain();
@@ -1723,7 +1731,10 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     /* NVTX ranges bracket the launches of each stage (host side, like the reference's range around its kernel) */
     if (!skip_sync) {
         nvtxRangePushA("gjd stage 1: entropy sync");
-        k_huff_sync<<<b.n_seq, GJD_SYNC_THREADS, 0, s>>>(b); n++;
+        if (b.entropy_mask & 1u) { k_huff_sync<false, false><<<b.n_seq, GJD_SYNC_THREADS, 0, s>>>(b); n++; }
+        if (b.entropy_mask & 2u) { k_huff_sync<true, false><<<b.n_seq, GJD_SYNC_THREADS, 0, s>>>(b); n++; }
+        if (b.entropy_mask & 4u) { k_huff_sync<false, true><<<b.n_seq, GJD_SYNC_THREADS, 0, s>>>(b); n++; }
+        if (b.entropy_mask & 8u) { k_huff_sync<true, true><<<b.n_seq, GJD_SYNC_THREADS, 0, s>>>(b); n++; }
         k_huff_fix<<<(b.n_seq + 127) / 128, 128, 0, s>>>(b); n++;
         nvtxRangePop();
     }
@@ -1731,10 +1742,16 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     nvtxRangePushA("gjd stage 2: count scan + coefficient write + DC bases");
     k_seq_scan<<<b.n_seg, 256, 0, s>>>(b); n++;
     if (!attrs_set || !*attrs_set) {   /* opt in to > 48 KB of dynamic shared memory; the caller's gjd_ctx remembers it */
-        GJD_CK(cudaFuncSetAttribute(k_huff_write, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GJD_WRITE_SMEM));
+        GJD_CK(cudaFuncSetAttribute(k_huff_write<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GJD_WRITE_SMEM));
+        GJD_CK(cudaFuncSetAttribute(k_huff_write<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GJD_WRITE_SMEM));
+        GJD_CK(cudaFuncSetAttribute(k_huff_write<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GJD_WRITE_SMEM));
+        GJD_CK(cudaFuncSetAttribute(k_huff_write<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GJD_WRITE_SMEM));
         if (attrs_set) *attrs_set = true;
     }
-    k_huff_write<<<b.n_seq, GJD_WRITE_THREADS, GJD_WRITE_SMEM, s>>>(b); n++;
+    if (b.entropy_mask & 1u) { k_huff_write<false, false><<<b.n_seq, GJD_WRITE_THREADS, GJD_WRITE_SMEM, s>>>(b); n++; }
+    if (b.entropy_mask & 2u) { k_huff_write<true, false><<<b.n_seq, GJD_WRITE_THREADS, GJD_WRITE_SMEM, s>>>(b); n++; }
+    if (b.entropy_mask & 4u) { k_huff_write<false, true><<<b.n_seq, GJD_WRITE_THREADS, GJD_WRITE_SMEM, s>>>(b); n++; }
+    if (b.entropy_mask & 8u) { k_huff_write<true, true><<<b.n_seq, GJD_WRITE_THREADS, GJD_WRITE_SMEM, s>>>(b); n++; }
     k_dc_tilesum<<<(b.n_tile + 255u) / 256u, 256, 0, s>>>(b); n++;
     k_dc_tilebase<<<b.n_img, 256, 0, s>>>(b); n++;
     nvtxRangePop();

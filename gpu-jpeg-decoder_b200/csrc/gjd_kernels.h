@@ -39,6 +39,8 @@ struct GjdDevBatch {
     uint8_t* rgb;          /* output arena (images with out_is_ptr == 0) */
     uint32_t any_gray;        /* some image is single-component: k_transform_gray is launched too */
     uint32_t any_sub;         /* some image is chroma-subsampled: k_dc_sub + k_transform_sub are launched too */
+    uint32_t any_rst;         /* some image has restart intervals */
+    uint32_t entropy_mask;    /* which instantiations of k_huff_sync / k_huff_write have work: bit (2 * SUB + RST) */
     int* dcabs;               /* [n_tile * 96] absolute DC per coefficient line (subsampled images only) */
     uint32_t any_interleaved; /* some image wants GJD_LAYOUT_INTERLEAVED: selects the transform kernel variant */
     /* device-side unstuffing (images whose raw scan bytes were uploaded instead of host-unstuffed ones) */
