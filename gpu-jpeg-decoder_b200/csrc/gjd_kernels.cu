@@ -1407,9 +1407,8 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_gray(Gjd
  * parser ignores the sampling factors and garbles such files).  An MCU is hs*vs luma blocks (row-major inside the MCU),
  * then Cb, then Cr (T.81 A.2.3); the entropy kernels run unchanged apart from the ring stepper (GjdRingSub) and write one
  * 128-byte coefficient line per block in scan order, so line = mcu * (hs*vs + 2) + block-in-MCU.  Two more kernels:
- *   k_dc_sub         images with restart intervals: one block per image, the three DC chains — luma blocks in scan order, Cb,
- *                    Cr — by block-wide segmented scans (heads at the restart intervals), absolute DC of every line -> dcabs
- *   k_dc_sub_tiles   images without: the same per tile, in parallel, on top of the tile bases of k_dc_tilebase
+ *   k_dc_sub_tiles   the three DC chains — luma blocks in scan order, Cb, Cr — per tile and in parallel on top of the tile bases
+ *                    of k_dc_tilebase (segmented scans, heads at the restart intervals): absolute DC of every line -> dcabs
  *   k_transform_sub  one thread per line: dequantise, dezigzag, IDCT (the same gjd_idct8x8 as everything else), samples
  *                    parked in shared memory; then 8-pixel row pieces: luma sample + the chroma sample that covers it
  *                    (sample replication, i.e. libjpeg's h2v1 / h2v2 "non-fancy" upsampling), the reference's colour
@@ -1417,9 +1416,9 @@ __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS, 4) k_transform_gray(Gjd
  * Pin (no reference output exists): coefficients against jpeg_read_coefficients of the reference's vendored libjpeg 9e,
  * pixels against the oracle's IDCT + replication + the oracle's colour function (tools/make_golden_sub.py).
  */
-/* Inclusive SEGMENTED scan over a block of WARPS warps (256 threads: block_seg_scan_256): v summed from the nearest thread at or below with head = true (from
+/* Inclusive SEGMENTED scan over a block of WARPS warps: v summed from the nearest thread at or below with head = true (from
  * `carry`, the running value in front of the block, when there is none).  Returns the thread's value; *carry_out = the
- * running value behind the block.  wv / wf: 8 words of shared memory each. */
+ * running value behind the block.  wv / wf: WARPS words of shared memory each. */
 template <uint32_t WARPS>
 __device__ __forceinline__ int block_seg_scan(int v, bool head, int carry, int* wv, uint32_t* wf, int* carry_out) {
     const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
@@ -1441,68 +1440,68 @@ __device__ __forceinline__ int block_seg_scan(int v, bool head, int carry, int* 
     *carry_out = run;
     return below ? seg : mine + seg;
 }
-__device__ __forceinline__ int block_seg_scan_256(int v, bool head, int carry, int* wv, uint32_t* wf, int* carry_out) {
-    return block_seg_scan<8u>(v, head, carry, wv, wf, carry_out);
-}
 
-/* The same without restart intervals, in parallel over the tiles (one huge 4:2:0 image is 16384 tiles, which one block would
- * walk in 6144 rounds): the DC base of each chain at the start of a tile comes from k_dc_tilesum / k_dc_tilebase (as for
- * 4:4:4), and the 96 lines of a tile are a segmented scan over three warps — threads in the order luma lines, Cb lines, Cr
- * lines (the order of k_transform_sub), which is the order of each chain. */
+/* Absolute DC of every line of a chroma-subsampled image, per tile and in parallel (one huge 4:2:0 image is 16384 tiles, which
+ * one block per image would walk in 6144 rounds).  The plain running sum of each chain at the start of a tile comes from
+ * k_dc_tilesum / k_dc_tilebase (as for 4:4:4); the 96 lines of a tile are one segmented scan over three warps — threads in the
+ * order luma lines, Cb lines, Cr lines (the order of k_transform_sub), which is the order of each chain.
+ * Restart intervals (T.81 E.1.4: the predictors restart with the interval, i.e. at the first line of each chain in it) add
+ * heads inside the tile; the lines in front of a chain's first head belong to the interval that is open at the tile start, and
+ * take "plain sum at the tile start minus plain sum at that interval's start" — the latter from the tile that holds the
+ * interval's first line: its base plus the chain's lines in front of that line (at most 95, summed by the block). */
 #define GJD_DCSUB_TILES 8u
 __global__ void __launch_bounds__(GJD_TRANSFORM_THREADS) k_dc_sub_tiles(GjdDevBatch b, int* __restrict__ dcabs) {
     __shared__ int wv[3];
     __shared__ uint32_t wf[3];
+    __shared__ int part[3];
     const uint32_t tid = threadIdx.x;
     for (uint32_t k = 0; k < GJD_DCSUB_TILES; k++) {
         const uint32_t t = blockIdx.x * GJD_DCSUB_TILES + k;
         if (t >= b.n_tile) break;                               /* block-uniform */
         const GjdImage& d = b.imgs[b.tile_img[t]];
         const uint32_t ny = (uint32_t)d.hs * d.vs;
-        if (d.gray || ny == 1u || d.restart_interval != 0u) continue;   /* block-uniform: k_transform's, or k_dc_sub's */
+        if (d.gray || ny == 1u) continue;                       /* block-uniform: k_transform's / k_transform_gray's */
         const uint32_t nblk = ny + 2u, mcus_tile = 96u / nblk, nluma = mcus_tile * ny;
         uint32_t ml, bp;
         if (tid < nluma) { ml = tid / ny; bp = tid - ml * ny; }
         else { const uint32_t q = tid - nluma, cc = q >= mcus_tile ? 1u : 0u; ml = q - cc * mcus_tile; bp = ny + cc; }
         const uint32_t c = bp < ny ? 0u : bp - ny + 1u;
-        const uint32_t j = (t - d.tile_first) * 96u + ml * nblk + bp;             /* line inside the image */
-        const size_t line = (size_t)d.tile_first * 96u + j;
+        const uint32_t l0 = (t - d.tile_first) * 96u;           /* first line of the tile, inside the image */
+        const uint32_t j = l0 + ml * nblk + bp;                 /* this thread's line */
+        const size_t line0 = (size_t)d.tile_first * 96u;
         const bool valid = j < d.mcu_count * nblk;
-        const int diff = valid ? (int)(int16_t)(__ldg(b.meta + line) & 0xffffu) : 0;
-        int unused;
-        const int pre = block_seg_scan<3u>(diff, tid == 0u || tid == nluma || tid == nluma + mcus_tile, 0, wv, wf, &unused);
-        const int4 tb = b.tilebase[t];
-        if (valid) dcabs[line] = pre + (c == 0u ? tb.x : c == 1u ? tb.y : tb.z);
-    }
-}
-
-__global__ void __launch_bounds__(256) k_dc_sub(GjdDevBatch b, int* __restrict__ dcabs) {
-    __shared__ int wv[8];
-    __shared__ uint32_t wf[8];
-    const GjdSegment& sg = b.segs[blockIdx.x];
-    const GjdImage& d = b.imgs[sg.img];
-    const uint32_t ny = (uint32_t)d.hs * d.vs;
-    if (d.gray || ny == 1u || d.restart_interval == 0u) return;   /* (without restart intervals: k_dc_sub_tiles) */
-    const uint32_t nblk = ny + 2u, tid = threadIdx.x;
-    const size_t line0 = (size_t)d.tile_first * 96u;
-    const uint32_t rb = d.restart_interval * nblk;          /* lines per restart interval (0: none) */
-    int pred[3] = {0, 0, 0};
-    for (uint32_t base = 0; base < sg.blk_count; base += 256u) {
-        const uint32_t j = sg.blk_first + base + tid;       /* line inside the image */
-        const bool valid = base + tid < sg.blk_count;
-        const uint32_t bp = j % nblk, c = bp < ny ? 0u : bp - ny + 1u;
-        /* T.81 E.1.4: the predictors restart with the interval — at the first block of each chain in it */
-        const bool head = rb != 0u && (j % rb) == (c == 0u ? 0u : ny + c - 1u);
         const int diff = valid ? (int)(int16_t)(__ldg(b.meta + line0 + j) & 0xffffu) : 0;
-        int mine = 0;
-#pragma unroll
-        for (uint32_t k = 0; k < 3u; k++) {
-            int next;
-            const int r = block_seg_scan_256(c == k ? diff : 0, c == k && head, pred[k], wv, wf, &next);
-            if (c == k) mine = r;
-            pred[k] = next;
+        const int4 tb = b.tilebase[t];
+        int carry = c == 0u ? tb.x : c == 1u ? tb.y : tb.z;     /* what the lines in front of the chain's first head take */
+        bool head = tid == 0u || tid == nluma || tid == nluma + mcus_tile;
+        bool after_head = false;
+        const uint32_t rb = d.restart_interval * nblk;          /* lines per restart interval (0: none) */
+        if (rb != 0u) {                                         /* block-uniform */
+            const uint32_t off = c == 0u ? 0u : ny + c - 1u;    /* the chain's first line inside an interval */
+            const uint32_t r0 = l0 % rb;
+            const uint32_t hc = l0 + (r0 <= off ? off - r0 : rb - r0 + off);   /* the chain's first head at or behind the tile start */
+            head = head || (j % rb) == off;
+            after_head = j >= hc;
+            const uint32_t s0 = l0 - r0;                        /* first line of the interval that is open at the tile start */
+            if (s0 < l0) {
+                const uint32_t ts = s0 / 96u, js = ts * 96u + tid;     /* the tile that holds it; its lines in front of s0 */
+                __syncthreads();
+                if (tid < 3u) part[tid] = 0;
+                __syncthreads();
+                if (js < s0) {
+                    const uint32_t bps = js % nblk;
+                    atomicAdd(&part[bps < ny ? 0u : bps - ny + 1u], (int)(int16_t)(__ldg(b.meta + line0 + js) & 0xffffu));
+                }
+                __syncthreads();
+                const int4 tbs = b.tilebase[d.tile_first + ts];
+                carry -= (c == 0u ? tbs.x : c == 1u ? tbs.y : tbs.z) + part[c];
+            } else {
+                carry = 0;                                      /* (an interval starts with the tile: every line is behind a head) */
+            }
         }
-        if (valid) dcabs[line0 + j] = mine;
+        int unused;
+        const int pre = block_seg_scan<3u>(diff, head, 0, wv, wf, &unused);
+        if (valid) dcabs[line0 + j] = pre + (after_head ? 0 : carry);
     }
 }
 
@@ -1765,7 +1764,6 @@ cudaError_t gjd_launch_pipeline(const GjdDevBatch& b, cudaStream_t s, const GjdS
     n++;
     if (b.any_gray) { k_transform_gray<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, nullptr); n++; }
     if (b.any_sub) {
-        k_dc_sub<<<b.n_seg, 256, 0, s>>>(b, b.dcabs); n++;
         k_dc_sub_tiles<<<(b.n_tile + GJD_DCSUB_TILES - 1u) / GJD_DCSUB_TILES, GJD_TRANSFORM_THREADS, 0, s>>>(b, b.dcabs); n++;
         k_transform_sub<false><<<b.n_tb, GJD_TRANSFORM_THREADS, 0, s>>>(b, b.dcabs, nullptr); n++;
     }

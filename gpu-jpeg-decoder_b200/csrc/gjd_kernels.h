@@ -38,7 +38,7 @@ struct GjdDevBatch {
     uint32_t tb_tiles;     /* tiles per transform block (1..GJD_TB_TILES, per batch: small batches get more blocks) */
     uint8_t* rgb;          /* output arena (images with out_is_ptr == 0) */
     uint32_t any_gray;        /* some image is single-component: k_transform_gray is launched too */
-    uint32_t any_sub;         /* some image is chroma-subsampled: k_dc_sub + k_transform_sub are launched too */
+    uint32_t any_sub;         /* some image is chroma-subsampled: k_dc_sub_tiles + k_transform_sub are launched too */
     uint32_t any_rst;         /* some image has restart intervals */
     uint32_t entropy_mask;    /* which instantiations of k_huff_sync / k_huff_write have work: bit (2 * SUB + RST) */
     int* dcabs;               /* [n_tile * 96] absolute DC per coefficient line (subsampled images only) */

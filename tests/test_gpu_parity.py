@@ -655,11 +655,16 @@ def test_subsampled_bench_sets_vs_pin(oracle, sub_log2, monkeypatch):
             data = gen_synth.synth_jpeg(seed, 1024, 1024, 90, False, 0, sample)
             coef, rgb, _ = mgs.compose(data, orc, zz_of_nat)
             files.append(data); want.append((coef, rgb))
+    # restart intervals that straddle the 96-line tiles of the DC kernel: one MCU row (64 MCUs), and 11 MCUs
+    for sample, restart in (("2x2", 1), ("2x1", "11B")):
+        data = gen_synth.synth_jpeg(7, 1024, 1024, 90, False, restart, sample)
+        coef, rgb, _ = mgs.compose(data, orc, zz_of_nat)
+        files.append(data); want.append((coef, rgb))
     with gjd.Decoder(0) as d:
-        for i in (0, 3):
+        for i in (0, 3, 6, 7):
             got, _, _ = d.decode_coeffs(files[i])
             assert np.array_equal(got, want[i][0])
-        batch = [files[i % len(files)] for i in range(30)]
+        batch = [files[i % len(files)] for i in range(32)]
         outs, st = d.decode(batch)
         assert st == [0] * len(batch)
         for i, o in enumerate(outs):
