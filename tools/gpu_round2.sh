@@ -1,5 +1,5 @@
 #!/bin/bash
-# Round-2 GPU-box visit.  usage: tools/gpu_round2.sh <tag> [tests] [bench] [c5] [ncu] [san] [micro]
+# Round-2 GPU-box visit.  usage: [NCU_SET=c3|420|422|dri] [NCU_KERNELS="..."] [AB_LIBS="default name..."] [AB_SET=..] tools/gpu_round2.sh <tag> [zz] [tests] [ablibs] [bench] [refarm] [c5] [configs] [launches] [ncu] [san] [ab] [micro]
 tag=${1:-r02x}; shift
 out=gpurun_out
 mkdir -p $out
