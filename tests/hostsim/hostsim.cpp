@@ -63,8 +63,12 @@ int hostsim_decode(const uint8_t* jpg, size_t len, int sub_log2_arg, int16_t* co
     const size_t raw = (size_t)(p.file_end - p.scan_begin);
     std::vector<uint8_t> scanbuf(raw + raw / 2 + 128, 0);
     std::vector<uint32_t> seg_off, seg_len;
-    long ulen = gjd_unstuff_segments(p.scan_begin, p.file_end, scanbuf.data(), &seg_off, &seg_len);
+    /* like batch_stage: restart markers are looked for only where the header announced a restart interval (an RSTn in a
+     * scan without DRI is GJD_E_UNSUPPORTED whatever its number) */
+    long ulen = p.restart_interval ? gjd_unstuff_segments(p.scan_begin, p.file_end, scanbuf.data(), &seg_off, &seg_len)
+                                   : gjd_unstuff(p.scan_begin, p.file_end, scanbuf.data());
     if (ulen < 0) return (int)ulen;
+    if (!p.restart_interval) { seg_off.assign(1, 0u); seg_len.assign(1, (uint32_t)ulen); }
     memset(scanbuf.data() + ulen, 0, 16);
     /* word-aligned copy */
     std::vector<uint32_t> scanw((scanbuf.size() + 3) / 4 + 4, 0);

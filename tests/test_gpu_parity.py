@@ -382,6 +382,35 @@ def test_fuzz_differential_vs_hostsim(decoder, hostsim, golden, rst_golden, gray
     assert {0, -4, -6} <= seen
 
 
+def test_fuzz_differential_subsampled(decoder, hostsim, golden, sub_golden):
+    """The same for chroma-subsampled seeds (4:2:0 / 4:2:2 / 4:4:0, with and without restart intervals): the ring stepper for
+    MCUs of 4 or 6 blocks, the checkpointed repeat decodes and the per-tile DC chains see damaged data too."""
+    import fuzzlib
+    seeds = [v for k, v in sorted(sub_golden.items()) if len(v) < 60000]
+    assert len(seeds) >= 5
+    good = golden["images/3_120x120"]
+    want_good, st = decoder.decode([good])
+    assert st == [0]
+    bad = []
+    for f in fuzzlib.cases(seeds, 200, 29):
+        rc, w, h = hostsim.parse(f)
+        if rc != 0 or w * h <= 1 << 20:
+            bad.append(f)
+    seen = set()
+    for first in range(0, len(bad), 50):
+        part = bad[first : first + 50]
+        outs, st = decoder.decode([good] + part + [good])
+        assert st[0] == 0 and st[-1] == 0
+        assert np.array_equal(outs[0], want_good[0]) and np.array_equal(outs[-1], want_good[0])
+        for f, o, s in zip(part, outs[1:-1], st[1:-1]):
+            rc, _, rgb, _ = hostsim.decode(f)
+            assert s == rc, (s, rc)
+            seen.add(rc)
+            if rc == 0:
+                assert np.array_equal(o, rgb)
+    assert {0, -6} <= seen
+
+
 def test_device_output_buffers(golden, ref_outputs, gray_golden, ref_outputs_gray):
     """rgb_on_device = 1: the caller's DEVICE buffers receive the pixels (no read-back inside the call) — tight
     planar, interleaved, and a padded pitch/plane stride — with the call forced through many sub-batches so that

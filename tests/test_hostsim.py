@@ -223,6 +223,7 @@ def test_fuzz_under_address_sanitizer(tmp_path):
     files = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "rst", "*.jpg")) +
                    glob.glob(os.path.join(ROOT, "tests", "golden", "gray", "*.jpg")))
     files += [os.path.join(ROOT, "tests", "golden", "images", n) for n in ("3_120x120.jpg", "5_200x200.jpg")]
+    files += [f for f in sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "sub", "*.jpg"))) if os.path.getsize(f) < 60000]
     r = subprocess.run([exe, "3000", "7", *files], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
     words = r.stdout.split()
