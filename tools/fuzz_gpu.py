@@ -1,6 +1,7 @@
 """Damaged files through libgjd, for `compute-sanitizer --tool memcheck python tools/fuzz_gpu.py [cases] [seed]`:
 a damaged file must end in a status code without any out-of-bounds access on the device.
-Prints the histogram of statuses."""
+Prints the histogram of statuses.  FUZZ_BIG=1: seeds are the 1024x1024 synthetic files (4:4:4, 4:2:0, 4:2:2, with and without
+restart intervals) instead of the small fixtures."""
 import collections
 import glob
 import os
@@ -15,9 +16,16 @@ import gjd
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 400
 seed = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 seeds = []
-for f in sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "*", "*.jpg"))):
-    if os.path.getsize(f) < 60000:
-        seeds.append(open(f, "rb").read())
+if os.environ.get("FUZZ_BIG"):
+    # long scans (1024x1024): many sequences per image, checkpointed repeats, restart tables that span thread blocks
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import gen_synth
+    for sample, restart in (("1x1", 0), ("2x2", 0), ("2x1", 0), ("1x1", 1), ("2x2", 1), ("2x1", "11B")):
+        seeds.append(gen_synth.synth_jpeg(7 if restart and sample != "1x1" else 0, 1024, 1024, 90, False, restart, sample))
+else:
+    for f in sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "*", "*.jpg"))):
+        if os.path.getsize(f) < 60000:
+            seeds.append(open(f, "rb").read())
 files = []
 for f in fuzzlib.cases(seeds, n, seed):
     rc, w, h = gjd.peek(f)
