@@ -371,8 +371,12 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
             total_bits += bits;
             if (b->geom[i].status == GJD_OK && (uint32_t)parsed[i].hs * parsed[i].vs > 1u) sub_bits_total += bits;
         }
-        const uint64_t want = sub_bits_total * 2 > total_bits ? std::max<uint64_t>(ctx->min_subseqs / 8, 1) : ctx->min_subseqs;
-        while (sub_log2 < GJD_SUB_LOG2_MAX && (total_bits >> (sub_log2 + 1)) >= want) sub_log2++;
+        const bool mostly_sub = sub_bits_total * 2 > total_bits;
+        const uint64_t want = mostly_sub ? std::max<uint64_t>(ctx->min_subseqs / 8, 1) : ctx->min_subseqs;
+        /* 2^13 only for the subsampled case: 4:4:4 batches of any size are fastest at 2^12 (C3 14.76 ms against 15.03, 4000
+         * images of the C5 set 23.30 against 24.30; profiles/r02I_sub_log2.txt, r02Z_c5_sub_log2.txt) */
+        const uint32_t longest = mostly_sub ? GJD_SUB_LOG2_MAX : GJD_SUB_LOG2_MAX - 1u;
+        while (sub_log2 < longest && (total_bits >> (sub_log2 + 1)) >= want) sub_log2++;
         if (ctx->force_sub_log2) sub_log2 = (uint32_t)ctx->force_sub_log2;
     }
     const uint64_t sub_bits = 1ull << sub_log2;
