@@ -1,5 +1,5 @@
 """Small driver for ncu: prepare a resident c3 batch and run the GPU pipeline a few times.
-usage: python tools/profile_run.py [images] [runs] [c3|422|420|dri]"""
+usage: python tools/profile_run.py [images] [runs] [c3|c5|422|420|dri]"""
 import os
 import sys
 
@@ -14,6 +14,8 @@ runs = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 which = sys.argv[3] if len(sys.argv) > 3 else "c3"
 if which in ("422", "420"):
     base = [gen_synth.synth_jpeg(s, 1024, 1024, 90, False, 0, "2x1" if which == "422" else "2x2") for s in range(16)]
+elif which == "c5":
+    base = gen_synth.c5_files(256)
 elif which == "dri":
     base = [gen_synth.synth_jpeg(s, 1024, 1024, 90, False, 1) for s in range(16)]
 else:
