@@ -379,7 +379,6 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
         while (sub_log2 < longest && (total_bits >> (sub_log2 + 1)) >= want) sub_log2++;
         if (ctx->force_sub_log2) sub_log2 = (uint32_t)ctx->force_sub_log2;
     }
-    const uint64_t sub_bits = 1ull << sub_log2;
 
     /* tiles per transform block: GJD_TB_TILES for big batches (one cold, unprefetched tile in 32); halved while
      * the batch would give the 148 SMs x 8 resident blocks fewer than four waves of blocks */
@@ -489,7 +488,14 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
             memset(&sg, 0, sizeof(sg));
             sg.scan_off = soff[i];
             sg.scan_bits = (uint32_t)ulen[i] * 8u;
-            sg.sub_count = std::max<uint32_t>(1u, (uint32_t)(((uint64_t)sg.scan_bits + sub_bits - 1) / sub_bits));
+            /* an image that would fill less than half a thread block (GJD_SEQ_SUBS subsequences) at the batch's length takes a
+             * shorter one: a 256x256 picture in a big batch is 32 subsequences of 2^12 bits, i.e. one block of 256 threads of
+             * which 224 wait; at 2^10 bits it is 128 that each do a quarter of the work */
+            uint32_t sl = sub_log2;
+            if (!ctx->force_sub_log2)
+                while (sl > GJD_SUB_LOG2_MIN && (((uint64_t)sg.scan_bits + (1ull << sl) - 1) >> sl) < GJD_SEQ_SUBS / 2u) sl--;
+            sg.sub_log2 = (uint8_t)sl;
+            sg.sub_count = std::max<uint32_t>(1u, (uint32_t)(((uint64_t)sg.scan_bits + (1ull << sl) - 1) >> sl));
             sg.seq_first = seq;
             sg.seq_count = (sg.sub_count + GJD_SEQ_SUBS - 1) / GJD_SEQ_SUBS;
             sg.img = (uint32_t)b->imgs.size();

@@ -245,8 +245,8 @@ __global__ void __launch_bounds__(256) k_unstuff_scan(GjdDevBatch b, uint32_t* _
         cnt[ce] = carry;
         rcnt[ce] = rcarry;
         sg.scan_bits = total * 8u;
-        const uint32_t S = 1u << b.sub_log2;
-        sg.sub_count = max(1u, (total * 8u + S - 1u) >> b.sub_log2);
+        const uint32_t S = 1u << sg.sub_log2;
+        sg.sub_count = max(1u, (total * 8u + S - 1u) >> sg.sub_log2);
         /* as many RSTn as the frame size and DRI call for (the host loop: GJD_E_CORRUPT otherwise) */
         if (markers != sg.rst_count) ustatus[r.img] = GJD_DEV_BADCOUNT;
     }
@@ -340,7 +340,7 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS, GJD_SYNC_MINB) k_huff_sync(G
     const uint32_t ls = g - d.seq_first;
     const uint32_t sub = ls * GJD_SEQ_SUBS + tid;
     const uint32_t sub_count = d.sub_count, scan_bits = d.scan_bits;
-    const uint32_t S = 1u << b.sub_log2;
+    const uint32_t S = 1u << d.sub_log2;
 #ifdef GJD_SCAN_TMA
     __shared__ __align__(128) uint8_t ring[GJD_RING_BYTES_PER_BLOCK];
     __shared__ uint64_t ring_bars[2 * GJD_SEQ_SUBS];
@@ -353,7 +353,7 @@ __global__ void __launch_bounds__(GJD_SYNC_THREADS, GJD_SYNC_MINB) k_huff_sync(G
     __syncthreads();
 
     const bool active = sub < sub_count;
-    const uint32_t start = sub << b.sub_log2;
+    const uint32_t start = sub << d.sub_log2;
     const uint32_t end = active ? min(start + S, scan_bits) : 0u;
     /* the same code for both MCU shapes (block-uniform choice): 4:4:4 / single-component, or ny luma blocks + Cb + Cr */
     auto body = [&](auto ring, auto rst) {
@@ -449,7 +449,7 @@ __global__ void __launch_bounds__(128) k_huff_fix(GjdDevBatch b) {
         uint32_t sub = ls * GJD_SEQ_SUBS + t;
         if (sub >= d.sub_count) { merged = true; break; }
         st.n = 0;
-        uint32_t end = min((sub + 1) << b.sub_log2, scan_bits);
+        uint32_t end = min((sub + 1) << d.sub_log2, scan_bits);
         if (d.rst_count) {
             const GjdRstTable rst(b.rst + d.rst_first, d.rst_count);
             if (d.ny > 1u) gjd_count_span(scan, glut, end, scan_bits, st, GjdRingSub(d.ny), rst);
@@ -622,7 +622,7 @@ __global__ void __launch_bounds__(GJD_WRITE_THREADS, GJD_WRITE_MINB) k_huff_writ
     sink.mp = b.meta + first;
     const uint32_t mcu_slots = ((uint32_t)d.ny + 2u) * 64u;       /* coefficient slots per MCU: 192 for 4:4:4 and single-component scans */
     if (active && idx0 % mcu_slots != st.pos && st.p < scan_bits) bad |= GJD_DEV_BADSTATE;
-    uint32_t end = min((sub + 1) << b.sub_log2, scan_bits);
+    uint32_t end = min((sub + 1) << d.sub_log2, scan_bits);
     /* block-uniform choices: the MCU shape, and restart intervals inside the scan */
     if constexpr (RST) {
         const GjdRstTable rst(b.rst + d.rst_first, d.rst_count);

@@ -27,7 +27,7 @@ struct GjdDevBatch {
     uint32_t* seq_base;    /* [n_seq]  coefficient index (within the segment) at the sequence start */
     uint2* seq_in;         /* [n_seq]  entry state {p, pos} of the sequence's first subsequence (k_huff_sync -> k_huff_fix) */
     uint32_t n_seq;
-    uint32_t sub_log2;     /* log2 of the subsequence length in bits (per batch) */
+    uint32_t sub_log2;     /* log2 of the subsequence length in bits chosen for the batch (an image may use a shorter one: GjdSegment.sub_log2) */
     int16_t* coef;         /* [n_tile * 96 * 64] quantised coefficients, one 128-byte line per block */
     uint32_t* meta;        /* [n_tile * 96] per block: DC difference | kmax << 16 */
     int4* tilebase;        /* [n_tile] DC predictors at the tile start (x,y,z = comp 0,1,2) */

@@ -117,7 +117,8 @@ typedef struct GjdSegment {
     uint16_t lut_id;        /* index into the GjdLutSet array                                  */
     uint8_t  ny;            /* luma blocks per MCU: 1 (4:4:4, single-component), 2 (4:2:2, 4:4:0) or 4 (4:2:0); an MCU is
                                ny luma blocks + Cb + Cr, i.e. ny + 2 blocks (three for the single-component trick)      */
-    uint8_t  pad0;
+    uint8_t  sub_log2;      /* log2 of this image's subsequence length in bits: the batch's (GjdDevBatch.sub_log2), or shorter for an
+                               image too small to fill half a thread block at that length */
     uint32_t rst_first;     /* restart intervals inside the scan: index of the segment's first entry in the rst arena ...     */
     uint32_t rst_count;     /* ... and the number of entries = restart markers = intervals - 1 (0: no restart intervals);
                                entry k - 1 = bit position in the unstuffed scan where interval k starts            */
