@@ -493,7 +493,7 @@ int batch_stage(gjd_ctx* ctx, gjd_batch* b, gjd_item* items, const GjdParsed* pa
              * which 224 wait; at 2^10 bits it is 128 that each do a quarter of the work */
             uint32_t sl = sub_log2;
             if (!ctx->force_sub_log2)
-                while (sl > GJD_SUB_LOG2_MIN && (((uint64_t)sg.scan_bits + (1ull << sl) - 1) >> sl) < GJD_SEQ_SUBS / 2u) sl--;
+                while (sl > GJD_SUB_LOG2_IMAGE_MIN && (((uint64_t)sg.scan_bits + (1ull << sl) - 1) >> sl) < GJD_SEQ_SUBS / 2u) sl--;
             sg.sub_log2 = (uint8_t)sl;
             sg.sub_count = std::max<uint32_t>(1u, (uint32_t)(((uint64_t)sg.scan_bits + (1ull << sl) - 1) >> sl));
             sg.seq_first = seq;

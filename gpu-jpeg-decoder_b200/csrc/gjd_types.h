@@ -26,6 +26,9 @@
 #include <stdint.h>
 
 #define GJD_SUB_LOG2_MIN   10u      /* subsequence (one thread) = 2^k bits, k chosen per batch:        */
+#ifndef GJD_SUB_LOG2_IMAGE_MIN
+#define GJD_SUB_LOG2_IMAGE_MIN 9u   /* the shortest a small image takes inside a batch of longer ones (GjdSegment.sub_log2) */
+#endif
 #define GJD_SUB_LOG2_MAX   13u      /* long enough to amortise the look-back, short enough to fill the GPU */
 #define GJD_LOOKBACK_BITS 512u     /* cold-start distance before a subsequence (k_huff_sync)          */
 #ifndef GJD_LOOKBACK_SUB_BITS
