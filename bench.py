@@ -9,7 +9,7 @@ Workloads:
       decodes its own batch of the same size.
   c5 (BASELINE.json configs[4]): ONE global list of 24000 mixed-size images (256 distinct files,
       default_rng(2024): sizes {256..2048}^2 + 10 % ragged, q in {75,90,95}), sharded over the N ranks with
-      gjd_partition (greedy LPT on padded pixels, include/gjd.h); rank r decodes part_of == r.  Strong scaling.
+      gjd_partition (greedy LPT on padded pixels + 5 x file bytes, include/gjd.h); rank r decodes part_of == r.  Strong scaling.
 Both are encoded with the reference's vendored IJG cjpeg.  One "step" = one pass of the whole decode path
 over the rank's images.  There is no data-path collective — torch.distributed carries the
 barrier, the max-over-ranks of the times and the sum of the parity counts.
@@ -18,7 +18,10 @@ barrier, the max-over-ranks of the times and the sum of the parity counts.
             CUDA events on the launching stream around every GPU stage (scratch clears included).  A shard
             that does not fit in HBM at once (c5 at small N) is decoded as successive resident chunks; a
             chunk's preparation (the reference's untimed extract()/allocate() loop,
-            cuda-decoder/benchmark_thoughput/benchmark.cu:49-60) is outside the event-timed region.
+            cuda-decoder/benchmark_thoughput/benchmark.cu:49-60) is outside the event-timed region.  With N > 1
+            the ranks pass a barrier before the timed runs of every chunk, so that no rank's untimed host work
+            (parity checks, freeing and preparing chunks) runs beside another rank's timed launches
+            (GJD_BENCH_LOCKSTEP=0 turns that off, GJD_BENCH_TRACE=1 prints every run's stage times per rank).
   e2e       gjd_decode_batch() through the C ABI with HOST buffers: JPEG files in page-locked host memory in, header
             parse, H2D of the raw scans, unstuffing + all GPU stages, D2H of the pixels into page-locked host memory,
             all timed (wall clock around the calls).
@@ -141,7 +144,7 @@ def config_dict(config, images, world):
     return {"workload": "c5: synthetic mixed-size 4:4:4 baseline JPEG ({256..2048}^2 + 10%% ragged, q 75/90/95), %d images "
                         "(256 distinct files tiled) sharded over the GPUs by gjd_partition" % images,
             "config": "c5", "images_total": images, "distinct_files": 256, "scaling": "strong",
-            "parallelism": "shards: gjd_partition (greedy LPT on padded pixels), one shard per GPU, no collective",
+            "parallelism": "shards: gjd_partition (greedy LPT on padded pixels + 5 x file bytes), one shard per GPU, no collective",
             "l2": "inputs+outputs larger than L2 (every resident chunk holds > 1 GPixel)"}
 
 
@@ -341,12 +344,21 @@ def main():
 
     # ---- the rank's images --------------------------------------------------------------------------
     base, paths, gids = load_workload(args.config, args.images)
-    imbalance, loads = 0.0, None
+    shards = None
     if args.config == "c5":
-        part_of, load, weight = gjd.partition([base[g] for g in gids], world)     # every rank computes the same partition
+        files = [base[g] for g in gids]
+        # every rank computes the same partition: greedy LPT on padded pixels + a term for the scan bytes
+        part_of, load, cost = gjd.partition(files, world, gjd.PARTITION_BYTE_WEIGHT)
         ids = [gids[i] for i in np.nonzero(part_of == rank)[0]]
-        loads = [int(x) for x in load]
-        imbalance = float(max(loads) / (sum(loads) / world) - 1.0)
+        nbytes = np.array([len(f) for f in files], np.uint64)
+        pixels = np.where(cost > 0, cost - np.uint64(gjd.PARTITION_BYTE_WEIGHT) * nbytes, 0).astype(np.uint64)
+        spread = lambda v: round(float(max(v) / (sum(v) / world) - 1.0), 6)
+        per_px = [int(pixels[part_of == r].sum()) for r in range(world)]
+        per_by = [int(nbytes[part_of == r].sum()) for r in range(world)]
+        shards = {"weight": "padded pixels + %d x file bytes" % gjd.PARTITION_BYTE_WEIGHT,
+                  "padded_pixels_per_rank": per_px, "file_bytes_per_rank": per_by,
+                  "imbalance": spread([int(x) for x in load]),
+                  "imbalance_pixels": spread(per_px), "imbalance_bytes": spread(per_by)}
     else:
         ids = gids
     n_local = len(ids)
@@ -380,19 +392,37 @@ def main():
     wall = 0.0
     barrier()
     t0 = time.time()
-    for ci, chunk in enumerate(chunks):
+    trace = os.environ.get("GJD_BENCH_TRACE") == "1"
+    lockstep = os.environ.get("GJD_BENCH_LOCKSTEP", "1") == "1" and dist is not None
+    rounds = len(chunks)
+    if lockstep:      # ranks may hold different numbers of chunks: all of them make the same number of barrier calls
+        r_ = torch.tensor([rounds], device="cuda")
+        dist.all_reduce(r_, op=dist.ReduceOp.MAX)
+        rounds = int(r_.item())
+    for ci in range(rounds):
+        if ci >= len(chunks):
+            barrier()
+            continue
+        chunk = chunks[ci]
         batch = dec.prepare([base[ids[p]] for p in chunk])
         for _ in range(max(args.warmup, 3) if ci == 0 else 1):
             batch.run()
             assert batch.sync() == 0, "device reported a corrupt image"
-        if ci == 0:
+        if ci == 0 or lockstep:
+            # every rank times chunk ci at the same time: the host work between chunks (parity checks against the
+            # oracle, header parsing of the next chunk) of one rank otherwise runs beside another rank's timed launches
             barrier()
+        if ci == 0:
             t0 = time.time()
         w0 = time.perf_counter()
         for _ in range(args.steps):
             batch.run()
             batch.sync()
-            stage += np.array(dec.stage_times())
+            st = np.array(dec.stage_times())
+            stage += st
+            if trace:
+                print("trace rank %d chunk %d: before_sync %.3f sync %.3f write %.3f transform %.3f pipeline %.3f ms"
+                      % (rank, ci, st[3] - st[0] - st[1] - st[2], st[0], st[1], st[2], st[3]), file=sys.stderr, flush=True)
         torch.cuda.synchronize()
         wall += time.perf_counter() - w0
         info = batch.info()
@@ -469,6 +499,16 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(s, op=dist.ReduceOp.SUM)
     dev_ms_max, e2e_s_max, wall_max, dout_s_max = (float(x) for x in t.cpu())
+    # what each rank saw (a shard that lags shows here, not in the maxima): ms per step and stage, scan bytes, chunks, clock
+    mine = torch.tensor([dev_ms / args.steps, stage[0] / args.steps, stage[1] / args.steps, stage[2] / args.steps,
+                         info_sum["scan_bytes"], len(chunks), (clocks or {}).get("sm_mhz") or 0.0, e2e_s / e2e_steps * 1e3],
+                        dtype=torch.float64, device="cuda")
+    per_rank = [torch.zeros_like(mine) for _ in range(world)]
+    if dist:
+        dist.all_gather(per_rank, mine)
+    else:
+        per_rank = [mine]
+    per_rank = [[round(float(x), 3) for x in r.cpu()] for r in per_rank]
     total_pixels, h2d, d2h, chk_v, chk_e, chk_d, launches, n_total, scan_total, subs_total = (int(x) for x in s.cpu())
     value = total_pixels * args.steps / (dev_ms_max * 1e-3) / 1e6
     e2e_value = total_pixels * e2e_steps / e2e_s_max / 1e6
@@ -513,8 +553,11 @@ def main():
             "gpu_launches": launches, "host_cores": os.cpu_count(), "host_threads_per_rank": int(os.environ.get("GJD_HOST_THREADS", os.cpu_count() or 1)),
             "clocks": clocks,
         }
-        if loads is not None:
-            line["shards"] = {"padded_pixels_per_rank": loads, "imbalance": round(imbalance, 6)}
+        if world > 1:
+            line["per_rank"] = {"columns": ["ms_per_step", "entropy_sync_ms", "entropy_write_ms", "transform_ms", "scan_bytes",
+                                            "resident_chunks", "sm_mhz", "e2e_ms_per_step"], "rows": per_rank}
+        if shards is not None:
+            line["shards"] = shards
         if world == 1 and not args.no_cpu_baseline:
             cb, _ = cpu_reference(float(os.environ.get("GJD_CPU_BASELINE_SECONDS", "12")), base, paths, args.config)
             line["cpu_baseline"] = cb

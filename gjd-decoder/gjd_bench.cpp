@@ -6,7 +6,7 @@
  * Mirrors cuda-decoder/benchmark_thoughput/benchmark.cu (getAllImages :14-22, batches of 3000 :30,
  * 10 iterations :129, only the device work timed :61-70, images/s and MB/s of compressed file bytes
  * :95-111) without Google Benchmark, and adds what the reference's driver lacks:
- *   --gpus N  the directory is sharded over N devices with gjd_partition (greedy LPT on padded pixels),
+ *   --gpus N  the directory is sharded over N devices with gjd_partition (greedy LPT on padded pixels + 5 x file bytes),
  *             one host thread + one gjd_ctx per device, no exchange between shards;
  *   --e2e     a second figure through gjd_decode_batch with host buffers (parse, unstuff, H2D, D2H timed);
  *   --tile    repeat the directory cyclically until a batch is full (the reference stops at the last file).
@@ -164,7 +164,7 @@ int main(int argc, char** argv) {
     const size_t total = tile ? std::max(paths.size(), (size_t)batch * (size_t)gpus) : paths.size();
     for (size_t i = 0; i < total; i++) work.push_back(&data[i % data.size()]);
 
-    /* shard by padded pixels: no exchange step between devices */
+    /* shard by padded pixels plus a term for the scan bytes: no exchange step between devices */
     std::vector<gjd_item> items(work.size());
     for (size_t i = 0; i < work.size(); i++) {
         memset(&items[i], 0, sizeof(gjd_item));
@@ -173,7 +173,7 @@ int main(int argc, char** argv) {
     }
     std::vector<uint64_t> weight(work.size()), load((size_t)gpus);
     std::vector<int32_t> part(work.size());
-    gjd_partition_weights(items.data(), (int32_t)items.size(), weight.data());
+    gjd_partition_costs(items.data(), (int32_t)items.size(), GJD_PARTITION_BYTE_WEIGHT, weight.data());
     gjd_partition(weight.data(), (int32_t)items.size(), gpus, part.data(), load.data());
     std::vector<std::vector<const std::vector<uint8_t>*>> shard((size_t)gpus);
     size_t rejected = 0;

@@ -272,3 +272,11 @@ extern "C" int gjd_partition_weights(const gjd_item* items, int32_t n, uint64_t*
     }
     return GJD_OK;
 }
+
+extern "C" int gjd_partition_costs(const gjd_item* items, int32_t n, uint32_t byte_weight, uint64_t* cost) {
+    const int rc = gjd_partition_weights(items, n, cost);
+    if (rc != GJD_OK) return rc;
+    for (int32_t i = 0; i < n; i++)
+        if (cost[i]) cost[i] += (uint64_t)byte_weight * (uint64_t)items[i].len;
+    return GJD_OK;
+}

@@ -15,6 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GJD_LIB") or os.path.join(_HERE, "build", "libgjd.so")   # GJD_LIB: A/B builds
 
 PLANAR, INTERLEAVED, INTERLEAVED_I16 = 0, 1, 2
+PARTITION_BYTE_WEIGHT = 5          # GJD_PARTITION_BYTE_WEIGHT (include/gjd.h)
 OK, E_ARG, E_CUDA, E_NOMEM, E_FORMAT, E_UNSUPPORTED, E_CORRUPT, E_NODEVICE, E_IO = 0, -1, -2, -3, -4, -5, -6, -7, -8
 
 
@@ -75,6 +76,7 @@ def lib():
     L.gjd_write_ppm.argtypes = [C.c_char_p, i32, i32, vp]
     L.gjd_partition.argtypes = [vp, i32, i32, vp, vp]
     L.gjd_partition_weights.argtypes = [C.POINTER(Item), i32, vp]
+    L.gjd_partition_costs.argtypes = [C.POINTER(Item), i32, C.c_uint32, vp]
     L.gjd_strerror.argtypes = [C.c_int]
     L.gjd_strerror.restype = C.c_char_p
     L.gjd_last_cuda_error.argtypes = [vp]
@@ -346,9 +348,11 @@ def write_ppm(path, rgb):
         raise GjdError(rc)
 
 
-def partition(files, parts):
+def partition(files, parts, byte_weight=0):
     """Greedy-LPT assignment of JPEG `bytes` objects to `parts` devices (gjd_partition over
-    gjd_partition_weights).  Returns (part_of int32[n], load uint64[parts], weight uint64[n])."""
+    gjd_partition_weights, or over gjd_partition_costs when byte_weight > 0: padded pixels +
+    byte_weight * compressed length).  Returns (part_of int32[n], load uint64[parts], weight uint64[n]);
+    load and weight are in the unit the partition balanced."""
     n = len(files)
     items = (Item * max(n, 1))()
     hold = []
@@ -360,7 +364,10 @@ def partition(files, parts):
     weight = np.zeros(max(n, 1), np.uint64)
     part_of = np.full(max(n, 1), -1, np.int32)
     load = np.zeros(parts, np.uint64)
-    rc = lib().gjd_partition_weights(items, n, weight.ctypes.data)
+    if byte_weight:
+        rc = lib().gjd_partition_costs(items, n, int(byte_weight), weight.ctypes.data)
+    else:
+        rc = lib().gjd_partition_weights(items, n, weight.ctypes.data)
     if rc == OK:
         rc = lib().gjd_partition(weight.ctypes.data, n, parts, part_of.ctypes.data, load.ctypes.data)
     if rc != OK:
@@ -368,7 +375,7 @@ def partition(files, parts):
     return part_of[:n], load, weight[:n]
 
 
-def shard_indices(files, rank, world):
+def shard_indices(files, rank, world, byte_weight=0):
     """Indices of the images rank `rank` of `world` decodes (every rank computes the same partition)."""
-    part_of, load, _ = partition(files, world)
+    part_of, load, _ = partition(files, world, byte_weight)
     return [int(i) for i in np.nonzero(part_of == rank)[0]], load

@@ -170,13 +170,22 @@ int  gjd_idct_blocks_static(int cuda_device, const int16_t* coef_zz, size_t nblo
  * longest-processing-time on the padded pixel count 8*ceil(W/8) * 8*ceil(H/8) (the unit both the
  * coefficient traffic and, roughly, the scan bits follow).  Deterministic: ties go to the lower image
  * index, then to the lower part.  part_of[i] receives the device of image i (or -1 when weight[i] is 0,
- * i.e. an image gjd_peek rejected); load[p] (may be NULL) the padded pixels assigned to part p.
+ * i.e. an image gjd_peek rejected); load[p] (may be NULL) the weight assigned to part p.  The weights are the
+ * caller's: gjd_partition_weights (padded pixels) or gjd_partition_costs (padded pixels + a byte term) below.
  * The reference has no multi-GPU path; this replaces "one batchDecodeKernel over everything"
  * (cuda-decoder/benchmark_thoughput/benchmark.cu:56-70) by one such launch per device.  There is no
  * exchange step between shards, hence no collective. */
 int  gjd_partition(const uint64_t* weight, int32_t n, int32_t parts, int32_t* part_of, uint64_t* load);
 /* Convenience over gjd_peek: weight[i] = padded pixel count of items[i] (0 if the header is unusable). */
 int  gjd_partition_weights(const gjd_item* items, int32_t n, uint64_t* weight);
+/* The same with a term for the compressed size: cost[i] = padded pixels + byte_weight * items[i].len (0 if the
+ * header is unusable).  The entropy stages follow the scan bytes and the IDCT/colour stage the padded pixels, so a
+ * set that mixes qualities balances pixels alone and still leaves one device with more bytes (24000 mixed files
+ * over 4 parts: bytes max/mean 1.165 with byte_weight 0, 1.000 with any byte_weight from 3 to 8).  The measured
+ * ratio of the two rates on B200 is GJD_PARTITION_BYTE_WEIGHT padded pixels per scan byte.
+ * No counterpart in the reference (no multi-GPU path). */
+#define GJD_PARTITION_BYTE_WEIGHT 5u
+int  gjd_partition_costs(const gjd_item* items, int32_t n, uint32_t byte_weight, uint64_t* cost);
 
 /* Pinned host memory helpers (callers that want full-speed H2D/D2H). */
 void* gjd_host_alloc(size_t bytes);

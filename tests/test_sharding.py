@@ -48,6 +48,31 @@ def test_partition_weights_from_headers(golden):
     assert int(load.sum()) == int(weight.sum())
 
 
+
+def test_partition_costs_add_the_byte_term(golden):
+    """gjd_partition_costs = padded pixels + byte_weight * file length, 0 for rejected headers; on a set whose
+    bytes per pixel vary (two qualities of one size) the byte term is what balances the scan bytes."""
+    import gjd
+    names = sorted(golden)
+    files = [golden[n] for n in names] + [b"\xff\xd8\xff\xd9", b""]
+    _, _, weight = gjd.partition(files, 2)
+    part_of, load, cost = gjd.partition(files, 2, gjd.PARTITION_BYTE_WEIGHT)
+    lens = np.array([len(f) for f in files], np.uint64)
+    expect = np.where(weight > 0, weight + np.uint64(gjd.PARTITION_BYTE_WEIGHT) * lens, 0).astype(np.uint64)
+    assert np.array_equal(cost, expect)
+    assert cost[-1] == 0 and cost[-2] == 0 and part_of[-1] == -1
+    assert int(load.sum()) == int(cost.sum())
+    L = gjd.lib()
+    assert L.gjd_partition_costs(None, 1, 5, None) == gjd.E_ARG and L.gjd_partition_costs(None, 0, 5, None) == 0
+    # light and heavy files of one size, the heavy ones first in every tie: pixels alone send them all one way
+    small, big = golden["synth/s10_1x1_q90_o0"], golden["synth/s10_1x1_q90_o0"] + bytes(4096)
+    mixed = [big, small] * 8
+    by_px, _, _ = gjd.partition(mixed, 2)
+    by_cost, _, _ = gjd.partition(mixed, 2, gjd.PARTITION_BYTE_WEIGHT)
+    spread = lambda po: abs(sum(len(f) for f, p in zip(mixed, po) if p == 0) - sum(len(f) for f, p in zip(mixed, po) if p == 1))
+    assert spread(by_cost) == 0 and spread(by_px) > 0
+
+
 _WORKER = r'''
 import hashlib, os, sys
 sys.path.insert(0, os.path.join(%(root)r, "tests"))
