@@ -84,7 +84,7 @@ dist.init_process_group("gloo", rank=rank, world_size=world)
 g = conftest.golden_files()
 names = sorted(g)
 files = [g[n] for n in names]
-mine, load = gjd.shard_indices(files, rank, world)
+mine, load = gjd.shard_indices(files, rank, world, gjd.PARTITION_BYTE_WEIGHT)      # the weights bench.py --config c5 uses
 hs = conftest.HostSim()
 res = {}
 for i in mine:
